@@ -1,0 +1,141 @@
+"""ctypes access to the CHECKERS: oracle/liboracle.so (our CPU restatement) and, when it was built in
+the build container, oracle/_ref/libreflens.so (the reference's own lens/RNG code). Test-only."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+sys.path.insert(0, ROOT)
+
+f32 = np.float32
+c_f = C.c_float
+FP = C.POINTER(C.c_float)
+IP = C.POINTER(C.c_int)
+UP = C.POINTER(C.c_uint32)
+
+
+def fp(a):
+    return a.ctypes.data_as(FP)
+
+
+def ip(a):
+    return a.ctypes.data_as(IP)
+
+
+def build_oracle():
+    so = os.path.join(ORACLE_DIR, "liboracle.so")
+    srcs = [os.path.join(ORACLE_DIR, f) for f in os.listdir(ORACLE_DIR) if f.startswith("oracle") and f.endswith((".cpp", ".h"))]
+    if not os.path.exists(so) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs):
+        subprocess.check_call(["make", "-C", ORACLE_DIR, "port"], stdout=subprocess.DEVNULL)
+    return so
+
+
+_ORC = None
+_REF = None
+
+
+def oracle():
+    global _ORC
+    if _ORC is None:
+        L = C.CDLL(build_oracle())
+        L.orc_tea_float32.restype = c_f
+        L.orc_material_ior.restype = c_f
+        L.orc_cam_from_prescription.restype = C.c_void_p
+        L.orc_cam_from_interfaces.restype = C.c_void_p
+        L.orc_cam_focus_delta.restype = c_f
+        for n in ("orc_cam_destroy", "orc_cam_num_interfaces", "orc_cam_focus_delta", "orc_cam_sample_to_film",
+                  "orc_cam_film_to_sample", "orc_cam_interface", "orc_cam_sample_ray", "orc_cam_trace"):
+            getattr(L, n).argtypes = None
+        _ORC = L
+    return _ORC
+
+
+def ref():
+    """The reference's own code (None on the GPU box if oracle/_ref was not shipped)."""
+    global _REF
+    if _REF is None:
+        so = os.path.join(ORACLE_DIR, "_ref", "libreflens.so")
+        if not os.path.exists(so):
+            if os.path.isdir("/root/reference"):
+                subprocess.check_call(["make", "-C", ORACLE_DIR, "ref"], stdout=subprocess.DEVNULL)
+            else:
+                return None
+        L = C.CDLL(so)
+        L.ref_tea_float32.restype = c_f
+        L.ref_material_ior.restype = c_f
+        L.ref_cam_create.restype = C.c_void_p
+        L.ref_cam_film_z.restype = c_f
+        _REF = L
+    return _REF
+
+
+EYE = np.eye(4, dtype=f32)
+
+
+class FilmSpec:
+    def __init__(self, width=256, height=256, crop=None, diagonal_mm=35.0):
+        self.width, self.height = width, height
+        self.crop = np.array(crop if crop else [width, height, 0, 0], np.int32)
+        self.diagonal_mm = diagonal_mm
+
+
+def orc_camera(design, film: FilmSpec, to_world=EYE, near=1e-2, far=1e4, object_distance=6.0):
+    """design: lens_designs.Prescription | InterfaceList -> opaque oracle camera handle."""
+    from importlib import import_module
+    L = oracle()
+    tw = np.ascontiguousarray(to_world, f32)
+    if hasattr(design, "rows"):
+        rows = np.ascontiguousarray(design.rows, f32)
+        return C.c_void_p(L.orc_cam_from_interfaces(
+            C.c_int(len(rows)), fp(rows), c_f(design.film_z), C.c_int(int(design.fine_focus)), c_f(object_distance),
+            C.c_int(film.width), C.c_int(film.height), ip(film.crop), c_f(film.diagonal_mm), fp(tw), c_f(near), c_f(far)))
+    p = design
+    return C.c_void_p(L.orc_cam_from_prescription(
+        C.c_int(len(p.kinds)), ip(p.kinds), fp(p.thickness), fp(p.radius), fp(p.semi_diameter), fp(p.kappa),
+        fp(np.ascontiguousarray(p.ai)), fp(np.ascontiguousarray(p.materials)), c_f(p.scale), c_f(p.stop_ratio),
+        C.c_int(int(p.fine_focus)), c_f(object_distance), C.c_int(film.width), C.c_int(film.height), ip(film.crop),
+        c_f(film.diagonal_mm), fp(tw), c_f(near), c_f(far)))
+
+
+def ref_camera(name, film: FilmSpec, to_world=EYE, near=1e-2, far=1e4, props=None):
+    L = ref()
+    props = props or {}
+    names = (C.c_char_p * len(props))(*[k.encode() for k in props])
+    vals = (C.c_double * len(props))(*[float(v) for v in props.values()])
+    tw = np.ascontiguousarray(to_world, f32)
+    h = L.ref_cam_create(name.encode(), C.c_int(film.width), C.c_int(film.height), ip(film.crop),
+                         c_f(film.diagonal_mm), fp(tw), c_f(near), c_f(far), c_f(0.0), C.c_int(len(props)), names, vals)
+    return C.c_void_p(h) if h else None
+
+
+def cam_interfaces(L, prefix, h):
+    n = getattr(L, prefix + "_cam_num_interfaces")(h)
+    out = np.zeros((n, 16), f32)
+    for i in range(n):
+        getattr(L, prefix + "_cam_interface")(h, C.c_int(i), fp(out[i]))
+    return out
+
+
+def cam_sample_ray(L, prefix, h, pos, ap):
+    n = len(pos)
+    out = np.zeros((n, 10), f32)
+    getattr(L, prefix + "_cam_sample_ray")(h, C.c_int(n), fp(np.ascontiguousarray(pos, f32)),
+                                           fp(np.ascontiguousarray(ap, f32)), fp(out))
+    return out
+
+
+def cam_trace(L, prefix, h, od, from_world):
+    n = len(od)
+    out = np.zeros((n, 7), f32)
+    getattr(L, prefix + "_cam_trace")(h, C.c_int(int(from_world)), C.c_int(n), fp(np.ascontiguousarray(od, f32)), fp(out))
+    return out
+
+
+def bits(a):
+    return np.ascontiguousarray(a, f32).view(np.uint32)
