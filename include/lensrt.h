@@ -1,0 +1,99 @@
+/* lensrt.h — C ABI of liblensrt.so, the B200-native replacement for the render hot path of
+ * gitmon/mitsuba3-camera (realistic-lens Sensor::sample_ray -> path integrator -> ImageBlock::put, and
+ * its adjoint). Plain pointers and sizes only; no C++/torch types. File:line citations name the
+ * reference interface each entry point stands in for (paths relative to the reference checkout).
+ *
+ * Conventions
+ *  - every function returns 0 on success, a negative LRT_E* code otherwise; lrt_last_error() gives the
+ *    message of the calling thread's last failure. Nothing throws across the boundary.
+ *  - `*_dev` pointers are CUDA device pointers owned by the caller (e.g. torch tensors); `stream` is a
+ *    cudaStream_t passed as void* (NULL = default stream). Calls are asynchronous on that stream unless
+ *    the name ends in `_host` (host buffers in/out, copies and a stream sync inside the call).
+ *  - handles are opaque, created/destroyed by the library, usable from one host thread at a time.
+ *  - there is NO CPU fallback: every compute entry point fails with LRT_ENODEVICE without a CUDA device.
+ */
+#ifndef LENSRT_H
+#define LENSRT_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LRT_OK 0
+#define LRT_EINVAL (-1)
+#define LRT_ENODEVICE (-2)
+#define LRT_ECUDA (-3)
+#define LRT_ELENS (-4) /* lens construction failed (paraxial focus ray blocked: realisticlens.cpp:2132-2154) */
+
+typedef struct lrt_sensor lrt_sensor;
+typedef struct lrt_scene lrt_scene;
+
+const char *lrt_last_error(void);
+int lrt_version(void);
+/* number of kernels launched by this process so far (bench.py's gpu_launches) */
+uint64_t lrt_launch_count(void);
+int lrt_device_count(void);
+int lrt_set_device(int device);
+
+/* ---------------------------------------------------------------------------------------- film geometry
+ * Film::size/crop_size/crop_offset + the fork's physical size (include/mitsuba/render/film.h:193-198,
+ * src/render/film.cpp:46-48: `diagonal` in millimetres). */
+typedef struct lrt_film_geom {
+    int32_t width, height;               /* full film resolution */
+    int32_t crop_w, crop_h, crop_x, crop_y;
+    float diagonal_mm;                   /* default 35 */
+} lrt_film_geom;
+
+/* ------------------------------------------------------------------------------------------- sensors
+ * RealisticLensCamera constructor (src/sensors/realisticlens.cpp:832-933).
+ * Prescription tables are front (world) -> rear (film), millimetres, as build_lens_from_data takes them
+ * (:1568-1651): kinds (0 sphere, 1 plane, 2 aperture, 3 asphere), thickness, curvature radius,
+ * semi-diameter, conic constant, 7 even-asphere coefficients per surface; `mats7` has n+1 rows
+ * [model, p0..p5] (0: Cauchy A,B; 1: Sellmeier B1..3,C1..3), world side first. `scale` multiplies all
+ * lengths (exp2*: 35/1.57), `stop_ratio` the aperture semi-diameter (:850,:1596). `fine_focus` runs the
+ * thick-lens autofocus for `object_distance` metres (:902-908, :2107-2171).
+ * to_world16: row-major 4x4 camera-to-world (no scale allowed, :833). */
+int lrt_sensor_create_prescription(int32_t n, const int32_t *kinds, const float *thickness_mm,
+                                   const float *radius_mm, const float *semi_diameter_mm, const float *kappa,
+                                   const float *ai7, const float *mats7, float scale, float stop_ratio,
+                                   int32_t fine_focus, float object_distance, const lrt_film_geom *film,
+                                   const float *to_world16, float near_clip, float far_clip,
+                                   lrt_sensor **out);
+/* Same camera from ready-made interfaces (rear -> front, metres), rows of 16 floats:
+ * [kind, z, semi_diameter, R (sphere) | c,K,r_scale (asphere, unitless as :557-572), -, a0..a6 at [6..12],
+ *  ior_left (film side), ior_right, -]. Used for the parametric designs (:936-975, :1322-1370) and for
+ * optimisation loops that own the lens parameters. */
+int lrt_sensor_create_interfaces(int32_t n, const float *rows16, float film_z, int32_t fine_focus,
+                                 float object_distance, const lrt_film_geom *film, const float *to_world16,
+                                 float near_clip, float far_clip, lrt_sensor **out);
+/* PerspectiveCamera (src/sensors/perspective.cpp): x-axis field of view in degrees. */
+int lrt_sensor_create_perspective(float x_fov_deg, const lrt_film_geom *film, const float *to_world16,
+                                  float near_clip, float far_clip, lrt_sensor **out);
+void lrt_sensor_destroy(lrt_sensor *s);
+int lrt_sensor_num_interfaces(const lrt_sensor *s);
+/* current interface table (after autofocus), rows16 as above */
+int lrt_sensor_get_interfaces(const lrt_sensor *s, float *rows16);
+/* parameters_changed(): replace the interface table / pose without re-running the autofocus */
+int lrt_sensor_set_interfaces(lrt_sensor *s, int32_t n, const float *rows16);
+int lrt_sensor_set_to_world(lrt_sensor *s, const float *to_world16);
+int lrt_sensor_get_info(const lrt_sensor *s, float *sample_to_film16, float *focus_delta, float *film_z);
+
+/* Sensor::sample_ray (realisticlens.cpp:2209-2292) for n samples: pos2/ap2 = film and aperture samples in
+ * [0,1]^2; out10 = origin[3], direction[3], maxt, weight[3] (world space). */
+int lrt_sensor_sample_ray(const lrt_sensor *s, int64_t n, const float *pos2_dev, const float *ap2_dev,
+                          float *out10_dev, void *stream);
+int lrt_sensor_sample_ray_host(const lrt_sensor *s, int64_t n, const float *pos2, const float *ap2, float *out10);
+/* trace_ray_from_film / trace_ray_from_world (:1654-1683 / :1960-1984) in camera space:
+ * od6 = o[3], d[3]; out7 = o[3], d[3], active (1/0). */
+int lrt_sensor_trace_host(const lrt_sensor *s, int32_t from_world, int64_t n, const float *od6, float *out7);
+
+/* --------------------------------------------------------------------------------------------- sampler
+ * IndependentSampler over per-sample PCG32 streams (src/samplers/independent.cpp:88-97,
+ * src/render/sampler.cpp:115-134 JIT branch): out[i*ndraw + k] = k-th next_1d() of wavefront lane idx0+i. */
+int lrt_sampler_draw(uint32_t seed, uint32_t idx0, int64_t n, int32_t ndraw, float *out_dev, void *stream);
+int lrt_sampler_draw_host(uint32_t seed, uint32_t idx0, int64_t n, int32_t ndraw, float *out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

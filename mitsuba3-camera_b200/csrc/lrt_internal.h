@@ -1,0 +1,46 @@
+// lensrt — internal declarations shared by the translation units of liblensrt.so
+#pragma once
+#include "../../include/lensrt.h"
+#include "lrt_lens.cuh"
+#include <atomic>
+#include <string>
+#include <vector>
+
+namespace lrt {
+
+void set_error(const std::string &msg);
+int cuda_fail(cudaError_t e, const char *what);
+bool have_device();
+extern std::atomic<uint64_t> g_launches;
+
+#define LRT_CUDA(call)                                                            \
+    do {                                                                          \
+        cudaError_t e_ = (call);                                                  \
+        if (e_ != cudaSuccess) return lrt::cuda_fail(e_, #call);                  \
+    } while (0)
+#define LRT_REQUIRE(cond, msg)                                                    \
+    do {                                                                          \
+        if (!(cond)) { lrt::set_error(msg); return LRT_EINVAL; }                  \
+    } while (0)
+#define LRT_NEED_DEVICE()                                                         \
+    do {                                                                          \
+        if (!lrt::have_device()) {                                                \
+            lrt::set_error("no CUDA device: liblensrt has no CPU fallback");      \
+            return LRT_ENODEVICE;                                                 \
+        }                                                                         \
+    } while (0)
+#define LRT_LAUNCHED() (lrt::g_launches.fetch_add(1, std::memory_order_relaxed))
+
+}  // namespace lrt
+
+struct lrt_sensor {
+    lrt::LensSystem host;            // authoritative copy
+    lrt::LensSystem *dev = nullptr;  // lazily uploaded mirror (per current device)
+    bool dev_dirty = true;
+    lrt_film_geom film;
+    float focus_delta = 0.f;
+    float sample_to_film[16];
+    float film_to_sample[16];
+    float normalization = 0.f;
+    int upload();                    // host -> dev if dirty
+};

@@ -1,0 +1,428 @@
+// lensrt — sensors: host-side lens construction (prescription -> interface table, thick-lens autofocus)
+// and the unit-level sample_ray / sampler kernels behind include/lensrt.h.
+// Host arithmetic that decides interface positions is float32 and strict (this TU is compiled with
+// -Xcompiler -ffp-contract=off) because every later ray/lens comparison depends on those z's
+// (realisticlens.cpp:1568-1651, :2107-2171).
+#include "lrt_internal.h"
+#include "lrt_rng.cuh"
+#include <cstring>
+#include <cstdio>
+#include <cmath>
+
+namespace lrt {
+
+static thread_local std::string g_error;
+std::atomic<uint64_t> g_launches{0};
+
+void set_error(const std::string &msg) { g_error = msg; }
+int cuda_fail(cudaError_t e, const char *what) {
+    g_error = std::string(what) + ": " + cudaGetErrorString(e);
+    cudaGetLastError();
+    return LRT_ECUDA;
+}
+bool have_device() {
+    static int n = -1;
+    if (n < 0) { int c = 0; if (cudaGetDeviceCount(&c) != cudaSuccess) { c = 0; cudaGetLastError(); } n = c; }
+    return n > 0;
+}
+
+// ------------------------------------------------------------------ interface records
+static float powi(float x, int y) {   // dr::pow(x, int): square-and-multiply (drjit/math.h:977-992)
+    unsigned n = (unsigned) (y < 0 ? -y : y); float r = 1.f;
+    while (n) { if (n & 1) r *= x; x *= x; n >>= 1; }
+    return y >= 0 ? r : 1.f / r;
+}
+
+static float material_ior(const float *m, float wavelength) {   // realisticlens.cpp:226-240
+    float w2 = wavelength * wavelength;
+    if (m[0] == 0.f) return m[1] + m[2] / w2;
+    float ior = 1.f;
+    ior += m[1] * w2 / (w2 - m[4]);
+    ior += m[2] * w2 / (w2 - m[5]);
+    ior += m[3] * w2 / (w2 - m[6]);
+    return sqrtf(ior);
+}
+
+// fill every derived constant of a record from its defining parameters
+static void finish_record(LensIf &f) {
+    f.elem_r2 = f.elem_radius * f.elem_radius;
+    f.eta = f.ior_right / f.ior_left;
+    f.rcp_eta = 1.f / f.eta;
+    f.center_z = f.z + f.curv_radius;
+    f.curv_r2 = f.curv_radius * f.curv_radius;
+    f.convex = f.curv_radius > 0.f ? 1 : 0;
+    f.plane_param = -1.0f * f.z;
+    f.rcp_R = 1.f / f.elem_radius;
+    f.rcp_R2 = 1.f / (f.elem_radius * f.elem_radius);
+    f.c2 = f.c * f.c;
+    f.one_p_K = 1.f + f.K;
+    f.k1 = f.one_p_K * f.c2;
+    f.lim = f.K > -1.0f ? f.elem_radius * (1.f / (1.0f + f.K)) : INFINITY;
+    for (int i = 0; i < 7; ++i) f.gi[i] = (2.f * i + 4.f) * f.ai[i];
+}
+
+static LensIf blank(int kind, float z, float elem_radius, float il, float ir) {
+    LensIf f; memset(&f, 0, sizeof f);
+    f.kind = kind; f.z = z; f.elem_radius = elem_radius; f.ior_left = il; f.ior_right = ir;
+    return f;
+}
+
+static void offset_along_axis(LensIf &f, float delta) { f.z += delta; finish_record(f); }
+
+// 16-float row <-> record (layout documented in lensrt.h)
+static LensIf record_from_row(const float *r) {
+    int kind = (int) r[0];
+    LensIf f = blank(kind, r[1], r[2], r[13], r[14]);
+    if (kind == IF_SPHERE) f.curv_radius = r[3];
+    if (kind == IF_ASPHERE) { f.c = r[3]; f.K = r[4]; f.r_scale = r[5]; for (int k = 0; k < 7; ++k) f.ai[k] = r[6 + k]; }
+    if (kind == IF_APERTURE) f.ior_right = f.ior_left;
+    finish_record(f);
+    return f;
+}
+static void row_from_record(const LensIf &f, float *r) {
+    for (int k = 0; k < 16; ++k) r[k] = 0.f;
+    r[0] = (float) f.kind; r[1] = f.z; r[2] = f.elem_radius;
+    if (f.kind == IF_SPHERE) r[3] = f.curv_radius;
+    if (f.kind == IF_ASPHERE) { r[3] = f.c; r[4] = f.K; r[5] = f.r_scale; for (int k = 0; k < 7; ++k) r[6 + k] = f.ai[k]; }
+    r[13] = f.ior_left; r[14] = f.ior_right;
+}
+
+// ------------------------------------------------------------------ film <-> sample transforms
+// Film::get_physical_size (film.h:193-198) + film_to_crop_transform (sensor.h:305-342) and its inverse
+// (realisticlens.cpp:2190-2207). The inverse is assembled from the inverses of the four factors, the way
+// Transform::inverse() composes them, so the entries round like the reference's.
+static void setup_film(lrt_sensor &s) {
+    const lrt_film_geom &g = s.film;
+    float diag = 0.001f * g.diagonal_mm;
+    float aspect = (float) g.height / (float) g.width;
+    float x = sqrtf(diag * diag / (1.f + aspect * aspect));
+    float y = aspect * x;
+    float px = x / 2, py = y / 2;
+    float relx = (float) g.crop_w / (float) g.width, rely = (float) g.crop_h / (float) g.height;
+    float offx = (float) g.crop_x / (float) g.width, offy = (float) g.crop_y / (float) g.height;
+    float ax = 1.f / (1.f / relx), ay = 1.f / (1.f / rely);
+    float cx = 1.f / (0.5f / px), cy = 1.f / (0.5f / py);
+    float *m = s.sample_to_film;
+    for (int i = 0; i < 16; ++i) m[i] = (i % 5 == 0) ? 1.f : 0.f;
+    m[0] = ax * cx; m[5] = ay * cy;
+    m[3] = offx * cx + (-px); m[7] = offy * cy + (-py);
+    float *q = s.film_to_sample;
+    for (int i = 0; i < 16; ++i) q[i] = (i % 5 == 0) ? 1.f : 0.f;
+    float fx = (1.f / relx) * (0.5f / px), fy = (1.f / rely) * (0.5f / py);
+    q[0] = fx; q[5] = fy;
+    q[3] = fx * px + (1.f / relx) * (-offx); q[7] = fy * py + (1.f / rely) * (-offy);
+    float x0 = m[3], y0 = m[7], x1 = m[0] + m[3], y1 = m[5] + m[7];
+    s.normalization = 1.f / ((fmaxf(x0, x1) - fminf(x0, x1)) * (fmaxf(y0, y1) - fminf(y0, y1)));
+    s.host.s2f_m00 = m[0]; s.host.s2f_m03 = m[3]; s.host.s2f_m11 = m[5]; s.host.s2f_m13 = m[7];
+    s.host.persp_norm = s.normalization;
+}
+
+// ------------------------------------------------------------------ thick-lens autofocus (:2107-2171)
+static void cardinal_points(const LensRay &start, const LensRay &end, float &z_p, float &z_f) {
+    float t_focus = -end.o.x / end.d.x;
+    z_f = end.d.z * t_focus + end.o.z;
+    float t_plane = (start.o.x - end.o.x) / end.d.x;
+    z_p = end.d.z * t_plane + end.o.z;
+}
+static bool focus_thick_lens(const lrt_sensor &s, float half_x, float focus_distance, float &delta) {
+    const LensSystem &L = s.host;
+    float r = 0.001f * half_x;
+    LensRay obj; obj.o = strict::v3(r, 0.f, L.ifs[L.n - 1].z + 1.f); obj.d = strict::v3(0.f, 0.f, -1.f);
+    LensRay obj_end = obj;
+    if (!lens_trace_from_world(L.ifs, L.n, obj_end)) return false;
+    float obj_plane, obj_focus; cardinal_points(obj, obj_end, obj_plane, obj_focus);
+    float p_img = obj_plane, f_img = obj_plane - obj_focus;
+    LensRay img; img.o = strict::v3(r, 0.f, L.ifs[0].z - 1.f); img.d = strict::v3(0.f, 0.f, 1.f);
+    LensRay img_end = img;
+    if (!lens_trace_from_film(L.ifs, L.n, img_end)) return false;
+    float img_plane, img_focus; cardinal_points(img, img_end, img_plane, img_focus);
+    float p_obj = img_plane;
+    float tmp = fmaxf(focus_distance, 4.01f * f_img) - p_obj;
+    delta = 0.5f * (p_img - tmp + sqrtf((p_img + tmp) * (p_img + tmp) - 4 * f_img * (p_img + tmp)));
+    return true;
+}
+
+static int finish_sensor(lrt_sensor *s, bool fine_focus, float object_distance) {
+    LensSystem &L = s->host;
+    if (fine_focus) {
+        float aspect = (float) s->film.height / (float) s->film.width;
+        float diag = 0.001f * s->film.diagonal_mm;
+        float half_x = sqrtf(diag * diag / (1.f + aspect * aspect)) / 2;
+        float delta;
+        if (!focus_thick_lens(*s, half_x, object_distance, delta)) {
+            set_error("compute_thick_lens_approximation: paraxial ray was not transmitted through lens");
+            return LRT_ELENS;
+        }
+        s->focus_delta = delta;
+        for (int i = 0; i < L.n; ++i) offset_along_axis(L.ifs[i], std::isnan(delta) ? 0.0f : -delta);
+    }
+    L.rear_z = L.ifs[0].z; L.rear_radius = L.ifs[0].elem_radius;
+    s->dev_dirty = true;
+    return LRT_OK;
+}
+
+static void set_common(lrt_sensor *s, const lrt_film_geom *film, const float *tw, float near_clip, float far_clip) {
+    memset(&s->host, 0, sizeof s->host);
+    s->film = *film;
+    for (int i = 0; i < 12; ++i) s->host.to_world[i] = tw[i];
+    s->host.near_clip = near_clip; s->host.far_clip = far_clip;
+    setup_film(*s);
+}
+
+}  // namespace lrt
+
+int lrt_sensor::upload() {
+    if (!dev) LRT_CUDA(cudaMalloc(&dev, sizeof(lrt::LensSystem)));
+    if (dev_dirty) { LRT_CUDA(cudaMemcpy(dev, &host, sizeof(lrt::LensSystem), cudaMemcpyHostToDevice)); dev_dirty = false; }
+    return LRT_OK;
+}
+
+// ================================================================================ kernels
+namespace lrt {
+
+// perspective pinhole (src/sensors/perspective.cpp sample_ray): near_p = s2c * (u,v,0), d = normalize(near_p)
+LRT_HD CameraRay persp_sample_ray(const LensSystem &L, float u, float v) {
+    const float *m = L.persp_s2c;
+    float x = m[0] * u + m[1] * v + m[3], y = m[4] * u + m[5] * v + m[7], z = m[8] * u + m[9] * v + m[11],
+          w = m[12] * u + m[13] * v + m[15];
+    float iw = 1.f / w;
+    float3 d = normalize(make_float3(x * iw, y * iw, z * iw));
+    const float *t = L.to_world;
+    float3 o = make_float3(t[3], t[7], t[11]);
+    float3 dw = make_float3(t[0] * d.x + t[1] * d.y + t[2] * d.z, t[4] * d.x + t[5] * d.y + t[6] * d.z,
+                            t[8] * d.x + t[9] * d.y + t[10] * d.z);
+    float inv_z = 1.f / d.z;
+    float near_t = L.near_clip * inv_z, far_t = L.far_clip * inv_z;
+    CameraRay r;
+    r.o = o + dw * near_t; r.d = dw; r.maxt = far_t - near_t; r.weight = 1.f; r.active = true; r.d_local = d;
+    return r;
+}
+
+LRT_HD CameraRay sensor_sample_ray(const LensSystem &L, const LensIf *ifs, float u, float v, float a, float b) {
+    return L.kind == 0 ? lens_sample_ray(L, ifs, u, v, a, b) : persp_sample_ray(L, u, v);
+}
+
+__global__ void __launch_bounds__(256) k_sample_ray(const LensSystem *__restrict__ Lg, int64_t n,
+                                                     const float2 *__restrict__ pos, const float2 *__restrict__ ap,
+                                                     float *__restrict__ out10) {
+    __shared__ LensSystem L;
+    {   // stage the lens table into shared memory (16-byte words)
+        const uint4 *src = reinterpret_cast<const uint4 *>(Lg);
+        uint4 *dst = reinterpret_cast<uint4 *>(&L);
+        for (int i = threadIdx.x; i < (int) (sizeof(LensSystem) / 16); i += blockDim.x) dst[i] = src[i];
+    }
+    __syncthreads();
+    for (int64_t i = blockIdx.x * (int64_t) blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) {
+        float2 p = pos[i], q = ap[i];
+        CameraRay r = sensor_sample_ray(L, L.ifs, p.x, p.y, q.x, q.y);
+        float *o = out10 + 10 * i;
+        o[0] = r.o.x; o[1] = r.o.y; o[2] = r.o.z; o[3] = r.d.x; o[4] = r.d.y; o[5] = r.d.z;
+        o[6] = r.maxt; o[7] = o[8] = o[9] = r.weight;
+    }
+}
+
+__global__ void __launch_bounds__(256) k_sampler_draw(uint32_t seed, uint32_t idx0, int64_t n, int ndraw, float *__restrict__ out) {
+    for (int64_t i = blockIdx.x * (int64_t) blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) {
+        Pcg32 rng; rng.seed_sample(seed, idx0 + (uint32_t) i);
+        for (int k = 0; k < ndraw; ++k) out[i * ndraw + k] = rng.next_f32();
+    }
+}
+
+static int grid_for(int64_t n, int block) {
+    int64_t g = (n + block - 1) / block;
+    int64_t cap = 148 * 16;
+    return (int) (g < 1 ? 1 : (g > cap ? cap : g));
+}
+
+}  // namespace lrt
+
+using namespace lrt;
+
+// ================================================================================ C ABI
+extern "C" {
+
+const char *lrt_last_error(void) { return g_error.c_str(); }
+int lrt_version(void) { return 100; }
+uint64_t lrt_launch_count(void) { return g_launches.load(); }
+int lrt_device_count(void) { int c = 0; if (cudaGetDeviceCount(&c) != cudaSuccess) { cudaGetLastError(); return 0; } return c; }
+int lrt_set_device(int device) { LRT_NEED_DEVICE(); LRT_CUDA(cudaSetDevice(device)); return LRT_OK; }
+
+int lrt_sensor_create_prescription(int32_t n, const int32_t *kinds, const float *thick, const float *curv,
+                                   const float *elemr, const float *kappa, const float *ai7, const float *mats7,
+                                   float scale, float stop_ratio, int32_t fine_focus, float object_distance,
+                                   const lrt_film_geom *film, const float *tw, float near_clip, float far_clip,
+                                   lrt_sensor **out) {
+    LRT_REQUIRE(n > 0 && n <= kMaxInterfaces, "lens must have 1..32 interfaces");
+    LRT_REQUIRE(kinds && thick && curv && elemr && kappa && ai7 && mats7 && film && tw && out, "null argument");
+    lrt_sensor *s = new lrt_sensor();
+    set_common(s, film, tw, near_clip, far_clip);
+    LensSystem &L = s->host;
+    // build_lens_from_data (:1568-1651): walk the table rear -> front accumulating z
+    float z_pos = 0.f;
+    for (int i = n - 1; i >= 0; --i) {
+        float elem_radius = elemr[i];
+        z_pos += thick[i];
+        float il = material_ior(mats7 + 7 * (i + 1), 0.5893f), ir = material_ior(mats7 + 7 * i, 0.5893f);
+        LensIf f;
+        switch (kinds[i]) {
+            case IF_APERTURE: f = blank(IF_APERTURE, 0.001f * scale * z_pos, 0.001f * scale * elem_radius * stop_ratio, il, il); break;
+            case IF_PLANE: f = blank(IF_PLANE, 0.001f * scale * z_pos, 0.001f * scale * elem_radius, il, ir); break;
+            case IF_ASPHERE: {
+                f = blank(IF_ASPHERE, 0.001f * scale * z_pos, 0.001f * scale * elem_radius, il, ir);
+                // AsphericalLens ctor (:557-572): coefficients to unitless radius r/R
+                f.K = kappa[i];
+                f.r_scale = 1.0f / 0.001f * f.elem_radius;
+                f.c = f.r_scale * (1.f / (scale * curv[i]));
+                for (int j = 0; j < 7; ++j) f.ai[j] = powi(f.r_scale, 2 * j + 3) * (ai7[7 * i + j] / powi(scale, 2 * j + 3));
+                break;
+            }
+            default: f = blank(IF_SPHERE, 0.001f * scale * z_pos, 0.001f * scale * elem_radius, il, ir);
+                     f.curv_radius = -0.001f * scale * curv[i];
+        }
+        finish_record(f);
+        L.ifs[L.n++] = f;
+    }
+    int rc = finish_sensor(s, fine_focus != 0, object_distance);
+    if (rc != LRT_OK) { delete s; return rc; }
+    *out = s;
+    return LRT_OK;
+}
+
+int lrt_sensor_create_interfaces(int32_t n, const float *rows16, float film_z, int32_t fine_focus, float object_distance,
+                                 const lrt_film_geom *film, const float *tw, float near_clip, float far_clip,
+                                 lrt_sensor **out) {
+    LRT_REQUIRE(n > 0 && n <= kMaxInterfaces, "lens must have 1..32 interfaces");
+    LRT_REQUIRE(rows16 && film && tw && out, "null argument");
+    lrt_sensor *s = new lrt_sensor();
+    set_common(s, film, tw, near_clip, far_clip);
+    for (int i = 0; i < n; ++i) s->host.ifs[i] = record_from_row(rows16 + 16 * i);
+    s->host.n = n; s->host.film_z = film_z;
+    int rc = finish_sensor(s, fine_focus != 0, object_distance);
+    if (rc != LRT_OK) { delete s; return rc; }
+    *out = s;
+    return LRT_OK;
+}
+
+int lrt_sensor_create_perspective(float x_fov_deg, const lrt_film_geom *film, const float *tw, float near_clip,
+                                  float far_clip, lrt_sensor **out) {
+    LRT_REQUIRE(film && tw && out, "null argument");
+    lrt_sensor *s = new lrt_sensor();
+    set_common(s, film, tw, near_clip, far_clip);
+    s->host.kind = 1;
+    // inverse of perspective_projection (sensor.h:262-303): S(1/rel) T(-off) S(-.5,-.5a,1) T(-1,-1/a,0) P(fov)
+    double W = film->width, H = film->height, aspect = W / H;
+    double relx = film->crop_w / W, rely = film->crop_h / H, offx = film->crop_x / W, offy = film->crop_y / H;
+    double recip = 1.0 / ((double) far_clip - (double) near_clip);
+    double tanh_ = std::tan(0.5 * (double) x_fov_deg * 3.14159265358979323846 / 180.0);
+    // sample (u,v,0) -> ndc: x_c = (u*relx + offx) / -0.5 + 1 ; y_c = (v*rely + offy)/(-0.5*aspect) + 1/aspect
+    // P^-1 at depth-buffer value 0 (near plane): camera = (x_c*tan, y_c*tan, 1) * near
+    double n_ = near_clip;
+    float *m = s->host.persp_s2c;
+    for (int i = 0; i < 16; ++i) m[i] = 0.f;
+    m[0] = (float) (relx / -0.5 * tanh_ * n_); m[3] = (float) ((offx / -0.5 + 1.0) * tanh_ * n_);
+    m[5] = (float) (rely / (-0.5 * aspect) * tanh_ * n_); m[7] = (float) ((offy / (-0.5 * aspect) + 1.0 / aspect) * tanh_ * n_);
+    m[11] = (float) n_; m[15] = 1.f;
+    (void) recip;
+    // image-plane normalisation (perspective.cpp update_camera_transforms): rect at z = 1
+    double x0 = (offx / -0.5 + 1.0) * tanh_, x1 = ((relx + offx) / -0.5 + 1.0) * tanh_;
+    double y0 = (offy / (-0.5 * aspect) + 1.0 / aspect) * tanh_, y1 = ((rely + offy) / (-0.5 * aspect) + 1.0 / aspect) * tanh_;
+    s->host.persp_norm = (float) (1.0 / (std::fabs(x1 - x0) * std::fabs(y1 - y0)));
+    s->dev_dirty = true;
+    *out = s;
+    return LRT_OK;
+}
+
+void lrt_sensor_destroy(lrt_sensor *s) {
+    if (!s) return;
+    if (s->dev) cudaFree(s->dev);
+    delete s;
+}
+int lrt_sensor_num_interfaces(const lrt_sensor *s) { return s ? s->host.n : 0; }
+int lrt_sensor_get_interfaces(const lrt_sensor *s, float *rows16) {
+    LRT_REQUIRE(s && rows16, "null argument");
+    for (int i = 0; i < s->host.n; ++i) row_from_record(s->host.ifs[i], rows16 + 16 * i);
+    return LRT_OK;
+}
+int lrt_sensor_set_interfaces(lrt_sensor *s, int32_t n, const float *rows16) {
+    LRT_REQUIRE(s && rows16 && n > 0 && n <= kMaxInterfaces, "bad argument");
+    for (int i = 0; i < n; ++i) s->host.ifs[i] = record_from_row(rows16 + 16 * i);
+    s->host.n = n; s->host.rear_z = s->host.ifs[0].z; s->host.rear_radius = s->host.ifs[0].elem_radius;
+    s->dev_dirty = true;
+    return LRT_OK;
+}
+int lrt_sensor_set_to_world(lrt_sensor *s, const float *tw) {
+    LRT_REQUIRE(s && tw, "null argument");
+    for (int i = 0; i < 12; ++i) s->host.to_world[i] = tw[i];
+    s->dev_dirty = true;
+    return LRT_OK;
+}
+int lrt_sensor_get_info(const lrt_sensor *s, float *s2f16, float *focus_delta, float *film_z) {
+    LRT_REQUIRE(s, "null argument");
+    if (s2f16) memcpy(s2f16, s->sample_to_film, 64);
+    if (focus_delta) *focus_delta = s->focus_delta;
+    if (film_z) *film_z = s->host.film_z;
+    return LRT_OK;
+}
+
+int lrt_sensor_sample_ray(const lrt_sensor *s_, int64_t n, const float *pos2, const float *ap2, float *out10, void *stream) {
+    LRT_NEED_DEVICE();
+    LRT_REQUIRE(s_ && pos2 && ap2 && out10 && n >= 0, "bad argument");
+    if (n == 0) return LRT_OK;
+    lrt_sensor *s = const_cast<lrt_sensor *>(s_);
+    int rc = s->upload(); if (rc) return rc;
+    k_sample_ray<<<grid_for(n, 256), 256, 0, (cudaStream_t) stream>>>(s->dev, n, (const float2 *) pos2, (const float2 *) ap2, out10);
+    LRT_LAUNCHED();
+    LRT_CUDA(cudaGetLastError());
+    return LRT_OK;
+}
+
+int lrt_sensor_sample_ray_host(const lrt_sensor *s, int64_t n, const float *pos2, const float *ap2, float *out10) {
+    LRT_NEED_DEVICE();
+    LRT_REQUIRE(s && pos2 && ap2 && out10 && n >= 0, "bad argument");
+    if (n == 0) return LRT_OK;
+    float *d = nullptr;
+    LRT_CUDA(cudaMalloc(&d, (size_t) n * 14 * sizeof(float)));
+    cudaMemcpy(d, pos2, (size_t) n * 8, cudaMemcpyHostToDevice);
+    cudaMemcpy(d + 2 * n, ap2, (size_t) n * 8, cudaMemcpyHostToDevice);
+    int rc = lrt_sensor_sample_ray(s, n, d, d + 2 * n, d + 4 * n, nullptr);
+    if (rc == LRT_OK) { cudaError_t e = cudaMemcpy(out10, d + 4 * n, (size_t) n * 40, cudaMemcpyDeviceToHost); if (e != cudaSuccess) rc = cuda_fail(e, "copy back"); }
+    cudaFree(d);
+    return rc;
+}
+
+// host-side trace through the interface table (same LRT_HD code as the kernels; used by the autofocus and
+// exposed for the lens-design front end's chief-ray queries: design_problem.py:415-417 uses prb_basic.trace)
+int lrt_sensor_trace_host(const lrt_sensor *s, int32_t from_world, int64_t n, const float *od6, float *out7) {
+    LRT_REQUIRE(s && od6 && out7 && n >= 0 && s->host.kind == 0, "bad argument");
+    for (int64_t i = 0; i < n; ++i) {
+        const float *r = od6 + 6 * i;
+        LensRay ray; ray.o = strict::v3(r[0], r[1], r[2]); ray.d = strict::v3(r[3], r[4], r[5]);
+        bool a = from_world ? lens_trace_from_world(s->host.ifs, s->host.n, ray) : lens_trace_from_film(s->host.ifs, s->host.n, ray);
+        float *o = out7 + 7 * i;
+        o[0] = ray.o.x; o[1] = ray.o.y; o[2] = ray.o.z; o[3] = ray.d.x; o[4] = ray.d.y; o[5] = ray.d.z; o[6] = a ? 1.f : 0.f;
+    }
+    return LRT_OK;
+}
+
+int lrt_sampler_draw(uint32_t seed, uint32_t idx0, int64_t n, int32_t ndraw, float *out, void *stream) {
+    LRT_NEED_DEVICE();
+    LRT_REQUIRE(out && n >= 0 && ndraw > 0, "bad argument");
+    if (n == 0) return LRT_OK;
+    k_sampler_draw<<<grid_for(n, 256), 256, 0, (cudaStream_t) stream>>>(seed, idx0, n, ndraw, out);
+    LRT_LAUNCHED();
+    LRT_CUDA(cudaGetLastError());
+    return LRT_OK;
+}
+int lrt_sampler_draw_host(uint32_t seed, uint32_t idx0, int64_t n, int32_t ndraw, float *out) {
+    LRT_NEED_DEVICE();
+    LRT_REQUIRE(out && n >= 0 && ndraw > 0, "bad argument");
+    if (n == 0) return LRT_OK;
+    float *d = nullptr;
+    LRT_CUDA(cudaMalloc(&d, (size_t) n * ndraw * sizeof(float)));
+    int rc = lrt_sampler_draw(seed, idx0, n, ndraw, d, nullptr);
+    if (rc == LRT_OK) { cudaError_t e = cudaMemcpy(out, d, (size_t) n * ndraw * 4, cudaMemcpyDeviceToHost); if (e != cudaSuccess) rc = cuda_fail(e, "copy back"); }
+    cudaFree(d);
+    return rc;
+}
+
+}  // extern "C"

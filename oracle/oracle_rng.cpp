@@ -52,10 +52,10 @@ extern "C" {
 void orc_tea32(uint32_t v0, uint32_t v1, int rounds, uint32_t *out) {
     orc::tea32(v0, v1, rounds, out[0], out[1]);
 }
-// include/mitsuba/core/random.h:107-111 sample_tea_float32
+// include/mitsuba/core/random.h:136-140 sample_tea_float32 (uses the SECOND word)
 float orc_tea_float32(uint32_t v0, uint32_t v1, int rounds) {
     uint32_t a, b; orc::tea32(v0, v1, rounds, a, b);
-    union { uint32_t u; float f; } x; x.u = (a >> 9) | 0x3f800000u;
+    union { uint32_t u; float f; } x; x.u = (b >> 9) | 0x3f800000u;
     return x.f - 1.f;
 }
 void orc_pcg32_u32(uint64_t initstate, uint64_t initseq, int n, uint32_t *out) {

@@ -40,6 +40,18 @@ _ORC = None
 _REF = None
 
 
+def load_lens_designs():
+    """mitsuba3-camera_b200/lens_designs.py as a standalone module (pure numpy; no CUDA library needed)."""
+    import importlib.util
+    name = "_lrt_lens_designs"
+    if name not in sys.modules:
+        spec = importlib.util.spec_from_file_location(name, os.path.join(ROOT, "mitsuba3-camera_b200", "lens_designs.py"))
+        mod = importlib.util.module_from_spec(spec)
+        sys.modules[name] = mod
+        spec.loader.exec_module(mod)
+    return sys.modules[name]
+
+
 def oracle():
     global _ORC
     if _ORC is None:
