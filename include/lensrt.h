@@ -93,6 +93,28 @@ int lrt_sensor_trace_host(const lrt_sensor *s, int32_t from_world, int64_t n, co
 int lrt_sampler_draw(uint32_t seed, uint32_t idx0, int64_t n, int32_t ndraw, float *out_dev, void *stream);
 int lrt_sampler_draw_host(uint32_t seed, uint32_t idx0, int64_t n, int32_t ndraw, float *out);
 
+/* ------------------------------------------------------------------------------------------------ film
+ * ImageBlock (include/mitsuba/render/imageblock.h:52-72 ctor arguments) + reconstruction filter. */
+typedef struct lrt_film_desc {
+    int32_t size_x, size_y;   /* block size = film crop size */
+    int32_t off_x, off_y;     /* block offset = film crop offset */
+    int32_t border;           /* border pixels on each side (0 when `border=false`) */
+    int32_t channels;         /* 4 for hdrfilm rgb: R,G,B,W (hdrfilm.cpp:245-273) */
+    int32_t filter;           /* 0 box, 1 tent, 2 gaussian */
+    float filter_param;       /* tent radius / gaussian stddev; 0 = plugin default (1 / 0.5) */
+    int32_t coalesce;         /* imageblock.cpp:418-531 window (render: spp >= 4, integrator.cpp:290) */
+    int32_t normalize;        /* imageblock.cpp:318-342 / :461-474 (ptracer splats) */
+} lrt_film_desc;
+
+/* ImageBlock::put (src/render/imageblock.cpp:174-532) for n samples: pos2 in pixel coordinates of the full
+ * film, values[n*channels]; accumulates (atomically) into accum [(size_y+2b),(size_x+2b),channels] f32. */
+int lrt_film_put(const lrt_film_desc *film, int64_t n, const float *pos2_dev, const float *values_dev,
+                 float *accum_dev, void *stream);
+/* HDRFilm::develop for pixel_format=rgb (src/films/hdrfilm.cpp:304-395): storage [npix,4] -> rgb [npix,3]. */
+int lrt_film_develop_rgb(int64_t npix, const float *storage4_dev, float *rgb_dev, void *stream);
+/* ReconstructionFilter::eval (host; same code as the kernels) */
+int lrt_filter_eval_host(int32_t filter, float param, int32_t n, const float *x, float *out, float *radius);
+
 #ifdef __cplusplus
 }
 #endif

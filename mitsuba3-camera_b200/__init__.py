@@ -3,6 +3,7 @@ gitmon/mitsuba3-camera). Import as `import lensrt as mi` (repo-root shim) — th
 hyphen, so it is loaded by path."""
 from . import _capi as capi           # fails loudly if liblensrt.so has not been built
 from . import lens_designs
+from .film import ReconstructionFilter, ImageBlock, FilmDesc, develop_rgb
 from .sensors import Film, Sensor, RealisticLensCamera, PerspectiveCamera
 
 __version__ = "0.1.0"

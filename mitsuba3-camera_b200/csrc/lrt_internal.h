@@ -2,6 +2,7 @@
 #pragma once
 #include "../../include/lensrt.h"
 #include "lrt_lens.cuh"
+#include "lrt_film.cuh"
 #include <atomic>
 #include <string>
 #include <vector>
@@ -12,6 +13,7 @@ void set_error(const std::string &msg);
 int cuda_fail(cudaError_t e, const char *what);
 bool have_device();
 extern std::atomic<uint64_t> g_launches;
+int film_params_from_desc(const lrt_film_desc *d, FilmParams &F);
 
 #define LRT_CUDA(call)                                                            \
     do {                                                                          \

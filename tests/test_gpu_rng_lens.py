@@ -62,5 +62,5 @@ def test_sample_ray_vs_oracle_1m(mi, name):
     want = cam_sample_ray(O, "orc", h, dn[:, 0:2], dn[:, 2:4])
     assert ((got[:, 7] > 0) == (want[:, 7] > 0)).all(), "lens ray-miss mask differs"
     act = want[:, 7] > 0
-    assert act.mean() > 0.001
+    assert act.sum() > 100
     assert (bits(got[act]) == bits(want[act])).all()
