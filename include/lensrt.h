@@ -115,6 +115,55 @@ int lrt_film_develop_rgb(int64_t npix, const float *storage4_dev, float *rgb_dev
 /* ReconstructionFilter::eval (host; same code as the kernels) */
 int lrt_filter_eval_host(int32_t filter, float param, int32_t n, const float *x, float *out, float *radius);
 
+/* ------------------------------------------------------------------------------------------------ scene
+ * Flat scene description (what mi.load_dict assembles from `rectangle` / `cube` / mesh shapes, `diffuse` /
+ * `conductor` / `dielectric` (+`twosided`) BSDFs and `area` emitters). All geometry is triangles;
+ * area emitters sit on rectangles (centre + two half-edge vectors, src/shapes/rectangle.cpp:115-185).
+ *   bsdfs   [n_bsdfs,16]   : type (0 diffuse, 1 conductor, 2 dielectric), twosided, reflectance rgb (diffuse)
+ *                            or specular_reflectance rgb, eta rgb, k rgb (conductor), specular_transmittance
+ *                            rgb, eta = int_ior/ext_ior (dielectric), pad
+ *   emitters[n_emitters,16]: radiance rgb, shape id, centre xyz, half-edge u xyz, half-edge v xyz, pad */
+typedef struct lrt_scene_desc {
+    int32_t n_vertices; const float *vertices;       /* [n_vertices,3] world space */
+    int64_t n_triangles; const int32_t *indices;     /* [n_triangles,3] */
+    const int32_t *tri_shape;                        /* [n_triangles] shape id */
+    int32_t n_shapes; const int32_t *shape_bsdf;     /* [n_shapes] */
+    const int32_t *shape_emitter;                    /* [n_shapes], -1 = not an emitter */
+    int32_t n_bsdfs; const float *bsdfs;
+    int32_t n_emitters; const float *emitters;
+} lrt_scene_desc;
+
+/* Scene::Scene (src/render/scene.cpp:22-96): builds the acceleration structure (8-wide quantised BVH, on the
+ * host) and uploads everything to the current device. */
+int lrt_scene_create(const lrt_scene_desc *desc, lrt_scene **out);
+void lrt_scene_destroy(lrt_scene *s);
+int lrt_scene_info(const lrt_scene *s, int64_t *n_nodes, int64_t *n_tris, int32_t *bvh_depth, double *build_seconds);
+/* Scene::ray_intersect_preliminary / ray_test (src/render/scene.cpp:181-210) for n rays:
+ * od7 = o[3], d[3], maxt; out4 = t, u, v, primitive index (-1: miss; t = inf). */
+int lrt_scene_intersect(const lrt_scene *s, int32_t any_hit, int64_t n, const float *od7_dev, float *out4_dev, void *stream);
+
+/* ----------------------------------------------------------------------------------------------- render
+ * Integrator::render (src/render/integrator.cpp:120-367, JIT sample order) with the `path` integrator
+ * (src/integrators/path.cpp:95-287; max_depth, rr_depth as in src/render/integrator.cpp:765-790). */
+typedef struct lrt_render_params {
+    uint32_t seed;
+    int32_t spp;
+    int32_t max_depth;        /* -1 = unbounded */
+    int32_t rr_depth;         /* default 5 */
+    int32_t shard_index, shard_count;   /* pixel tiles are dealt round-robin over shards (multi-GPU) */
+    int32_t chunks;           /* 0 = automatic split of a pixel's samples into work items */
+} lrt_render_params;
+
+/* Accumulates R,G,B,W into accum_dev [size_y+2b, size_x+2b, 4] (caller zeroes it; ImageBlock storage of
+ * hdrfilm). Asynchronous on `stream`. */
+int lrt_render(const lrt_scene *scene, const lrt_sensor *sensor, const lrt_film_desc *film,
+               const lrt_render_params *params, float *accum_dev, void *stream);
+/* mi.render(scene) for host callers: render + HDRFilm::develop; rgb_out [size_y,size_x,3] host memory. */
+int lrt_render_host(const lrt_scene *scene, const lrt_sensor *sensor, const lrt_film_desc *film,
+                    const lrt_render_params *params, float *rgb_out);
+/* counters of the last render on this scene: samples, lens misses, rays traced, path-loop iterations */
+int lrt_render_stats(const lrt_scene *scene, uint64_t *out4);
+
 #ifdef __cplusplus
 }
 #endif

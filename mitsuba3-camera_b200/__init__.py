@@ -7,3 +7,24 @@ from .film import ReconstructionFilter, ImageBlock, FilmDesc, develop_rgb
 from .sensors import Film, Sensor, RealisticLensCamera, PerspectiveCamera
 
 __version__ = "0.1.0"
+from .transform import Transform4f, ScalarTransform4f
+from .scene import (Scene, SceneData, PathIntegrator, IndependentSampler, load_dict, render, cornell_box, bsdf_row,
+                    film_desc, RenderParams, SceneDesc, load_obj, load_ply)
+
+_variant = "b200_ad_rgb"
+
+
+def variants():
+    return ["b200_ad_rgb"]
+
+
+def variant():
+    return _variant
+
+
+def set_variant(*names):
+    """mi.set_variant: this build has one variant; reference names of the *_rgb family are accepted."""
+    for n in names:
+        if n in ("b200_ad_rgb", "cuda_ad_rgb", "llvm_ad_rgb", "scalar_rgb", "cuda_rgb", "llvm_rgb"):
+            return
+    raise ImportError(f"variant(s) {names} not available; this build provides 'b200_ad_rgb'")

@@ -1,0 +1,168 @@
+// lensrt — host BVH builder: binned-SAH binary tree -> greedy collapse to 8-wide nodes -> quantised boxes.
+// See lrt_bvh.h for the layout and the reference interfaces this replaces.
+#include <vector_types.h>
+#include "lrt_bvh.h"
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <limits>
+
+namespace lrt {
+namespace {
+
+struct Box {
+    float lo[3], hi[3];
+    void reset() { for (int a = 0; a < 3; ++a) { lo[a] = std::numeric_limits<float>::infinity(); hi[a] = -lo[a]; } }
+    void grow(const float *p) { for (int a = 0; a < 3; ++a) { lo[a] = std::min(lo[a], p[a]); hi[a] = std::max(hi[a], p[a]); } }
+    void grow(const Box &b) { for (int a = 0; a < 3; ++a) { lo[a] = std::min(lo[a], b.lo[a]); hi[a] = std::max(hi[a], b.hi[a]); } }
+    float area() const {
+        float dx = hi[0] - lo[0], dy = hi[1] - lo[1], dz = hi[2] - lo[2];
+        return (dx < 0) ? 0.f : 2.f * (dx * dy + dy * dz + dz * dx);
+    }
+};
+
+struct BinNode { Box box; int left = -1, right = -1, first = 0, count = 0; };
+
+struct Builder {
+    const float *verts; const int32_t *idx; int64_t nt;
+    std::vector<Box> tbox; std::vector<float> cent;   // per triangle
+    std::vector<int> order;
+    std::vector<BinNode> bn;
+    static constexpr int kBins = 16, kLeaf = 3;
+
+    int build(int first, int count, int depth, int &max_depth) {
+        BinNode nd; nd.box.reset(); nd.first = first; nd.count = count;
+        Box cb; cb.reset();
+        for (int i = first; i < first + count; ++i) { nd.box.grow(tbox[order[i]]); cb.grow(&cent[3 * (size_t) order[i]]); }
+        int id = (int) bn.size(); bn.push_back(nd);
+        max_depth = std::max(max_depth, depth);
+        if (count <= kLeaf) return id;
+        // binned SAH over the longest centroid axis first, then the others
+        float best_cost = std::numeric_limits<float>::infinity(); int best_axis = -1, best_bin = -1;
+        for (int axis = 0; axis < 3; ++axis) {
+            float lo = cb.lo[axis], ext = cb.hi[axis] - lo;
+            if (!(ext > 0.f)) continue;
+            Box bb[kBins]; int bc[kBins];
+            for (int b = 0; b < kBins; ++b) { bb[b].reset(); bc[b] = 0; }
+            float k = kBins * (1.f - 1e-6f) / ext;
+            for (int i = first; i < first + count; ++i) {
+                int t = order[i]; int b = std::min(kBins - 1, std::max(0, (int) ((cent[3 * (size_t) t + axis] - lo) * k)));
+                bb[b].grow(tbox[t]); bc[b]++;
+            }
+            float ra[kBins]; Box acc; acc.reset(); int cnt = 0;
+            int rc[kBins];
+            for (int b = kBins - 1; b > 0; --b) { acc.grow(bb[b]); cnt += bc[b]; ra[b] = acc.area(); rc[b] = cnt; }
+            acc.reset(); cnt = 0;
+            for (int b = 0; b < kBins - 1; ++b) {
+                acc.grow(bb[b]); cnt += bc[b];
+                if (cnt == 0 || rc[b + 1] == 0) continue;
+                float cost = acc.area() * cnt + ra[b + 1] * rc[b + 1];
+                if (cost < best_cost) { best_cost = cost; best_axis = axis; best_bin = b; }
+            }
+        }
+        int mid;
+        if (best_axis < 0) {   // all centroids coincide: split in the middle
+            mid = first + count / 2;
+        } else {
+            float lo = cb.lo[best_axis], ext = cb.hi[best_axis] - lo, k = kBins * (1.f - 1e-6f) / ext;
+            auto it = std::partition(order.begin() + first, order.begin() + first + count, [&](int t) {
+                int b = std::min(kBins - 1, std::max(0, (int) ((cent[3 * (size_t) t + best_axis] - lo) * k)));
+                return b <= best_bin;
+            });
+            mid = (int) (it - order.begin());
+            if (mid == first || mid == first + count) mid = first + count / 2;
+        }
+        int l = build(first, mid - first, depth + 1, max_depth);
+        int r = build(mid, first + count - mid, depth + 1, max_depth);
+        bn[id].left = l; bn[id].right = r; bn[id].count = 0;
+        return id;
+    }
+};
+
+uint8_t exponent_for(float extent) {
+    // smallest e with 255 * 2^(e-127) >= extent
+    if (!(extent > 0.f)) return 1;
+    int e; std::frexp(extent / 255.f, &e);   // extent/255 = m * 2^e, m in [.5,1)  =>  2^e >= extent/255
+    int biased = e + 127;
+    return (uint8_t) std::min(254, std::max(1, biased));
+}
+
+}  // namespace
+
+void build_bvh8(const float *verts, const int32_t *idx, const int32_t *tri_shape, int64_t nt,
+                std::vector<BvhNode> &nodes, std::vector<BvhTri> &tris, BvhBuildStats *stats) {
+    nodes.clear(); tris.clear();
+    Builder B; B.verts = verts; B.idx = idx; B.nt = nt;
+    B.tbox.resize(nt); B.cent.resize(3 * (size_t) nt); B.order.resize(nt);
+    for (int64_t t = 0; t < nt; ++t) {
+        Box b; b.reset();
+        for (int k = 0; k < 3; ++k) b.grow(verts + 3 * (size_t) idx[3 * t + k]);
+        B.tbox[t] = b; B.order[t] = (int) t;
+        for (int a = 0; a < 3; ++a) B.cent[3 * t + a] = 0.5f * (b.lo[a] + b.hi[a]);
+    }
+    int max_depth = 0;
+    if (nt == 0) {   // empty scene: a root whose children are all empty
+        BvhNode n; memset(&n, 0, sizeof n); n.ex = n.ey = n.ez = 1; nodes.push_back(n);
+        if (stats) *stats = BvhBuildStats();
+        return;
+    }
+    B.bn.reserve(2 * (size_t) nt);
+    B.build(0, (int) nt, 0, max_depth);
+
+    // collapse: breadth-first emission so that the inner children of a node are contiguous
+    struct Pending { int bin; };   // binary subtree root that becomes one wide node
+    std::vector<int> queue; queue.push_back(0);
+    nodes.resize(1);
+    size_t head = 0; int leaves = 0;
+    while (head < queue.size()) {
+        int bin_root = queue[head]; size_t self = head; head++;
+        // gather up to 8 children by repeatedly opening the inner child with the largest area
+        int ch[8]; int nch = 0;
+        const BinNode &root = B.bn[bin_root];
+        if (root.left < 0) { ch[nch++] = bin_root; }
+        else { ch[nch++] = root.left; ch[nch++] = root.right; }
+        while (nch < 8) {
+            int best = -1; float ba = -1.f;
+            for (int i = 0; i < nch; ++i) if (B.bn[ch[i]].left >= 0) { float a = B.bn[ch[i]].box.area(); if (a > ba) { ba = a; best = i; } }
+            if (best < 0) break;
+            int c = ch[best]; ch[best] = B.bn[c].left; ch[nch++] = B.bn[c].right;
+        }
+        BvhNode n; memset(&n, 0, sizeof n);
+        const Box &nb = root.box;
+        n.ox = nb.lo[0]; n.oy = nb.lo[1]; n.oz = nb.lo[2];
+        n.ex = exponent_for(nb.hi[0] - nb.lo[0]); n.ey = exponent_for(nb.hi[1] - nb.lo[1]); n.ez = exponent_for(nb.hi[2] - nb.lo[2]);
+        n.child_base = (uint32_t) queue.size(); n.tri_base = (uint32_t) tris.size();
+        float sc[3] = { std::ldexp(1.f, n.ex - 127), std::ldexp(1.f, n.ey - 127), std::ldexp(1.f, n.ez - 127) };
+        int inner_k = 0, tri_off = 0;
+        for (int i = 0; i < nch; ++i) {
+            const BinNode &c = B.bn[ch[i]];
+            uint8_t *ql[3] = { n.qlo_x, n.qlo_y, n.qlo_z }, *qh[3] = { n.qhi_x, n.qhi_y, n.qhi_z };
+            const float org[3] = { n.ox, n.oy, n.oz };
+            for (int a = 0; a < 3; ++a) {
+                float lo = std::floor((c.box.lo[a] - org[a]) / sc[a]), hi = std::ceil((c.box.hi[a] - org[a]) / sc[a]);
+                // one extra step of slack guards the float rounding of (x - org)/scale and of the ray-box test
+                ql[a][i] = (uint8_t) std::min(255.f, std::max(0.f, lo - 1.f));
+                qh[a][i] = (uint8_t) std::min(255.f, std::max(0.f, hi + 1.f));
+            }
+            if (c.left >= 0) { n.meta[i] = (uint8_t) (0x80 | inner_k); inner_k++; queue.push_back(ch[i]); }
+            else {
+                n.meta[i] = (uint8_t) ((c.count << 5) | tri_off); tri_off += c.count; leaves++;
+                for (int k = c.first; k < c.first + c.count; ++k) {
+                    int t = B.order[k]; BvhTri tr; memset(&tr, 0, sizeof tr);
+                    for (int a = 0; a < 3; ++a) {
+                        tr.p0[a] = verts[3 * (size_t) idx[3 * (size_t) t] + a];
+                        tr.p1[a] = verts[3 * (size_t) idx[3 * (size_t) t + 1] + a];
+                        tr.p2[a] = verts[3 * (size_t) idx[3 * (size_t) t + 2] + a];
+                    }
+                    tr.shape = tri_shape ? tri_shape[t] : 0; tr.prim = t;
+                    tris.push_back(tr);
+                }
+            }
+        }
+        if (nodes.size() < queue.size()) nodes.resize(queue.size());
+        nodes[self] = n;
+    }
+    if (stats) { stats->nodes = (int) nodes.size(); stats->leaves = leaves; stats->max_depth = max_depth; }
+}
+
+}  // namespace lrt

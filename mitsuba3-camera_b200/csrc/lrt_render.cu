@@ -1,0 +1,282 @@
+// lensrt — the render megakernel: sampler -> sensor (realistic lens / pinhole) -> path integrator -> film splat.
+// Replaces SamplingIntegrator::render + render_sample, JIT branch (src/render/integrator.cpp:247-330,419-491),
+// PathIntegrator::sample (src/integrators/path.cpp:95-287) and ImageBlock::put + put_block
+// (src/render/imageblock.cpp:135-172,174-532) for hdrfilm's R,G,B,W storage (src/films/hdrfilm.cpp:245-297).
+//
+// Execution model (not the reference's wavefront): persistent CTAs pull work items (pixel tile x sample
+// chunk) from a global counter. A CTA is 4 warps = a tile of 32x4 pixels; each lane owns ONE pixel and walks
+// its samples sequentially, so all lanes stay busy until the tile is done (no cross-lane compaction needed).
+// Sample `j` of pixel `p` always uses PCG32 stream idx = p*spp + j (sampler.cpp:121-130) whatever the
+// sharding, so images are identical up to float summation order for any tile/chunk/GPU split.
+// Dead lanes are refilled in batches (warp ballot): the divergent lens section only runs when >= 8 lanes
+// need a new camera ray or nobody has a live path. Splats go to a shared-memory tile (one lane = one pixel
+// => a given tap never collides inside a warp) and the tile is flushed once with global float atomics.
+#include "lrt_internal.h"
+#include "lrt_rng.cuh"
+#include "lrt_shade.cuh"
+#include "lrt_scene.h"
+
+namespace lrt {
+
+constexpr int kTileW = 32, kTileH = 4, kCtaThreads = kTileW * kTileH;
+constexpr int kRefillThreshold = 8;
+
+struct RenderArgs {
+    SceneView sc;
+    const LensSystem *lens;
+    FilmParams film;
+    uint32_t seed; int spp, max_depth, rr_depth;
+    int tiles_x, n_chunks, chunk_spp;
+    int shard_index, shard_count; long long n_items;
+    int pad, smem_w, smem_h;
+    unsigned long long *counter;
+    float *accum;
+    unsigned long long *stats;     // [0] samples, [1] lens misses, [2] rays traced, [3] bounces
+};
+
+__global__ void __launch_bounds__(kCtaThreads) k_render(RenderArgs A) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    LensSystem &L = *reinterpret_cast<LensSystem *>(smem_raw);
+    float *tile = reinterpret_cast<float *>(smem_raw + sizeof(LensSystem));
+    __shared__ long long s_item;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    {
+        const uint4 *src = reinterpret_cast<const uint4 *>(A.lens);
+        uint4 *dst = reinterpret_cast<uint4 *>(&L);
+        for (int i = tid; i < (int) (sizeof(LensSystem) / 16); i += kCtaThreads) dst[i] = src[i];
+    }
+    const FilmParams &F = A.film;
+    const int tile_elems = A.smem_w * A.smem_h * 4;
+    const float scale_x = 1.f / (float) F.size_x, scale_y = 1.f / (float) F.size_y;
+    const float offs_x = -(float) F.off_x * scale_x, offs_y = -(float) F.off_y * scale_y;
+    unsigned long long n_samples = 0, n_miss = 0, n_rays = 0, n_bounces = 0;
+
+    while (true) {
+        __syncthreads();
+        if (tid == 0) s_item = (long long) atomicAdd(A.counter, 1ULL);
+        for (int i = tid; i < tile_elems; i += kCtaThreads) tile[i] = 0.f;
+        __syncthreads();
+        long long item = s_item;
+        if (item >= A.n_items) break;
+        const int chunk = (int) (item % A.n_chunks);
+        const long long tile_id = (long long) A.shard_index + (item / A.n_chunks) * A.shard_count;
+        const int tx = (int) (tile_id % A.tiles_x), ty = (int) (tile_id / A.tiles_x);
+        const int px = tx * kTileW + lane, py = ty * kTileH + warp;
+        const bool in_film = px < F.size_x && py < F.size_y;
+        const int ox = tx * kTileW - A.pad, oy = ty * kTileH - A.pad;   // tensor coords of smem (0,0)
+        int j = chunk * A.chunk_spp;
+        const int j_end = in_film ? min(A.spp, j + A.chunk_spp) : j;
+        const uint32_t idx_base = (uint32_t) (py * F.size_x + px) * (uint32_t) A.spp;
+        const float posx = (float) (px + F.off_x), posy = (float) (py + F.off_y);
+
+        // ---- per-lane path state
+        bool have_path = false;
+        Pcg32 rng; rng.state = 0; rng.inc = 1;
+        float3 ro = make_float3(0, 0, 0), rd = make_float3(0, 0, 1); float rmaxt = 0.f;
+        float3 throughput = make_float3(1, 1, 1), result = make_float3(0, 0, 0), prev_p = make_float3(0, 0, 0);
+        float eta = 1.f, prev_pdf = 1.f, cam_weight = 0.f, spx = 0.f, spy = 0.f;
+        int depth = 0; bool prev_delta = true, valid_ray = false;
+
+        while (true) {
+            const bool need = !have_path && j < j_end;
+            const unsigned need_mask = __ballot_sync(0xffffffffu, need);
+            const unsigned live_mask = __ballot_sync(0xffffffffu, have_path);
+            if (!need_mask && !live_mask) break;
+            const bool refill = live_mask == 0 || __popc(need_mask) >= kRefillThreshold;
+            bool splat = false; float3 value = make_float3(0, 0, 0);
+
+            if (refill && need) {
+                // ---- render_sample(): draws in the reference's order (integrator.cpp:435-448)
+                rng.seed_sample(A.seed, idx_base + (uint32_t) j); j++; n_samples++;
+                float u0 = rng.next_f32(), u1 = rng.next_f32();
+                spx = strict::add(posx, u0); spy = strict::add(posy, u1);
+                float ax = strict::fmadd(spx, scale_x, offs_x), ay = strict::fmadd(spy, scale_y, offs_y);
+                float a = .5f, b = .5f;
+                if (L.kind == 0) { a = rng.next_f32(); b = rng.next_f32(); }
+                CameraRay cr = sensor_sample_ray(L, L.ifs, ax, ay, a, b);
+                cam_weight = cr.weight;
+                if (cr.weight > 0.f) {
+                    have_path = true; ro = cr.o; rd = cr.d; rmaxt = cr.maxt;
+                    throughput = make_float3(1, 1, 1); result = make_float3(0, 0, 0); eta = 1.f; depth = 0;
+                    prev_p = make_float3(0, 0, 0); prev_pdf = 1.f; prev_delta = true; valid_ray = false;
+                    if (A.max_depth == 0) { have_path = false; splat = true; }
+                } else { n_miss++; splat = true; }      // vignetted: RGB 0, weight 1 (integrator.cpp:461-490)
+            } else if (have_path) {
+                // ---- one iteration of PathIntegrator::sample's loop (path.cpp:142-281)
+                n_bounces++; n_rays++;
+                RayHit h = bvh_intersect<false>(A.sc.bvh, ro, rd, rmaxt);
+                bool hit = h.tri >= 0;
+                Surface si;
+                if (hit) si = make_surface(A.sc, h, rd);
+                int em = hit ? __ldg(A.sc.shape_emitter + si.shape) : -1;
+                if (em >= 0) {
+                    float3 rel = si.p - prev_p; float dist = sqrtf(dot(rel, rel)); float3 dd = rel * (1.f / dist);
+                    float em_pdf = prev_delta ? 0.f : pdf_emitter_direction(A.sc, em, dd, dist, si.n);
+                    float mis_bsdf = mis_weight(prev_pdf, em_pdf);
+                    if (si.wi.z > 0.f && prev_pdf > 0.f) {
+                        float4 e0 = __ldg(A.sc.emitters + 5 * (size_t) em);
+                        result += throughput * make_float3(e0.x, e0.y, e0.z) * mis_bsdf;
+                    }
+                }
+                bool active_next = (depth + 1 < A.max_depth) && hit;
+                float e_sx = rng.next_f32(), e_sy = rng.next_f32();
+                float s1 = rng.next_f32(), s2x = rng.next_f32(), s2y = rng.next_f32();
+                float rr_sample = rng.next_f32();
+                bool alive = false;
+                if (active_next) {
+                    int bsdf_id = __ldg(A.sc.shape_bsdf + si.shape);
+                    bool active_em = bsdf_is_smooth(A.sc, bsdf_id);
+                    EmitterSample es; es.pdf = 0.f; float3 wo = make_float3(0, 0, 0);
+                    if (active_em) {
+                        es = sample_emitter_direction(A.sc, si.p, e_sx, e_sy);
+                        if (es.pdf != 0.f) {   // shadow ray: Interaction::spawn_ray_to (interaction.h:139-146)
+                            float3 so = offset_p(si.p, si.n, es.p - si.p);
+                            float3 sd = es.p - so; float sdist = sqrtf(dot(sd, sd)); sd = sd * (1.f / sdist);
+                            n_rays++;
+                            RayHit sh = bvh_intersect<true>(A.sc.bvh, so, sd, sdist * (1.f - kShadowEpsilon));
+                            if (sh.tri >= 0) es.pdf = 0.f;
+                        }
+                        active_em = es.pdf != 0.f;
+                        wo = si.to_local(es.d);
+                    }
+                    BsdfResult bs = bsdf_eval_pdf_sample(A.sc, bsdf_id, si.wi, wo, s1, s2x, s2y);
+                    if (active_em) result += throughput * (bs.val * es.weight * mis_weight(es.pdf, bs.pdf));
+                    float3 wo_w = si.to_world(bs.wo);
+                    ro = offset_p(si.p, si.n, wo_w); rd = wo_w; rmaxt = kLargest;
+                    throughput *= bs.weight; eta *= bs.seta;
+                    valid_ray = true;
+                    prev_p = si.p; prev_pdf = bs.spdf; prev_delta = bs.delta;
+                    depth++;
+                    float tmax = max3(throughput);
+                    float rr_prob = fminf(tmax * eta * eta, .95f);
+                    bool rr_active = depth >= A.rr_depth;
+                    if (rr_active) throughput *= 1.f / rr_prob;
+                    alive = (!rr_active || rr_sample < rr_prob) && tmax != 0.f;
+                }
+                if (!alive) {
+                    have_path = false; splat = true;
+                    if (valid_ray) value = result * cam_weight;
+                }
+            }
+
+            if (splat) {
+                Footprint fp;
+                const bool box = F.kind == FILTER_BOX;
+                if (film_footprint(F, box ? posx : spx, box ? posy : spy, fp)) {
+                    const int sw = box ? F.size_x : F.size_x + 2 * F.border, shh = F.size_y + 2 * F.border;
+                    for (int iy = 0; iy < fp.ny; ++iy) {
+                        int y = fp.y0 + iy;
+                        if ((unsigned) y >= (unsigned) shh) continue;
+                        for (int ix = 0; ix < fp.nx; ++ix) {
+                            int x = fp.x0 + ix;
+                            if ((unsigned) x >= (unsigned) sw) continue;
+                            float w = fp.wy[iy] * fp.wx[ix];
+                            float *dst = tile + ((y - oy) * A.smem_w + (x - ox)) * 4;
+                            if (value.x != 0.f) atomicAdd(dst, value.x * w);
+                            if (value.y != 0.f) atomicAdd(dst + 1, value.y * w);
+                            if (value.z != 0.f) atomicAdd(dst + 2, value.z * w);
+                            atomicAdd(dst + 3, w);
+                        }
+                    }
+                }
+            }
+        }
+
+        // ---- put_block(): flush the tile into the film accumulator
+        __syncthreads();
+        const int sw = F.size_x + 2 * F.border, shh = F.size_y + 2 * F.border;
+        for (int i = tid; i < A.smem_w * A.smem_h; i += kCtaThreads) {
+            int ly = i / A.smem_w, lx = i - ly * A.smem_w;
+            int x = ox + lx, y = oy + ly;
+            if ((unsigned) x >= (unsigned) sw || (unsigned) y >= (unsigned) shh) continue;
+            float4 v = reinterpret_cast<const float4 *>(tile)[i];
+            if (v.w == 0.f && v.x == 0.f && v.y == 0.f && v.z == 0.f) continue;
+            float *dst = A.accum + ((size_t) y * sw + x) * 4;
+            if (v.x != 0.f) atomicAdd(dst, v.x);
+            if (v.y != 0.f) atomicAdd(dst + 1, v.y);
+            if (v.z != 0.f) atomicAdd(dst + 2, v.z);
+            if (v.w != 0.f) atomicAdd(dst + 3, v.w);
+        }
+    }
+    if (A.stats) {
+        for (int o = 16; o > 0; o >>= 1) {
+            n_samples += __shfl_down_sync(0xffffffffu, n_samples, o); n_miss += __shfl_down_sync(0xffffffffu, n_miss, o);
+            n_rays += __shfl_down_sync(0xffffffffu, n_rays, o); n_bounces += __shfl_down_sync(0xffffffffu, n_bounces, o);
+        }
+        if (lane == 0) {
+            atomicAdd(A.stats, n_samples); atomicAdd(A.stats + 1, n_miss); atomicAdd(A.stats + 2, n_rays); atomicAdd(A.stats + 3, n_bounces);
+        }
+    }
+}
+
+// unit-level Scene::ray_intersect / ray_test
+__global__ void __launch_bounds__(128) k_intersect(SceneView sc, int any_hit, int64_t n, const float *__restrict__ od7, float *__restrict__ out4) {
+    for (int64_t i = blockIdx.x * (int64_t) blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) {
+        const float *r = od7 + 7 * i;
+        float3 o = make_float3(r[0], r[1], r[2]), d = make_float3(r[3], r[4], r[5]);
+        RayHit h = any_hit ? bvh_intersect<true>(sc.bvh, o, d, r[6]) : bvh_intersect<false>(sc.bvh, o, d, r[6]);
+        float *q = out4 + 4 * i;
+        q[0] = h.t; q[1] = h.u; q[2] = h.v;
+        q[3] = h.tri >= 0 ? (float) __float_as_int(__ldg(sc.bvh.tris + 3 * (size_t) h.tri + 2).z) : -1.f;
+    }
+}
+
+}  // namespace lrt
+
+// ================================================================================ host side
+namespace lrt {
+
+int launch_render(const lrt_scene *sc, lrt_sensor *sensor, const lrt_film_desc *film, const lrt_render_params *rp,
+                  float *accum_dev, cudaStream_t stream) {
+    RenderArgs A; memset(&A, 0, sizeof A);
+    int rc = film_params_from_desc(film, A.film); if (rc) return rc;
+    LRT_REQUIRE(film->channels == 4, "render needs the R,G,B,W film of hdrfilm (channels = 4)");
+    LRT_REQUIRE(rp->spp > 0 && rp->max_depth >= -1 && rp->shard_count >= 1 && rp->shard_index >= 0 && rp->shard_index < rp->shard_count, "bad render parameters");
+    // one PCG32 stream per sample: the wavefront must fit 32 bits (integrator.cpp:247-265 splits into passes)
+    LRT_REQUIRE((double) film->size_x * film->size_y * rp->spp < 4294967296.0, "W*H*spp exceeds 2^32: render in passes");
+    rc = sensor->upload(); if (rc) return rc;
+    A.sc = sc->view; A.lens = sensor->dev;
+    A.seed = rp->seed; A.spp = rp->spp; A.max_depth = rp->max_depth < 0 ? 0x7fffffff : rp->max_depth; A.rr_depth = rp->rr_depth;
+    A.film.coalesce = rp->spp >= 4 ? film->coalesce : 0;   // integrator.cpp:290
+    const FilmParams &F = A.film;
+    A.pad = F.kind == FILTER_BOX ? 0 : (F.coalesce ? F.n_half : (int) std::ceil(F.radius + .5f));
+    A.smem_w = kTileW + 2 * A.pad; A.smem_h = kTileH + 2 * A.pad;
+    A.tiles_x = (F.size_x + kTileW - 1) / kTileW;
+    int tiles_y = (F.size_y + kTileH - 1) / kTileH;
+    long long n_tiles = (long long) A.tiles_x * tiles_y;
+    long long my_tiles = (n_tiles - rp->shard_index + rp->shard_count - 1) / rp->shard_count;
+    int dev = 0, sms = 148; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    size_t smem = sizeof(LensSystem) + (size_t) A.smem_w * A.smem_h * 16;
+    static bool attr_set = false;
+    if (!attr_set) { cudaFuncSetAttribute(k_render, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024); attr_set = true; }
+    int per_sm = 1; cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_render, kCtaThreads, smem);
+    if (per_sm < 1) per_sm = 1;
+    long long resident = (long long) sms * per_sm;
+    // split the samples of a pixel into chunks until there are ~4 work items per resident CTA
+    int n_chunks = 1;
+    while (my_tiles * n_chunks < 4 * resident && n_chunks * 2 <= rp->spp) n_chunks *= 2;
+    if (rp->chunks > 0) n_chunks = std::min(rp->chunks, rp->spp);
+    A.n_chunks = n_chunks; A.chunk_spp = (rp->spp + n_chunks - 1) / n_chunks;
+    A.shard_index = rp->shard_index; A.shard_count = rp->shard_count; A.n_items = my_tiles * n_chunks;
+    A.counter = sc->d_counter; A.stats = sc->d_counter + 1; A.accum = accum_dev;
+    LRT_CUDA(cudaMemsetAsync(sc->d_counter, 0, 8 * sizeof(unsigned long long), stream));
+    long long grid = std::min(resident, A.n_items);
+    if (grid < 1) return LRT_OK;
+    k_render<<<(int) grid, kCtaThreads, smem, stream>>>(A);
+    LRT_LAUNCHED();
+    LRT_CUDA(cudaGetLastError());
+    return LRT_OK;
+}
+
+}  // namespace lrt
+
+extern "C" int lrt_scene_intersect(const lrt_scene *sc, int32_t any_hit, int64_t n, const float *od7_dev, float *out4_dev, void *stream) {
+    LRT_NEED_DEVICE();
+    LRT_REQUIRE(sc && od7_dev && out4_dev && n >= 0, "bad argument");
+    if (n == 0) return LRT_OK;
+    int64_t g = (n + 127) / 128; if (g > 148 * 32) g = 148 * 32;
+    lrt::k_intersect<<<(int) g, 128, 0, (cudaStream_t) stream>>>(sc->view, any_hit, n, od7_dev, out4_dev);
+    LRT_LAUNCHED();
+    LRT_CUDA(cudaGetLastError());
+    return LRT_OK;
+}

@@ -1,0 +1,121 @@
+// lensrt — scene construction (host BVH build + upload) and the render entry points of include/lensrt.h.
+#include "lrt_scene.h"
+#include <chrono>
+#include <cstring>
+#include <cmath>
+
+namespace lrt {
+struct RenderArgs;
+int launch_render(const lrt_scene *sc, lrt_sensor *sensor, const lrt_film_desc *film, const lrt_render_params *rp,
+                  float *accum_dev, cudaStream_t stream);
+}
+using namespace lrt;
+
+template <typename T> static int upload(void **dst, const T *src, size_t n) {
+    size_t bytes = std::max<size_t>(n, 1) * sizeof(T);
+    LRT_CUDA(cudaMalloc(dst, bytes));
+    if (n) LRT_CUDA(cudaMemcpy(*dst, src, n * sizeof(T), cudaMemcpyHostToDevice));
+    return LRT_OK;
+}
+
+extern "C" {
+
+int lrt_scene_create(const lrt_scene_desc *d, lrt_scene **out) {
+    LRT_NEED_DEVICE();
+    LRT_REQUIRE(d && out, "null argument");
+    LRT_REQUIRE(d->n_triangles >= 0 && d->n_shapes >= 0 && d->n_bsdfs >= 0 && d->n_emitters >= 0, "negative count");
+    LRT_REQUIRE(d->n_triangles == 0 || (d->vertices && d->indices && d->tri_shape), "null geometry");
+    LRT_REQUIRE(d->n_triangles < (1 << 28), "too many triangles (2^28 max)");
+    for (int64_t t = 0; t < d->n_triangles; ++t) {
+        LRT_REQUIRE(d->tri_shape[t] >= 0 && d->tri_shape[t] < d->n_shapes, "tri_shape out of range");
+        for (int k = 0; k < 3; ++k) LRT_REQUIRE(d->indices[3 * t + k] >= 0 && d->indices[3 * t + k] < d->n_vertices, "vertex index out of range");
+    }
+    for (int s = 0; s < d->n_shapes; ++s) {
+        LRT_REQUIRE(d->shape_bsdf[s] >= 0 && d->shape_bsdf[s] < d->n_bsdfs, "shape_bsdf out of range");
+        LRT_REQUIRE(d->shape_emitter[s] >= -1 && d->shape_emitter[s] < d->n_emitters, "shape_emitter out of range");
+    }
+    auto t0 = std::chrono::steady_clock::now();
+    std::vector<BvhNode> nodes; std::vector<BvhTri> tris; BvhBuildStats st;
+    build_bvh8(d->vertices, d->indices, d->tri_shape, d->n_triangles, nodes, tris, &st);
+    lrt_scene *s = new lrt_scene();
+    s->build_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    s->n_nodes = (int64_t) nodes.size(); s->n_tris = (int64_t) tris.size(); s->bvh_depth = st.max_depth;
+    s->n_shapes = d->n_shapes; s->n_bsdfs = d->n_bsdfs; s->n_emitters = d->n_emitters;
+    // emitters: 16-float rows -> 5 x float4 with the rectangle's normal and 1/area (rectangle.cpp:115-123)
+    std::vector<float> em((size_t) d->n_emitters * 20, 0.f);
+    for (int i = 0; i < d->n_emitters; ++i) {
+        const float *r = d->emitters + 16 * i; float *o = em.data() + 20 * (size_t) i;
+        o[0] = r[0]; o[1] = r[1]; o[2] = r[2]; o[3] = r[3];
+        o[4] = r[4]; o[5] = r[5]; o[6] = r[6];
+        for (int k = 0; k < 3; ++k) { o[8 + k] = r[7 + k]; o[12 + k] = r[10 + k]; }
+        float ex[3] = { r[7], r[8], r[9] }, ey[3] = { r[10], r[11], r[12] };
+        float cx = ex[1] * ey[2] - ex[2] * ey[1], cy = ex[2] * ey[0] - ex[0] * ey[2], cz = ex[0] * ey[1] - ex[1] * ey[0];
+        float len = std::sqrt(cx * cx + cy * cy + cz * cz);
+        o[16] = cx / len; o[17] = cy / len; o[18] = cz / len;
+        o[7] = 1.f / (4.f * len);
+    }
+    int rc = LRT_OK;
+    if ((rc = upload(&s->d_nodes, nodes.data(), nodes.size())) || (rc = upload(&s->d_tris, tris.data(), tris.size())) ||
+        (rc = upload(&s->d_shape_bsdf, d->shape_bsdf, (size_t) d->n_shapes)) ||
+        (rc = upload(&s->d_shape_emitter, d->shape_emitter, (size_t) d->n_shapes)) ||
+        (rc = upload(&s->d_bsdfs, d->bsdfs, (size_t) d->n_bsdfs * 16)) || (rc = upload(&s->d_emitters, em.data(), em.size()))) {
+        lrt_scene_destroy(s); return rc;
+    }
+    if (cudaMalloc(&s->d_counter, 8 * sizeof(unsigned long long)) != cudaSuccess) { lrt_scene_destroy(s); return cuda_fail(cudaGetLastError(), "cudaMalloc"); }
+    s->view.bvh.nodes = (const uint4 *) s->d_nodes; s->view.bvh.tris = (const float4 *) s->d_tris;
+    s->view.shape_bsdf = (const int *) s->d_shape_bsdf; s->view.shape_emitter = (const int *) s->d_shape_emitter;
+    s->view.bsdfs = (const float4 *) s->d_bsdfs; s->view.emitters = (const float4 *) s->d_emitters;
+    s->view.n_emitters = d->n_emitters;
+    *out = s;
+    return LRT_OK;
+}
+
+void lrt_scene_destroy(lrt_scene *s) {
+    if (!s) return;
+    void *p[] = { s->d_nodes, s->d_tris, s->d_shape_bsdf, s->d_shape_emitter, s->d_bsdfs, s->d_emitters, s->d_counter };
+    for (void *q : p) if (q) cudaFree(q);
+    delete s;
+}
+
+int lrt_scene_info(const lrt_scene *s, int64_t *n_nodes, int64_t *n_tris, int32_t *bvh_depth, double *build_seconds) {
+    LRT_REQUIRE(s, "null scene");
+    if (n_nodes) *n_nodes = s->n_nodes;
+    if (n_tris) *n_tris = s->n_tris;
+    if (bvh_depth) *bvh_depth = s->bvh_depth;
+    if (build_seconds) *build_seconds = s->build_seconds;
+    return LRT_OK;
+}
+
+int lrt_render(const lrt_scene *sc, const lrt_sensor *sensor, const lrt_film_desc *film, const lrt_render_params *rp,
+               float *accum_dev, void *stream) {
+    LRT_NEED_DEVICE();
+    LRT_REQUIRE(sc && sensor && film && rp && accum_dev, "null argument");
+    return launch_render(sc, const_cast<lrt_sensor *>(sensor), film, rp, accum_dev, (cudaStream_t) stream);
+}
+
+int lrt_render_stats(const lrt_scene *sc, uint64_t *out4) {
+    LRT_NEED_DEVICE();
+    LRT_REQUIRE(sc && out4, "null argument");
+    LRT_CUDA(cudaMemcpy(out4, sc->d_counter + 1, 4 * sizeof(uint64_t), cudaMemcpyDeviceToHost));
+    return LRT_OK;
+}
+
+// mi.render() for host callers: accumulate + develop; rgb_out [size_y, size_x, 3] on the host
+int lrt_render_host(const lrt_scene *sc, const lrt_sensor *sensor, const lrt_film_desc *film, const lrt_render_params *rp,
+                    float *rgb_out) {
+    LRT_NEED_DEVICE();
+    LRT_REQUIRE(sc && sensor && film && rp && rgb_out, "null argument");
+    LRT_REQUIRE(film->border == 0 && film->channels == 4, "render_host needs a borderless R,G,B,W film");
+    size_t npix = (size_t) film->size_x * film->size_y;
+    float *acc = nullptr, *rgb = nullptr;
+    LRT_CUDA(cudaMalloc(&acc, npix * 16)); 
+    if (cudaMalloc(&rgb, npix * 12) != cudaSuccess) { cudaFree(acc); return cuda_fail(cudaGetLastError(), "cudaMalloc"); }
+    cudaMemsetAsync(acc, 0, npix * 16, nullptr);
+    int rc = lrt_render(sc, sensor, film, rp, acc, nullptr);
+    if (rc == LRT_OK) rc = lrt_film_develop_rgb((int64_t) npix, acc, rgb, nullptr);
+    if (rc == LRT_OK) { cudaError_t e = cudaMemcpy(rgb_out, rgb, npix * 12, cudaMemcpyDeviceToHost); if (e != cudaSuccess) rc = cuda_fail(e, "copy back"); }
+    cudaFree(acc); cudaFree(rgb);
+    return rc;
+}
+
+}  // extern "C"

@@ -180,28 +180,6 @@ int lrt_sensor::upload() {
 // ================================================================================ kernels
 namespace lrt {
 
-// perspective pinhole (src/sensors/perspective.cpp sample_ray): near_p = s2c * (u,v,0), d = normalize(near_p)
-LRT_HD CameraRay persp_sample_ray(const LensSystem &L, float u, float v) {
-    const float *m = L.persp_s2c;
-    float x = m[0] * u + m[1] * v + m[3], y = m[4] * u + m[5] * v + m[7], z = m[8] * u + m[9] * v + m[11],
-          w = m[12] * u + m[13] * v + m[15];
-    float iw = 1.f / w;
-    float3 d = normalize(make_float3(x * iw, y * iw, z * iw));
-    const float *t = L.to_world;
-    float3 o = make_float3(t[3], t[7], t[11]);
-    float3 dw = make_float3(t[0] * d.x + t[1] * d.y + t[2] * d.z, t[4] * d.x + t[5] * d.y + t[6] * d.z,
-                            t[8] * d.x + t[9] * d.y + t[10] * d.z);
-    float inv_z = 1.f / d.z;
-    float near_t = L.near_clip * inv_z, far_t = L.far_clip * inv_z;
-    CameraRay r;
-    r.o = o + dw * near_t; r.d = dw; r.maxt = far_t - near_t; r.weight = 1.f; r.active = true; r.d_local = d;
-    return r;
-}
-
-LRT_HD CameraRay sensor_sample_ray(const LensSystem &L, const LensIf *ifs, float u, float v, float a, float b) {
-    return L.kind == 0 ? lens_sample_ray(L, ifs, u, v, a, b) : persp_sample_ray(L, u, v);
-}
-
 __global__ void __launch_bounds__(256) k_sample_ray(const LensSystem *__restrict__ Lg, int64_t n,
                                                      const float2 *__restrict__ pos, const float2 *__restrict__ ap,
                                                      float *__restrict__ out10) {

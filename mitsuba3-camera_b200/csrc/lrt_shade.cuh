@@ -1,0 +1,185 @@
+// lensrt — surface interaction, BSDFs, area emitters and the per-bounce logic of the path integrator.
+// Replaces: Mesh::compute_surface_interaction (src/render/mesh.cpp:1376-1500, flat-shaded triangles),
+// SurfaceInteraction::initialize_sh_frame / finalize (include/mitsuba/render/interaction.h:245-255,464-484),
+// Interaction::spawn_ray / spawn_ray_to / offset_p (:133-162), coordinate_system (core/vector.h:116-136),
+// SmoothDiffuse (src/bsdfs/diffuse.cpp:101-175), SmoothConductor (conductor.cpp:248-310 + fresnel_conductor
+// render/fresnel.h:93-117), SmoothDielectric (dielectric.cpp sample), TwoSidedBRDF (twosided.cpp),
+// AreaLight (src/emitters/area.cpp:83-211) on rectangles (src/shapes/rectangle.cpp:166-185),
+// Shape::sample_direction / pdf_direction (src/render/shape.cpp:358-388),
+// Scene::sample_emitter_direction / pdf_emitter_direction (src/render/scene.cpp:227-366).
+#pragma once
+#include "lrt_trace.cuh"
+#include "lrt_lens.cuh"
+
+namespace lrt {
+
+enum : int { BSDF_DIFFUSE = 0, BSDF_CONDUCTOR = 1, BSDF_DIELECTRIC = 2 };
+
+struct SceneView {
+    BvhView bvh;
+    const int *shape_bsdf, *shape_emitter;
+    const float4 *bsdfs;      // 4 x float4: [type, twosided, refl.rgb | eta.rgb, k.rgb | trans.rgb, eta_s, -]
+    const float4 *emitters;   // 5 x float4: [radiance.rgb, shape | c.xyz, inv_area | ex.xyz | ey.xyz | n.xyz]
+    int n_emitters;
+};
+
+struct Surface {
+    float3 p, n, s, t;   // position, (geometric = shading) normal, tangent frame
+    float3 wi;           // incident direction in the local frame
+    int shape;
+    LRT_D float3 to_local(float3 v) const { return make_float3(dot(v, s), dot(v, t), dot(v, n)); }
+    LRT_D float3 to_world(float3 v) const { return s * v.x + t * v.y + n * v.z; }
+};
+
+LRT_D void coordinate_system(float3 n, float3 &s, float3 &t) {
+    float sign = copysignf(1.f, n.z);
+    float a = -1.f / (sign + n.z), b = n.x * n.y * a;
+    s = make_float3(copysignf(1.f, n.z) * (n.x * n.x * a) + 1.f, copysignf(1.f, n.z) * b, n.z >= 0.f ? -n.x : n.x);
+    t = make_float3(b, n.y * (n.y * a) + sign, -n.y);
+}
+
+LRT_D Surface make_surface(const SceneView &sc, const RayHit &h, float3 ray_d) {
+    const float4 *tp = sc.bvh.tris + 3 * (size_t) h.tri;
+    float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);
+    float3 p0 = make_float3(a.x, a.y, a.z), p1 = make_float3(a.w, b.x, b.y), p2 = make_float3(b.z, b.w, c.x);
+    Surface si;
+    float b1 = h.u, b2 = h.v, b0 = 1.f - b1 - b2;
+    si.p = p0 * b0 + (p1 * b1 + p2 * b2);
+    si.n = normalize(cross(p1 - p0, p2 - p0));
+    float3 dp_du, dp_dv; coordinate_system(si.n, dp_du, dp_dv);
+    si.s = normalize(dp_du - si.n * dot(si.n, dp_du));
+    si.t = cross(si.n, si.s);
+    si.wi = si.to_local(-ray_d);
+    si.shape = __float_as_int(c.y);
+    return si;
+}
+
+LRT_D float3 offset_p(float3 p, float3 n, float3 d) {
+    float mag = (1.f + fmaxf(fabsf(p.x), fmaxf(fabsf(p.y), fabsf(p.z)))) * kRayEpsilon;
+    mag = copysignf(mag, dot(n, d));
+    return p + n * mag;
+}
+
+LRT_D float fresnel_conductor(float ci, float eta_r, float eta_i) {
+    float ci2 = ci * ci, si2 = 1.f - ci2, si4 = si2 * si2;
+    float temp_1 = eta_r * eta_r - eta_i * eta_i - si2;
+    float a2pb2 = sqrtf(fmaxf(temp_1 * temp_1 + 4.f * eta_i * eta_i * eta_r * eta_r, 0.f));
+    float a = sqrtf(fmaxf(.5f * (a2pb2 + temp_1), 0.f));
+    float term_1 = a2pb2 + ci2, term_2 = 2.f * ci * a;
+    float r_s = (term_1 - term_2) / (term_1 + term_2);
+    float term_3 = a2pb2 * ci2 + si4, term_4 = term_2 * si2;
+    float r_p = r_s * (term_3 - term_4) / (term_3 + term_4);
+    return 0.5f * (r_s + r_p);
+}
+
+// fresnel.h:35-84 (relaxed arithmetic; the lens uses the strict copy in lrt_lens.cuh)
+LRT_D void fresnel_dielectric(float ci, float eta, float &r, float &ct, float &eta_it, float &eta_ti) {
+    bool outside = ci >= 0.f;
+    float rcp_eta = 1.f / eta;
+    eta_it = outside ? eta : rcp_eta; eta_ti = outside ? rcp_eta : eta;
+    float ct2 = 1.f - (1.f - ci * ci) * (eta_ti * eta_ti);
+    float cia = fabsf(ci), cta = sqrtf(fmaxf(ct2, 0.f));
+    float a_s = (cia - eta_it * cta) / (cia + eta_it * cta);
+    float a_p = (cta - eta_it * cia) / (cta + eta_it * cia);
+    r = 0.5f * (a_s * a_s + a_p * a_p);
+    if (eta == 1.f) r = 0.f; else if (cia == 0.f) r = 1.f;
+    ct = ci >= 0.f ? -cta : cta;
+}
+
+struct BsdfResult {
+    float3 val; float pdf;          // eval_pdf(wo)
+    float3 wo; float spdf, seta;    // sample
+    float3 weight; bool delta;
+};
+
+// BSDF::eval_pdf_sample: eval/pdf for the emitter direction `wo` and a fresh sample from (s1, s2)
+LRT_D BsdfResult bsdf_eval_pdf_sample(const SceneView &sc, int bsdf_id, float3 wi, float3 wo, float s1, float s2x, float s2y) {
+    const float4 *bp = sc.bsdfs + 4 * (size_t) bsdf_id;
+    float4 b0 = __ldg(bp), b1 = __ldg(bp + 1), b2 = __ldg(bp + 2), b3 = __ldg(bp + 3);
+    int type = (int) b0.x; bool twosided = b0.y != 0.f;
+    float3 refl = make_float3(b0.z, b0.w, b1.x);
+    BsdfResult o;
+    o.val = make_float3(0, 0, 0); o.pdf = 0.f; o.wo = make_float3(0, 0, 0); o.spdf = 0.f; o.seta = 1.f;
+    o.weight = make_float3(0, 0, 0); o.delta = false;
+    bool flip = twosided && wi.z < 0.f;
+    if (flip) { wi.z = -wi.z; wo.z = -wo.z; }
+    if (type == BSDF_DIFFUSE) {
+        float ci = wi.z, co = wo.z;
+        if (ci > 0.f && co > 0.f) { o.val = refl * (kInvPi * co); o.pdf = kInvPi * co; }
+        if (ci > 0.f) {
+            float px, py; square_to_disk_concentric(s2x, s2y, px, py);   // same (strict) warp as the aperture
+            float z = sqrtf(fmaxf(1.f - (px * px + py * py), 0.f));
+            o.wo = make_float3(px, py, z); o.spdf = kInvPi * z;
+            if (o.spdf > 0.f) o.weight = refl;
+        }
+    } else if (type == BSDF_CONDUCTOR) {
+        float ci = wi.z; o.delta = true;
+        if (ci > 0.f) {
+            o.wo = make_float3(-wi.x, -wi.y, wi.z); o.spdf = 1.f;
+            o.weight = make_float3(refl.x * fresnel_conductor(ci, b1.y, b2.x), refl.y * fresnel_conductor(ci, b1.z, b2.y),
+                                   refl.z * fresnel_conductor(ci, b1.w, b2.z));
+        }
+    } else {
+        float ci = wi.z, r_i, ct, eit, eti;
+        fresnel_dielectric(ci, b3.z, r_i, ct, eit, eti);
+        bool sel_r = s1 <= r_i;
+        o.delta = true; o.spdf = sel_r ? r_i : 1.f - r_i;
+        o.wo = sel_r ? make_float3(-wi.x, -wi.y, wi.z) : make_float3(-eti * wi.x, -eti * wi.y, ct);
+        o.seta = sel_r ? 1.f : eit;
+        o.weight = sel_r ? refl : make_float3(b2.w, b3.x, b3.y) * (eti * eti);
+    }
+    if (flip) o.wo.z = -o.wo.z;
+    return o;
+}
+
+LRT_D bool bsdf_is_smooth(const SceneView &sc, int bsdf_id) { return (int) __ldg(sc.bsdfs + 4 * (size_t) bsdf_id).x == BSDF_DIFFUSE; }
+
+struct EmitterSample { float3 p, n, d; float dist, pdf; float3 weight; };
+
+// Scene::sample_emitter_direction (scene.cpp:299-353) without the visibility test (done by the caller)
+LRT_D EmitterSample sample_emitter_direction(const SceneView &sc, float3 ref_p, float sx, float sy) {
+    EmitterSample es; es.pdf = 0.f; es.weight = make_float3(0, 0, 0); es.p = es.n = es.d = make_float3(0, 0, 0); es.dist = 0.f;
+    int count = sc.n_emitters;
+    if (count == 0) return es;
+    int index = 0; float emitter_weight = 1.f, pmf = 1.f;
+    if (count > 1) {
+        float cf = (float) count, scaled = sx * cf;
+        index = min((int) scaled, count - 1);
+        emitter_weight = cf; sx = scaled - (float) index; pmf = 1.f / cf;
+    }
+    const float4 *ep = sc.emitters + 5 * (size_t) index;
+    float4 e0 = __ldg(ep), e1 = __ldg(ep + 1), e2 = __ldg(ep + 2), e3 = __ldg(ep + 3), e4 = __ldg(ep + 4);
+    float ux = sx * 2.f - 1.f, uy = sy * 2.f - 1.f;
+    es.p = make_float3(e1.x, e1.y, e1.z) + make_float3(e2.x, e2.y, e2.z) * ux + make_float3(e3.x, e3.y, e3.z) * uy;
+    es.n = make_float3(e4.x, e4.y, e4.z);
+    float3 d = es.p - ref_p;
+    float dist2 = dot(d, d);
+    es.dist = sqrtf(dist2);
+    es.d = d * (1.f / es.dist);
+    float dn = dot(es.d, es.n);
+    float x = dist2 / fabsf(dn);
+    float pdf = e1.w * (isfinite(x) ? x : 0.f);
+    bool active = dn < 0.f && pdf != 0.f;
+    if (active) {
+        es.weight = make_float3(e0.x, e0.y, e0.z) * (emitter_weight / pdf);
+        es.pdf = pdf * pmf;
+    }
+    return es;
+}
+
+// Scene::pdf_emitter_direction for a surface hit on emitter `em` seen from `ref_p`
+LRT_D float pdf_emitter_direction(const SceneView &sc, int em, float3 d, float dist, float3 n) {
+    float dp = dot(d, n);
+    if (!(dp < 0.f)) return 0.f;
+    float inv_area = __ldg(sc.emitters + 5 * (size_t) em + 1).w;
+    float adp = fabsf(dp);
+    float pdf = inv_area * (adp != 0.f ? dist * dist / adp : 0.f);
+    return sc.n_emitters > 1 ? pdf / (float) sc.n_emitters : pdf;
+}
+
+LRT_D float mis_weight(float a, float b) {
+    a *= a; b *= b; float w = a / (a + b);
+    return isfinite(w) ? w : 0.f;
+}
+
+}  // namespace lrt

@@ -151,3 +151,51 @@ def cam_trace(L, prefix, h, od, from_world):
 
 def bits(a):
     return np.ascontiguousarray(a, f32).view(np.uint32)
+
+
+# ------------------------------------------------------------------------------------------------ scenes / render
+def orc_scene(a):
+    """a: dict of flat arrays (mitsuba3-camera_b200/scene.py SceneData.arrays()) -> oracle scene handle."""
+    L = oracle()
+    L.orc_scene_create.restype = C.c_void_p
+    keep = {k: np.ascontiguousarray(v) for k, v in a.items()}
+    h = L.orc_scene_create(C.c_int(len(keep["vertices"])), fp(keep["vertices"]), C.c_int(len(keep["indices"])), ip(keep["indices"]),
+                           ip(keep["tri_shape"]), C.c_int(len(keep["shape_bsdf"])), ip(keep["shape_bsdf"]), ip(keep["shape_emitter"]),
+                           C.c_int(len(keep["bsdfs"])), fp(keep["bsdfs"]), C.c_int(len(keep["emitters"])), fp(keep["emitters"]))
+    return C.c_void_p(h)
+
+
+def orc_intersect(scene_h, o, d, maxt, any_hit=False):
+    L = oracle()
+    n = len(o)
+    od = np.ascontiguousarray(np.concatenate([o, d, np.broadcast_to(np.asarray(maxt, f32).reshape(-1, 1), (n, 1))], 1), f32)
+    out = np.zeros((n, 4), f32)
+    L.orc_scene_intersect(scene_h, C.c_int(int(any_hit)), C.c_int64(n), fp(od), fp(out))
+    return out
+
+
+def orc_render(scene_h, film, spp, seed=0, max_depth=8, rr_depth=5, cam_h=None, fov=45.0, to_world=EYE, near=1e-2, far=1e4,
+               filter_kind=2, filter_param=0.0, idx_range=None):
+    """film: FilmSpec. Returns (storage float64 [ch, cw, 4], lens_miss_count)."""
+    L = oracle()
+    cw, ch, cx, cy = (int(v) for v in film.crop)
+    st = np.zeros((ch, cw, 4), np.float64)
+    miss = C.c_int64(0)
+    tw = np.ascontiguousarray(to_world, f32)
+    total = cw * ch * spp
+    b, e = idx_range if idx_range else (0, total)
+    L.orc_render(scene_h, cam_h, c_f(fov), fp(tw), c_f(near), c_f(far), C.c_int(film.width), C.c_int(film.height),
+                 C.c_int(cw), C.c_int(ch), C.c_int(cx), C.c_int(cy), C.c_int(filter_kind), c_f(filter_param), C.c_uint32(seed),
+                 C.c_int(spp), C.c_int(max_depth), C.c_int(rr_depth), C.c_int64(b), C.c_int64(e),
+                 st.ctypes.data_as(C.POINTER(C.c_double)), C.byref(miss))
+    return st, miss.value
+
+
+def develop(storage):
+    w = storage[..., 3:4]
+    return (storage[..., :3] / np.where(w == 0, 1.0, w)).astype(f32)
+
+
+def rel_rmse(a, b):
+    a = np.asarray(a, np.float64); b = np.asarray(b, np.float64)
+    return float(np.sqrt(np.mean((a - b) ** 2)) / max(np.sqrt(np.mean(b ** 2)), 1e-12))

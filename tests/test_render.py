@@ -1,0 +1,223 @@
+"""Integrator step. CPU: known-answer checks of the oracle's path tracer. GPU: BVH traversal and full renders
+(pinhole and realistic lens) through the C ABI against the oracle at matched seeds/spp.
+
+Stated image tolerance: relative RMSE <= 2e-3 of the developed image at matched spp and seed (the sample
+streams are identical, so the residual is float rounding of traversal/shading plus the rare path whose
+branch flips on a rounding difference; measured values are ~1e-5..1e-4)."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from oracle_lib import *  # noqa
+
+ld = load_lens_designs()
+IMG_TOL = 2e-3
+
+
+def cornell(mi, res=64, spp=16, sensor=None):
+    d = mi.cornell_box()
+    d["sensor"]["film"]["width"] = d["sensor"]["film"]["height"] = res
+    d["sensor"]["sampler"]["sample_count"] = spp
+    if sensor is not None:
+        film, smp = d["sensor"]["film"], d["sensor"]["sampler"]
+        d["sensor"] = dict(sensor, film=film, sampler=smp)
+    return d
+
+
+def scene_arrays(mi, d):
+    """The flat arrays the product would upload (built without touching the GPU)."""
+    import copy
+    sc = mi.scene
+    data = sc.SceneData()
+    named = {}
+    for k, v in d.items():
+        if isinstance(v, dict) and v.get("type") in ("diffuse", "conductor", "dielectric", "twosided"):
+            named[k] = data.add_bsdf(k, sc.bsdf_row(v))
+    for k, v in d.items():
+        if isinstance(v, dict) and v.get("type") in ("rectangle", "cube", "mesh"):
+            tw = v.get("to_world"); tw = tw if isinstance(tw, mi.Transform4f) else mi.Transform4f(tw)
+            if v["type"] == "rectangle":
+                verts, faces = sc._rect_mesh(tw)
+            elif v["type"] == "cube":
+                verts, faces = sc._cube_mesh(tw)
+            else:
+                verts, faces = tw.transform_affine(np.asarray(v["vertices"], f32)), np.asarray(v["faces"], np.int32)
+            b = v["bsdf"]
+            bid = named[b["id"]] if b.get("type") == "ref" else data.add_bsdf(k + ".bsdf", sc.bsdf_row(b))
+            em = v.get("emitter")
+            emitter = None
+            if em:
+                emitter = {"radiance": sc._rgb(em["radiance"], [1, 1, 1]), "center": tw.transform_affine(np.zeros(3, f32)),
+                           "ex": tw.transform_vector(np.array([1, 0, 0], f32)), "ey": tw.transform_vector(np.array([0, 1, 0], f32))}
+            data.add_shape(k, verts, faces, bid, emitter)
+    return data.arrays()
+
+
+# ------------------------------------------------------------------------------------------------ CPU
+def test_cornell_scene_data(mi):
+    a = scene_arrays(mi, mi.cornell_box())
+    assert a["indices"].shape == (6 * 2 + 2 * 12, 3) and len(a["shape_bsdf"]) == 8
+    assert len(a["emitters"]) == 1 and a["shape_emitter"].tolist().count(-1) == 7
+    # the light faces down (rectangle normal = to_world * +z)
+    e = a["emitters"][0]
+    assert np.allclose(np.cross(e[7:10], e[10:13]) / np.linalg.norm(np.cross(e[7:10], e[10:13])), [0, -1, 0], atol=1e-6)
+
+
+def test_oracle_intersect_vs_bruteforce(mi):
+    rng = np.random.default_rng(3)
+    nt = 500
+    verts = rng.random((nt * 3, 3)).astype(f32)
+    verts[1::3] = verts[0::3] + (rng.random((nt, 3)).astype(f32) - 0.5) * 0.2
+    verts[2::3] = verts[0::3] + (rng.random((nt, 3)).astype(f32) - 0.5) * 0.2
+    a = dict(vertices=verts, indices=np.arange(nt * 3, dtype=np.int32).reshape(-1, 3), tri_shape=np.zeros(nt, np.int32),
+             shape_bsdf=np.zeros(1, np.int32), shape_emitter=-np.ones(1, np.int32),
+             bsdfs=np.zeros((1, 16), f32), emitters=np.zeros((0, 16), f32))
+    h = orc_scene(a)
+    n = 2000
+    o = (rng.random((n, 3)).astype(f32) - 0.5) * 3 + 0.5
+    d = rng.standard_normal((n, 3)).astype(f32); d /= np.linalg.norm(d, axis=1, keepdims=True)
+    got = orc_intersect(h, o, d, np.float32(3.4e38))
+    # numpy Moeller-Trumbore in float64 over all triangles
+    p0, p1, p2 = (verts[i::3].astype(np.float64) for i in range(3))
+    e1, e2 = p1 - p0, p2 - p0
+    best = np.full(n, np.inf)
+    for i in range(n):
+        pv = np.cross(d[i].astype(np.float64), e2); det = (e1 * pv).sum(1)
+        tv = o[i].astype(np.float64) - p0; u = (tv * pv).sum(1) / det
+        qv = np.cross(tv, e1); v = (qv * d[i].astype(np.float64)).sum(1) / det; t = (e2 * qv).sum(1) / det
+        ok = (u >= 0) & (v >= 0) & (u + v <= 1) & (t >= 0)
+        if ok.any():
+            best[i] = t[ok].min()
+    hit = np.isfinite(best)
+    assert ((got[:, 3] >= 0) == hit).mean() > 0.999          # grazing-edge rays may differ between f32 and f64
+    both = hit & (got[:, 3] >= 0)
+    assert np.allclose(got[both, 0], best[both], rtol=1e-4, atol=1e-5)
+
+
+def test_oracle_emitter_seen_directly(mi):
+    # a camera staring at an area light sees exactly its radiance (path.cpp:158-174 with prev_bsdf_delta = true)
+    T = mi.Transform4f
+    d = {"type": "scene",
+         "light": {"type": "rectangle", "to_world": T.translate([0, 0, 0]).scale(10.0), "bsdf": {"type": "diffuse"},
+                   "emitter": {"type": "area", "radiance": {"type": "rgb", "value": [2.0, 3.0, 5.0]}}}}
+    h = orc_scene(scene_arrays(mi, d))
+    tw = T.look_at(origin=[0, 0, 4], target=[0, 0, 0], up=[0, 1, 0]).matrix
+    st, _ = orc_render(h, FilmSpec(8, 8), 4, fov=30.0, to_world=tw)
+    img = develop(st)
+    assert np.allclose(img, [2.0, 3.0, 5.0], rtol=1e-5)
+
+
+def test_oracle_cornell_statistics(mi):
+    """Energy sanity of the CPU path tracer: the Cornell box is brighter under the light than in the corners,
+    red/green walls bleed, and two seeds agree within Monte Carlo noise."""
+    a = scene_arrays(mi, mi.cornell_box())
+    h = orc_scene(a)
+    tw = mi.cornell_box()["sensor"]["to_world"].matrix
+    imgs = [develop(orc_render(h, FilmSpec(32, 32), 64, seed=s, fov=39.3077, to_world=tw, near=1e-3, far=100.0)[0]) for s in (0, 1)]
+    m = imgs[0]
+    assert 0.1 < m.mean() < 1.5
+    assert m[:, :4, 0].mean() > 1.5 * m[:, :4, 1].mean()       # left wall is red
+    assert m[:, -4:, 1].mean() > 1.5 * m[:, -4:, 0].mean()     # right wall is green
+    assert rel_rmse(imgs[0], imgs[1]) < 0.35
+
+
+# ------------------------------------------------------------------------------------------------ GPU
+@pytest.mark.gpu
+@pytest.mark.parametrize("nt", [1, 3, 200, 20000])
+def test_gpu_bvh_vs_oracle(mi, nt):
+    import torch
+    rng = np.random.default_rng(nt)
+    verts = rng.random((nt * 3, 3)).astype(f32)
+    s = 0.5 / max(nt, 1) ** (1 / 3)
+    verts[1::3] = verts[0::3] + (rng.random((nt, 3)).astype(f32) - 0.5) * s * 2
+    verts[2::3] = verts[0::3] + (rng.random((nt, 3)).astype(f32) - 0.5) * s * 2
+    faces = np.arange(nt * 3, dtype=np.int32).reshape(-1, 3)
+    d = {"type": "scene", "soup": {"type": "mesh", "vertices": verts, "faces": faces, "bsdf": {"type": "diffuse"}}}
+    sc = mi.load_dict(d)
+    h = orc_scene(sc.arrays)
+    n = 100000
+    o = (rng.random((n, 3)).astype(f32) - 0.5) * 2.5 + 0.5
+    dd = (0.5 + (rng.random((n, 3)) - 0.5) * 0.8 - o).astype(f32); dd /= np.linalg.norm(dd, axis=1, keepdims=True)
+    maxt = np.where(rng.random(n) < 0.3, rng.random(n) * 2, 3.4e38).astype(f32)
+    want = orc_intersect(h, o, dd, maxt)
+    t, u, v, prim = (x.cpu().numpy() for x in sc.ray_intersect(o, dd, maxt))
+    hit_w, hit_g = want[:, 3] >= 0, prim >= 0
+    assert (hit_w == hit_g).mean() > 0.9995
+    both = hit_w & hit_g
+    assert np.allclose(t[both], want[both, 0], rtol=2e-5, atol=1e-6)
+    same = prim[both] == want[both, 3].astype(np.int64)
+    assert same.mean() > 0.999
+    assert np.allclose(u[both][same], want[both, 1][same], atol=2e-4) and np.allclose(v[both][same], want[both, 2][same], atol=2e-4)
+    # any-hit (ray_test) agrees with closest-hit on occlusion
+    _, _, _, prim_any = (x.cpu().numpy() for x in sc.ray_intersect(o, dd, maxt, any_hit=True))
+    assert ((prim_any >= 0) == hit_g).all()
+    info = sc.info()
+    assert info["triangles"] == nt
+
+
+@pytest.mark.gpu
+def test_gpu_cornell_box_vs_oracle(mi):
+    """BASELINE config 1 shape (Cornell box, path, max_depth as given) at reduced size, pinhole sensor."""
+    d = cornell(mi, res=64, spp=16)
+    d["integrator"]["max_depth"] = 6
+    sc = mi.load_dict(d)
+    img = mi.render(sc, seed=0).cpu().numpy()
+    st, _ = orc_render(orc_scene(sc.arrays), FilmSpec(64, 64), 16, seed=0, max_depth=6, fov=39.3077,
+                       to_world=d["sensor"]["to_world"].matrix, near=1e-3, far=100.0)
+    want = develop(st)
+    err = rel_rmse(img, want)
+    assert err < IMG_TOL, err
+    assert sc.stats()["samples"] == 64 * 64 * 16
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("design", ["doublet", "gauss", "exp1a"])
+@pytest.mark.parametrize("rfilter", ["gaussian", "tent", "box"])
+def test_gpu_cornell_through_realistic_lens(mi, design, rfilter):
+    T = mi.Transform4f
+    tw = T.look_at(origin=[0, 0, 3.9], target=[0, 0, 0], up=[0, 1, 0])
+    sensor = {"type": "realisticlens", "lens_design": design, "to_world": tw, "object_distance": 3.9, "near_clip": 1e-3, "far_clip": 100.0}
+    d = cornell(mi, res=48, spp=8, sensor=sensor)
+    d["sensor"]["film"]["rfilter"] = {"type": rfilter}
+    d["sensor"]["film"]["diagonal"] = 30.0
+    d["integrator"]["max_depth"] = 5
+    sc = mi.load_dict(d)
+    img = mi.render(sc, seed=3).cpu().numpy()
+    cam = orc_camera(ld.design(design, {"object_distance": 3.9}), FilmSpec(48, 48, None, 30.0), to_world=tw.matrix, near=1e-3, far=100.0,
+                     object_distance=3.9)
+    st, miss = orc_render(orc_scene(sc.arrays), FilmSpec(48, 48, None, 30.0), 8, seed=3, max_depth=5, cam_h=cam,
+                          filter_kind={"box": 0, "tent": 1, "gaussian": 2}[rfilter])
+    want = develop(st)
+    assert sc.stats()["lens_misses"] == miss, "lens ray-miss count differs from the oracle"
+    err = rel_rmse(img, want)
+    assert want.mean() > 1e-3 and err < IMG_TOL, err
+
+
+@pytest.mark.gpu
+def test_gpu_sharding_and_chunking_invariance(mi):
+    """Samples keep their PCG32 stream under any tile/chunk/shard split: images agree to float summation order."""
+    import torch
+    d = cornell(mi, res=40, spp=12)
+    sc = mi.load_dict(d)
+    full = mi.render(sc, seed=1, develop=False)
+    parts = torch.zeros_like(full)
+    for r in range(3):
+        mi.render(sc, seed=1, develop=False, shard=(r, 3), storage=parts)
+    assert torch.allclose(full, parts, rtol=1e-5, atol=1e-6)
+    assert torch.allclose(full[..., 3].sum(), torch.tensor(float(40 * 40 * 12) * 1.0, device="cuda"), rtol=0.05)
+
+
+@pytest.mark.gpu
+def test_gpu_conductor_and_dielectric(mi):
+    T = mi.Transform4f
+    d = cornell(mi, res=48, spp=16)
+    d["small-box"]["bsdf"] = {"type": "conductor", "eta": [0.2, 0.92, 1.1], "k": [3.9, 2.45, 2.14]}
+    d["large-box"]["bsdf"] = {"type": "dielectric", "int_ior": 1.5, "ext_ior": 1.0}
+    d["integrator"]["max_depth"] = 7
+    sc = mi.load_dict(d)
+    img = mi.render(sc, seed=2).cpu().numpy()
+    st, _ = orc_render(orc_scene(sc.arrays), FilmSpec(48, 48), 16, seed=2, max_depth=7, fov=39.3077,
+                       to_world=d["sensor"]["to_world"].matrix, near=1e-3, far=100.0)
+    err = rel_rmse(img, develop(st))
+    assert err < 5 * IMG_TOL, err    # delta lobes amplify rounding differences of the reflected direction
