@@ -161,8 +161,9 @@ int lrt_render(const lrt_scene *scene, const lrt_sensor *sensor, const lrt_film_
 /* mi.render(scene) for host callers: render + HDRFilm::develop; rgb_out [size_y,size_x,3] host memory. */
 int lrt_render_host(const lrt_scene *scene, const lrt_sensor *sensor, const lrt_film_desc *film,
                     const lrt_render_params *params, float *rgb_out);
-/* counters of the last render on this scene: samples, lens misses, rays traced, path-loop iterations */
-int lrt_render_stats(const lrt_scene *scene, uint64_t *out4);
+/* counters of the last render on this scene: samples, lens misses, rays traced, path-loop iterations,
+ * BVH nodes fetched (80 B each), triangles tested (48 B each) */
+int lrt_render_stats(const lrt_scene *scene, uint64_t *out6);
 
 #ifdef __cplusplus
 }

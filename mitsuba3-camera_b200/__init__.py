@@ -9,7 +9,8 @@ from .sensors import Film, Sensor, RealisticLensCamera, PerspectiveCamera
 __version__ = "0.1.0"
 from .transform import Transform4f, ScalarTransform4f
 from .scene import (Scene, SceneData, PathIntegrator, IndependentSampler, load_dict, render, cornell_box, bsdf_row,
-                    film_desc, RenderParams, SceneDesc, load_obj, load_ply)
+                    film_desc, RenderParams, SceneDesc, load_obj, load_ply, scene_data_from_dict)
+from . import scene, workloads
 
 _variant = "b200_ad_rgb"
 

@@ -31,7 +31,7 @@ struct RenderArgs {
     int pad, smem_w, smem_h;
     unsigned long long *counter;
     float *accum;
-    unsigned long long *stats;     // [0] samples, [1] lens misses, [2] rays traced, [3] bounces
+    unsigned long long *stats;     // [0] samples, [1] lens misses, [2] rays, [3] bounces, [4] BVH nodes fetched, [5] triangles tested
 };
 
 __global__ void __launch_bounds__(kCtaThreads) k_render(RenderArgs A) {
@@ -49,7 +49,7 @@ __global__ void __launch_bounds__(kCtaThreads) k_render(RenderArgs A) {
     const int tile_elems = A.smem_w * A.smem_h * 4;
     const float scale_x = 1.f / (float) F.size_x, scale_y = 1.f / (float) F.size_y;
     const float offs_x = -(float) F.off_x * scale_x, offs_y = -(float) F.off_y * scale_y;
-    unsigned long long n_samples = 0, n_miss = 0, n_rays = 0, n_bounces = 0;
+    unsigned long long n_samples = 0, n_miss = 0, n_rays = 0, n_bounces = 0, n_nodes = 0, n_tris = 0;
 
     while (true) {
         __syncthreads();
@@ -104,7 +104,8 @@ __global__ void __launch_bounds__(kCtaThreads) k_render(RenderArgs A) {
             } else if (have_path) {
                 // ---- one iteration of PathIntegrator::sample's loop (path.cpp:142-281)
                 n_bounces++; n_rays++;
-                RayHit h = bvh_intersect<false>(A.sc.bvh, ro, rd, rmaxt);
+                unsigned work = 0;
+                RayHit h = bvh_intersect<false>(A.sc.bvh, ro, rd, rmaxt, work);
                 bool hit = h.tri >= 0;
                 Surface si;
                 if (hit) si = make_surface(A.sc, h, rd);
@@ -133,7 +134,7 @@ __global__ void __launch_bounds__(kCtaThreads) k_render(RenderArgs A) {
                             float3 so = offset_p(si.p, si.n, es.p - si.p);
                             float3 sd = es.p - so; float sdist = sqrtf(dot(sd, sd)); sd = sd * (1.f / sdist);
                             n_rays++;
-                            RayHit sh = bvh_intersect<true>(A.sc.bvh, so, sd, sdist * (1.f - kShadowEpsilon));
+                            RayHit sh = bvh_intersect<true>(A.sc.bvh, so, sd, sdist * (1.f - kShadowEpsilon), work);
                             if (sh.tri >= 0) es.pdf = 0.f;
                         }
                         active_em = es.pdf != 0.f;
@@ -153,6 +154,7 @@ __global__ void __launch_bounds__(kCtaThreads) k_render(RenderArgs A) {
                     if (rr_active) throughput *= 1.f / rr_prob;
                     alive = (!rr_active || rr_sample < rr_prob) && tmax != 0.f;
                 }
+                n_nodes += work & 0xffffu; n_tris += work >> 16;
                 if (!alive) {
                     have_path = false; splat = true;
                     if (valid_ray) value = result * cam_weight;
@@ -202,9 +204,11 @@ __global__ void __launch_bounds__(kCtaThreads) k_render(RenderArgs A) {
         for (int o = 16; o > 0; o >>= 1) {
             n_samples += __shfl_down_sync(0xffffffffu, n_samples, o); n_miss += __shfl_down_sync(0xffffffffu, n_miss, o);
             n_rays += __shfl_down_sync(0xffffffffu, n_rays, o); n_bounces += __shfl_down_sync(0xffffffffu, n_bounces, o);
+            n_nodes += __shfl_down_sync(0xffffffffu, n_nodes, o); n_tris += __shfl_down_sync(0xffffffffu, n_tris, o);
         }
         if (lane == 0) {
             atomicAdd(A.stats, n_samples); atomicAdd(A.stats + 1, n_miss); atomicAdd(A.stats + 2, n_rays); atomicAdd(A.stats + 3, n_bounces);
+            atomicAdd(A.stats + 4, n_nodes); atomicAdd(A.stats + 5, n_tris);
         }
     }
 }
@@ -214,7 +218,8 @@ __global__ void __launch_bounds__(128) k_intersect(SceneView sc, int any_hit, in
     for (int64_t i = blockIdx.x * (int64_t) blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) {
         const float *r = od7 + 7 * i;
         float3 o = make_float3(r[0], r[1], r[2]), d = make_float3(r[3], r[4], r[5]);
-        RayHit h = any_hit ? bvh_intersect<true>(sc.bvh, o, d, r[6]) : bvh_intersect<false>(sc.bvh, o, d, r[6]);
+        unsigned work = 0;
+        RayHit h = any_hit ? bvh_intersect<true>(sc.bvh, o, d, r[6], work) : bvh_intersect<false>(sc.bvh, o, d, r[6], work);
         float *q = out4 + 4 * i;
         q[0] = h.t; q[1] = h.u; q[2] = h.v;
         q[3] = h.tri >= 0 ? (float) __float_as_int(__ldg(sc.bvh.tris + 3 * (size_t) h.tri + 2).z) : -1.f;

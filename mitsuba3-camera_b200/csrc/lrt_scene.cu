@@ -93,10 +93,10 @@ int lrt_render(const lrt_scene *sc, const lrt_sensor *sensor, const lrt_film_des
     return launch_render(sc, const_cast<lrt_sensor *>(sensor), film, rp, accum_dev, (cudaStream_t) stream);
 }
 
-int lrt_render_stats(const lrt_scene *sc, uint64_t *out4) {
+int lrt_render_stats(const lrt_scene *sc, uint64_t *out6) {
     LRT_NEED_DEVICE();
-    LRT_REQUIRE(sc && out4, "null argument");
-    LRT_CUDA(cudaMemcpy(out4, sc->d_counter + 1, 4 * sizeof(uint64_t), cudaMemcpyDeviceToHost));
+    LRT_REQUIRE(sc && out6, "null argument");
+    LRT_CUDA(cudaMemcpy(out6, sc->d_counter + 1, 6 * sizeof(uint64_t), cudaMemcpyDeviceToHost));
     return LRT_OK;
 }
 

@@ -10,11 +10,13 @@
 namespace lrt {
 
 struct RayHit { float t, u, v; int tri; };   // tri = index into the reordered triangle array, -1 = miss
+// `work` accumulates the algorithmic traffic of a traversal: nodes fetched (low 16 bits) and triangles tested
+// (high 16 bits); the render kernel sums it into its statistics (bench.py's roofline `achieved`).
 
 LRT_D float q2f(uint32_t w, int byte) { return (float) ((w >> (8 * byte)) & 0xffu); }
 
 template <bool ANY_HIT>
-LRT_D RayHit bvh_intersect(const BvhView &bvh, float3 o, float3 d, float tmax) {
+LRT_D RayHit bvh_intersect(const BvhView &bvh, float3 o, float3 d, float tmax, unsigned &work) {
     RayHit hit; hit.t = inf_f(); hit.u = hit.v = 0.f; hit.tri = -1;
     // guard against 0 * inf in the slab test
     const float tiny = 1e-30f;
@@ -23,7 +25,7 @@ LRT_D RayHit bvh_intersect(const BvhView &bvh, float3 o, float3 d, float tmax) {
     float3 idir = make_float3(1.f / dd.x, 1.f / dd.y, 1.f / dd.z);
     const bool nx = idir.x < 0.f, ny = idir.y < 0.f, nz = idir.z < 0.f;
 
-    constexpr int kStack = 48;
+    constexpr int kStack = 64;
     uint32_t st_ref[kStack]; float st_t[kStack];
     int sp = 0;
     uint32_t cur = 0;            // bit31 = leaf; leaf: bits 29..28 count, 27..0 first triangle
@@ -31,6 +33,7 @@ LRT_D RayHit bvh_intersect(const BvhView &bvh, float3 o, float3 d, float tmax) {
     while (true) {
         if (cur_t <= tmax) {
             if (!(cur & 0x80000000u)) {
+                work += 1u;
                 const uint4 *np = bvh.nodes + 5 * (size_t) cur;
                 uint4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
                 float sx = __uint_as_float((n0.w & 0xffu) << 23) * idir.x, sy = __uint_as_float(((n0.w >> 8) & 0xffu) << 23) * idir.y,
@@ -62,6 +65,7 @@ LRT_D RayHit bvh_intersect(const BvhView &bvh, float3 o, float3 d, float tmax) {
                 if (best != 0xffffffffu) { cur = best; cur_t = best_t; continue; }
             } else {
                 uint32_t first = cur & 0x0fffffffu, count = (cur >> 28) & 3u;
+                work += count << 16;
                 for (uint32_t k = 0; k < count; ++k) {
                     const float4 *tp = bvh.tris + 3 * (size_t) (first + k);
                     float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);

@@ -286,9 +286,9 @@ class Scene:
         return out[:, 0], out[:, 1], out[:, 2], out[:, 3].to(torch.int64)
 
     def stats(self):
-        out = (C.c_uint64 * 4)()
+        out = (C.c_uint64 * 6)()
         capi.check(capi.lib.lrt_render_stats(self.handle, out))
-        return {"samples": out[0], "lens_misses": out[1], "rays": out[2], "bounces": out[3]}
+        return {"samples": out[0], "lens_misses": out[1], "rays": out[2], "bounces": out[3], "bvh_nodes": out[4], "triangles": out[5]}
 
 
 def film_desc(film: Film, coalesce=True, normalize=False) -> FilmDesc:
@@ -352,24 +352,11 @@ _SHAPES = ("rectangle", "cube", "mesh", "obj", "ply")
 _BSDFS = ("diffuse", "conductor", "dielectric", "twosided")
 
 
-def load_dict(d: dict):
-    """mi.load_dict for: scene, realisticlens/perspective (+hdrfilm, independent, rfilters), path, diffuse/
-    conductor/dielectric/twosided, rectangle/cube/mesh/obj/ply, area."""
-    t = d.get("type")
-    if t in ("perspective", "realisticlens"):
-        return _sensor_from(d)
-    if t == "hdrfilm":
-        return _film_from(d)
-    if t == "independent":
-        return IndependentSampler(d.get("sample_count", 4), d.get("seed", 0))
-    if t in ("gaussian", "tent", "box"):
-        return ReconstructionFilter(t, float(d.get("stddev", d.get("radius", 0.0))) if t != "box" else 0.0)
-    if t == "path":
-        return PathIntegrator(d.get("max_depth", -1), d.get("rr_depth", 5), d.get("hide_emitters", False))
-    if t != "scene":
-        raise ValueError(f"plugin '{t}' is outside the hot path of this build")
+def scene_data_from_dict(d: dict):
+    """The GPU-free half of load_dict('scene'): flat geometry/material tables (SceneData) plus the sensor and
+    integrator sub-dictionaries. Also what the tests hand to the CPU oracle."""
     data = SceneData()
-    named_bsdf, sensors, integrator = {}, [], PathIntegrator()
+    named_bsdf, sensor_dicts, integ = {}, [], None
     default_bsdf = None
     for key, v in d.items():   # named BSDFs first: they are the targets of {'type': 'ref'}
         if isinstance(v, dict) and v.get("type") in _BSDFS:
@@ -379,9 +366,9 @@ def load_dict(d: dict):
             continue
         vt = v.get("type")
         if vt in ("perspective", "realisticlens"):
-            sensors.append(_sensor_from(v))
+            sensor_dicts.append(v)
         elif vt == "path":
-            integrator = load_dict(v)
+            integ = v
         elif vt in _SHAPES:
             tw = v.get("to_world")
             tw = tw if isinstance(tw, Transform4f) else Transform4f(tw)
@@ -418,7 +405,27 @@ def load_dict(d: dict):
             pass
         else:
             raise ValueError(f"plugin '{vt}' ('{key}') is outside the hot path of this build")
-    return Scene(data, sensors, integrator)
+    return data, sensor_dicts, integ
+
+
+def load_dict(d: dict):
+    """mi.load_dict for: scene, realisticlens/perspective (+hdrfilm, independent, rfilters), path, diffuse/
+    conductor/dielectric/twosided, rectangle/cube/mesh/obj/ply, area."""
+    t = d.get("type")
+    if t in ("perspective", "realisticlens"):
+        return _sensor_from(d)
+    if t == "hdrfilm":
+        return _film_from(d)
+    if t == "independent":
+        return IndependentSampler(d.get("sample_count", 4), d.get("seed", 0))
+    if t in ("gaussian", "tent", "box"):
+        return ReconstructionFilter(t, float(d.get("stddev", d.get("radius", 0.0))) if t != "box" else 0.0)
+    if t == "path":
+        return PathIntegrator(d.get("max_depth", -1), d.get("rr_depth", 5), d.get("hide_emitters", False))
+    if t != "scene":
+        raise ValueError(f"plugin '{t}' is outside the hot path of this build")
+    data, sensor_dicts, integ = scene_data_from_dict(d)
+    return Scene(data, [_sensor_from(v) for v in sensor_dicts], load_dict(integ) if integ else PathIntegrator())
 
 
 def cornell_box():
