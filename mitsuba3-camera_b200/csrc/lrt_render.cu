@@ -245,7 +245,8 @@ int launch_render(const lrt_scene *sc, lrt_sensor *sensor, const lrt_film_desc *
     A.film.coalesce = rp->spp >= 4 ? film->coalesce : 0;   // integrator.cpp:290
     const FilmParams &F = A.film;
     A.pad = F.kind == FILTER_BOX ? 0 : (F.coalesce ? F.n_half : (int) std::ceil(F.radius + .5f));
-    A.smem_w = kTileW + 2 * A.pad; A.smem_h = kTileH + 2 * A.pad;
+    // +1: pos + u (u < 1) can round up to the next integer in float32 (ulp(2048) = 2.4e-4), shifting the window by one
+    A.smem_w = kTileW + 2 * A.pad + 1; A.smem_h = kTileH + 2 * A.pad + 1;
     A.tiles_x = (F.size_x + kTileW - 1) / kTileW;
     int tiles_y = (F.size_y + kTileH - 1) / kTileH;
     long long n_tiles = (long long) A.tiles_x * tiles_y;
