@@ -80,9 +80,9 @@ struct Builder {
 };
 
 uint8_t exponent_for(float extent) {
-    // smallest e with 255 * 2^(e-127) >= extent
+    // smallest e with 253 * 2^(e-127) >= extent (one quantisation step is reserved on each side, see below)
     if (!(extent > 0.f)) return 1;
-    int e; std::frexp(extent / 255.f, &e);   // extent/255 = m * 2^e, m in [.5,1)  =>  2^e >= extent/255
+    int e; std::frexp(extent / 253.f, &e);   // extent/253 = m * 2^e, m in [.5,1)  =>  2^e >= extent/253
     int biased = e + 127;
     return (uint8_t) std::min(254, std::max(1, biased));
 }
@@ -129,10 +129,13 @@ void build_bvh8(const float *verts, const int32_t *idx, const int32_t *tri_shape
         }
         BvhNode n; memset(&n, 0, sizeof n);
         const Box &nb = root.box;
-        n.ox = nb.lo[0]; n.oy = nb.lo[1]; n.oz = nb.lo[2];
         n.ex = exponent_for(nb.hi[0] - nb.lo[0]); n.ey = exponent_for(nb.hi[1] - nb.lo[1]); n.ez = exponent_for(nb.hi[2] - nb.lo[2]);
         n.child_base = (uint32_t) queue.size(); n.tri_base = (uint32_t) tris.size();
         float sc[3] = { std::ldexp(1.f, n.ex - 127), std::ldexp(1.f, n.ey - 127), std::ldexp(1.f, n.ez - 127) };
+        // the grid starts one step below the box so that every child bound keeps a full step of slack on both
+        // sides (q_lo = floor(x) - 1 >= 0, q_hi = ceil(x) + 1 <= 255): this absorbs the float rounding of the
+        // quantisation and of the biased-FMA decode in the traversal (lrt_trace.cuh)
+        n.ox = nb.lo[0] - sc[0]; n.oy = nb.lo[1] - sc[1]; n.oz = nb.lo[2] - sc[2];
         int inner_k = 0, tri_off = 0;
         for (int i = 0; i < nch; ++i) {
             const BinNode &c = B.bn[ch[i]];
@@ -140,7 +143,6 @@ void build_bvh8(const float *verts, const int32_t *idx, const int32_t *tri_shape
             const float org[3] = { n.ox, n.oy, n.oz };
             for (int a = 0; a < 3; ++a) {
                 float lo = std::floor((c.box.lo[a] - org[a]) / sc[a]), hi = std::ceil((c.box.hi[a] - org[a]) / sc[a]);
-                // one extra step of slack guards the float rounding of (x - org)/scale and of the ray-box test
                 ql[a][i] = (uint8_t) std::min(255.f, std::max(0.f, lo - 1.f));
                 qh[a][i] = (uint8_t) std::min(255.f, std::max(0.f, hi + 1.f));
             }

@@ -69,18 +69,20 @@ __global__ void __launch_bounds__(kCtaThreads) k_render(RenderArgs A) {
         const uint32_t idx_base = (uint32_t) (py * F.size_x + px) * (uint32_t) A.spp;
         const float posx = (float) (px + F.off_x), posy = (float) (py + F.off_y);
 
-        // ---- per-lane path state
-        bool have_path = false;
+        // ---- per-lane path state. phase: 0 = needs a new sample, 1 = path segment (closest hit), 2 = shadow ray
+        int phase = 0;
         Pcg32 rng; rng.state = 0; rng.inc = 1;
-        float3 ro = make_float3(0, 0, 0), rd = make_float3(0, 0, 1); float rmaxt = 0.f;
+        float3 ro = make_float3(0, 0, 0), rd = make_float3(0, 0, 1); float rmaxt = 0.f;      // ray being traced now
+        float3 wi_w = make_float3(0, 0, 1);                                                   // direction of the path segment
         float3 throughput = make_float3(1, 1, 1), result = make_float3(0, 0, 0), prev_p = make_float3(0, 0, 0);
         float eta = 1.f, prev_pdf = 1.f, cam_weight = 0.f, spx = 0.f, spy = 0.f;
         int depth = 0; bool prev_delta = true, valid_ray = false;
+        RayHit seg; seg.t = 0.f; seg.u = seg.v = 0.f; seg.tri = -1;                           // hit of the current segment
 
         while (true) {
-            const bool need = !have_path && j < j_end;
+            const bool need = phase == 0 && j < j_end;
             const unsigned need_mask = __ballot_sync(0xffffffffu, need);
-            const unsigned live_mask = __ballot_sync(0xffffffffu, have_path);
+            const unsigned live_mask = __ballot_sync(0xffffffffu, phase != 0);
             if (!need_mask && !live_mask) break;
             const bool refill = live_mask == 0 || __popc(need_mask) >= kRefillThreshold;
             bool splat = false; float3 value = make_float3(0, 0, 0);
@@ -95,51 +97,67 @@ __global__ void __launch_bounds__(kCtaThreads) k_render(RenderArgs A) {
                 if (L.kind == 0) { a = rng.next_f32(); b = rng.next_f32(); }
                 CameraRay cr = sensor_sample_ray(L, L.ifs, ax, ay, a, b);
                 cam_weight = cr.weight;
-                if (cr.weight > 0.f) {
-                    have_path = true; ro = cr.o; rd = cr.d; rmaxt = cr.maxt;
+                if (cr.weight > 0.f && A.max_depth != 0) {
+                    phase = 1; ro = cr.o; rd = cr.d; rmaxt = cr.maxt;
                     throughput = make_float3(1, 1, 1); result = make_float3(0, 0, 0); eta = 1.f; depth = 0;
                     prev_p = make_float3(0, 0, 0); prev_pdf = 1.f; prev_delta = true; valid_ray = false;
-                    if (A.max_depth == 0) { have_path = false; splat = true; }
-                } else { n_miss++; splat = true; }      // vignetted: RGB 0, weight 1 (integrator.cpp:461-490)
-            } else if (have_path) {
-                // ---- one iteration of PathIntegrator::sample's loop (path.cpp:142-281)
-                n_bounces++; n_rays++;
+                } else { if (!(cr.weight > 0.f)) n_miss++; splat = true; }   // vignetted: RGB 0, weight 1 (integrator.cpp:461-490)
+            } else if (phase != 0) {
+                // ---- the ONE traversal site: path segments and shadow rays of different lanes run together
                 unsigned work = 0;
-                RayHit h = bvh_intersect<false>(A.sc.bvh, ro, rd, rmaxt, work);
-                bool hit = h.tri >= 0;
-                Surface si;
-                if (hit) si = make_surface(A.sc, h, rd);
-                int em = hit ? __ldg(A.sc.shape_emitter + si.shape) : -1;
-                if (em >= 0) {
-                    float3 rel = si.p - prev_p; float dist = sqrtf(dot(rel, rel)); float3 dd = rel * (1.f / dist);
-                    float em_pdf = prev_delta ? 0.f : pdf_emitter_direction(A.sc, em, dd, dist, si.n);
-                    float mis_bsdf = mis_weight(prev_pdf, em_pdf);
-                    if (si.wi.z > 0.f && prev_pdf > 0.f) {
-                        float4 e0 = __ldg(A.sc.emitters + 5 * (size_t) em);
-                        result += throughput * make_float3(e0.x, e0.y, e0.z) * mis_bsdf;
-                    }
-                }
-                bool active_next = (depth + 1 < A.max_depth) && hit;
-                float e_sx = rng.next_f32(), e_sy = rng.next_f32();
-                float s1 = rng.next_f32(), s2x = rng.next_f32(), s2y = rng.next_f32();
-                float rr_sample = rng.next_f32();
-                bool alive = false;
-                if (active_next) {
-                    int bsdf_id = __ldg(A.sc.shape_bsdf + si.shape);
-                    bool active_em = bsdf_is_smooth(A.sc, bsdf_id);
-                    EmitterSample es; es.pdf = 0.f; float3 wo = make_float3(0, 0, 0);
-                    if (active_em) {
-                        es = sample_emitter_direction(A.sc, si.p, e_sx, e_sy);
-                        if (es.pdf != 0.f) {   // shadow ray: Interaction::spawn_ray_to (interaction.h:139-146)
-                            float3 so = offset_p(si.p, si.n, es.p - si.p);
-                            float3 sd = es.p - so; float sdist = sqrtf(dot(sd, sd)); sd = sd * (1.f / sdist);
-                            n_rays++;
-                            RayHit sh = bvh_intersect<true>(A.sc.bvh, so, sd, sdist * (1.f - kShadowEpsilon), work);
-                            if (sh.tri >= 0) es.pdf = 0.f;
+                const RayHit h = bvh_intersect(A.sc.bvh, ro, rd, rmaxt, phase == 2, work);
+                n_rays++; n_nodes += work & 0xffffu; n_tris += work >> 16;
+                bool finish = false, occluded = true;
+                if (phase == 1) {
+                    // ---- first half of one iteration of PathIntegrator::sample's loop (path.cpp:142-208)
+                    n_bounces++;
+                    seg = h; wi_w = rd;
+                    const bool hit = h.tri >= 0;
+                    bool want_shadow = false;
+                    if (hit) {
+                        valid_ray = true;   // path.cpp:256 uses the loop mask `active`, not `active_next`
+                        const Surface si = make_surface(A.sc, h, rd);
+                        const int em = __ldg(A.sc.shape_emitter + si.shape);
+                        if (em >= 0) {     // direct emission, MIS against the previous bounce's BSDF sample (:158-174)
+                            float3 rel = si.p - prev_p; float dist = sqrtf(dot(rel, rel)); float3 dd = rel * (1.f / dist);
+                            float em_pdf = prev_delta ? 0.f : pdf_emitter_direction(A.sc, em, dd, dist, si.n);
+                            if (si.wi.z > 0.f && prev_pdf > 0.f) {
+                                float4 e0 = __ldg(A.sc.emitters + 5 * (size_t) em);
+                                result += throughput * make_float3(e0.x, e0.y, e0.z) * mis_weight(prev_pdf, em_pdf);
+                            }
                         }
-                        active_em = es.pdf != 0.f;
-                        wo = si.to_local(es.d);
+                        if (depth + 1 < A.max_depth) {
+                            finish = true;
+                            if (bsdf_is_smooth(A.sc, __ldg(A.sc.shape_bsdf + si.shape))) {
+                                // emitter sampling (:193-208) with a COPY of the generator: the six draws of this
+                                // iteration are committed when the bounce is finished
+                                Pcg32 peek = rng;
+                                float e_sx = peek.next_f32(), e_sy = peek.next_f32();
+                                EmitterSample es = sample_emitter_direction(A.sc, si.p, e_sx, e_sy);
+                                if (es.pdf != 0.f) {   // shadow ray: Interaction::spawn_ray_to (interaction.h:139-146)
+                                    float3 so = offset_p(si.p, si.n, es.p - si.p);
+                                    float3 sd = es.p - so; float sdist = sqrtf(dot(sd, sd));
+                                    ro = so; rd = sd * (1.f / sdist); rmaxt = sdist * (1.f - kShadowEpsilon);
+                                    want_shadow = true;
+                                }
+                            }
+                        }
                     }
+                    if (want_shadow) { phase = 2; finish = false; }
+                    else if (!finish) { phase = 0; splat = true; if (valid_ray) value = result * cam_weight; }
+                } else {
+                    finish = true; occluded = h.tri >= 0;
+                }
+                if (finish) {
+                    // ---- second half (path.cpp:210-281): BSDF eval/sample, NEE contribution, next ray, Russian roulette
+                    const Surface si = make_surface(A.sc, seg, wi_w);
+                    const int bsdf_id = __ldg(A.sc.shape_bsdf + si.shape);
+                    float e_sx = rng.next_f32(), e_sy = rng.next_f32();
+                    float s1 = rng.next_f32(), s2x = rng.next_f32(), s2y = rng.next_f32();
+                    float rr_sample = rng.next_f32();
+                    EmitterSample es; es.pdf = 0.f; float3 wo = make_float3(0, 0, 0);
+                    const bool active_em = phase == 2 && !occluded;
+                    if (active_em) { es = sample_emitter_direction(A.sc, si.p, e_sx, e_sy); wo = si.to_local(es.d); }
                     BsdfResult bs = bsdf_eval_pdf_sample(A.sc, bsdf_id, si.wi, wo, s1, s2x, s2y);
                     if (active_em) result += throughput * (bs.val * es.weight * mis_weight(es.pdf, bs.pdf));
                     float3 wo_w = si.to_world(bs.wo);
@@ -152,12 +170,9 @@ __global__ void __launch_bounds__(kCtaThreads) k_render(RenderArgs A) {
                     float rr_prob = fminf(tmax * eta * eta, .95f);
                     bool rr_active = depth >= A.rr_depth;
                     if (rr_active) throughput *= 1.f / rr_prob;
-                    alive = (!rr_active || rr_sample < rr_prob) && tmax != 0.f;
-                }
-                n_nodes += work & 0xffffu; n_tris += work >> 16;
-                if (!alive) {
-                    have_path = false; splat = true;
-                    if (valid_ray) value = result * cam_weight;
+                    bool alive = (!rr_active || rr_sample < rr_prob) && tmax != 0.f;
+                    phase = alive ? 1 : 0;
+                    if (!alive) { splat = true; value = result * cam_weight; }
                 }
             }
 
@@ -219,7 +234,7 @@ __global__ void __launch_bounds__(128) k_intersect(SceneView sc, int any_hit, in
         const float *r = od7 + 7 * i;
         float3 o = make_float3(r[0], r[1], r[2]), d = make_float3(r[3], r[4], r[5]);
         unsigned work = 0;
-        RayHit h = any_hit ? bvh_intersect<true>(sc.bvh, o, d, r[6], work) : bvh_intersect<false>(sc.bvh, o, d, r[6], work);
+        RayHit h = bvh_intersect(sc.bvh, o, d, r[6], any_hit != 0, work);
         float *q = out4 + 4 * i;
         q[0] = h.t; q[1] = h.u; q[2] = h.v;
         q[3] = h.tri >= 0 ? (float) __float_as_int(__ldg(sc.bvh.tris + 3 * (size_t) h.tri + 2).z) : -1.f;

@@ -317,6 +317,8 @@ static V3 path_sample(const Scene &s, PCG32 &rng, Ray ray, int max_depth, int rr
         float sample_1 = rng.next_float32();
         V2 sample_2; sample_2.x = rng.next_float32(); sample_2.y = rng.next_float32();
         float rr_sample = rng.next_float32();
+        // path.cpp:256 (JIT: no early break) — valid_ray |= active && si.is_valid(), with the loop mask `active`
+        if (si.valid()) valid_ray = true;
         if (!active_next) break;
         const Bsdf &bsdf = s.bsdfs[s.shape_bsdf[si.shape]];
         bool active_em = bsdf.type == 0;          // BSDFFlags::Smooth
@@ -335,7 +337,6 @@ static V3 path_sample(const Scene &s, PCG32 &rng, Ray ray, int max_depth, int rr
         ray = spawn_ray(si.p, si.n, si.to_world(b.wo));
         throughput = throughput * b.weight;
         eta *= b.seta;
-        valid_ray = true;                          // |= active && si.is_valid() && !Null
         prev_p = si.p; prev_bsdf_pdf = b.spdf; prev_bsdf_delta = b.delta;
         depth += 1;
         float tmax = std::fmax(throughput.x, std::fmax(throughput.y, throughput.z));
