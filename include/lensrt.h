@@ -86,6 +86,19 @@ int lrt_sensor_sample_ray_host(const lrt_sensor *s, int64_t n, const float *pos2
 /* trace_ray_from_film / trace_ray_from_world (:1654-1683 / :1960-1984) in camera space:
  * od6 = o[3], d[3]; out7 = o[3], d[3], active (1/0). */
 int lrt_sensor_trace_host(const lrt_sensor *s, int32_t from_world, int64_t n, const float *od6, float *out7);
+/* Sensor::sample_direction (realisticlens.cpp:2301-2394) for n reference points given in CAMERA space (apply
+ * to_world^-1 first); s2 = aperture samples; out11 = uv[2] (pixels of the crop window), p[3], d[3], dist, pdf,
+ * weight (camera space). Invalid connections return zeros. */
+int lrt_sensor_sample_direction(const lrt_sensor *s, int64_t n, const float *p3_dev, const float *s2_dev,
+                                float *out11_dev, void *stream);
+int lrt_sensor_sample_direction_host(const lrt_sensor *s, int64_t n, const float *p3, const float *s2, float *out11);
+/* Host vector-Jacobian product of one lens trace (chief-ray sensitivities; the reference has no counterpart:
+ * its lens tables are constants, its notebooks differentiate mesh lenses through Dr.Jit,
+ * notebooks/scripts/lens_design/lens.py:67-85). od6 as lrt_sensor_trace_host, bar6 = adjoint of the outgoing
+ * ray; out_bar6 = adjoint of the incoming ray; d/d(rows16) is ADDED to grad_rows16 [n_if,16] (same column
+ * layout as rows16: z at 1, R | c at 3, K at 4, a0..a6 at 6..12, ior_left 13, ior_right 14). */
+int lrt_sensor_trace_vjp_host(const lrt_sensor *s, int32_t from_world, int64_t n, const float *od6, const float *bar6,
+                              float *out_bar6, float *grad_rows16, int32_t *active);
 
 /* --------------------------------------------------------------------------------------------- sampler
  * IndependentSampler over per-sample PCG32 streams (src/samplers/independent.cpp:88-97,
@@ -164,6 +177,30 @@ int lrt_render_host(const lrt_scene *scene, const lrt_sensor *sensor, const lrt_
 /* counters of the last render on this scene: samples, lens misses, rays traced, path-loop iterations,
  * BVH nodes fetched (80 B each), triangles tested (48 B each) */
 int lrt_render_stats(const lrt_scene *scene, uint64_t *out6);
+
+/* ------------------------------------------------------------------------------- lens-design spot path
+ * Light-traced spot image of a point emitter through the realistic lens and its adjoint: the B200 form of
+ * one `ptracer` render + render_backward of the notebooks' design loop
+ * (notebooks/scripts/lens_design/design_problem.py:495-584; src/integrators/ptracer.cpp connect_sensor ->
+ * Sensor::sample_direction realisticlens.cpp:2301-2394 -> ImageBlock::put normalize=true, coalesce=false,
+ * src/render/integrator.cpp:706-717; generic Integrator::render_backward src/render/integrator.cpp:66-84). */
+typedef struct lrt_spot_params {
+    uint32_t seed;
+    int32_t spp;                       /* size_x*size_y*spp samples in total; sample scale 1/spp (integrator.cpp:671-676) */
+    float src_p[3];                    /* point emitter, CAMERA space (a distant point = a field angle) */
+    float intensity[3];                /* RGB radiant intensity */
+    int32_t shard_index, shard_count;  /* sample idx = shard_index + k*shard_count: identical streams for any GPU count */
+} lrt_spot_params;
+
+/* Accumulates intensity*weight/spp (R,G,B) and 1/spp (W) times the normalised filter weights into accum_dev
+ * [size_y+2b, size_x+2b, 4]; the spot image is channels 0..2 (AdjointIntegrator films are not weight-divided).
+ * stats_dev (optional, 2 x u64, caller-zeroed): samples traced, samples that reached the film. */
+int lrt_spot_render(const lrt_sensor *sensor, const lrt_film_desc *film, const lrt_spot_params *params,
+                    float *accum_dev, uint64_t *stats_dev, void *stream);
+/* Adjoint: grad_accum_dev = d(loss)/d(accum) (same shape); ADDS d(loss)/d(rows16) to grad_rows16_dev [n_if,16]
+ * (caller zeroes it). Samples, streams and vignetting masks are those of lrt_spot_render with equal params. */
+int lrt_spot_render_backward(const lrt_sensor *sensor, const lrt_film_desc *film, const lrt_spot_params *params,
+                             const float *grad_accum_dev, float *grad_rows16_dev, uint64_t *stats_dev, void *stream);
 
 #ifdef __cplusplus
 }

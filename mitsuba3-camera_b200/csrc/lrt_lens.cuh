@@ -39,6 +39,10 @@ struct alignas(16) LensSystem {
     float to_world[12];                         // rows of the affine camera-to-world matrix
     // perspective (src/sensors/perspective.cpp): sample -> camera and image-plane normalisation
     float persp_s2c[16]; float persp_norm, pad0, pad1, pad2;
+    // film -> sample (diagonal + translation), film-plane normalisation 1/area and crop resolution: what
+    // sample_direction needs (realisticlens.cpp:2190-2207,2352-2372)
+    float f2s_m00, f2s_m03, f2s_m11, f2s_m13;
+    float normalization, res_x, res_y, pad3;
     LensIf ifs[kMaxInterfaces];
 };
 
@@ -291,6 +295,49 @@ LRT_HD CameraRay lens_sample_ray(const LensSystem &L, const LensIf *ifs, float u
     return r;
 }
 
+
+// RealisticLensCamera::sample_direction (:2301-2394) in CAMERA space (the caller applies to_world^-1 to the
+// reference point and to_world to p / d): sample the front-element disk, trace front -> rear, project the ray
+// to the film plane z = 0. Returns the `valid` mask; uv in pixels of the crop window (ds.uv).
+struct DirectionSample { float uv_x, uv_y; strict::V3 p, d; float dist, pdf, weight; bool valid; LensRay ray_out; };
+
+LRT_HD DirectionSample lens_sample_direction(const LensSystem &L, const LensIf *ifs, strict::V3 ref_p, float a, float b) {
+    using namespace strict;
+    DirectionSample ds; ds.uv_x = ds.uv_y = 0.f; ds.p = v3(0, 0, 0); ds.d = v3(0, 0, 0); ds.dist = 0.f; ds.pdf = 0.f; ds.weight = 0.f;
+    ds.valid = false; ds.ray_out.o = v3(0, 0, 0); ds.ray_out.d = v3(0, 0, 0);
+    bool active = ref_p.z >= L.near_clip && ref_p.z <= L.far_clip;
+    if (!active) return ds;
+    const LensIf &front = ifs[L.n - 1];
+    float front_radius = mul(1.0f, front.elem_radius), front_z = front.z;
+    float dx, dy; square_to_disk_concentric(a, b, dx, dy);
+    V3 aperture_p = v3(mul(dx, front_radius), mul(dy, front_radius), front_z);
+    V3 dir = sub(ref_p, aperture_p);
+    float dist = norm(dir), inv_dist = rcp(dist);
+    dir = mul(dir, inv_dist);
+    LensRay ray; ray.o = ref_p; ray.d = neg(dir);
+    bool valid = lens_trace_from_world(ifs, L.n, ray);
+    ds.ray_out = ray;
+    if (!valid) return ds;
+    float t = div(-ray.o.z, ray.d.z);
+    V3 pf = at(ray.o, ray.d, t);
+    // Transform4f::transform_affine column chain (transform.h:104-111); film_to_sample is diagonal + translation
+    float sx = fmadd(0.f, pf.z, fmadd(0.f, pf.y, fmadd(L.f2s_m00, pf.x, L.f2s_m03)));
+    float sy = fmadd(0.f, pf.z, fmadd(L.f2s_m11, pf.y, fmadd(0.f, pf.x, L.f2s_m13)));
+    valid = valid && sx >= 0.f && sy >= 0.f && sx <= 1.f && sy <= 1.f;
+    float ct_film = -ray.d.z, inv_ct = rcp(ct_film);
+    float value = valid ? mul(mul(L.normalization, sqr(sqr(inv_ct))), sqr(L.rear_z)) : 0.f;
+    if (!valid) return ds;
+    ds.valid = true;
+    ds.uv_x = mul(sx, L.res_x); ds.uv_y = mul(sy, L.res_y);
+    ds.p = aperture_p; ds.d = neg(dir);   // (ds.p - it.p) * inv_dist, expressed with the values already at hand
+    ds.d = mul(sub(aperture_p, ref_p), inv_dist);
+    ds.dist = dist;
+    float aperture_pdf = rcp(mul(kPi, sqr(front_radius)));
+    float ct_ref = dir.z;
+    ds.pdf = mul(mul(mul(aperture_pdf, dist), dist), rcp(ct_ref));
+    ds.weight = mul(mul(mul(value, inv_dist), inv_dist), ct_ref);
+    return ds;
+}
 
 // perspective pinhole (src/sensors/perspective.cpp sample_ray): near_p = s2c * (u,v,0), d = normalize(near_p)
 LRT_HD CameraRay persp_sample_ray(const LensSystem &L, float u, float v) {

@@ -115,6 +115,8 @@ static void setup_film(lrt_sensor &s) {
     s.normalization = 1.f / ((fmaxf(x0, x1) - fminf(x0, x1)) * (fmaxf(y0, y1) - fminf(y0, y1)));
     s.host.s2f_m00 = m[0]; s.host.s2f_m03 = m[3]; s.host.s2f_m11 = m[5]; s.host.s2f_m13 = m[7];
     s.host.persp_norm = s.normalization;
+    s.host.f2s_m00 = q[0]; s.host.f2s_m03 = q[3]; s.host.f2s_m11 = q[5]; s.host.f2s_m13 = q[7];
+    s.host.normalization = s.normalization; s.host.res_x = (float) g.crop_w; s.host.res_y = (float) g.crop_h;
 }
 
 // ------------------------------------------------------------------ thick-lens autofocus (:2107-2171)

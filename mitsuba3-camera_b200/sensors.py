@@ -161,6 +161,37 @@ class RealisticLensCamera(Sensor):
         return out[:, 0:3], out[:, 3:6], out[:, 6] > 0
 
 
+    def sample_direction(self, it_p, sample, active=True):
+        """Sensor::sample_direction (realisticlens.cpp:2301-2394) for [n,3] reference points (world space) and
+        [n,2] aperture samples -> dict(uv, p, d, dist, pdf, weight); p/d are returned in world space."""
+        import torch
+        p = np.asarray(it_p.cpu() if hasattr(it_p, "cpu") else it_p, f32).reshape(-1, 3)
+        s2 = np.ascontiguousarray(np.asarray(sample.cpu() if hasattr(sample, "cpu") else sample, f32).reshape(-1, 2))
+        tw = self.to_world.astype(np.float64)
+        inv = np.linalg.inv(tw)
+        pc = np.ascontiguousarray((p.astype(np.float64) @ inv[:3, :3].T + inv[:3, 3]).astype(f32))
+        out = np.zeros((len(pc), 11), f32)
+        capi.check(capi.lib.lrt_sensor_sample_direction_host(self.handle, C.c_int64(len(pc)), capi.fp(pc), capi.fp(s2), capi.fp(out)))
+        R = tw[:3, :3].astype(f32)
+        valid = out[:, 9] > 0
+        return {"uv": out[:, 0:2], "p": np.where(valid[:, None], out[:, 2:5] @ R.T + tw[:3, 3].astype(f32), 0), "d": out[:, 5:8] @ R.T,
+                "dist": out[:, 8], "pdf": out[:, 9], "weight": out[:, 10]}
+
+    def trace_vjp(self, origins, directions, bar_o, bar_d, from_world=False):
+        """Vector-Jacobian product of one lens trace (host): returns (adjoint of the incoming ray [n,6], gradient
+        w.r.t. the interface table [n_if,16] summed over rays, active mask)."""
+        od = np.ascontiguousarray(np.concatenate([np.asarray(origins, f32).reshape(-1, 3),
+                                                  np.asarray(directions, f32).reshape(-1, 3)], axis=1))
+        bar = np.ascontiguousarray(np.concatenate([np.asarray(bar_o, f32).reshape(-1, 3),
+                                                   np.asarray(bar_d, f32).reshape(-1, 3)], axis=1))
+        out = np.zeros((len(od), 6), f32)
+        grad = np.zeros((self.num_interfaces(), 16), f32)
+        act = np.zeros(len(od), np.int32)
+        capi.check(capi.lib.lrt_sensor_trace_vjp_host(self.handle, C.c_int32(int(from_world)), C.c_int64(len(od)), capi.fp(od),
+                                                      capi.fp(bar), capi.fp(out), capi.fp(grad), capi.ip(act)))
+        return out, grad, act > 0
+
+
 class PerspectiveCamera(Sensor):
     """`perspective` plugin (src/sensors/perspective.cpp): fov (x axis, degrees), to_world, clips."""
 

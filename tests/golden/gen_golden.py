@@ -78,3 +78,27 @@ for name in ld.all_designs():
 np.savez_compressed(os.path.join(HERE, "lens.npz"), **out)
 for k in ("rng.npz", "maths.npz", "lens.npz"):
     print(k, os.path.getsize(os.path.join(HERE, k)) // 1024, "KiB")
+
+# ---- Sensor::sample_direction (realisticlens.cpp:2301-2394): distant / near reference points in camera space
+rng2 = np.random.default_rng(20261105)
+out = {}
+N = 256
+for name in ld.all_designs():
+    film = FILMS["default"]
+    h = ref_camera(name, film)
+    ifs = cam_interfaces(R, "ref", h)
+    front_z, front_r = ifs[-1, 1], ifs[-1, 2]
+    p = np.zeros((N, 3), f32)
+    ang = np.radians(rng2.random(N) * 6.0); phi = rng2.random(N) * 2 * np.pi
+    dist = np.where(np.arange(N) % 2 == 0, 1000.0, 0.5 + rng2.random(N) * 5)
+    p[:, 0] = dist * np.tan(ang) * np.cos(phi); p[:, 1] = dist * np.tan(ang) * np.sin(phi); p[:, 2] = front_z + dist
+    p[0] = [0, 0, front_z + 10.0]
+    s2 = rng2.random((N, 2), dtype=f32); s2[0] = 0.5
+    s2[N // 2:] = 0.5 + (s2[N // 2:] - 0.5) * 0.1
+    o = np.zeros((N, 11), f32)
+    R.ref_cam_sample_direction(h, N, fp(p), fp(s2), fp(o))
+    out[name + ".p"] = p; out[name + ".s"] = s2; out[name + ".out"] = o
+    R.ref_cam_destroy(h)
+np.savez_compressed(os.path.join(HERE, "sample_direction.npz"), **out)
+print("sample_direction.npz", os.path.getsize(os.path.join(HERE, "sample_direction.npz")) // 1024, "KiB",
+      {k[:-4]: int((v[:, 9] > 0).sum()) for k, v in out.items() if k.endswith(".out")})

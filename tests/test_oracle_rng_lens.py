@@ -141,3 +141,19 @@ def test_oracle_vs_reference_code_large(name):
     assert ((a[:, 7] > 0) == (b[:, 7] > 0)).all()
     act = b[:, 7] > 0
     assert act.any() and (bits(a[act]) == bits(b[act])).all()
+
+
+@pytest.mark.parametrize("name", ld.all_designs())
+def test_oracle_sample_direction_matches_reference_vectors(name):
+    """Sensor::sample_direction (realisticlens.cpp:2301-2394): the port against vectors produced by the reference's
+    own code (tests/golden/gen_golden.py, oracle/_ref)."""
+    g = np.load(os.path.join(ROOT, "tests", "golden", "sample_direction.npz"))
+    L = oracle()
+    film = FilmSpec(256, 192, [200, 100, 20, 30], 35.0)
+    h = orc_camera(ld.design(name, {}), film)
+    p, s2, want = g[name + ".p"], g[name + ".s"], g[name + ".out"]
+    got = np.zeros_like(want)
+    L.orc_cam_sample_direction(h, C.c_int(len(p)), fp(np.ascontiguousarray(p)), fp(np.ascontiguousarray(s2)), fp(got))
+    assert ((got[:, 9] > 0) == (want[:, 9] > 0)).all()
+    assert (bits(got) == bits(want)).all()
+    L.orc_cam_destroy(h)
