@@ -51,7 +51,8 @@ class Sensor:
 
     def __del__(self):
         if getattr(self, "handle", None):
-            capi.lib.lrt_sensor_destroy(self.handle)
+            if capi is not None and capi.lib is not None:
+                capi.lib.lrt_sensor_destroy(self.handle)
             self.handle = None
 
     def needs_aperture_sample(self) -> bool:

@@ -199,3 +199,35 @@ def develop(storage):
 def rel_rmse(a, b):
     a = np.asarray(a, np.float64); b = np.asarray(b, np.float64)
     return float(np.sqrt(np.mean((a - b) ** 2)) / max(np.sqrt(np.mean(b ** 2)), 1e-12))
+
+
+# ------------------------------------------------------------------------------------------------ spot path
+def orc_spot_render(cam_h, film: FilmSpec, src_p, intensity, seed, spp, filter_kind=1, filter_param=0.0):
+    """float32 checker of lrt_spot_render -> (storage float64 [ch,cw,4], valid samples)."""
+    L = oracle()
+    L.orc_spot_render.restype = C.c_longlong
+    cw, ch, cx, cy = (int(v) for v in film.crop)
+    st = np.zeros((ch, cw, 4), np.float64)
+    valid = L.orc_spot_render(cam_h, C.c_int(cw), C.c_int(ch), C.c_int(cx), C.c_int(cy), C.c_int(filter_kind), c_f(filter_param),
+                              C.c_uint32(seed), C.c_int(spp), fp(np.ascontiguousarray(src_p, f32)),
+                              fp(np.ascontiguousarray(intensity, f32)), st.ctypes.data_as(C.POINTER(C.c_double)))
+    return st, valid
+
+
+def orc_spot_grad(rows, f2s, normalization, near, far, film: FilmSpec, src_p, intensity, seed, spp, G, sel, filter_kind=1,
+                  filter_param=0.0, delta=None):
+    """float64 dual-number checker: (Phi, dPhi/d rows[sel]) for Phi = <G, storage(rows)> with frozen masks."""
+    L = oracle()
+    L.orc_spot_grad.restype = C.c_double
+    cw, ch, cx, cy = (int(v) for v in film.crop)
+    sel = np.ascontiguousarray(sel, np.int32).reshape(-1, 2)
+    out = np.zeros(len(sel), np.float64)
+    dl = None if delta is None else np.ascontiguousarray(delta, np.float64)
+    phi = L.orc_spot_grad(C.c_int(len(rows)), fp(np.ascontiguousarray(rows, f32)), fp(np.ascontiguousarray(f2s, f32).ravel()),
+                          c_f(normalization), c_f(near), c_f(far), C.c_int(cw), C.c_int(ch), C.c_int(cx), C.c_int(cy),
+                          C.c_int(filter_kind), c_f(filter_param), C.c_uint32(seed), C.c_int(spp),
+                          fp(np.ascontiguousarray(src_p, f32)), fp(np.ascontiguousarray(intensity, f32)),
+                          fp(np.ascontiguousarray(G, f32)), C.c_int(len(sel)), sel.ctypes.data_as(IP),
+                          dl.ctypes.data_as(C.POINTER(C.c_double)) if dl is not None else None,
+                          out.ctypes.data_as(C.POINTER(C.c_double)))
+    return phi, out

@@ -63,3 +63,49 @@ def test_trace_vjp_matches_dual_number_jacobian(mi, name, from_world):
         assert np.abs(in_bar[0, :3] - want[:3]).max() <= 2e-3 * so
         assert np.abs(proj @ in_bar[0, 3:] - proj @ want[3:6]).max() <= 2e-3 * so
     assert checked >= 3
+
+
+# ------------------------------------------------------------------------------------------------ spot path
+def spot_case(name="doublet", angle=1.5, n_pix=24, full=8192, spp=2, props=None, distance=1000.0):
+    """A field source at `angle` degrees and a crop window of n_pix^2 pixels of a full^2 film centred on the chief ray."""
+    L = oracle()
+    design = ld.design(name, props or {})
+    big = FilmSpec(full, full, None, 35.0)
+    h = orc_camera(design, big)
+    rows = cam_interfaces(L, "orc", h)
+    src = np.array([distance * np.tan(np.radians(angle)), 0.0, rows[-1, 1] + distance], f32)
+    o = np.zeros(11, f32)
+    L.orc_cam_sample_direction(h, C.c_int(1), fp(src), fp(np.array([.5, .5], f32)), fp(o))
+    assert o[9] > 0, "chief ray blocked"
+    cx, cy = int(o[0]) - n_pix // 2, int(o[1]) - n_pix // 2
+    L.orc_cam_destroy(h)
+    film = FilmSpec(full, full, [n_pix, n_pix, cx, cy], 35.0)
+    h = orc_camera(design, film)
+    f2s = np.zeros(16, f32); L.orc_cam_film_to_sample(h, fp(f2s))
+    s2f = np.zeros(16, f32); L.orc_cam_sample_to_film(h, fp(s2f))
+    norm = 1.0 / (abs(float(s2f[0])) * abs(float(s2f[5])))
+    return dict(design=design, film=film, h=h, rows=rows, src=src, f2s=f2s, norm=norm, spp=spp, name=name, props=props or {})
+
+
+@pytest.mark.parametrize("filter_kind,tol", [(2, 2e-4), (1, 2e-2)])
+def test_checker_gradient_agrees_with_finite_differences(filter_kind, tol):
+    """The dual-number checker against central differences of its own value (float64): pins the derivative that the
+    CUDA adjoint is compared with on the GPU."""
+    c = spot_case("doublet", 1.5, n_pix=24, spp=2)
+    rng = np.random.default_rng(3)
+    G = rng.standard_normal((24, 24, 4)).astype(f32)
+    rows = c["rows"]
+    sel = [(i, col) for i in range(len(rows)) for col in COLS[int(rows[i, 0])]]
+    args = (rows, c["f2s"], c["norm"], 1e-2, 1e4, c["film"], c["src"], [1.0, 0.8, 0.6], 5, c["spp"], G, sel)
+    # gaussian: smooth, tight tolerance; tent: the estimate is piecewise linear in the splat position, so a finite
+    # step that carries samples across pixel centres sees the kinks (loose tolerance)
+    kw = dict(filter_kind=filter_kind)
+    phi, grad = orc_spot_grad(*args, **kw)
+    assert np.isfinite(grad).all() and np.abs(grad).max() > 0
+    for s, (i, col) in enumerate(sel):
+        hstep = 1e-7 * max(abs(float(rows[i, col])), 1e-2)
+        d = np.zeros(len(sel)); d[s] = hstep
+        pp, _ = orc_spot_grad(*args, delta=d, **kw)
+        pm, _ = orc_spot_grad(*args, delta=-d, **kw)
+        fd = (pp - pm) / (2 * hstep)
+        assert abs(fd - grad[s]) <= tol * max(abs(grad[s]), 1e-2 * np.abs(grad).max()), (i, col, fd, grad[s])
