@@ -126,3 +126,142 @@ def spot_image(rows, sensor, src_p, intensity=(1.0, 1.0, 1.0), seed=0, spp=None,
     spp = int(spp if spp else sensor.sampler.sample_count())
     return _SpotRender.apply(rows, sensor, src_p, tuple(intensity), int(seed), spp, int(seed if seed_grad is None else seed_grad),
                              int(spp_grad if spp_grad else spp), shard)
+
+
+# ------------------------------------------------------------------------------------------------ design problem
+def asphere_table(curv_mm, thickness_mm, semi_diameter_mm, glass_iors, air=1.000277):
+    """Even-asphere interface table (rear -> front rows16, metres) from a front-to-rear prescription in millimetres, the
+    way AsphericalLens's constructor scales it (realisticlens.cpp:557-572: unitless radius r/R_e, c = R_e / curv).
+    glass_iors[i] = index of the medium behind surface i (front to rear); the last one is the image space (air)."""
+    n = len(curv_mm)
+    rows, z = [], 0.0
+    media = [air] + list(glass_iors)             # media[i] in front of surface i, media[i+1] behind it
+    for i in range(n - 1, -1, -1):
+        z += float(thickness_mm[i])
+        r = np.zeros(16, f32)
+        r[0], r[1], r[2] = 3, 1e-3 * z, 1e-3 * float(semi_diameter_mm[i])
+        r[3] = float(semi_diameter_mm[i]) / float(curv_mm[i]) if np.isfinite(curv_mm[i]) and curv_mm[i] != 0 else 0.0
+        r[5] = float(semi_diameter_mm[i])
+        r[13], r[14] = media[i + 1], media[i]
+        rows.append(r)
+    return np.stack(rows)
+
+
+def cauchy_ior(A, B, wavelength_um=0.5893):
+    return A + B / (wavelength_um * wavelength_um)     # realisticlens.cpp:169-179
+
+
+def paraxial_trace(z, kappa, n_left, n_right, upto=0):
+    """Marginal paraxial ray (height 1, parallel to the axis) from the front surface down to surface `upto` (rear = 0):
+    returns (y, u) just behind that surface. z, kappa (= curvature seen by a ray travelling towards the film,
+    -1/R of the table), n_left/n_right: torch 1-D tensors, rear -> front. Stand-in for the notebooks' ABCD matrices
+    (notebooks/scripts/lens_design/lens.py:850-960)."""
+    y, u = 1.0, 0.0
+    n = len(z)
+    for i in range(n - 1, upto - 1, -1):
+        u = (n_right[i] * u - y * (n_left[i] - n_right[i]) * kappa[i]) / n_left[i]
+        if i > upto:
+            y = y + u * (z[i] - z[i - 1])
+    return y, u
+
+
+def efl_bfl(z, kappa, n_left, n_right):
+    """Effective focal length and back focal distance (measured from the rear vertex) of the table."""
+    y, u = paraxial_trace(z, kappa, n_left, n_right, 0)
+    return -1.0 / u, -y / u
+
+
+def efl_constrained_rear(z, kappa, n_left, n_right, f):
+    """Rear-surface vertex position and curvature that give the system the focal length `f` and put its focus on the film
+    (z = 0): the role of LensSystem.get_rear_surface_params (lens.py:970-997). Differentiable in every input."""
+    y1, u1 = paraxial_trace(z, kappa, n_left, n_right, 1)      # behind surface 1, in the medium n_right[0]
+    z0 = (y1 + u1 * z[1]) / (u1 + 1.0 / f)
+    y0 = y1 + u1 * (z[1] - z0)
+    k0 = (n_right[0] * u1 + n_left[0] / f) / (y0 * (n_left[0] - n_right[0]))
+    return z0, k0
+
+
+class LensDesignProblem:
+    """The notebooks' multi-spot design loop (design_problem.py:355-584) on the analytic table.
+
+    variables: dict name -> (row index, column) of free table entries (all start from `rows0`); every field source gets
+    its own sensor whose crop window of `resolution`^2 pixels (pixel pitch = film diagonal / full_res) is centred on
+    the chief ray. loss = sum over fields of rms_loss (pixel^2) * pitch^2. One `step()` = primal renders at `spp`,
+    image-space loss gradient, adjoint renders at `spp_grad` (fresh seed), Adam update."""
+
+    def __init__(self, mi, rows0, field_angles, resolution=128, full_res=4096, diagonal=35.0, spp=256, spp_grad=128,
+                 free=None, lr=3e-5, source_distance=10.0, rfilter="tent", efl_target=None, shard=(0, 1), film_z=0.0):
+        import torch
+        from .lens_designs import InterfaceList
+        self.mi, self.torch = mi, torch
+        self.rows0 = np.ascontiguousarray(rows0, f32).copy()
+        self.n = len(self.rows0)
+        self.spp, self.spp_grad, self.shard = int(spp), int(spp_grad), shard
+        self.pitch = 1e-3 * diagonal / np.sqrt(2.0) / full_res          # square film: side = diagonal / sqrt(2)
+        self.efl_target = efl_target
+        if free is None:   # every curvature, vertex position and (for aspheres) conic + polynomial coefficient
+            free = [(i, c) for i in range(self.n) for c in ([1, 3] + ([4] + list(range(6, 13)) if self.rows0[i, 0] == 3 else []))
+                    if self.rows0[i, 0] != 2]
+        if efl_target is not None:
+            free = [(i, c) for (i, c) in free if not (i == 0 and c in (1, 3))]   # the rear vertex / curvature are constrained
+        self.free = list(free)
+        self.theta = torch.tensor([self.rows0[i, c] for i, c in self.free], dtype=torch.float32, requires_grad=True)
+        self.opt = torch.optim.Adam([self.theta], lr=lr)
+        self.sensors, self.sources = [], []
+        probe = mi.RealisticLensCamera(mi.Film(full_res, full_res, diagonal=diagonal, rfilter=rfilter), "custom",
+                                       prescription=InterfaceList(self.rows0, film_z=film_z, fine_focus=False))
+        s2f = probe.info()["sample_to_film"]
+        front_z, front_r = float(self.rows0[-1, 1]), float(self.rows0[-1, 2])
+        for a in field_angles:
+            src = field_source(a, source_distance, front_z=front_z)
+            d = np.array([0, 0, front_z], f32) - src
+            d = (d / np.linalg.norm(d)).astype(f32)
+            o, dd, act = probe.trace(src[None], d[None], from_world=True)
+            if not act[0]:
+                raise ValueError(f"chief ray of the {a} degree field is blocked")
+            t = -o[0, 2] / dd[0, 2]
+            pf = o[0] + t * dd[0]
+            px = (pf[0] - s2f[0, 3]) / s2f[0, 0] * full_res
+            py = (pf[1] - s2f[1, 3]) / s2f[1, 1] * full_res
+            cx, cy = int(np.floor(px)) - resolution // 2, int(np.floor(py)) - resolution // 2
+            film = mi.Film(full_res, full_res, crop=(resolution, resolution, cx, cy), diagonal=diagonal, rfilter=rfilter)
+            s = mi.RealisticLensCamera(film, "custom", prescription=InterfaceList(self.rows0, film_z=film_z, fine_focus=False))
+            self.sensors.append(s); self.sources.append(src)
+        self.iteration, self.losses = 0, []
+
+    def rows(self):
+        """theta -> interface table (torch, differentiable); applies the EFL constraint when one is set."""
+        torch = self.torch
+        rows = torch.tensor(self.rows0)
+        idx_i = torch.tensor([i for i, _ in self.free]); idx_c = torch.tensor([c for _, c in self.free])
+        rows = rows.index_put((idx_i, idx_c), self.theta)
+        if self.efl_target is not None:
+            Re = rows[:, 2]
+            sph = torch.tensor(self.rows0[:, 0] == 0)
+            asp = torch.tensor(self.rows0[:, 0] == 3)
+            safe_R = torch.where(sph, rows[:, 3], torch.ones_like(Re))
+            kappa = torch.where(sph, -1.0 / safe_R, torch.where(asp, rows[:, 3] / Re, torch.zeros_like(Re)))
+            z0, k0 = efl_constrained_rear(rows[:, 1], kappa, rows[:, 13], rows[:, 14], self.efl_target)
+            col3 = k0 * Re[0] if self.rows0[0, 0] == 3 else -1.0 / k0
+            rows = rows.index_put((torch.tensor([0, 0]), torch.tensor([1, 3])), torch.stack([z0, col3]))
+        return rows
+
+    def loss(self, rows, seed):
+        total = 0.0
+        for k, (s, src) in enumerate(zip(self.sensors, self.sources)):
+            img = spot_image(rows, s, src, seed=seed * 64 + k, spp=self.spp, seed_grad=(seed * 64 + k) ^ 0x5bd1e995,
+                             spp_grad=self.spp_grad, shard=self.shard)
+            total = total + rms_loss(img) * (self.pitch * 1e3) ** 2       # mm^2, as evaluate_rms_loss (design_problem.py:268-282)
+        return total
+
+    def step(self, all_reduce=None):
+        """One optimisation iteration; `all_reduce(tensor)` sums the table gradient over ranks when sharded."""
+        self.opt.zero_grad(set_to_none=True)
+        l = self.loss(self.rows(), self.iteration)
+        l.backward()
+        if all_reduce is not None:
+            all_reduce(self.theta.grad)
+        self.opt.step()
+        self.iteration += 1
+        self.losses.append(float(l.detach()))
+        return self.losses[-1]
