@@ -37,6 +37,8 @@ def parse():
     p.add_argument("--max-depth", type=int, default=6)
     p.add_argument("--cpu-crop", type=int, nargs=2, default=[192, 108], help="crop window of the CPU baseline sample")
     p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--no-lens-grad", action="store_true", help="skip the lens-gradient iterations/s section (C2 / C3 shapes)")
+    p.add_argument("--lens-iters", type=int, default=10)
     return p.parse_args()
 
 
@@ -96,6 +98,100 @@ def cpu_sample(a, scene_arrays, sensor_dict, steps=1, warmup=0):
     sec = sum(times) / len(times)
     return {"value": paths / sec / 1e6, "unit": "Mpaths/s", "cores": os.cpu_count(), "kind": "port",
             "sample": f"centred {cw}x{ch} crop of the {a.width}x{a.height} film, {a.spp_per_step} spp ({paths} paths, {sec:.2f} s/step)"}, sec
+
+
+def doublet_table(mi):
+    """C2: the notebooks' cemented doublet (doublet_full_optim.ipynb cell 6) as three even-asphere interfaces."""
+    L = mi.lens_design
+    n1, n2 = L.cauchy_ior(1.45608, 0.021087), L.cauchy_ior(1.56895, 0.026305)
+    return L.asphere_table([24.0, -24.0, -168.0107], [3.0, 2.2529, 46.7471], [8, 8, 8], [n1, n2, 1.000277])
+
+
+def triplet_table(mi):
+    """C3: a Cooke triplet (six even-asphere surfaces; paraxial EFL 50.0 mm, BFL 46.3 mm, semi-diameters 7 / 5 / 7 mm),
+    synthetic prescription."""
+    L = mi.lens_design
+    crown, flint = L.cauchy_ior(1.6030, 0.00600), L.cauchy_ior(1.6000, 0.01500)
+    return L.asphere_table([17.223, -128.586, -16.413, 15.643, 114.483, -14.009], [3.242, 2.431, 1.621, 2.431, 3.242, 46.2], [7, 7, 5, 5, 7, 7],
+                           [crown, 1.000277, flint, 1.000277, crown, 1.000277])
+
+
+def lens_grad_section(mi, torch, dist, a, rank, world):
+    """Lens-gradient iterations/s: one iteration = per field a primal spot render (spp), the RMS-spot loss, the adjoint
+    render (spp_grad, fresh seed), an all-reduce of the table gradient (N > 1: samples are sharded by index) and an Adam
+    step. Timed with CUDA events around whole iterations (host work included), max over ranks."""
+    out = {}
+    shapes = {"C2": dict(table=doublet_table, fields=[0.0, 2.5, 5.0], res=128, spp=256, spp_grad=128, efl=None),
+              "C3": dict(table=triplet_table, fields=[0.0, 1.875, 3.75, 5.625, 7.5], res=512, spp=256, spp_grad=256, efl=0.05)}
+    for name, cfg in shapes.items():
+        rows = cfg["table"](mi)
+        try:
+            prob = mi.lens_design.LensDesignProblem(mi, rows, cfg["fields"], resolution=cfg["res"], full_res=4096, spp=cfg["spp"],
+                                                    spp_grad=cfg["spp_grad"], lr=3e-5, efl_target=cfg["efl"],
+                                                    shard=(rank, world))
+        except Exception as e:   # a blocked chief ray in a synthetic prescription must not take the bench line down
+            out[name] = {"error": str(e)[:200]}
+            continue
+        red = (lambda g: dist.all_reduce(g)) if world > 1 else None
+
+        def it():
+            if world > 1:     # theta.grad lives on the host: reduce through a device copy
+                prob.opt.zero_grad(set_to_none=True)
+                l = prob.loss(prob.rows(), prob.iteration); l.backward()
+                g = prob.theta.grad.cuda(); dist.all_reduce(g); prob.theta.grad.copy_(g.cpu())
+                prob.opt.step(); prob.iteration += 1; prob.losses.append(float(l.detach()))
+            else:
+                prob.step()
+        for _ in range(3):
+            it()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(a.lens_iters):
+            it()
+        e1.record(); torch.cuda.synchronize()
+        ms = torch.tensor([e0.elapsed_time(e1) / a.lens_iters], device="cuda", dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        rays = len(cfg["fields"]) * cfg["res"] ** 2 * (cfg["spp"] + cfg["spp_grad"])
+        out[name] = {"workload": f"{len(rows)}-surface even-asphere lens, {len(prob.free)} free variables, {len(cfg['fields'])} fields, "
+                                 f"{cfg['res']}^2 px, spp {cfg['spp']} primal + {cfg['spp_grad']} adjoint" + (", EFL held at 50 mm" if cfg["efl"] else ""),
+                     "iters_per_s": 1e3 / ms.item(), "ms_per_iter": ms.item(), "lens_rays_per_iter": rays,
+                     "Grays_per_s": rays / (ms.item() * 1e-3) / 1e9, "loss_first": prob.losses[0], "loss_last": prob.losses[-1]}
+    return out
+
+
+def lens_grad_cpu(mi, a):
+    """CPU arm of the lens-gradient metric: the oracle's float32 spot render + float64 dual-number gradient (the only CPU
+    derivative of this path that exists: the reference cannot differentiate its lens table) on a bounded sample of C2:
+    one field, 128^2 x 2 spp, 30 seeds; scaled to the full iteration by ray count. Single thread."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import numpy as np
+    import oracle_lib as ol
+    from test_lens_adjoint import COLS
+    rows = doublet_table(mi)
+    from mitsuba3_camera_b200.lens_designs import InterfaceList
+    film = ol.FilmSpec(4096, 4096, [128, 128, 1984, 1984], 35.0)
+    h = ol.orc_camera(InterfaceList(rows, film_z=0.0, fine_focus=False), film)
+    O = ol.oracle()
+    f2s = np.zeros(16, np.float32); O.orc_cam_film_to_sample(h, ol.fp(f2s))
+    s2f = np.zeros(16, np.float32); O.orc_cam_sample_to_film(h, ol.fp(s2f))
+    src = mi.lens_design.field_source(0.0, 1.0e3, front_z=float(rows[-1, 1]))
+    spp = 2
+    t0 = time.perf_counter()
+    st, valid = ol.orc_spot_render(h, film, src, [1, 1, 1], 0, spp, origin_offset=0.016)
+    G = np.random.default_rng(0).standard_normal((128, 128, 4)).astype(np.float32)
+    sel = [(i, c) for i in range(3) for c in [1, 3, 4, 6, 7, 8, 9, 10, 11, 12]]
+    ol.orc_spot_grad(rows, f2s, 1.0 / (abs(float(s2f[0])) * abs(float(s2f[5]))), 1e-2, 1e4, film, src, [1, 1, 1], 1, spp, G, sel,
+                     origin_offset=0.016)
+    sec = time.perf_counter() - t0
+    rays_sample = 128 * 128 * spp * 2
+    rays_iter = 3 * 128 * 128 * (256 + 128)
+    return {"value": 1.0 / (sec * rays_iter / rays_sample), "unit": "iters/s (C2)", "cores": 1, "kind": "port",
+            "sample": f"1 field, 128^2 x {spp} spp primal + adjoint ({rays_sample} lens rays, {sec:.2f} s), scaled by ray count to the "
+                      f"{rays_iter}-ray iteration; forward-mode float64 dual numbers (30 seeds)"}
 
 
 def main():
@@ -181,6 +277,7 @@ def main():
         step(2000 + i, e2e=True)
     ms_e2e = timed(a.steps, True, 100)
     sampler.stop_flag = True
+    lens_grad = None if a.no_lens_grad else lens_grad_section(mi, torch, dist, a, rank, world)
 
     if rank == 0:
         value = paths_per_step / (ms * 1e-3) / 1e6
@@ -204,8 +301,12 @@ def main():
                                      "latency/issue bound (divergent traversal), see DESIGN.md"},
                 "stats": {k: int(v) * world for k, v in stats.items()}, "scene_build_s": build_s,
                 "bvh": scene.info()}
+        if lens_grad is not None:
+            line["lens_grad"] = lens_grad
         if not a.no_cpu_baseline:
             line["cpu_baseline"], _ = cpu_sample(a, scene.arrays, d["sensor"])
+            if lens_grad is not None:
+                line["lens_grad"]["cpu_baseline"] = lens_grad_cpu(mi, a)
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

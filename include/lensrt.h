@@ -190,6 +190,9 @@ typedef struct lrt_spot_params {
     float src_p[3];                    /* point emitter, CAMERA space (a distant point = a field angle) */
     float intensity[3];                /* RGB radiant intensity */
     int32_t shard_index, shard_count;  /* sample idx = shard_index + k*shard_count: identical streams for any GPU count */
+    float origin_offset;               /* 0: rays start at src_p as in sample_direction (:2336). > 0: the same ray starts this
+                                          many metres in front of the sampled front-plane point (well-conditioned in float32
+                                          for distant sources; see lrt_lens.cuh) */
 } lrt_spot_params;
 
 /* Accumulates intensity*weight/spp (R,G,B) and 1/spp (W) times the normalised filter weights into accum_dev

@@ -301,7 +301,12 @@ LRT_HD CameraRay lens_sample_ray(const LensSystem &L, const LensIf *ifs, float u
 // to the film plane z = 0. Returns the `valid` mask; uv in pixels of the crop window (ds.uv).
 struct DirectionSample { float uv_x, uv_y; strict::V3 p, d; float dist, pdf, weight; bool valid; LensRay ray_out; };
 
-LRT_HD DirectionSample lens_sample_direction(const LensSystem &L, const LensIf *ifs, strict::V3 ref_p, float a, float b) {
+// `origin_offset` = 0 reproduces the reference (the ray starts at ref_p). A positive value starts the SAME ray
+// origin_offset metres in front of the sampled front-plane point instead: from a distant reference point the
+// float32 products t*d cancel against o (0.3 px of noise from 1 km) and the asphere's absolute Newton tolerance
+// (10 eps metres) is unreachable, so the lens-design path uses a nearby origin.
+LRT_HD DirectionSample lens_sample_direction(const LensSystem &L, const LensIf *ifs, strict::V3 ref_p, float a, float b,
+                                             float origin_offset = 0.f) {
     using namespace strict;
     DirectionSample ds; ds.uv_x = ds.uv_y = 0.f; ds.p = v3(0, 0, 0); ds.d = v3(0, 0, 0); ds.dist = 0.f; ds.pdf = 0.f; ds.weight = 0.f;
     ds.valid = false; ds.ray_out.o = v3(0, 0, 0); ds.ray_out.d = v3(0, 0, 0);
@@ -314,7 +319,7 @@ LRT_HD DirectionSample lens_sample_direction(const LensSystem &L, const LensIf *
     V3 dir = sub(ref_p, aperture_p);
     float dist = norm(dir), inv_dist = rcp(dist);
     dir = mul(dir, inv_dist);
-    LensRay ray; ray.o = ref_p; ray.d = neg(dir);
+    LensRay ray; ray.o = origin_offset > 0.f ? at(aperture_p, dir, origin_offset) : ref_p; ray.d = neg(dir);
     bool valid = lens_trace_from_world(ifs, L.n, ray);
     ds.ray_out = ray;
     if (!valid) return ds;
@@ -329,7 +334,7 @@ LRT_HD DirectionSample lens_sample_direction(const LensSystem &L, const LensIf *
     if (!valid) return ds;
     ds.valid = true;
     ds.uv_x = mul(sx, L.res_x); ds.uv_y = mul(sy, L.res_y);
-    ds.p = aperture_p; ds.d = neg(dir);   // (ds.p - it.p) * inv_dist, expressed with the values already at hand
+    ds.p = aperture_p;
     ds.d = mul(sub(aperture_p, ref_p), inv_dist);
     ds.dist = dist;
     float aperture_pdf = rcp(mul(kPi, sqr(front_radius)));

@@ -33,7 +33,7 @@ struct SpotArgs {
     const LensSystem *lens;
     FilmParams film;
     uint32_t seed; int spp;
-    float src[3], intensity[3];
+    float src[3], intensity[3], origin_offset;
     long long n_my; int shard_index, shard_count;
     int win_x0, win_y0;             // tensor coordinates of the window origin
     float scale;
@@ -124,7 +124,7 @@ __global__ void __launch_bounds__(kSpotThreads) k_spot(SpotArgs A) {
         const float sa = rng.next_f32(), sb = rng.next_f32();
         n_samples++;
         if (!kAdjoint) {
-            DirectionSample ds = lens_sample_direction(L, L.ifs, src_p, sa, sb);
+            DirectionSample ds = lens_sample_direction(L, L.ifs, src_p, sa, sb, A.origin_offset);
             if (!ds.valid) continue;
             n_valid++;
             FootprintD fp;
@@ -153,7 +153,7 @@ __global__ void __launch_bounds__(kSpotThreads) k_spot(SpotArgs A) {
             V3 dirv = sub(src_p, ap);
             float dist = norm(dirv), inv_dist = rcp(dist);
             V3 dir = mul(dirv, inv_dist);
-            LensRay ray; ray.o = src_p; ray.d = neg(dir);
+            LensRay ray; ray.o = A.origin_offset > 0.f ? at(ap, dir, A.origin_offset) : src_p; ray.d = neg(dir);
             float tape[kMaxInterfaces][6];
             if (!lens_trace_from_world_taped(L.ifs, n_if, ray, tape)) continue;
             float t = div(-ray.o.z, ray.d.z);
@@ -213,10 +213,13 @@ __global__ void __launch_bounds__(kSpotThreads) k_spot(SpotArgs A) {
                 g_loc[k][10] += g[G_IORL]; g_loc[k][11] += g[G_IORR];
             }
             // ---- the ray's start: o0 = source (fixed), d0 = -dir, dir = (src - ap) / dist, ap.z = front.z
+            // (with an origin offset: o0 = ap + offset * dir, the same line through ap)
             float3 dir_bar = make_float3(-bar.d.x, -bar.d.y, -bar.d.z + dirz_bar);
+            float apz_bar = 0.f;
+            if (A.origin_offset > 0.f) { dir_bar += bar.o * A.origin_offset; apz_bar = bar.o.z; }
             const float3 dirf = f3(dir);
             float3 v_bar = (dir_bar - dirf * dot(dirf, dir_bar)) * inv_dist + dirf * dist_bar;
-            g_loc[n_if - 1][0] += -v_bar.z;
+            g_loc[n_if - 1][0] += apz_bar - v_bar.z;
         }
     }
 
@@ -268,12 +271,13 @@ static int spot_launch(lrt_sensor *s, const lrt_film_desc *film, const lrt_spot_
     rc = s->upload(); if (rc) return rc;
     A.lens = s->dev; A.seed = sp->seed; A.spp = sp->spp;
     for (int k = 0; k < 3; ++k) { A.src[k] = sp->src_p[k]; A.intensity[k] = sp->intensity[k]; }
+    A.origin_offset = sp->origin_offset;
     const long long nt = (long long) n_total;
     A.n_my = (nt - sp->shard_index + sp->shard_count - 1) / sp->shard_count;
     A.shard_index = sp->shard_index; A.shard_count = sp->shard_count;
     A.scale = 1.f / (float) sp->spp;
     // window centre: the chief ray (centre of the front element), traced on the host with the same code
-    DirectionSample c = lens_sample_direction(s->host, s->host.ifs, strict::v3(sp->src_p[0], sp->src_p[1], sp->src_p[2]), .5f, .5f);
+    DirectionSample c = lens_sample_direction(s->host, s->host.ifs, strict::v3(sp->src_p[0], sp->src_p[1], sp->src_p[2]), .5f, .5f, sp->origin_offset);
     float cx = c.valid ? c.uv_x : .5f * film->size_x, cy = c.valid ? c.uv_y : .5f * film->size_y;
     A.win_x0 = (int) floorf(cx) + film->border - kWin / 2; A.win_y0 = (int) floorf(cy) + film->border - kWin / 2;
     A.accum = accum; A.grad_accum = grad_accum; A.grad_rows = grad_rows; A.stats = stats;

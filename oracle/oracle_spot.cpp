@@ -25,7 +25,8 @@ static V3 xform_affine_diag(const float *m, V3 p) {   // Transform4f::transform_
 }
 
 // realisticlens.cpp:2301-2394, camera space (to_world = identity in the tests that call this)
-bool camera_sample_direction(const Camera &c, V3 ref_p, V2 sample, float *out11) {
+// origin_offset > 0: the product's well-conditioned variant (same ray, started near the lens; lrt_lens.cuh)
+bool camera_sample_direction(const Camera &c, V3 ref_p, V2 sample, float *out11, float origin_offset = 0.f) {
     for (int i = 0; i < 11; ++i) out11[i] = 0.f;
     bool active = ref_p.z >= c.near_clip && ref_p.z <= c.far_clip;
     if (!active) return false;
@@ -37,6 +38,8 @@ bool camera_sample_direction(const Camera &c, V3 ref_p, V2 sample, float *out11)
     float dist = norm(dir), inv_dist = rcp(dist);
     dir = dir * inv_dist;
     Ray world_ray { ref_p, -dir }, ray_out;
+    if (origin_offset > 0.f)
+        world_ray.o = { fmadd(dir.x, origin_offset, aperture_p.x), fmadd(dir.y, origin_offset, aperture_p.y), fmadd(dir.z, origin_offset, aperture_p.z) };
     bool valid = c.trace_from_world(world_ray, ray_out);
     if (!valid) return false;
     float t = -ray_out.o.z / ray_out.d.z;
@@ -218,14 +221,14 @@ int orc_trace_jac(int n_if, const float *rows16, int from_world, const float *od
 
 // ptracer-style spot image in float64 accumulators: storage [size_y, size_x, 4]; returns the number of valid samples
 long long orc_spot_render(void *h, int size_x, int size_y, int off_x, int off_y, int filter_kind, float filter_param,
-                          uint32_t seed, int spp, const float *src3, const float *intensity3, double *storage);
+                          uint32_t seed, int spp, const float *src3, const float *intensity3, float origin_offset, double *storage);
 
 // d/d(rows16[sel]) of  Phi = sum_samples sum_taps G[tap] . contribution  (masks frozen), forward-mode in float64.
 // rows16: [n_if,16] interface table (rear -> front); sel: n_sel pairs (interface, column); grad_out[n_sel].
 // Also returns Phi itself (value) so that tests can finite-difference it.
 double orc_spot_grad(int n_if, const float *rows16, const float *f2s16, float normalization, float near_clip, float far_clip,
                      int size_x, int size_y, int off_x, int off_y, int filter_kind, float filter_param, uint32_t seed, int spp,
-                     const float *src3, const float *intensity3, const float *G /* [sy,sx,4] */, int n_sel, const int *sel,
+                     const float *src3, const float *intensity3, float origin_offset, const float *G /* [sy,sx,4] */, int n_sel, const int *sel,
                      const double *delta /* optional [n_sel] perturbation added to the selected entries */, double *grad_out) {
     g_nseeds = std::min(n_sel, kMaxSeeds);
     std::vector<DIf> ifs(n_if);
@@ -267,7 +270,7 @@ double orc_spot_grad(int n_if, const float *rows16, const float *f2s16, float no
         DV3 v = src - ap;
         Dual dist = dsqrt(ddot(v, v));
         DV3 dir = v * (Dual(1.0) / dist);
-        DRay ray { src, dir * Dual(-1.0) };
+        DRay ray { origin_offset > 0.f ? ap + dir * Dual(origin_offset) : src, dir * Dual(-1.0) };
         bool ok = true;
         for (int i = n_if - 1; i >= 0 && ok; --i) ok = d_interact(ifs[i], ray);
         if (!ok) continue;
@@ -305,7 +308,7 @@ double orc_spot_grad(int n_if, const float *rows16, const float *f2s16, float no
 
 // float32 spot image (the checker of lrt_spot_render): pinned sample_direction + the oracle's ImageBlock::put
 extern "C" long long orc_spot_render(void *h, int size_x, int size_y, int off_x, int off_y, int filter_kind, float filter_param,
-                                     uint32_t seed, int spp, const float *src3, const float *intensity3, double *storage) {
+                                     uint32_t seed, int spp, const float *src3, const float *intensity3, float origin_offset, double *storage) {
     const Camera &c = *(Camera *) h;
     orc::Filter flt; flt.init(filter_kind, filter_param);
     const long long n = (long long) size_x * size_y * spp;
@@ -315,7 +318,7 @@ extern "C" long long orc_spot_render(void *h, int size_x, int size_y, int off_x,
         PCG32 rng; sampler_seed_jit(rng, seed, (uint32_t) idx);
         float sa = rng.next_float32(), sb = rng.next_float32();
         float o[11];
-        if (!camera_sample_direction(c, { src3[0], src3[1], src3[2] }, { sa, sb }, o)) continue;
+        if (!camera_sample_direction(c, { src3[0], src3[1], src3[2] }, { sa, sb }, o, origin_offset)) continue;
         valid++;
         float wv = o[10] * scale;
         float vals[4] = { intensity3[0] * wv, intensity3[1] * wv, intensity3[2] * wv, scale };

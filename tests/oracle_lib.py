@@ -202,7 +202,7 @@ def rel_rmse(a, b):
 
 
 # ------------------------------------------------------------------------------------------------ spot path
-def orc_spot_render(cam_h, film: FilmSpec, src_p, intensity, seed, spp, filter_kind=1, filter_param=0.0):
+def orc_spot_render(cam_h, film: FilmSpec, src_p, intensity, seed, spp, filter_kind=1, filter_param=0.0, origin_offset=0.0):
     """float32 checker of lrt_spot_render -> (storage float64 [ch,cw,4], valid samples)."""
     L = oracle()
     L.orc_spot_render.restype = C.c_longlong
@@ -210,12 +210,12 @@ def orc_spot_render(cam_h, film: FilmSpec, src_p, intensity, seed, spp, filter_k
     st = np.zeros((ch, cw, 4), np.float64)
     valid = L.orc_spot_render(cam_h, C.c_int(cw), C.c_int(ch), C.c_int(cx), C.c_int(cy), C.c_int(filter_kind), c_f(filter_param),
                               C.c_uint32(seed), C.c_int(spp), fp(np.ascontiguousarray(src_p, f32)),
-                              fp(np.ascontiguousarray(intensity, f32)), st.ctypes.data_as(C.POINTER(C.c_double)))
+                              fp(np.ascontiguousarray(intensity, f32)), c_f(origin_offset), st.ctypes.data_as(C.POINTER(C.c_double)))
     return st, valid
 
 
 def orc_spot_grad(rows, f2s, normalization, near, far, film: FilmSpec, src_p, intensity, seed, spp, G, sel, filter_kind=1,
-                  filter_param=0.0, delta=None):
+                  filter_param=0.0, delta=None, origin_offset=0.0):
     """float64 dual-number checker: (Phi, dPhi/d rows[sel]) for Phi = <G, storage(rows)> with frozen masks."""
     L = oracle()
     L.orc_spot_grad.restype = C.c_double
@@ -226,7 +226,7 @@ def orc_spot_grad(rows, f2s, normalization, near, far, film: FilmSpec, src_p, in
     phi = L.orc_spot_grad(C.c_int(len(rows)), fp(np.ascontiguousarray(rows, f32)), fp(np.ascontiguousarray(f2s, f32).ravel()),
                           c_f(normalization), c_f(near), c_f(far), C.c_int(cw), C.c_int(ch), C.c_int(cx), C.c_int(cy),
                           C.c_int(filter_kind), c_f(filter_param), C.c_uint32(seed), C.c_int(spp),
-                          fp(np.ascontiguousarray(src_p, f32)), fp(np.ascontiguousarray(intensity, f32)),
+                          fp(np.ascontiguousarray(src_p, f32)), fp(np.ascontiguousarray(intensity, f32)), c_f(origin_offset),
                           fp(np.ascontiguousarray(G, f32)), C.c_int(len(sel)), sel.ctypes.data_as(IP),
                           dl.ctypes.data_as(C.POINTER(C.c_double)) if dl is not None else None,
                           out.ctypes.data_as(C.POINTER(C.c_double)))
