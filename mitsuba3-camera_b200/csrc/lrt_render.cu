@@ -3,14 +3,19 @@
 // PathIntegrator::sample (src/integrators/path.cpp:95-287) and ImageBlock::put + put_block
 // (src/render/imageblock.cpp:135-172,174-532) for hdrfilm's R,G,B,W storage (src/films/hdrfilm.cpp:245-297).
 //
-// Execution model (not the reference's wavefront): persistent CTAs pull work items (pixel tile x sample
-// chunk) from a global counter. A CTA is 4 warps = a tile of 32x4 pixels; each lane owns ONE pixel and walks
-// its samples sequentially, so all lanes stay busy until the tile is done (no cross-lane compaction needed).
-// Sample `j` of pixel `p` always uses PCG32 stream idx = p*spp + j (sampler.cpp:121-130) whatever the
-// sharding, so images are identical up to float summation order for any tile/chunk/GPU split.
-// Dead lanes are refilled in batches (warp ballot): the divergent lens section only runs when >= 8 lanes
-// need a new camera ray or nobody has a live path. Splats go to a shared-memory tile (one lane = one pixel
-// => a given tap never collides inside a warp) and the tile is flushed once with global float atomics.
+// Execution model (not the reference's wavefront): persistent CTAs pull work items (pixel tile x sample chunk) from
+// a global counter. A CTA is 4 warps = a tile of 32x4 pixels; each WARP owns one pixel row of the tile and the pool of
+// its 32 x chunk_spp samples. Sample `j` of pixel `p` always uses PCG32 stream idx = p*spp + j (sampler.cpp:121-130)
+// whatever the sharding, so images are identical up to float summation order for any tile / chunk / GPU split.
+// The three stages have very different shapes, so each runs at its own width and they meet in shared-memory queues:
+//   * camera rays are generated 32 at a time with all lanes active (the lens trace is the same instruction sequence for
+//     every lane) and the transmitted ones are pushed into a per-warp FIFO (ray, weight, film position, RNG state);
+//   * a lane whose path ended pops the next camera ray, so lanes never wait for each other's paths;
+//   * BVH traversal is resumable (lrt_trace.cuh): path segments and shadow rays of different lanes share ONE traversal
+//     site, and a burst ends as soon as a quarter of its lanes have finished, so they can shade and fetch new rays;
+//   * finished samples go to a per-warp splat queue that is drained 32 entries at a time into the shared-memory film
+//     tile (float atomics in shared memory are CAS loops on this architecture: run them at full width), and the tile
+//     is flushed once per work item with global float atomics.
 #include "lrt_internal.h"
 #include "lrt_rng.cuh"
 #include "lrt_shade.cuh"
@@ -18,8 +23,9 @@
 
 namespace lrt {
 
-constexpr int kTileW = 32, kTileH = 4, kCtaThreads = kTileW * kTileH;
-constexpr int kRefillThreshold = 8;
+constexpr int kTileW = 32, kTileH = 4, kCtaThreads = kTileW * kTileH, kWarps = kCtaThreads / 32;
+constexpr int kFifo = 64, kFifoWords = 14;      // camera-ray FIFO per warp: o[3] d[3] maxt weight sx sy rng.state rng.inc
+constexpr int kQueue = 64, kQueueWords = 5;     // splat queue per warp: sx sy r g b
 
 struct RenderArgs {
     SceneView sc;
@@ -28,11 +34,33 @@ struct RenderArgs {
     uint32_t seed; int spp, max_depth, rr_depth;
     int tiles_x, n_chunks, chunk_spp;
     int shard_index, shard_count; long long n_items;
-    int pad, smem_w, smem_h;
+    int pad, smem_w, smem_h, exit_drop, leaf_min;
     unsigned long long *counter;
     float *accum;
     unsigned long long *stats;     // [0] samples, [1] lens misses, [2] rays, [3] bounces, [4] BVH nodes fetched, [5] triangles tested
 };
+
+// ImageBlock::put of one sample into the shared-memory tile (tensor coordinates of tile(0,0) = (ox, oy))
+LRT_D void splat_to_tile(const FilmParams &F, float *tile, int smem_w, int ox, int oy, float sx, float sy, float3 value) {
+    Footprint fp;
+    if (!film_footprint(F, sx, sy, fp)) return;
+    const bool box = F.kind == FILTER_BOX;
+    const int sw = box ? F.size_x : F.size_x + 2 * F.border, shh = F.size_y + 2 * F.border;
+    for (int iy = 0; iy < fp.ny; ++iy) {
+        const int y = fp.y0 + iy;
+        if ((unsigned) y >= (unsigned) shh) continue;
+        for (int ix = 0; ix < fp.nx; ++ix) {
+            const int x = fp.x0 + ix;
+            if ((unsigned) x >= (unsigned) sw) continue;
+            const float w = fp.wy[iy] * fp.wx[ix];
+            float *dst = tile + ((y - oy) * smem_w + (x - ox)) * 4;
+            if (value.x != 0.f) atomicAdd(dst, value.x * w);
+            if (value.y != 0.f) atomicAdd(dst + 1, value.y * w);
+            if (value.z != 0.f) atomicAdd(dst + 2, value.z * w);
+            atomicAdd(dst + 3, w);
+        }
+    }
+}
 
 __global__ void __launch_bounds__(kCtaThreads) k_render(RenderArgs A) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -40,73 +68,140 @@ __global__ void __launch_bounds__(kCtaThreads) k_render(RenderArgs A) {
     float *tile = reinterpret_cast<float *>(smem_raw + sizeof(LensSystem));
     __shared__ long long s_item;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    const int tile_elems = A.smem_w * A.smem_h * 4;
+    float *fifo = tile + tile_elems + warp * (kFifo * kFifoWords + kQueue * kQueueWords);   // [word][slot]
+    float *queue = fifo + kFifo * kFifoWords;                                                // [word][slot]
     {
         const uint4 *src = reinterpret_cast<const uint4 *>(A.lens);
         uint4 *dst = reinterpret_cast<uint4 *>(&L);
         for (int i = tid; i < (int) (sizeof(LensSystem) / 16); i += kCtaThreads) dst[i] = src[i];
     }
     const FilmParams &F = A.film;
-    const int tile_elems = A.smem_w * A.smem_h * 4;
+    const bool box = F.kind == FILTER_BOX;
     const float scale_x = 1.f / (float) F.size_x, scale_y = 1.f / (float) F.size_y;
     const float offs_x = -(float) F.off_x * scale_x, offs_y = -(float) F.off_y * scale_y;
     unsigned long long n_samples = 0, n_miss = 0, n_rays = 0, n_bounces = 0, n_nodes = 0, n_tris = 0;
+    uint32_t st_ref[kTravStack]; float st_t[kTravStack];
 
     while (true) {
         __syncthreads();
         if (tid == 0) s_item = (long long) atomicAdd(A.counter, 1ULL);
         for (int i = tid; i < tile_elems; i += kCtaThreads) tile[i] = 0.f;
         __syncthreads();
-        long long item = s_item;
+        const long long item = s_item;
         if (item >= A.n_items) break;
         const int chunk = (int) (item % A.n_chunks);
         const long long tile_id = (long long) A.shard_index + (item / A.n_chunks) * A.shard_count;
         const int tx = (int) (tile_id % A.tiles_x), ty = (int) (tile_id / A.tiles_x);
-        const int px = tx * kTileW + lane, py = ty * kTileH + warp;
+        const int px = tx * kTileW + lane, py = ty * kTileH + warp;      // the pixel this lane GENERATES samples for
         const bool in_film = px < F.size_x && py < F.size_y;
-        const int ox = tx * kTileW - A.pad, oy = ty * kTileH - A.pad;   // tensor coords of smem (0,0)
-        int j = chunk * A.chunk_spp;
-        const int j_end = in_film ? min(A.spp, j + A.chunk_spp) : j;
+        const int ox = tx * kTileW - A.pad, oy = ty * kTileH - A.pad;    // tensor coords of smem (0,0)
+        const int j0 = chunk * A.chunk_spp;
+        const int n_rounds = py < F.size_y ? max(0, min(A.spp, j0 + A.chunk_spp) - j0) : 0;   // generation rounds of this warp
         const uint32_t idx_base = (uint32_t) (py * F.size_x + px) * (uint32_t) A.spp;
         const float posx = (float) (px + F.off_x), posy = (float) (py + F.off_y);
+        int round = 0, fifo_head = 0, fifo_count = 0, q_count = 0;       // warp-uniform
 
-        // ---- per-lane path state. phase: 0 = needs a new sample, 1 = path segment (closest hit), 2 = shadow ray
+        // ---- per-lane path state. phase: 0 = idle, 1 = path segment (closest hit), 2 = shadow ray
         int phase = 0;
         Pcg32 rng; rng.state = 0; rng.inc = 1;
-        float3 ro = make_float3(0, 0, 0), rd = make_float3(0, 0, 1); float rmaxt = 0.f;      // ray being traced now
+        float3 ro = make_float3(0, 0, 0), rd = make_float3(0, 0, 1);                          // ray being traced now
         float3 wi_w = make_float3(0, 0, 1);                                                   // direction of the path segment
         float3 throughput = make_float3(1, 1, 1), result = make_float3(0, 0, 0), prev_p = make_float3(0, 0, 0);
-        float eta = 1.f, prev_pdf = 1.f, cam_weight = 0.f, spx = 0.f, spy = 0.f;
+        float eta = 1.f, prev_pdf = 1.f, cam_weight = 0.f, sx = 0.f, sy = 0.f;
         int depth = 0; bool prev_delta = true, valid_ray = false;
         RayHit seg; seg.t = 0.f; seg.u = seg.v = 0.f; seg.tri = -1;                           // hit of the current segment
+        Trav T; trav_init(T, 0.f); T.cur = kTravDone;
+
+        // drain `n` entries from the top of the splat queue (n <= 32), one per lane
+        auto drain = [&](int n) {
+            __syncwarp();
+            if (lane < n) {
+                const int s = q_count - n + lane;
+                splat_to_tile(F, tile, A.smem_w, ox, oy, queue[0 * kQueue + s], queue[1 * kQueue + s],
+                              make_float3(queue[2 * kQueue + s], queue[3 * kQueue + s], queue[4 * kQueue + s]));
+            }
+            q_count -= n;
+            __syncwarp();
+        };
+        // push one finished sample per lane with `pred`
+        auto push_splat = [&](bool pred, float qx, float qy, float3 v) {
+            const unsigned m = __ballot_sync(0xffffffffu, pred);
+            if (pred) {
+                const int s = q_count + __popc(m & lt_mask);
+                queue[0 * kQueue + s] = qx; queue[1 * kQueue + s] = qy;
+                queue[2 * kQueue + s] = v.x; queue[3 * kQueue + s] = v.y; queue[4 * kQueue + s] = v.z;
+            }
+            q_count += __popc(m);
+        };
 
         while (true) {
-            const bool need = phase == 0 && j < j_end;
-            const unsigned need_mask = __ballot_sync(0xffffffffu, need);
-            const unsigned live_mask = __ballot_sync(0xffffffffu, phase != 0);
-            if (!need_mask && !live_mask) break;
-            const bool refill = live_mask == 0 || __popc(need_mask) >= kRefillThreshold;
-            bool splat = false; float3 value = make_float3(0, 0, 0);
-
-            if (refill && need) {
-                // ---- render_sample(): draws in the reference's order (integrator.cpp:435-448)
-                rng.seed_sample(A.seed, idx_base + (uint32_t) j); j++; n_samples++;
-                float u0 = rng.next_f32(), u1 = rng.next_f32();
-                spx = strict::add(posx, u0); spy = strict::add(posy, u1);
-                float ax = strict::fmadd(spx, scale_x, offs_x), ay = strict::fmadd(spy, scale_y, offs_y);
-                float a = .5f, b = .5f;
-                if (L.kind == 0) { a = rng.next_f32(); b = rng.next_f32(); }
-                CameraRay cr = sensor_sample_ray(L, L.ifs, ax, ay, a, b);
-                cam_weight = cr.weight;
-                if (cr.weight > 0.f && A.max_depth != 0) {
-                    phase = 1; ro = cr.o; rd = cr.d; rmaxt = cr.maxt;
+            if (q_count >= 32) drain(32);
+            // ---- A. camera rays, 32 at a time: render_sample() draws in the reference's order (integrator.cpp:435-448)
+            if (fifo_count < 32 && round < n_rounds) {
+                const int j = j0 + round; round++;
+                bool hit = false; CameraRay cr; Pcg32 g; float gx = 0.f, gy = 0.f;
+                if (in_film) {
+                    g.seed_sample(A.seed, idx_base + (uint32_t) j); n_samples++;
+                    const float u0 = g.next_f32(), u1 = g.next_f32();
+                    const float spx = strict::add(posx, u0), spy = strict::add(posy, u1);
+                    const float ax = strict::fmadd(spx, scale_x, offs_x), ay = strict::fmadd(spy, scale_y, offs_y);
+                    float a = .5f, b = .5f;
+                    if (L.kind == 0) { a = g.next_f32(); b = g.next_f32(); }
+                    cr = sensor_sample_ray(L, L.ifs, ax, ay, a, b);
+                    gx = box ? posx : spx; gy = box ? posy : spy;
+                    hit = cr.weight > 0.f && A.max_depth != 0;
+                    if (!(cr.weight > 0.f)) n_miss++;
+                }
+                // vignetted (or max_depth == 0): RGB 0, weight 1 (integrator.cpp:461-490)
+                push_splat(in_film && !hit, gx, gy, make_float3(0, 0, 0));
+                const unsigned hm = __ballot_sync(0xffffffffu, hit);
+                if (hit) {
+                    const int s = (fifo_head + fifo_count + __popc(hm & lt_mask)) & (kFifo - 1);
+                    fifo[0 * kFifo + s] = cr.o.x; fifo[1 * kFifo + s] = cr.o.y; fifo[2 * kFifo + s] = cr.o.z;
+                    fifo[3 * kFifo + s] = cr.d.x; fifo[4 * kFifo + s] = cr.d.y; fifo[5 * kFifo + s] = cr.d.z;
+                    fifo[6 * kFifo + s] = cr.maxt; fifo[7 * kFifo + s] = cr.weight; fifo[8 * kFifo + s] = gx; fifo[9 * kFifo + s] = gy;
+                    fifo[10 * kFifo + s] = __uint_as_float((uint32_t) g.state); fifo[11 * kFifo + s] = __uint_as_float((uint32_t) (g.state >> 32));
+                    fifo[12 * kFifo + s] = __uint_as_float((uint32_t) g.inc); fifo[13 * kFifo + s] = __uint_as_float((uint32_t) (g.inc >> 32));
+                }
+                fifo_count += __popc(hm);
+                __syncwarp();
+                if (q_count >= 32) drain(32);
+            }
+            // ---- B. idle lanes take the next camera rays
+            {
+                const unsigned nm = __ballot_sync(0xffffffffu, phase == 0);
+                const int take = min(__popc(nm), fifo_count), rank = __popc(nm & lt_mask);
+                if (phase == 0 && rank < take) {
+                    const int s = (fifo_head + rank) & (kFifo - 1);
+                    ro = make_float3(fifo[0 * kFifo + s], fifo[1 * kFifo + s], fifo[2 * kFifo + s]);
+                    rd = make_float3(fifo[3 * kFifo + s], fifo[4 * kFifo + s], fifo[5 * kFifo + s]);
+                    trav_init(T, fifo[6 * kFifo + s]);
+                    cam_weight = fifo[7 * kFifo + s]; sx = fifo[8 * kFifo + s]; sy = fifo[9 * kFifo + s];
+                    rng.state = (uint64_t) __float_as_uint(fifo[10 * kFifo + s]) | ((uint64_t) __float_as_uint(fifo[11 * kFifo + s]) << 32);
+                    rng.inc = (uint64_t) __float_as_uint(fifo[12 * kFifo + s]) | ((uint64_t) __float_as_uint(fifo[13 * kFifo + s]) << 32);
+                    phase = 1;
                     throughput = make_float3(1, 1, 1); result = make_float3(0, 0, 0); eta = 1.f; depth = 0;
                     prev_p = make_float3(0, 0, 0); prev_pdf = 1.f; prev_delta = true; valid_ray = false;
-                } else { if (!(cr.weight > 0.f)) n_miss++; splat = true; }   // vignetted: RGB 0, weight 1 (integrator.cpp:461-490)
-            } else if (phase != 0) {
-                // ---- the ONE traversal site: path segments and shadow rays of different lanes run together
-                unsigned work = 0;
-                const RayHit h = bvh_intersect(A.sc.bvh, ro, rd, rmaxt, phase == 2, work);
-                n_rays++; n_nodes += work & 0xffffu; n_tris += work >> 16;
+                }
+                fifo_head = (fifo_head + take) & (kFifo - 1); fifo_count -= take;
+                __syncwarp();
+            }
+            if (__ballot_sync(0xffffffffu, phase != 0) == 0) {
+                if (fifo_count == 0 && round >= n_rounds) break;
+                continue;
+            }
+            // ---- C. the ONE traversal site: path segments and shadow rays of different lanes advance together
+            unsigned work = 0;
+            bvh_burst(A.sc.bvh, ro, rd, T, st_ref, st_t, phase != 0, phase == 2, A.exit_drop, A.leaf_min, work);
+            n_nodes += work & 0xffffu; n_tris += work >> 16;
+
+            // ---- D. lanes whose ray is finished shade it
+            bool done_path = false; float3 value = make_float3(0, 0, 0);
+            if (phase != 0 && T.cur == kTravDone) {
+                const RayHit h = T.hit;
+                n_rays++;
                 bool finish = false, occluded = true;
                 if (phase == 1) {
                     // ---- first half of one iteration of PathIntegrator::sample's loop (path.cpp:142-208)
@@ -137,14 +232,14 @@ __global__ void __launch_bounds__(kCtaThreads) k_render(RenderArgs A) {
                                 if (es.pdf != 0.f) {   // shadow ray: Interaction::spawn_ray_to (interaction.h:139-146)
                                     float3 so = offset_p(si.p, si.n, es.p - si.p);
                                     float3 sd = es.p - so; float sdist = sqrtf(dot(sd, sd));
-                                    ro = so; rd = sd * (1.f / sdist); rmaxt = sdist * (1.f - kShadowEpsilon);
+                                    ro = so; rd = sd * (1.f / sdist); trav_init(T, sdist * (1.f - kShadowEpsilon));
                                     want_shadow = true;
                                 }
                             }
                         }
                     }
                     if (want_shadow) { phase = 2; finish = false; }
-                    else if (!finish) { phase = 0; splat = true; if (valid_ray) value = result * cam_weight; }
+                    else if (!finish) { phase = 0; done_path = true; if (valid_ray) value = result * cam_weight; }
                 } else {
                     finish = true; occluded = h.tri >= 0;
                 }
@@ -161,7 +256,7 @@ __global__ void __launch_bounds__(kCtaThreads) k_render(RenderArgs A) {
                     BsdfResult bs = bsdf_eval_pdf_sample(A.sc, bsdf_id, si.wi, wo, s1, s2x, s2y);
                     if (active_em) result += throughput * (bs.val * es.weight * mis_weight(es.pdf, bs.pdf));
                     float3 wo_w = si.to_world(bs.wo);
-                    ro = offset_p(si.p, si.n, wo_w); rd = wo_w; rmaxt = kLargest;
+                    ro = offset_p(si.p, si.n, wo_w); rd = wo_w; trav_init(T, kLargest);
                     throughput *= bs.weight; eta *= bs.seta;
                     valid_ray = true;
                     prev_p = si.p; prev_pdf = bs.spdf; prev_delta = bs.delta;
@@ -172,34 +267,14 @@ __global__ void __launch_bounds__(kCtaThreads) k_render(RenderArgs A) {
                     if (rr_active) throughput *= 1.f / rr_prob;
                     bool alive = (!rr_active || rr_sample < rr_prob) && tmax != 0.f;
                     phase = alive ? 1 : 0;
-                    if (!alive) { splat = true; value = result * cam_weight; }
+                    if (!alive) { done_path = true; value = result * cam_weight; T.cur = kTravDone; }
                 }
             }
-
-            if (splat) {
-                Footprint fp;
-                const bool box = F.kind == FILTER_BOX;
-                if (film_footprint(F, box ? posx : spx, box ? posy : spy, fp)) {
-                    const int sw = box ? F.size_x : F.size_x + 2 * F.border, shh = F.size_y + 2 * F.border;
-                    for (int iy = 0; iy < fp.ny; ++iy) {
-                        int y = fp.y0 + iy;
-                        if ((unsigned) y >= (unsigned) shh) continue;
-                        for (int ix = 0; ix < fp.nx; ++ix) {
-                            int x = fp.x0 + ix;
-                            if ((unsigned) x >= (unsigned) sw) continue;
-                            float w = fp.wy[iy] * fp.wx[ix];
-                            float *dst = tile + ((y - oy) * A.smem_w + (x - ox)) * 4;
-                            if (value.x != 0.f) atomicAdd(dst, value.x * w);
-                            if (value.y != 0.f) atomicAdd(dst + 1, value.y * w);
-                            if (value.z != 0.f) atomicAdd(dst + 2, value.z * w);
-                            atomicAdd(dst + 3, w);
-                        }
-                    }
-                }
-            }
+            push_splat(done_path, sx, sy, value);
         }
-
-        // ---- put_block(): flush the tile into the film accumulator
+        // ---- drain what is left, then put_block(): flush the tile into the film accumulator
+        if (q_count > 32) drain(32);
+        if (q_count > 0) drain(q_count);
         __syncthreads();
         const int sw = F.size_x + 2 * F.border, shh = F.size_y + 2 * F.border;
         for (int i = tid; i < A.smem_w * A.smem_h; i += kCtaThreads) {
@@ -267,7 +342,13 @@ int launch_render(const lrt_scene *sc, lrt_sensor *sensor, const lrt_film_desc *
     long long n_tiles = (long long) A.tiles_x * tiles_y;
     long long my_tiles = (n_tiles - rp->shard_index + rp->shard_count - 1) / rp->shard_count;
     int dev = 0, sms = 148; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    size_t smem = sizeof(LensSystem) + (size_t) A.smem_w * A.smem_h * 16;
+    size_t smem = sizeof(LensSystem) + (size_t) A.smem_w * A.smem_h * 16 + (size_t) kWarps * (kFifo * kFifoWords + kQueue * kQueueWords) * 4;
+    {   // traversal bursts end when this many 32nds of their lanes have finished (LRT_EXIT_DROP overrides; tuning knob)
+        const char *e = getenv("LRT_EXIT_DROP"); A.exit_drop = e ? atoi(e) : 24;
+        if (A.exit_drop < 1) A.exit_drop = 1; if (A.exit_drop > 32) A.exit_drop = 32;
+        e = getenv("LRT_LEAF_MIN"); A.leaf_min = e ? atoi(e) : 6;
+        if (A.leaf_min < 1) A.leaf_min = 1;
+    }
     static bool attr_set = false;
     if (!attr_set) { cudaFuncSetAttribute(k_render, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024); attr_set = true; }
     int per_sm = 1; cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_render, kCtaThreads, smem);

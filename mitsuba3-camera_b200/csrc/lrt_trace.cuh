@@ -22,87 +22,128 @@ struct RayHit { float t, u, v; int tri; };   // tri = index into the reordered t
 // 0x4B0000qq as float = 8388608 + q
 LRT_D float qbias(uint32_t w, uint32_t sel) { return __uint_as_float(__byte_perm(w, 0x4B000000u, sel)); }
 
-LRT_D RayHit bvh_intersect(const BvhView &bvh, float3 o, float3 d, float tmax, bool any_hit, unsigned &work) {
-    RayHit hit; hit.t = inf_f(); hit.u = hit.v = 0.f; hit.tri = -1;
-    const float tiny = 1e-30f;   // guard against 0 * inf in the slab test
-    float3 idir = make_float3(1.f / (fabsf(d.x) < tiny ? copysignf(tiny, d.x) : d.x), 1.f / (fabsf(d.y) < tiny ? copysignf(tiny, d.y) : d.y),
-                              1.f / (fabsf(d.z) < tiny ? copysignf(tiny, d.z) : d.z));
-    const bool nx = idir.x < 0.f, ny = idir.y < 0.f, nz = idir.z < 0.f;
+constexpr int kTravStack = 64;
+constexpr uint32_t kTravDone = 0x7fffffffu;
 
-    constexpr int kStack = 64;
-    constexpr uint32_t kDone = 0x7fffffffu;
-    uint32_t st_ref[kStack]; float st_t[kStack];
-    int sp = 0;
-    uint32_t cur = 0;            // bit31 = leaf; leaf: bits 29..28 count, 27..0 first triangle
-    while (cur != kDone) {
-        // ---- inner nodes: descend to the nearest child until a leaf (or nothing) is reached
-        while (!(cur & 0x80000000u)) {
-            work += 1u;
-            const uint4 *np = bvh.nodes + 5 * (size_t) cur;
-            const uint4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
-            const float sx = __uint_as_float((n0.w & 0xffu) << 23) * idir.x, sy = __uint_as_float(((n0.w >> 8) & 0xffu) << 23) * idir.y,
-                        sz = __uint_as_float(((n0.w >> 16) & 0xffu) << 23) * idir.z;
-            const float bx = fmaf(-8388608.f, sx, (__uint_as_float(n0.x) - o.x) * idir.x),
-                        by = fmaf(-8388608.f, sy, (__uint_as_float(n0.y) - o.y) * idir.y),
-                        bz = fmaf(-8388608.f, sz, (__uint_as_float(n0.z) - o.z) * idir.z);
-            // near / far bound words per axis, children 0-3 (a) and 4-7 (b)
-            const uint32_t nxa = nx ? n3.z : n2.x, nxb = nx ? n3.w : n2.y, fxa = nx ? n2.x : n3.z, fxb = nx ? n2.y : n3.w;
-            const uint32_t nya = ny ? n4.x : n2.z, nyb = ny ? n4.y : n2.w, fya = ny ? n2.z : n4.x, fyb = ny ? n2.w : n4.y;
-            const uint32_t nza = nz ? n4.z : n3.x, nzb = nz ? n4.w : n3.y, fza = nz ? n3.x : n4.z, fzb = nz ? n3.y : n4.w;
-            uint32_t best = kDone; float best_t = inf_f();
+// Resumable traversal state of one ray: `cur` = node / leaf to visit next (bit31 = leaf: bits 29..28 count, 27..0 first
+// triangle; kTravDone = finished), the stack (t_near, reference) lives in the caller's local memory.
+struct Trav { uint32_t cur; int sp; RayHit hit; float tmax; };
+
+LRT_D void trav_init(Trav &T, float tmax) {
+    T.cur = 0; T.sp = 0; T.tmax = tmax;
+    T.hit.t = inf_f(); T.hit.u = T.hit.v = 0.f; T.hit.tri = -1;
+}
+
+LRT_D float3 trav_idir(float3 d) {
+    const float tiny = 1e-30f;   // guard against 0 * inf in the slab test
+    return make_float3(1.f / (fabsf(d.x) < tiny ? copysignf(tiny, d.x) : d.x), 1.f / (fabsf(d.y) < tiny ? copysignf(tiny, d.y) : d.y),
+                       1.f / (fabsf(d.z) < tiny ? copysignf(tiny, d.z) : d.z));
+}
+
+// One inner node: test the 8 quantised child boxes, continue with the nearest hit child, push the others; if nothing is
+// hit pop the next candidate. Requires T.cur to be an inner node.
+LRT_D void trav_node_step(const BvhView &bvh, float3 o, float3 idir, Trav &T, uint32_t *st_ref, float *st_t, unsigned &work) {
+    const bool nx = idir.x < 0.f, ny = idir.y < 0.f, nz = idir.z < 0.f;
+    int sp = T.sp; const float tmax = T.tmax;
+    work += 1u;
+    const uint4 *np = bvh.nodes + 5 * (size_t) T.cur;
+    const uint4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
+    const float sx = __uint_as_float((n0.w & 0xffu) << 23) * idir.x, sy = __uint_as_float(((n0.w >> 8) & 0xffu) << 23) * idir.y,
+                sz = __uint_as_float(((n0.w >> 16) & 0xffu) << 23) * idir.z;
+    const float bx = fmaf(-8388608.f, sx, (__uint_as_float(n0.x) - o.x) * idir.x),
+                by = fmaf(-8388608.f, sy, (__uint_as_float(n0.y) - o.y) * idir.y),
+                bz = fmaf(-8388608.f, sz, (__uint_as_float(n0.z) - o.z) * idir.z);
+    // near / far bound words per axis, children 0-3 (a) and 4-7 (b)
+    const uint32_t nxa = nx ? n3.z : n2.x, nxb = nx ? n3.w : n2.y, fxa = nx ? n2.x : n3.z, fxb = nx ? n2.y : n3.w;
+    const uint32_t nya = ny ? n4.x : n2.z, nyb = ny ? n4.y : n2.w, fya = ny ? n2.z : n4.x, fyb = ny ? n2.w : n4.y;
+    const uint32_t nza = nz ? n4.z : n3.x, nzb = nz ? n4.w : n3.y, fza = nz ? n3.x : n4.z, fzb = nz ? n3.y : n4.w;
+    uint32_t best = kTravDone; float best_t = inf_f();
 #pragma unroll
-            for (int c = 0; c < 8; ++c) {
-                const uint32_t meta = ((c < 4 ? n1.z : n1.w) >> (8 * (c & 3))) & 0xffu;
-                const uint32_t sel = 0x7440u | (uint32_t) (c & 3);
-                const float t0x = fmaf(qbias(c < 4 ? nxa : nxb, sel), sx, bx), t1x = fmaf(qbias(c < 4 ? fxa : fxb, sel), sx, bx);
-                const float t0y = fmaf(qbias(c < 4 ? nya : nyb, sel), sy, by), t1y = fmaf(qbias(c < 4 ? fya : fyb, sel), sy, by);
-                const float t0z = fmaf(qbias(c < 4 ? nza : nzb, sel), sz, bz), t1z = fmaf(qbias(c < 4 ? fza : fzb, sel), sz, bz);
-                const float tn = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, 0.f));
-                const float tf = fminf(fminf(t1x, t1y), fminf(t1z, tmax));
-                if (meta != 0 && tn <= tf) {
-                    const uint32_t ref = (meta & 0x80u) ? (n1.x + (meta & 0x7fu))
-                                                        : (0x80000000u | ((meta >> 5) << 28) | (n1.y + (meta & 0x1fu)));
-                    const bool closer = tn < best_t;
-                    const uint32_t push_ref = closer ? best : ref; const float push_t = closer ? best_t : tn;
-                    if (closer) { best = ref; best_t = tn; }
-                    if (push_ref != kDone && sp < kStack) { st_ref[sp] = push_ref; st_t[sp] = push_t; sp++; }
-                }
-            }
-            cur = best;
-            if (cur == kDone) {   // nothing hit: pop the next entry that can still matter
-                while (sp > 0) { --sp; if (st_t[sp] <= tmax) { cur = st_ref[sp]; break; } }
-                if (cur == kDone) break;
-            }
-        }
-        if (cur == kDone) break;
-        // ---- leaf: up to 3 triangles
-        {
-            const uint32_t first = cur & 0x0fffffffu, count = (cur >> 28) & 3u;
-            work += count << 16;
-            for (uint32_t k = 0; k < count; ++k) {
-                const float4 *tp = bvh.tris + 3 * (size_t) (first + k);
-                const float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);
-                const float3 p0 = make_float3(a.x, a.y, a.z), p1 = make_float3(a.w, b.x, b.y), p2 = make_float3(b.z, b.w, c.x);
-                // mesh.h:432-452
-                const float3 e1 = p1 - p0, e2 = p2 - p0;
-                const float3 pvec = cross(d, e2);
-                const float inv_det = 1.f / dot(e1, pvec);
-                const float3 tvec = o - p0;
-                const float u = dot(tvec, pvec) * inv_det;
-                const float3 qvec = cross(tvec, e1);
-                const float v = dot(d, qvec) * inv_det;
-                const float t = dot(e2, qvec) * inv_det;
-                const bool ok = u >= 0.f && u <= 1.f && v >= 0.f && u + v <= 1.f && t >= 0.f && t <= tmax;
-                if (ok && (t < hit.t || (t == hit.t && (int) (first + k) < hit.tri))) {
-                    hit.t = t; hit.u = u; hit.v = v; hit.tri = (int) (first + k); tmax = t;
-                }
-            }
-            if (any_hit && hit.tri >= 0) return hit;
-            cur = kDone;
-            while (sp > 0) { --sp; if (st_t[sp] <= tmax) { cur = st_ref[sp]; break; } }
+    for (int c = 0; c < 8; ++c) {
+        const uint32_t meta = ((c < 4 ? n1.z : n1.w) >> (8 * (c & 3))) & 0xffu;
+        const uint32_t sel = 0x7440u | (uint32_t) (c & 3);
+        const float t0x = fmaf(qbias(c < 4 ? nxa : nxb, sel), sx, bx), t1x = fmaf(qbias(c < 4 ? fxa : fxb, sel), sx, bx);
+        const float t0y = fmaf(qbias(c < 4 ? nya : nyb, sel), sy, by), t1y = fmaf(qbias(c < 4 ? fya : fyb, sel), sy, by);
+        const float t0z = fmaf(qbias(c < 4 ? nza : nzb, sel), sz, bz), t1z = fmaf(qbias(c < 4 ? fza : fzb, sel), sz, bz);
+        const float tn = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, 0.f));
+        const float tf = fminf(fminf(t1x, t1y), fminf(t1z, tmax));
+        // branch-free child bookkeeping (selects + one predicated stack store): the lanes of a warp hit different children
+        const bool hitc = meta != 0 && tn <= tf;
+        const uint32_t ref = (meta & 0x80u) ? (n1.x + (meta & 0x7fu)) : (0x80000000u | ((meta >> 5) << 28) | (n1.y + (meta & 0x1fu)));
+        const bool closer = hitc && tn < best_t;
+        const uint32_t push_ref = closer ? best : (hitc ? ref : kTravDone);
+        const float push_t = closer ? best_t : tn;
+        best = closer ? ref : best; best_t = closer ? tn : best_t;
+        if (push_ref != kTravDone && sp < kTravStack) { st_ref[sp] = push_ref; st_t[sp] = push_t; sp++; }
+    }
+    uint32_t cur = best;
+    if (cur == kTravDone)   // nothing hit: pop the next entry that can still matter
+        while (sp > 0) { --sp; if (st_t[sp] <= tmax) { cur = st_ref[sp]; break; } }
+    T.cur = cur; T.sp = sp;
+}
+
+// One leaf (up to 3 triangles, Moeller-Trumbore as mesh.h:432-452), then pop. Requires T.cur to be a leaf.
+LRT_D void trav_leaf_step(const BvhView &bvh, float3 o, float3 d, Trav &T, uint32_t *st_ref, float *st_t, bool any_hit, unsigned &work) {
+    const uint32_t first = T.cur & 0x0fffffffu, count = (T.cur >> 28) & 3u;
+    int sp = T.sp; float tmax = T.tmax;
+    work += count << 16;
+    for (uint32_t k = 0; k < count; ++k) {
+        const float4 *tp = bvh.tris + 3 * (size_t) (first + k);
+        const float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);
+        const float3 p0 = make_float3(a.x, a.y, a.z), p1 = make_float3(a.w, b.x, b.y), p2 = make_float3(b.z, b.w, c.x);
+        const float3 e1 = p1 - p0, e2 = p2 - p0;
+        const float3 pvec = cross(d, e2);
+        const float inv_det = 1.f / dot(e1, pvec);
+        const float3 tvec = o - p0;
+        const float u = dot(tvec, pvec) * inv_det;
+        const float3 qvec = cross(tvec, e1);
+        const float v = dot(d, qvec) * inv_det;
+        const float t = dot(e2, qvec) * inv_det;
+        const bool ok = u >= 0.f && u <= 1.f && v >= 0.f && u + v <= 1.f && t >= 0.f && t <= tmax;
+        if (ok && (t < T.hit.t || (t == T.hit.t && (int) (first + k) < T.hit.tri))) {
+            T.hit.t = t; T.hit.u = u; T.hit.v = v; T.hit.tri = (int) (first + k); tmax = t;
         }
     }
-    return hit;
+    uint32_t cur = kTravDone;
+    if (!(any_hit && T.hit.tri >= 0))
+        while (sp > 0) { --sp; if (st_t[sp] <= tmax) { cur = st_ref[sp]; break; } }
+    T.cur = cur; T.sp = sp; T.tmax = tmax;
+}
+
+// A burst of traversal for a whole warp (all 32 lanes must call it). Every iteration is warp-uniform: EITHER all lanes
+// standing on an inner node process that one node, OR (once `leaf_min` lanes wait on a leaf, or no lane has a node left)
+// all lanes standing on a leaf test its triangles — node code and triangle code never run interleaved at low width.
+// The burst ends when the number of traversing lanes has dropped by `exit_drop` 32nds of what it was at entry (at
+// least by one): finished lanes go and shade / fetch new rays instead of idling until the slowest ray is done.
+LRT_D void bvh_burst(const BvhView &bvh, float3 o, float3 d, Trav &T, uint32_t *st_ref, float *st_t, bool live, bool any_hit,
+                     int exit_drop, int leaf_min, unsigned &work) {
+    const float3 idir = trav_idir(d);
+    const int a0 = __popc(__ballot_sync(0xffffffffu, live && T.cur != kTravDone));
+    if (a0 == 0) return;
+    const int floor_active = a0 - max(1, (a0 * exit_drop) >> 5);
+    while (true) {
+        const bool act = live && T.cur != kTravDone;
+        const bool at_leaf = act && (T.cur & 0x80000000u) != 0u;
+        const unsigned lm = __ballot_sync(0xffffffffu, at_leaf), nm = __ballot_sync(0xffffffffu, act && !at_leaf);
+        if (__popc(lm | nm) <= floor_active) break;
+        if (nm == 0u || __popc(lm) >= leaf_min) {
+            if (at_leaf) trav_leaf_step(bvh, o, d, T, st_ref, st_t, any_hit, work);
+        } else {
+            if (act && !at_leaf) trav_node_step(bvh, o, idir, T, st_ref, st_t, work);
+        }
+    }
+}
+
+// One ray, run to completion (unit-level Scene::ray_intersect / ray_test).
+LRT_D RayHit bvh_intersect(const BvhView &bvh, float3 o, float3 d, float tmax, bool any_hit, unsigned &work) {
+    uint32_t st_ref[kTravStack]; float st_t[kTravStack];
+    Trav T; trav_init(T, tmax);
+    const float3 idir = trav_idir(d);
+    while (T.cur != kTravDone) {
+        if (T.cur & 0x80000000u) trav_leaf_step(bvh, o, d, T, st_ref, st_t, any_hit, work);
+        else trav_node_step(bvh, o, idir, T, st_ref, st_t, work);
+    }
+    return T.hit;
 }
 
 }  // namespace lrt
