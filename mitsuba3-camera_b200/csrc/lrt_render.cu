@@ -4,8 +4,8 @@
 // (src/render/imageblock.cpp:135-172,174-532) for hdrfilm's R,G,B,W storage (src/films/hdrfilm.cpp:245-297).
 //
 // Execution model (not the reference's wavefront): persistent CTAs pull work items (pixel tile x sample chunk) from
-// a global counter. A CTA is 4 warps = a tile of 32x4 pixels; each WARP owns one pixel row of the tile and the pool of
-// its 32 x chunk_spp samples. Sample `j` of pixel `p` always uses PCG32 stream idx = p*spp + j (sampler.cpp:121-130)
+// a global counter. The unit of work is a WARP: a tile is one row of 32 pixels, the warp owns the pool of its
+// 32 x chunk_spp samples and a private shared-memory film tile; the warps of a CTA share only the staged lens table. Sample `j` of pixel `p` always uses PCG32 stream idx = p*spp + j (sampler.cpp:121-130)
 // whatever the sharding, so images are identical up to float summation order for any tile / chunk / GPU split.
 // The three stages have very different shapes, so each runs at its own width and they meet in shared-memory queues:
 //   * camera rays are generated 32 at a time with all lanes active (the lens trace is the same instruction sequence for
@@ -14,8 +14,8 @@
 //   * BVH traversal is resumable (lrt_trace.cuh): path segments and shadow rays of different lanes share ONE traversal
 //     site, and a burst ends as soon as a quarter of its lanes have finished, so they can shade and fetch new rays;
 //   * finished samples go to a per-warp splat queue that is drained 32 entries at a time into the shared-memory film
-//     tile (float atomics in shared memory are CAS loops on this architecture: run them at full width), and the tile
-//     is flushed once per work item with global float atomics.
+//     tile (float atomics in shared memory are CAS loops on this architecture: run them at full width, two channels
+//     per 64-bit CAS), and the tile is flushed once per work item with global float atomics.
 #include "lrt_internal.h"
 #include "lrt_rng.cuh"
 #include "lrt_shade.cuh"
@@ -23,7 +23,7 @@
 
 namespace lrt {
 
-constexpr int kTileW = 32, kTileH = 4, kCtaThreads = kTileW * kTileH, kWarps = kCtaThreads / 32;
+constexpr int kTileW = 32, kTileH = 1, kCtaThreads = 128, kWarps = kCtaThreads / 32;
 constexpr int kFifo = 64, kFifoWords = 14;      // camera-ray FIFO per warp: o[3] d[3] maxt weight sx sy rng.state rng.inc
 constexpr int kQueue = 64, kQueueWords = 5;     // splat queue per warp: sx sy r g b
 
@@ -40,6 +40,17 @@ struct RenderArgs {
     unsigned long long *stats;     // [0] samples, [1] lens misses, [2] rays, [3] bounces, [4] BVH nodes fetched, [5] triangles tested
 };
 
+// Shared-memory float atomics are CAS loops on sm_100 (ATOMS.CAST.SPIN): add two neighbouring channels with ONE 64-bit CAS.
+LRT_D void atomic_add2_shared(float *p, float a, float b) {
+    unsigned long long *q = reinterpret_cast<unsigned long long *>(p);
+    unsigned long long old = *q, assumed;
+    do {
+        assumed = old;
+        const float x = __uint_as_float((unsigned) assumed) + a, y = __uint_as_float((unsigned) (assumed >> 32)) + b;
+        old = atomicCAS(q, assumed, (unsigned long long) __float_as_uint(x) | ((unsigned long long) __float_as_uint(y) << 32));
+    } while (old != assumed);
+}
+
 // ImageBlock::put of one sample into the shared-memory tile (tensor coordinates of tile(0,0) = (ox, oy))
 LRT_D void splat_to_tile(const FilmParams &F, float *tile, int smem_w, int ox, int oy, float sx, float sy, float3 value) {
     Footprint fp;
@@ -54,24 +65,25 @@ LRT_D void splat_to_tile(const FilmParams &F, float *tile, int smem_w, int ox, i
             if ((unsigned) x >= (unsigned) sw) continue;
             const float w = fp.wy[iy] * fp.wx[ix];
             float *dst = tile + ((y - oy) * smem_w + (x - ox)) * 4;
-            if (value.x != 0.f) atomicAdd(dst, value.x * w);
-            if (value.y != 0.f) atomicAdd(dst + 1, value.y * w);
-            if (value.z != 0.f) atomicAdd(dst + 2, value.z * w);
-            atomicAdd(dst + 3, w);
+            if (value.x != 0.f || value.y != 0.f) atomic_add2_shared(dst, value.x * w, value.y * w);
+            atomic_add2_shared(dst + 2, value.z * w, w);
         }
     }
 }
 
-__global__ void __launch_bounds__(kCtaThreads) k_render(RenderArgs A) {
+#ifndef LRT_RENDER_MIN_BLOCKS
+#define LRT_RENDER_MIN_BLOCKS 4
+#endif
+__global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(RenderArgs A) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     LensSystem &L = *reinterpret_cast<LensSystem *>(smem_raw);
-    float *tile = reinterpret_cast<float *>(smem_raw + sizeof(LensSystem));
-    __shared__ long long s_item;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const unsigned lt_mask = (1u << lane) - 1u;
     const int tile_elems = A.smem_w * A.smem_h * 4;
-    float *fifo = tile + tile_elems + warp * (kFifo * kFifoWords + kQueue * kQueueWords);   // [word][slot]
-    float *queue = fifo + kFifo * kFifoWords;                                                // [word][slot]
+    // per-warp private storage: film tile, camera-ray FIFO [word][slot], splat queue [word][slot]
+    float *tile = reinterpret_cast<float *>(smem_raw + sizeof(LensSystem)) + warp * (tile_elems + kFifo * kFifoWords + kQueue * kQueueWords);
+    float *fifo = tile + tile_elems;
+    float *queue = fifo + kFifo * kFifoWords;
     {
         const uint4 *src = reinterpret_cast<const uint4 *>(A.lens);
         uint4 *dst = reinterpret_cast<uint4 *>(&L);
@@ -83,18 +95,19 @@ __global__ void __launch_bounds__(kCtaThreads) k_render(RenderArgs A) {
     const float offs_x = -(float) F.off_x * scale_x, offs_y = -(float) F.off_y * scale_y;
     unsigned long long n_samples = 0, n_miss = 0, n_rays = 0, n_bounces = 0, n_nodes = 0, n_tris = 0;
     uint32_t st_ref[kTravStack]; float st_t[kTravStack];
+    __syncthreads();   // lens table staged; from here on the warps of a CTA never wait for each other
 
     while (true) {
-        __syncthreads();
-        if (tid == 0) s_item = (long long) atomicAdd(A.counter, 1ULL);
-        for (int i = tid; i < tile_elems; i += kCtaThreads) tile[i] = 0.f;
-        __syncthreads();
-        const long long item = s_item;
+        long long item = 0;
+        if (lane == 0) item = (long long) atomicAdd(A.counter, 1ULL);
+        item = __shfl_sync(0xffffffffu, item, 0);
         if (item >= A.n_items) break;
+        for (int i = lane; i < tile_elems; i += 32) tile[i] = 0.f;
+        __syncwarp();
         const int chunk = (int) (item % A.n_chunks);
         const long long tile_id = (long long) A.shard_index + (item / A.n_chunks) * A.shard_count;
         const int tx = (int) (tile_id % A.tiles_x), ty = (int) (tile_id / A.tiles_x);
-        const int px = tx * kTileW + lane, py = ty * kTileH + warp;      // the pixel this lane GENERATES samples for
+        const int px = tx * kTileW + lane, py = ty;                      // the pixel this lane GENERATES samples for
         const bool in_film = px < F.size_x && py < F.size_y;
         const int ox = tx * kTileW - A.pad, oy = ty * kTileH - A.pad;    // tensor coords of smem (0,0)
         const int j0 = chunk * A.chunk_spp;
@@ -275,9 +288,8 @@ __global__ void __launch_bounds__(kCtaThreads) k_render(RenderArgs A) {
         // ---- drain what is left, then put_block(): flush the tile into the film accumulator
         if (q_count > 32) drain(32);
         if (q_count > 0) drain(q_count);
-        __syncthreads();
         const int sw = F.size_x + 2 * F.border, shh = F.size_y + 2 * F.border;
-        for (int i = tid; i < A.smem_w * A.smem_h; i += kCtaThreads) {
+        for (int i = lane; i < A.smem_w * A.smem_h; i += 32) {
             int ly = i / A.smem_w, lx = i - ly * A.smem_w;
             int x = ox + lx, y = oy + ly;
             if ((unsigned) x >= (unsigned) sw || (unsigned) y >= (unsigned) shh) continue;
@@ -289,6 +301,7 @@ __global__ void __launch_bounds__(kCtaThreads) k_render(RenderArgs A) {
             if (v.z != 0.f) atomicAdd(dst + 2, v.z);
             if (v.w != 0.f) atomicAdd(dst + 3, v.w);
         }
+        __syncwarp();
     }
     if (A.stats) {
         for (int o = 16; o > 0; o >>= 1) {
@@ -342,7 +355,7 @@ int launch_render(const lrt_scene *sc, lrt_sensor *sensor, const lrt_film_desc *
     long long n_tiles = (long long) A.tiles_x * tiles_y;
     long long my_tiles = (n_tiles - rp->shard_index + rp->shard_count - 1) / rp->shard_count;
     int dev = 0, sms = 148; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    size_t smem = sizeof(LensSystem) + (size_t) A.smem_w * A.smem_h * 16 + (size_t) kWarps * (kFifo * kFifoWords + kQueue * kQueueWords) * 4;
+    size_t smem = sizeof(LensSystem) + (size_t) kWarps * ((size_t) A.smem_w * A.smem_h * 4 + kFifo * kFifoWords + kQueue * kQueueWords) * 4;
     {   // traversal bursts end when this many 32nds of their lanes have finished (LRT_EXIT_DROP overrides; tuning knob)
         const char *e = getenv("LRT_EXIT_DROP"); A.exit_drop = e ? atoi(e) : 24;
         if (A.exit_drop < 1) A.exit_drop = 1; if (A.exit_drop > 32) A.exit_drop = 32;
@@ -354,15 +367,15 @@ int launch_render(const lrt_scene *sc, lrt_sensor *sensor, const lrt_film_desc *
     int per_sm = 1; cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_render, kCtaThreads, smem);
     if (per_sm < 1) per_sm = 1;
     long long resident = (long long) sms * per_sm;
-    // split the samples of a pixel into chunks until there are ~4 work items per resident CTA
+    // split the samples of a pixel into chunks until there are ~4 work items per resident warp
     int n_chunks = 1;
-    while (my_tiles * n_chunks < 4 * resident && n_chunks * 2 <= rp->spp) n_chunks *= 2;
+    while (my_tiles * n_chunks < 4 * resident * kWarps && n_chunks * 2 <= rp->spp) n_chunks *= 2;
     if (rp->chunks > 0) n_chunks = std::min(rp->chunks, rp->spp);
     A.n_chunks = n_chunks; A.chunk_spp = (rp->spp + n_chunks - 1) / n_chunks;
     A.shard_index = rp->shard_index; A.shard_count = rp->shard_count; A.n_items = my_tiles * n_chunks;
     A.counter = sc->d_counter; A.stats = sc->d_counter + 1; A.accum = accum_dev;
     LRT_CUDA(cudaMemsetAsync(sc->d_counter, 0, 8 * sizeof(unsigned long long), stream));
-    long long grid = std::min(resident, A.n_items);
+    long long grid = std::min(resident, (A.n_items + kWarps - 1) / kWarps);
     if (grid < 1) return LRT_OK;
     k_render<<<(int) grid, kCtaThreads, smem, stream>>>(A);
     LRT_LAUNCHED();

@@ -1,14 +1,14 @@
 """Multi-GPU plumbing: one process per GPU (torch.distributed; NCCL on GPUs, gloo in the CPU tests).
 
 The reference has no multi-device code. The path shards without any data-path exchange: every path is
-a function of (seed, sample index) only. Render: pixel tiles of 32x4 are dealt round-robin over ranks (the kernel does the
+a function of (seed, sample index) only. Render: pixel tiles of 32x1 are dealt round-robin over ranks (the kernel does the
 dealing from shard_index / shard_count, lrt_render.cu); spot path: sample idx = rank + k * world. The one collective per
 step is a sum of the film accumulator (and of the lens-table gradient)."""
 from __future__ import annotations
 
 import os
 
-TILE_W, TILE_H = 32, 4      # lrt_render.cu kTileW / kTileH
+TILE_W, TILE_H = 32, 1      # lrt_render.cu kTileW / kTileH
 
 
 def shard_from_env():
@@ -33,7 +33,7 @@ def init(backend=None):
 
 
 def tiles_of_shard(width, height, rank, world):
-    """Tile ids (row-major over ceil(W/32) x ceil(H/4)) rendered by `rank`: tile_id = rank + k * world — the same formula as
+    """Tile ids (row-major over ceil(W/32) x ceil(H/1)) rendered by `rank`: tile_id = rank + k * world — the same formula as
     the kernel (lrt_render.cu: tile_id = shard_index + (item / n_chunks) * shard_count)."""
     tx, ty = (width + TILE_W - 1) // TILE_W, (height + TILE_H - 1) // TILE_H
     return list(range(rank, tx * ty, world)), tx

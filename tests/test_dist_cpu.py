@@ -22,7 +22,7 @@ def _worker(rank, world, port, q):
     from mitsuba3_camera_b200 import parallel as par
     r, w = par.init("gloo")
     assert (r, w) == (rank, world)
-    W, H = 100, 37                                   # ragged: not a multiple of the 32x4 tile
+    W, H = 100, 37                                   # ragged: not a multiple of the 32-pixel tile
     film = torch.zeros((H, W, 4))
     film[torch.from_numpy(par.pixel_owner_mask(W, H, r, w))] = 1.0      # stand-in for this rank's accumulator
     par.all_reduce_sum(film)
