@@ -149,6 +149,9 @@ typedef struct lrt_scene_desc {
 /* Scene::Scene (src/render/scene.cpp:22-96): builds the acceleration structure (8-wide quantised BVH, on the
  * host) and uploads everything to the current device. */
 int lrt_scene_create(const lrt_scene_desc *desc, lrt_scene **out);
+/* SceneParameters.update() (src/python/python/util.py:292-353) for the differentiable parameters: replace the BSDF rows
+ * ([n_bsdfs,16], NULL = keep) and / or the emitters' radiance ([n_emitters,3], NULL = keep). Geometry is untouched. */
+int lrt_scene_set_params(lrt_scene *s, const float *bsdfs, const float *emitter_radiance3);
 void lrt_scene_destroy(lrt_scene *s);
 int lrt_scene_info(const lrt_scene *s, int64_t *n_nodes, int64_t *n_tris, int32_t *bvh_depth, double *build_seconds);
 /* Scene::ray_intersect_preliminary / ray_test (src/render/scene.cpp:181-210) for n rays:
@@ -171,6 +174,16 @@ typedef struct lrt_render_params {
  * hdrfilm). Asynchronous on `stream`. */
 int lrt_render(const lrt_scene *scene, const lrt_sensor *sensor, const lrt_film_desc *film,
                const lrt_render_params *params, float *accum_dev, void *stream);
+/* Adjoint of lrt_render for the scene parameters the path is linear in — the part of PRBIntegrator.render_backward
+ * (src/python/python/ad/integrators/prb.py:59-257, common.py:631-796) that reaches diffuse `reflectance`, conductor
+ * `specular_reflectance` and area-light `radiance`. grad_storage_dev = d(loss)/d(accum) [size_y+2b, size_x+2b, 4] (the RGB
+ * channels are used; W does not depend on parameters). ADDS to grad_bsdfs_dev [n_bsdfs,16] (columns 2..4) and
+ * grad_emitters_dev [n_emitters,16] (columns 0..2), laid out like the tables of lrt_scene_desc; the caller zeroes them.
+ * Same samples, streams and Russian-roulette decisions as lrt_render with equal params (sampling is detached, as in prb).
+ * One pass: instead of prb's second replay pass, each path keeps (BSDF id, radiance gathered so far) per bounce. */
+int lrt_render_backward(const lrt_scene *scene, const lrt_sensor *sensor, const lrt_film_desc *film,
+                        const lrt_render_params *params, const float *grad_storage_dev, float *grad_bsdfs_dev,
+                        float *grad_emitters_dev, void *stream);
 /* mi.render(scene) for host callers: render + HDRFilm::develop; rgb_out [size_y,size_x,3] host memory. */
 int lrt_render_host(const lrt_scene *scene, const lrt_sensor *sensor, const lrt_film_desc *film,
                     const lrt_render_params *params, float *rgb_out);

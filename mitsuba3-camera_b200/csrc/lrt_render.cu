@@ -26,6 +26,8 @@ namespace lrt {
 constexpr int kTileW = 32, kTileH = 1, kCtaThreads = 128, kWarps = kCtaThreads / 32;
 constexpr int kFifo = 64, kFifoWords = 14;      // camera-ray FIFO per warp: o[3] d[3] maxt weight sx sy rng.state rng.inc
 constexpr int kQueue = 64, kQueueWords = 5;     // splat queue per warp: sx sy r g b
+constexpr int kMaxRec = 12;                     // adjoint: bounces of one path that can receive a BSDF gradient
+constexpr int kGradSlots = 1024;                // adjoint: per-CTA shared accumulators (3 per BSDF, 3 per emitter)
 
 struct RenderArgs {
     SceneView sc;
@@ -37,6 +39,8 @@ struct RenderArgs {
     int pad, smem_w, smem_h, exit_drop, leaf_min;
     unsigned long long *counter;
     float *accum;
+    // adjoint (k_render<true>): d(loss)/d(storage) in, parameter gradients out (rows laid out like the scene tables)
+    const float *grad_storage; float *grad_bsdfs, *grad_emitters; int n_bsdfs;
     unsigned long long *stats;     // [0] samples, [1] lens misses, [2] rays, [3] bounces, [4] BVH nodes fetched, [5] triangles tested
 };
 
@@ -74,6 +78,7 @@ LRT_D void splat_to_tile(const FilmParams &F, float *tile, int smem_w, int ox, i
 #ifndef LRT_RENDER_MIN_BLOCKS
 #define LRT_RENDER_MIN_BLOCKS 4
 #endif
+template <bool kAdj>
 __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(RenderArgs A) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     LensSystem &L = *reinterpret_cast<LensSystem *>(smem_raw);
@@ -95,6 +100,15 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
     const float offs_x = -(float) F.off_x * scale_x, offs_y = -(float) F.off_y * scale_y;
     unsigned long long n_samples = 0, n_miss = 0, n_rays = 0, n_bounces = 0, n_nodes = 0, n_tris = 0;
     uint32_t st_ref[kTravStack]; float st_t[kTravStack];
+    // adjoint state: gradient slots shared by the CTA, per-path records (BSDF id, radiance gathered before the bounce)
+    __shared__ float s_grad[kAdj ? kGradSlots : 1];
+    const bool grad_in_smem = kAdj && (A.n_bsdfs + A.sc.n_emitters) * 3 <= kGradSlots;
+    if (kAdj) for (int i = tid; i < kGradSlots; i += kCtaThreads) s_grad[i] = 0.f;
+    float rec[kAdj ? kMaxRec : 1][4]; int nrec = 0; float3 dL = make_float3(0, 0, 0);
+    auto add_grad = [&](int slot, float *gptr, float v) {   // slot: index into s_grad, gptr: the global entry
+        if (v == 0.f) return;
+        if (grad_in_smem) atomicAdd(&s_grad[slot], v); else atomicAdd(gptr, v);
+    };
     __syncthreads();   // lens table staged; from here on the warps of a CTA never wait for each other
 
     while (true) {
@@ -168,7 +182,7 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
                     if (!(cr.weight > 0.f)) n_miss++;
                 }
                 // vignetted (or max_depth == 0): RGB 0, weight 1 (integrator.cpp:461-490)
-                push_splat(in_film && !hit, gx, gy, make_float3(0, 0, 0));
+                if (!kAdj) push_splat(in_film && !hit, gx, gy, make_float3(0, 0, 0));
                 const unsigned hm = __ballot_sync(0xffffffffu, hit);
                 if (hit) {
                     const int s = (fifo_head + fifo_count + __popc(hm & lt_mask)) & (kFifo - 1);
@@ -197,6 +211,25 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
                     phase = 1;
                     throughput = make_float3(1, 1, 1); result = make_float3(0, 0, 0); eta = 1.f; depth = 0;
                     prev_p = make_float3(0, 0, 0); prev_pdf = 1.f; prev_delta = true; valid_ray = false;
+                    if (kAdj) {   // transpose of the splat: dL = sum over the footprint of w * d(loss)/d(storage RGB)
+                        nrec = 0; dL = make_float3(0, 0, 0);
+                        Footprint fp;
+                        if (film_footprint(F, sx, sy, fp)) {
+                            const int sw = box ? F.size_x : F.size_x + 2 * F.border, shh = F.size_y + 2 * F.border;
+                            for (int iy = 0; iy < fp.ny; ++iy) {
+                                const int y = fp.y0 + iy;
+                                if ((unsigned) y >= (unsigned) shh) continue;
+                                for (int ix = 0; ix < fp.nx; ++ix) {
+                                    const int x = fp.x0 + ix;
+                                    if ((unsigned) x >= (unsigned) sw) continue;
+                                    const float4 G = __ldg(reinterpret_cast<const float4 *>(A.grad_storage) + (size_t) y * sw + x);
+                                    const float w = fp.wy[iy] * fp.wx[ix];
+                                    dL += make_float3(G.x, G.y, G.z) * w;
+                                }
+                            }
+                        }
+                        dL *= cam_weight;
+                    }
                 }
                 fifo_head = (fifo_head + take) & (kFifo - 1); fifo_count -= take;
                 __syncwarp();
@@ -231,7 +264,13 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
                             float em_pdf = prev_delta ? 0.f : pdf_emitter_direction(A.sc, em, dd, dist, si.n);
                             if (si.wi.z > 0.f && prev_pdf > 0.f) {
                                 float4 e0 = __ldg(A.sc.emitters + 5 * (size_t) em);
-                                result += throughput * make_float3(e0.x, e0.y, e0.z) * mis_weight(prev_pdf, em_pdf);
+                                const float mw = mis_weight(prev_pdf, em_pdf);
+                                result += throughput * make_float3(e0.x, e0.y, e0.z) * mw;
+                                if (kAdj) {   // radiance enters linearly
+                                    const float3 g = dL * throughput * mw;
+                                    float *gp = A.grad_emitters + 16 * (size_t) em; const int sl = (A.n_bsdfs + em) * 3;
+                                    add_grad(sl, gp, g.x); add_grad(sl + 1, gp + 1, g.y); add_grad(sl + 2, gp + 2, g.z);
+                                }
                             }
                         }
                         if (depth + 1 < A.max_depth) {
@@ -267,7 +306,24 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
                     const bool active_em = phase == 2 && !occluded;
                     if (active_em) { es = sample_emitter_direction(A.sc, si.p, e_sx, e_sy); wo = si.to_local(es.d); }
                     BsdfResult bs = bsdf_eval_pdf_sample(A.sc, bsdf_id, si.wi, wo, s1, s2x, s2y);
-                    if (active_em) result += throughput * (bs.val * es.weight * mis_weight(es.pdf, bs.pdf));
+                    if (kAdj) {   // everything gathered from here on is linear in this surface's (specular) reflectance
+                        const int btype = (int) __ldg(reinterpret_cast<const float *>(A.sc.bsdfs) + 16 * (size_t) bsdf_id);
+                        if (nrec < kMaxRec && btype != BSDF_DIELECTRIC) {
+                            rec[nrec][0] = __int_as_float(bsdf_id); rec[nrec][1] = result.x; rec[nrec][2] = result.y; rec[nrec][3] = result.z; nrec++;
+                        }
+                    }
+                    if (active_em) {
+                        const float3 c3 = throughput * (bs.val * es.weight * mis_weight(es.pdf, bs.pdf));
+                        result += c3;
+                        if (kAdj) {
+                            const int cnt = A.sc.n_emitters, ei = cnt > 1 ? min((int) (e_sx * (float) cnt), cnt - 1) : 0;
+                            const float4 e0 = __ldg(A.sc.emitters + 5 * (size_t) ei);
+                            float *gp = A.grad_emitters + 16 * (size_t) ei; const int sl = (A.n_bsdfs + ei) * 3;
+                            if (e0.x != 0.f) add_grad(sl, gp, dL.x * c3.x / e0.x);
+                            if (e0.y != 0.f) add_grad(sl + 1, gp + 1, dL.y * c3.y / e0.y);
+                            if (e0.z != 0.f) add_grad(sl + 2, gp + 2, dL.z * c3.z / e0.z);
+                        }
+                    }
                     float3 wo_w = si.to_world(bs.wo);
                     ro = offset_p(si.p, si.n, wo_w); rd = wo_w; trav_init(T, kLargest);
                     throughput *= bs.weight; eta *= bs.seta;
@@ -283,9 +339,22 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
                     if (!alive) { done_path = true; value = result * cam_weight; T.cur = kTravDone; }
                 }
             }
-            push_splat(done_path, sx, sy, value);
+            if (!kAdj) push_splat(done_path, sx, sy, value);
+            else if (done_path) {   // suffix of the path behind every recorded bounce, divided by that bounce's reflectance
+                for (int k = 0; k < nrec; ++k) {
+                    const int b = __float_as_int(rec[k][0]);
+                    const float *row = reinterpret_cast<const float *>(A.sc.bsdfs) + 16 * (size_t) b;
+                    float *gp = A.grad_bsdfs + 16 * (size_t) b + 2; const int sl = b * 3;
+                    const float r0 = __ldg(row + 2), r1 = __ldg(row + 3), r2 = __ldg(row + 4);
+                    if (r0 != 0.f) add_grad(sl, gp, dL.x * (result.x - rec[k][1]) / r0);
+                    if (r1 != 0.f) add_grad(sl + 1, gp + 1, dL.y * (result.y - rec[k][2]) / r1);
+                    if (r2 != 0.f) add_grad(sl + 2, gp + 2, dL.z * (result.z - rec[k][3]) / r2);
+                }
+                nrec = 0;
+            }
         }
         // ---- drain what is left, then put_block(): flush the tile into the film accumulator
+        if (kAdj) { __syncwarp(); continue; }
         if (q_count > 32) drain(32);
         if (q_count > 0) drain(q_count);
         const int sw = F.size_x + 2 * F.border, shh = F.size_y + 2 * F.border;
@@ -302,6 +371,15 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
             if (v.w != 0.f) atomicAdd(dst + 3, v.w);
         }
         __syncwarp();
+    }
+    if (kAdj && grad_in_smem) {
+        __syncthreads();
+        for (int i = tid; i < (A.n_bsdfs + A.sc.n_emitters) * 3; i += kCtaThreads) {
+            const float v = s_grad[i];
+            if (v == 0.f) continue;
+            const int e = i / 3, c = i - 3 * e;
+            atomicAdd(e < A.n_bsdfs ? A.grad_bsdfs + 16 * (size_t) e + 2 + c : A.grad_emitters + 16 * (size_t) (e - A.n_bsdfs) + c, v);
+        }
     }
     if (A.stats) {
         for (int o = 16; o > 0; o >>= 1) {
@@ -335,7 +413,7 @@ __global__ void __launch_bounds__(128) k_intersect(SceneView sc, int any_hit, in
 namespace lrt {
 
 int launch_render(const lrt_scene *sc, lrt_sensor *sensor, const lrt_film_desc *film, const lrt_render_params *rp,
-                  float *accum_dev, cudaStream_t stream) {
+                  float *accum_dev, const float *grad_storage, float *grad_bsdfs, float *grad_emitters, cudaStream_t stream) {
     RenderArgs A; memset(&A, 0, sizeof A);
     int rc = film_params_from_desc(film, A.film); if (rc) return rc;
     LRT_REQUIRE(film->channels == 4, "render needs the R,G,B,W film of hdrfilm (channels = 4)");
@@ -363,8 +441,16 @@ int launch_render(const lrt_scene *sc, lrt_sensor *sensor, const lrt_film_desc *
         if (A.leaf_min < 1) A.leaf_min = 1;
     }
     static bool attr_set = false;
-    if (!attr_set) { cudaFuncSetAttribute(k_render, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024); attr_set = true; }
-    int per_sm = 1; cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_render, kCtaThreads, smem);
+    if (!attr_set) {
+        cudaFuncSetAttribute(k_render<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+        cudaFuncSetAttribute(k_render<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+        attr_set = true;
+    }
+    const bool adjoint = grad_storage != nullptr;
+    A.grad_storage = grad_storage; A.grad_bsdfs = grad_bsdfs; A.grad_emitters = grad_emitters; A.n_bsdfs = sc->n_bsdfs;
+    int per_sm = 1;
+    if (adjoint) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_render<true>, kCtaThreads, smem);
+    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_render<false>, kCtaThreads, smem);
     if (per_sm < 1) per_sm = 1;
     long long resident = (long long) sms * per_sm;
     // split the samples of a pixel into chunks until there are ~4 work items per resident warp
@@ -377,7 +463,8 @@ int launch_render(const lrt_scene *sc, lrt_sensor *sensor, const lrt_film_desc *
     LRT_CUDA(cudaMemsetAsync(sc->d_counter, 0, 8 * sizeof(unsigned long long), stream));
     long long grid = std::min(resident, (A.n_items + kWarps - 1) / kWarps);
     if (grid < 1) return LRT_OK;
-    k_render<<<(int) grid, kCtaThreads, smem, stream>>>(A);
+    if (adjoint) k_render<true><<<(int) grid, kCtaThreads, smem, stream>>>(A);
+    else k_render<false><<<(int) grid, kCtaThreads, smem, stream>>>(A);
     LRT_LAUNCHED();
     LRT_CUDA(cudaGetLastError());
     return LRT_OK;

@@ -7,7 +7,7 @@
 namespace lrt {
 struct RenderArgs;
 int launch_render(const lrt_scene *sc, lrt_sensor *sensor, const lrt_film_desc *film, const lrt_render_params *rp,
-                  float *accum_dev, cudaStream_t stream);
+                  float *accum_dev, const float *grad_storage, float *grad_bsdfs, float *grad_emitters, cudaStream_t stream);
 }
 using namespace lrt;
 
@@ -70,6 +70,17 @@ int lrt_scene_create(const lrt_scene_desc *d, lrt_scene **out) {
     return LRT_OK;
 }
 
+// parameters_changed() for the differentiable scene parameters: new BSDF rows (same count) and / or emitter radiances
+int lrt_scene_set_params(lrt_scene *s, const float *bsdfs, const float *emitter_radiance3) {
+    LRT_NEED_DEVICE();
+    LRT_REQUIRE(s, "null scene");
+    if (bsdfs && s->n_bsdfs) LRT_CUDA(cudaMemcpy(s->d_bsdfs, bsdfs, (size_t) s->n_bsdfs * 64, cudaMemcpyHostToDevice));
+    if (emitter_radiance3)
+        for (int i = 0; i < s->n_emitters; ++i)   // radiance is the first 3 floats of the 20-float device record
+            LRT_CUDA(cudaMemcpy((float *) s->d_emitters + 20 * (size_t) i, emitter_radiance3 + 3 * i, 12, cudaMemcpyHostToDevice));
+    return LRT_OK;
+}
+
 void lrt_scene_destroy(lrt_scene *s) {
     if (!s) return;
     void *p[] = { s->d_nodes, s->d_tris, s->d_shape_bsdf, s->d_shape_emitter, s->d_bsdfs, s->d_emitters, s->d_counter };
@@ -90,7 +101,15 @@ int lrt_render(const lrt_scene *sc, const lrt_sensor *sensor, const lrt_film_des
                float *accum_dev, void *stream) {
     LRT_NEED_DEVICE();
     LRT_REQUIRE(sc && sensor && film && rp && accum_dev, "null argument");
-    return launch_render(sc, const_cast<lrt_sensor *>(sensor), film, rp, accum_dev, (cudaStream_t) stream);
+    return launch_render(sc, const_cast<lrt_sensor *>(sensor), film, rp, accum_dev, nullptr, nullptr, nullptr, (cudaStream_t) stream);
+}
+
+int lrt_render_backward(const lrt_scene *sc, const lrt_sensor *sensor, const lrt_film_desc *film, const lrt_render_params *rp,
+                        const float *grad_storage_dev, float *grad_bsdfs_dev, float *grad_emitters_dev, void *stream) {
+    LRT_NEED_DEVICE();
+    LRT_REQUIRE(sc && sensor && film && rp && grad_storage_dev && grad_bsdfs_dev && grad_emitters_dev, "null argument");
+    return launch_render(sc, const_cast<lrt_sensor *>(sensor), film, rp, nullptr, grad_storage_dev, grad_bsdfs_dev, grad_emitters_dev,
+                         (cudaStream_t) stream);
 }
 
 int lrt_render_stats(const lrt_scene *sc, uint64_t *out6) {

@@ -314,6 +314,64 @@ def render(scene: Scene, params=None, sensor=0, integrator=None, seed=0, seed_gr
     return develop_rgb(storage) if develop else storage
 
 
+def render_backward(scene: Scene, grad_storage, sensor=0, integrator=None, seed=0, spp=0, shard=(0, 1)):
+    """Adjoint of render() for diffuse reflectance / conductor specular reflectance / area-light radiance
+    (RBIntegrator.render_backward, src/python/python/ad/integrators/common.py:631-796 with prb.py): grad_storage = d(loss)/
+    d(R,G,B,W storage) [H,W,4] -> (grad_bsdfs [n_bsdfs,16], grad_emitters [n_emitters,16]) torch CUDA tensors."""
+    import torch
+    s = scene.sensors()[sensor] if isinstance(sensor, int) else sensor
+    it = integrator or scene.integrator()
+    spp = int(spp) if spp else s.sampler.sample_count()
+    fd = film_desc(s.film)
+    gb = torch.zeros((max(len(scene.arrays["bsdfs"]), 1), 16), dtype=torch.float32, device="cuda")
+    ge = torch.zeros((max(len(scene.arrays["emitters"]), 1), 16), dtype=torch.float32, device="cuda")
+    rp = RenderParams((s.sampler.base_seed + int(seed)) & 0xffffffff, spp, it.max_depth, it.rr_depth, shard[0], shard[1], 0)
+    capi.check(capi.lib.lrt_render_backward(scene.handle, s.handle, C.byref(fd), C.byref(rp), capi.dev_ptr(grad_storage.contiguous()),
+                                            capi.dev_ptr(gb), capi.dev_ptr(ge), capi.stream_ptr()))
+    return gb[:len(scene.arrays["bsdfs"])], ge[:len(scene.arrays["emitters"])]
+
+
+class SceneParameters(dict):
+    """mi.traverse(scene) for the parameters the adjoint reaches: '<bsdf key>.reflectance.value' (diffuse),
+    '<bsdf key>.specular_reflectance.value' (conductor), '<shape key>.emitter.radiance.value' — torch tensors of 3 floats.
+    update() pushes them to the device tables (src/python/python/util.py:292-353)."""
+
+    def __init__(self, scene):
+        import torch
+        super().__init__()
+        self.scene, self._where = scene, {}
+        a = scene.arrays
+        for i, name in enumerate(scene.data.bsdf_names):
+            t = int(a["bsdfs"][i, 0])
+            if t in (0, 1):
+                key = f"{name}.{'reflectance' if t == 0 else 'specular_reflectance'}.value"
+                self[key] = torch.tensor(a["bsdfs"][i, 2:5].copy()); self._where[key] = ("bsdf", i)
+        for sid, e in enumerate(a["shape_emitter"]):
+            if e >= 0:
+                key = f"{scene.data.shape_names[sid]}.emitter.radiance.value"
+                self[key] = torch.tensor(a["emitters"][e, 0:3].copy()); self._where[key] = ("emitter", int(e))
+
+    def update(self):
+        a = self.scene.arrays
+        for key, (kind, i) in self._where.items():
+            v = self[key].detach().cpu().numpy().astype(f32)
+            if kind == "bsdf":
+                a["bsdfs"][i, 2:5] = v
+            else:
+                a["emitters"][i, 0:3] = v
+        rad = np.ascontiguousarray(a["emitters"][:, 0:3], f32)
+        capi.check(capi.lib.lrt_scene_set_params(self.scene.handle, capi.fp(a["bsdfs"].reshape(-1)) if a["bsdfs"].size else None,
+                                                 capi.fp(rad.reshape(-1)) if rad.size else None))
+
+    def gradients(self, grad_bsdfs, grad_emitters):
+        """Split the adjoint's tables into per-key gradients."""
+        return {k: (grad_bsdfs[i, 2:5] if kind == "bsdf" else grad_emitters[i, 0:3]) for k, (kind, i) in self._where.items()}
+
+
+def traverse(scene):
+    return SceneParameters(scene)
+
+
 # ------------------------------------------------------------------------------------------------ load_dict
 def _film_from(d):
     d = d or {"type": "hdrfilm"}

@@ -199,3 +199,55 @@ def test_gpu_conductor_and_dielectric(mi):
                        to_world=d["sensor"]["to_world"].matrix, near=1e-3, far=100.0)
     err = rel_rmse(img, develop(st))
     assert err < 5 * IMG_TOL, err    # delta lobes amplify rounding differences of the reflected direction
+
+
+@pytest.mark.gpu
+def test_gpu_render_backward_vs_oracle_finite_differences(mi):
+    """lrt_render_backward (reflectance / specular reflectance / radiance gradients) against central finite differences of
+    the ORACLE's render in float64 accumulators. max_depth = 4 < rr_depth keeps Russian roulette out of the way (prb detaches
+    it; a finite difference of the primal would not). Tolerance: cosine >= 0.999, per entry 3 % of the largest."""
+    import torch
+    d = cornell(mi, res=32, spp=16)
+    d["integrator"]["max_depth"] = 4
+    d["small-box"]["bsdf"] = {"type": "conductor", "material": "Cu", "specular_reflectance": {"type": "rgb", "value": [0.9, 0.8, 0.7]}}
+    sc = mi.load_dict(d)
+    tw = d["sensor"]["to_world"].matrix
+    rng = np.random.default_rng(1)
+    G = np.zeros((32, 32, 4), f32); G[..., :3] = rng.standard_normal((32, 32, 3))
+
+    def phi(arrays):
+        st, _ = orc_render(orc_scene(arrays), FilmSpec(32, 32), 16, seed=5, max_depth=4, fov=39.3077, to_world=tw, near=1e-3, far=100.0)
+        return float((st * G).sum())
+
+    gb, ge = mi.render_backward(sc, torch.from_numpy(G).cuda(), seed=5, spp=16)
+    gb, ge = gb.cpu().numpy(), ge.cpu().numpy()
+    got, want = [], []
+    base = {k: v.copy() for k, v in sc.arrays.items()}
+    for b in range(len(base["bsdfs"])):
+        if not np.any(base["tri_shape"][:, None] == np.nonzero(base["shape_bsdf"] == b)[0][None, :]):
+            continue
+        for c in range(3):
+            h = 0.02
+            ap = {k: v.copy() for k, v in base.items()}; am = {k: v.copy() for k, v in base.items()}
+            ap["bsdfs"][b, 2 + c] += h; am["bsdfs"][b, 2 + c] -= h
+            want.append((phi(ap) - phi(am)) / (2 * h)); got.append(gb[b, 2 + c])
+    for e in range(len(base["emitters"])):
+        for c in range(3):
+            h = 0.5
+            ap = {k: v.copy() for k, v in base.items()}; am = {k: v.copy() for k, v in base.items()}
+            ap["emitters"][e, c] += h; am["emitters"][e, c] -= h
+            want.append((phi(ap) - phi(am)) / (2 * h)); got.append(ge[e, c])
+    got, want = np.array(got, np.float64), np.array(want, np.float64)
+    cos = float(got @ want / (np.linalg.norm(got) * np.linalg.norm(want)))
+    assert cos >= 0.999, (cos, got, want)
+    assert np.abs(got - want).max() <= 3e-2 * np.abs(want).max(), (got, want)
+    # the traverse() view: keys, update() round trip, gradients() split
+    params = mi.traverse(sc)
+    assert "white.reflectance.value" in params and "light.emitter.radiance.value" in params
+    g = params.gradients(torch.from_numpy(gb), torch.from_numpy(ge))
+    assert g["red.reflectance.value"].shape == (3,)
+    img0 = mi.render(sc, seed=1, spp=4).cpu().numpy()
+    params["light.emitter.radiance.value"] = params["light.emitter.radiance.value"] * 2
+    params.update()
+    img1 = mi.render(sc, seed=1, spp=4).cpu().numpy()
+    assert rel_rmse(img1, 2 * img0) < 1e-5
