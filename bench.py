@@ -35,7 +35,7 @@ def parse():
     p.add_argument("--n-side", type=int, default=708)
     p.add_argument("--lens", default="gauss")
     p.add_argument("--max-depth", type=int, default=6)
-    p.add_argument("--cpu-crop", type=int, nargs=2, default=[192, 108], help="crop window of the CPU baseline sample")
+    p.add_argument("--cpu-crop", type=int, nargs=2, default=[1280, 720], help="crop window of the CPU baseline sample")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-lens-grad", action="store_true", help="skip the lens-gradient iterations/s section (C2 / C3 shapes)")
     p.add_argument("--lens-iters", type=int, default=10)
@@ -206,6 +206,8 @@ def main():
     if a.impl == "reference":
         if rank != 0:
             return
+        # torchrun exports OMP_NUM_THREADS=1; the CPU arm is meant to use every host core (libgomp reads this at load time)
+        os.environ["OMP_NUM_THREADS"] = str(os.cpu_count())
         import lensrt as mi   # scene front end only (flat arrays); no kernel of ours runs in this arm
         d = workload_dict(mi, a)
         arrays = mi.scene_data_from_dict(d)[0].arrays()
@@ -303,7 +305,7 @@ def main():
                 "bvh": scene.info()}
         if lens_grad is not None:
             line["lens_grad"] = lens_grad
-        if not a.no_cpu_baseline:
+        if not a.no_cpu_baseline and world == 1:     # the contract wants the CPU baseline on rank 0 at N = 1 only
             line["cpu_baseline"], _ = cpu_sample(a, scene.arrays, d["sensor"])
             if lens_grad is not None:
                 line["lens_grad"]["cpu_baseline"] = lens_grad_cpu(mi, a)

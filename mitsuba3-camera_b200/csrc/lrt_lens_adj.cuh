@@ -23,31 +23,21 @@ enum : int { G_Z = 1, G_R = 3, G_C = 3, G_K = 4, G_A0 = 6, G_IORL = 13, G_IORR =
 
 struct AdjRay { float3 o, d; };   // adjoints of a ray's origin and direction
 
-// Reverse of one interface. (o, d): the ray that ENTERED the interface in the forward trace (taped);
-// `bar` holds the adjoint of the ray that LEFT it and is overwritten with the adjoint of the ray that entered;
-// g[16] accumulates the parameter adjoints of this interface.
-LRT_HD void lens_interact_adj(const LensIf &f, float3 o, float3 d, AdjRay &bar, float *g) {
-    // ---- recompute the hit point p, surface gradient gF (F = 0 on the surface), and unit normal n as used
-    float t; float3 p, n, gF;
+// Reverse of one interface. (o, d): the ray that ENTERED the interface in the forward trace (taped); p: the hit point
+// the forward trace found (= the origin of the ray that left the interface, so it is on the tape as well and neither
+// the sphere's root nor the asphere's Newton solve is repeated); `bar` holds the adjoint of the ray that LEFT the
+// interface and is overwritten with the adjoint of the ray that entered; g[16] accumulates the parameter adjoints.
+LRT_HD void lens_interact_adj(const LensIf &f, float3 o, float3 d, float3 p, AdjRay &bar, float *g) {
+    // ---- local geometry at the hit point: distance t, surface gradient gF (F = 0 on the surface), unit normal n as used
+    const float t = dot(p - o, d); float3 n, gF;
     float u = 0.f, w = 1.f, Sp = 0.f, Spp = 0.f, inv_m = 1.f;   // asphere / normalisation temporaries
     if (f.kind == IF_SPHERE) {
         float3 c = make_float3(0.f, 0.f, f.center_z);
-        float3 pcl = c - o;
-        float proj = dot(pcl, d);
-        float3 perp_v = pcl - d * proj;
-        float disc = f.curv_r2 - dot(perp_v, perp_v);
-        float sq = sqrtf(fmaxf(disc, 0.f));
-        t = ((f.convex != 0) != (d.z < 0.f)) ? proj - sq : proj + sq;
-        p = o + d * t;
         float3 m = p - c;
         inv_m = 1.f / sqrtf(dot(m, m));
         n = m * (f.convex ? inv_m : -inv_m);
         gF = m * 2.f;
     } else if (f.kind == IF_ASPHERE) {
-        // converged Newton point: re-run the strict solver (it is the forward code) and read its hit distance
-        LensRay r; r.o = strict::v3(o.x, o.y, o.z); r.d = strict::v3(d.x, d.y, d.z);
-        LensHit h = hit_asphere(f, r);
-        t = h.t; p = f3(h.p);
         u = (p.x * p.x + p.y * p.y) * f.rcp_R2;
         // S(u) = P(u) u^2 + c u / (1 + w), w = sqrt(1 - k1 u);  S' = P' u^2 + 2 u P + c / (2 w)
         float P = 0.f, Pp = 0.f, Ppp = 0.f;
@@ -60,9 +50,7 @@ LRT_HD void lens_interact_adj(const LensIf &f, float3 o, float3 d, AdjRay &bar, 
         inv_m = 1.f / sqrtf(dot(m, m));
         n = m * inv_m;
         gF = make_float3(-m.x, -m.y, 1.f);
-    } else {
-        t = (f.z - o.z) / d.z;                         // plane z = f.z
-        p = o + d * t;
+    } else {                                           // plane z = f.z
         n = make_float3(0.f, 0.f, -1.f);
         gF = make_float3(0.f, 0.f, 1.f);
     }

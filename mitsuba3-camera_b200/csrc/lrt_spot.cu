@@ -205,8 +205,10 @@ __global__ void __launch_bounds__(kSpotThreads) k_spot(SpotArgs A) {
                 float g[kGradRow];
 #pragma unroll
                 for (int q = 0; q < kGradRow; ++q) g[q] = 0.f;
+                // the hit point on interface k is the origin of the ray that entered interface k - 1 (or the final ray)
+                const float3 hp = k > 0 ? make_float3(tape[k - 1][0], tape[k - 1][1], tape[k - 1][2]) : o;
                 lens_interact_adj(L.ifs[k], make_float3(tape[k][0], tape[k][1], tape[k][2]),
-                                  make_float3(tape[k][3], tape[k][4], tape[k][5]), bar, g);
+                                  make_float3(tape[k][3], tape[k][4], tape[k][5]), hp, bar, g);
                 g_loc[k][0] += g[G_Z]; g_loc[k][1] += g[G_R]; g_loc[k][2] += g[G_K];
 #pragma unroll
                 for (int q = 0; q < 7; ++q) g_loc[k][3 + q] += g[G_A0 + q];
@@ -364,11 +366,12 @@ int lrt_sensor_trace_vjp_host(const lrt_sensor *s, int32_t from_world, int64_t n
     for (int64_t i = 0; i < n; ++i) {
         const float *r = od6 + 6 * i;
         LensRay ray; ray.o = strict::v3(r[0], r[1], r[2]); ray.d = strict::v3(r[3], r[4], r[5]);
-        float tape[kMaxInterfaces][6]; bool ok = true;
+        float tape[kMaxInterfaces][6], hitp[kMaxInterfaces][3]; bool ok = true;
         for (int q = 0; q < L.n && ok; ++q) {
             int k = from_world ? L.n - 1 - q : q;
             tape[k][0] = ray.o.x; tape[k][1] = ray.o.y; tape[k][2] = ray.o.z; tape[k][3] = ray.d.x; tape[k][4] = ray.d.y; tape[k][5] = ray.d.z;
             ok = lens_interact(L.ifs[k], ray);
+            hitp[k][0] = ray.o.x; hitp[k][1] = ray.o.y; hitp[k][2] = ray.o.z;
         }
         if (active) active[i] = ok ? 1 : 0;
         float *ob = out_bar6 + 6 * i;
@@ -378,7 +381,8 @@ int lrt_sensor_trace_vjp_host(const lrt_sensor *s, int32_t from_world, int64_t n
         for (int q = L.n - 1; q >= 0; --q) {
             int k = from_world ? L.n - 1 - q : q;
             float g[kGradRow]; for (int c = 0; c < kGradRow; ++c) g[c] = 0.f;
-            lens_interact_adj(L.ifs[k], make_float3(tape[k][0], tape[k][1], tape[k][2]), make_float3(tape[k][3], tape[k][4], tape[k][5]), bar, g);
+            lens_interact_adj(L.ifs[k], make_float3(tape[k][0], tape[k][1], tape[k][2]), make_float3(tape[k][3], tape[k][4], tape[k][5]),
+                              make_float3(hitp[k][0], hitp[k][1], hitp[k][2]), bar, g);
             for (int c = 0; c < kGradRow; ++c) grad_rows16[16 * k + c] += g[c];
         }
         ob[0] = bar.o.x; ob[1] = bar.o.y; ob[2] = bar.o.z; ob[3] = bar.d.x; ob[4] = bar.d.y; ob[5] = bar.d.z;

@@ -75,6 +75,19 @@ def bsdf_row(d: dict) -> np.ndarray:
             return IOR[v] if isinstance(v, str) else float(v)
         r[0] = 2; r[2:5] = _rgb(d.get("specular_reflectance"), [1, 1, 1]); r[11:14] = _rgb(d.get("specular_transmittance"), [1, 1, 1])
         r[14] = f32(ior("int_ior", "bk7")) / f32(ior("ext_ior", "air"))
+    elif t == "dispersive":
+        # the fork's DispersiveDielectric (src/bsdfs/dispersive_dielectric.cpp:209-224,425-431): Cauchy fit through
+        # (n_d, V_d). The *_rgb variants evaluate it at 589.3 nm, where A + B / 0.5893^2 collapses to n_d (up to float32
+        # rounding, reproduced here), so the surface behaves as a `dielectric` with eta = int_ior(589.3) / ext_ior(589.3).
+        def eval_ior(n_d, V_d, wl=f32(0.5893)):
+            n_d, V_d = f32(n_d), f32(V_d)
+            B = f32(0) if not V_d > f32(5.9604644775390625e-08) else f32(f32(n_d - f32(1)) * f32(f32(1) / f32(V_d * f32(
+                f32(f32(1) / f32(f32(0.48613) * f32(0.48613))) - f32(f32(1) / f32(f32(0.65627) * f32(0.65627)))))))
+            A = f32(n_d - f32(B * f32(f32(1) / f32(f32(0.5893) * f32(0.5893)))))
+            return f32(A + f32(B * f32(f32(1) / f32(wl * wl))))
+        r[0] = 2; r[2:5] = _rgb(d.get("specular_reflectance"), [1, 1, 1]); r[11:14] = _rgb(d.get("specular_transmittance"), [1, 1, 1])
+        r[14] = f32(eval_ior(d.get("int_ior", 1.5046), d.get("int_V_d", 64.17)) *
+                    f32(f32(1) / eval_ior(d.get("ext_ior", 1.0), d.get("ext_V_d", 0.0))))
     else:
         raise ValueError(f"BSDF plugin '{t}' is outside the hot path of this build")
     return r
@@ -407,7 +420,7 @@ def _sensor_from(d):
 
 
 _SHAPES = ("rectangle", "cube", "mesh", "obj", "ply")
-_BSDFS = ("diffuse", "conductor", "dielectric", "twosided")
+_BSDFS = ("diffuse", "conductor", "dielectric", "dispersive", "twosided")
 
 
 def scene_data_from_dict(d: dict):

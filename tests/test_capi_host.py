@@ -63,3 +63,11 @@ def test_blocked_focus_ray_is_an_error(mi):
     rows[:, 2] = 1e-6   # semi-diameters too small for the paraxial focus rays (realisticlens.cpp:2132-2134)
     with pytest.raises(mi.capi.LensrtError):
         mi.RealisticLensCamera(mi.Film(64, 64), "custom", prescription=ld.InterfaceList(rows))
+
+
+def test_dispersive_bsdf_row_is_a_dielectric_at_589nm(mi):
+    """dispersive_dielectric.cpp:425-431 at the RGB variants' fixed 589.3 nm: eta = n_d(int) / n_d(ext) up to float32 rounding."""
+    r = mi.bsdf_row({"type": "dispersive", "int_ior": 1.7, "int_V_d": 30.0})
+    assert r[0] == 2 and abs(float(r[14]) - 1.7) < 1e-6
+    r2 = mi.bsdf_row({"type": "dispersive"})
+    assert abs(float(r2[14]) - 1.5046) < 1e-6
