@@ -40,6 +40,23 @@ LRT_D float3 trav_idir(float3 d) {
                        1.f / (fabsf(d.z) < tiny ? copysignf(tiny, d.z) : d.z));
 }
 
+// child slot c of a node (n1 = its second 128-bit word) -> traversal reference (inner node index | leaf encoding)
+LRT_D uint32_t trav_child_ref(const uint4 &n1, uint32_t c) {
+    const uint32_t meta = ((c < 4u ? n1.z : n1.w) >> (8u * (c & 3u))) & 0xffu;
+    return (meta & 0x80u) ? (n1.x + (meta & 0x7fu)) : (0x80000000u | ((meta >> 5) << 28) | (n1.y + (meta & 0x1fu)));
+}
+
+// Stack entries are (node index, key) with key = (bits of t_near & ~7) | child slot: children are pushed without decoding
+// them; the reference is rebuilt from the node's second word only when an entry is actually popped.
+LRT_D uint32_t trav_pop(const BvhView &bvh, int &sp, const uint32_t *st_ref, const float *st_t, float tmax) {
+    while (sp > 0) {
+        --sp;
+        const uint32_t key = __float_as_uint(st_t[sp]);
+        if (__uint_as_float(key & ~7u) <= tmax) return trav_child_ref(__ldg(bvh.nodes + 5 * (size_t) st_ref[sp] + 1), key & 7u);
+    }
+    return kTravDone;
+}
+
 // One inner node: test the 8 quantised child boxes, continue with the nearest hit child, push the others; if nothing is
 // hit pop the next candidate. Requires T.cur to be an inner node.
 LRT_D void trav_node_step(const BvhView &bvh, float3 o, float3 idir, Trav &T, uint32_t *st_ref, float *st_t, unsigned &work) {
@@ -57,7 +74,8 @@ LRT_D void trav_node_step(const BvhView &bvh, float3 o, float3 idir, Trav &T, ui
     const uint32_t nxa = nx ? n3.z : n2.x, nxb = nx ? n3.w : n2.y, fxa = nx ? n2.x : n3.z, fxb = nx ? n2.y : n3.w;
     const uint32_t nya = ny ? n4.x : n2.z, nyb = ny ? n4.y : n2.w, fya = ny ? n2.z : n4.x, fyb = ny ? n2.w : n4.y;
     const uint32_t nza = nz ? n4.z : n3.x, nzb = nz ? n4.w : n3.y, fza = nz ? n3.x : n4.z, fzb = nz ? n3.y : n4.w;
-    uint32_t best = kTravDone; float best_t = inf_f();
+    const uint32_t node = T.cur;
+    uint32_t best = 0xffffffffu;
 #pragma unroll
     for (int c = 0; c < 8; ++c) {
         const uint32_t meta = ((c < 4 ? n1.z : n1.w) >> (8 * (c & 3))) & 0xffu;
@@ -67,19 +85,15 @@ LRT_D void trav_node_step(const BvhView &bvh, float3 o, float3 idir, Trav &T, ui
         const float t0z = fmaf(qbias(c < 4 ? nza : nzb, sel), sz, bz), t1z = fmaf(qbias(c < 4 ? fza : fzb, sel), sz, bz);
         const float tn = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, 0.f));
         const float tf = fminf(fminf(t1x, t1y), fminf(t1z, tmax));
-        // branch-free child bookkeeping (selects + one predicated stack store): the lanes of a warp hit different children
-        const bool hitc = meta != 0 && tn <= tf;
-        const uint32_t ref = (meta & 0x80u) ? (n1.x + (meta & 0x7fu)) : (0x80000000u | ((meta >> 5) << 28) | (n1.y + (meta & 0x1fu)));
-        const bool closer = hitc && tn < best_t;
-        const uint32_t push_ref = closer ? best : (hitc ? ref : kTravDone);
-        const float push_t = closer ? best_t : tn;
-        best = closer ? ref : best; best_t = closer ? tn : best_t;
-        if (push_ref != kTravDone && sp < kTravStack) { st_ref[sp] = push_ref; st_t[sp] = push_t; sp++; }
+        // branch-free bookkeeping on packed keys (t_near >= 0, so unsigned order = float order): keep the smallest key,
+        // push the other one. The 3 cleared mantissa bits make t_near at most 7 ulp smaller: conservative for culling.
+        const uint32_t key = (meta != 0 && tn <= tf) ? ((__float_as_uint(tn) & ~7u) | (uint32_t) c) : 0xffffffffu;
+        const uint32_t hi = max(best, key);
+        best = min(best, key);
+        if (hi != 0xffffffffu && sp < kTravStack) { st_ref[sp] = node; st_t[sp] = __uint_as_float(hi); sp++; }
     }
-    uint32_t cur = best;
-    if (cur == kTravDone)   // nothing hit: pop the next entry that can still matter
-        while (sp > 0) { --sp; if (st_t[sp] <= tmax) { cur = st_ref[sp]; break; } }
-    T.cur = cur; T.sp = sp;
+    T.cur = best != 0xffffffffu ? trav_child_ref(n1, best & 7u) : trav_pop(bvh, sp, st_ref, st_t, tmax);
+    T.sp = sp;
 }
 
 // One leaf (up to 3 triangles, Moeller-Trumbore as mesh.h:432-452), then pop. Requires T.cur to be a leaf.
@@ -104,10 +118,8 @@ LRT_D void trav_leaf_step(const BvhView &bvh, float3 o, float3 d, Trav &T, uint3
             T.hit.t = t; T.hit.u = u; T.hit.v = v; T.hit.tri = (int) (first + k); tmax = t;
         }
     }
-    uint32_t cur = kTravDone;
-    if (!(any_hit && T.hit.tri >= 0))
-        while (sp > 0) { --sp; if (st_t[sp] <= tmax) { cur = st_ref[sp]; break; } }
-    T.cur = cur; T.sp = sp; T.tmax = tmax;
+    T.cur = (any_hit && T.hit.tri >= 0) ? kTravDone : trav_pop(bvh, sp, st_ref, st_t, tmax);
+    T.sp = sp; T.tmax = tmax;
 }
 
 // A burst of traversal for a whole warp (all 32 lanes must call it). Every iteration is warp-uniform: EITHER all lanes
