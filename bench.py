@@ -8,7 +8,7 @@ Workload (config.workload): BASELINE.json configs[4] — the 1M-triangle diffuse
 `gauss` realistic lens at 3840x2160 — the configuration the metric "Mpaths/s at 1/2/4/8 B200" is quoted on.
 One step = one pass of --spp-per-step samples per pixel over the whole film (the 4096-spp job is 4096/spp such
 steps; throughput in paths/s does not depend on the split). Pixel tiles are dealt round-robin over ranks, each
-rank accumulates into its own film storage and one NCCL all-reduce merges them (weak scaling is NOT used: the
+rank accumulates into its own film storage and one NCCL reduce to rank 0 merges them (weak scaling is NOT used: the
 film is fixed, so `scaling` is "strong")."""
 import argparse
 import ctypes as C
@@ -201,7 +201,7 @@ def main():
                           f"{a.width}x{a.height}, path max_depth={a.max_depth}, {a.spp_per_step} spp per step "
                           f"(1/{4096 // max(a.spp_per_step, 1)} of the 4096-spp job)",
               "l2": "flushed between steps (256 MiB write); BVH+triangles ~60 MB are L2-resident by design",
-              "parallelism": f"tile-sharded x{world}, one NCCL all-reduce of the film per step" if world > 1 else "single GPU"}
+              "parallelism": f"tile-sharded x{world}, one NCCL reduce of the film to rank 0 per step" if world > 1 else "single GPU"}
 
     if a.impl == "reference":
         if rank != 0:
@@ -244,8 +244,8 @@ def main():
         storage.zero_()
         mi.render(scene, seed=seed, spp=a.spp_per_step, develop=False, shard=(rank, world), storage=storage)
         if world > 1:
-            dist.all_reduce(storage)
-        if e2e:
+            dist.reduce(storage, dst=0)         # the film is needed on rank 0 only
+        if e2e and rank == 0:
             img = mi.develop_rgb(storage)
             host_img.copy_(img, non_blocking=True)
 
@@ -279,6 +279,21 @@ def main():
         step(2000 + i, e2e=True)
     ms_e2e = timed(a.steps, True, 100)
     sampler.stop_flag = True
+    # adjoint of the path loop (reflectance / radiance gradients): same workload, one pass of lrt_render_backward per step
+    gstore = torch.randn((H, W, 4), dtype=torch.float32, device="cuda")
+    def bstep(seed):
+        gb, ge = mi.render_backward(scene, gstore, seed=seed, spp=a.spp_per_step, shard=(rank, world))
+        if world > 1:
+            dist.all_reduce(gb); dist.all_reduce(ge)
+    bstep(0); torch.cuda.synchronize()
+    eb = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+    eb[0].record()
+    for i in range(max(a.steps // 2, 1)):
+        bstep(10 + i)
+    eb[1].record(); torch.cuda.synchronize()
+    ms_bwd = torch.tensor([eb[0].elapsed_time(eb[1]) / max(a.steps // 2, 1)], device="cuda", dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(ms_bwd, op=dist.ReduceOp.MAX)
     lens_grad = None if a.no_lens_grad else lens_grad_section(mi, torch, dist, a, rank, world)
 
     if rank == 0:
@@ -303,6 +318,9 @@ def main():
                                      "latency/issue bound (divergent traversal), see DESIGN.md"},
                 "stats": {k: int(v) * world for k, v in stats.items()}, "scene_build_s": build_s,
                 "bvh": scene.info()}
+        line["render_backward"] = {"value": paths_per_step / (ms_bwd.item() * 1e-3) / 1e6, "unit": "Mpaths/s", "ms_per_step": ms_bwd.item(),
+                                   "what": "lrt_render_backward on the same workload: gradients of diffuse reflectance / conductor "
+                                           "specular reflectance / area-light radiance (one-pass PRB)"}
         if lens_grad is not None:
             line["lens_grad"] = lens_grad
         if not a.no_cpu_baseline and world == 1:     # the contract wants the CPU baseline on rank 0 at N = 1 only
