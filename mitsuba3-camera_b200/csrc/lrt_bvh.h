@@ -38,6 +38,9 @@ void build_bvh8(const float *verts, const int32_t *idx, const int32_t *tri_shape
 struct BvhView {
     const uint4 *nodes;   // 5 x uint4 per node
     const float4 *tris;   // 3 x float4 per triangle
+    // two constants the traversal wants in REGISTERS rather than as immediates (0x4B000000 and ~7, lrt_trace.cuh):
+    // passed as data so that ptxas cannot fold them back into the instructions
+    uint32_t kb, km;
 };
 
 }  // namespace lrt

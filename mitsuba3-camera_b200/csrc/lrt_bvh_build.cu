@@ -102,7 +102,9 @@ void build_bvh8(const float *verts, const int32_t *idx, const int32_t *tri_shape
     }
     int max_depth = 0;
     if (nt == 0) {   // empty scene: a root whose children are all empty
-        BvhNode n; memset(&n, 0, sizeof n); n.ex = n.ey = n.ez = 1; nodes.push_back(n);
+        BvhNode n; memset(&n, 0, sizeof n); n.ex = n.ey = n.ez = 1;
+        memset(n.qlo_x, 255, 24);   // qlo_x, qlo_y, qlo_z: inverted boxes (lo 255, hi 0) never pass the slab test
+        nodes.push_back(n);
         if (stats) *stats = BvhBuildStats();
         return;
     }
@@ -128,6 +130,7 @@ void build_bvh8(const float *verts, const int32_t *idx, const int32_t *tri_shape
             int c = ch[best]; ch[best] = B.bn[c].left; ch[nch++] = B.bn[c].right;
         }
         BvhNode n; memset(&n, 0, sizeof n);
+        memset(n.qlo_x, 255, 24);   // unused child slots keep an inverted box (lo 255, hi 0): the traversal relies on it
         const Box &nb = root.box;
         n.ex = exponent_for(nb.hi[0] - nb.lo[0]); n.ey = exponent_for(nb.hi[1] - nb.lo[1]); n.ez = exponent_for(nb.hi[2] - nb.lo[2]);
         n.child_base = (uint32_t) queue.size(); n.tri_base = (uint32_t) tris.size();

@@ -99,7 +99,7 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
     const float scale_x = 1.f / (float) F.size_x, scale_y = 1.f / (float) F.size_y;
     const float offs_x = -(float) F.off_x * scale_x, offs_y = -(float) F.off_y * scale_y;
     unsigned long long n_samples = 0, n_miss = 0, n_rays = 0, n_bounces = 0, n_nodes = 0, n_tris = 0;
-    uint32_t st_ref[kTravStack]; float st_t[kTravStack];
+    uint2 st[kTravStack];
     // adjoint state: gradient slots shared by the CTA, per-path records (BSDF id, radiance gathered before the bounce)
     __shared__ float s_grad[kAdj ? kGradSlots : 1];
     const bool grad_in_smem = kAdj && (A.n_bsdfs + A.sc.n_emitters) * 3 <= kGradSlots;
@@ -240,7 +240,7 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
             }
             // ---- C. the ONE traversal site: path segments and shadow rays of different lanes advance together
             unsigned work = 0;
-            bvh_burst(A.sc.bvh, ro, rd, T, st_ref, st_t, phase != 0, phase == 2, A.exit_drop, A.leaf_min, work);
+            bvh_burst(A.sc.bvh, ro, rd, T, st, phase != 0, phase == 2, A.exit_drop, A.leaf_min, work);
             n_nodes += work & 0xffffu; n_tris += work >> 16;
 
             // ---- D. lanes whose ray is finished shade it

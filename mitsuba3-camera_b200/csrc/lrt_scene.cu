@@ -63,6 +63,7 @@ int lrt_scene_create(const lrt_scene_desc *d, lrt_scene **out) {
     }
     if (cudaMalloc(&s->d_counter, 8 * sizeof(unsigned long long)) != cudaSuccess) { lrt_scene_destroy(s); return cuda_fail(cudaGetLastError(), "cudaMalloc"); }
     s->view.bvh.nodes = (const uint4 *) s->d_nodes; s->view.bvh.tris = (const float4 *) s->d_tris;
+    s->view.bvh.kb = 0x4B000000u; s->view.bvh.km = 0xfffffff8u;
     s->view.shape_bsdf = (const int *) s->d_shape_bsdf; s->view.shape_emitter = (const int *) s->d_shape_emitter;
     s->view.bsdfs = (const float4 *) s->d_bsdfs; s->view.emitters = (const float4 *) s->d_emitters;
     s->view.n_emitters = d->n_emitters;

@@ -19,8 +19,9 @@ struct RayHit { float t, u, v; int tri; };   // tri = index into the reordered t
 // `work` accumulates the algorithmic traffic of a traversal: nodes fetched (low 16 bits) and triangles tested
 // (high 16 bits); the render kernel sums it into its statistics (bench.py's roofline `achieved`).
 
-// 0x4B0000qq as float = 8388608 + q
-LRT_D float qbias(uint32_t w, uint32_t sel) { return __uint_as_float(__byte_perm(w, 0x4B000000u, sel)); }
+// 0x4B0000qq as float = 8388608 + q. `kb` = 0x4B000000 comes from BvhView (data, not a literal), so that the byte selector
+// and not the constant becomes PRMT's immediate operand: no selector MOVs in the unrolled node test.
+LRT_D float qbias(uint32_t w, uint32_t kb, uint32_t sel) { return __uint_as_float(__byte_perm(w, kb, sel)); }
 
 constexpr int kTravStack = 64;
 constexpr uint32_t kTravDone = 0x7fffffffu;
@@ -46,25 +47,27 @@ LRT_D uint32_t trav_child_ref(const uint4 &n1, uint32_t c) {
     return (meta & 0x80u) ? (n1.x + (meta & 0x7fu)) : (0x80000000u | ((meta >> 5) << 28) | (n1.y + (meta & 0x1fu)));
 }
 
-// Stack entries are (node index, key) with key = (bits of t_near & ~7) | child slot: children are pushed without decoding
-// them; the reference is rebuilt from the node's second word only when an entry is actually popped.
-LRT_D uint32_t trav_pop(const BvhView &bvh, int &sp, const uint32_t *st_ref, const float *st_t, float tmax) {
+// Stack entries are (node index, key) with key = (bits of t_near & ~7) | child slot, one 64-bit word each: children are
+// pushed without decoding them; the reference is rebuilt from the node's second word only when an entry is popped.
+LRT_D uint32_t trav_pop(const BvhView &bvh, int &sp, const uint2 *st, float tmax) {
     while (sp > 0) {
         --sp;
-        const uint32_t key = __float_as_uint(st_t[sp]);
-        if (__uint_as_float(key & ~7u) <= tmax) return trav_child_ref(__ldg(bvh.nodes + 5 * (size_t) st_ref[sp] + 1), key & 7u);
+        const uint2 e = st[sp];
+        if (__uint_as_float(e.y & ~7u) <= tmax) return trav_child_ref(__ldg(bvh.nodes + 5 * (size_t) e.x + 1), e.y & 7u);
     }
     return kTravDone;
 }
 
 // One inner node: test the 8 quantised child boxes, continue with the nearest hit child, push the others; if nothing is
-// hit pop the next candidate. Requires T.cur to be an inner node.
-LRT_D void trav_node_step(const BvhView &bvh, float3 o, float3 idir, Trav &T, uint32_t *st_ref, float *st_t, unsigned &work) {
+// hit pop the next candidate. Requires T.cur to be an inner node. Empty child slots carry an inverted box (lo 255,
+// hi 0: the builder writes it), so they fail the slab test by themselves and `meta` is not looked at here.
+LRT_D void trav_node_step(const BvhView &bvh, float3 o, float3 idir, Trav &T, uint2 *st, unsigned &work) {
+    const uint32_t kb = bvh.kb, km = bvh.km;   // 0x4B000000 and ~7 as register operands, see qbias() and the key below
     const bool nx = idir.x < 0.f, ny = idir.y < 0.f, nz = idir.z < 0.f;
-    int sp = T.sp; const float tmax = T.tmax;
+    const float tmax = T.tmax;
     work += 1u;
     const uint4 *np = bvh.nodes + 5 * (size_t) T.cur;
-    const uint4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
+    const uint4 n0 = __ldg(np), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
     const float sx = __uint_as_float((n0.w & 0xffu) << 23) * idir.x, sy = __uint_as_float(((n0.w >> 8) & 0xffu) << 23) * idir.y,
                 sz = __uint_as_float(((n0.w >> 16) & 0xffu) << 23) * idir.z;
     const float bx = fmaf(-8388608.f, sx, (__uint_as_float(n0.x) - o.x) * idir.x),
@@ -75,29 +78,31 @@ LRT_D void trav_node_step(const BvhView &bvh, float3 o, float3 idir, Trav &T, ui
     const uint32_t nya = ny ? n4.x : n2.z, nyb = ny ? n4.y : n2.w, fya = ny ? n2.z : n4.x, fyb = ny ? n2.w : n4.y;
     const uint32_t nza = nz ? n4.z : n3.x, nzb = nz ? n4.w : n3.y, fza = nz ? n3.x : n4.z, fzb = nz ? n3.y : n4.w;
     const uint32_t node = T.cur;
+    // a full stack drops its deepest candidates instead of overflowing (never seen: 8 pushes of slack per node)
+    int sp = min(T.sp, kTravStack - 8);
     uint32_t best = 0xffffffffu;
 #pragma unroll
     for (int c = 0; c < 8; ++c) {
-        const uint32_t meta = ((c < 4 ? n1.z : n1.w) >> (8 * (c & 3))) & 0xffu;
         const uint32_t sel = 0x7440u | (uint32_t) (c & 3);
-        const float t0x = fmaf(qbias(c < 4 ? nxa : nxb, sel), sx, bx), t1x = fmaf(qbias(c < 4 ? fxa : fxb, sel), sx, bx);
-        const float t0y = fmaf(qbias(c < 4 ? nya : nyb, sel), sy, by), t1y = fmaf(qbias(c < 4 ? fya : fyb, sel), sy, by);
-        const float t0z = fmaf(qbias(c < 4 ? nza : nzb, sel), sz, bz), t1z = fmaf(qbias(c < 4 ? fza : fzb, sel), sz, bz);
+        const float t0x = fmaf(qbias(c < 4 ? nxa : nxb, kb, sel), sx, bx), t1x = fmaf(qbias(c < 4 ? fxa : fxb, kb, sel), sx, bx);
+        const float t0y = fmaf(qbias(c < 4 ? nya : nyb, kb, sel), sy, by), t1y = fmaf(qbias(c < 4 ? fya : fyb, kb, sel), sy, by);
+        const float t0z = fmaf(qbias(c < 4 ? nza : nzb, kb, sel), sz, bz), t1z = fmaf(qbias(c < 4 ? fza : fzb, kb, sel), sz, bz);
         const float tn = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, 0.f));
         const float tf = fminf(fminf(t1x, t1y), fminf(t1z, tmax));
         // branch-free bookkeeping on packed keys (t_near >= 0, so unsigned order = float order): keep the smallest key,
         // push the other one. The 3 cleared mantissa bits make t_near at most 7 ulp smaller: conservative for culling.
-        const uint32_t key = (meta != 0 && tn <= tf) ? ((__float_as_uint(tn) & ~7u) | (uint32_t) c) : 0xffffffffu;
+        const uint32_t key = tn <= tf ? ((__float_as_uint(tn) & km) | (uint32_t) c) : 0xffffffffu;
         const uint32_t hi = max(best, key);
         best = min(best, key);
-        if (hi != 0xffffffffu && sp < kTravStack) { st_ref[sp] = node; st_t[sp] = __uint_as_float(hi); sp++; }
+        st[sp] = make_uint2(node, hi);   // stored unconditionally, kept only if it is a candidate
+        if (hi != 0xffffffffu) ++sp;
     }
-    T.cur = best != 0xffffffffu ? trav_child_ref(n1, best & 7u) : trav_pop(bvh, sp, st_ref, st_t, tmax);
+    T.cur = best != 0xffffffffu ? trav_child_ref(__ldg(np + 1), best & 7u) : trav_pop(bvh, sp, st, tmax);
     T.sp = sp;
 }
 
 // One leaf (up to 3 triangles, Moeller-Trumbore as mesh.h:432-452), then pop. Requires T.cur to be a leaf.
-LRT_D void trav_leaf_step(const BvhView &bvh, float3 o, float3 d, Trav &T, uint32_t *st_ref, float *st_t, bool any_hit, unsigned &work) {
+LRT_D void trav_leaf_step(const BvhView &bvh, float3 o, float3 d, Trav &T, uint2 *st, bool any_hit, unsigned &work) {
     const uint32_t first = T.cur & 0x0fffffffu, count = (T.cur >> 28) & 3u;
     int sp = T.sp; float tmax = T.tmax;
     work += count << 16;
@@ -118,7 +123,7 @@ LRT_D void trav_leaf_step(const BvhView &bvh, float3 o, float3 d, Trav &T, uint3
             T.hit.t = t; T.hit.u = u; T.hit.v = v; T.hit.tri = (int) (first + k); tmax = t;
         }
     }
-    T.cur = (any_hit && T.hit.tri >= 0) ? kTravDone : trav_pop(bvh, sp, st_ref, st_t, tmax);
+    T.cur = (any_hit && T.hit.tri >= 0) ? kTravDone : trav_pop(bvh, sp, st, tmax);
     T.sp = sp; T.tmax = tmax;
 }
 
@@ -127,7 +132,7 @@ LRT_D void trav_leaf_step(const BvhView &bvh, float3 o, float3 d, Trav &T, uint3
 // all lanes standing on a leaf test its triangles — node code and triangle code never run interleaved at low width.
 // The burst ends when the number of traversing lanes has dropped by `exit_drop` 32nds of what it was at entry (at
 // least by one): finished lanes go and shade / fetch new rays instead of idling until the slowest ray is done.
-LRT_D void bvh_burst(const BvhView &bvh, float3 o, float3 d, Trav &T, uint32_t *st_ref, float *st_t, bool live, bool any_hit,
+LRT_D void bvh_burst(const BvhView &bvh, float3 o, float3 d, Trav &T, uint2 *st, bool live, bool any_hit,
                      int exit_drop, int leaf_min, unsigned &work) {
     const float3 idir = trav_idir(d);
     const int a0 = __popc(__ballot_sync(0xffffffffu, live && T.cur != kTravDone));
@@ -139,21 +144,21 @@ LRT_D void bvh_burst(const BvhView &bvh, float3 o, float3 d, Trav &T, uint32_t *
         const unsigned lm = __ballot_sync(0xffffffffu, at_leaf), nm = __ballot_sync(0xffffffffu, act && !at_leaf);
         if (__popc(lm | nm) <= floor_active) break;
         if (nm == 0u || __popc(lm) >= leaf_min) {
-            if (at_leaf) trav_leaf_step(bvh, o, d, T, st_ref, st_t, any_hit, work);
+            if (at_leaf) trav_leaf_step(bvh, o, d, T, st, any_hit, work);
         } else {
-            if (act && !at_leaf) trav_node_step(bvh, o, idir, T, st_ref, st_t, work);
+            if (act && !at_leaf) trav_node_step(bvh, o, idir, T, st, work);
         }
     }
 }
 
 // One ray, run to completion (unit-level Scene::ray_intersect / ray_test).
 LRT_D RayHit bvh_intersect(const BvhView &bvh, float3 o, float3 d, float tmax, bool any_hit, unsigned &work) {
-    uint32_t st_ref[kTravStack]; float st_t[kTravStack];
+    uint2 st[kTravStack];
     Trav T; trav_init(T, tmax);
     const float3 idir = trav_idir(d);
     while (T.cur != kTravDone) {
-        if (T.cur & 0x80000000u) trav_leaf_step(bvh, o, d, T, st_ref, st_t, any_hit, work);
-        else trav_node_step(bvh, o, idir, T, st_ref, st_t, work);
+        if (T.cur & 0x80000000u) trav_leaf_step(bvh, o, d, T, st, any_hit, work);
+        else trav_node_step(bvh, o, idir, T, st, work);
     }
     return T.hit;
 }
