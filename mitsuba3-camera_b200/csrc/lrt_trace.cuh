@@ -53,7 +53,8 @@ LRT_D uint32_t trav_pop(const BvhView &bvh, int &sp, const uint2 *st, float tmax
     while (sp > 0) {
         --sp;
         const uint2 e = st[sp];
-        if (__uint_as_float(e.y & ~7u) <= tmax) return trav_child_ref(__ldg(bvh.nodes + 5 * (size_t) e.x + 1), e.y & 7u);
+        if (__uint_as_float(e.y & ~7u) <= tmax)
+            return trav_child_ref(__ldg(bvh.nodes + 5 * (size_t) (e.x & 0x7fffffffu) + 1), (e.y & 3u) | ((e.x >> 31) << 2));
     }
     return kTravDone;
 }
@@ -61,6 +62,9 @@ LRT_D uint32_t trav_pop(const BvhView &bvh, int &sp, const uint2 *st, float tmax
 // One inner node: test the 8 quantised child boxes, continue with the nearest hit child, push the others; if nothing is
 // hit pop the next candidate. Requires T.cur to be an inner node. Empty child slots carry an inverted box (lo 255,
 // hi 0: the builder writes it), so they fail the slab test by themselves and `meta` is not looked at here.
+// The children are tested in two rounds of four by a loop that is NOT unrolled: the traversal loop then fits the
+// instruction cache next to the leaf test. Keys carry the slot within the round (2 bits); the round is bit 31 of the
+// stack entry's node word.
 LRT_D void trav_node_step(const BvhView &bvh, float3 o, float3 idir, Trav &T, uint2 *st, unsigned &work) {
     const uint32_t kb = bvh.kb, km = bvh.km;   // 0x4B000000 and ~7 as register operands, see qbias() and the key below
     const bool nx = idir.x < 0.f, ny = idir.y < 0.f, nz = idir.z < 0.f;
@@ -77,31 +81,42 @@ LRT_D void trav_node_step(const BvhView &bvh, float3 o, float3 idir, Trav &T, ui
     const uint32_t nxa = nx ? n3.z : n2.x, nxb = nx ? n3.w : n2.y, fxa = nx ? n2.x : n3.z, fxb = nx ? n2.y : n3.w;
     const uint32_t nya = ny ? n4.x : n2.z, nyb = ny ? n4.y : n2.w, fya = ny ? n2.z : n4.x, fyb = ny ? n2.w : n4.y;
     const uint32_t nza = nz ? n4.z : n3.x, nzb = nz ? n4.w : n3.y, fza = nz ? n3.x : n4.z, fzb = nz ? n3.y : n4.w;
-    const uint32_t node = T.cur;
-    // a full stack drops its deepest candidates instead of overflowing (never seen: 8 pushes of slack per node)
-    int sp = min(T.sp, kTravStack - 8);
-    uint32_t best = 0xffffffffu;
+    // a full stack drops its deepest candidates instead of overflowing (never seen: 9 pushes of slack per node)
+    int sp = min(T.sp, kTravStack - 9);
+    uint32_t best = 0xffffffffu, best0 = 0xffffffffu, xh = T.cur;
+#pragma unroll 1
+    for (int h = 0; h < 2; ++h) {
+        best0 = best; best = 0xffffffffu;   // after the loop: best0 = nearest of children 0-3, best = nearest of 4-7
+        const uint32_t wnx = h ? nxb : nxa, wfx = h ? fxb : fxa, wny = h ? nyb : nya, wfy = h ? fyb : fya, wnz = h ? nzb : nza, wfz = h ? fzb : fza;
 #pragma unroll
-    for (int c = 0; c < 8; ++c) {
-        const uint32_t sel = 0x7440u | (uint32_t) (c & 3);
-        const float t0x = fmaf(qbias(c < 4 ? nxa : nxb, kb, sel), sx, bx), t1x = fmaf(qbias(c < 4 ? fxa : fxb, kb, sel), sx, bx);
-        const float t0y = fmaf(qbias(c < 4 ? nya : nyb, kb, sel), sy, by), t1y = fmaf(qbias(c < 4 ? fya : fyb, kb, sel), sy, by);
-        const float t0z = fmaf(qbias(c < 4 ? nza : nzb, kb, sel), sz, bz), t1z = fmaf(qbias(c < 4 ? fza : fzb, kb, sel), sz, bz);
-        const float tn = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, 0.f));
-        const float tf = fminf(fminf(t1x, t1y), fminf(t1z, tmax));
-        // branch-free bookkeeping on packed keys (t_near >= 0, so unsigned order = float order): keep the smallest key,
-        // push the other one. The 3 cleared mantissa bits make t_near at most 7 ulp smaller: conservative for culling.
-        const uint32_t key = tn <= tf ? ((__float_as_uint(tn) & km) | (uint32_t) c) : 0xffffffffu;
-        const uint32_t hi = max(best, key);
-        best = min(best, key);
-        st[sp] = make_uint2(node, hi);   // stored unconditionally, kept only if it is a candidate
-        if (hi != 0xffffffffu) ++sp;
+        for (int c = 0; c < 4; ++c) {
+            const uint32_t sel = 0x7440u | (uint32_t) c;
+            const float t0x = fmaf(qbias(wnx, kb, sel), sx, bx), t1x = fmaf(qbias(wfx, kb, sel), sx, bx);
+            const float t0y = fmaf(qbias(wny, kb, sel), sy, by), t1y = fmaf(qbias(wfy, kb, sel), sy, by);
+            const float t0z = fmaf(qbias(wnz, kb, sel), sz, bz), t1z = fmaf(qbias(wfz, kb, sel), sz, bz);
+            const float tn = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, 0.f));
+            const float tf = fminf(fminf(t1x, t1y), fminf(t1z, tmax));
+            // branch-free bookkeeping on packed keys (t_near >= 0, so unsigned order = float order): keep the smallest
+            // key, push the other one. The 3 cleared mantissa bits make t_near at most 7 ulp smaller: conservative.
+            const uint32_t key = tn <= tf ? ((__float_as_uint(tn) & km) | (uint32_t) c) : 0xffffffffu;
+            const uint32_t hi = max(best, key);
+            best = min(best, key);
+            st[sp] = make_uint2(xh, hi);   // stored unconditionally, kept only if it is a candidate
+            if (hi != 0xffffffffu) ++sp;
+        }
+        xh |= 0x80000000u;
     }
-    T.cur = best != 0xffffffffu ? trav_child_ref(__ldg(np + 1), best & 7u) : trav_pop(bvh, sp, st, tmax);
+    // nearest of the two rounds continues, the other one is pushed
+    const bool first = best0 <= best;
+    const uint32_t nearest = first ? best0 : best, other = first ? best : best0;
+    st[sp] = make_uint2(first ? xh : (xh & 0x7fffffffu), other);
+    if (other != 0xffffffffu) ++sp;
+    T.cur = nearest != 0xffffffffu ? trav_child_ref(__ldg(np + 1), (nearest & 3u) | (first ? 0u : 4u)) : trav_pop(bvh, sp, st, tmax);
     T.sp = sp;
 }
 
 // One leaf (up to 3 triangles, Moeller-Trumbore as mesh.h:432-452), then pop. Requires T.cur to be a leaf.
+// (Fetching the stack top and its node word ahead of the triangle tests was measured slower: 706 vs 718 Mpaths/s.)
 LRT_D void trav_leaf_step(const BvhView &bvh, float3 o, float3 d, Trav &T, uint2 *st, bool any_hit, unsigned &work) {
     const uint32_t first = T.cur & 0x0fffffffu, count = (T.cur >> 28) & 3u;
     int sp = T.sp; float tmax = T.tmax;
