@@ -25,7 +25,9 @@ namespace lrt {
 
 constexpr int kTileW = 32, kTileH = 1, kCtaThreads = 128, kWarps = kCtaThreads / 32;
 constexpr int kFifo = 64, kFifoWords = 14;      // camera-ray FIFO per warp: o[3] d[3] maxt weight sx sy rng.state rng.inc
-constexpr int kQueue = 64, kQueueWords = 5;     // splat queue per warp: sx sy r g b
+constexpr int kQueue = 96, kQueueWords = 5;     // splat queue per warp: sx sy r g b. Drained (32 at a time) at ONE place, the top
+                                                // of the warp's loop, where it holds < 32 entries afterwards; camera-ray
+                                                // generation and shading add at most 32 each before the next drain
 constexpr int kMaxRec = 12;                     // adjoint: bounces of one path that can receive a BSDF gradient
 constexpr int kGradSlots = 1024;                // adjoint: per-CTA shared accumulators (3 per BSDF, 3 per emitter)
 
@@ -163,8 +165,11 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
             q_count += __popc(m);
         };
 
+        bool exhausted = false;   // no lane active, no camera ray left: only the queue remains to be drained
         while (true) {
-            if (q_count >= 32) drain(32);
+            // the only drain site (splat_to_tile is ~500 instructions; inlining it four times cost instruction-cache misses)
+            if (q_count >= 32 || (exhausted && q_count > 0)) drain(min(q_count, 32));
+            if (exhausted) { if (q_count == 0) break; continue; }
             // ---- A. camera rays, 32 at a time: render_sample() draws in the reference's order (integrator.cpp:435-448)
             if (fifo_count < 32 && round < n_rounds) {
                 const int j = j0 + round; round++;
@@ -194,7 +199,6 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
                 }
                 fifo_count += __popc(hm);
                 __syncwarp();
-                if (q_count >= 32) drain(32);
             }
             // ---- B. idle lanes take the next camera rays
             {
@@ -235,7 +239,7 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
                 __syncwarp();
             }
             if (__ballot_sync(0xffffffffu, phase != 0) == 0) {
-                if (fifo_count == 0 && round >= n_rounds) break;
+                exhausted = fifo_count == 0 && round >= n_rounds;
                 continue;
             }
             // ---- C. the ONE traversal site: path segments and shadow rays of different lanes advance together
@@ -355,8 +359,6 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
         }
         // ---- drain what is left, then put_block(): flush the tile into the film accumulator
         if (kAdj) { __syncwarp(); continue; }
-        if (q_count > 32) drain(32);
-        if (q_count > 0) drain(q_count);
         const int sw = F.size_x + 2 * F.border, shh = F.size_y + 2 * F.border;
         for (int i = lane; i < A.smem_w * A.smem_h; i += 32) {
             int ly = i / A.smem_w, lx = i - ly * A.smem_w;
