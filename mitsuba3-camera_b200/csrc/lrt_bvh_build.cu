@@ -4,6 +4,7 @@
 #include "lrt_bvh.h"
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <limits>
 
@@ -28,7 +29,8 @@ struct Builder {
     std::vector<Box> tbox; std::vector<float> cent;   // per triangle
     std::vector<int> order;
     std::vector<BinNode> bn;
-    static constexpr int kBins = 16, kLeaf = 3;
+    static constexpr int kBins = 16;
+    int kLeaf = 3;
 
     int build(int first, int count, int depth, int &max_depth) {
         BinNode nd; nd.box.reset(); nd.first = first; nd.count = count;
@@ -93,6 +95,7 @@ void build_bvh8(const float *verts, const int32_t *idx, const int32_t *tri_shape
                 std::vector<BvhNode> &nodes, std::vector<BvhTri> &tris, BvhBuildStats *stats) {
     nodes.clear(); tris.clear();
     Builder B; B.verts = verts; B.idx = idx; B.nt = nt;
+    if (const char *e = getenv("LRT_BVH_LEAF")) B.kLeaf = std::min(3, std::max(1, atoi(e)));
     B.tbox.resize(nt); B.cent.resize(3 * (size_t) nt); B.order.resize(nt);
     for (int64_t t = 0; t < nt; ++t) {
         Box b; b.reset();
