@@ -29,7 +29,9 @@ def parse():
     p.add_argument("--steps", type=int, default=5)
     p.add_argument("--warmup", type=int, default=3)
     p.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    p.add_argument("--spp-per-step", type=int, default=16)
+    p.add_argument("--spp-per-step", type=int, default=64,
+                   help="samples per pixel of one step (one pass; the reference's own passes are bounded by W*H*spp < 2^32, i.e. <= 517 spp here)")
+    p.add_argument("--cpu-spp", type=int, default=16, help="spp of the bounded CPU sample (same film crop, same scene)")
     p.add_argument("--width", type=int, default=3840)
     p.add_argument("--height", type=int, default=2160)
     p.add_argument("--n-side", type=int, default=708)
@@ -76,7 +78,8 @@ def workload_dict(mi, a):
 
 
 def cpu_sample(a, scene_arrays, sensor_dict, steps=1, warmup=0):
-    """The CPU arm: the oracle port (OpenMP, all host cores) on a centred crop of the same film at the same spp."""
+    """The CPU arm: the oracle port (OpenMP, all host cores) on a centred crop of the same film at --cpu-spp samples per pixel
+    (a bounded sample: paths/s of the port does not depend on the pass size)."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import numpy as np
     import oracle_lib as ol
@@ -88,16 +91,17 @@ def cpu_sample(a, scene_arrays, sensor_dict, steps=1, warmup=0):
     tw = sensor_dict["to_world"].matrix
     cam = ol.orc_camera(ld.design(a.lens, {"object_distance": sensor_dict["object_distance"]}), film, to_world=tw,
                         near=sensor_dict["near_clip"], far=sensor_dict["far_clip"], object_distance=sensor_dict["object_distance"])
-    paths = cw * ch * a.spp_per_step
+    cpu_spp = min(a.cpu_spp, a.spp_per_step)
+    paths = cw * ch * cpu_spp
     times = []
     for i in range(warmup + steps):
         t0 = time.perf_counter()
-        ol.orc_render(h, film, a.spp_per_step, seed=i, max_depth=a.max_depth, cam_h=cam)
+        ol.orc_render(h, film, cpu_spp, seed=i, max_depth=a.max_depth, cam_h=cam)
         if i >= warmup:
             times.append(time.perf_counter() - t0)
     sec = sum(times) / len(times)
     return {"value": paths / sec / 1e6, "unit": "Mpaths/s", "cores": os.cpu_count(), "kind": "port",
-            "sample": f"centred {cw}x{ch} crop of the {a.width}x{a.height} film, {a.spp_per_step} spp ({paths} paths, {sec:.2f} s/step)"}, sec
+            "sample": f"centred {cw}x{ch} crop of the {a.width}x{a.height} film, {cpu_spp} spp ({paths} paths, {sec:.2f} s/step)"}, sec
 
 
 def doublet_table(mi):
