@@ -78,6 +78,17 @@ int lrt_sensor_set_interfaces(lrt_sensor *s, int32_t n, const float *rows16);
 int lrt_sensor_set_to_world(lrt_sensor *s, const float *to_world16);
 int lrt_sensor_get_info(const lrt_sensor *s, float *sample_to_film16, float *focus_delta, float *film_z);
 
+/* Exit-pupil sampling (the sensor's `sample_exit_pupil` property, src/sensors/realisticlens.cpp:913-921).
+ * enable != 0 builds the 64-segment LUT on the GPU -- compute_exit_pupil_bounds / bound_exit_pupil (:1685-1809):
+ * 64 x 2^20 Halton rays (RadicalInverse::eval, include/mitsuba/core/qmc.h:68-91) traced film -> world -- and switches
+ * sample_ray to sample_exit_pupil (:1812-1845) with the weight shutter_open_time * box area / rear_z^2 (:2279-2289).
+ * shutter_open_time is Sensor::shutter_open_time() (0 unless the scene sets shutter_open/close, as in the reference).
+ * set_interfaces() rebuilds the LUT while the mode is on. get: bounds256 = 64 x (min.x, min.y, max.x, max.y), metres. */
+int lrt_sensor_set_exit_pupil(lrt_sensor *s, int32_t enable, float shutter_open_time, void *stream);
+int lrt_sensor_get_exit_pupil(const lrt_sensor *s, float *bounds256);
+/* RadicalInverse::eval(base_index, index) for base_index 0..2 (primes 2, 3, 5); host function, -1 if out of range */
+float lrt_radical_inverse(int32_t base_index, uint64_t index);
+
 /* Sensor::sample_ray (realisticlens.cpp:2209-2292) for n samples: pos2/ap2 = film and aperture samples in
  * [0,1]^2; out10 = origin[3], direction[3], maxt, weight[3] (world space). */
 int lrt_sensor_sample_ray(const lrt_sensor *s, int64_t n, const float *pos2_dev, const float *ap2_dev,

@@ -36,6 +36,7 @@ def _load():
 lib = _load()
 lib.lrt_last_error.restype = C.c_char_p
 lib.lrt_launch_count.restype = C.c_uint64
+lib.lrt_radical_inverse.restype = C.c_float
 
 
 def check(rc: int):

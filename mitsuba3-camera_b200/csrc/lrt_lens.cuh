@@ -31,6 +31,8 @@ struct alignas(16) LensIf {
 };
 static_assert(sizeof(LensIf) == 144, "LensIf layout");
 
+constexpr int kPupilSegments = 64;               // realisticlens.cpp:1772
+constexpr int kPupilRaysLog2 = 20;               // 1024 * 1024 rays per segment (:1686)
 struct alignas(16) LensSystem {
     int n; int kind;   // kind: 0 = realisticlens, 1 = perspective pinhole
     float rear_z, rear_radius;
@@ -38,12 +40,15 @@ struct alignas(16) LensSystem {
     float s2f_m00, s2f_m03, s2f_m11, s2f_m13;   // sample -> film (diagonal + translation)
     float to_world[12];                         // rows of the affine camera-to-world matrix
     // perspective (src/sensors/perspective.cpp): sample -> camera and image-plane normalisation
-    float persp_s2c[16]; float persp_norm, pad0, pad1, pad2;
+    float persp_s2c[16]; float persp_norm; int pupil_mode; float pad1, pad2;   // pupil_mode: sample_exit_pupil (see pupil_bounds)
     // film -> sample (diagonal + translation), film-plane normalisation 1/area and crop resolution: what
     // sample_direction needs (realisticlens.cpp:2190-2207,2352-2372)
     float f2s_m00, f2s_m03, f2s_m11, f2s_m13;
-    float normalization, res_x, res_y, pad3;
+    float normalization, res_x, res_y, film_diagonal;
     LensIf ifs[kMaxInterfaces];
+    // exit-pupil LUT (realisticlens.cpp:1769-1809): per radial film segment, (min.x, min.y, max.x, max.y) of the region of
+    // the rear plane z = rear_z through which rays from that segment leave the lens; filled by lrt_sensor_set_exit_pupil
+    float pupil_bounds[kPupilSegments][4];
 };
 
 struct LensRay { strict::V3 o, d; };
@@ -269,11 +274,47 @@ struct CameraRay { float3 o, d; float maxt; float weight; bool active; float3 d_
 
 // RealisticLensCamera::sample_ray (:2209-2292), rear-element sampling branch. (u,v): film sample in
 // [0,1]^2 of the crop window, (a,b): aperture sample.
+// RadicalInverse::eval (include/mitsuba/core/qmc.h:68-91), unscrambled, for the prime bases 2, 3, 5 (base_index 0..2):
+// the digits of `index` mirrored at the radix point; the scale is a running product of the rounded reciprocal.
+LRT_HD float radical_inverse(int base_index, uint64_t index) {
+    const uint64_t divisor = base_index == 0 ? 2u : (base_index == 1 ? 3u : 5u);
+    const float recip = strict::div(1.f, (float) divisor);
+    uint64_t value = 0; float factor = 1.f;
+    while (index != 0) {
+        const uint64_t next = index / divisor;
+        factor = strict::mul(factor, recip);
+        value = (value - next) * divisor + index;
+        index = next;
+    }
+    return fminf(u2f(0x3f7fffffu), strict::mul((float) value, factor));
+}
+
+// dr::lerp (drjit/array_router.h:332): fmadd(b, t, fnmadd(a, t, a)), every step rounded
+LRT_HD float lerp_drjit(float a, float b, float t) { return strict::add(strict::mul(b, t), strict::sub(a, strict::mul(a, t))); }
+
+// sample_exit_pupil (realisticlens.cpp:1812-1845): a point of the rear plane inside the LUT box of the film point's radial
+// segment, rotated to the film point's azimuth; `bounds_area` = area of that box
+LRT_HD strict::V3 lens_sample_exit_pupil(const LensSystem &L, strict::V3 film_p, float a, float b, float &bounds_area) {
+    using namespace strict;
+    const float r_film = sqrt(add(sqr(film_p.x), sqr(film_p.y)));
+    int idx = (int) floorf(mul(div(r_film, L.film_diagonal), (float) kPupilSegments));
+    idx = idx < 0 ? 0 : (idx > kPupilSegments - 1 ? kPupilSegments - 1 : idx);
+    const float minx = L.pupil_bounds[idx][0], miny = L.pupil_bounds[idx][1], maxx = L.pupil_bounds[idx][2], maxy = L.pupil_bounds[idx][3];
+    bounds_area = mul(sub(maxx, minx), sub(maxy, miny));
+    const float px = lerp_drjit(minx, maxx, a), py = lerp_drjit(miny, maxy, b);
+    const float sin_t = r_film > 0.f ? mul(film_p.y, rcp(r_film)) : 0.f, cos_t = r_film > 0.f ? mul(film_p.x, rcp(r_film)) : 1.f;
+    return v3(sub(mul(cos_t, px), mul(sin_t, py)), add(mul(sin_t, px), mul(cos_t, py)), L.rear_z);
+}
+
 LRT_HD CameraRay lens_sample_ray(const LensSystem &L, const LensIf *ifs, float u, float v, float a, float b) {
     using namespace strict;
     V3 film_p = v3(add(mul(L.s2f_m00, u), L.s2f_m03), add(mul(L.s2f_m11, v), L.s2f_m13), 0.f);
-    float dx, dy; square_to_disk_concentric(a, b, dx, dy);
-    V3 ap = v3(mul(L.rear_radius, dx), mul(L.rear_radius, dy), L.rear_z);
+    V3 ap; float bounds_area = 0.f;
+    if (L.pupil_mode) ap = lens_sample_exit_pupil(L, film_p, a, b, bounds_area);
+    else {
+        float dx, dy; square_to_disk_concentric(a, b, dx, dy);
+        ap = v3(mul(L.rear_radius, dx), mul(L.rear_radius, dy), L.rear_z);
+    }
     LensRay ray; ray.o = film_p; ray.d = normalize(sub(ap, film_p));
     bool active = lens_trace_from_film(ifs, L.n, ray);
     V3 dl = ray.d, o = ray.o;
@@ -290,7 +331,10 @@ LRT_HD CameraRay lens_sample_ray(const LensSystem &L, const LensIf *ifs, float u
     ow = at(ow, dw, near_t);
     CameraRay r;
     r.o = f3(ow); r.d = f3(dw); r.maxt = sub(far_t, near_t);
-    r.weight = active ? sqr(sqr(dl.z)) : 0.f;
+    // weight (:2279-2289): cos^4 of the exit direction, or in pupil mode shutter_open_time * box area / rear_z^2
+    // (the reference's shutter_open_time() is 0 unless shutter_open/close are set: its pupil-mode images are then black)
+    const float w = L.pupil_mode ? mul(mul(L.shutter_open_time, bounds_area), rcp(sqr(L.rear_z))) : sqr(sqr(dl.z));
+    r.weight = active ? w : 0.f;
     r.active = active; r.d_local = f3(dl);
     return r;
 }

@@ -181,6 +181,7 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
                     const float ax = strict::fmadd(spx, scale_x, offs_x), ay = strict::fmadd(spy, scale_y, offs_y);
                     float a = .5f, b = .5f;
                     if (L.kind == 0) { a = g.next_f32(); b = g.next_f32(); }
+                    if (L.shutter_open_time > 0.f) (void) g.next_f32();   // the time sample (integrator.cpp:442-444)
                     cr = sensor_sample_ray(L, L.ifs, ax, ay, a, b);
                     gx = box ? posx : spx; gy = box ? posy : spy;
                     hit = cr.weight > 0.f && A.max_depth != 0;

@@ -117,6 +117,7 @@ static void setup_film(lrt_sensor &s) {
     s.host.persp_norm = s.normalization;
     s.host.f2s_m00 = q[0]; s.host.f2s_m03 = q[3]; s.host.f2s_m11 = q[5]; s.host.f2s_m13 = q[7];
     s.host.normalization = s.normalization; s.host.res_x = (float) g.crop_w; s.host.res_y = (float) g.crop_h;
+    s.host.film_diagonal = sqrtf(px * px + py * py);   // m_film_diagonal = norm(get_physical_size()) (realisticlens.cpp:838)
 }
 
 // ------------------------------------------------------------------ thick-lens autofocus (:2107-2171)
@@ -206,6 +207,81 @@ __global__ void __launch_bounds__(256) k_sampler_draw(uint32_t seed, uint32_t id
         Pcg32 rng; rng.seed_sample(seed, idx0 + (uint32_t) i);
         for (int k = 0; k < ndraw; ++k) out[i * ndraw + k] = rng.next_f32();
     }
+}
+
+// bound_exit_pupil (realisticlens.cpp:1685-1767) for all 64 film segments at once: blockIdx.y = segment, the 2^20 Halton
+// rays of a segment are dealt over blockIdx.x. The reference walks them in order and skips rays whose rear-plane point is
+// already inside the box found so far; the box is the min / max over TRANSMITTED points either way, so the order does not
+// matter. out[seg] = { min.x, min.y, max.x, max.y as order-preserving uints, transmitted count }.
+LRT_D uint32_t ordered_bits(float f) { const uint32_t u = __float_as_uint(f); return (u & 0x80000000u) ? ~u : (u | 0x80000000u); }
+__global__ void __launch_bounds__(256) k_exit_pupil(const LensSystem *__restrict__ Lg, uint32_t *__restrict__ out) {
+    __shared__ LensSystem L;
+    {
+        const uint4 *src = reinterpret_cast<const uint4 *>(Lg);
+        uint4 *dst = reinterpret_cast<uint4 *>(&L);
+        for (int i = threadIdx.x; i < (int) (sizeof(LensSystem) / 16); i += blockDim.x) dst[i] = src[i];
+    }
+    __syncthreads();
+    using namespace strict;
+    const int seg = blockIdx.y;
+    const uint32_t n_rays = 1u << kPupilRaysLog2;
+    const float r0 = div(mul((float) seg, L.film_diagonal), (float) kPupilSegments),
+                r1 = div(mul((float) (seg + 1), L.film_diagonal), (float) kPupilSegments);
+    const float R = mul(L.ifs[0].elem_radius, 1.5f), rear_z = L.ifs[0].z;
+    uint32_t mnx = 0xffffffffu, mny = 0xffffffffu, mxx = 0u, mxy = 0u, cnt = 0u;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_rays; i += gridDim.x * blockDim.x) {
+        const float fx = lerp_drjit(r0, r1, div(add((float) i, .5f), (float) n_rays));
+        const float px = lerp_drjit(-R, R, radical_inverse(0, i)), py = lerp_drjit(-R, R, radical_inverse(1, i));
+        LensRay ray; ray.o = v3(fx, 0.f, 0.f); ray.d = normalize(sub(v3(px, py, rear_z), ray.o));
+        if (lens_trace_from_film(L.ifs, L.n, ray)) {
+            mnx = min(mnx, ordered_bits(px)); mxx = max(mxx, ordered_bits(px));
+            mny = min(mny, ordered_bits(py)); mxy = max(mxy, ordered_bits(py));
+            cnt++;
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        mnx = min(mnx, __shfl_xor_sync(0xffffffffu, mnx, o)); mny = min(mny, __shfl_xor_sync(0xffffffffu, mny, o));
+        mxx = max(mxx, __shfl_xor_sync(0xffffffffu, mxx, o)); mxy = max(mxy, __shfl_xor_sync(0xffffffffu, mxy, o));
+        cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+    }
+    if ((threadIdx.x & 31) == 0 && cnt) {
+        uint32_t *q = out + 5 * seg;
+        atomicMin(q, mnx); atomicMin(q + 1, mny); atomicMax(q + 2, mxx); atomicMax(q + 3, mxy); atomicAdd(q + 4, cnt);
+    }
+}
+
+static float from_ordered_bits(uint32_t u) { u = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u; float f; memcpy(&f, &u, 4); return f; }
+
+// compute_exit_pupil_bounds (realisticlens.cpp:1769-1809): fills host.pupil_bounds from the current interfaces
+static int build_exit_pupil(lrt_sensor *s, cudaStream_t stream) {
+    LRT_REQUIRE(s->host.kind == 0 && s->host.n > 0, "exit-pupil sampling needs a lens sensor");
+    const int was = s->host.pupil_mode;
+    s->host.pupil_mode = 0; s->dev_dirty = true;      // the build itself traces plain film -> world rays
+    int rc = s->upload(); if (rc) return rc;
+    uint32_t init[kPupilSegments][5], *d = nullptr;
+    for (auto &r : init) { r[0] = r[1] = 0xffffffffu; r[2] = r[3] = r[4] = 0u; }
+    LRT_CUDA(cudaMalloc(&d, sizeof init));
+    cudaError_t e = cudaMemcpyAsync(d, init, sizeof init, cudaMemcpyHostToDevice, stream);
+    if (e == cudaSuccess) {
+        k_exit_pupil<<<dim3(148, kPupilSegments), 256, 0, stream>>>(s->dev, d);
+        LRT_LAUNCHED();
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(init, d, sizeof init, cudaMemcpyDeviceToHost, stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(stream);
+    cudaFree(d);
+    if (e != cudaSuccess) { s->host.pupil_mode = was; return cuda_fail(e, "exit-pupil LUT"); }
+    const float R = s->host.ifs[0].elem_radius * 1.5f;
+    const float spacing = 4 * R * sqrtf(2.f / (float) (1u << kPupilRaysLog2));   // :1762 (its own TODO notes the extra factor)
+    for (int i = 0; i < kPupilSegments; ++i) {
+        float mn[2] = { -R, -R }, mx[2] = { R, R };                              // zero transmission: the whole sampled square
+        if (init[i][4]) { mn[0] = from_ordered_bits(init[i][0]); mn[1] = from_ordered_bits(init[i][1]);
+                          mx[0] = from_ordered_bits(init[i][2]); mx[1] = from_ordered_bits(init[i][3]); }
+        float *b = s->host.pupil_bounds[i];
+        b[0] = mn[0] - spacing; b[1] = mn[1] - spacing; b[2] = mx[0] + spacing; b[3] = mx[1] + spacing;
+    }
+    s->host.pupil_mode = was; s->dev_dirty = true;
+    return LRT_OK;
 }
 
 static int grid_for(int64_t n, int block) {
@@ -328,7 +404,29 @@ int lrt_sensor_set_interfaces(lrt_sensor *s, int32_t n, const float *rows16) {
     for (int i = 0; i < n; ++i) s->host.ifs[i] = record_from_row(rows16 + 16 * i);
     s->host.n = n; s->host.rear_z = s->host.ifs[0].z; s->host.rear_radius = s->host.ifs[0].elem_radius;
     s->dev_dirty = true;
+    if (s->host.pupil_mode) return build_exit_pupil(s, nullptr);   // the LUT belongs to the interfaces it was traced through
     return LRT_OK;
+}
+// sample_exit_pupil = true|false (realisticlens.cpp:913-921) and the shutter interval the pupil-mode weight is scaled by
+// (Sensor::shutter_open_time(), sensor.h; 0 unless the scene sets shutter_open / shutter_close)
+int lrt_sensor_set_exit_pupil(lrt_sensor *s, int32_t enable, float shutter_open_time, void *stream) {
+    LRT_REQUIRE(s, "null argument");
+    s->host.shutter_open_time = shutter_open_time;
+    s->dev_dirty = true;
+    if (!enable) { s->host.pupil_mode = 0; return LRT_OK; }
+    LRT_NEED_DEVICE();
+    int rc = build_exit_pupil(s, (cudaStream_t) stream); if (rc) return rc;
+    s->host.pupil_mode = 1; s->dev_dirty = true;
+    return LRT_OK;
+}
+int lrt_sensor_get_exit_pupil(const lrt_sensor *s, float *bounds256) {
+    LRT_REQUIRE(s && bounds256, "null argument");
+    LRT_REQUIRE(s->host.pupil_mode, "exit-pupil sampling is not enabled on this sensor");
+    memcpy(bounds256, s->host.pupil_bounds, sizeof s->host.pupil_bounds);
+    return LRT_OK;
+}
+float lrt_radical_inverse(int32_t base_index, uint64_t index) {
+    return (base_index < 0 || base_index > 2) ? -1.f : lrt::radical_inverse(base_index, index);
 }
 int lrt_sensor_set_to_world(lrt_sensor *s, const float *tw) {
     LRT_REQUIRE(s && tw, "null argument");

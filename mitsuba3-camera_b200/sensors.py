@@ -104,8 +104,11 @@ class RealisticLensCamera(Sensor):
         self.near_clip, self.far_clip = float(near_clip), float(far_clip)
         self.to_world = _to_world_array(to_world)
         self.object_distance = float(props.get("object_distance", 6.0))
-        if props.get("sample_exit_pupil", False):
-            raise NotImplementedError("sample_exit_pupil (realisticlens.cpp:1685-1845) is not built yet")
+        # ProjectiveCamera / Sensor: shutter_open, shutter_close (src/render/sensor.cpp:27-33); the pupil-mode weight
+        # is scaled by shutter_open_time() = close - open, which is 0 unless the scene sets them (as in the reference)
+        self._shutter_open = float(props.get("shutter_open", 0.0))
+        self._shutter_open_time = float(props.get("shutter_close", self._shutter_open)) - self._shutter_open
+        self.sample_exit_pupil = bool(props.get("sample_exit_pupil", False))
         d = prescription if prescription is not None else ld.design(lens_design, props)
         self.design = d
         h = C.c_void_p()
@@ -125,9 +128,30 @@ class RealisticLensCamera(Sensor):
                 capi.c_f(self.near_clip), capi.c_f(self.far_clip), C.byref(h))
         capi.check(rc)
         self.handle = h
+        if self.sample_exit_pupil:   # realisticlens.cpp:913-921: build the exit-pupil LUT (a GPU kernel here)
+            capi.check(capi.lib.lrt_sensor_set_exit_pupil(self.handle, C.c_int32(1), capi.c_f(self._shutter_open_time), None))
 
     def needs_aperture_sample(self) -> bool:   # m_needs_sample_3 = true (:840)
         return True
+
+    def shutter_open(self):
+        return self._shutter_open
+
+    def shutter_open_time(self):
+        return self._shutter_open_time
+
+    def set_exit_pupil(self, enable=True, shutter_open_time=None):
+        """Switch `sample_exit_pupil` on an existing sensor (builds the LUT when enabling)."""
+        if shutter_open_time is not None:
+            self._shutter_open_time = float(shutter_open_time)
+        capi.check(capi.lib.lrt_sensor_set_exit_pupil(self.handle, C.c_int32(int(enable)), capi.c_f(self._shutter_open_time), None))
+        self.sample_exit_pupil = bool(enable)
+
+    def exit_pupil_bounds(self) -> np.ndarray:
+        """The 64 x (min.x, min.y, max.x, max.y) LUT of compute_exit_pupil_bounds (realisticlens.cpp:1769-1809), metres."""
+        out = np.zeros((64, 4), f32)
+        capi.check(capi.lib.lrt_sensor_get_exit_pupil(self.handle, capi.fp(out)))
+        return out
 
     def num_interfaces(self) -> int:
         return capi.lib.lrt_sensor_num_interfaces(self.handle)

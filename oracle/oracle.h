@@ -109,6 +109,10 @@ struct Camera {
     float film_z = 0.f, rear_z = 0, rear_radius = 0, film_half_x = 0, film_half_y = 0;
     float normalization = 0, res_x = 0, res_y = 0;
     float focus_delta = 0.f;
+    // exit-pupil sampling (realisticlens.cpp:913-921, 1685-1845): 64 radial segments x (min.x, min.y, max.x, max.y)
+    bool pupil_mode = false; float film_diagonal = 0.f; float pupil_bounds[64][4] = {};
+    void compute_exit_pupil_bounds();
+    V3 sample_exit_pupil(V3 film_p, V2 ap, float &bounds_area) const;
     bool trace_from_film(Ray in, Ray &out) const;
     bool trace_from_world(Ray in, Ray &out) const;
     // returns weight (0 if the ray did not make it through); ray always written
@@ -116,5 +120,6 @@ struct Camera {
 };
 
 bool interact(const Interface &f, const Ray &in, Ray &out);
+float radical_inverse(int base_index, uint64_t index);   // core/qmc.h:68-91, bases 2, 3, 5
 
 }  // namespace orc

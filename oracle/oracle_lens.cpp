@@ -365,6 +365,7 @@ void setup_film(Camera &cam, int w, int h, int cw, int ch, int cx, int cy, float
     float y = aspect * x;
     cam.film_half_x = x / 2; cam.film_half_y = y / 2;
     float px = cam.film_half_x, py = cam.film_half_y;
+    cam.film_diagonal = std::sqrt(px * px + py * py);   // realisticlens.cpp:838 m_film_diagonal = norm(get_physical_size())
     float relx = (float) cw / (float) w, rely = (float) ch / (float) h;
     float offx = (float) cx / (float) w, offy = (float) cy / (float) h;
     // forward: S(1/rel) * T(-off) * S(0.5/phys) * T(phys); inverse composed from the parts' inverses
@@ -411,11 +412,71 @@ static V3 xform_vector(const float *m, V3 v) {    // transform.h:132-140
     return r;
 }
 
-// realisticlens.cpp:2209-2292 (rear-element sampling branch, :1870-1878)
+// RadicalInverse::eval (include/mitsuba/core/qmc.h:68-91), unscrambled; base table as src/core/qmc.cpp:46-52 fills it
+// (recip = 1.f / (float) prime). base_index 0, 1, 2 = primes 2, 3, 5.
+float radical_inverse(int base_index, uint64_t index) {
+    const uint64_t divisor = base_index == 0 ? 2u : (base_index == 1 ? 3u : 5u);
+    const float recip = 1.f / (float) divisor;
+    uint64_t value = 0; float factor = 1.f;
+    while (index != 0) {
+        uint64_t next = index / divisor;
+        factor = factor * recip;
+        value = (value - next) * divisor + index;
+        index = next;
+    }
+    float one_minus_eps; uint32_t u = 0x3f7fffffu; memcpy(&one_minus_eps, &u, 4);
+    return std::min(one_minus_eps, (float) value * factor);
+}
+
+static float lerp(float a, float b, float t) { return fmadd(b, t, fmadd(-a, t, a)); }   // drjit/array_router.h:332
+
+// bound_exit_pupil + compute_exit_pupil_bounds (realisticlens.cpp:1685-1809). The reference walks the 2^20 rays of a
+// segment in order and skips those whose rear-plane point already lies in the box; the box is the min / max over the
+// transmitted points either way, so the rays are simply dealt over threads here.
+void Camera::compute_exit_pupil_bounds() {
+    const size_t num_segments = 64, rays_per_segment = 1024 * 1024;
+    const float R = ifs.front().elem_radius * 1.5f, rz = ifs.front().z;
+    for (size_t seg = 0; seg < num_segments; ++seg) {
+        const float r0 = seg * film_diagonal / num_segments, r1 = (seg + 1) * film_diagonal / num_segments;
+        float mnx = INFINITY, mny = INFINITY, mxx = -INFINITY, mxy = -INFINITY; long transmitted = 0;
+        #pragma omp parallel for reduction(min : mnx, mny) reduction(max : mxx, mxy) reduction(+ : transmitted) schedule(static)
+        for (long i = 0; i < (long) rays_per_segment; ++i) {
+            V3 p_film { lerp(r0, r1, ((size_t) i + 0.5f) / rays_per_segment), 0.f, 0.f };
+            V3 p_rear { lerp(-R, R, radical_inverse(0, (uint64_t) i)), lerp(-R, R, radical_inverse(1, (uint64_t) i)), rz };
+            Ray ray { p_film, normalize(p_rear - p_film) }, ro;
+            if (!trace_from_film(ray, ro)) continue;
+            mnx = std::min(mnx, p_rear.x); mny = std::min(mny, p_rear.y); mxx = std::max(mxx, p_rear.x); mxy = std::max(mxy, p_rear.y);
+            transmitted++;
+        }
+        if (transmitted == 0) { mnx = mny = -R; mxx = mxy = R; }
+        const float spacing = 4 * R * std::sqrt(2.f / rays_per_segment);
+        pupil_bounds[seg][0] = mnx - spacing; pupil_bounds[seg][1] = mny - spacing;
+        pupil_bounds[seg][2] = mxx + spacing; pupil_bounds[seg][3] = mxy + spacing;
+    }
+}
+
+// sample_exit_pupil (realisticlens.cpp:1812-1845)
+V3 Camera::sample_exit_pupil(V3 film_p, V2 ap, float &bounds_area) const {
+    float r_film = std::sqrt(sqr(film_p.x) + sqr(film_p.y));
+    int idx = (int) std::floor(r_film / film_diagonal * 64);
+    idx = std::min(std::max(idx, 0), 63);
+    const float *b = pupil_bounds[idx];
+    bounds_area = (b[2] - b[0]) * (b[3] - b[1]);
+    float px = lerp(b[0], b[2], ap.x), py = lerp(b[1], b[3], ap.y);
+    float sin_t = r_film > 0.f ? film_p.y * rcp(r_film) : 0.f, cos_t = r_film > 0.f ? film_p.x * rcp(r_film) : 1.f;
+    return { cos_t * px - sin_t * py, sin_t * px + cos_t * py, rear_z };
+}
+
+// realisticlens.cpp:2209-2292 (rear-element sampling :1870-1878, or the exit-pupil LUT :1812-1845)
 float Camera::sample_ray(V2 pos, V2 ap, Ray &out) const {
     V3 film_p = xform_point(sample_to_film, { pos.x, pos.y, 0.f });   // w == 1: the /w is exact
-    V2 tmp = square_to_uniform_disk_concentric(ap);
-    V3 aperture_p { rear_radius * tmp.x, rear_radius * tmp.y, rear_z };
+    float bounds_area = 0.f;
+    V3 aperture_p;
+    if (pupil_mode) aperture_p = sample_exit_pupil(film_p, ap, bounds_area);
+    else {
+        V2 tmp = square_to_uniform_disk_concentric(ap);
+        aperture_p = { rear_radius * tmp.x, rear_radius * tmp.y, rear_z };
+    }
     Ray ray { film_p, normalize(aperture_p - film_p) };
     Ray ro; bool active = trace_from_film(ray, ro);
     V3 d_local = ro.d;
@@ -428,7 +489,8 @@ float Camera::sample_ray(V2 pos, V2 ap, Ray &out) const {
     ro.o = { fmadd(ro.d.x, near_t, ro.o.x), fmadd(ro.d.y, near_t, ro.o.y), fmadd(ro.d.z, near_t, ro.o.z) };
     ro.maxt = far_t - near_t;
     float ct = d_local.z, cos4t = sqr(sqr(ct));
-    weight *= cos4t;
+    if (pupil_mode) weight *= shutter_open_time * bounds_area * rcp(sqr(rear_z));   // :2284-2286
+    else weight *= cos4t;
     out = ro;
     return weight;
 }
@@ -523,6 +585,14 @@ void orc_cam_interface(void *h, int i, float *o) {
     if (f.kind == ASPHERE) { o[3] = f.c; o[4] = f.K; o[5] = f.r_scale; for (int k = 0; k < 7; ++k) o[6 + k] = f.ai[k]; }
     o[13] = f.ior_left; o[14] = f.ior_right;
 }
+float orc_radical_inverse(int base_index, uint64_t index) { return radical_inverse(base_index, index); }
+void orc_cam_set_exit_pupil(void *h, int enable, float shutter_open_time) {
+    Camera *c = (Camera *) h;
+    c->shutter_open_time = shutter_open_time;
+    if (enable) c->compute_exit_pupil_bounds();
+    c->pupil_mode = enable != 0;
+}
+void orc_cam_get_exit_pupil(void *h, float *out256) { memcpy(out256, ((Camera *) h)->pupil_bounds, 64 * 4 * sizeof(float)); }
 // out10 = o[3] d[3] maxt weight[3]
 void orc_cam_sample_ray(void *h, int n, const float *pos2, const float *ap2, float *out10) {
     const Camera *c = (const Camera *) h;

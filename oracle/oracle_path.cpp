@@ -464,6 +464,7 @@ void orc_render(void *scene_h, void *cam_h, float fov, const float *to_world16, 
             Ray ray; float weight;
             if (cam) {
                 V2 ap; ap.x = rng.next_float32(); ap.y = rng.next_float32();
+                if (cam->shutter_open_time > 0.f) (void) rng.next_float32();   // the time sample (integrator.cpp:442-444)
                 weight = cam->sample_ray(adjusted, ap, ray);
             } else weight = persp_sample_ray(P, adjusted, ray);
             V3 L { 0, 0, 0 };

@@ -17,7 +17,6 @@
 #include <mitsuba/core/transform.h>
 #include <mitsuba/core/bbox.h>
 #include <mitsuba/core/warp.h>
-#include <mitsuba/core/qmc.h>
 #include <mitsuba/core/random.h>
 #include <mitsuba/core/math.h>
 #include <mitsuba/render/fresnel.h>
@@ -27,6 +26,14 @@
 #include <sstream>
 #include <iostream>
 #include <cstring>
+#include <memory>
+#include <vector>
+
+// RadicalInverse (core/qmc.h) keeps its base table private and builds it in src/core/qmc.cpp, which cannot be linked
+// here; its eval() is header-only. The glue below fills the table exactly as qmc.cpp:46-52 does, hence the access.
+#define private public
+#include <mitsuba/core/qmc.h>
+#undef private
 
 // the glue reads a few private fields of the lens classes for the parameter dump
 #define private public
@@ -36,6 +43,8 @@ NAMESPACE_BEGIN(mitsuba)
 
 // Throw()/Log() outside a class name this global (defined in src/core/class.cpp as nullptr)
 const Class *m_class = nullptr;
+// RadicalInverse::eval()'s Throw() names the class's own m_class (src/core/qmc.cpp, not linked here)
+Class *RadicalInverse::m_class = nullptr;
 // src/core/logger.cpp's detail::Throw formats and throws std::runtime_error; same here
 namespace detail {
 void (Throw)(LogLevel, const Class *, const char *, int, const std::string &msg) {
@@ -91,10 +100,13 @@ struct RefLensCamera {
     // the reference dumps every focus ray to stdout here (realisticlens.cpp:2028-2099); silenced
     void draw_ray_from_world(const Ray3f &) const {}
     void draw_ray_from_film(const Ray3f &) const {}
-    // exit-pupil LUT needs RadicalInverse (src/core/qmc.cpp, not header-only): not built here
-    Point3f sample_exit_pupil(const Point3f, const Point2f, Float &) const { abort(); }
+    // exit-pupil LUT (realisticlens.cpp:2430-2436): the bounds, their flat copies, the Halton generator
+    std::vector<BoundingBox2f> m_exit_pupil_bounds;
+    DynamicBuffer<Float> m_min_bounds_ptr, m_max_bounds_ptr;
+    RadicalInverse *m_qmc_sampler = nullptr;
 
     #include "_ref/ref_builders.inc"     // :936-1683  build_*_lens, build_lens_from_data, trace_ray_from_film
+    #include "_ref/ref_pupil.inc"        // :1685-1845 bound_exit_pupil, compute_exit_pupil_bounds, sample_exit_pupil
     #include "_ref/ref_rear.inc"         // :1870-1878 sample_rear_element
     #include "_ref/ref_trace_world.inc"  // :1960-1984 trace_ray_from_world
     #include "_ref/ref_transforms.inc"   // :2190-2207 update_camera_transforms
@@ -242,6 +254,46 @@ float ref_material_ior(int cauchy, const float *coef, float wavelength_um) {
     using M = DispersiveMaterial<float, Color<float, 3>>;
     if (cauchy) return M("m", coef[0], coef[1]).compute_ior(wavelength_um);
     return M("m", V3(coef[0], coef[1], coef[2]), V3(coef[3], coef[4], coef[5])).compute_ior(wavelength_um);
+}
+// Exit-pupil LUT (realisticlens.cpp:913-921): `m_qmc_sampler = new RadicalInverse()` then compute_exit_pupil_bounds().
+// The generator object is assembled without its constructor (src/core/qmc.cpp is not linkable here): the three prime
+// bases eval() can be asked for (2, 3, 5) are filled as qmc.cpp:46-52 does. Returns 64 x (min.x, min.y, max.x, max.y).
+void ref_cam_compute_exit_pupil(void *h, float *out256) {
+    CoutSilencer quiet;
+    Cam *c = (Cam *) h;
+    if (!c->m_qmc_sampler) {
+        RadicalInverse *q = (RadicalInverse *) ::operator new(sizeof(RadicalInverse));
+        memset((void *) q, 0, sizeof(RadicalInverse));
+        const uint64_t primes[3] = { 2, 3, 5 };
+        auto *base = new RadicalInverse::PrimeBase[3];
+        for (int i = 0; i < 3; ++i) {
+            base[i].value = (uint16_t) primes[i];
+            base[i].recip = 1.f / (float) primes[i];
+            base[i].divisor = dr::divisor<uint64_t>(primes[i]);
+        }
+        new (&q->m_base) std::unique_ptr<RadicalInverse::PrimeBase[]>(base);
+        q->m_base_count = 3;
+        c->m_qmc_sampler = q;
+    }
+    c->m_sample_exit_pupil = true;
+    c->compute_exit_pupil_bounds();
+    for (size_t i = 0; i < c->m_exit_pupil_bounds.size() && i < 64; ++i) {
+        const auto &b = c->m_exit_pupil_bounds[i];
+        out256[4 * i] = b.min.x(); out256[4 * i + 1] = b.min.y(); out256[4 * i + 2] = b.max.x(); out256[4 * i + 3] = b.max.y();
+    }
+}
+float ref_radical_inverse(int base_index, uint64_t index) {
+    static RadicalInverse *q = nullptr;
+    if (!q) {
+        q = (RadicalInverse *) ::operator new(sizeof(RadicalInverse));
+        memset((void *) q, 0, sizeof(RadicalInverse));
+        const uint64_t primes[3] = { 2, 3, 5 };
+        auto *base = new RadicalInverse::PrimeBase[3];
+        for (int i = 0; i < 3; ++i) { base[i].value = (uint16_t) primes[i]; base[i].recip = 1.f / (float) primes[i]; base[i].divisor = dr::divisor<uint64_t>(primes[i]); }
+        new (&q->m_base) std::unique_ptr<RadicalInverse::PrimeBase[]>(base);
+        q->m_base_count = 3;
+    }
+    return q->eval<float>((size_t) base_index, index);
 }
 // Sensor::sample_ray (realisticlens.cpp:2209-2292): out = o[3] d[3] maxt weight[3] per sample
 void ref_cam_sample_ray(void *h, int n, const float *pos2, const float *ap2, float *out10) {

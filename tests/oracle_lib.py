@@ -115,15 +115,31 @@ def orc_camera(design, film: FilmSpec, to_world=EYE, near=1e-2, far=1e4, object_
         c_f(film.diagonal_mm), fp(tw), c_f(near), c_f(far)))
 
 
-def ref_camera(name, film: FilmSpec, to_world=EYE, near=1e-2, far=1e4, props=None):
+def ref_camera(name, film: FilmSpec, to_world=EYE, near=1e-2, far=1e4, props=None, shutter_open_time=0.0):
     L = ref()
     props = props or {}
     names = (C.c_char_p * len(props))(*[k.encode() for k in props])
     vals = (C.c_double * len(props))(*[float(v) for v in props.values()])
     tw = np.ascontiguousarray(to_world, f32)
     h = L.ref_cam_create(name.encode(), C.c_int(film.width), C.c_int(film.height), ip(film.crop),
-                         c_f(film.diagonal_mm), fp(tw), c_f(near), c_f(far), c_f(0.0), C.c_int(len(props)), names, vals)
+                         c_f(film.diagonal_mm), fp(tw), c_f(near), c_f(far), c_f(shutter_open_time), C.c_int(len(props)), names, vals)
     return C.c_void_p(h) if h else None
+
+
+def cam_exit_pupil(L, prefix, h, shutter_open_time=1.0):
+    """Enable exit-pupil sampling on a reference ('ref') or oracle ('orc') camera; returns the 64 x 4 LUT."""
+    out = np.zeros((64, 4), f32)
+    if prefix == "ref":
+        L.ref_cam_compute_exit_pupil(h, fp(out))
+    else:
+        L.orc_cam_set_exit_pupil(h, C.c_int(1), c_f(shutter_open_time))
+        L.orc_cam_get_exit_pupil(h, fp(out))
+    return out
+
+
+def radical_inverse(L, prefix, base_index, indices):
+    f = getattr(L, prefix + "_radical_inverse"); f.restype = c_f
+    return np.array([f(C.c_int(base_index), C.c_uint64(int(i))) for i in indices], f32)
 
 
 def cam_interfaces(L, prefix, h):

@@ -64,3 +64,46 @@ def test_sample_ray_vs_oracle_1m(mi, name):
     act = want[:, 7] > 0
     assert act.sum() > 100
     assert (bits(got[act]) == bits(want[act])).all()
+
+
+# ------------------------------------------------------------------------------------------------ exit-pupil sampling (L7)
+PUPIL_FILMS = {"doublet": dict(width=256, height=256, diagonal=35.0), "gauss": dict(width=256, height=192, crop=(200, 100, 20, 30), diagonal=35.0),
+               "asph": dict(width=128, height=128, diagonal=20.0), "exp1a": dict(width=256, height=256, diagonal=35.0)}
+
+
+def test_radical_inverse_host_entry(mi):
+    g = np.load(os.path.join(ROOT, "tests", "golden", "exit_pupil.npz"))
+    for b in range(3):
+        got = np.array([mi.capi.lib.lrt_radical_inverse(C.c_int32(b), C.c_uint64(int(i))) for i in g["ri.index"][:1500]], f32)
+        assert (bits(got) == bits(g[f"ri.base{b}"][:1500])).all()
+    assert mi.capi.lib.lrt_radical_inverse(C.c_int32(3), C.c_uint64(1)) == -1.0
+
+
+@pytest.mark.parametrize("name", list(PUPIL_FILMS))
+def test_exit_pupil_lut_and_sample_ray_golden(mi, name):
+    """The LUT kernel (64 x 2^20 Halton rays) and sample_ray in pupil mode == the reference's own code, bit for bit."""
+    g = np.load(os.path.join(ROOT, "tests", "golden", "exit_pupil.npz"))
+    s = mi.RealisticLensCamera(mi.Film(**PUPIL_FILMS[name]), name, sample_exit_pupil=True, shutter_open=0.0, shutter_close=1.0)
+    assert s.shutter_open_time() == 1.0
+    assert (bits(s.exit_pupil_bounds()) == bits(g[name + ".bounds"])).all()
+    o, d, maxt, w = s.sample_ray(0.0, 0.0, g[name + ".pos"], g[name + ".ap"])
+    got = np.concatenate([o.numpy(), d.numpy(), maxt.numpy()[:, None], w.numpy()], 1)
+    want = g[name + ".ray"]
+    assert ((got[:, 7] > 0) == (want[:, 7] > 0)).all(), "lens ray-miss mask differs"
+    act = want[:, 7] > 0
+    assert (bits(got[act]) == bits(want[act])).all()
+    # switching the mode off restores rear-element sampling; a new interface table rebuilds the LUT
+    rows = s.interfaces()
+    s.set_interfaces(rows)
+    assert (bits(s.exit_pupil_bounds()) == bits(g[name + ".bounds"])).all()
+    s.set_exit_pupil(False)
+    with pytest.raises(mi.capi.LensrtError):
+        s.exit_pupil_bounds()
+
+
+def test_exit_pupil_default_shutter_is_black(mi):
+    """shutter_open_time() is 0 unless the scene sets shutter_open/close: the reference's pupil-mode weight is then 0."""
+    s = mi.RealisticLensCamera(mi.Film(width=64, height=64), "doublet", sample_exit_pupil=True)
+    rng = np.random.default_rng(3)
+    o, d, maxt, w = s.sample_ray(0.0, 0.0, rng.random((256, 2), dtype=f32), rng.random((256, 2), dtype=f32))
+    assert float(w.abs().max()) == 0.0

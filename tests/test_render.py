@@ -173,6 +173,30 @@ def test_gpu_cornell_through_realistic_lens(mi, design, rfilter):
 
 
 @pytest.mark.gpu
+def test_gpu_cornell_exit_pupil_mode(mi):
+    """sample_exit_pupil = true with an open shutter: LUT-guided aperture sampling, weight shutter * area / z^2, and the
+    extra time draw of render_sample (integrator.cpp:442-444) -- image and miss count vs the oracle in the same mode."""
+    T = mi.Transform4f
+    tw = T.look_at(origin=[0, 0, 3.9], target=[0, 0, 0], up=[0, 1, 0])
+    sensor = {"type": "realisticlens", "lens_design": "gauss", "to_world": tw, "object_distance": 3.9, "near_clip": 1e-3, "far_clip": 100.0,
+              "sample_exit_pupil": True, "shutter_open": 0.0, "shutter_close": 2.0}
+    d = cornell(mi, res=48, spp=8, sensor=sensor)
+    d["sensor"]["film"]["diagonal"] = 30.0
+    d["integrator"]["max_depth"] = 5
+    sc = mi.load_dict(d)
+    img = mi.render(sc, seed=5).cpu().numpy()
+    cam = orc_camera(ld.design("gauss", {"object_distance": 3.9}), FilmSpec(48, 48, None, 30.0), to_world=tw.matrix, near=1e-3, far=100.0,
+                     object_distance=3.9)
+    lut = cam_exit_pupil(oracle(), "orc", cam, shutter_open_time=2.0)
+    assert (bits(sc.sensors()[0].exit_pupil_bounds()) == bits(lut)).all()
+    st, miss = orc_render(orc_scene(sc.arrays), FilmSpec(48, 48, None, 30.0), 8, seed=5, max_depth=5, cam_h=cam, filter_kind=2)
+    want = develop(st)
+    assert sc.stats()["lens_misses"] == miss, "lens ray-miss count differs from the oracle"
+    err = rel_rmse(img, want)
+    assert want.mean() > 1e-6 and err < IMG_TOL, err
+
+
+@pytest.mark.gpu
 def test_gpu_sharding_and_chunking_invariance(mi):
     """Samples keep their PCG32 stream under any tile/chunk/shard split: images agree to float summation order."""
     import torch
