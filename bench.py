@@ -299,6 +299,16 @@ def main():
     if world > 1:
         dist.all_reduce(ms_bwd, op=dist.ReduceOp.MAX)
     lens_grad = None if a.no_lens_grad else lens_grad_section(mi, torch, dist, a, rank, world)
+    pupil = None
+    if rank == 0 and not a.no_lens_grad:   # exit-pupil LUT of the workload's lens: 64 x 2^20 lens traces in one kernel
+        sens = scene.sensors()[0]
+        sens.set_exit_pupil(True, 1.0); torch.cuda.synchronize()      # warm-up
+        t0 = time.perf_counter()
+        sens.set_exit_pupil(True, 1.0)                                # synchronous: kernel + 1.3 KB read-back
+        sec = time.perf_counter() - t0
+        sens.set_exit_pupil(False, 0.0)
+        pupil = {"ms": sec * 1e3, "lens_rays": 64 << 20, "Grays_per_s": (64 << 20) / sec / 1e9,
+                 "what": "lrt_sensor_set_exit_pupil: compute_exit_pupil_bounds of the `%s` lens (host wall clock, synchronous call)" % a.lens}
 
     if rank == 0:
         value = paths_per_step / (ms * 1e-3) / 1e6
@@ -309,6 +319,12 @@ def main():
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
         peak = peaks.get("hbm_gbs", 6546.9)
         ach = alg_bytes / world / (ms * 1e-3) / 1e9
+        traffic, traffic_src = None, None
+        tj = os.path.join(ROOT, "profiles", "render_traffic.json")
+        if os.path.exists(tj):   # dram__bytes_read.sum + dram__bytes_write.sum of one k_render launch, from ncu --set full
+            t = json.load(open(tj))
+            if t.get("spp_per_step") == a.spp_per_step and t.get("width") == a.width and t.get("height") == a.height and world == 1:
+                traffic, traffic_src = t["dram_bytes_per_launch"] / 1e9, t.get("source")
         line = {"metric": "Mpaths/s", "value": value, "unit": "Mpaths/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
                 "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
                 "data": "synthetic", "config": config,
@@ -316,7 +332,9 @@ def main():
                         "d2h_bytes_per_step": int(H * W * 3 * 4), "ms_per_step": ms_e2e},
                 "gpu_launches": int(launches),
                 "clocks": sampler.result(),
-                "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
+                "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": traffic,
+                             "traffic_unit": "GB per launch (ncu dram read+write)", "traffic_source": traffic_src,
+                             "algorithmic_gb_per_launch": alg_bytes / world / 1e9,
                              "kernel": "lrt::k_render", "peak_source": "MEASURED_PEAKS.json hbm_gbs (burst copy)",
                              "note": "algorithmic bytes = nodes*80 + triangles*48 + samples*taps*16 + film; the kernel is "
                                      "latency/issue bound (divergent traversal), see DESIGN.md"},
@@ -327,6 +345,8 @@ def main():
                                            "specular reflectance / area-light radiance (one-pass PRB)"}
         if lens_grad is not None:
             line["lens_grad"] = lens_grad
+        if pupil is not None:
+            line["exit_pupil_lut"] = pupil
         if not a.no_cpu_baseline and world == 1:     # the contract wants the CPU baseline on rank 0 at N = 1 only
             line["cpu_baseline"], _ = cpu_sample(a, scene.arrays, d["sensor"])
             if lens_grad is not None:
