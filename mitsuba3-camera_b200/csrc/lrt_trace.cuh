@@ -101,16 +101,16 @@ LRT_D void trav_node_step(const BvhView &bvh, float3 o, float3 idir, Trav &T, ui
             const uint32_t key = tn <= tf ? ((__float_as_uint(tn) & km) | (uint32_t) c) : 0xffffffffu;
             const uint32_t hi = max(best, key);
             best = min(best, key);
-            st[sp] = make_uint2(xh, hi);   // stored unconditionally, kept only if it is a candidate
-            if (hi != 0xffffffffu) ++sp;
+            // predicated store: an unconditional one costs no instruction less and was measured to fill L1 with
+            // dead stack sectors (78 G local-store sectors per launch, local loads hitting L1 only 45 %)
+            if (hi != 0xffffffffu) { st[sp] = make_uint2(xh, hi); ++sp; }
         }
         xh |= 0x80000000u;
     }
     // nearest of the two rounds continues, the other one is pushed
     const bool first = best0 <= best;
     const uint32_t nearest = first ? best0 : best, other = first ? best : best0;
-    st[sp] = make_uint2(first ? xh : (xh & 0x7fffffffu), other);
-    if (other != 0xffffffffu) ++sp;
+    if (other != 0xffffffffu) { st[sp] = make_uint2(first ? xh : (xh & 0x7fffffffu), other); ++sp; }
     T.cur = nearest != 0xffffffffu ? trav_child_ref(__ldg(np + 1), (nearest & 3u) | (first ? 0u : 4u)) : trav_pop(bvh, sp, st, tmax);
     T.sp = sp;
 }
