@@ -40,7 +40,9 @@ struct alignas(16) LensSystem {
     float s2f_m00, s2f_m03, s2f_m11, s2f_m13;   // sample -> film (diagonal + translation)
     float to_world[12];                         // rows of the affine camera-to-world matrix
     // perspective (src/sensors/perspective.cpp): sample -> camera and image-plane normalisation
-    float persp_s2c[16]; float persp_norm; int pupil_mode; float pad1, pad2;   // pupil_mode: sample_exit_pupil (see pupil_bounds)
+    float persp_s2c[16]; float persp_norm; int pupil_mode;   // pupil_mode: sample_exit_pupil (see pupil_bounds)
+    const float *pupil_lut;   // -> pupil_bounds of the copy that lives in the same address space (host struct: host array, device
+                              //    struct: device array); kernels that stage only the header + n interfaces read the LUT through it
     // film -> sample (diagonal + translation), film-plane normalisation 1/area and crop resolution: what
     // sample_direction needs (realisticlens.cpp:2190-2207,2352-2372)
     float f2s_m00, f2s_m03, f2s_m11, f2s_m13;
@@ -299,7 +301,8 @@ LRT_HD strict::V3 lens_sample_exit_pupil(const LensSystem &L, strict::V3 film_p,
     const float r_film = sqrt(add(sqr(film_p.x), sqr(film_p.y)));
     int idx = (int) floorf(mul(div(r_film, L.film_diagonal), (float) kPupilSegments));
     idx = idx < 0 ? 0 : (idx > kPupilSegments - 1 ? kPupilSegments - 1 : idx);
-    const float minx = L.pupil_bounds[idx][0], miny = L.pupil_bounds[idx][1], maxx = L.pupil_bounds[idx][2], maxy = L.pupil_bounds[idx][3];
+    const float *lut = L.pupil_lut + 4 * idx;
+    const float minx = lut[0], miny = lut[1], maxx = lut[2], maxy = lut[3];
     bounds_area = mul(sub(maxx, minx), sub(maxy, miny));
     const float px = lerp_drjit(minx, maxx, a), py = lerp_drjit(miny, maxy, b);
     const float sin_t = r_film > 0.f ? mul(film_p.y, rcp(r_film)) : 0.f, cos_t = r_film > 0.f ? mul(film_p.x, rcp(r_film)) : 1.f;

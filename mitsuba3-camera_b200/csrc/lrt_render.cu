@@ -16,6 +16,7 @@
 //   * finished samples go to a per-warp splat queue that is drained 32 entries at a time into the shared-memory film
 //     tile (float atomics in shared memory are CAS loops on this architecture: run them at full width, two channels
 //     per 64-bit CAS), and the tile is flushed once per work item with global float atomics.
+#include <cstddef>
 #include "lrt_internal.h"
 #include "lrt_rng.cuh"
 #include "lrt_shade.cuh"
@@ -41,6 +42,7 @@ struct RenderArgs {
     int pad, smem_w, smem_h, exit_drop, leaf_min;
     unsigned long long *counter;
     float *accum;
+    int lens_bytes;                // bytes of the LensSystem staged into shared memory (header + interfaces in use)
     // adjoint (k_render<true>): d(loss)/d(storage) in, parameter gradients out (rows laid out like the scene tables)
     const float *grad_storage; float *grad_bsdfs, *grad_emitters; int n_bsdfs;
     unsigned long long *stats;     // [0] samples, [1] lens misses, [2] rays, [3] bounces, [4] BVH nodes fetched, [5] triangles tested
@@ -88,13 +90,13 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
     const unsigned lt_mask = (1u << lane) - 1u;
     const int tile_elems = A.smem_w * A.smem_h * 4;
     // per-warp private storage: film tile, camera-ray FIFO [word][slot], splat queue [word][slot]
-    float *tile = reinterpret_cast<float *>(smem_raw + sizeof(LensSystem)) + warp * (tile_elems + kFifo * kFifoWords + kQueue * kQueueWords);
+    float *tile = reinterpret_cast<float *>(smem_raw + A.lens_bytes) + warp * (tile_elems + kFifo * kFifoWords + kQueue * kQueueWords);
     float *fifo = tile + tile_elems;
     float *queue = fifo + kFifo * kFifoWords;
     {
         const uint4 *src = reinterpret_cast<const uint4 *>(A.lens);
         uint4 *dst = reinterpret_cast<uint4 *>(&L);
-        for (int i = tid; i < (int) (sizeof(LensSystem) / 16); i += kCtaThreads) dst[i] = src[i];
+        for (int i = tid; i < A.lens_bytes / 16; i += kCtaThreads) dst[i] = src[i];   // header + the n interfaces in use
     }
     const FilmParams &F = A.film;
     const bool box = F.kind == FILTER_BOX;
@@ -436,7 +438,10 @@ int launch_render(const lrt_scene *sc, lrt_sensor *sensor, const lrt_film_desc *
     long long n_tiles = (long long) A.tiles_x * tiles_y;
     long long my_tiles = (n_tiles - rp->shard_index + rp->shard_count - 1) / rp->shard_count;
     int dev = 0, sms = 148; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    size_t smem = sizeof(LensSystem) + (size_t) kWarps * ((size_t) A.smem_w * A.smem_h * 4 + kFifo * kFifoWords + kQueue * kQueueWords) * 4;
+    // only the header and the interfaces in use are staged (not all 32 records, not the exit-pupil LUT): every KB of
+    // shared memory given back is L1 for the traversal
+    A.lens_bytes = (int) ((offsetof(LensSystem, ifs) + (size_t) sensor->host.n * sizeof(LensIf) + 15) / 16 * 16);
+    size_t smem = (size_t) A.lens_bytes + (size_t) kWarps * ((size_t) A.smem_w * A.smem_h * 4 + kFifo * kFifoWords + kQueue * kQueueWords) * 4;
     {   // traversal bursts end when this many 32nds of their lanes have finished (LRT_EXIT_DROP overrides; tuning knob)
         const char *e = getenv("LRT_EXIT_DROP"); A.exit_drop = e ? atoi(e) : 24;
         if (A.exit_drop < 1) A.exit_drop = 1; if (A.exit_drop > 32) A.exit_drop = 32;

@@ -3,6 +3,7 @@
 // Host arithmetic that decides interface positions is float32 and strict (this TU is compiled with
 // -Xcompiler -ffp-contract=off) because every later ray/lens comparison depends on those z's
 // (realisticlens.cpp:1568-1651, :2107-2171).
+#include <cstddef>
 #include "lrt_internal.h"
 #include "lrt_rng.cuh"
 #include <cstring>
@@ -169,6 +170,7 @@ static void set_common(lrt_sensor *s, const lrt_film_geom *film, const float *tw
     s->film = *film;
     for (int i = 0; i < 12; ++i) s->host.to_world[i] = tw[i];
     s->host.near_clip = near_clip; s->host.far_clip = far_clip;
+    s->host.pupil_lut = &s->host.pupil_bounds[0][0];
     setup_film(*s);
 }
 
@@ -176,7 +178,12 @@ static void set_common(lrt_sensor *s, const lrt_film_geom *film, const float *tw
 
 int lrt_sensor::upload() {
     if (!dev) LRT_CUDA(cudaMalloc(&dev, sizeof(lrt::LensSystem)));
-    if (dev_dirty) { LRT_CUDA(cudaMemcpy(dev, &host, sizeof(lrt::LensSystem), cudaMemcpyHostToDevice)); dev_dirty = false; }
+    host.pupil_lut = &host.pupil_bounds[0][0];
+    if (dev_dirty) {
+        lrt::LensSystem tmp = host;   // the device copy's LUT pointer names the device copy's own array
+        tmp.pupil_lut = reinterpret_cast<const float *>(reinterpret_cast<const char *>(dev) + offsetof(lrt::LensSystem, pupil_bounds));
+        LRT_CUDA(cudaMemcpy(dev, &tmp, sizeof(lrt::LensSystem), cudaMemcpyHostToDevice)); dev_dirty = false;
+    }
     return LRT_OK;
 }
 
