@@ -84,7 +84,7 @@ extern "C" {
 int lrt_film_put(const lrt_film_desc *desc, int64_t n, const float *pos2_dev, const float *values_dev, float *accum_dev, void *stream) {
     LRT_NEED_DEVICE();
     FilmParams F; int rc = film_params_from_desc(desc, F); if (rc) return rc;
-    LRT_REQUIRE(pos2_dev && values_dev && accum_dev && n >= 0, "bad argument");
+    LRT_REQUIRE(accum_dev && n >= 0 && (n == 0 || (pos2_dev && values_dev)), "bad argument");
     if (n == 0) return LRT_OK;
     int64_t g = (n + 255) / 256; if (g > 148 * 16) g = 148 * 16;
     k_film_put<<<(int) g, 256, 0, (cudaStream_t) stream>>>(F, n, (const float2 *) pos2_dev, values_dev, accum_dev);

@@ -482,7 +482,7 @@ int launch_render(const lrt_scene *sc, lrt_sensor *sensor, const lrt_film_desc *
 
 extern "C" int lrt_scene_intersect(const lrt_scene *sc, int32_t any_hit, int64_t n, const float *od7_dev, float *out4_dev, void *stream) {
     LRT_NEED_DEVICE();
-    LRT_REQUIRE(sc && od7_dev && out4_dev && n >= 0, "bad argument");
+    LRT_REQUIRE(sc && n >= 0 && (n == 0 || (od7_dev && out4_dev)), "bad argument");   // an empty batch may come with null pointers
     if (n == 0) return LRT_OK;
     int64_t g = (n + 127) / 128; if (g > 148 * 32) g = 148 * 32;
     lrt::k_intersect<<<(int) g, 128, 0, (cudaStream_t) stream>>>(sc->view, any_hit, n, od7_dev, out4_dev);

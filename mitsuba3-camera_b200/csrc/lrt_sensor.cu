@@ -451,7 +451,7 @@ int lrt_sensor_get_info(const lrt_sensor *s, float *s2f16, float *focus_delta, f
 
 int lrt_sensor_sample_ray(const lrt_sensor *s_, int64_t n, const float *pos2, const float *ap2, float *out10, void *stream) {
     LRT_NEED_DEVICE();
-    LRT_REQUIRE(s_ && pos2 && ap2 && out10 && n >= 0, "bad argument");
+    LRT_REQUIRE(s_ && n >= 0 && (n == 0 || (pos2 && ap2 && out10)), "bad argument");
     if (n == 0) return LRT_OK;
     lrt_sensor *s = const_cast<lrt_sensor *>(s_);
     int rc = s->upload(); if (rc) return rc;
@@ -463,7 +463,7 @@ int lrt_sensor_sample_ray(const lrt_sensor *s_, int64_t n, const float *pos2, co
 
 int lrt_sensor_sample_ray_host(const lrt_sensor *s, int64_t n, const float *pos2, const float *ap2, float *out10) {
     LRT_NEED_DEVICE();
-    LRT_REQUIRE(s && pos2 && ap2 && out10 && n >= 0, "bad argument");
+    LRT_REQUIRE(s && n >= 0 && (n == 0 || (pos2 && ap2 && out10)), "bad argument");
     if (n == 0) return LRT_OK;
     float *d = nullptr;
     LRT_CUDA(cudaMalloc(&d, (size_t) n * 14 * sizeof(float)));

@@ -331,7 +331,7 @@ int lrt_spot_render_backward(const lrt_sensor *s, const lrt_film_desc *film, con
 
 int lrt_sensor_sample_direction(const lrt_sensor *s_, int64_t n, const float *p3_dev, const float *s2_dev, float *out11_dev, void *stream) {
     LRT_NEED_DEVICE();
-    LRT_REQUIRE(s_ && p3_dev && s2_dev && out11_dev && n >= 0 && s_->host.kind == 0, "bad argument");
+    LRT_REQUIRE(s_ && n >= 0 && (n == 0 || (p3_dev && s2_dev && out11_dev)) && s_->host.kind == 0, "bad argument");
     if (n == 0) return LRT_OK;
     lrt_sensor *s = const_cast<lrt_sensor *>(s_);
     int rc = s->upload(); if (rc) return rc;

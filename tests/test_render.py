@@ -275,3 +275,57 @@ def test_gpu_render_backward_vs_oracle_finite_differences(mi):
     params.update()
     img1 = mi.render(sc, seed=1, spp=4).cpu().numpy()
     assert rel_rmse(img1, 2 * img0) < 1e-5
+
+
+# ------------------------------------------------------------------------------------------------ edge cases
+@pytest.mark.gpu
+@pytest.mark.parametrize("size,crop,spp", [((37, 19), None, 5), ((70, 33), (41, 17, 13, 9), 3), ((33, 1), None, 16), ((1, 45), None, 2)])
+def test_gpu_ragged_films_and_crops_vs_oracle(mi, size, crop, spp):
+    """Film sizes that are not multiples of the 32-pixel row tile, crop windows with odd offsets, odd sample counts
+    (spp < 4 also switches ImageBlock::put to its non-coalesced branch, integrator.cpp:290)."""
+    w, h = size
+    d = cornell(mi, res=w, spp=spp)
+    d["sensor"]["film"]["height"] = h
+    fs = FilmSpec(w, h, list(crop) if crop else None)
+    if crop:
+        d["sensor"]["film"].update(crop_width=crop[0], crop_height=crop[1], crop_offset_x=crop[2], crop_offset_y=crop[3])
+    d["integrator"]["max_depth"] = 4
+    sc = mi.load_dict(d)
+    img = mi.render(sc, seed=9).cpu().numpy()
+    cw, ch = (crop[0], crop[1]) if crop else (w, h)
+    assert img.shape == (ch, cw, 3)
+    # the Cornell sensor's fov is given along the smaller axis (fov_axis = "smaller"); the oracle takes the x fov
+    st, _ = orc_render(orc_scene(sc.arrays), fs, spp, seed=9, max_depth=4, fov=float(sc.sensors()[0].x_fov),
+                       to_world=d["sensor"]["to_world"].matrix, near=1e-3, far=100.0)
+    want = develop(st)
+    assert sc.stats()["samples"] == cw * ch * spp
+    assert rel_rmse(img, want) < IMG_TOL
+
+
+@pytest.mark.gpu
+def test_gpu_empty_scene_and_empty_batches(mi):
+    """No triangles at all: every path misses, RGB stays 0 and the weight channel still receives the filter weights;
+    zero-length batches of the unit entry points are accepted."""
+    import torch
+    d = {"type": "scene", "integrator": {"type": "path", "max_depth": 4},
+         "sensor": {"type": "realisticlens", "lens_design": "doublet", "film": {"type": "hdrfilm", "width": 40, "height": 24},
+                    "sampler": {"type": "independent", "sample_count": 4}}}
+    sc = mi.load_dict(d)
+    st = mi.render(sc, seed=1, develop=False).cpu().numpy()
+    assert np.all(st[..., :3] == 0) and st[..., 3].sum() > 0
+    stats = sc.stats()
+    assert stats["samples"] == 40 * 24 * 4 and stats["triangles"] == 0
+    s = sc.sensors()[0]
+    o, dd, maxt, w = s.sample_ray(0.0, 0.0, np.zeros((0, 2), f32), np.zeros((0, 2), f32))
+    assert len(o) == 0 and len(w) == 0
+    out = torch.zeros((0, 4), device="cuda")
+    mi.capi.check(mi.capi.lib.lrt_scene_intersect(sc.handle, C.c_int32(0), C.c_int64(0), mi.capi.dev_ptr(out), mi.capi.dev_ptr(out), None))
+
+
+@pytest.mark.gpu
+def test_gpu_wavefront_size_guard(mi):
+    """W*H*spp must fit 32 bits (one PCG32 stream per sample index, integrator.cpp:247-265 splits into passes)."""
+    d = cornell(mi, res=64, spp=1 << 21)
+    sc = mi.load_dict(d)
+    with pytest.raises(mi.capi.LensrtError):
+        mi.render(sc, seed=0)
