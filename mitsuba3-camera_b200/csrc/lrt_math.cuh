@@ -63,8 +63,14 @@ LRT_HD float div(float a, float b) { return a / b; }
 LRT_HD float sqrt(float a) { return ::sqrtf(a); }
 #endif
 LRT_HD float sqr(float a) { return mul(a, a); }
+// 1 / a: the correctly rounded reciprocal IS the correctly rounded quotient 1.f / a, so the shorter __frcp_rn sequence
+// gives the same bits as the division the reference performs (dr::rcp in scalar mode, array_utils.h:212-214)
+#ifdef __CUDA_ARCH__
+LRT_HD float rcp(float a) { return __frcp_rn(a); }
+#else
 LRT_HD float rcp(float a) { return div(1.f, a); }
-LRT_HD float rsqrt(float a) { return div(1.f, sqrt(a)); }
+#endif
+LRT_HD float rsqrt(float a) { return rcp(sqrt(a)); }
 LRT_HD float fmadd(float a, float b, float c) { return add(mul(a, b), c); }    // two roundings
 LRT_HD float fmsub(float a, float b, float c) { return sub(mul(a, b), c); }
 LRT_HD float fnmadd(float a, float b, float c) { return sub(c, mul(a, b)); }
