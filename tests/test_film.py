@@ -3,6 +3,8 @@ test (src/render/tests/test_imageblock.py:37-121, restated here), filters agains
 code of the product against the oracle. GPU: lrt_film_put / develop against the oracle."""
 import ctypes as C
 
+import os
+
 import numpy as np
 import pytest
 
@@ -156,3 +158,14 @@ def test_exr_and_pfm_round_trip(mi, tmp_path):
     assert (mi.imageio.read_pfm(pf) == img).all()
     with pytest.raises(ValueError):
         mi.util.write_bitmap(tmp_path / "img.png", img)
+    # an independent OpenEXR implementation (OpenCV's bundled one), when present, reads the same pixels
+    os.environ["OPENCV_IO_ENABLE_OPENEXR"] = "1"
+    try:
+        import cv2
+    except ImportError:
+        return
+    p3 = tmp_path / "cv.exr"
+    mi.util.write_bitmap(p3, img)
+    a = cv2.imread(str(p3), cv2.IMREAD_UNCHANGED)
+    if a is not None:   # builds without the EXR codec return None
+        assert a.dtype == np.float32 and (a[..., ::-1] == img).all()
