@@ -443,7 +443,7 @@ int launch_render(const lrt_scene *sc, lrt_sensor *sensor, const lrt_film_desc *
     A.lens_bytes = (int) ((offsetof(LensSystem, ifs) + (size_t) sensor->host.n * sizeof(LensIf) + 15) / 16 * 16);
     size_t smem = (size_t) A.lens_bytes + (size_t) kWarps * ((size_t) A.smem_w * A.smem_h * 4 + kFifo * kFifoWords + kQueue * kQueueWords) * 4;
     {   // traversal bursts end when this many 32nds of their lanes have finished (LRT_EXIT_DROP overrides; tuning knob)
-        const char *e = getenv("LRT_EXIT_DROP"); A.exit_drop = e ? atoi(e) : 24;
+        const char *e = getenv("LRT_EXIT_DROP"); A.exit_drop = e ? atoi(e) : 26;
         if (A.exit_drop < 1) A.exit_drop = 1; if (A.exit_drop > 32) A.exit_drop = 32;
         e = getenv("LRT_LEAF_MIN"); A.leaf_min = e ? atoi(e) : 6;
         if (A.leaf_min < 1) A.leaf_min = 1;
