@@ -319,12 +319,14 @@ def main():
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
         peak = peaks.get("hbm_gbs", 6546.9)
         ach = alg_bytes / world / (ms * 1e-3) / 1e9
-        traffic, traffic_src = None, None
+        traffic, traffic_src, ncu_facts = None, None, None
         tj = os.path.join(ROOT, "profiles", "render_traffic.json")
         if os.path.exists(tj):   # dram__bytes_read.sum + dram__bytes_write.sum of one k_render launch, from ncu --set full
             t = json.load(open(tj))
             if t.get("spp_per_step") == a.spp_per_step and t.get("width") == a.width and t.get("height") == a.height and world == 1:
                 traffic, traffic_src = t["dram_bytes_per_launch"] / 1e9, t.get("source")
+                ncu_facts = {k: t[k] for k in ("issue_slot_utilisation", "active_lanes_per_instruction", "l1_hit_rate", "l2_hit_rate",
+                                               "top_stalls_per_issue") if k in t}
         line = {"metric": "Mpaths/s", "value": value, "unit": "Mpaths/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
                 "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
                 "data": "synthetic", "config": config,
@@ -335,6 +337,7 @@ def main():
                 "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": traffic,
                              "traffic_unit": "GB per launch (ncu dram read+write)", "traffic_source": traffic_src,
                              "algorithmic_gb_per_launch": alg_bytes / world / 1e9,
+                             "ncu": ncu_facts,   # what actually bounds the kernel (issue slots / latency), from the same capture
                              "kernel": "lrt::k_render", "peak_source": "MEASURED_PEAKS.json hbm_gbs (burst copy)",
                              "note": "algorithmic bytes = nodes*80 + triangles*48 + samples*taps*16 + film; the kernel is "
                                      "latency/issue bound (divergent traversal), see DESIGN.md"},
