@@ -71,7 +71,7 @@ LRT_D void trav_node_step(const BvhView &bvh, float3 o, float3 idir, Trav &T, ui
     const float tmax = T.tmax;
     work += 1u;
     const uint4 *np = bvh.nodes + 5 * (size_t) T.cur;
-    const uint4 n0 = __ldg(np), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
+    const uint4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
     const float sx = __uint_as_float((n0.w & 0xffu) << 23) * idir.x, sy = __uint_as_float(((n0.w >> 8) & 0xffu) << 23) * idir.y,
                 sz = __uint_as_float(((n0.w >> 16) & 0xffu) << 23) * idir.z;
     const float bx = fmaf(-8388608.f, sx, (__uint_as_float(n0.x) - o.x) * idir.x),
@@ -111,7 +111,7 @@ LRT_D void trav_node_step(const BvhView &bvh, float3 o, float3 idir, Trav &T, ui
     const bool first = best0 <= best;
     const uint32_t nearest = first ? best0 : best, other = first ? best : best0;
     if (other != 0xffffffffu) { st[sp] = make_uint2(first ? xh : (xh & 0x7fffffffu), other); ++sp; }
-    T.cur = nearest != 0xffffffffu ? trav_child_ref(__ldg(np + 1), (nearest & 3u) | (first ? 0u : 4u)) : trav_pop(bvh, sp, st, tmax);
+    T.cur = nearest != 0xffffffffu ? trav_child_ref(n1, (nearest & 3u) | (first ? 0u : 4u)) : trav_pop(bvh, sp, st, tmax);
     T.sp = sp;
 }
 
