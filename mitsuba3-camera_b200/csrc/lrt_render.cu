@@ -102,7 +102,8 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
     const bool box = F.kind == FILTER_BOX;
     const float scale_x = 1.f / (float) F.size_x, scale_y = 1.f / (float) F.size_y;
     const float offs_x = -(float) F.off_x * scale_x, offs_y = -(float) F.off_y * scale_y;
-    unsigned long long n_samples = 0, n_miss = 0, n_rays = 0, n_bounces = 0, n_nodes = 0, n_tris = 0;
+    // per-lane statistics: 32 bits are enough (W*H*spp < 2^32 is spread over the lanes) and leave 6 registers to the traversal
+    unsigned n_samples = 0, n_miss = 0, n_rays = 0, n_bounces = 0, n_nodes = 0, n_tris = 0;
     uint2 st[kTravStack];
     // adjoint state: gradient slots shared by the CTA, per-path records (BSDF id, radiance gathered before the bounce)
     __shared__ float s_grad[kAdj ? kGradSlots : 1];
@@ -387,14 +388,11 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
         }
     }
     if (A.stats) {
-        for (int o = 16; o > 0; o >>= 1) {
-            n_samples += __shfl_down_sync(0xffffffffu, n_samples, o); n_miss += __shfl_down_sync(0xffffffffu, n_miss, o);
-            n_rays += __shfl_down_sync(0xffffffffu, n_rays, o); n_bounces += __shfl_down_sync(0xffffffffu, n_bounces, o);
-            n_nodes += __shfl_down_sync(0xffffffffu, n_nodes, o); n_tris += __shfl_down_sync(0xffffffffu, n_tris, o);
-        }
-        if (lane == 0) {
-            atomicAdd(A.stats, n_samples); atomicAdd(A.stats + 1, n_miss); atomicAdd(A.stats + 2, n_rays); atomicAdd(A.stats + 3, n_bounces);
-            atomicAdd(A.stats + 4, n_nodes); atomicAdd(A.stats + 5, n_tris);
+        unsigned long long c[6] = { n_samples, n_miss, n_rays, n_bounces, n_nodes, n_tris };
+#pragma unroll
+        for (int k = 0; k < 6; ++k) {
+            for (int o = 16; o > 0; o >>= 1) c[k] += __shfl_down_sync(0xffffffffu, c[k], o);
+            if (lane == 0) atomicAdd(A.stats + k, c[k]);
         }
     }
 }
