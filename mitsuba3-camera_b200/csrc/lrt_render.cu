@@ -93,6 +93,9 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
     float *tile = reinterpret_cast<float *>(smem_raw + A.lens_bytes) + warp * (tile_elems + kFifo * kFifoWords + kQueue * kQueueWords);
     float *fifo = tile + tile_elems;
     float *queue = fifo + kFifo * kFifoWords;
+    // per-thread parking slots [word][thread] for path constants that are only needed at shading time (camera weight,
+    // splat position, the PCG32 increment): 5 registers less across the traversal loop
+    float *park = reinterpret_cast<float *>(smem_raw + A.lens_bytes) + kWarps * (tile_elems + kFifo * kFifoWords + kQueue * kQueueWords) + tid;
     {
         const uint4 *src = reinterpret_cast<const uint4 *>(A.lens);
         uint4 *dst = reinterpret_cast<uint4 *>(&L);
@@ -137,11 +140,11 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
 
         // ---- per-lane path state. phase: 0 = idle, 1 = path segment (closest hit), 2 = shadow ray
         int phase = 0;
-        Pcg32 rng; rng.state = 0; rng.inc = 1;
+        uint64_t rng_state = 0;   // the stream's increment is parked, see `park`
         float3 ro = make_float3(0, 0, 0), rd = make_float3(0, 0, 1);                          // ray being traced now
         float3 wi_w = make_float3(0, 0, 1);                                                   // direction of the path segment
         float3 throughput = make_float3(1, 1, 1), result = make_float3(0, 0, 0), prev_p = make_float3(0, 0, 0);
-        float eta = 1.f, prev_pdf = 1.f, cam_weight = 0.f, sx = 0.f, sy = 0.f;
+        float eta = 1.f, prev_pdf = 1.f;
         int depth = 0; bool prev_delta = true, valid_ray = false;
         RayHit seg; seg.t = 0.f; seg.u = seg.v = 0.f; seg.tri = -1;                           // hit of the current segment
         Trav T; trav_init(T, 0.f); T.cur = kTravDone;
@@ -213,9 +216,10 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
                     ro = make_float3(fifo[0 * kFifo + s], fifo[1 * kFifo + s], fifo[2 * kFifo + s]);
                     rd = make_float3(fifo[3 * kFifo + s], fifo[4 * kFifo + s], fifo[5 * kFifo + s]);
                     trav_init(T, fifo[6 * kFifo + s]);
-                    cam_weight = fifo[7 * kFifo + s]; sx = fifo[8 * kFifo + s]; sy = fifo[9 * kFifo + s];
-                    rng.state = (uint64_t) __float_as_uint(fifo[10 * kFifo + s]) | ((uint64_t) __float_as_uint(fifo[11 * kFifo + s]) << 32);
-                    rng.inc = (uint64_t) __float_as_uint(fifo[12 * kFifo + s]) | ((uint64_t) __float_as_uint(fifo[13 * kFifo + s]) << 32);
+                    const float cam_weight = fifo[7 * kFifo + s], sx = fifo[8 * kFifo + s], sy = fifo[9 * kFifo + s];
+                    park[0 * kCtaThreads] = cam_weight; park[1 * kCtaThreads] = sx; park[2 * kCtaThreads] = sy;
+                    park[3 * kCtaThreads] = fifo[12 * kFifo + s]; park[4 * kCtaThreads] = fifo[13 * kFifo + s];
+                    rng_state = (uint64_t) __float_as_uint(fifo[10 * kFifo + s]) | ((uint64_t) __float_as_uint(fifo[11 * kFifo + s]) << 32);
                     phase = 1;
                     throughput = make_float3(1, 1, 1); result = make_float3(0, 0, 0); eta = 1.f; depth = 0;
                     prev_p = make_float3(0, 0, 0); prev_pdf = 1.f; prev_delta = true; valid_ray = false;
@@ -257,6 +261,9 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
                 const RayHit h = T.hit;
                 n_rays++;
                 bool finish = false, occluded = true;
+                Pcg32 rng; rng.state = rng_state;
+                rng.inc = (uint64_t) __float_as_uint(park[3 * kCtaThreads]) | ((uint64_t) __float_as_uint(park[4 * kCtaThreads]) << 32);
+                const float cam_weight = park[0 * kCtaThreads];
                 if (phase == 1) {
                     // ---- first half of one iteration of PathIntegrator::sample's loop (path.cpp:142-208)
                     n_bounces++;
@@ -345,9 +352,10 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
                     bool alive = (!rr_active || rr_sample < rr_prob) && tmax != 0.f;
                     phase = alive ? 1 : 0;
                     if (!alive) { done_path = true; value = result * cam_weight; T.cur = kTravDone; }
+                    rng_state = rng.state;
                 }
             }
-            if (!kAdj) push_splat(done_path, sx, sy, value);
+            if (!kAdj) push_splat(done_path, park[1 * kCtaThreads], park[2 * kCtaThreads], value);
             else if (done_path) {   // suffix of the path behind every recorded bounce, divided by that bounce's reflectance
                 for (int k = 0; k < nrec; ++k) {
                     const int b = __float_as_int(rec[k][0]);
@@ -439,7 +447,7 @@ int launch_render(const lrt_scene *sc, lrt_sensor *sensor, const lrt_film_desc *
     // only the header and the interfaces in use are staged (not all 32 records, not the exit-pupil LUT): every KB of
     // shared memory given back is L1 for the traversal
     A.lens_bytes = (int) ((offsetof(LensSystem, ifs) + (size_t) sensor->host.n * sizeof(LensIf) + 15) / 16 * 16);
-    size_t smem = (size_t) A.lens_bytes + (size_t) kWarps * ((size_t) A.smem_w * A.smem_h * 4 + kFifo * kFifoWords + kQueue * kQueueWords) * 4;
+    size_t smem = (size_t) A.lens_bytes + (size_t) kCtaThreads * 5 * 4 + (size_t) kWarps * ((size_t) A.smem_w * A.smem_h * 4 + kFifo * kFifoWords + kQueue * kQueueWords) * 4;
     {   // traversal bursts end when this many 32nds of their lanes have finished (LRT_EXIT_DROP overrides; tuning knob)
         const char *e = getenv("LRT_EXIT_DROP"); A.exit_drop = e ? atoi(e) : 26;
         if (A.exit_drop < 1) A.exit_drop = 1; if (A.exit_drop > 32) A.exit_drop = 32;
