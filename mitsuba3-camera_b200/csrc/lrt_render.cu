@@ -454,10 +454,12 @@ int launch_render(const lrt_scene *sc, lrt_sensor *sensor, const lrt_film_desc *
         e = getenv("LRT_LEAF_MIN"); A.leaf_min = e ? atoi(e) : 6;
         if (A.leaf_min < 1) A.leaf_min = 1;
     }
+    // wide reconstruction filters make the private film tiles large; beyond the opt-in limit the render is refused
+    LRT_REQUIRE(smem <= 200 * 1024, "reconstruction filter radius too large for the shared-memory film tiles of this build");
     static bool attr_set = false;
     if (!attr_set) {
-        cudaFuncSetAttribute(k_render<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
-        cudaFuncSetAttribute(k_render<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024);
+        cudaFuncSetAttribute(k_render<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        cudaFuncSetAttribute(k_render<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
         attr_set = true;
     }
     const bool adjoint = grad_storage != nullptr;

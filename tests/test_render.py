@@ -329,3 +329,23 @@ def test_gpu_wavefront_size_guard(mi):
     sc = mi.load_dict(d)
     with pytest.raises(mi.capi.LensrtError):
         mi.render(sc, seed=0)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("rf,kind,param", [({"type": "gaussian", "stddev": 0.8}, 2, 0.8), ({"type": "tent", "radius": 3.0}, 1, 3.0)])
+def test_gpu_wide_reconstruction_filters(mi, rf, kind, param):
+    """Filters wider than the defaults (gaussian stddev 0.8 -> radius 3.2, tent radius 3: 7 taps per axis, the build's
+    maximum is 8): the private film tiles grow with the footprint and the image still matches the oracle. Anything
+    wider is refused with an error, not rendered wrongly."""
+    d0 = cornell(mi, res=32, spp=4)
+    d0["sensor"]["film"]["rfilter"] = {"type": "gaussian", "stddev": 1.25}
+    with pytest.raises(mi.capi.LensrtError):
+        mi.render(mi.load_dict(d0), seed=0)
+    d = cornell(mi, res=56, spp=8)
+    d["sensor"]["film"]["rfilter"] = rf
+    d["integrator"]["max_depth"] = 4
+    sc = mi.load_dict(d)
+    img = mi.render(sc, seed=4).cpu().numpy()
+    st, _ = orc_render(orc_scene(sc.arrays), FilmSpec(56, 56), 8, seed=4, max_depth=4, fov=39.3077,
+                       to_world=d["sensor"]["to_world"].matrix, near=1e-3, far=100.0, filter_kind=kind, filter_param=param)
+    assert rel_rmse(img, develop(st)) < IMG_TOL
