@@ -24,6 +24,8 @@ int film_params_from_desc(const lrt_film_desc *d, FilmParams &F) {
     LRT_REQUIRE(d, "null film descriptor");
     LRT_REQUIRE(d->size_x > 0 && d->size_y > 0 && d->channels > 0 && d->channels <= 8 && d->border >= 0, "bad film size");
     LRT_REQUIRE(d->filter >= 0 && d->filter <= 2, "filter must be box(0) / tent(1) / gaussian(2)");
+    // ImageBlock's border is the filter's border_size(): 0 for the box filter (imageblock.cpp:24-29)
+    LRT_REQUIRE(d->filter != 0 || d->border == 0, "a box-filtered block has no border");
     memset(&F, 0, sizeof F);
     F.size_x = d->size_x; F.size_y = d->size_y; F.off_x = d->off_x; F.off_y = d->off_y; F.border = d->border;
     F.channels = d->channels; F.kind = d->filter; F.coalesce = d->coalesce; F.normalize = d->normalize;
@@ -47,7 +49,6 @@ int film_params_from_desc(const lrt_film_desc *d, FilmParams &F) {
 __global__ void __launch_bounds__(256) k_film_put(FilmParams F, int64_t n, const float2 *__restrict__ pos,
                                                    const float *__restrict__ values, float *__restrict__ accum) {
     int sx = F.size_x + 2 * F.border, sy = F.size_y + 2 * F.border;
-    if (F.kind == FILTER_BOX) sx = F.size_x;
     for (int64_t i = blockIdx.x * (int64_t) blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) {
         float2 p = pos[i];
         Footprint fp;

@@ -44,5 +44,8 @@ struct lrt_sensor {
     float sample_to_film[16];
     float film_to_sample[16];
     float normalization = 0.f;
-    int upload();                    // host -> dev if dirty
+    lrt::LensSystem *staging = nullptr;   // pinned copy the asynchronous upload reads from
+    cudaEvent_t staged = nullptr;         // completion of the last upload (the staging copy is reused after it)
+    // host -> dev if dirty, ordered on `stream` (renders launched earlier on that stream keep reading the old table)
+    int upload(cudaStream_t stream = nullptr);
 };

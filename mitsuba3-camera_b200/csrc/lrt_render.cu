@@ -17,6 +17,7 @@
 //     tile (float atomics in shared memory are CAS loops on this architecture: run them at full width, two channels
 //     per 64-bit CAS), and the tile is flushed once per work item with global float atomics.
 #include <cstddef>
+#include <mutex>
 #include "lrt_internal.h"
 #include "lrt_rng.cuh"
 #include "lrt_shade.cuh"
@@ -63,8 +64,7 @@ LRT_D void atomic_add2_shared(float *p, float a, float b) {
 LRT_D void splat_to_tile(const FilmParams &F, float *tile, int smem_w, int ox, int oy, float sx, float sy, float3 value) {
     Footprint fp;
     if (!film_footprint(F, sx, sy, fp)) return;
-    const bool box = F.kind == FILTER_BOX;
-    const int sw = box ? F.size_x : F.size_x + 2 * F.border, shh = F.size_y + 2 * F.border;
+    const int sw = F.size_x + 2 * F.border, shh = F.size_y + 2 * F.border;   // (box filters have no border)
     for (int iy = 0; iy < fp.ny; ++iy) {
         const int y = fp.y0 + iy;
         if ((unsigned) y >= (unsigned) shh) continue;
@@ -131,7 +131,7 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
         const int tx = (int) (tile_id % A.tiles_x), ty = (int) (tile_id / A.tiles_x);
         const int px = tx * kTileW + lane, py = ty;                      // the pixel this lane GENERATES samples for
         const bool in_film = px < F.size_x && py < F.size_y;
-        const int ox = tx * kTileW - A.pad, oy = ty * kTileH - A.pad;    // tensor coords of smem (0,0)
+        const int ox = tx * kTileW + F.border - A.pad, oy = ty * kTileH + F.border - A.pad;   // tensor coords of smem (0,0)
         const int j0 = chunk * A.chunk_spp;
         const int n_rounds = py < F.size_y ? max(0, min(A.spp, j0 + A.chunk_spp) - j0) : 0;   // generation rounds of this warp
         const uint32_t idx_base = (uint32_t) (py * F.size_x + px) * (uint32_t) A.spp;
@@ -174,7 +174,7 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
         bool exhausted = false;   // no lane active, no camera ray left: only the queue remains to be drained
         while (true) {
             // the only drain site (splat_to_tile is ~500 instructions; inlining it four times cost instruction-cache misses)
-            if (q_count >= 32 || (exhausted && q_count > 0)) drain(min(q_count, 32));
+            while (q_count >= 32 || (exhausted && q_count > 0)) drain(min(q_count, 32));   // leaves < 32 entries: 32 + 32 more fit
             if (exhausted) { if (q_count == 0) break; continue; }
             // ---- A. camera rays, 32 at a time: render_sample() draws in the reference's order (integrator.cpp:435-448)
             if (fifo_count < 32 && round < n_rounds) {
@@ -227,7 +227,7 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
                         nrec = 0; dL = make_float3(0, 0, 0);
                         Footprint fp;
                         if (film_footprint(F, sx, sy, fp)) {
-                            const int sw = box ? F.size_x : F.size_x + 2 * F.border, shh = F.size_y + 2 * F.border;
+                            const int sw = F.size_x + 2 * F.border, shh = F.size_y + 2 * F.border;
                             for (int iy = 0; iy < fp.ny; ++iy) {
                                 const int y = fp.y0 + iy;
                                 if ((unsigned) y >= (unsigned) shh) continue;
@@ -431,7 +431,7 @@ int launch_render(const lrt_scene *sc, lrt_sensor *sensor, const lrt_film_desc *
     LRT_REQUIRE(rp->spp > 0 && rp->max_depth >= -1 && rp->shard_count >= 1 && rp->shard_index >= 0 && rp->shard_index < rp->shard_count, "bad render parameters");
     // one PCG32 stream per sample: the wavefront must fit 32 bits (integrator.cpp:247-265 splits into passes)
     LRT_REQUIRE((double) film->size_x * film->size_y * rp->spp < 4294967296.0, "W*H*spp exceeds 2^32: render in passes");
-    rc = sensor->upload(); if (rc) return rc;
+    rc = sensor->upload(stream); if (rc) return rc;
     A.sc = sc->view; A.lens = sensor->dev;
     A.seed = rp->seed; A.spp = rp->spp; A.max_depth = rp->max_depth < 0 ? 0x7fffffff : rp->max_depth; A.rr_depth = rp->rr_depth;
     A.film.coalesce = rp->spp >= 4 ? film->coalesce : 0;   // integrator.cpp:290
@@ -456,11 +456,14 @@ int launch_render(const lrt_scene *sc, lrt_sensor *sensor, const lrt_film_desc *
     }
     // wide reconstruction filters make the private film tiles large; beyond the opt-in limit the render is refused
     LRT_REQUIRE(smem <= 200 * 1024, "reconstruction filter radius too large for the shared-memory film tiles of this build");
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaFuncSetAttribute(k_render<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-        cudaFuncSetAttribute(k_render<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-        attr_set = true;
+    {   // the shared-memory opt-in is a per-device function attribute
+        static std::mutex mu; static bool attr_set[64] = {};
+        std::lock_guard<std::mutex> lock(mu);
+        if (dev >= 64 || !attr_set[dev]) {
+            LRT_CUDA(cudaFuncSetAttribute(k_render<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+            LRT_CUDA(cudaFuncSetAttribute(k_render<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+            if (dev < 64) attr_set[dev] = true;
+        }
     }
     const bool adjoint = grad_storage != nullptr;
     A.grad_storage = grad_storage; A.grad_bsdfs = grad_bsdfs; A.grad_emitters = grad_emitters; A.n_bsdfs = sc->n_bsdfs;
@@ -475,8 +478,12 @@ int launch_render(const lrt_scene *sc, lrt_sensor *sensor, const lrt_film_desc *
     if (rp->chunks > 0) n_chunks = std::min(rp->chunks, rp->spp);
     A.n_chunks = n_chunks; A.chunk_spp = (rp->spp + n_chunks - 1) / n_chunks;
     A.shard_index = rp->shard_index; A.shard_count = rp->shard_count; A.n_items = my_tiles * n_chunks;
-    A.counter = sc->d_counter; A.stats = sc->d_counter + 1; A.accum = accum_dev;
-    LRT_CUDA(cudaMemsetAsync(sc->d_counter, 0, 8 * sizeof(unsigned long long), stream));
+    // every launch takes its own work counter from a ring (renders of one scene may overlap on different streams); the
+    // statistics block is per scene: it describes the last render launched and is meaningless while two overlap
+    unsigned long long *ctr = sc->d_counter + (sc->launch_seq.fetch_add(1, std::memory_order_relaxed) % kCounterRing);
+    A.counter = ctr; A.stats = sc->d_counter + kCounterRing; A.accum = accum_dev;
+    LRT_CUDA(cudaMemsetAsync(ctr, 0, sizeof(unsigned long long), stream));
+    LRT_CUDA(cudaMemsetAsync(A.stats, 0, 8 * sizeof(unsigned long long), stream));
     long long grid = std::min(resident, (A.n_items + kWarps - 1) / kWarps);
     if (grid < 1) return LRT_OK;
     if (adjoint) k_render<true><<<(int) grid, kCtaThreads, smem, stream>>>(A);

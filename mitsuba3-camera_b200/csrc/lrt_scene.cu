@@ -61,7 +61,7 @@ int lrt_scene_create(const lrt_scene_desc *d, lrt_scene **out) {
         (rc = upload(&s->d_bsdfs, d->bsdfs, (size_t) d->n_bsdfs * 16)) || (rc = upload(&s->d_emitters, em.data(), em.size()))) {
         lrt_scene_destroy(s); return rc;
     }
-    if (cudaMalloc(&s->d_counter, 8 * sizeof(unsigned long long)) != cudaSuccess) { lrt_scene_destroy(s); return cuda_fail(cudaGetLastError(), "cudaMalloc"); }
+    if (cudaMalloc(&s->d_counter, (kCounterRing + 8) * sizeof(unsigned long long)) != cudaSuccess) { lrt_scene_destroy(s); return cuda_fail(cudaGetLastError(), "cudaMalloc"); }
     s->view.bvh.nodes = (const uint4 *) s->d_nodes; s->view.bvh.tris = (const float4 *) s->d_tris;
     s->view.bvh.kb = 0x4B000000u; s->view.bvh.km = 0xfffffff8u;
     s->view.shape_bsdf = (const int *) s->d_shape_bsdf; s->view.shape_emitter = (const int *) s->d_shape_emitter;
@@ -116,7 +116,7 @@ int lrt_render_backward(const lrt_scene *sc, const lrt_sensor *sensor, const lrt
 int lrt_render_stats(const lrt_scene *sc, uint64_t *out6) {
     LRT_NEED_DEVICE();
     LRT_REQUIRE(sc && out6, "null argument");
-    LRT_CUDA(cudaMemcpy(out6, sc->d_counter + 1, 6 * sizeof(uint64_t), cudaMemcpyDeviceToHost));
+    LRT_CUDA(cudaMemcpy(out6, sc->d_counter + kCounterRing, 6 * sizeof(uint64_t), cudaMemcpyDeviceToHost));
     return LRT_OK;
 }
 

@@ -176,13 +176,20 @@ static void set_common(lrt_sensor *s, const lrt_film_geom *film, const float *tw
 
 }  // namespace lrt
 
-int lrt_sensor::upload() {
+int lrt_sensor::upload(cudaStream_t stream) {
     if (!dev) LRT_CUDA(cudaMalloc(&dev, sizeof(lrt::LensSystem)));
+    if (!staging) {
+        LRT_CUDA(cudaMallocHost(&staging, sizeof(lrt::LensSystem)));
+        LRT_CUDA(cudaEventCreateWithFlags(&staged, cudaEventDisableTiming));
+    }
     host.pupil_lut = &host.pupil_bounds[0][0];
     if (dev_dirty) {
-        lrt::LensSystem tmp = host;   // the device copy's LUT pointer names the device copy's own array
-        tmp.pupil_lut = reinterpret_cast<const float *>(reinterpret_cast<const char *>(dev) + offsetof(lrt::LensSystem, pupil_bounds));
-        LRT_CUDA(cudaMemcpy(dev, &tmp, sizeof(lrt::LensSystem), cudaMemcpyHostToDevice)); dev_dirty = false;
+        LRT_CUDA(cudaEventSynchronize(staged));   // the previous upload has consumed the staging copy (no-op if none)
+        *staging = host;   // the device copy's LUT pointer names the device copy's own array
+        staging->pupil_lut = reinterpret_cast<const float *>(reinterpret_cast<const char *>(dev) + offsetof(lrt::LensSystem, pupil_bounds));
+        LRT_CUDA(cudaMemcpyAsync(dev, staging, sizeof(lrt::LensSystem), cudaMemcpyHostToDevice, stream));
+        LRT_CUDA(cudaEventRecord(staged, stream));
+        dev_dirty = false;
     }
     return LRT_OK;
 }
@@ -264,7 +271,7 @@ static int build_exit_pupil(lrt_sensor *s, cudaStream_t stream) {
     LRT_REQUIRE(s->host.kind == 0 && s->host.n > 0, "exit-pupil sampling needs a lens sensor");
     const int was = s->host.pupil_mode;
     s->host.pupil_mode = 0; s->dev_dirty = true;      // the build itself traces plain film -> world rays
-    int rc = s->upload(); if (rc) return rc;
+    int rc = s->upload(stream); if (rc) return rc;
     uint32_t init[kPupilSegments][5], *d = nullptr;
     for (auto &r : init) { r[0] = r[1] = 0xffffffffu; r[2] = r[3] = r[4] = 0u; }
     LRT_CUDA(cudaMalloc(&d, sizeof init));
@@ -398,6 +405,8 @@ int lrt_sensor_create_perspective(float x_fov_deg, const lrt_film_geom *film, co
 void lrt_sensor_destroy(lrt_sensor *s) {
     if (!s) return;
     if (s->dev) cudaFree(s->dev);
+    if (s->staging) cudaFreeHost(s->staging);
+    if (s->staged) cudaEventDestroy(s->staged);
     delete s;
 }
 int lrt_sensor_num_interfaces(const lrt_sensor *s) { return s ? s->host.n : 0; }
@@ -454,7 +463,7 @@ int lrt_sensor_sample_ray(const lrt_sensor *s_, int64_t n, const float *pos2, co
     LRT_REQUIRE(s_ && n >= 0 && (n == 0 || (pos2 && ap2 && out10)), "bad argument");
     if (n == 0) return LRT_OK;
     lrt_sensor *s = const_cast<lrt_sensor *>(s_);
-    int rc = s->upload(); if (rc) return rc;
+    int rc = s->upload((cudaStream_t) stream); if (rc) return rc;
     k_sample_ray<<<grid_for(n, 256), 256, 0, (cudaStream_t) stream>>>(s->dev, n, (const float2 *) pos2, (const float2 *) ap2, out10);
     LRT_LAUNCHED();
     LRT_CUDA(cudaGetLastError());

@@ -270,7 +270,7 @@ static int spot_launch(lrt_sensor *s, const lrt_film_desc *film, const lrt_spot_
     LRT_REQUIRE(sp->spp > 0 && sp->shard_count >= 1 && sp->shard_index >= 0 && sp->shard_index < sp->shard_count, "bad spot parameters");
     const double n_total = (double) film->size_x * film->size_y * sp->spp;
     LRT_REQUIRE(n_total < 4294967296.0, "W*H*spp exceeds 2^32: render in passes");
-    rc = s->upload(); if (rc) return rc;
+    rc = s->upload(stream); if (rc) return rc;
     A.lens = s->dev; A.seed = sp->seed; A.spp = sp->spp;
     for (int k = 0; k < 3; ++k) { A.src[k] = sp->src_p[k]; A.intensity[k] = sp->intensity[k]; }
     A.origin_offset = sp->origin_offset;
@@ -334,7 +334,7 @@ int lrt_sensor_sample_direction(const lrt_sensor *s_, int64_t n, const float *p3
     LRT_REQUIRE(s_ && n >= 0 && (n == 0 || (p3_dev && s2_dev && out11_dev)) && s_->host.kind == 0, "bad argument");
     if (n == 0) return LRT_OK;
     lrt_sensor *s = const_cast<lrt_sensor *>(s_);
-    int rc = s->upload(); if (rc) return rc;
+    int rc = s->upload((cudaStream_t) stream); if (rc) return rc;
     int64_t g = (n + 255) / 256; if (g > 148 * 16) g = 148 * 16;
     k_sample_direction<<<(int) g, 256, 0, (cudaStream_t) stream>>>(s->dev, n, p3_dev, (const float2 *) s2_dev, out11_dev);
     LRT_LAUNCHED();
