@@ -141,12 +141,21 @@ int lrt_filter_eval_host(int32_t filter, float param, int32_t n, const float *x,
 
 /* ------------------------------------------------------------------------------------------------ scene
  * Flat scene description (what mi.load_dict assembles from `rectangle` / `cube` / mesh shapes, `diffuse` /
- * `conductor` / `dielectric` (+`twosided`) BSDFs and `area` emitters). All geometry is triangles;
+ * `conductor` / `dielectric` (+`twosided`) BSDFs, `bitmap` textures and `area` emitters). All geometry is triangles;
  * area emitters sit on rectangles (centre + two half-edge vectors, src/shapes/rectangle.cpp:115-185).
  *   bsdfs   [n_bsdfs,16]   : type (0 diffuse, 1 conductor, 2 dielectric), twosided, reflectance rgb (diffuse)
  *                            or specular_reflectance rgb, eta rgb, k rgb (conductor), specular_transmittance
- *                            rgb, eta = int_ior/ext_ior (dielectric), pad
- *   emitters[n_emitters,16]: radiance rgb, shape id, centre xyz, half-edge u xyz, half-edge v xyz, pad */
+ *                            rgb, eta = int_ior/ext_ior (dielectric), texture id + 1 of a diffuse `reflectance`
+ *                            bitmap (0 = the constant rgb)
+ *   emitters[n_emitters,16]: radiance rgb, shape id, centre xyz, half-edge u xyz, half-edge v xyz, pad
+ * BitmapTexture (src/textures/bitmap.cpp:115-310): RGB float texels (already linear), bilinear filter. */
+typedef struct lrt_texture_desc {
+    int32_t width, height;
+    int32_t wrap;              /* wrap_mode: 0 repeat, 1 mirror, 2 clamp */
+    const float *rgb;          /* [height, width, 3] host memory */
+    float to_uv[6];            /* first two rows of the 3x3 `to_uv` transform (identity: 1 0 0 / 0 1 0) */
+} lrt_texture_desc;
+
 typedef struct lrt_scene_desc {
     int32_t n_vertices; const float *vertices;       /* [n_vertices,3] world space */
     int64_t n_triangles; const int32_t *indices;     /* [n_triangles,3] */
@@ -155,6 +164,12 @@ typedef struct lrt_scene_desc {
     const int32_t *shape_emitter;                    /* [n_shapes], -1 = not an emitter */
     int32_t n_bsdfs; const float *bsdfs;
     int32_t n_emitters; const float *emitters;
+    /* Mesh vertex attributes (src/render/mesh.cpp:1448-1500), all optional (NULL): shape_flags[s] bit 0 = the vertices of
+     * shape s carry normals (interpolated shading normal), bit 1 = texture coordinates (si.uv and dp_du). */
+    const float *vertex_normals;                     /* [n_vertices,3] */
+    const float *vertex_uvs;                         /* [n_vertices,2] */
+    const int32_t *shape_flags;                      /* [n_shapes] */
+    int32_t n_textures; const lrt_texture_desc *textures;
 } lrt_scene_desc;
 
 /* Scene::Scene (src/render/scene.cpp:22-96): builds the acceleration structure (8-wide quantised BVH, on the

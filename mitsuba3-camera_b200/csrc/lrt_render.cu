@@ -276,7 +276,7 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
                         const int em = __ldg(A.sc.shape_emitter + si.shape);
                         if (em >= 0) {     // direct emission, MIS against the previous bounce's BSDF sample (:158-174)
                             float3 rel = si.p - prev_p; float dist = sqrtf(dot(rel, rel)); float3 dd = rel * (1.f / dist);
-                            float em_pdf = prev_delta ? 0.f : pdf_emitter_direction(A.sc, em, dd, dist, si.n);
+                            float em_pdf = prev_delta ? 0.f : pdf_emitter_direction(A.sc, em, dd, dist, si.sn);
                             if (si.wi.z > 0.f && prev_pdf > 0.f) {
                                 float4 e0 = __ldg(A.sc.emitters + 5 * (size_t) em);
                                 const float mw = mis_weight(prev_pdf, em_pdf);
@@ -320,10 +320,10 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
                     EmitterSample es; es.pdf = 0.f; float3 wo = make_float3(0, 0, 0);
                     const bool active_em = phase == 2 && !occluded;
                     if (active_em) { es = sample_emitter_direction(A.sc, si.p, e_sx, e_sy); wo = si.to_local(es.d); }
-                    BsdfResult bs = bsdf_eval_pdf_sample(A.sc, bsdf_id, si.wi, wo, s1, s2x, s2y);
+                    BsdfResult bs = bsdf_eval_pdf_sample(A.sc, bsdf_id, si.uv, si.wi, wo, s1, s2x, s2y);
                     if (kAdj) {   // everything gathered from here on is linear in this surface's (specular) reflectance
                         const int btype = (int) __ldg(reinterpret_cast<const float *>(A.sc.bsdfs) + 16 * (size_t) bsdf_id);
-                        if (nrec < kMaxRec && btype != BSDF_DIELECTRIC) {
+                        if (nrec < kMaxRec && btype != BSDF_DIELECTRIC && __ldg(reinterpret_cast<const float *>(A.sc.bsdfs) + 16 * (size_t) bsdf_id + 15) == 0.f) {   // (textured reflectances are not parameters)
                             rec[nrec][0] = __int_as_float(bsdf_id); rec[nrec][1] = result.x; rec[nrec][2] = result.y; rec[nrec][3] = result.z; nrec++;
                         }
                     }

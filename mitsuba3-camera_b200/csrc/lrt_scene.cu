@@ -34,9 +34,36 @@ int lrt_scene_create(const lrt_scene_desc *d, lrt_scene **out) {
         LRT_REQUIRE(d->shape_bsdf[s] >= 0 && d->shape_bsdf[s] < d->n_bsdfs, "shape_bsdf out of range");
         LRT_REQUIRE(d->shape_emitter[s] >= -1 && d->shape_emitter[s] < d->n_emitters, "shape_emitter out of range");
     }
+    LRT_REQUIRE(d->n_textures >= 0 && (d->n_textures == 0 || d->textures), "bad texture table");
+    for (int t = 0; t < d->n_textures; ++t)
+        LRT_REQUIRE(d->textures[t].width > 0 && d->textures[t].height > 0 && d->textures[t].rgb && d->textures[t].wrap >= 0 && d->textures[t].wrap <= 2,
+                    "bad texture");
+    for (int b = 0; b < d->n_bsdfs; ++b) {
+        const float tid = d->bsdfs[16 * b + 15];
+        LRT_REQUIRE(tid >= 0.f && tid <= (float) d->n_textures && tid == (float) (int) tid, "bsdf texture id out of range");
+    }
     auto t0 = std::chrono::steady_clock::now();
     std::vector<BvhNode> nodes; std::vector<BvhTri> tris; BvhBuildStats st;
     build_bvh8(d->vertices, d->indices, d->tri_shape, d->n_triangles, nodes, tris, &st);
+    // per-triangle vertex attributes in BVH order; the triangle record's pad word carries the flags
+    std::vector<float> attr;
+    if (d->shape_flags && (d->vertex_normals || d->vertex_uvs)) {
+        bool any = false;
+        for (size_t i = 0; i < tris.size(); ++i) {
+            int fl = d->shape_flags[tris[i].shape] & ((d->vertex_normals ? 1 : 0) | (d->vertex_uvs ? 2 : 0));
+            memcpy(&tris[i].pad, &fl, 4);
+            any = any || fl != 0;
+        }
+        if (any) {
+            attr.assign(tris.size() * 16, 0.f);
+            for (size_t i = 0; i < tris.size(); ++i) {
+                int fl; memcpy(&fl, &tris[i].pad, 4);
+                const int32_t *f = d->indices + 3 * (size_t) tris[i].prim; float *o = attr.data() + 16 * i;
+                if (fl & 1) for (int k = 0; k < 3; ++k) for (int a = 0; a < 3; ++a) o[3 * k + a] = d->vertex_normals[3 * (size_t) f[k] + a];
+                if (fl & 2) for (int k = 0; k < 3; ++k) for (int a = 0; a < 2; ++a) o[9 + 2 * k + a] = d->vertex_uvs[2 * (size_t) f[k] + a];
+            }
+        }
+    }
     lrt_scene *s = new lrt_scene();
     s->build_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     s->n_nodes = (int64_t) nodes.size(); s->n_tris = (int64_t) tris.size(); s->bvh_depth = st.max_depth;
@@ -61,12 +88,30 @@ int lrt_scene_create(const lrt_scene_desc *d, lrt_scene **out) {
         (rc = upload(&s->d_bsdfs, d->bsdfs, (size_t) d->n_bsdfs * 16)) || (rc = upload(&s->d_emitters, em.data(), em.size()))) {
         lrt_scene_destroy(s); return rc;
     }
+    if (!attr.empty() && (rc = upload(&s->d_tri_attr, attr.data(), attr.size()))) { lrt_scene_destroy(s); return rc; }
+    if (d->n_textures) {
+        size_t total = 0;
+        for (int t = 0; t < d->n_textures; ++t) total += (size_t) d->textures[t].width * d->textures[t].height * 3;
+        std::vector<float> texels; texels.reserve(total);
+        for (int t = 0; t < d->n_textures; ++t) texels.insert(texels.end(), d->textures[t].rgb, d->textures[t].rgb + (size_t) d->textures[t].width * d->textures[t].height * 3);
+        if ((rc = upload(&s->d_tex_data, texels.data(), texels.size()))) { lrt_scene_destroy(s); return rc; }
+        std::vector<TexView> tv(d->n_textures); size_t off = 0;
+        for (int t = 0; t < d->n_textures; ++t) {
+            tv[t].data = (const float *) s->d_tex_data + off; tv[t].w = d->textures[t].width; tv[t].h = d->textures[t].height;
+            tv[t].wrap = d->textures[t].wrap; tv[t].pad = 0;
+            for (int k = 0; k < 6; ++k) tv[t].to_uv[k] = d->textures[t].to_uv[k];
+            off += (size_t) tv[t].w * tv[t].h * 3;
+        }
+        if ((rc = upload(&s->d_textures, tv.data(), tv.size()))) { lrt_scene_destroy(s); return rc; }
+        s->n_textures = d->n_textures;
+    }
     if (cudaMalloc(&s->d_counter, (kCounterRing + 8) * sizeof(unsigned long long)) != cudaSuccess) { lrt_scene_destroy(s); return cuda_fail(cudaGetLastError(), "cudaMalloc"); }
     s->view.bvh.nodes = (const uint4 *) s->d_nodes; s->view.bvh.tris = (const float4 *) s->d_tris;
     s->view.bvh.kb = 0x4B000000u; s->view.bvh.km = 0xfffffff8u;
     s->view.shape_bsdf = (const int *) s->d_shape_bsdf; s->view.shape_emitter = (const int *) s->d_shape_emitter;
     s->view.bsdfs = (const float4 *) s->d_bsdfs; s->view.emitters = (const float4 *) s->d_emitters;
     s->view.n_emitters = d->n_emitters;
+    s->view.tri_attr = (const float4 *) s->d_tri_attr; s->view.textures = (const TexView *) s->d_textures;
     *out = s;
     return LRT_OK;
 }
@@ -84,7 +129,8 @@ int lrt_scene_set_params(lrt_scene *s, const float *bsdfs, const float *emitter_
 
 void lrt_scene_destroy(lrt_scene *s) {
     if (!s) return;
-    void *p[] = { s->d_nodes, s->d_tris, s->d_shape_bsdf, s->d_shape_emitter, s->d_bsdfs, s->d_emitters, s->d_counter };
+    void *p[] = { s->d_nodes, s->d_tris, s->d_shape_bsdf, s->d_shape_emitter, s->d_bsdfs, s->d_emitters, s->d_counter,
+                  s->d_tri_attr, s->d_tex_data, s->d_textures };
     for (void *q : p) if (q) cudaFree(q);
     delete s;
 }

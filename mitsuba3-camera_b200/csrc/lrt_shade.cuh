@@ -6,7 +6,10 @@
 // render/fresnel.h:93-117), SmoothDielectric (dielectric.cpp sample), TwoSidedBRDF (twosided.cpp),
 // AreaLight (src/emitters/area.cpp:83-211) on rectangles (src/shapes/rectangle.cpp:166-185),
 // Shape::sample_direction / pdf_direction (src/render/shape.cpp:358-388),
-// Scene::sample_emitter_direction / pdf_emitter_direction (src/render/scene.cpp:227-366).
+// Scene::sample_emitter_direction / pdf_emitter_direction (src/render/scene.cpp:227-366),
+// vertex normals / texture coordinates of Mesh::compute_surface_interaction (src/render/mesh.cpp:1448-1500),
+// BitmapTexture bilinear lookups (src/textures/bitmap.cpp:696-711 -> dr::Texture::eval_nonaccel,
+// ext/drjit/include/drjit/texture.h:346-412, wrap modes :1143-1172).
 #pragma once
 #include "lrt_trace.cuh"
 #include "lrt_lens.cuh"
@@ -15,20 +18,28 @@ namespace lrt {
 
 enum : int { BSDF_DIFFUSE = 0, BSDF_CONDUCTOR = 1, BSDF_DIELECTRIC = 2 };
 
+struct TexView { const float *data; int w, h, wrap, pad; float to_uv[6]; };   // RGB float texels, row-major; wrap 0 repeat 1 mirror 2 clamp
+
 struct SceneView {
     BvhView bvh;
     const int *shape_bsdf, *shape_emitter;
-    const float4 *bsdfs;      // 4 x float4: [type, twosided, refl.rgb | eta.rgb, k.rgb | trans.rgb, eta_s, -]
+    const float4 *bsdfs;      // 4 x float4: [type, twosided, refl.rgb | eta.rgb, k.rgb | trans.rgb, eta_s, texture id + 1]
     const float4 *emitters;   // 5 x float4: [radiance.rgb, shape | c.xyz, inv_area | ex.xyz | ey.xyz | n.xyz]
     int n_emitters;
+    // optional per-triangle attributes, indexed like bvh.tris (4 x float4: n0.xyz n1.x | n1.yz n2.xy | n2.z uv0.xy uv1.x |
+    // uv1.y uv2.xy -); the triangle's flag word (third 128-bit word, .w) says which are valid: bit 0 normals, bit 1 uvs
+    const float4 *tri_attr;
+    const TexView *textures;
 };
 
 struct Surface {
-    float3 p, n, s, t;   // position, (geometric = shading) normal, tangent frame
+    float3 p, n;         // position, geometric normal
+    float3 sn, s, t;     // shading frame (sn = interpolated vertex normal when the mesh has them, else n)
     float3 wi;           // incident direction in the local frame
+    float2 uv;
     int shape;
-    LRT_D float3 to_local(float3 v) const { return make_float3(dot(v, s), dot(v, t), dot(v, n)); }
-    LRT_D float3 to_world(float3 v) const { return s * v.x + t * v.y + n * v.z; }
+    LRT_D float3 to_local(float3 v) const { return make_float3(dot(v, s), dot(v, t), dot(v, sn)); }
+    LRT_D float3 to_world(float3 v) const { return s * v.x + t * v.y + sn * v.z; }
 };
 
 LRT_D void coordinate_system(float3 n, float3 &s, float3 &t) {
@@ -45,10 +56,30 @@ LRT_D Surface make_surface(const SceneView &sc, const RayHit &h, float3 ray_d) {
     Surface si;
     float b1 = h.u, b2 = h.v, b0 = 1.f - b1 - b2;
     si.p = p0 * b0 + (p1 * b1 + p2 * b2);
-    si.n = normalize(cross(p1 - p0, p2 - p0));
+    const float3 dp0 = p1 - p0, dp1 = p2 - p0;
+    si.n = normalize(cross(dp0, dp1));
     float3 dp_du, dp_dv; coordinate_system(si.n, dp_du, dp_dv);
-    si.s = normalize(dp_du - si.n * dot(si.n, dp_du));
-    si.t = cross(si.n, si.s);
+    si.sn = si.n; si.uv = make_float2(b1, b2);
+    const int flags = __float_as_int(c.w);
+    if (flags != 0) {   // mesh.cpp:1448-1500: texture coordinates give dp_du, vertex normals the shading normal
+        const float4 *ap = sc.tri_attr + 4 * (size_t) h.tri;
+        const float4 a2 = __ldg(ap + 2);
+        if (flags & 2) {
+            const float4 a3 = __ldg(ap + 3);
+            const float2 uv0 = make_float2(a2.y, a2.z), uv1 = make_float2(a2.w, a3.x), uv2 = make_float2(a3.y, a3.z);
+            si.uv = make_float2(uv2.x * b2 + (uv1.x * b1 + uv0.x * b0), uv2.y * b2 + (uv1.y * b1 + uv0.y * b0));
+            const float2 duv0 = make_float2(uv1.x - uv0.x, uv1.y - uv0.y), duv1 = make_float2(uv2.x - uv0.x, uv2.y - uv0.y);
+            const float det = duv0.x * duv1.y - duv0.y * duv1.x;
+            if (det != 0.f) dp_du = (dp0 * duv1.y - dp1 * duv0.y) * (1.f / det);
+        }
+        if (flags & 1) {
+            const float4 a0 = __ldg(ap), a1 = __ldg(ap + 1);
+            const float3 n0 = make_float3(a0.x, a0.y, a0.z), n1 = make_float3(a0.w, a1.x, a1.y), n2 = make_float3(a1.z, a1.w, a2.x);
+            si.sn = normalize(n2 * b2 + (n1 * b1 + n0 * b0));
+        }
+    }
+    si.s = normalize(dp_du - si.sn * dot(si.sn, dp_du));
+    si.t = cross(si.sn, si.s);
     si.wi = si.to_local(-ray_d);
     si.shape = __float_as_int(c.y);
     return si;
@@ -86,6 +117,33 @@ LRT_D void fresnel_dielectric(float ci, float eta, float &r, float &ct, float &e
     ct = ci >= 0.f ? -cta : cta;
 }
 
+// dr::Texture<Float, 2>::wrap (texture.h:1143-1172): integer texel coordinate -> [0, shape)
+LRT_D int tex_wrap(int pos, int shape, int mode) {
+    if (mode == 2) return min(max(pos, 0), shape - 1);
+    const int shifted = pos < 0 ? pos + 1 : pos, div = shifted / shape;
+    int mod = pos - div * shape;
+    if (mod < 0) mod += shape;
+    if (mode == 1 && !(((div & 1) == 0) != (pos < 0))) mod = shape - 1 - mod;
+    return mod;
+}
+
+// BitmapTexture::eval for an RGB texture, bilinear filter
+LRT_D float3 texture_eval(const TexView *tv, float2 uv_in) {
+    const float *m = tv->to_uv;
+    const float u = m[1] * uv_in.y + (m[0] * uv_in.x + m[2]), v = m[4] * uv_in.y + (m[3] * uv_in.x + m[5]);
+    const int w = tv->w, h = tv->h, mode = tv->wrap;
+    const float px = fmaf(u, (float) w, -.5f), py = fmaf(v, (float) h, -.5f);
+    const float fx = floorf(px), fy = floorf(py);
+    const int ix = (int) fx, iy = (int) fy;
+    const float w1x = px - fx, w1y = py - fy, w0x = 1.f - w1x, w0y = 1.f - w1y;
+    const int x0 = tex_wrap(ix, w, mode), x1 = tex_wrap(ix + 1, w, mode), y0 = tex_wrap(iy, h, mode), y1 = tex_wrap(iy + 1, h, mode);
+    const float *d = tv->data;
+    auto texel = [&](int x, int y) { const float *q = d + 3 * ((size_t) y * w + x); return make_float3(__ldg(q), __ldg(q + 1), __ldg(q + 2)); };
+    float3 out = texel(x0, y0) * (w0x * w0y);
+    out += texel(x1, y0) * (w1x * w0y); out += texel(x0, y1) * (w0x * w1y); out += texel(x1, y1) * (w1x * w1y);
+    return out;
+}
+
 struct BsdfResult {
     float3 val; float pdf;          // eval_pdf(wo)
     float3 wo; float spdf, seta;    // sample
@@ -93,7 +151,7 @@ struct BsdfResult {
 };
 
 // BSDF::eval_pdf_sample: eval/pdf for the emitter direction `wo` and a fresh sample from (s1, s2)
-LRT_D BsdfResult bsdf_eval_pdf_sample(const SceneView &sc, int bsdf_id, float3 wi, float3 wo, float s1, float s2x, float s2y) {
+LRT_D BsdfResult bsdf_eval_pdf_sample(const SceneView &sc, int bsdf_id, float2 uv, float3 wi, float3 wo, float s1, float s2x, float s2y) {
     const float4 *bp = sc.bsdfs + 4 * (size_t) bsdf_id;
     float4 b0 = __ldg(bp), b1 = __ldg(bp + 1), b2 = __ldg(bp + 2), b3 = __ldg(bp + 3);
     int type = (int) b0.x; bool twosided = b0.y != 0.f;
@@ -104,6 +162,7 @@ LRT_D BsdfResult bsdf_eval_pdf_sample(const SceneView &sc, int bsdf_id, float3 w
     bool flip = twosided && wi.z < 0.f;
     if (flip) { wi.z = -wi.z; wo.z = -wo.z; }
     if (type == BSDF_DIFFUSE) {
+        if (b3.w != 0.f) refl = texture_eval(sc.textures + ((int) b3.w - 1), uv);   // `reflectance` is a bitmap texture
         float ci = wi.z, co = wo.z;
         if (ci > 0.f && co > 0.f) { o.val = refl * (kInvPi * co); o.pdf = kInvPi * co; }
         if (ci > 0.f) {

@@ -20,12 +20,20 @@ from .transform import Transform4f
 f32 = np.float32
 
 
+class TextureDesc(C.Structure):
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("wrap", C.c_int32), ("rgb", C.POINTER(C.c_float)),
+                ("to_uv", C.c_float * 6)]
+
+
 class SceneDesc(C.Structure):
     _fields_ = [("n_vertices", C.c_int32), ("vertices", C.POINTER(C.c_float)),
                 ("n_triangles", C.c_int64), ("indices", C.POINTER(C.c_int32)), ("tri_shape", C.POINTER(C.c_int32)),
                 ("n_shapes", C.c_int32), ("shape_bsdf", C.POINTER(C.c_int32)), ("shape_emitter", C.POINTER(C.c_int32)),
                 ("n_bsdfs", C.c_int32), ("bsdfs", C.POINTER(C.c_float)),
-                ("n_emitters", C.c_int32), ("emitters", C.POINTER(C.c_float))]
+                ("n_emitters", C.c_int32), ("emitters", C.POINTER(C.c_float)),
+                ("vertex_normals", C.POINTER(C.c_float)), ("vertex_uvs", C.POINTER(C.c_float)),
+                ("shape_flags", C.POINTER(C.c_int32)),
+                ("n_textures", C.c_int32), ("textures", C.POINTER(TextureDesc))]
 
 
 class RenderParams(C.Structure):
@@ -43,25 +51,77 @@ def _rgb(v, default):
     return np.repeat(a, 3) if a.size == 1 else a
 
 
-# a few entries of the reference's conductor table (src/render/ior.h / data/ior): RGB eta, k
-CONDUCTORS = {"Cu": ([0.200438, 0.924033, 1.102212], [3.912949, 2.452848, 2.142188]),
-              "Au": ([0.143119, 0.374957, 1.442479], [3.983160, 2.385721, 1.603215]),
-              "Al": ([1.657460, 0.880369, 0.521229], [9.223869, 6.269523, 4.837001]),
-              "Ag": ([0.155265, 0.116723, 0.138342], [4.828371, 3.122500, 2.147038]),
+# the reference's conductor table (resources/data/ior/*.spd converted to RGB by its scalar_rgb build: values read back
+# through mi.traverse(mi.load_dict({'type': 'conductor', 'material': m})); float32)
+CONDUCTORS = {"Cu": ([0.2010054737329483, 0.9237495064735413, 1.1022154092788696], [3.913262128829956, 2.453045129776001, 2.14208984375]),
+              "Au": ([0.14303597807884216, 0.3753070831298828, 1.4420453310012817], [3.982996940612793, 2.38555645942688, 1.6033592224121094]),
+              "Al": ([1.6575008630752563, 0.8804047107696533, 0.521244466304779], [9.223811149597168, 6.26950216293335, 4.8370041847229]),
+              "Ag": ([0.15527619421482086, 0.11672795563936234, 0.13838763535022736], [4.828354358673096, 3.122222423553467, 2.1469011306762695]),
+              "Cr": ([4.3696675300598145, 2.9165053367614746, 1.6549046039581299], [5.206546783447266, 4.231306076049805, 3.7546987533569336]),
+              "W": ([4.370816707611084, 3.300246477127075, 2.9984073638916016], [3.500640630722046, 2.6048738956451416, 2.27323317527771]),
               "none": ([0.0, 0.0, 0.0], [1.0, 1.0, 1.0])}
 IOR = {"vacuum": 1.0, "air": 1.000277, "water": 1.3330, "bk7": 1.5046, "diamond": 2.419, "acrylic glass": 1.49, "pyrex": 1.470}
 
 
-def bsdf_row(d: dict) -> np.ndarray:
-    """One BSDF dict -> the 16-float row of lrt_scene_desc."""
+WRAP_MODES = {"repeat": 0, "mirror": 1, "clamp": 2}
+
+
+def load_texture(d: dict) -> dict:
+    """`bitmap` texture plugin (src/textures/bitmap.cpp:115-310) -> {'rgb': [h,w,3] float32 linear, 'wrap', 'to_uv'}.
+    Sources: 'filename' (.exr / .pfm natively; 8-bit formats through OpenCV when present, sRGB -> linear unless raw)
+    or 'data' ([h,w,3] array). Only the bilinear filter of RGB textures is on the hot path."""
+    if d.get("type") != "bitmap":
+        raise ValueError(f"texture plugin '{d.get('type')}' is outside the hot path of this build")
+    if d.get("filter_type", "bilinear") != "bilinear":
+        raise ValueError("bitmap textures: only filter_type='bilinear' is built")
+    if "data" in d:
+        img = np.asarray(d["data"], f32)
+    else:
+        fn = d["filename"]
+        ext = fn.lower().rsplit(".", 1)[-1]
+        if ext in ("exr", "pfm"):
+            from . import imageio
+            img = (imageio.read_exr if ext == "exr" else imageio.read_pfm)(fn).astype(f32)
+        else:
+            try:
+                import cv2
+            except ImportError as e:
+                raise ValueError(f"reading '{fn}' needs OpenCV; .exr and .pfm are read natively") from e
+            raw = cv2.imread(fn, cv2.IMREAD_UNCHANGED)
+            if raw is None:
+                raise ValueError(f"cannot read '{fn}'")
+            if raw.ndim == 2:
+                raw = raw[..., None].repeat(3, -1)
+            img = raw[..., 2::-1].astype(f32) / f32(255 if raw.dtype == np.uint8 else 65535)
+            if not d.get("raw", False):    # Bitmap::convert undoes the sRGB gamma of 8-bit images
+                img = np.where(img <= 0.04045, img / 12.92, ((img + 0.055) / 1.055) ** 2.4).astype(f32)
+    if img.ndim == 2:
+        img = img[..., None].repeat(3, -1)
+    if img.ndim != 3 or img.shape[2] < 3:
+        raise ValueError("bitmap texture: expected an RGB image")
+    tu = d.get("to_uv")
+    m = np.eye(3, dtype=f32) if tu is None else np.asarray(getattr(tu, "matrix", tu), f32).reshape(3, 3)
+    return {"rgb": np.ascontiguousarray(img[..., :3], f32), "wrap": WRAP_MODES[d.get("wrap_mode", "repeat")],
+            "to_uv": np.ascontiguousarray(m[:2].reshape(-1), f32)}
+
+
+def bsdf_row(d: dict, textures=None) -> np.ndarray:
+    """One BSDF dict -> the 16-float row of lrt_scene_desc. A `bitmap` reflectance is appended to `textures` and
+    referenced from column 15 (texture id + 1)."""
     r = np.zeros(16, f32)
     t = d["type"]
     if t == "twosided":
         inner = next(v for v in d.values() if isinstance(v, dict) and "type" in v)
-        r = bsdf_row(inner); r[1] = 1
+        r = bsdf_row(inner, textures); r[1] = 1
         return r
     if t == "diffuse":
-        r[0] = 0; r[2:5] = _rgb(d.get("reflectance"), [0.5, 0.5, 0.5])
+        refl = d.get("reflectance")
+        if isinstance(refl, dict) and refl.get("type") == "bitmap":
+            if textures is None:
+                raise ValueError("a textured BSDF needs a scene to live in")
+            textures.append(load_texture(refl)); r[15] = len(textures)
+            refl = None
+        r[0] = 0; r[2:5] = _rgb(refl, [0.5, 0.5, 0.5])
     elif t == "conductor":
         r[0] = 1; r[2:5] = _rgb(d.get("specular_reflectance"), [1, 1, 1])
         if "material" in d:
@@ -94,21 +154,58 @@ def bsdf_row(d: dict) -> np.ndarray:
 
 
 def _rect_mesh(tw: Transform4f):
+    """rectangle.cpp as two triangles carrying the rectangle's own parameterisation uv = (x, y) / 2 + 1/2 (:556-557), so
+    that dp_du (hence the shading frame, interaction.h:245-255) and si.uv are those of the analytic shape."""
     v = tw.transform_affine(np.array([[-1, -1, 0], [1, -1, 0], [1, 1, 0], [-1, 1, 0]], f32))
-    return v, np.array([[0, 1, 2], [0, 2, 3]], np.int32)
+    return v, np.array([[0, 1, 2], [0, 2, 3]], np.int32), None, np.array([[0, 0], [1, 0], [1, 1], [0, 1]], f32)
+
+
+def _transform_normals(tw: Transform4f, n):
+    """Transform * Normal (transform.h:146-155: inverse transpose), normalised as the mesh loaders do."""
+    it = np.linalg.inv(tw.matrix[:3, :3].astype(np.float64)).T
+    out = np.asarray(n, np.float64) @ it.T
+    return (out / np.maximum(np.linalg.norm(out, axis=1, keepdims=True), 1e-30)).astype(f32)
 
 
 def _cube_mesh(tw: Transform4f):
-    c = np.array([[x, y, z] for z in (-1, 1) for y in (-1, 1) for x in (-1, 1)], f32)
-    quads = [(0, 2, 3, 1), (4, 5, 7, 6), (0, 1, 5, 4), (2, 6, 7, 3), (0, 4, 6, 2), (1, 3, 7, 5)]   # outward facing
-    faces = []
-    for a, b, cc, d in quads:
-        faces += [[a, b, cc], [a, cc, d]]
-    return tw.transform_affine(c), np.array(faces, np.int32)
+    """src/shapes/cube.cpp:107-133: 24 vertices with per-face normals and a [0,1]^2 parameterisation of every face."""
+    v = np.array([[1, -1, -1], [1, -1, 1], [-1, -1, 1], [-1, -1, -1], [1, 1, -1], [-1, 1, -1], [-1, 1, 1], [1, 1, 1],
+                  [1, -1, -1], [1, 1, -1], [1, 1, 1], [1, -1, 1], [1, -1, 1], [1, 1, 1], [-1, 1, 1], [-1, -1, 1],
+                  [-1, -1, 1], [-1, 1, 1], [-1, 1, -1], [-1, -1, -1], [1, 1, -1], [1, -1, -1], [-1, -1, -1], [-1, 1, -1]], f32)
+    n = np.repeat(np.array([[0, -1, 0], [0, 1, 0], [1, 0, 0], [0, 0, 1], [-1, 0, 0], [0, 0, -1]], f32), 4, 0)
+    uv = np.tile(np.array([[0, 1], [1, 1], [1, 0], [0, 0]], f32), (6, 1))
+    f = np.array([[0, 1, 2], [3, 0, 2], [4, 5, 6], [7, 4, 6], [8, 9, 10], [11, 8, 10], [12, 13, 14], [15, 12, 14],
+                  [16, 17, 18], [19, 16, 18], [20, 21, 22], [23, 20, 22]], np.int32)
+    return tw.transform_affine(v), f, _transform_normals(tw, n), uv
+
+
+def vertex_normals(verts, faces):
+    """Mesh::recompute_vertex_normals (src/render/mesh.cpp:321-375): face normals weighted by the face angle at the
+    vertex (Thuermer & Wuethrich); what the obj / ply loaders do for files without normals unless face_normals=true."""
+    v = np.asarray(verts, np.float64); f = np.asarray(faces, np.int64)
+    p = [v[f[:, k]] for k in range(3)]
+    n = np.cross(p[1] - p[0], p[2] - p[0])
+    ln = np.linalg.norm(n, axis=1, keepdims=True)
+    ok = ln[:, 0] > 0
+    n = np.where(ln > 0, n / np.maximum(ln, 1e-300), 0.0)
+    out = np.zeros_like(v)
+    for k in range(3):
+        d0 = p[(k + 1) % 3] - p[k]; d1 = p[(k + 2) % 3] - p[k]
+        d0 /= np.maximum(np.linalg.norm(d0, axis=1, keepdims=True), 1e-300); d1 /= np.maximum(np.linalg.norm(d1, axis=1, keepdims=True), 1e-300)
+        # unit_angle (math.h): numerically robust angle between unit vectors
+        dp = (d0 * d1).sum(1)
+        ang = np.where(dp < 0, np.pi - 2 * np.arcsin(np.clip(0.5 * np.linalg.norm(d1 + d0, axis=1), -1, 1)),
+                       2 * np.arcsin(np.clip(0.5 * np.linalg.norm(d1 - d0, axis=1), -1, 1)))
+        np.add.at(out, f[:, k], n * (ang * ok)[:, None])
+    ln = np.linalg.norm(out, axis=1, keepdims=True)
+    out = np.where(ln > 0, out / np.maximum(ln, 1e-300), np.array([1.0, 0.0, 0.0]))
+    return out.astype(f32)
 
 
 def load_obj(path):
-    vs, fs = [], []
+    """Wavefront OBJ (src/shapes/obj.cpp): positions, optional vt / vn; vertices are split per (v, vt, vn) triple.
+    Returns (verts, faces, normals | None, uvs | None)."""
+    vs, vts, vns, fs, key_of, out_v, out_t, out_n = [], [], [], [], {}, [], [], []
     with open(path) as f:
         for line in f:
             p = line.split()
@@ -116,12 +213,26 @@ def load_obj(path):
                 continue
             if p[0] == "v":
                 vs.append([float(x) for x in p[1:4]])
+            elif p[0] == "vt":
+                vts.append([float(x) for x in p[1:3]])
+            elif p[0] == "vn":
+                vns.append([float(x) for x in p[1:4]])
             elif p[0] == "f":
-                idx = [int(tok.split("/")[0]) for tok in p[1:]]
-                idx = [i - 1 if i > 0 else len(vs) + i for i in idx]
+                idx = []
+                for tok in p[1:]:
+                    q = (tok.split("/") + ["", ""])[:3]
+                    key = tuple((int(x) - 1 if int(x) > 0 else n + int(x)) if x else -1 for x, n in zip(q, (len(vs), len(vts), len(vns))))
+                    if key not in key_of:
+                        key_of[key] = len(out_v); out_v.append(vs[key[0]])
+                        out_t.append(vts[key[1]] if key[1] >= 0 else [0.0, 0.0]); out_n.append(vns[key[2]] if key[2] >= 0 else [0.0, 0.0, 0.0])
+                    idx.append(key_of[key])
                 for k in range(1, len(idx) - 1):
                     fs.append([idx[0], idx[k], idx[k + 1]])
-    return np.array(vs, f32).reshape(-1, 3), np.array(fs, np.int32).reshape(-1, 3)
+    uv = np.array(out_t, f32).reshape(-1, 2) if vts else None
+    if uv is not None:
+        uv[:, 1] = 1 - uv[:, 1]      # obj.cpp flips v by default (flip_tex_coords = true)
+    return (np.array(out_v, f32).reshape(-1, 3), np.array(fs, np.int32).reshape(-1, 3),
+            np.array(out_n, f32).reshape(-1, 3) if vns else None, uv)
 
 
 def load_ply(path):
@@ -141,7 +252,7 @@ def load_ply(path):
                 cur["props"].append(p[1:])
         tmap = {"float": "f", "float32": "f", "double": "d", "float64": "d", "uchar": "B", "uint8": "B", "char": "b", "int": "i",
                 "int32": "i", "uint": "I", "uint32": "I", "short": "h", "ushort": "H", "int16": "h", "uint16": "H"}
-        verts, faces = None, []
+        verts, faces, normals, uvs = None, [], None, None
         for e in elems:
             if fmt == "ascii":
                 rows = [f.readline().split() for _ in range(e["count"])]
@@ -149,6 +260,11 @@ def load_ply(path):
                     names = [p[-1] for p in e["props"]]
                     ix = [names.index(c) for c in "xyz"]
                     verts = np.array([[float(r[i]) for i in ix] for r in rows], f32)
+                    if "nx" in names:
+                        normals = np.array([[float(r[names.index(c)]) for c in ("nx", "ny", "nz")] for r in rows], f32)
+                    for cu, cv in (("u", "v"), ("texture_u", "texture_v"), ("s", "t")):
+                        if cu in names and cv in names:
+                            uvs = np.array([[float(r[names.index(cu)]), float(r[names.index(cv)])] for r in rows], f32); break
                 elif e["name"] == "face":
                     for r in rows:
                         n = int(r[0]); idx = [int(x) for x in r[1:1 + n]]
@@ -159,6 +275,11 @@ def load_ply(path):
                     dt = np.dtype([(p[-1], "<" + tmap[p[0]]) for p in e["props"]])
                     a = np.frombuffer(f.read(dt.itemsize * e["count"]), dt)
                     verts = np.stack([a["x"], a["y"], a["z"]], 1).astype(f32)
+                    if "nx" in dt.names:
+                        normals = np.stack([a["nx"], a["ny"], a["nz"]], 1).astype(f32)
+                    for cu, cv in (("u", "v"), ("texture_u", "texture_v"), ("s", "t")):
+                        if cu in dt.names and cv in dt.names:
+                            uvs = np.stack([a[cu], a[cv]], 1).astype(f32); break
                 elif e["name"] == "face":
                     p = e["props"][0]   # list <count type> <index type> vertex_indices
                     ct, it = tmap[p[1]], tmap[p[2]]
@@ -168,7 +289,7 @@ def load_ply(path):
                         faces += [[idx[0], idx[k], idx[k + 1]] for k in range(1, n - 1)]
                 else:
                     raise ValueError("unsupported ply element " + e["name"])
-    return verts, np.array(faces, np.int32).reshape(-1, 3)
+    return verts, np.array(faces, np.int32).reshape(-1, 3), normals, uvs
 
 
 class SceneData:
@@ -178,16 +299,21 @@ class SceneData:
         self.vertices, self.indices, self.tri_shape = [], [], []
         self.shape_bsdf, self.shape_emitter, self.shape_names = [], [], []
         self.bsdf_rows, self.bsdf_names, self.emitter_rows = [], [], []
+        self.normals, self.uvs, self.shape_flags, self.textures = [], [], [], []
+        self.rectangles = []      # (shape id, to_world 4x4) of `rectangle` shapes (the oracle can intersect them analytically)
         self._nv = 0
 
     def add_bsdf(self, name, row):
         self.bsdf_rows.append(np.asarray(row, f32)); self.bsdf_names.append(name)
         return len(self.bsdf_rows) - 1
 
-    def add_shape(self, name, verts, faces, bsdf_id, emitter=None):
+    def add_shape(self, name, verts, faces, bsdf_id, emitter=None, normals=None, uvs=None):
         sid = len(self.shape_bsdf)
         verts = np.ascontiguousarray(verts, f32).reshape(-1, 3); faces = np.ascontiguousarray(faces, np.int32).reshape(-1, 3)
         self.vertices.append(verts); self.indices.append(faces + self._nv); self._nv += len(verts)
+        self.normals.append(np.zeros((len(verts), 3), f32) if normals is None else np.ascontiguousarray(normals, f32).reshape(len(verts), 3))
+        self.uvs.append(np.zeros((len(verts), 2), f32) if uvs is None else np.ascontiguousarray(uvs, f32).reshape(len(verts), 2))
+        self.shape_flags.append((1 if normals is not None else 0) | (2 if uvs is not None else 0))
         self.tri_shape.append(np.full(len(faces), sid, np.int32))
         self.shape_bsdf.append(bsdf_id); self.shape_names.append(name)
         if emitter is not None:
@@ -204,7 +330,12 @@ class SceneData:
                     tri_shape=cat(self.tri_shape, np.int32, (0,)),
                     shape_bsdf=np.array(self.shape_bsdf, np.int32), shape_emitter=np.array(self.shape_emitter, np.int32),
                     bsdfs=np.ascontiguousarray(np.stack(self.bsdf_rows) if self.bsdf_rows else np.zeros((0, 16), f32), f32),
-                    emitters=np.ascontiguousarray(np.stack(self.emitter_rows) if self.emitter_rows else np.zeros((0, 16), f32), f32))
+                    emitters=np.ascontiguousarray(np.stack(self.emitter_rows) if self.emitter_rows else np.zeros((0, 16), f32), f32),
+                    vertex_normals=cat(self.normals, f32, (0, 3)), vertex_uvs=cat(self.uvs, f32, (0, 2)),
+                    shape_flags=np.array(self.shape_flags, np.int32), textures=list(self.textures),
+                    rect_shapes=np.array([r[0] for r in self.rectangles], np.int32),
+                    rect_to_world=np.ascontiguousarray(np.stack([r[1] for r in self.rectangles]) if self.rectangles
+                                                       else np.zeros((0, 4, 4), f32), f32))
 
 
 # ------------------------------------------------------------------------------------------------ objects
@@ -258,10 +389,19 @@ class Scene:
     def _upload(self):
         a = self.arrays
         opt = lambda arr, conv: conv(arr.reshape(-1)) if arr.size else None
+        flags = a.get("shape_flags")
+        has_attr = flags is not None and flags.size and bool(flags.any())
+        tex = a.get("textures") or []
+        tdesc = (TextureDesc * max(len(tex), 1))()
+        for i, t in enumerate(tex):
+            h, w, _ = t["rgb"].shape
+            tdesc[i] = TextureDesc(w, h, int(t["wrap"]), capi.fp(t["rgb"].reshape(-1)), (C.c_float * 6)(*[float(x) for x in t["to_uv"]]))
         d = SceneDesc(len(a["vertices"]), opt(a["vertices"], capi.fp), len(a["indices"]), opt(a["indices"], capi.ip),
                       opt(a["tri_shape"], capi.ip), len(a["shape_bsdf"]), opt(a["shape_bsdf"], capi.ip),
                       opt(a["shape_emitter"], capi.ip), len(a["bsdfs"]), opt(a["bsdfs"], capi.fp),
-                      len(a["emitters"]), opt(a["emitters"], capi.fp))
+                      len(a["emitters"]), opt(a["emitters"], capi.fp),
+                      opt(a["vertex_normals"], capi.fp) if has_attr else None, opt(a["vertex_uvs"], capi.fp) if has_attr else None,
+                      opt(flags, capi.ip) if has_attr else None, len(tex), tdesc if tex else None)
         h = C.c_void_p()
         capi.check(capi.lib.lrt_scene_create(C.byref(d), C.byref(h)))
         if self.handle:
@@ -431,7 +571,7 @@ def scene_data_from_dict(d: dict):
     default_bsdf = None
     for key, v in d.items():   # named BSDFs first: they are the targets of {'type': 'ref'}
         if isinstance(v, dict) and v.get("type") in _BSDFS:
-            named_bsdf[v.get("id", key)] = data.add_bsdf(key, bsdf_row(v))
+            named_bsdf[v.get("id", key)] = data.add_bsdf(key, bsdf_row(v, data.textures))
     for key, v in d.items():
         if not isinstance(v, dict):
             continue
@@ -443,18 +583,33 @@ def scene_data_from_dict(d: dict):
         elif vt in _SHAPES:
             tw = v.get("to_world")
             tw = tw if isinstance(tw, Transform4f) else Transform4f(tw)
+            if v.get("flip_normals", False) and vt == "rectangle":
+                tw = tw @ Transform4f(np.diag(np.array([1, 1, -1, 1], f32)))     # rectangle.cpp:100-103
             if vt == "rectangle":
-                verts, faces = _rect_mesh(tw)
+                verts, faces, normals, uvs = _rect_mesh(tw)
             elif vt == "cube":
-                verts, faces = _cube_mesh(tw)
+                verts, faces, normals, uvs = _cube_mesh(tw)
             else:
-                if vt == "mesh":
+                if vt == "mesh":     # in-memory mesh (mi.Mesh): flat-shaded unless the arrays carry normals
                     verts, faces = np.asarray(v["vertices"], f32), np.asarray(v["faces"], np.int32)
+                    normals, uvs = v.get("vertex_normals"), v.get("vertex_texcoords")
                 else:
-                    verts, faces = (load_obj if vt == "obj" else load_ply)(v["filename"])
+                    verts, faces, normals, uvs = (load_obj if vt == "obj" else load_ply)(v["filename"])
+                    if vt == "ply" and uvs is not None and v.get("flip_tex_coords", False):
+                        uvs = uvs.copy(); uvs[:, 1] = 1 - uvs[:, 1]
+                    if vt == "obj" and uvs is not None and not v.get("flip_tex_coords", True):
+                        uvs = uvs.copy(); uvs[:, 1] = 1 - uvs[:, 1]
                 verts = tw.transform_affine(verts)
-            if v.get("flip_normals", False):
-                faces = faces[:, ::-1]
+                if v.get("face_normals", False):
+                    normals = None
+                elif normals is not None:
+                    normals = _transform_normals(tw, normals)
+                elif vt in ("obj", "ply"):     # ply.cpp:444-449 / obj.cpp:401-404
+                    normals = vertex_normals(verts, faces)
+            if v.get("flip_normals", False) and vt != "rectangle":
+                faces = faces[:, ::-1]                              # mesh.cpp:1539-1542: si.n and sh_frame.n change sign
+                if normals is not None:
+                    normals = -np.asarray(normals, f32)
             b = v.get("bsdf")
             if b is None:
                 if default_bsdf is None:
@@ -463,7 +618,7 @@ def scene_data_from_dict(d: dict):
             elif b.get("type") == "ref":
                 bid = named_bsdf[b["id"]]
             else:
-                bid = data.add_bsdf(f"{key}.bsdf", bsdf_row(b))
+                bid = data.add_bsdf(f"{key}.bsdf", bsdf_row(b, data.textures))
             em = v.get("emitter")
             emitter = None
             if em is not None:
@@ -471,7 +626,9 @@ def scene_data_from_dict(d: dict):
                     raise ValueError("this build supports `area` emitters on `rectangle` shapes")
                 emitter = {"radiance": _rgb(em.get("radiance"), [1, 1, 1]), "center": tw.transform_affine(np.zeros(3, f32)),
                            "ex": tw.transform_vector(np.array([1, 0, 0], f32)), "ey": tw.transform_vector(np.array([0, 1, 0], f32))}
-            data.add_shape(key, verts, faces, bid, emitter)
+            sid = data.add_shape(key, verts, faces, bid, emitter, normals, uvs)
+            if vt == "rectangle":
+                data.rectangles.append((sid, tw.matrix.copy()))
         elif vt in _BSDFS or vt is None:
             pass
         else:

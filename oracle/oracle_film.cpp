@@ -15,7 +15,7 @@ static int floor2int(float x) { return (int) std::floor(x); }
 
 // imageblock.cpp:174-532; tensor is (size+2*border)^2 x channels, float64 accumulators
 void block_put(const Filter &flt, int size_x, int size_y, int off_x, int off_y, int border, int channels,
-               bool coalesce, bool normalize, float pos_x, float pos_y, const float *values, double *tensor) {
+               bool coalesce, bool normalize, bool discretized, float pos_x, float pos_y, const float *values, double *tensor) {
     if (flt.kind == 0) {   // :210-233 (m_rfilter == nullptr for the box filter)
         int px = floor2int(pos_x) - off_x, py = floor2int(pos_y) - off_y;
         if (px < 0 || py < 0 || px >= size_x || py >= size_y) return;
@@ -25,7 +25,7 @@ void block_put(const Filter &flt, int size_x, int size_y, int off_x, int off_y, 
     }
     float radius = flt.radius;
     int sx = size_x + 2 * border, sy = size_y + 2 * border;
-    if (!coalesce) {       // :264-412 (JIT: continuous filter, conservative count)
+    if (!coalesce || discretized) {       // :264-412 (JIT: continuous filter, conservative count; scalar: discretised filter)
         float pfx = pos_x + ((float) (border - off_x) - .5f), pfy = pos_y + ((float) (border - off_y) - .5f);
         float p0x = pfx - radius, p0y = pfy - radius, p1x = pfx + radius, p1y = pfy + radius;
         int x0 = std::max(ceil2int(p0x), 0), y0 = std::max(ceil2int(p0y), 0);
@@ -34,11 +34,12 @@ void block_put(const Filter &flt, int size_x, int size_y, int off_x, int off_y, 
         int count_max = ceil2int(2.f * radius);
         float wx[16], wy[16];
         float rx = (float) x0 - pfx, ry = (float) y0 - pfy;
-        for (int i = 0; i < count_max; ++i) { wx[i] = flt.eval(rx); rx += 1.f; wy[i] = flt.eval(ry); ry += 1.f; }
+        auto ev = [&](float x) { return discretized ? flt.eval_discretized(x) : flt.eval(x); };
+        for (int i = 0; i < count_max; ++i) { wx[i] = ev(rx); rx += 1.f; wy[i] = ev(ry); ry += 1.f; }
         if (normalize) {   // :318-342
             float sxw = 0.f, syw = 0.f;
             float r2x = std::ceil(p0x) - pfx, r2y = std::ceil(p0y) - pfy;
-            for (int i = 0; i < count_max; ++i) { sxw += flt.eval(r2x); syw += flt.eval(r2y); r2x += 1.f; r2y += 1.f; }
+            for (int i = 0; i < count_max; ++i) { sxw += ev(r2x); syw += ev(r2y); r2x += 1.f; r2y += 1.f; }
             float factor = sxw * syw;
             factor = factor != 0.f ? rcp(factor) : 0.f;
             for (int i = 0; i < count_max; ++i) wx[i] *= factor;
@@ -95,7 +96,7 @@ void orc_block_put(int kind, float param, int size_x, int size_y, int off_x, int
                    int coalesce, int normalize, int64_t n, const float *pos, const float *values, double *tensor64) {
     Filter f; f.init(kind, param);
     for (int64_t i = 0; i < n; ++i)
-        block_put(f, size_x, size_y, off_x, off_y, border, channels, coalesce != 0, normalize != 0,
+        block_put(f, size_x, size_y, off_x, off_y, border, channels, coalesce != 0, normalize != 0, false,
                   pos[2 * i], pos[2 * i + 1], values + (size_t) i * channels, tensor64);
 }
 // hdrfilm.cpp:390-392 develop for pixel_format rgb: storage [H,W,4] (R,G,B,W) -> [H,W,3]

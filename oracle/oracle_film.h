@@ -26,8 +26,9 @@ struct Filter {
     float radius;
     float coeff[10];  // gaussian Remez coefficients (CPU/LLVM branch, gaussian.cpp:55-89)
     float inv_radius;
+    float values[32], scale_factor;   // init_discretization (src/core/rfilter.cpp:9-24), MI_FILTER_RESOLUTION = 31
     void init(int k, float param) {
-        kind = k;
+        kind = k; inv_radius = 0.f;
         if (k == 0) radius = 0.5f;
         if (k == 1) { radius = param > 0 ? param : 1.f; inv_radius = 1.f / radius; }
         if (k == 2) {
@@ -39,6 +40,14 @@ struct Filter {
             for (int i = 0; i < 10; ++i) { coeff[i] = (float) (c[i] * scale); scale /= (double) stddev * (double) stddev; }
             coeff[0] -= estrin(sqr(radius), coeff, 10);
         }
+        for (int i = 0; i < 31; ++i) values[i] = eval((radius * (float) i) / 31.f);
+        values[31] = 0.f;
+        scale_factor = 31.f / radius;
+    }
+    // include/mitsuba/core/rfilter.h:66-76 (scalar variants): index = min(uint(|x * scale|), 31)
+    float eval_discretized(float x) const {
+        uint32_t index = (uint32_t) std::fabs(x * scale_factor);
+        return values[index < 31u ? index : 31u];
     }
     float eval(float x) const {
         if (kind == 1) return std::fmax(0.f, 1.f - std::fabs(x * inv_radius));                 // tent.cpp:53-55
@@ -48,8 +57,9 @@ struct Filter {
 };
 
 
-// imageblock.cpp:174-532; tensor is (size+2*border)^2 x channels, float64 accumulators
+// imageblock.cpp:174-532; tensor is (size+2*border)^2 x channels, float64 accumulators. discretized = the scalar variants'
+// path: non-coalesced window, exact tap counts, eval_discretized (imageblock.cpp:264-379 with JIT = false)
 void block_put(const Filter &flt, int size_x, int size_y, int off_x, int off_y, int border, int channels,
-               bool coalesce, bool normalize, float pos_x, float pos_y, const float *values, double *tensor);
+               bool coalesce, bool normalize, bool discretized, float pos_x, float pos_y, const float *values, double *tensor);
 
 }  // namespace orc

@@ -322,7 +322,7 @@ extern "C" long long orc_spot_render(void *h, int size_x, int size_y, int off_x,
         valid++;
         float wv = o[10] * scale;
         float vals[4] = { intensity3[0] * wv, intensity3[1] * wv, intensity3[2] * wv, scale };
-        block_put(flt, size_x, size_y, off_x, off_y, 0, 4, false, true, o[0] + (float) off_x, o[1] + (float) off_y, vals, storage);
+        block_put(flt, size_x, size_y, off_x, off_y, 0, 4, false, true, false, o[0] + (float) off_x, o[1] + (float) off_y, vals, storage);
     }
     return valid;
 }

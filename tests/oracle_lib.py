@@ -170,15 +170,30 @@ def bits(a):
 
 
 # ------------------------------------------------------------------------------------------------ scenes / render
-def orc_scene(a):
-    """a: dict of flat arrays (mitsuba3-camera_b200/scene.py SceneData.arrays()) -> oracle scene handle."""
+def orc_scene(a, analytic_rectangles=False):
+    """a: dict of flat arrays (mitsuba3-camera_b200/scene.py SceneData.arrays()) -> oracle scene handle.
+    analytic_rectangles: intersect `rectangle` shapes as the reference does (rectangle.cpp) instead of as two triangles."""
     L = oracle()
-    L.orc_scene_create.restype = C.c_void_p
-    keep = {k: np.ascontiguousarray(v) for k, v in a.items()}
-    h = L.orc_scene_create(C.c_int(len(keep["vertices"])), fp(keep["vertices"]), C.c_int(len(keep["indices"])), ip(keep["indices"]),
-                           ip(keep["tri_shape"]), C.c_int(len(keep["shape_bsdf"])), ip(keep["shape_bsdf"]), ip(keep["shape_emitter"]),
-                           C.c_int(len(keep["bsdfs"])), fp(keep["bsdfs"]), C.c_int(len(keep["emitters"])), fp(keep["emitters"]))
-    return C.c_void_p(h)
+    L.orc_scene_create2.restype = C.c_void_p
+    keep = {k: np.ascontiguousarray(v) for k, v in a.items() if isinstance(v, np.ndarray)}
+    flags = keep.get("shape_flags")
+    has_attr = flags is not None and flags.size and bool(flags.any())
+    tex = a.get("textures") or []
+    dims = np.array([[t["rgb"].shape[1], t["rgb"].shape[0], t["wrap"]] for t in tex], np.int32).reshape(-1, 3)
+    tdata = np.concatenate([t["rgb"].reshape(-1) for t in tex]).astype(f32) if tex else np.zeros(1, f32)
+    tuv = np.concatenate([np.asarray(t["to_uv"], f32) for t in tex]) if tex else np.zeros(6, f32)
+    h = C.c_void_p(L.orc_scene_create2(
+        C.c_int(len(keep["vertices"])), fp(keep["vertices"]), fp(keep["vertex_normals"]) if has_attr else None,
+        fp(keep["vertex_uvs"]) if has_attr else None, C.c_int(len(keep["indices"])), ip(keep["indices"]), ip(keep["tri_shape"]),
+        C.c_int(len(keep["shape_bsdf"])), ip(keep["shape_bsdf"]), ip(keep["shape_emitter"]), ip(keep["shape_flags"]) if has_attr else None,
+        C.c_int(len(keep["bsdfs"])), fp(keep["bsdfs"]), C.c_int(len(keep["emitters"])), fp(keep["emitters"]),
+        C.c_int(len(tex)), ip(dims), fp(tdata), fp(tuv)))
+    if analytic_rectangles and len(keep.get("rect_shapes", [])):
+        tw = keep["rect_to_world"].astype(f32)
+        inv = np.stack([np.linalg.inv(m.astype(np.float64)) for m in tw]).astype(f32)
+        L.orc_scene_set_rectangles(h, C.c_int(len(tw)), ip(keep["rect_shapes"]), fp(np.ascontiguousarray(tw[:, :3, :].reshape(-1))),
+                                   fp(np.ascontiguousarray(inv[:, :3, :].reshape(-1))))
+    return h
 
 
 def orc_intersect(scene_h, o, d, maxt, any_hit=False):
@@ -204,6 +219,21 @@ def orc_render(scene_h, film, spp, seed=0, max_depth=8, rr_depth=5, cam_h=None, 
                  C.c_int(cw), C.c_int(ch), C.c_int(cx), C.c_int(cy), C.c_int(filter_kind), c_f(filter_param), C.c_uint32(seed),
                  C.c_int(spp), C.c_int(max_depth), C.c_int(rr_depth), C.c_int64(b), C.c_int64(e),
                  st.ctypes.data_as(C.POINTER(C.c_double)), C.byref(miss))
+    return st, miss.value
+
+
+def orc_render_scalar(scene_h, film, spp, seed=0, base_seed=0, max_depth=8, rr_depth=5, cam_h=None, fov=45.0, to_world=EYE, near=1e-2,
+                      far=1e4, filter_kind=2, filter_param=0.0, block_size=32):
+    """The reference's SCALAR render loop (per-pixel streams, spiral blocks, Morton order, discretised filter)."""
+    L = oracle()
+    cw, ch, cx, cy = (int(v) for v in film.crop)
+    st = np.zeros((ch, cw, 4), np.float64)
+    miss = C.c_int64(0)
+    tw = np.ascontiguousarray(to_world, f32)
+    L.orc_render_scalar(scene_h, cam_h, c_f(fov), fp(tw), c_f(near), c_f(far), C.c_int(film.width), C.c_int(film.height),
+                        C.c_int(cw), C.c_int(ch), C.c_int(cx), C.c_int(cy), C.c_int(filter_kind), c_f(filter_param),
+                        C.c_uint32(base_seed), C.c_uint32(seed), C.c_int(spp), C.c_int(max_depth), C.c_int(rr_depth), C.c_int(block_size),
+                        st.ctypes.data_as(C.POINTER(C.c_double)), C.byref(miss))
     return st, miss.value
 
 
