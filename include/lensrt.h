@@ -165,7 +165,9 @@ typedef struct lrt_scene_desc {
     int32_t n_bsdfs; const float *bsdfs;
     int32_t n_emitters; const float *emitters;
     /* Mesh vertex attributes (src/render/mesh.cpp:1448-1500), all optional (NULL): shape_flags[s] bit 0 = the vertices of
-     * shape s carry normals (interpolated shading normal), bit 1 = texture coordinates (si.uv and dp_du). */
+     * shape s carry normals (interpolated shading normal), bit 1 = texture coordinates (si.uv and dp_du), bit 2 = the shape
+     * is a `rectangle` given as the two triangles (0,1,2),(0,2,3) of its corners (-1,-1),(1,-1),(1,1),(-1,1): its shading
+     * frame follows the rectangle's parameterisation (src/shapes/rectangle.cpp:115-123) with or without texture coordinates. */
     const float *vertex_normals;                     /* [n_vertices,3] */
     const float *vertex_uvs;                         /* [n_vertices,2] */
     const int32_t *shape_flags;                      /* [n_shapes] */
@@ -194,6 +196,14 @@ typedef struct lrt_render_params {
     int32_t rr_depth;         /* default 5 */
     int32_t shard_index, shard_count;   /* pixel tiles are dealt round-robin over shards (multi-GPU) */
     int32_t chunks;           /* 0 = automatic split of a pixel's samples into work items */
+    /* Sampler convention (src/render/sampler.cpp:115-134). 0: the JIT variants' — one PCG32 stream per sample,
+     * (v0, v1) = tea(seed, idx) — the fast path. 1: the scalar variants' — one stream per pixel seeded with
+     * base_seed + seed * W * H + block_id * block_size^2 + morton index (src/render/integrator.cpp:195-200,388-402), spiral
+     * block order, discretised filter, scalar control flow of the path loop: a single-GPU parity mode whose images
+     * match the reference's scalar_rgb variant sample for sample. */
+    int32_t rng_mode;
+    int32_t block_size;       /* rng_mode 1: render block size, 0 = 32 (MI_BLOCK_SIZE) */
+    uint32_t base_seed;       /* rng_mode 1: the sampler's `seed` property (rng_mode 0 callers fold it into `seed`) */
 } lrt_render_params;
 
 /* Accumulates R,G,B,W into accum_dev [size_y+2b, size_x+2b, 4] (caller zeroes it; ImageBlock storage of

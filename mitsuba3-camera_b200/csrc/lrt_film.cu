@@ -40,6 +40,8 @@ int film_params_from_desc(const lrt_film_desc *d, FilmParams &F) {
         for (int i = 0; i < 10; ++i) { F.coeff[i] = (float) (c[i] * scale); scale /= (double) stddev * (double) stddev; }
         F.coeff[0] -= estrin_host(F.radius * F.radius, F.coeff, 10);
     }
+    for (int i = 0; i < 31; ++i) F.disc[i] = filter_eval(F, (F.radius * (float) i) / 31.f);
+    F.disc[31] = 0.f; F.disc_scale = 31.f / F.radius; F.discretized = 0;
     F.n_half = (int) std::ceil(F.radius - .5f); F.count = 2 * F.n_half + 1;
     F.count_max = (int) std::ceil(2.f * F.radius);
     LRT_REQUIRE(F.count <= kMaxTaps && F.count_max <= kMaxTaps, "filter radius too large (max 8 taps per axis)");

@@ -17,6 +17,9 @@ struct FilmParams {
     int count_max;              // non-coalesced: ceil(2*radius)
     float radius, inv_radius;
     float coeff[10];
+    // scalar-variant splat (imageblock.cpp:264-379 with JIT = false): 31-tap table of ReconstructionFilter::
+    // init_discretization (src/core/rfilter.cpp:9-24); `discretized` switches the non-coalesced footprint to it
+    int discretized; float disc_scale; float disc[32];
 };
 
 LRT_HD float filter_eval(const FilmParams &F, float x) {
@@ -37,13 +40,19 @@ LRT_HD float filter_eval(const FilmParams &F, float x) {
     return (x >= -.5f && x < .5f) ? 1.f : 0.f;
 }
 
+// ReconstructionFilter::eval_discretized (include/mitsuba/core/rfilter.h:66-76)
+LRT_HD float filter_eval_discretized(const FilmParams &F, float x) {
+    const unsigned index = (unsigned) fabsf(x * F.disc_scale);
+    return F.disc[index < 31u ? index : 31u];
+}
+
 // Footprint of one sample: window origin (x0,y0) in tensor coordinates, extent, separable weights.
 struct Footprint {
     int x0, y0, nx, ny;         // taps ix in [0,nx) land on pixel x0+ix (still to be clipped to the tensor)
     float wx[kMaxTaps], wy[kMaxTaps];
 };
 
-LRT_HD bool film_footprint(const FilmParams &F, float px, float py, Footprint &fp) {
+template <bool kDisc = false> LRT_HD bool film_footprint(const FilmParams &F, float px, float py, Footprint &fp) {
     int sx = F.size_x + 2 * F.border, sy = F.size_y + 2 * F.border;
     if (F.kind == FILTER_BOX) {
         int ix = (int) floorf(px) - F.off_x, iy = (int) floorf(py) - F.off_y;
@@ -59,7 +68,10 @@ LRT_HD bool film_footprint(const FilmParams &F, float px, float py, Footprint &f
         if (x0 > x1 || y0 > y1) return false;
         fp.x0 = x0; fp.y0 = y0; fp.nx = min(x1 - x0 + 1, F.count_max); fp.ny = min(y1 - y0 + 1, F.count_max);
         float rx = (float) x0 - pfx, ry = (float) y0 - pfy;
-        for (int i = 0; i < F.count_max; ++i) { fp.wx[i] = filter_eval(F, rx); fp.wy[i] = filter_eval(F, ry); rx += 1.f; ry += 1.f; }
+        if (kDisc)   // (compile-time: the render megakernel never carries the table lookups)
+            for (int i = 0; i < F.count_max; ++i) { fp.wx[i] = filter_eval_discretized(F, rx); fp.wy[i] = filter_eval_discretized(F, ry); rx += 1.f; ry += 1.f; }
+        else
+            for (int i = 0; i < F.count_max; ++i) { fp.wx[i] = filter_eval(F, rx); fp.wy[i] = filter_eval(F, ry); rx += 1.f; ry += 1.f; }
         if (F.normalize) {
             float a = 0.f, b = 0.f, r2x = ceilf(p0x) - pfx, r2y = ceilf(p0y) - pfy;
             for (int i = 0; i < F.count_max; ++i) { a += filter_eval(F, r2x); b += filter_eval(F, r2y); r2x += 1.f; r2y += 1.f; }

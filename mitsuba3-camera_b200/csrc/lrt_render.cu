@@ -82,7 +82,9 @@ LRT_D void splat_to_tile(const FilmParams &F, float *tile, int smem_w, int ox, i
 #ifndef LRT_RENDER_MIN_BLOCKS
 #define LRT_RENDER_MIN_BLOCKS 4
 #endif
-template <bool kAdj>
+// kAttr: the scene has vertex normals / texture coordinates / textures (lrt_shade.cuh); without them the attribute code is
+// compiled out so that the hot loop keeps its instruction-cache footprint
+template <bool kAdj, bool kAttr>
 __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(RenderArgs A) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     LensSystem &L = *reinterpret_cast<LensSystem *>(smem_raw);
@@ -174,7 +176,10 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
         bool exhausted = false;   // no lane active, no camera ray left: only the queue remains to be drained
         while (true) {
             // the only drain site (splat_to_tile is ~500 instructions; inlining it four times cost instruction-cache misses)
-            while (q_count >= 32 || (exhausted && q_count > 0)) drain(min(q_count, 32));   // leaves < 32 entries: 32 + 32 more fit
+            if (q_count >= 32 || (exhausted && q_count > 0)) {
+                drain(min(q_count, 32));
+                if (q_count >= 32) continue;   // back to this (single) drain site: < 32 entries are left below, 32 + 32 more fit
+            }
             if (exhausted) { if (q_count == 0) break; continue; }
             // ---- A. camera rays, 32 at a time: render_sample() draws in the reference's order (integrator.cpp:435-448)
             if (fifo_count < 32 && round < n_rounds) {
@@ -272,7 +277,7 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
                     bool want_shadow = false;
                     if (hit) {
                         valid_ray = true;   // path.cpp:256 uses the loop mask `active`, not `active_next`
-                        const Surface si = make_surface(A.sc, h, rd);
+                        const Surface si = make_surface<kAttr>(A.sc, h, rd);
                         const int em = __ldg(A.sc.shape_emitter + si.shape);
                         if (em >= 0) {     // direct emission, MIS against the previous bounce's BSDF sample (:158-174)
                             float3 rel = si.p - prev_p; float dist = sqrtf(dot(rel, rel)); float3 dd = rel * (1.f / dist);
@@ -312,7 +317,7 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
                 }
                 if (finish) {
                     // ---- second half (path.cpp:210-281): BSDF eval/sample, NEE contribution, next ray, Russian roulette
-                    const Surface si = make_surface(A.sc, seg, wi_w);
+                    const Surface si = make_surface<kAttr>(A.sc, seg, wi_w);
                     const int bsdf_id = __ldg(A.sc.shape_bsdf + si.shape);
                     float e_sx = rng.next_f32(), e_sy = rng.next_f32();
                     float s1 = rng.next_f32(), s2x = rng.next_f32(), s2y = rng.next_f32();
@@ -320,7 +325,7 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
                     EmitterSample es; es.pdf = 0.f; float3 wo = make_float3(0, 0, 0);
                     const bool active_em = phase == 2 && !occluded;
                     if (active_em) { es = sample_emitter_direction(A.sc, si.p, e_sx, e_sy); wo = si.to_local(es.d); }
-                    BsdfResult bs = bsdf_eval_pdf_sample(A.sc, bsdf_id, si.uv, si.wi, wo, s1, s2x, s2y);
+                    BsdfResult bs = bsdf_eval_pdf_sample<kAttr>(A.sc, bsdf_id, si.uv, si.wi, wo, s1, s2x, s2y);
                     if (kAdj) {   // everything gathered from here on is linear in this surface's (specular) reflectance
                         const int btype = (int) __ldg(reinterpret_cast<const float *>(A.sc.bsdfs) + 16 * (size_t) bsdf_id);
                         if (nrec < kMaxRec && btype != BSDF_DIELECTRIC && __ldg(reinterpret_cast<const float *>(A.sc.bsdfs) + 16 * (size_t) bsdf_id + 15) == 0.f) {   // (textured reflectances are not parameters)
@@ -460,16 +465,19 @@ int launch_render(const lrt_scene *sc, lrt_sensor *sensor, const lrt_film_desc *
         static std::mutex mu; static bool attr_set[64] = {};
         std::lock_guard<std::mutex> lock(mu);
         if (dev >= 64 || !attr_set[dev]) {
-            LRT_CUDA(cudaFuncSetAttribute(k_render<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-            LRT_CUDA(cudaFuncSetAttribute(k_render<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+            LRT_CUDA(cudaFuncSetAttribute(k_render<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+            LRT_CUDA(cudaFuncSetAttribute(k_render<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+            LRT_CUDA(cudaFuncSetAttribute(k_render<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+            LRT_CUDA(cudaFuncSetAttribute(k_render<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
             if (dev < 64) attr_set[dev] = true;
         }
     }
     const bool adjoint = grad_storage != nullptr;
     A.grad_storage = grad_storage; A.grad_bsdfs = grad_bsdfs; A.grad_emitters = grad_emitters; A.n_bsdfs = sc->n_bsdfs;
     int per_sm = 1;
-    if (adjoint) cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_render<true>, kCtaThreads, smem);
-    else cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_render<false>, kCtaThreads, smem);
+    const bool attr = sc->view.tri_attr != nullptr || sc->view.textures != nullptr;
+    void (*kern)(RenderArgs) = adjoint ? (attr ? k_render<true, true> : k_render<true, false>) : (attr ? k_render<false, true> : k_render<false, false>);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kCtaThreads, smem);
     if (per_sm < 1) per_sm = 1;
     long long resident = (long long) sms * per_sm;
     // split the samples of a pixel into chunks until there are ~4 work items per resident warp
@@ -486,8 +494,7 @@ int launch_render(const lrt_scene *sc, lrt_sensor *sensor, const lrt_film_desc *
     LRT_CUDA(cudaMemsetAsync(A.stats, 0, 8 * sizeof(unsigned long long), stream));
     long long grid = std::min(resident, (A.n_items + kWarps - 1) / kWarps);
     if (grid < 1) return LRT_OK;
-    if (adjoint) k_render<true><<<(int) grid, kCtaThreads, smem, stream>>>(A);
-    else k_render<false><<<(int) grid, kCtaThreads, smem, stream>>>(A);
+    kern<<<(int) grid, kCtaThreads, smem, stream>>>(A);
     LRT_LAUNCHED();
     LRT_CUDA(cudaGetLastError());
     return LRT_OK;

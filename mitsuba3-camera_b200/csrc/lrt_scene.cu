@@ -8,6 +8,8 @@ namespace lrt {
 struct RenderArgs;
 int launch_render(const lrt_scene *sc, lrt_sensor *sensor, const lrt_film_desc *film, const lrt_render_params *rp,
                   float *accum_dev, const float *grad_storage, float *grad_bsdfs, float *grad_emitters, cudaStream_t stream);
+int launch_render_scalar(const lrt_scene *sc, lrt_sensor *sensor, const lrt_film_desc *film, const lrt_render_params *rp,
+                         float *accum_dev, cudaStream_t stream);
 }
 using namespace lrt;
 
@@ -47,12 +49,20 @@ int lrt_scene_create(const lrt_scene_desc *d, lrt_scene **out) {
     build_bvh8(d->vertices, d->indices, d->tri_shape, d->n_triangles, nodes, tris, &st);
     // per-triangle vertex attributes in BVH order; the triangle record's pad word carries the flags
     std::vector<float> attr;
-    if (d->shape_flags && (d->vertex_normals || d->vertex_uvs)) {
+    if (d->shape_flags) {
         bool any = false;
+        // first triangle of every shape (rectangles are the quads (0,1,2),(0,2,3) of their four vertices)
+        std::vector<int64_t> first((size_t) d->n_shapes, d->n_triangles);
+        for (int64_t t = d->n_triangles - 1; t >= 0; --t) first[d->tri_shape[t]] = t;
         for (size_t i = 0; i < tris.size(); ++i) {
-            int fl = d->shape_flags[tris[i].shape] & ((d->vertex_normals ? 1 : 0) | (d->vertex_uvs ? 2 : 0));
+            const int sf = d->shape_flags[tris[i].shape];
+            int fl = sf & ((d->vertex_normals ? 1 : 0) | (d->vertex_uvs ? 2 : 0));
+            if (sf & 4) {   // rectangle: the frame comes from the triangle's edges; its uvs are only needed by textures
+                fl = (tris[i].prim - first[tris[i].shape]) == 0 ? 4 : 8;
+                if (d->n_textures > 0 && d->vertex_uvs) fl |= 2;
+            }
             memcpy(&tris[i].pad, &fl, 4);
-            any = any || fl != 0;
+            any = any || (fl & 3) != 0;
         }
         if (any) {
             attr.assign(tris.size() * 16, 0.f);
@@ -148,6 +158,8 @@ int lrt_render(const lrt_scene *sc, const lrt_sensor *sensor, const lrt_film_des
                float *accum_dev, void *stream) {
     LRT_NEED_DEVICE();
     LRT_REQUIRE(sc && sensor && film && rp && accum_dev, "null argument");
+    LRT_REQUIRE(rp->rng_mode == 0 || rp->rng_mode == 1, "rng_mode must be 0 (per-sample streams) or 1 (scalar convention)");
+    if (rp->rng_mode == 1) return launch_render_scalar(sc, const_cast<lrt_sensor *>(sensor), film, rp, accum_dev, (cudaStream_t) stream);
     return launch_render(sc, const_cast<lrt_sensor *>(sensor), film, rp, accum_dev, nullptr, nullptr, nullptr, (cudaStream_t) stream);
 }
 
@@ -155,6 +167,7 @@ int lrt_render_backward(const lrt_scene *sc, const lrt_sensor *sensor, const lrt
                         const float *grad_storage_dev, float *grad_bsdfs_dev, float *grad_emitters_dev, void *stream) {
     LRT_NEED_DEVICE();
     LRT_REQUIRE(sc && sensor && film && rp && grad_storage_dev && grad_bsdfs_dev && grad_emitters_dev, "null argument");
+    LRT_REQUIRE(rp->rng_mode == 0, "the adjoint follows the JIT sampler convention (rng_mode 0)");
     return launch_render(sc, const_cast<lrt_sensor *>(sensor), film, rp, nullptr, grad_storage_dev, grad_bsdfs_dev, grad_emitters_dev,
                          (cudaStream_t) stream);
 }

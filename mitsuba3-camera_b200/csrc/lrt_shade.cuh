@@ -28,6 +28,7 @@ struct SceneView {
     int n_emitters;
     // optional per-triangle attributes, indexed like bvh.tris (4 x float4: n0.xyz n1.x | n1.yz n2.xy | n2.z uv0.xy uv1.x |
     // uv1.y uv2.xy -); the triangle's flag word (third 128-bit word, .w) says which are valid: bit 0 normals, bit 1 uvs
+    // (bits 2 / 3 mark the two triangles of a tessellated rectangle, see make_surface)
     const float4 *tri_attr;
     const TexView *textures;
 };
@@ -49,7 +50,29 @@ LRT_D void coordinate_system(float3 n, float3 &s, float3 &t) {
     t = make_float3(b, n.y * (n.y * a) + sign, -n.y);
 }
 
-LRT_D Surface make_surface(const SceneView &sc, const RayHit &h, float3 ray_d) {
+// Cold path of make_surface, kept out of line so that the render megakernel's hot loop stays inside the instruction
+// cache (scenes without vertex attributes never call it): mesh.cpp:1448-1500 — texture coordinates give si.uv and dp_du,
+// vertex normals the shading normal.
+static __device__ __noinline__ void surface_attributes(const float4 *__restrict__ ap, int flags, float b0, float b1, float b2, float3 dp0, float3 dp1,
+                                                float3 &dp_du, float3 &sn, float2 &uv) {
+    const float4 a2 = __ldg(ap + 2);
+    if (flags & 2) {
+        const float4 a3 = __ldg(ap + 3);
+        const float2 uv0 = make_float2(a2.y, a2.z), uv1 = make_float2(a2.w, a3.x), uv2 = make_float2(a3.y, a3.z);
+        uv = make_float2(uv2.x * b2 + (uv1.x * b1 + uv0.x * b0), uv2.y * b2 + (uv1.y * b1 + uv0.y * b0));
+        const float2 duv0 = make_float2(uv1.x - uv0.x, uv1.y - uv0.y), duv1 = make_float2(uv2.x - uv0.x, uv2.y - uv0.y);
+        const float det = duv0.x * duv1.y - duv0.y * duv1.x;
+        if (det != 0.f) dp_du = (dp0 * duv1.y - dp1 * duv0.y) * (1.f / det);
+    }
+    if (flags & 1) {
+        const float4 a0 = __ldg(ap), a1 = __ldg(ap + 1);
+        const float3 n0 = make_float3(a0.x, a0.y, a0.z), n1 = make_float3(a0.w, a1.x, a1.y), n2 = make_float3(a1.z, a1.w, a2.x);
+        sn = normalize(n2 * b2 + (n1 * b1 + n0 * b0));
+    }
+}
+
+// kAttr = false compiles the vertex-attribute path out (scenes without normals / uvs / textures: the fast kernel variant)
+template <bool kAttr = true> LRT_D Surface make_surface(const SceneView &sc, const RayHit &h, float3 ray_d) {
     const float4 *tp = sc.bvh.tris + 3 * (size_t) h.tri;
     float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);
     float3 p0 = make_float3(a.x, a.y, a.z), p1 = make_float3(a.w, b.x, b.y), p2 = make_float3(b.z, b.w, c.x);
@@ -61,23 +84,11 @@ LRT_D Surface make_surface(const SceneView &sc, const RayHit &h, float3 ray_d) {
     float3 dp_du, dp_dv; coordinate_system(si.n, dp_du, dp_dv);
     si.sn = si.n; si.uv = make_float2(b1, b2);
     const int flags = __float_as_int(c.w);
-    if (flags != 0) {   // mesh.cpp:1448-1500: texture coordinates give dp_du, vertex normals the shading normal
-        const float4 *ap = sc.tri_attr + 4 * (size_t) h.tri;
-        const float4 a2 = __ldg(ap + 2);
-        if (flags & 2) {
-            const float4 a3 = __ldg(ap + 3);
-            const float2 uv0 = make_float2(a2.y, a2.z), uv1 = make_float2(a2.w, a3.x), uv2 = make_float2(a3.y, a3.z);
-            si.uv = make_float2(uv2.x * b2 + (uv1.x * b1 + uv0.x * b0), uv2.y * b2 + (uv1.y * b1 + uv0.y * b0));
-            const float2 duv0 = make_float2(uv1.x - uv0.x, uv1.y - uv0.y), duv1 = make_float2(uv2.x - uv0.x, uv2.y - uv0.y);
-            const float det = duv0.x * duv1.y - duv0.y * duv1.x;
-            if (det != 0.f) dp_du = (dp0 * duv1.y - dp1 * duv0.y) * (1.f / det);
-        }
-        if (flags & 1) {
-            const float4 a0 = __ldg(ap), a1 = __ldg(ap + 1);
-            const float3 n0 = make_float3(a0.x, a0.y, a0.z), n1 = make_float3(a0.w, a1.x, a1.y), n2 = make_float3(a1.z, a1.w, a2.x);
-            si.sn = normalize(n2 * b2 + (n1 * b1 + n0 * b0));
-        }
-    }
+    // tessellated `rectangle` shapes (bits 2 / 3: first / second triangle of the quad (0,1,2),(0,2,3)): dp_du of the
+    // rectangle's own parameterisation (rectangle.cpp:118-121) is an edge of the triangle — the value the uv formula of
+    // mesh.cpp:1471-1480 yields for uv = (x, y) / 2 + 1/2, without fetching any attribute
+    if (flags & 12) dp_du = (flags & 4) ? dp0 : dp0 - dp1;
+    if (kAttr && (flags & 3)) surface_attributes(sc.tri_attr + 4 * (size_t) h.tri, flags, b0, b1, b2, dp0, dp1, dp_du, si.sn, si.uv);
     si.s = normalize(dp_du - si.sn * dot(si.sn, dp_du));
     si.t = cross(si.sn, si.s);
     si.wi = si.to_local(-ray_d);
@@ -127,8 +138,8 @@ LRT_D int tex_wrap(int pos, int shape, int mode) {
     return mod;
 }
 
-// BitmapTexture::eval for an RGB texture, bilinear filter
-LRT_D float3 texture_eval(const TexView *tv, float2 uv_in) {
+// BitmapTexture::eval for an RGB texture, bilinear filter (out of line: cold for untextured scenes)
+static __device__ __noinline__ float3 texture_eval(const TexView *tv, float2 uv_in) {
     const float *m = tv->to_uv;
     const float u = m[1] * uv_in.y + (m[0] * uv_in.x + m[2]), v = m[4] * uv_in.y + (m[3] * uv_in.x + m[5]);
     const int w = tv->w, h = tv->h, mode = tv->wrap;
@@ -151,7 +162,7 @@ struct BsdfResult {
 };
 
 // BSDF::eval_pdf_sample: eval/pdf for the emitter direction `wo` and a fresh sample from (s1, s2)
-LRT_D BsdfResult bsdf_eval_pdf_sample(const SceneView &sc, int bsdf_id, float2 uv, float3 wi, float3 wo, float s1, float s2x, float s2y) {
+template <bool kAttr = true> LRT_D BsdfResult bsdf_eval_pdf_sample(const SceneView &sc, int bsdf_id, float2 uv, float3 wi, float3 wo, float s1, float s2x, float s2y) {
     const float4 *bp = sc.bsdfs + 4 * (size_t) bsdf_id;
     float4 b0 = __ldg(bp), b1 = __ldg(bp + 1), b2 = __ldg(bp + 2), b3 = __ldg(bp + 3);
     int type = (int) b0.x; bool twosided = b0.y != 0.f;
@@ -162,7 +173,7 @@ LRT_D BsdfResult bsdf_eval_pdf_sample(const SceneView &sc, int bsdf_id, float2 u
     bool flip = twosided && wi.z < 0.f;
     if (flip) { wi.z = -wi.z; wo.z = -wo.z; }
     if (type == BSDF_DIFFUSE) {
-        if (b3.w != 0.f) refl = texture_eval(sc.textures + ((int) b3.w - 1), uv);   // `reflectance` is a bitmap texture
+        if (kAttr && b3.w != 0.f) refl = texture_eval(sc.textures + ((int) b3.w - 1), uv);   // `reflectance` is a bitmap texture
         float ci = wi.z, co = wo.z;
         if (ci > 0.f && co > 0.f) { o.val = refl * (kInvPi * co); o.pdf = kInvPi * co; }
         if (ci > 0.f) {

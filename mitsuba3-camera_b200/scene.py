@@ -38,7 +38,8 @@ class SceneDesc(C.Structure):
 
 class RenderParams(C.Structure):
     _fields_ = [("seed", C.c_uint32), ("spp", C.c_int32), ("max_depth", C.c_int32), ("rr_depth", C.c_int32),
-                ("shard_index", C.c_int32), ("shard_count", C.c_int32), ("chunks", C.c_int32)]
+                ("shard_index", C.c_int32), ("shard_count", C.c_int32), ("chunks", C.c_int32),
+                ("rng_mode", C.c_int32), ("block_size", C.c_int32), ("base_seed", C.c_uint32)]
 
 
 # ------------------------------------------------------------------------------------------------ plugins
@@ -307,13 +308,13 @@ class SceneData:
         self.bsdf_rows.append(np.asarray(row, f32)); self.bsdf_names.append(name)
         return len(self.bsdf_rows) - 1
 
-    def add_shape(self, name, verts, faces, bsdf_id, emitter=None, normals=None, uvs=None):
+    def add_shape(self, name, verts, faces, bsdf_id, emitter=None, normals=None, uvs=None, rectangle=False):
         sid = len(self.shape_bsdf)
         verts = np.ascontiguousarray(verts, f32).reshape(-1, 3); faces = np.ascontiguousarray(faces, np.int32).reshape(-1, 3)
         self.vertices.append(verts); self.indices.append(faces + self._nv); self._nv += len(verts)
         self.normals.append(np.zeros((len(verts), 3), f32) if normals is None else np.ascontiguousarray(normals, f32).reshape(len(verts), 3))
         self.uvs.append(np.zeros((len(verts), 2), f32) if uvs is None else np.ascontiguousarray(uvs, f32).reshape(len(verts), 2))
-        self.shape_flags.append((1 if normals is not None else 0) | (2 if uvs is not None else 0))
+        self.shape_flags.append((1 if normals is not None else 0) | (2 if uvs is not None else 0) | (4 if rectangle else 0))
         self.tri_shape.append(np.full(len(faces), sid, np.int32))
         self.shape_bsdf.append(bsdf_id); self.shape_names.append(name)
         if emitter is not None:
@@ -449,10 +450,44 @@ def film_desc(film: Film, coalesce=True, normalize=False) -> FilmDesc:
     return FilmDesc(film.crop_w, film.crop_h, film.crop_x, film.crop_y, 0, 4, rf.kind, rf.param, int(coalesce), int(normalize))
 
 
+WAVEFRONT_LIMIT = 0xffffffff     # integrator.cpp:248: one 32-bit sample index per wavefront lane
+
+
+def tea32(v0, v1, rounds=4):
+    """mi.sample_tea_32 (include/mitsuba/core/random.h:76-90) on host integers."""
+    v0 &= 0xffffffff; v1 &= 0xffffffff; s = 0
+    for _ in range(rounds):
+        s = (s + 0x9e3779b9) & 0xffffffff
+        v0 = (v0 + ((((v1 << 4) & 0xffffffff) + 0xa341316c) ^ (v1 + s) ^ ((v1 >> 5) + 0xc8013ea4))) & 0xffffffff
+        v1 = (v1 + ((((v0 << 4) & 0xffffffff) + 0xad90777d) ^ (v0 + s) ^ ((v0 >> 5) + 0x7e95761e))) & 0xffffffff
+    return v0, v1
+
+
+def render_passes(n_pixels, spp, seed, wavefront_limit=WAVEFRONT_LIMIT):
+    """[(pass seed, pass spp)] of one render: SamplingIntegrator::render splits W*H*spp > 2^32 - 1 samples into equal passes
+    (src/render/integrator.cpp:247-265: spp_per_pass = spp / ceil(wavefront / limit)). The reference keeps the 2^32 sampler
+    states alive between passes (64 GB of PCG32 state); here pass k > 0 starts fresh streams from the seed
+    sample_tea_32(seed, k)[0] — statistically equivalent, not the same numbers — and a remainder pass keeps the total at
+    exactly `spp` where the reference's integer division would drop samples."""
+    wavefront = n_pixels * spp
+    if wavefront <= wavefront_limit:
+        return [(seed & 0xffffffff, spp)]
+    per = spp // ((wavefront + wavefront_limit - 1) // wavefront_limit)
+    if per < 1:
+        raise ValueError("film too large: a single sample per pixel exceeds the 2^32 wavefront limit")
+    out, done, k = [], 0, 0
+    while done < spp:
+        n = min(per, spp - done)
+        out.append((seed & 0xffffffff if k == 0 else tea32(seed, k)[0], n))
+        done += n; k += 1
+    return out
+
+
 def render(scene: Scene, params=None, sensor=0, integrator=None, seed=0, seed_grad=0, spp=0, spp_grad=0, develop=True,
-           shard=(0, 1), storage=None):
+           shard=(0, 1), storage=None, rng_mode=0, wavefront_limit=WAVEFRONT_LIMIT):
     """mi.render (src/python/python/util.py:410-525), forward part: returns the developed [H,W,3] image as a
-    torch CUDA tensor (or the raw R,G,B,W storage with develop=False)."""
+    torch CUDA tensor (or the raw R,G,B,W storage with develop=False). rng_mode=1 selects the scalar variants' sampler
+    convention (lensrt.h). Renders of more than 2^32 - 1 samples run as several passes (render_passes)."""
     import torch
     if params is not None:
         params.update()
@@ -462,12 +497,19 @@ def render(scene: Scene, params=None, sensor=0, integrator=None, seed=0, seed_gr
     fd = film_desc(s.film)
     if storage is None:
         storage = torch.zeros((s.film.crop_h, s.film.crop_w, 4), dtype=torch.float32, device="cuda")
-    rp = RenderParams((s.sampler.base_seed + int(seed)) & 0xffffffff, spp, it.max_depth, it.rr_depth, shard[0], shard[1], 0)
-    capi.check(capi.lib.lrt_render(scene.handle, s.handle, C.byref(fd), C.byref(rp), capi.dev_ptr(storage), capi.stream_ptr()))
+    if rng_mode == 1:
+        rp = RenderParams(int(seed) & 0xffffffff, spp, it.max_depth, it.rr_depth, 0, 1, 0, 1, 0, s.sampler.base_seed & 0xffffffff)
+        if tuple(shard) != (0, 1):
+            raise ValueError("rng_mode=1 (scalar sampler convention) is a single-GPU parity mode")
+        capi.check(capi.lib.lrt_render(scene.handle, s.handle, C.byref(fd), C.byref(rp), capi.dev_ptr(storage), capi.stream_ptr()))
+    else:
+        for pseed, pspp in render_passes(s.film.crop_w * s.film.crop_h, spp, s.sampler.base_seed + int(seed), wavefront_limit):
+            rp = RenderParams(pseed, pspp, it.max_depth, it.rr_depth, shard[0], shard[1], 0, 0, 0, 0)
+            capi.check(capi.lib.lrt_render(scene.handle, s.handle, C.byref(fd), C.byref(rp), capi.dev_ptr(storage), capi.stream_ptr()))
     return develop_rgb(storage) if develop else storage
 
 
-def render_backward(scene: Scene, grad_storage, sensor=0, integrator=None, seed=0, spp=0, shard=(0, 1)):
+def render_backward(scene: Scene, grad_storage, sensor=0, integrator=None, seed=0, spp=0, shard=(0, 1), wavefront_limit=WAVEFRONT_LIMIT):
     """Adjoint of render() for diffuse reflectance / conductor specular reflectance / area-light radiance
     (RBIntegrator.render_backward, src/python/python/ad/integrators/common.py:631-796 with prb.py): grad_storage = d(loss)/
     d(R,G,B,W storage) [H,W,4] -> (grad_bsdfs [n_bsdfs,16], grad_emitters [n_emitters,16]) torch CUDA tensors."""
@@ -478,9 +520,11 @@ def render_backward(scene: Scene, grad_storage, sensor=0, integrator=None, seed=
     fd = film_desc(s.film)
     gb = torch.zeros((max(len(scene.arrays["bsdfs"]), 1), 16), dtype=torch.float32, device="cuda")
     ge = torch.zeros((max(len(scene.arrays["emitters"]), 1), 16), dtype=torch.float32, device="cuda")
-    rp = RenderParams((s.sampler.base_seed + int(seed)) & 0xffffffff, spp, it.max_depth, it.rr_depth, shard[0], shard[1], 0)
-    capi.check(capi.lib.lrt_render_backward(scene.handle, s.handle, C.byref(fd), C.byref(rp), capi.dev_ptr(grad_storage.contiguous()),
-                                            capi.dev_ptr(gb), capi.dev_ptr(ge), capi.stream_ptr()))
+    gs = grad_storage.contiguous()
+    for pseed, pspp in render_passes(s.film.crop_w * s.film.crop_h, spp, s.sampler.base_seed + int(seed), wavefront_limit):
+        rp = RenderParams(pseed, pspp, it.max_depth, it.rr_depth, shard[0], shard[1], 0, 0, 0, 0)
+        capi.check(capi.lib.lrt_render_backward(scene.handle, s.handle, C.byref(fd), C.byref(rp), capi.dev_ptr(gs),
+                                                capi.dev_ptr(gb), capi.dev_ptr(ge), capi.stream_ptr()))
     return gb[:len(scene.arrays["bsdfs"])], ge[:len(scene.arrays["emitters"])]
 
 
@@ -626,7 +670,7 @@ def scene_data_from_dict(d: dict):
                     raise ValueError("this build supports `area` emitters on `rectangle` shapes")
                 emitter = {"radiance": _rgb(em.get("radiance"), [1, 1, 1]), "center": tw.transform_affine(np.zeros(3, f32)),
                            "ex": tw.transform_vector(np.array([1, 0, 0], f32)), "ey": tw.transform_vector(np.array([0, 1, 0], f32))}
-            sid = data.add_shape(key, verts, faces, bid, emitter, normals, uvs)
+            sid = data.add_shape(key, verts, faces, bid, emitter, normals, uvs, rectangle=vt == "rectangle")
             if vt == "rectangle":
                 data.rectangles.append((sid, tw.matrix.copy()))
         elif vt in _BSDFS or vt is None:

@@ -32,7 +32,7 @@ def _value_noise(n, rng, octaves=5, base=6):
 
 
 def heightfield_scene(n_side=708, width=3840, height=2160, spp=16, lens_design="gauss", max_depth=6, seed=1,
-                      extent=10.0, amplitude=1.2, patch=16, n_diffuse=8, sensor="realisticlens"):
+                      extent=10.0, amplitude=1.2, patch=16, n_diffuse=8, sensor="realisticlens", sensor_extra=None):
     """Config 5: ~1M-triangle displaced grid (n_side=708 -> 999,698 triangles), 50 % diffuse (albedo U[0.2,0.8]) /
     50 % conductor (Cu) in square patches, one large area light + 4 emissive quads, realistic lens."""
     rng = np.random.default_rng(seed)
@@ -76,6 +76,7 @@ def heightfield_scene(n_side=708, width=3840, height=2160, spp=16, lens_design="
     if sensor == "realisticlens":
         d["sensor"] = {"type": "realisticlens", "lens_design": lens_design, "object_distance": 16.0, "to_world": tw,
                        "near_clip": 1e-2, "far_clip": 1e3, "film": film, "sampler": smp}
+        d["sensor"].update(sensor_extra or {})
     else:
         d["sensor"] = {"type": "perspective", "fov": 40.0, "to_world": tw, "near_clip": 1e-2, "far_clip": 1e3, "film": film, "sampler": smp}
     return d

@@ -323,15 +323,6 @@ def test_gpu_empty_scene_and_empty_batches(mi):
 
 
 @pytest.mark.gpu
-def test_gpu_wavefront_size_guard(mi):
-    """W*H*spp must fit 32 bits (one PCG32 stream per sample index, integrator.cpp:247-265 splits into passes)."""
-    d = cornell(mi, res=64, spp=1 << 21)
-    sc = mi.load_dict(d)
-    with pytest.raises(mi.capi.LensrtError):
-        mi.render(sc, seed=0)
-
-
-@pytest.mark.gpu
 @pytest.mark.parametrize("rf,kind,param", [({"type": "gaussian", "stddev": 0.8}, 2, 0.8), ({"type": "tent", "radius": 3.0}, 1, 3.0)])
 def test_gpu_wide_reconstruction_filters(mi, rf, kind, param):
     """Filters wider than the defaults (gaussian stddev 0.8 -> radius 3.2, tent radius 3: 7 taps per axis, the build's
