@@ -31,7 +31,10 @@ def parse():
     p.add_argument("--impl", default="ours", choices=["ours", "reference"])
     p.add_argument("--spp-per-step", type=int, default=64,
                    help="samples per pixel of one step (one pass; the reference's own passes are bounded by W*H*spp < 2^32, i.e. <= 517 spp here)")
-    p.add_argument("--cpu-spp", type=int, default=16, help="spp of the bounded CPU sample (same film crop, same scene)")
+    p.add_argument("--cpu-spp", type=int, default=16, help="spp of the parity crop rendered by the oracle port (same film crop, same scene)")
+    p.add_argument("--ref-spp", type=int, default=1, help="spp of the bounded sample the reference's own scalar_rgb build renders (FULL film: "
+                                                            "the same vignetting mix as the GPU's step)")
+    p.add_argument("--ref-flavour", default="native", choices=["native", "pinned"], help="which build under baseline/_ref is timed")
     p.add_argument("--width", type=int, default=3840)
     p.add_argument("--height", type=int, default=2160)
     p.add_argument("--n-side", type=int, default=708)
@@ -77,7 +80,28 @@ def workload_dict(mi, a):
                                 max_depth=a.max_depth)
 
 
-def cpu_sample(a, scene_arrays, sensor_dict, steps=1, warmup=0):
+def parity_crop(mi, torch, a, d, port):
+    """GPU render of the crop the oracle port rendered (same seed / spp / sample streams): rel-RMSE of the developed images
+    and the lens ray-miss counts, which must be equal."""
+    import copy
+    import numpy as np
+    cw, ch = min(a.cpu_crop[0], a.width), min(a.cpu_crop[1], a.height)
+    d2 = dict(d); d2["sensor"] = dict(d["sensor"]); d2["sensor"]["film"] = dict(d["sensor"]["film"])
+    d2["sensor"]["film"].update(crop_width=cw, crop_height=ch, crop_offset_x=(a.width - cw) // 2, crop_offset_y=(a.height - ch) // 2)
+    sensor = mi.load_dict(d2["sensor"])
+    scene = parity_crop.scene
+    spp = min(a.cpu_spp, a.spp_per_step)
+    img = mi.render(scene, sensor=sensor, seed=0, spp=spp).cpu().numpy().astype(np.float64)
+    miss_gpu = int(scene.stats()["lens_misses"])
+    want = port["image"].astype(np.float64)
+    rel = float(np.sqrt(np.mean((img - want) ** 2)) / max(np.sqrt(np.mean(want ** 2)), 1e-12))
+    assert miss_gpu == port["lens_miss"], f"lens ray-miss count differs: GPU {miss_gpu}, oracle {port['lens_miss']}"
+    return {"what": f"centred {cw}x{ch} crop, {spp} spp, seed 0: GPU vs oracle port (pinned to the reference, tests/test_ref_parity.py)",
+            "rel_rmse": rel, "lens_miss_gpu": miss_gpu, "lens_miss_cpu": int(port["lens_miss"]), "image_mean_gpu": float(img.mean()),
+            "image_mean_cpu": float(want.mean())}
+
+
+def cpu_sample(a, scene_arrays, sensor_dict, steps=1, warmup=0, keep_image=False):
     """The CPU arm: the oracle port (OpenMP, all host cores) on a centred crop of the same film at --cpu-spp samples per pixel
     (a bounded sample: paths/s of the port does not depend on the pass size)."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
@@ -94,14 +118,47 @@ def cpu_sample(a, scene_arrays, sensor_dict, steps=1, warmup=0):
     cpu_spp = min(a.cpu_spp, a.spp_per_step)
     paths = cw * ch * cpu_spp
     times = []
+    st = miss = None
     for i in range(warmup + steps):
         t0 = time.perf_counter()
-        ol.orc_render(h, film, cpu_spp, seed=i, max_depth=a.max_depth, cam_h=cam)
+        st_i, miss_i = ol.orc_render(h, film, cpu_spp, seed=i, max_depth=a.max_depth, cam_h=cam)
+        if i == 0:
+            st, miss = st_i, miss_i
         if i >= warmup:
             times.append(time.perf_counter() - t0)
     sec = sum(times) / len(times)
-    return {"value": paths / sec / 1e6, "unit": "Mpaths/s", "cores": os.cpu_count(), "kind": "port",
-            "sample": f"centred {cw}x{ch} crop of the {a.width}x{a.height} film, {cpu_spp} spp ({paths} paths, {sec:.2f} s/step)"}, sec
+    out = {"value": paths / sec / 1e6, "unit": "Mpaths/s", "cores": os.cpu_count(), "kind": "port",
+           "sample": f"oracle port (OpenMP), centred {cw}x{ch} crop of the {a.width}x{a.height} film, {cpu_spp} spp ({paths} paths, {sec:.2f} s/step)"}
+    if keep_image:
+        out["image"], out["lens_miss"] = ol.develop(st), int(miss)
+    return out, sec
+
+
+def reference_sample(a, steps=1, warmup=0):
+    """The CPU arm proper: the REFERENCE's own scalar_rgb build (tools/build_reference.sh -> baseline/_ref, shipped to the GPU box)
+    renders the same scene over the FULL film at --ref-spp samples per pixel with every host core, in a subprocess that never
+    imports the product (tools/ref_bench.py). None if the build is not there."""
+    py = os.path.join(ROOT, "baseline", "_ref", a.ref_flavour, "python")
+    if not os.path.isdir(os.path.join(py, "mitsuba")):
+        return None
+    env = dict(os.environ); env["PYTHONPATH"] = py; env.pop("OMP_NUM_THREADS", None)
+    # the build tree the extension modules' RUNPATH names does not exist on the GPU box: the libraries travel next to them
+    env["LD_LIBRARY_PATH"] = os.pathsep.join([os.path.join(py, "mitsuba"), os.path.join(py, "drjit"), env.get("LD_LIBRARY_PATH", "")])
+    cmd = [sys.executable, os.path.join(ROOT, "tools", "ref_bench.py"), "--workload", "c5", "--width", str(a.width), "--height", str(a.height),
+           "--n-side", str(a.n_side), "--lens", a.lens, "--max-depth", str(a.max_depth), "--spp", str(a.ref_spp),
+           "--steps", str(steps), "--warmup", str(warmup)]
+    try:
+        out = subprocess.run(cmd, capture_output=True, text=True, timeout=1500, env=env, cwd="/tmp")
+        r = json.loads([ln for ln in out.stdout.splitlines() if ln.startswith("{")][-1])
+    except Exception as e:
+        sys.stderr.write(f"reference build failed to run: {e}\n{out.stderr[-2000:] if 'out' in dir() else ''}\n")
+        return None
+    return {"value": r["paths"] / r["seconds"] / 1e6, "unit": "Mpaths/s", "cores": r["threads"], "kind": "reference",
+            "sample": f"the reference's own scalar_rgb build ({a.ref_flavour}: "
+                      + ("-march=x86-64-v3, -ffp-contract=fast" if a.ref_flavour == "native" else "plain x86-64, -ffp-contract=off")
+                      + f"), full {a.width}x{a.height} film at {a.ref_spp} spp ({r['paths']} paths, {r['seconds']:.2f} s/step, native kd-tree, "
+                        f"scene load {r['scene_load_s']:.1f} s not timed)",
+            "image_mean": r["mean"]}, r["seconds"]
 
 
 def doublet_table(mi):
@@ -212,10 +269,13 @@ def main():
             return
         # torchrun exports OMP_NUM_THREADS=1; the CPU arm is meant to use every host core (libgomp reads this at load time)
         os.environ["OMP_NUM_THREADS"] = str(os.cpu_count())
-        import lensrt as mi   # scene front end only (flat arrays); no kernel of ours runs in this arm
-        d = workload_dict(mi, a)
-        arrays = mi.scene_data_from_dict(d)[0].arrays()
-        cb, sec = cpu_sample(a, arrays, d["sensor"], steps=a.steps, warmup=a.warmup)
+        got = reference_sample(a, steps=a.steps, warmup=a.warmup)      # the reference's own build: nothing of ours is loaded
+        if got is None:     # no reference build in the tree: the oracle port (needs the scene front end of the package)
+            import lensrt as mi
+            d = workload_dict(mi, a)
+            arrays = mi.scene_data_from_dict(d)[0].arrays()
+            got = cpu_sample(a, arrays, d["sensor"], steps=a.steps, warmup=a.warmup)
+        cb, sec = got
         line = {"impl": "reference", "metric": "Mpaths/s", "value": cb["value"], "unit": "Mpaths/s", "n_gpus": a.gpus, "steps": a.steps,
                 "warmup": a.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
                 "dtype": "f32", "data": "synthetic", "config": config, "cpu_baseline": cb,
@@ -233,11 +293,16 @@ def main():
     d = workload_dict(mi, a)
     t0 = time.perf_counter()
     scene = mi.load_dict(d)
+    parity_crop.scene = scene
     build_s = time.perf_counter() - t0
     sensor = scene.sensors()[0]
     H, W = a.height, a.width
-    storage = torch.zeros((H, W, 4), dtype=torch.float32, device="cuda")
+    # two film accumulators: the all-reduce of step i (communication stream) overlaps the render kernel of step i+1
+    storages = [torch.zeros((H, W, 4), dtype=torch.float32, device="cuda") for _ in range(2 if world > 1 else 1)]
+    comm = torch.cuda.Stream() if world > 1 else None
+    reduced = [None, None]          # event: the all-reduce that last used storages[k] has finished
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    step_no = [0]
     host_img = torch.empty((H, W, 3), dtype=torch.float32).pin_memory()
     host_lens = torch.from_numpy(sensor.interfaces().copy()).pin_memory()
     paths_per_step = H * W * a.spp_per_step
@@ -245,22 +310,43 @@ def main():
     def step(seed, e2e=False):
         if e2e:   # parameters_changed(): lens table from pinned host memory -> device
             sensor.set_interfaces(host_lens.numpy())
+        k = step_no[0] % len(storages); step_no[0] += 1
+        storage = storages[k]
+        main = torch.cuda.current_stream()
+        if reduced[k] is not None:
+            main.wait_event(reduced[k])         # the collective that read this accumulator two steps ago is done
         storage.zero_()
         mi.render(scene, seed=seed, spp=a.spp_per_step, develop=False, shard=(rank, world), storage=storage)
-        if world > 1:
-            dist.reduce(storage, dst=0)         # the film is needed on rank 0 only
+        if world > 1:                           # sum of the film accumulators over ranks (all-reduce)
+            done = torch.cuda.Event(); done.record(main)
+            with torch.cuda.stream(comm):
+                comm.wait_event(done)
+                dist.all_reduce(storage)
+                reduced[k] = torch.cuda.Event(); reduced[k].record(comm)
         if e2e and rank == 0:
+            if world > 1:
+                main.wait_event(reduced[k])     # the end-to-end step hands the merged image to the host
             img = mi.develop_rgb(storage)
             host_img.copy_(img, non_blocking=True)
 
+    def drain():
+        for ev in reduced:
+            if ev is not None:
+                torch.cuda.current_stream().wait_event(ev)
+
     def timed(n_steps, e2e, seed0):
-        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(n_steps)]
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
-        for i, (s, e) in enumerate(ev):
-            flush.fill_(i & 0xff)           # L2 flush, outside the timed events
-            s.record(); step(seed0 + i, e2e); e.record()
+        # one timed region around the K steps (the collective of step i overlaps the kernel of step i+1; the last one is
+        # drained inside the region). The L2 flush between steps is a 256 MiB write on the same stream: ~0.1 ms of the step.
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))]
+        ev[0][0].record()
+        for i in range(n_steps):
+            flush.fill_(i & 0xff)
+            step(seed0 + i, e2e)
+        drain()
+        ev[0][1].record()
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
@@ -279,12 +365,18 @@ def main():
     ms = timed(a.steps, False, 0)
     launches = capi.lib.lrt_launch_count() - l0
     stats = scene.stats()
+    if world > 1:    # sum the per-rank counters (every rank traced its own tiles)
+        t = torch.tensor([float(stats[k]) for k in sorted(stats)], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t)
+        stats = {k: int(v) for k, v in zip(sorted(stats), t.tolist())}
     for i in range(min(a.warmup, 2)):
         step(2000 + i, e2e=True)
     ms_e2e = timed(a.steps, True, 100)
     sampler.stop_flag = True
     # adjoint of the path loop (reflectance / radiance gradients): same workload, one pass of lrt_render_backward per step
     gstore = torch.randn((H, W, 4), dtype=torch.float32, device="cuda")
+    drain(); torch.cuda.synchronize()
+
     def bstep(seed):
         gb, ge = mi.render_backward(scene, gstore, seed=seed, spp=a.spp_per_step, shard=(rank, world))
         if world > 1:
@@ -315,7 +407,7 @@ def main():
         e2e_v = paths_per_step / (ms_e2e * 1e-3) / 1e6
         # algorithmic bytes of the dominant (only) kernel per launch: BVH nodes + triangles fetched, splat taps, film
         fp = 25 if a.spp_per_step >= 4 else 16
-        alg_bytes = world * (stats["bvh_nodes"] * 80 + stats["triangles"] * 48 + stats["samples"] * fp * 16) + H * W * 16
+        alg_bytes = stats["bvh_nodes"] * 80 + stats["triangles"] * 48 + stats["samples"] * fp * 16 + H * W * 16 * world
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
         peak = peaks.get("hbm_gbs", 6546.9)
         ach = alg_bytes / world / (ms * 1e-3) / 1e9
@@ -327,21 +419,57 @@ def main():
                 traffic, traffic_src = t["dram_bytes_per_launch"] / 1e9, t.get("source")
                 ncu_facts = {k: t[k] for k in ("issue_slot_utilisation", "active_lanes_per_instruction", "l1_hit_rate", "l2_hit_rate",
                                                "top_stalls_per_issue") if k in t}
+        # measured ceilings of this box (lrt_measure_peaks: FMA / issue / L1 / L2 / shared-atomic micro-kernels) and the stage
+        # rooflines SURVEY.md 8(d) asks for: counters per launch from the committed ncu capture of this very workload
+        # (profiles/render_traffic.json), time measured live
+        pk = (C.c_double * 6)()
+        capi.check(capi.lib.lrt_measure_peaks(pk, None))
+        measured = {"fp32_tflops": pk[0], "issue_gwarp_inst_per_s": pk[1], "l1_hit_gbs": pk[2], "l2_hit_gbs": pk[3],
+                    "smem_atomic_g_per_s": pk[4], "sm_mhz": pk[5], "hbm_gbs": peak,
+                    "how": "lrt_measure_peaks (csrc/lrt_peaks.cu), best of 3, CUDA events; hbm_gbs from MEASURED_PEAKS.json"}
+        stages = None
+        if tj and os.path.exists(tj):
+            t = json.load(open(tj))
+            if t.get("counters") and traffic is not None:
+                c, sec = t["counters"], ms * 1e-3
+                inst, tinst = c["smsp__inst_executed.sum"], c["smsp__thread_inst_executed.sum"]
+                stages = [
+                    {"stage": "whole kernel (lens trace, traversal, shading)", "bound": "issue", "achieved": inst / sec / 1e9, "peak": pk[1],
+                     "unit": "G warp-inst/s", "frac": inst / sec / 1e9 / pk[1], "lane_frac": tinst / inst / 32.0,
+                     "note": "frac x lane_frac = share of the SMs' lane-issue capacity doing useful work"},
+                    {"stage": "FP32 pipe (FFMA/FMUL/FADD)", "bound": "fp32", "achieved": 2 * c.get("sm__inst_executed_pipe_fma.sum", 0) * 32 / sec / 1e12,
+                     "peak": pk[0], "unit": "TFLOP/s (warp-level FMA-pipe instructions x 32 x 2)",
+                     "frac": 2 * c.get("sm__inst_executed_pipe_fma.sum", 0) * 32 / sec / 1e12 / pk[0]},
+                    {"stage": "BVH traversal + stack (L1)", "bound": "l1", "achieved": c["l1tex__t_sectors.sum"] * 32 / sec / 1e9, "peak": pk[2],
+                     "unit": "GB/s of L1 sectors", "frac": c["l1tex__t_sectors.sum"] * 32 / sec / 1e9 / pk[2]},
+                    {"stage": "BVH traversal (L2)", "bound": "l2", "achieved": c["lts__t_sectors.sum"] * 32 / sec / 1e9, "peak": pk[3],
+                     "unit": "GB/s of L2 sectors", "frac": c["lts__t_sectors.sum"] * 32 / sec / 1e9 / pk[3]},
+                    {"stage": "DRAM", "bound": "hbm", "achieved": t["dram_bytes_per_launch"] / sec / 1e9, "peak": peak, "unit": "GB/s",
+                     "frac": t["dram_bytes_per_launch"] / sec / 1e9 / peak, "note": "the scene lives in L2: DRAM is not a bound"},
+                ]
+        traced = stats["samples"] - stats["lens_misses"]
         line = {"metric": "Mpaths/s", "value": value, "unit": "Mpaths/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
                 "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
                 "data": "synthetic", "config": config,
                 "e2e": {"value": e2e_v, "unit": "Mpaths/s", "h2d_bytes_per_step": int(host_lens.numel() * 4),
                         "d2h_bytes_per_step": int(H * W * 3 * 4), "ms_per_step": ms_e2e},
                 "gpu_launches": int(launches),
+                "paths": {"samples_per_step": int(stats["samples"]), "lens_miss_fraction": stats["lens_misses"] / max(stats["samples"], 1),
+                          "traced_Mpaths_per_s": traced / (ms * 1e-3) / 1e6,
+                          "note": "value counts every film sample (W*H*spp, the metric's definition); vignetted samples trace no ray, "
+                                  "traced_Mpaths_per_s counts only the paths that left the lens"},
+                "measured_peaks": measured, "roofline_stages": stages,
                 "clocks": sampler.result(),
                 "roofline": {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": traffic,
                              "traffic_unit": "GB per launch (ncu dram read+write)", "traffic_source": traffic_src,
                              "algorithmic_gb_per_launch": alg_bytes / world / 1e9,
                              "ncu": ncu_facts,   # what actually bounds the kernel (issue slots / latency), from the same capture
                              "kernel": "lrt::k_render", "peak_source": "MEASURED_PEAKS.json hbm_gbs (burst copy)",
-                             "note": "algorithmic bytes = nodes*80 + triangles*48 + samples*taps*16 + film; the kernel is "
-                                     "latency/issue bound (divergent traversal), see DESIGN.md"},
-                "stats": {k: int(v) * world for k, v in stats.items()}, "scene_build_s": build_s,
+                             "dram_achieved_gbs": (traffic / (ms * 1e-3)) if traffic is not None else None,
+                             "note": "contract figure: algorithmic bytes (nodes*80 + triangles*48 + samples*taps*16 + film) / launch time vs the "
+                                     "measured HBM copy rate. Those bytes are served by L1/L2 (DRAM traffic per launch = `traffic`, "
+                                     "dram_achieved_gbs): the kernel is issue / latency bound, see roofline_stages and DESIGN.md 3"},
+                "stats": {k: int(v) for k, v in stats.items()}, "scene_build_s": build_s,
                 "bvh": scene.info()}
         line["render_backward"] = {"value": paths_per_step / (ms_bwd.item() * 1e-3) / 1e6, "unit": "Mpaths/s", "ms_per_step": ms_bwd.item(),
                                    "what": "lrt_render_backward on the same workload: gradients of diffuse reflectance / conductor "
@@ -351,7 +479,12 @@ def main():
         if pupil is not None:
             line["exit_pupil_lut"] = pupil
         if not a.no_cpu_baseline and world == 1:     # the contract wants the CPU baseline on rank 0 at N = 1 only
-            line["cpu_baseline"], _ = cpu_sample(a, scene.arrays, d["sensor"])
+            port, _ = cpu_sample(a, scene.arrays, d["sensor"], keep_image=True)
+            ref = reference_sample(a)
+            line["cpu_baseline_port"] = {k: v for k, v in port.items() if k not in ("image", "lens_miss")}
+            line["cpu_baseline"] = ref[0] if ref else line["cpu_baseline_port"]
+            # parity on the headline workload itself: the same centred crop, same seed, same spp on the GPU vs the oracle port
+            line["parity"] = parity_crop(mi, torch, a, d, port)
             if lens_grad is not None:
                 line["lens_grad"]["cpu_baseline"] = lens_grad_cpu(mi, a)
         print(json.dumps(line))

@@ -34,6 +34,10 @@ int lrt_version(void);
 uint64_t lrt_launch_count(void);
 int lrt_device_count(void);
 int lrt_set_device(int device);
+/* Measured ceilings of the current device for the roofline report (the path is neither HBM- nor tensor-bound; SURVEY.md 8d
+ * asks for an FMA micro-kernel): out6 = FP32 TFLOP/s, G warp-instructions issued /s, L1-hit GB/s, L2-hit GB/s,
+ * G shared-memory float atomics /s, SM clock MHz during the run. A few milliseconds per figure; synchronous. */
+int lrt_measure_peaks(double *out6, void *stream);
 
 /* ---------------------------------------------------------------------------------------- film geometry
  * Film::size/crop_size/crop_offset + the fork's physical size (include/mitsuba/render/film.h:193-198,

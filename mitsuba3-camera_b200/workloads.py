@@ -4,11 +4,12 @@ from __future__ import annotations
 
 import numpy as np
 
-from .scene import cornell_box
-from .transform import Transform4f
+try:
+    from .transform import Transform4f
+except ImportError:      # loaded by path (tools/ref_bench.py: the reference arm must not import the product package)
+    from transform import Transform4f
 
 f32 = np.float32
-CU_ETA, CU_K = [0.200438, 0.924033, 1.102212], [3.912949, 2.452848, 2.142188]
 
 
 def _value_noise(n, rng, octaves=5, base=6):
@@ -60,7 +61,7 @@ def heightfield_scene(n_side=708, width=3840, height=2160, spp=16, lens_design="
             continue
         used, inv = np.unique(sel.reshape(-1), return_inverse=True)
         bsdf = ({"type": "diffuse", "reflectance": {"type": "rgb", "value": albedo[m].tolist()}} if m < n_diffuse
-                else {"type": "conductor", "eta": CU_ETA, "k": CU_K})
+                else {"type": "conductor", "material": "Cu"})
         d[f"field{m}"] = {"type": "mesh", "vertices": verts[used], "faces": inv.reshape(-1, 3).astype(np.int32), "bsdf": bsdf}
     black = {"type": "diffuse", "reflectance": {"type": "rgb", "value": [0.0, 0.0, 0.0]}}
     d["sun"] = {"type": "rectangle", "to_world": T.translate([0, 9.0, 0]).rotate([1, 0, 0], 90).scale([5.0, 5.0, 1.0]),
@@ -84,6 +85,7 @@ def heightfield_scene(n_side=708, width=3840, height=2160, spp=16, lens_design="
 
 def cornell_config1(res=256, spp=64, max_depth=6):
     """Config 1: mi.cornell_box(), 256x256, 64 spp, path max_depth=6."""
+    from .scene import cornell_box
     d = cornell_box()
     d["integrator"]["max_depth"] = max_depth
     d["sensor"]["film"]["width"] = d["sensor"]["film"]["height"] = res

@@ -1,7 +1,7 @@
 """Generates tests/golden/ref_integrator.npz and tests/golden/ref_renders.npz with the REFERENCE's own scalar_rgb build
 (tools/build_reference.sh pinned -> baseline/_ref/pinned). Run in the build container only:
 
-    PYTHONPATH=baseline/_ref/pinned/python python tests/golden/gen_ref_integrator.py
+    R=baseline/_ref/pinned/python; LD_LIBRARY_PATH=$R/mitsuba:$R/drjit PYTHONPATH=$R python tests/golden/gen_ref_integrator.py
 
 Function-level vectors (perspective sample_ray, BSDF sample / eval_pdf, emitter sampling, ray_intersect with the full
 surface interaction, bitmap texture lookups) pin rows P0 / B1 / I2 / T1 of SURVEY.md 8(a); the renders pin I1 and the scalar
