@@ -30,7 +30,6 @@ constexpr int kFifo = 64, kFifoWords = 14;      // camera-ray FIFO per warp: o[3
 constexpr int kQueue = 96, kQueueWords = 5;     // splat queue per warp: sx sy r g b. Drained (32 at a time) at ONE place, the top
                                                 // of the warp's loop, where it holds < 32 entries afterwards; camera-ray
                                                 // generation and shading add at most 32 each before the next drain
-constexpr int kMaxChunks = 24;                  // sample chunks per pixel (work-item granularity)
 constexpr int kMaxRec = 12;                     // adjoint: bounces of one path that can receive a BSDF gradient
 constexpr int kGradSlots = 1024;                // adjoint: per-CTA shared accumulators (3 per BSDF, 3 per emitter)
 
@@ -39,12 +38,11 @@ struct RenderArgs {
     const LensSystem *lens;
     FilmParams film;
     uint32_t seed; int spp, max_depth, rr_depth;
-    // work items = (sample chunk, pixel tile), chunk-major: every tile's chunk 0 first, ..., every tile's last chunk last. The
-    // chunks of a pixel's samples [chunk_begin[c], chunk_begin[c+1]) shrink towards the end (launch_render) so that the items
-    // in flight when the work counter runs out are short: the tail of the launch is one SMALL item, not one full tile
-    int tiles_x, n_chunks, chunk_begin[kMaxChunks + 1];
-    int chunk_spp;   // > 0: more chunks than the table holds (tiny films, huge spp): equal chunks of this size instead
-    int shard_index, shard_count; long long n_items, my_tiles;
+    // base work items = (pixel tile, sample chunk), tile-major. The LAST `n_split` base items are handed out in `n_sub`
+    // pieces each (guided self-scheduling): when the work counter runs out, the items still in flight are short, so the
+    // tail of the launch is a fraction of a tile's work while all but a few per cent of the samples run in full-size items
+    int tiles_x, n_chunks, chunk_spp, n_sub;
+    int shard_index, shard_count; long long n_items, n_whole;
     int pad, smem_w, smem_h, exit_drop, leaf_min;
     unsigned long long *counter;
     float *accum;
@@ -133,14 +131,16 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
         if (item >= A.n_items) break;
         for (int i = lane; i < tile_elems; i += 32) tile[i] = 0.f;
         __syncwarp();
-        const int chunk = (int) (item / A.my_tiles);
-        const long long tile_id = (long long) A.shard_index + (item - chunk * A.my_tiles) * A.shard_count;
+        long long base = item; int sub = -1;
+        if (item >= A.n_whole) { const long long k = item - A.n_whole; base = A.n_whole + k / A.n_sub; sub = (int) (k % A.n_sub); }
+        const int chunk = (int) (base % A.n_chunks);
+        const long long tile_id = (long long) A.shard_index + (base / A.n_chunks) * A.shard_count;
         const int tx = (int) (tile_id % A.tiles_x), ty = (int) (tile_id / A.tiles_x);
         const int px = tx * kTileW + lane, py = ty;                      // the pixel this lane GENERATES samples for
         const bool in_film = px < F.size_x && py < F.size_y;
         const int ox = tx * kTileW + F.border - A.pad, oy = ty * kTileH + F.border - A.pad;   // tensor coords of smem (0,0)
-        const int j0 = A.chunk_spp > 0 ? chunk * A.chunk_spp : A.chunk_begin[chunk];
-        const int j1 = A.chunk_spp > 0 ? min(A.spp, j0 + A.chunk_spp) : A.chunk_begin[chunk + 1];
+        int j0 = chunk * A.chunk_spp, j1 = min(A.spp, j0 + A.chunk_spp);
+        if (sub >= 0) { const int len = max(0, j1 - j0); j1 = j0 + (len * (sub + 1)) / A.n_sub; j0 += (len * sub) / A.n_sub; }
         const int n_rounds = py < F.size_y ? max(0, j1 - j0) : 0;   // generation rounds of this warp
         const uint32_t idx_base = (uint32_t) (py * F.size_x + px) * (uint32_t) A.spp;
         const float posx = (float) (px + F.off_x), posy = (float) (py + F.off_y);
@@ -490,28 +490,19 @@ int launch_render(const lrt_scene *sc, lrt_sensor *sensor, const lrt_film_desc *
     int n_chunks = 1;
     while (my_tiles * n_chunks < 4 * resident * kWarps && n_chunks * 2 <= rp->spp) n_chunks *= 2;
     if (rp->chunks > 0) n_chunks = std::min(rp->chunks, rp->spp);
-    // equal chunks first; then the LAST chunk (the one every tile still has to do when the counter runs out) is cut into a
-    // 3/4 piece and four small ones, e.g. 64 spp -> [0, 48, 52, 56, 60, 64): the launch's tail shrinks 16-fold for four more
-    // tile flushes per pixel tile (LRT_TAIL_SPLIT=0 turns it off)
-    if (n_chunks > kMaxChunks - 4) {
-        A.chunk_spp = (rp->spp + n_chunks - 1) / n_chunks;
-        n_chunks = (rp->spp + A.chunk_spp - 1) / A.chunk_spp;
-    } else {
-        const int cs = (rp->spp + n_chunks - 1) / n_chunks;
-        int nb = 0;
-        for (int c = 0; c < n_chunks && c * cs < rp->spp; ++c) A.chunk_begin[nb++] = c * cs;
-        const int last0 = A.chunk_begin[nb - 1], last = rp->spp - last0;
+    A.n_chunks = n_chunks; A.chunk_spp = (rp->spp + n_chunks - 1) / n_chunks;
+    A.shard_index = rp->shard_index; A.shard_count = rp->shard_count;
+    // guided tail: the last (resident warps) base items are handed out in pieces of >= 4 spp (LRT_TAIL_SPLIT=0 turns it off;
+    // an explicit rp->chunks does too). Those pieces are ~1/16 of a full item: one resident warp's worth of them keeps every
+    // warp busy while the last full-size items drain.
+    {
+        const long long n_base = my_tiles * n_chunks;
         const char *e = getenv("LRT_TAIL_SPLIT");
-        const bool split = rp->chunks == 0 && last >= 16 && nb + 4 <= kMaxChunks && !(e && atoi(e) == 0);
-        if (split) {
-            const int big = (last * 3 / 4) & ~3, rest = last - big;
-            for (int k = 0; k < 4; ++k) A.chunk_begin[nb++] = last0 + big + (rest * k) / 4;
-        }
-        A.chunk_begin[nb] = rp->spp;
-        n_chunks = nb;
+        int n_sub = std::min(16, A.chunk_spp / 4);
+        long long n_split = std::min(n_base, resident * kWarps);
+        if (rp->chunks > 0 || n_sub < 2 || (e && atoi(e) == 0)) { n_sub = 1; n_split = 0; }
+        A.n_sub = n_sub; A.n_whole = n_base - n_split; A.n_items = A.n_whole + n_split * n_sub;
     }
-    A.n_chunks = n_chunks; A.my_tiles = my_tiles;
-    A.shard_index = rp->shard_index; A.shard_count = rp->shard_count; A.n_items = my_tiles * n_chunks;
     // every launch takes its own work counter from a ring (renders of one scene may overlap on different streams); the
     // statistics block is per scene: it describes the last render launched and is meaningless while two overlap
     unsigned long long *ctr = sc->d_counter + (sc->launch_seq.fetch_add(1, std::memory_order_relaxed) % kCounterRing);

@@ -411,7 +411,8 @@ class Scene:
 
     def __del__(self):
         if getattr(self, "handle", None):
-            capi.lib.lrt_scene_destroy(self.handle)
+            if capi is not None and getattr(capi, "lib", None) is not None:     # (module globals are gone at interpreter exit)
+                capi.lib.lrt_scene_destroy(self.handle)
             self.handle = None
 
     def sensors(self):
