@@ -35,16 +35,24 @@ def parse():
     p.add_argument("--ref-spp", type=int, default=1, help="spp of the bounded sample the reference's own scalar_rgb build renders (FULL film: "
                                                             "the same vignetting mix as the GPU's step)")
     p.add_argument("--ref-flavour", default="native", choices=["native", "pinned"], help="which build under baseline/_ref is timed")
-    p.add_argument("--width", type=int, default=3840)
-    p.add_argument("--height", type=int, default=2160)
+    p.add_argument("--workload", default="c5", choices=["c5", "c4"],
+                   help="c5 (default, the configuration the metric is quoted on): 1M-triangle height field, `gauss` lens, 3840x2160; "
+                        "c4: 64 textured boxes through the Nikon `exp2a` stack with exit-pupil sampling, 1920x1080 (1024 spp = 16 steps)")
+    p.add_argument("--width", type=int, default=None)
+    p.add_argument("--height", type=int, default=None)
     p.add_argument("--n-side", type=int, default=708)
-    p.add_argument("--lens", default="gauss")
+    p.add_argument("--n-boxes", type=int, default=64)
+    p.add_argument("--tex-size", type=int, default=2048)
+    p.add_argument("--lens", default=None)
     p.add_argument("--max-depth", type=int, default=6)
     p.add_argument("--cpu-crop", type=int, nargs=2, default=[1280, 720], help="crop window of the CPU baseline sample")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-lens-grad", action="store_true", help="skip the lens-gradient iterations/s section (C2 / C3 shapes)")
     p.add_argument("--lens-iters", type=int, default=10)
-    return p.parse_args()
+    a = p.parse_args()
+    dflt = {"c5": (3840, 2160, "gauss"), "c4": (1920, 1080, "exp2a")}[a.workload]
+    a.width, a.height, a.lens = a.width or dflt[0], a.height or dflt[1], a.lens or dflt[2]
+    return a
 
 
 class ClockSampler(threading.Thread):
@@ -76,6 +84,9 @@ class ClockSampler(threading.Thread):
 
 
 def workload_dict(mi, a):
+    if a.workload == "c4":
+        return mi.workloads.textured_boxes_scene(n_boxes=a.n_boxes, width=a.width, height=a.height, spp=a.spp_per_step, lens_design=a.lens,
+                                                 max_depth=a.max_depth, tex_size=a.tex_size)
     return mi.workloads.heightfield_scene(n_side=a.n_side, width=a.width, height=a.height, spp=a.spp_per_step, lens_design=a.lens,
                                 max_depth=a.max_depth)
 
@@ -115,6 +126,8 @@ def cpu_sample(a, scene_arrays, sensor_dict, steps=1, warmup=0, keep_image=False
     tw = sensor_dict["to_world"].matrix
     cam = ol.orc_camera(ld.design(a.lens, {"object_distance": sensor_dict["object_distance"]}), film, to_world=tw,
                         near=sensor_dict["near_clip"], far=sensor_dict["far_clip"], object_distance=sensor_dict["object_distance"])
+    if sensor_dict.get("sample_exit_pupil"):     # the 64 x 2^20-ray LUT on the host: ~20 s, not timed
+        ol.cam_exit_pupil(ol.oracle(), "orc", cam, shutter_open_time=sensor_dict.get("shutter_close", 0.0) - sensor_dict.get("shutter_open", 0.0))
     cpu_spp = min(a.cpu_spp, a.spp_per_step)
     paths = cw * ch * cpu_spp
     times = []
@@ -144,7 +157,8 @@ def reference_sample(a, steps=1, warmup=0):
     env = dict(os.environ); env["PYTHONPATH"] = py; env.pop("OMP_NUM_THREADS", None)
     # the build tree the extension modules' RUNPATH names does not exist on the GPU box: the libraries travel next to them
     env["LD_LIBRARY_PATH"] = os.pathsep.join([os.path.join(py, "mitsuba"), os.path.join(py, "drjit"), env.get("LD_LIBRARY_PATH", "")])
-    cmd = [sys.executable, os.path.join(ROOT, "tools", "ref_bench.py"), "--workload", "c5", "--width", str(a.width), "--height", str(a.height),
+    cmd = [sys.executable, os.path.join(ROOT, "tools", "ref_bench.py"), "--workload", a.workload, "--n-boxes", str(a.n_boxes),
+           "--tex-size", str(a.tex_size), "--width", str(a.width), "--height", str(a.height),
            "--n-side", str(a.n_side), "--lens", a.lens, "--max-depth", str(a.max_depth), "--spp", str(a.ref_spp),
            "--steps", str(steps), "--warmup", str(warmup)]
     try:
@@ -258,9 +272,12 @@ def lens_grad_cpu(mi, a):
 def main():
     a = parse()
     rank = int(os.environ.get("RANK", 0)); world = int(os.environ.get("WORLD_SIZE", 1)); local = int(os.environ.get("LOCAL_RANK", 0))
-    config = {"workload": f"C5: {2 * (a.n_side - 1) ** 2}-triangle diffuse/conductor height field, `{a.lens}` realistic lens, "
-                          f"{a.width}x{a.height}, path max_depth={a.max_depth}, {a.spp_per_step} spp per step "
-                          f"(1/{4096 // max(a.spp_per_step, 1)} of the 4096-spp job)",
+    what = (f"C5: {2 * (a.n_side - 1) ** 2}-triangle diffuse/conductor height field, `{a.lens}` realistic lens" if a.workload == "c5" else
+            f"C4: ground + {a.n_boxes} boxes (vertex normals + uvs), {a.tex_size}^2 RGB bitmap texture (bilinear), Cu conductors, "
+            f"Nikon `{a.lens}` 22-interface lens with exit-pupil sampling")
+    job = 4096 if a.workload == "c5" else 1024
+    config = {"workload": f"{what}, {a.width}x{a.height}, path max_depth={a.max_depth}, {a.spp_per_step} spp per step "
+                          f"(1/{job // max(a.spp_per_step, 1)} of the {job}-spp job)",
               "l2": "flushed between steps (256 MiB write); BVH+triangles ~60 MB are L2-resident by design",
               "parallelism": f"tile-sharded x{world}, one NCCL reduce of the film to rank 0 per step" if world > 1 else "single GPU"}
 

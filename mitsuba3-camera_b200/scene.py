@@ -120,7 +120,10 @@ def bsdf_row(d: dict, textures=None) -> np.ndarray:
         if isinstance(refl, dict) and refl.get("type") == "bitmap":
             if textures is None:
                 raise ValueError("a textured BSDF needs a scene to live in")
-            textures.append(load_texture(refl)); r[15] = len(textures)
+            hit = next((i for i, t in enumerate(textures) if t.get("_src") is refl), None)    # one dictionary shared by many BSDFs = one texture
+            if hit is None:
+                textures.append(dict(load_texture(refl), _src=refl)); hit = len(textures) - 1
+            r[15] = hit + 1
             refl = None
         r[0] = 0; r[2:5] = _rgb(refl, [0.5, 0.5, 0.5])
     elif t == "conductor":

@@ -91,3 +91,58 @@ def cornell_config1(res=256, spp=64, max_depth=6):
     d["sensor"]["film"]["width"] = d["sensor"]["film"]["height"] = res
     d["sensor"]["sampler"]["sample_count"] = spp
     return d
+
+
+def lowpass_texture(n=2048, seed=0, passes=3, radius=None):
+    """Config 4's texture: numpy.random.default_rng(seed).random((n, n, 3)) low-passed (repeated box blur, wrap-around) and
+    stretched back to [0.05, 0.95]; float32 [n, n, 3]."""
+    rng = np.random.default_rng(seed)
+    a = rng.random((n, n, 3), dtype=np.float32).astype(np.float64)
+    r = radius if radius is not None else max(1, n // 64)
+    for _ in range(passes):
+        for axis in (0, 1):
+            c = np.cumsum(np.concatenate([a.take(range(n - r - 1, n), axis), a, a.take(range(0, r), axis)], axis), axis)
+            hi = c.take(range(2 * r + 1, n + 2 * r + 1), axis); lo = c.take(range(0, n), axis)
+            a = (hi - lo) / (2 * r + 1)
+    a -= a.min(axis=(0, 1), keepdims=True); a /= np.maximum(a.max(axis=(0, 1), keepdims=True), 1e-12)
+    return (0.05 + 0.9 * a).astype(f32)
+
+
+def textured_boxes_scene(n_boxes=64, width=1920, height=1080, spp=64, lens_design="exp2a", max_depth=6, seed=0, tex_size=2048,
+                         sensor="realisticlens", sensor_extra=None):
+    """Config 4: ground plane + n_boxes boxes (cube shapes: per-vertex normals and uvs), one RGB bitmap texture (bilinear,
+    repeat) on the ground and on every other box, one area light, imaged through the Nikon `exp2a` 22-interface stack with
+    exit-pupil sampling (rear-element sampling vignettes ~99 % of the samples of this design on a 35 mm film)."""
+    rng = np.random.default_rng(seed)
+    T = Transform4f
+    tex = {"type": "bitmap", "data": lowpass_texture(tex_size, seed), "filter_type": "bilinear", "wrap_mode": "repeat", "raw": True}
+    d = {"type": "scene", "integrator": {"type": "path", "max_depth": max_depth, "rr_depth": 5},
+         "ground": {"type": "rectangle", "to_world": T.rotate([1, 0, 0], -90).scale(12.0),
+                    "bsdf": {"type": "diffuse", "reflectance": tex}},
+         "lamp": {"type": "rectangle", "to_world": T.translate([0, 9.0, 2.0]).rotate([1, 0, 0], 90).scale([4.0, 4.0, 1.0]),
+                  "bsdf": {"type": "diffuse", "reflectance": {"type": "rgb", "value": [0.0, 0.0, 0.0]}},
+                  "emitter": {"type": "area", "radiance": {"type": "rgb", "value": [9.0, 8.5, 8.0]}}}}
+    side = int(np.ceil(np.sqrt(n_boxes)))
+    for b in range(n_boxes):
+        gx, gz = b % side, b // side
+        pos = [(gx - (side - 1) / 2) * 2.2 + rng.uniform(-0.3, 0.3), 0.0, (gz - (side - 1) / 2) * 2.2 + rng.uniform(-0.3, 0.3)]
+        sx, sy, sz = rng.uniform(0.35, 0.8), rng.uniform(0.3, 1.6), rng.uniform(0.35, 0.8)
+        pos[1] = sy
+        if b % 2 == 0:
+            bsdf = {"type": "diffuse", "reflectance": tex}
+        elif b % 8 == 1:
+            bsdf = {"type": "conductor", "material": "Cu"}
+        else:
+            bsdf = {"type": "diffuse", "reflectance": {"type": "rgb", "value": rng.uniform(0.2, 0.8, 3).tolist()}}
+        d[f"box{b:02d}"] = {"type": "cube", "to_world": T.translate(pos).rotate([0, 1, 0], float(rng.uniform(0, 90))).scale([sx, sy, sz]),
+                            "bsdf": bsdf}
+    tw = T.look_at(origin=[0.0, 7.0, 16.0], target=[0.0, 0.5, 0.0], up=[0, 1, 0])
+    film = {"type": "hdrfilm", "width": width, "height": height, "rfilter": {"type": "gaussian"}, "pixel_format": "rgb"}
+    smp = {"type": "independent", "sample_count": spp}
+    if sensor == "realisticlens":
+        d["sensor"] = {"type": "realisticlens", "lens_design": lens_design, "object_distance": 17.0, "to_world": tw, "near_clip": 1e-2,
+                       "far_clip": 1e3, "sample_exit_pupil": True, "shutter_open": 0.0, "shutter_close": 1.0, "film": film, "sampler": smp}
+        d["sensor"].update(sensor_extra or {})
+    else:
+        d["sensor"] = {"type": "perspective", "fov": 40.0, "to_world": tw, "near_clip": 1e-2, "far_clip": 1e3, "film": film, "sampler": smp}
+    return d

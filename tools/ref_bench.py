@@ -52,6 +52,8 @@ def to_reference(d, tmp):
             out[k] = to_reference(v, tmp)
         elif hasattr(v, "matrix"):
             out[k] = mi.ScalarTransform4f(np.asarray(v.matrix, np.float32))
+        elif isinstance(v, np.ndarray) and k == "data":      # in-memory bitmap texture
+            out[k] = mi.TensorXf(np.ascontiguousarray(v, np.float32))
         else:
             out[k] = v
     return out
@@ -62,6 +64,7 @@ def main():
     p.add_argument("--workload", default="c5")
     p.add_argument("--width", type=int, default=3840); p.add_argument("--height", type=int, default=2160)
     p.add_argument("--n-side", type=int, default=708); p.add_argument("--lens", default="gauss")
+    p.add_argument("--n-boxes", type=int, default=64); p.add_argument("--tex-size", type=int, default=2048)
     p.add_argument("--max-depth", type=int, default=6); p.add_argument("--spp", type=int, default=2)
     p.add_argument("--crop", type=int, nargs=4, default=None, help="crop_width crop_height offset_x offset_y")
     p.add_argument("--steps", type=int, default=1); p.add_argument("--warmup", type=int, default=0)
@@ -78,6 +81,9 @@ def main():
     with tempfile.TemporaryDirectory() as tmp:
         if a.workload == "c5":
             d = wl.heightfield_scene(n_side=a.n_side, width=a.width, height=a.height, spp=a.spp, lens_design=a.lens, max_depth=a.max_depth)
+        elif a.workload == "c4":
+            d = wl.textured_boxes_scene(n_boxes=a.n_boxes, width=a.width, height=a.height, spp=a.spp, lens_design=a.lens, max_depth=a.max_depth,
+                                        tex_size=a.tex_size)
         elif a.workload == "c1":
             d = mi.cornell_box(); d["integrator"]["max_depth"] = a.max_depth
             d["sensor"]["film"]["width"] = a.width; d["sensor"]["film"]["height"] = a.height
@@ -86,7 +92,7 @@ def main():
         if a.crop:
             d["sensor"]["film"].update(crop_width=a.crop[0], crop_height=a.crop[1], crop_offset_x=a.crop[2], crop_offset_y=a.crop[3])
         t0 = time.perf_counter()
-        scene = mi.load_dict(to_reference(d, tmp) if a.workload == "c5" else d)
+        scene = mi.load_dict(to_reference(d, tmp) if a.workload in ("c5", "c4") else d)
         load_s = time.perf_counter() - t0
     cw, ch = (a.crop[0], a.crop[1]) if a.crop else (a.width, a.height)
     times = []
