@@ -215,12 +215,15 @@ typedef struct lrt_render_params {
 int lrt_render(const lrt_scene *scene, const lrt_sensor *sensor, const lrt_film_desc *film,
                const lrt_render_params *params, float *accum_dev, void *stream);
 /* Adjoint of lrt_render for the scene parameters the path is linear in — the part of PRBIntegrator.render_backward
- * (src/python/python/ad/integrators/prb.py:59-257, common.py:631-796) that reaches diffuse `reflectance`, conductor
- * `specular_reflectance` and area-light `radiance`. grad_storage_dev = d(loss)/d(accum) [size_y+2b, size_x+2b, 4] (the RGB
- * channels are used; W does not depend on parameters). ADDS to grad_bsdfs_dev [n_bsdfs,16] (columns 2..4) and
- * grad_emitters_dev [n_emitters,16] (columns 0..2), laid out like the tables of lrt_scene_desc; the caller zeroes them.
- * Same samples, streams and Russian-roulette decisions as lrt_render with equal params (sampling is detached, as in prb).
- * One pass: instead of prb's second replay pass, each path keeps (BSDF id, radiance gathered so far) per bounce. */
+ * (src/python/python/ad/integrators/prb.py:59-257, common.py:631-796) that reaches diffuse `reflectance`, conductor /
+ * dielectric `specular_reflectance`, dielectric `specular_transmittance` and area-light `radiance`. grad_storage_dev =
+ * d(loss)/d(accum) [size_y+2b, size_x+2b, 4] (the RGB channels are used; W does not depend on parameters). ADDS to
+ * grad_bsdfs_dev [n_bsdfs,16] (columns 2..4 and, for the transmittance, 11..13) and grad_emitters_dev [n_emitters,16]
+ * (columns 0..2), laid out like the tables of lrt_scene_desc; the caller zeroes them. Same samples, streams and
+ * Russian-roulette decisions as lrt_render with equal params (sampling and the roulette weight are detached, as in prb).
+ * One pass: instead of prb's second replay pass, each path keeps (BSDF id, lobe, radiance gathered so far) per bounce —
+ * at most 16 bounces: max_depth outside [0, 17] is an error (LRT_EINVAL), never a silent truncation. Textured reflectances
+ * receive no gradient. */
 int lrt_render_backward(const lrt_scene *scene, const lrt_sensor *sensor, const lrt_film_desc *film,
                         const lrt_render_params *params, const float *grad_storage_dev, float *grad_bsdfs_dev,
                         float *grad_emitters_dev, void *stream);
@@ -228,8 +231,9 @@ int lrt_render_backward(const lrt_scene *scene, const lrt_sensor *sensor, const 
 int lrt_render_host(const lrt_scene *scene, const lrt_sensor *sensor, const lrt_film_desc *film,
                     const lrt_render_params *params, float *rgb_out);
 /* counters of the last render on this scene: samples, lens misses, rays traced, path-loop iterations,
- * BVH nodes fetched (80 B each), triangles tested (48 B each) */
-int lrt_render_stats(const lrt_scene *scene, uint64_t *out6);
+ * BVH nodes fetched (80 B each), triangles tested (48 B each), traversal-stack clamp events (must be 0: a clamped stack
+ * may miss the closest hit) */
+int lrt_render_stats(const lrt_scene *scene, uint64_t *out7);
 
 /* ------------------------------------------------------------------------------- lens-design spot path
  * Light-traced spot image of a point emitter through the realistic lens and its adjoint: the B200 form of

@@ -30,8 +30,8 @@ constexpr int kFifo = 64, kFifoWords = 14;      // camera-ray FIFO per warp: o[3
 constexpr int kQueue = 96, kQueueWords = 5;     // splat queue per warp: sx sy r g b. Drained (32 at a time) at ONE place, the top
                                                 // of the warp's loop, where it holds < 32 entries afterwards; camera-ray
                                                 // generation and shading add at most 32 each before the next drain
-constexpr int kMaxRec = 12;                     // adjoint: bounces of one path that can receive a BSDF gradient
-constexpr int kGradSlots = 1024;                // adjoint: per-CTA shared accumulators (3 per BSDF, 3 per emitter)
+constexpr int kMaxRec = 16;                     // adjoint: bounces of one path that can receive a BSDF gradient
+constexpr int kGradSlots = 1024;                // adjoint: per-CTA shared accumulators (6 per BSDF: columns 2..4 and 11..13 of its row; 3 per emitter)
 
 struct RenderArgs {
     SceneView sc;
@@ -49,7 +49,7 @@ struct RenderArgs {
     int lens_bytes;                // bytes of the LensSystem staged into shared memory (header + interfaces in use)
     // adjoint (k_render<true>): d(loss)/d(storage) in, parameter gradients out (rows laid out like the scene tables)
     const float *grad_storage; float *grad_bsdfs, *grad_emitters; int n_bsdfs;
-    unsigned long long *stats;     // [0] samples, [1] lens misses, [2] rays, [3] bounces, [4] BVH nodes fetched, [5] triangles tested
+    unsigned long long *stats;     // [0] samples, [1] lens misses, [2] rays, [3] bounces, [4] BVH nodes fetched, [5] triangles tested, [6] traversal-stack clamps
 };
 
 // Shared-memory float atomics are CAS loops on sm_100 (ATOMS.CAST.SPIN): add two neighbouring channels with ONE 64-bit CAS.
@@ -111,11 +111,11 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
     const float scale_x = 1.f / (float) F.size_x, scale_y = 1.f / (float) F.size_y;
     const float offs_x = -(float) F.off_x * scale_x, offs_y = -(float) F.off_y * scale_y;
     // per-lane statistics: 32 bits are enough (W*H*spp < 2^32 is spread over the lanes) and leave 6 registers to the traversal
-    unsigned n_samples = 0, n_miss = 0, n_rays = 0, n_bounces = 0, n_nodes = 0, n_tris = 0;
+    unsigned n_samples = 0, n_miss = 0, n_rays = 0, n_bounces = 0, n_nodes = 0, n_tris = 0, n_clamp = 0;
     uint2 st[kTravStack];
     // adjoint state: gradient slots shared by the CTA, per-path records (BSDF id, radiance gathered before the bounce)
     __shared__ float s_grad[kAdj ? kGradSlots : 1];
-    const bool grad_in_smem = kAdj && (A.n_bsdfs + A.sc.n_emitters) * 3 <= kGradSlots;
+    const bool grad_in_smem = kAdj && A.n_bsdfs * 6 + A.sc.n_emitters * 3 <= kGradSlots;
     if (kAdj) for (int i = tid; i < kGradSlots; i += kCtaThreads) s_grad[i] = 0.f;
     float rec[kAdj ? kMaxRec : 1][4]; int nrec = 0; float3 dL = make_float3(0, 0, 0);
     auto add_grad = [&](int slot, float *gptr, float v) {   // slot: index into s_grad, gptr: the global entry
@@ -264,7 +264,7 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
             // ---- C. the ONE traversal site: path segments and shadow rays of different lanes advance together
             unsigned work = 0;
             bvh_burst(A.sc.bvh, ro, rd, T, st, phase != 0, phase == 2, A.exit_drop, A.leaf_min, work);
-            n_nodes += work & 0xffffu; n_tris += work >> 16;
+            n_nodes += work & 0xffffu; n_tris += (work >> 16) & 0x7fffu; n_clamp += work >> 31;
 
             // ---- D. lanes whose ray is finished shade it
             bool done_path = false; float3 value = make_float3(0, 0, 0);
@@ -294,7 +294,7 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
                                 result += throughput * make_float3(e0.x, e0.y, e0.z) * mw;
                                 if (kAdj) {   // radiance enters linearly
                                     const float3 g = dL * throughput * mw;
-                                    float *gp = A.grad_emitters + 16 * (size_t) em; const int sl = (A.n_bsdfs + em) * 3;
+                                    float *gp = A.grad_emitters + 16 * (size_t) em; const int sl = A.n_bsdfs * 6 + em * 3;
                                     add_grad(sl, gp, g.x); add_grad(sl + 1, gp + 1, g.y); add_grad(sl + 2, gp + 2, g.z);
                                 }
                             }
@@ -333,9 +333,9 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
                     if (active_em) { es = sample_emitter_direction(A.sc, si.p, e_sx, e_sy); wo = si.to_local(es.d); }
                     BsdfResult bs = bsdf_eval_pdf_sample<kAttr>(A.sc, bsdf_id, si.uv, si.wi, wo, s1, s2x, s2y);
                     if (kAdj) {   // everything gathered from here on is linear in this surface's (specular) reflectance
-                        const int btype = (int) __ldg(reinterpret_cast<const float *>(A.sc.bsdfs) + 16 * (size_t) bsdf_id);
-                        if (nrec < kMaxRec && btype != BSDF_DIELECTRIC && __ldg(reinterpret_cast<const float *>(A.sc.bsdfs) + 16 * (size_t) bsdf_id + 15) == 0.f) {   // (textured reflectances are not parameters)
-                            rec[nrec][0] = __int_as_float(bsdf_id); rec[nrec][1] = result.x; rec[nrec][2] = result.y; rec[nrec][3] = result.z; nrec++;
+                        // the sampled lobe's colour: (specular) reflectance, or the dielectric's specular_transmittance
+                        if (nrec < kMaxRec && __ldg(reinterpret_cast<const float *>(A.sc.bsdfs) + 16 * (size_t) bsdf_id + 15) == 0.f) {   // (textured reflectances are not parameters)
+                            rec[nrec][0] = __int_as_float(2 * bsdf_id + (bs.transmitted ? 1 : 0)); rec[nrec][1] = result.x; rec[nrec][2] = result.y; rec[nrec][3] = result.z; nrec++;
                         }
                     }
                     if (active_em) {
@@ -344,7 +344,7 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
                         if (kAdj) {
                             const int cnt = A.sc.n_emitters, ei = cnt > 1 ? min((int) (e_sx * (float) cnt), cnt - 1) : 0;
                             const float4 e0 = __ldg(A.sc.emitters + 5 * (size_t) ei);
-                            float *gp = A.grad_emitters + 16 * (size_t) ei; const int sl = (A.n_bsdfs + ei) * 3;
+                            float *gp = A.grad_emitters + 16 * (size_t) ei; const int sl = A.n_bsdfs * 6 + ei * 3;
                             if (e0.x != 0.f) add_grad(sl, gp, dL.x * c3.x / e0.x);
                             if (e0.y != 0.f) add_grad(sl + 1, gp + 1, dL.y * c3.y / e0.y);
                             if (e0.z != 0.f) add_grad(sl + 2, gp + 2, dL.z * c3.z / e0.z);
@@ -369,10 +369,10 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
             if (!kAdj) push_splat(done_path, park[1 * kCtaThreads], park[2 * kCtaThreads], value);
             else if (done_path) {   // suffix of the path behind every recorded bounce, divided by that bounce's reflectance
                 for (int k = 0; k < nrec; ++k) {
-                    const int b = __float_as_int(rec[k][0]);
-                    const float *row = reinterpret_cast<const float *>(A.sc.bsdfs) + 16 * (size_t) b;
-                    float *gp = A.grad_bsdfs + 16 * (size_t) b + 2; const int sl = b * 3;
-                    const float r0 = __ldg(row + 2), r1 = __ldg(row + 3), r2 = __ldg(row + 4);
+                    const int code = __float_as_int(rec[k][0]), b = code >> 1, col = (code & 1) ? 11 : 2;
+                    const float *row = reinterpret_cast<const float *>(A.sc.bsdfs) + 16 * (size_t) b + col;
+                    float *gp = A.grad_bsdfs + 16 * (size_t) b + col; const int sl = b * 6 + ((code & 1) ? 3 : 0);
+                    const float r0 = __ldg(row), r1 = __ldg(row + 1), r2 = __ldg(row + 2);
                     if (r0 != 0.f) add_grad(sl, gp, dL.x * (result.x - rec[k][1]) / r0);
                     if (r1 != 0.f) add_grad(sl + 1, gp + 1, dL.y * (result.y - rec[k][2]) / r1);
                     if (r2 != 0.f) add_grad(sl + 2, gp + 2, dL.z * (result.z - rec[k][3]) / r2);
@@ -399,17 +399,19 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
     }
     if (kAdj && grad_in_smem) {
         __syncthreads();
-        for (int i = tid; i < (A.n_bsdfs + A.sc.n_emitters) * 3; i += kCtaThreads) {
+        for (int i = tid; i < A.n_bsdfs * 6 + A.sc.n_emitters * 3; i += kCtaThreads) {
             const float v = s_grad[i];
             if (v == 0.f) continue;
-            const int e = i / 3, c = i - 3 * e;
-            atomicAdd(e < A.n_bsdfs ? A.grad_bsdfs + 16 * (size_t) e + 2 + c : A.grad_emitters + 16 * (size_t) (e - A.n_bsdfs) + c, v);
+            float *dst;
+            if (i < A.n_bsdfs * 6) { const int bb = i / 6, c = i - 6 * bb; dst = A.grad_bsdfs + 16 * (size_t) bb + (c < 3 ? 2 + c : 8 + c); }
+            else { const int j = i - A.n_bsdfs * 6, e = j / 3; dst = A.grad_emitters + 16 * (size_t) e + (j - 3 * e); }
+            atomicAdd(dst, v);
         }
     }
     if (A.stats) {
-        unsigned long long c[6] = { n_samples, n_miss, n_rays, n_bounces, n_nodes, n_tris };
+        unsigned long long c[7] = { n_samples, n_miss, n_rays, n_bounces, n_nodes, n_tris, n_clamp };
 #pragma unroll
-        for (int k = 0; k < 6; ++k) {
+        for (int k = 0; k < 7; ++k) {
             for (int o = 16; o > 0; o >>= 1) c[k] += __shfl_down_sync(0xffffffffu, c[k], o);
             if (lane == 0) atomicAdd(A.stats + k, c[k]);
         }
@@ -479,6 +481,9 @@ int launch_render(const lrt_scene *sc, lrt_sensor *sensor, const lrt_film_desc *
         }
     }
     const bool adjoint = grad_storage != nullptr;
+    // the one-pass adjoint keeps one record per bounce of a path: longer paths are refused, not truncated
+    LRT_REQUIRE(!adjoint || (rp->max_depth >= 0 && rp->max_depth <= kMaxRec + 1),
+                "lrt_render_backward: max_depth must be in [0, 17] (one gradient record per bounce; unbounded paths are not supported)");
     A.grad_storage = grad_storage; A.grad_bsdfs = grad_bsdfs; A.grad_emitters = grad_emitters; A.n_bsdfs = sc->n_bsdfs;
     int per_sm = 1;
     const bool attr = sc->view.tri_attr != nullptr || sc->view.textures != nullptr;

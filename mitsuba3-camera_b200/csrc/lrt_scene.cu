@@ -172,10 +172,10 @@ int lrt_render_backward(const lrt_scene *sc, const lrt_sensor *sensor, const lrt
                          (cudaStream_t) stream);
 }
 
-int lrt_render_stats(const lrt_scene *sc, uint64_t *out6) {
+int lrt_render_stats(const lrt_scene *sc, uint64_t *out7) {
     LRT_NEED_DEVICE();
-    LRT_REQUIRE(sc && out6, "null argument");
-    LRT_CUDA(cudaMemcpy(out6, sc->d_counter + kCounterRing, 6 * sizeof(uint64_t), cudaMemcpyDeviceToHost));
+    LRT_REQUIRE(sc && out7, "null argument");
+    LRT_CUDA(cudaMemcpy(out7, sc->d_counter + kCounterRing, 7 * sizeof(uint64_t), cudaMemcpyDeviceToHost));
     return LRT_OK;
 }
 

@@ -158,7 +158,7 @@ static __device__ __noinline__ float3 texture_eval(const TexView *tv, float2 uv_
 struct BsdfResult {
     float3 val; float pdf;          // eval_pdf(wo)
     float3 wo; float spdf, seta;    // sample
-    float3 weight; bool delta;
+    float3 weight; bool delta, transmitted;   // transmitted: the dielectric's refraction lobe was sampled
 };
 
 // BSDF::eval_pdf_sample: eval/pdf for the emitter direction `wo` and a fresh sample from (s1, s2)
@@ -169,7 +169,7 @@ template <bool kAttr = true> LRT_D BsdfResult bsdf_eval_pdf_sample(const SceneVi
     float3 refl = make_float3(b0.z, b0.w, b1.x);
     BsdfResult o;
     o.val = make_float3(0, 0, 0); o.pdf = 0.f; o.wo = make_float3(0, 0, 0); o.spdf = 0.f; o.seta = 1.f;
-    o.weight = make_float3(0, 0, 0); o.delta = false;
+    o.weight = make_float3(0, 0, 0); o.delta = false; o.transmitted = false;
     bool flip = twosided && wi.z < 0.f;
     if (flip) { wi.z = -wi.z; wo.z = -wo.z; }
     if (type == BSDF_DIFFUSE) {
@@ -195,7 +195,7 @@ template <bool kAttr = true> LRT_D BsdfResult bsdf_eval_pdf_sample(const SceneVi
         bool sel_r = s1 <= r_i;
         o.delta = true; o.spdf = sel_r ? r_i : 1.f - r_i;
         o.wo = sel_r ? make_float3(-wi.x, -wi.y, wi.z) : make_float3(-eti * wi.x, -eti * wi.y, ct);
-        o.seta = sel_r ? 1.f : eit;
+        o.seta = sel_r ? 1.f : eit; o.transmitted = !sel_r;
         o.weight = sel_r ? refl : make_float3(b2.w, b3.x, b3.y) * (eti * eti);
     }
     if (flip) o.wo.z = -o.wo.z;

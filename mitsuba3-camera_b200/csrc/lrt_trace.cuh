@@ -81,7 +81,10 @@ LRT_D void trav_node_step(const BvhView &bvh, float3 o, float3 idir, Trav &T, ui
     const uint32_t nxa = nx ? n3.z : n2.x, nxb = nx ? n3.w : n2.y, fxa = nx ? n2.x : n3.z, fxb = nx ? n2.y : n3.w;
     const uint32_t nya = ny ? n4.x : n2.z, nyb = ny ? n4.y : n2.w, fya = ny ? n2.z : n4.x, fyb = ny ? n2.w : n4.y;
     const uint32_t nza = nz ? n4.z : n3.x, nzb = nz ? n4.w : n3.y, fza = nz ? n3.x : n4.z, fzb = nz ? n3.y : n4.w;
-    // a full stack drops its deepest candidates instead of overflowing (never seen: 9 pushes of slack per node)
+    // a full stack cannot take this node's (up to 8) pushes: the newest candidates are overwritten and the event is flagged in
+    // bit 31 of `work` (the render kernel counts it into its statistics: tests and bench assert the count is zero; a BVH8 over
+    // a million triangles keeps < 30 entries)
+    if (T.sp > kTravStack - 9) work |= 0x80000000u;
     int sp = min(T.sp, kTravStack - 9);
     uint32_t best = 0xffffffffu, best0 = 0xffffffffu, xh = T.cur;
 #pragma unroll 1

@@ -353,6 +353,36 @@ class PathIntegrator:
         return render(scene, sensor=sensor, integrator=self, seed=seed, spp=spp, develop=develop)
 
 
+class PRBIntegrator(PathIntegrator):
+    """`prb` plugin (src/python/python/ad/integrators/prb.py): the `path` estimator with a reverse-mode derivative.
+    render() is PathIntegrator's; render_backward() is RBIntegrator.render_backward (common.py:631-796): the gradient image is
+    pulled through develop (division by the filter-weight sum, recomputed for the differential phase's own sample positions)
+    and the splat, then lrt_render_backward walks the same paths (sampling and Russian roulette detached)."""
+
+    def render_backward(self, scene, params, grad_in, sensor=0, seed=0, spp=0):
+        import torch
+        s = scene.sensors()[sensor] if isinstance(sensor, int) else sensor
+        spp = int(spp) if spp else s.sampler.sample_count()
+        grad_in = torch.as_tensor(grad_in, dtype=torch.float32, device="cuda")
+        # W of the differential phase: a max_depth = 0 render splats weight 1 (and RGB 0) at the very positions it samples
+        wsum = render(scene, sensor=s, integrator=PathIntegrator(0, self.rr_depth), seed=seed, spp=spp, develop=False)[..., 3]
+        gs = torch.zeros((s.film.crop_h, s.film.crop_w, 4), dtype=torch.float32, device="cuda")
+        gs[..., :3] = grad_in / torch.where(wsum == 0, torch.ones_like(wsum), wsum)[..., None]     # hdrfilm.cpp:390-392, transposed
+        gb, ge = render_backward(scene, gs, sensor=s, integrator=self, seed=seed, spp=spp)
+        grads = params.gradients(gb, ge)
+        for k, g in grads.items():
+            t = params[k]
+            if getattr(t, "requires_grad", False):
+                g = g.to(t.device, t.dtype)
+                t.grad = g.clone() if t.grad is None else t.grad + g
+        return grads
+
+    def render_forward(self, scene, params, sensor=0, seed=0, spp=0):
+        """Forward-mode derivative image for the tangents stored in `params[key].grad`-style `.tangent` attributes is not part
+        of the hot path; the notebooks and the prb tests of the path use reverse mode only."""
+        raise ValueError("render_forward: forward-mode differentiation is outside the hot path of this build (use render_backward)")
+
+
 class IndependentSampler:
     """`independent` plugin (src/samplers/independent.cpp): sample_count, seed (base seed)."""
 
@@ -444,9 +474,10 @@ class Scene:
         return out[:, 0], out[:, 1], out[:, 2], out[:, 3].to(torch.int64)
 
     def stats(self):
-        out = (C.c_uint64 * 6)()
+        out = (C.c_uint64 * 7)()
         capi.check(capi.lib.lrt_render_stats(self.handle, out))
-        return {"samples": out[0], "lens_misses": out[1], "rays": out[2], "bounces": out[3], "bvh_nodes": out[4], "triangles": out[5]}
+        return {"samples": out[0], "lens_misses": out[1], "rays": out[2], "bounces": out[3], "bvh_nodes": out[4], "triangles": out[5],
+                "stack_clamps": out[6]}
 
 
 def film_desc(film: Film, coalesce=True, normalize=False) -> FilmDesc:
@@ -494,6 +525,16 @@ def render(scene: Scene, params=None, sensor=0, integrator=None, seed=0, seed_gr
     convention (lensrt.h). Renders of more than 2^32 - 1 samples run as several passes (render_passes)."""
     import torch
     if params is not None:
+        if not isinstance(params, SceneParameters):
+            raise Exception("params should be an instance of mi.SceneParameter!")
+        diff = [k for k in params if getattr(params[k], "requires_grad", False)]
+        if diff and develop and torch.is_grad_enabled():
+            if seed_grad == 0:
+                seed_grad = tea32(int(seed), 1)[0]                # util.py:518-520
+            elif seed_grad == seed:
+                raise Exception("The primal and differential seed should be different to ensure unbiased gradient computation!")
+            return _RenderOp.apply(scene, sensor, params, integrator or scene.integrator(), (int(seed), int(seed_grad)),
+                                   (int(spp), int(spp_grad) if spp_grad else int(spp)), diff, *[params[k] for k in diff])
         params.update()
     s = scene.sensors()[sensor] if isinstance(sensor, int) else sensor
     it = integrator or scene.integrator()
@@ -532,6 +573,53 @@ def render_backward(scene: Scene, grad_storage, sensor=0, integrator=None, seed=
     return gb[:len(scene.arrays["bsdfs"])], ge[:len(scene.arrays["emitters"])]
 
 
+def _make_render_op():
+    import torch
+
+    class RenderOp(torch.autograd.Function):
+        """_RenderOp (src/python/python/util.py:356-407) as a torch.autograd.Function: forward = integrator.render with the
+        primal seed / spp, backward = integrator.render_backward with the differential seed / spp."""
+
+        @staticmethod
+        def forward(ctx, scene, sensor, params, integrator, seeds, spps, keys, *tensors):
+            ctx.args = (scene, sensor, params, integrator, seeds, spps, keys)
+            params.update()
+            with torch.no_grad():
+                return render(scene, None, sensor, integrator, seed=seeds[0], spp=spps[0])
+
+        @staticmethod
+        def backward(ctx, grad_out):
+            scene, sensor, params, integrator, seeds, spps, keys = ctx.args
+            if not hasattr(integrator, "render_backward"):
+                raise Exception("the integrator has no reverse-mode derivative: use {'type': 'prb'}")
+            s = scene.sensors()[sensor] if isinstance(sensor, int) else sensor
+            saved = {k: params[k].grad for k in keys}
+            for k in keys:
+                params[k].grad = None
+            integrator.render_backward(scene, params, grad_out.contiguous(), s, seeds[1], spps[1])
+            out = []
+            for k in keys:
+                g = params[k].grad
+                out.append(torch.zeros_like(params[k]) if g is None else g)
+                params[k].grad = saved[k]
+            return (None,) * 7 + tuple(out)
+
+    return RenderOp
+
+
+class _LazyRenderOp:
+    _op = None
+
+    @classmethod
+    def apply(cls, *a):
+        if cls._op is None:
+            cls._op = _make_render_op()
+        return cls._op.apply(*a)
+
+
+_RenderOp = _LazyRenderOp
+
+
 class SceneParameters(dict):
     """mi.traverse(scene) for the parameters the adjoint reaches: '<bsdf key>.reflectance.value' (diffuse),
     '<bsdf key>.specular_reflectance.value' (conductor), '<shape key>.emitter.radiance.value' — torch tensors of 3 floats.
@@ -544,20 +632,31 @@ class SceneParameters(dict):
         a = scene.arrays
         for i, name in enumerate(scene.data.bsdf_names):
             t = int(a["bsdfs"][i, 0])
-            if t in (0, 1):
-                key = f"{name}.{'reflectance' if t == 0 else 'specular_reflectance'}.value"
-                self[key] = torch.tensor(a["bsdfs"][i, 2:5].copy()); self._where[key] = ("bsdf", i)
+            if a["bsdfs"][i, 15] != 0:
+                continue                  # a bitmap reflectance is not a differentiable parameter of this build
+            key = f"{name}.{'reflectance' if t == 0 else 'specular_reflectance'}.value"
+            self[key] = torch.tensor(a["bsdfs"][i, 2:5].copy()); self._where[key] = ("bsdf", i)
+            if t == 2:
+                key = f"{name}.specular_transmittance.value"
+                self[key] = torch.tensor(a["bsdfs"][i, 11:14].copy()); self._where[key] = ("bsdf_t", i)
         for sid, e in enumerate(a["shape_emitter"]):
             if e >= 0:
                 key = f"{scene.data.shape_names[sid]}.emitter.radiance.value"
                 self[key] = torch.tensor(a["emitters"][e, 0:3].copy()); self._where[key] = ("emitter", int(e))
 
-    def update(self):
+    def update(self, values=None):
+        """params.update() / params.update(optimizer): push the current values to the device tables."""
+        if values is not None:
+            for k in values:
+                if k in self._where:
+                    self[k] = values[k]
         a = self.scene.arrays
         for key, (kind, i) in self._where.items():
             v = self[key].detach().cpu().numpy().astype(f32)
             if kind == "bsdf":
                 a["bsdfs"][i, 2:5] = v
+            elif kind == "bsdf_t":
+                a["bsdfs"][i, 11:14] = v
             else:
                 a["emitters"][i, 0:3] = v
         rad = np.ascontiguousarray(a["emitters"][:, 0:3], f32)
@@ -566,7 +665,8 @@ class SceneParameters(dict):
 
     def gradients(self, grad_bsdfs, grad_emitters):
         """Split the adjoint's tables into per-key gradients."""
-        return {k: (grad_bsdfs[i, 2:5] if kind == "bsdf" else grad_emitters[i, 0:3]) for k, (kind, i) in self._where.items()}
+        pick = {"bsdf": lambda i: grad_bsdfs[i, 2:5], "bsdf_t": lambda i: grad_bsdfs[i, 11:14], "emitter": lambda i: grad_emitters[i, 0:3]}
+        return {k: pick[kind](i) for k, (kind, i) in self._where.items()}
 
 
 def traverse(scene):
@@ -626,7 +726,7 @@ def scene_data_from_dict(d: dict):
         vt = v.get("type")
         if vt in ("perspective", "realisticlens"):
             sensor_dicts.append(v)
-        elif vt == "path":
+        elif vt in ("path", "prb"):
             integ = v
         elif vt in _SHAPES:
             tw = v.get("to_world")
@@ -696,8 +796,10 @@ def load_dict(d: dict):
         return IndependentSampler(d.get("sample_count", 4), d.get("seed", 0))
     if t in ("gaussian", "tent", "box"):
         return ReconstructionFilter(t, float(d.get("stddev", d.get("radius", 0.0))) if t != "box" else 0.0)
-    if t == "path":
-        return PathIntegrator(d.get("max_depth", -1), d.get("rr_depth", 5), d.get("hide_emitters", False))
+    if t in ("path", "prb"):
+        # hide_emitters only removes an environment emitter from directly visible pixels (path.cpp:113-114); this build has no
+        # environment emitter, so the flag has nothing to act on — as in the reference for such scenes
+        return (PRBIntegrator if t == "prb" else PathIntegrator)(d.get("max_depth", -1), d.get("rr_depth", 5), d.get("hide_emitters", False))
     if t != "scene":
         raise ValueError(f"plugin '{t}' is outside the hot path of this build")
     data, sensor_dicts, integ = scene_data_from_dict(d)

@@ -404,8 +404,13 @@ static float pdf_emitter_direction(const Scene &s, const DS &ds) {
 // scalar = false: the JIT draw order (every active lane draws its 6 numbers per iteration, no early exit);
 // scalar = true : the scalar variant's control flow — `break` before any draw once the path cannot continue
 //                 (path.cpp:178-179) and emitter samples drawn only at smooth surfaces (any_or<true> evaluates the mask).
+// g_rr_scene (test hook, orc_set_rr_scene): Russian roulette DETACHED as in prb (path.cpp:270-275 dr::detach(rr_prob)) — the
+// survival probabilities and the termination test follow the throughput of this frozen copy of the scene, so that finite
+// differences of a perturbed scene's render see the same paths with the same roulette weights.
+static const Scene *g_rr_scene = nullptr;
+
 static V3 path_sample(const Scene &s, PCG32 &rng, Ray ray, int max_depth, int rr_depth, bool scalar, bool &valid_ray) {
-    V3 throughput { 1, 1, 1 }, result { 0, 0, 0 };
+    V3 throughput { 1, 1, 1 }, result { 0, 0, 0 }, throughput_rr { 1, 1, 1 };
     float eta = 1.f; int depth = 0;
     valid_ray = false;
     V3 prev_p { 0, 0, 0 }; float prev_bsdf_pdf = 1.f; bool prev_bsdf_delta = true;
@@ -451,14 +456,16 @@ static V3 path_sample(const Scene &s, PCG32 &rng, Ray ray, int max_depth, int rr
         }
         ray = spawn_ray(si.p, si.n, si.to_world(b.wo));
         throughput = throughput * b.weight;
+        throughput_rr = g_rr_scene ? throughput_rr * eval_pdf_sample(*g_rr_scene, g_rr_scene->bsdfs[g_rr_scene->shape_bsdf[si.shape]], si.uv, si.wi, wo,
+                                                                     sample_1, sample_2).weight : throughput;
         eta *= b.seta;
         prev_p = si.p; prev_bsdf_pdf = b.spdf; prev_bsdf_delta = b.delta;
         depth += 1;
-        float tmax = std::fmax(throughput.x, std::fmax(throughput.y, throughput.z));
+        float tmax = std::fmax(throughput_rr.x, std::fmax(throughput_rr.y, throughput_rr.z));
         float rr_prob = std::fmin(tmax * sqr(eta), .95f);
         if (scalar) rr_sample = rng.next_float32();
         bool rr_active = depth >= rr_depth, rr_continue = rr_sample < rr_prob;
-        if (rr_active) throughput = throughput * rcp(rr_prob);
+        if (rr_active) { throughput = throughput * rcp(rr_prob); if (g_rr_scene) throughput_rr = throughput_rr * rcp(rr_prob); }
         active = active_next && (!rr_active || rr_continue) && tmax != 0.f;
     }
     // (a camera ray that escapes or a path cut short leaves valid_ray as is: no environment emitter)
@@ -595,6 +602,8 @@ void orc_scene_set_rectangles(void *h, int n, const int *shape_ids, const float 
     s->build();
 }
 void orc_scene_destroy(void *h) { delete (Scene *) h; }
+// Russian roulette follows this (unperturbed) scene in every later render; NULL restores the attached behaviour
+void orc_set_rr_scene(void *h) { g_rr_scene = (const Scene *) h; }
 
 // closest hit / any hit for n rays: od7 = o, d, maxt -> out4 = t, u, v, prim (prim = -1: miss)
 void orc_scene_intersect(void *h, int any_hit, int64_t n, const float *od7, float *out4) {
