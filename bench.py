@@ -207,16 +207,11 @@ def lens_grad_section(mi, torch, dist, a, rank, world):
         except Exception as e:   # a blocked chief ray in a synthetic prescription must not take the bench line down
             out[name] = {"error": str(e)[:200]}
             continue
-        red = (lambda g: dist.all_reduce(g)) if world > 1 else None
-
-        def it():
-            if world > 1:     # theta.grad lives on the host: reduce through a device copy
-                prob.opt.zero_grad(set_to_none=True)
-                l = prob.loss(prob.rows(), prob.iteration); l.backward()
-                g = prob.theta.grad.cuda(); dist.all_reduce(g); prob.theta.grad.copy_(g.cpu())
-                prob.opt.step(); prob.iteration += 1; prob.losses.append(float(l.detach()))
-            else:
-                prob.step()
+        def it(record=False):
+            # sharded runs: the spot accumulators are all-reduced before the (non-linear) loss and the table gradients after
+            # the adjoint (LensDesignProblem.step); variables, table and optimiser state stay on the device
+            prob.step(record_loss=record)
+        it(record=True)
         for _ in range(3):
             it()
         torch.cuda.synchronize()
@@ -227,6 +222,7 @@ def lens_grad_section(mi, torch, dist, a, rank, world):
         for _ in range(a.lens_iters):
             it()
         e1.record(); torch.cuda.synchronize()
+        it(record=True)
         ms = torch.tensor([e0.elapsed_time(e1) / a.lens_iters], device="cuda", dtype=torch.float64)
         if world > 1:
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
@@ -264,7 +260,10 @@ def lens_grad_cpu(mi, a):
     sec = time.perf_counter() - t0
     rays_sample = 128 * 128 * spp * 2
     rays_iter = 3 * 128 * 128 * (256 + 128)
-    return {"value": 1.0 / (sec * rays_iter / rays_sample), "unit": "iters/s (C2)", "cores": 1, "kind": "port",
+    return {"value": 1.0 / (sec * rays_iter / rays_sample), "unit": "iters/s (C2)", "cores": 1, "kind": "port", "meaningful": False,
+            "note": "NOT a like-for-like baseline: one thread, forward-mode float64 dual numbers (30 seeds) of the checker; the reference "
+                    "cannot differentiate its analytic lens table at all and no llvm_ad_rgb variant can run on this box. Reported for "
+                    "completeness only: do not quote the ratio.",
             "sample": f"1 field, 128^2 x {spp} spp primal + adjoint ({rays_sample} lens rays, {sec:.2f} s), scaled by ray count to the "
                       f"{rays_iter}-ray iteration; forward-mode float64 dual numbers (30 seeds)"}
 

@@ -79,6 +79,9 @@ int lrt_sensor_num_interfaces(const lrt_sensor *s);
 int lrt_sensor_get_interfaces(const lrt_sensor *s, float *rows16);
 /* parameters_changed(): replace the interface table / pose without re-running the autofocus */
 int lrt_sensor_set_interfaces(lrt_sensor *s, int32_t n, const float *rows16);
+/* the same with the table in DEVICE memory (rows16_dev [n,16]): one small kernel on `stream`, no host round trip — for design
+ * loops whose variables live on the GPU. The host copy is refreshed lazily by the getters / *_host entry points. */
+int lrt_sensor_set_interfaces_dev(lrt_sensor *s, int32_t n, const float *rows16_dev, void *stream);
 int lrt_sensor_set_to_world(lrt_sensor *s, const float *to_world16);
 int lrt_sensor_get_info(const lrt_sensor *s, float *sample_to_film16, float *focus_delta, float *film_z);
 

@@ -48,4 +48,6 @@ struct lrt_sensor {
     cudaEvent_t staged = nullptr;         // completion of the last upload (the staging copy is reused after it)
     // host -> dev if dirty, ordered on `stream` (renders launched earlier on that stream keep reading the old table)
     int upload(cudaStream_t stream = nullptr);
+    bool host_stale = false;              // the device table is newer than `host.ifs` (lrt_sensor_set_interfaces_dev)
+    int sync_host();
 };

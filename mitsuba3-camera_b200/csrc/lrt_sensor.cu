@@ -44,8 +44,8 @@ static float material_ior(const float *m, float wavelength) {   // realisticlens
     return sqrtf(ior);
 }
 
-// fill every derived constant of a record from its defining parameters
-static void finish_record(LensIf &f) {
+// fill every derived constant of a record from its defining parameters (host and device: lrt_sensor_set_interfaces_dev)
+LRT_HD static void finish_record(LensIf &f) {
     f.elem_r2 = f.elem_radius * f.elem_radius;
     f.eta = f.ior_right / f.ior_left;
     f.rcp_eta = 1.f / f.eta;
@@ -58,11 +58,11 @@ static void finish_record(LensIf &f) {
     f.c2 = f.c * f.c;
     f.one_p_K = 1.f + f.K;
     f.k1 = f.one_p_K * f.c2;
-    f.lim = f.K > -1.0f ? f.elem_radius * (1.f / (1.0f + f.K)) : INFINITY;
+    f.lim = f.K > -1.0f ? f.elem_radius * (1.f / (1.0f + f.K)) : inf_f();
     for (int i = 0; i < 7; ++i) f.gi[i] = (2.f * i + 4.f) * f.ai[i];
 }
 
-static LensIf blank(int kind, float z, float elem_radius, float il, float ir) {
+LRT_HD static LensIf blank(int kind, float z, float elem_radius, float il, float ir) {
     LensIf f; memset(&f, 0, sizeof f);
     f.kind = kind; f.z = z; f.elem_radius = elem_radius; f.ior_left = il; f.ior_right = ir;
     return f;
@@ -71,7 +71,7 @@ static LensIf blank(int kind, float z, float elem_radius, float il, float ir) {
 static void offset_along_axis(LensIf &f, float delta) { f.z += delta; finish_record(f); }
 
 // 16-float row <-> record (layout documented in lensrt.h)
-static LensIf record_from_row(const float *r) {
+LRT_HD static LensIf record_from_row(const float *r) {
     int kind = (int) r[0];
     LensIf f = blank(kind, r[1], r[2], r[13], r[14]);
     if (kind == IF_SPHERE) f.curv_radius = r[3];
@@ -176,7 +176,18 @@ static void set_common(lrt_sensor *s, const lrt_film_geom *film, const float *tw
 
 }  // namespace lrt
 
+// the device table was written by lrt_sensor_set_interfaces_dev: bring the host copy up to date before it is read or re-uploaded
+int lrt_sensor::sync_host() {
+    if (!host_stale) return LRT_OK;
+    LRT_CUDA(cudaDeviceSynchronize());
+    LRT_CUDA(cudaMemcpy(host.ifs, reinterpret_cast<const char *>(dev) + offsetof(lrt::LensSystem, ifs), sizeof host.ifs, cudaMemcpyDeviceToHost));
+    host.rear_z = host.ifs[0].z; host.rear_radius = host.ifs[0].elem_radius;
+    host_stale = false;
+    return LRT_OK;
+}
+
 int lrt_sensor::upload(cudaStream_t stream) {
+    if (host_stale && dev_dirty) { int rc = sync_host(); if (rc) return rc; }
     if (!dev) LRT_CUDA(cudaMalloc(&dev, sizeof(lrt::LensSystem)));
     if (!staging) {
         LRT_CUDA(cudaMallocHost(&staging, sizeof(lrt::LensSystem)));
@@ -412,11 +423,35 @@ void lrt_sensor_destroy(lrt_sensor *s) {
 int lrt_sensor_num_interfaces(const lrt_sensor *s) { return s ? s->host.n : 0; }
 int lrt_sensor_get_interfaces(const lrt_sensor *s, float *rows16) {
     LRT_REQUIRE(s && rows16, "null argument");
+    { int rc = const_cast<lrt_sensor *>(s)->sync_host(); if (rc) return rc; }
     for (int i = 0; i < s->host.n; ++i) row_from_record(s->host.ifs[i], rows16 + 16 * i);
+    return LRT_OK;
+}
+namespace lrt {
+__global__ void k_set_interfaces(LensSystem *L, int n, const float *__restrict__ rows16) {
+    const int i = threadIdx.x;
+    if (i < n) L->ifs[i] = record_from_row(rows16 + 16 * i);
+    if (i == 0) { L->n = n; L->rear_z = rows16[1]; L->rear_radius = rows16[2]; }
+}
+}
+// parameters_changed() for optimisation loops that keep the interface table on the DEVICE (rows16_dev [n,16] float32, same
+// layout as lrt_sensor_set_interfaces): one small kernel on `stream`, no host round trip. The host copy is refreshed lazily
+// (lrt_sensor_get_interfaces, the *_host entry points). Not available while exit-pupil sampling is on (its LUT is rebuilt
+// from the host copy).
+int lrt_sensor_set_interfaces_dev(lrt_sensor *s, int32_t n, const float *rows16_dev, void *stream) {
+    LRT_NEED_DEVICE();
+    LRT_REQUIRE(s && rows16_dev && n > 0 && n <= kMaxInterfaces && n <= 32, "bad argument");
+    LRT_REQUIRE(s->host.kind == 0 && !s->host.pupil_mode, "set_interfaces_dev needs a realisticlens sensor in rear-element sampling mode");
+    int rc = s->upload((cudaStream_t) stream); if (rc) return rc;
+    lrt::k_set_interfaces<<<1, 32, 0, (cudaStream_t) stream>>>(s->dev, n, rows16_dev);
+    LRT_LAUNCHED();
+    LRT_CUDA(cudaGetLastError());
+    s->host.n = n; s->host_stale = true;
     return LRT_OK;
 }
 int lrt_sensor_set_interfaces(lrt_sensor *s, int32_t n, const float *rows16) {
     LRT_REQUIRE(s && rows16 && n > 0 && n <= kMaxInterfaces, "bad argument");
+    s->host_stale = false;
     for (int i = 0; i < n; ++i) s->host.ifs[i] = record_from_row(rows16 + 16 * i);
     s->host.n = n; s->host.rear_z = s->host.ifs[0].z; s->host.rear_radius = s->host.ifs[0].elem_radius;
     s->dev_dirty = true;
@@ -487,6 +522,7 @@ int lrt_sensor_sample_ray_host(const lrt_sensor *s, int64_t n, const float *pos2
 // host-side trace through the interface table (same LRT_HD code as the kernels; used by the autofocus and
 // exposed for the lens-design front end's chief-ray queries: design_problem.py:415-417 uses prb_basic.trace)
 int lrt_sensor_trace_host(const lrt_sensor *s, int32_t from_world, int64_t n, const float *od6, float *out7) {
+    if (s) { int rc_ = const_cast<lrt_sensor *>(s)->sync_host(); if (rc_) return rc_; }
     LRT_REQUIRE(s && od6 && out7 && n >= 0 && s->host.kind == 0, "bad argument");
     for (int64_t i = 0; i < n; ++i) {
         const float *r = od6 + 6 * i;

@@ -361,6 +361,7 @@ int lrt_sensor_sample_direction_host(const lrt_sensor *s, int64_t n, const float
 // is the adjoint of the outgoing ray; writes the adjoint of the incoming ray and ADDS d/d(rows16) to grad_rows16.
 int lrt_sensor_trace_vjp_host(const lrt_sensor *s, int32_t from_world, int64_t n, const float *od6, const float *bar6,
                               float *out_bar6, float *grad_rows16, int32_t *active) {
+    if (s) { int rc_ = const_cast<lrt_sensor *>(s)->sync_host(); if (rc_) return rc_; }
     LRT_REQUIRE(s && od6 && bar6 && out_bar6 && grad_rows16 && n >= 0 && s->host.kind == 0, "bad argument");
     const LensSystem &L = s->host;
     for (int64_t i = 0; i < n; ++i) {

@@ -89,6 +89,50 @@ def rms_loss(image):
     return (I * ((ii - ibar) ** 2 + (jj - jbar) ** 2)).sum() * inv
 
 
+def _set_rows(sensor, rows):
+    """The interface table of a design iteration: device tensors stay on the device (lrt_sensor_set_interfaces_dev)."""
+    if rows.is_cuda:
+        sensor.set_interfaces_dev(rows)
+    else:
+        sensor.set_interfaces(rows.numpy())
+
+
+def _all_reduce_image():
+    import torch
+    import torch.distributed as dist
+
+    class SumOverRanks(torch.autograd.Function):
+        """image = sum over ranks of the partial spot images (each rank traces its share of the sample indices). Every rank
+        then evaluates the SAME loss on the SAME image, so d(loss)/d(partial image of rank r) = d(loss)/d(image): the
+        backward is the identity, and the table gradients (each rank: its own samples) are summed afterwards."""
+
+        @staticmethod
+        def forward(ctx, img):
+            out = img.contiguous().clone()
+            dist.all_reduce(out)
+            return out
+
+        @staticmethod
+        def backward(ctx, g):
+            return g
+
+    return SumOverRanks
+
+
+_SumOverRanks = None
+
+
+def sum_over_ranks(img):
+    """All-reduce (sum) of a partial image with the autograd rule above; the identity for a single process."""
+    global _SumOverRanks
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
+        return img
+    if _SumOverRanks is None:
+        _SumOverRanks = _all_reduce_image()
+    return _SumOverRanks.apply(img)
+
+
 def _spot_function():
     import torch
 
@@ -98,16 +142,16 @@ def _spot_function():
 
         @staticmethod
         def forward(ctx, rows, sensor, src_p, intensity, seed, spp, seed_grad, spp_grad, shard, origin_offset):
-            sensor.set_interfaces(rows.detach().cpu().numpy())
+            ctx.rows = rows.detach()
+            _set_rows(sensor, ctx.rows)
             st = spot_render(sensor, src_p, intensity, seed, spp, shard, origin_offset=origin_offset)
             ctx.args = (sensor, src_p, intensity, seed_grad, spp_grad, shard, rows.device, origin_offset)
-            ctx.rows_np = rows.detach().cpu().numpy().copy()
             return st[..., :3]
 
         @staticmethod
         def backward(ctx, grad_img):
             sensor, src_p, intensity, seed_grad, spp_grad, shard, dev, origin_offset = ctx.args
-            sensor.set_interfaces(ctx.rows_np)
+            _set_rows(sensor, ctx.rows)
             g = torch.zeros(grad_img.shape[:2] + (4,), dtype=torch.float32, device=grad_img.device)
             g[..., :3] = grad_img
             gr = spot_render_backward(sensor, src_p, g, intensity, seed_grad, spp_grad, shard, origin_offset=origin_offset)
@@ -193,7 +237,7 @@ class LensDesignProblem:
     image-space loss gradient, adjoint renders at `spp_grad` (fresh seed), Adam update."""
 
     def __init__(self, mi, rows0, field_angles, resolution=128, full_res=4096, diagonal=35.0, spp=256, spp_grad=128,
-                 free=None, lr=3e-5, source_distance=1.0e3, rfilter="tent", efl_target=None, shard=(0, 1), film_z=0.0):
+                 free=None, lr=3e-5, source_distance=1.0e3, rfilter="tent", efl_target=None, shard=(0, 1), film_z=0.0, device="cuda"):
         import torch
         from .lens_designs import InterfaceList
         self.mi, self.torch = mi, torch
@@ -209,8 +253,15 @@ class LensDesignProblem:
         if efl_target is not None:
             free = [(i, c) for (i, c) in free if not (i == 0 and c in (1, 3))]   # the rear vertex / curvature are constrained
         self.free = list(free)
-        self.theta = torch.tensor([self.rows0[i, c] for i, c in self.free], dtype=torch.float32, requires_grad=True)
-        self.opt = torch.optim.Adam([self.theta], lr=lr)
+        # the design variables, the table they map to and the optimiser state all live on the device: an iteration has no
+        # host <-> device round trip (the table reaches the sensors through lrt_sensor_set_interfaces_dev)
+        self.device = torch.device(device)
+        self.theta = torch.tensor([self.rows0[i, c] for i, c in self.free], dtype=torch.float32, device=self.device, requires_grad=True)
+        self.opt = torch.optim.Adam([self.theta], lr=lr, capturable=self.device.type == "cuda")
+        self._rows0_t = torch.tensor(self.rows0, device=self.device)
+        self._idx = (torch.tensor([i for i, _ in self.free], device=self.device), torch.tensor([c for _, c in self.free], device=self.device))
+        self._sph = torch.tensor(self.rows0[:, 0] == 0, device=self.device); self._asp = torch.tensor(self.rows0[:, 0] == 3, device=self.device)
+        self._rear_idx = (torch.tensor([0, 0], device=self.device), torch.tensor([1, 3], device=self.device))
         self.sensors, self.sources = [], []
         probe = mi.RealisticLensCamera(mi.Film(full_res, full_res, diagonal=diagonal, rfilter=rfilter), "custom",
                                        prescription=InterfaceList(self.rows0, film_z=film_z, fine_focus=False))
@@ -237,18 +288,14 @@ class LensDesignProblem:
     def rows(self):
         """theta -> interface table (torch, differentiable); applies the EFL constraint when one is set."""
         torch = self.torch
-        rows = torch.tensor(self.rows0)
-        idx_i = torch.tensor([i for i, _ in self.free]); idx_c = torch.tensor([c for _, c in self.free])
-        rows = rows.index_put((idx_i, idx_c), self.theta)
+        rows = self._rows0_t.index_put(self._idx, self.theta)
         if self.efl_target is not None:
             Re = rows[:, 2]
-            sph = torch.tensor(self.rows0[:, 0] == 0)
-            asp = torch.tensor(self.rows0[:, 0] == 3)
-            safe_R = torch.where(sph, rows[:, 3], torch.ones_like(Re))
-            kappa = torch.where(sph, -1.0 / safe_R, torch.where(asp, rows[:, 3] / Re, torch.zeros_like(Re)))
+            safe_R = torch.where(self._sph, rows[:, 3], torch.ones_like(Re))
+            kappa = torch.where(self._sph, -1.0 / safe_R, torch.where(self._asp, rows[:, 3] / Re, torch.zeros_like(Re)))
             z0, k0 = efl_constrained_rear(rows[:, 1], kappa, rows[:, 13], rows[:, 14], self.efl_target)
             col3 = k0 * Re[0] if self.rows0[0, 0] == 3 else -1.0 / k0
-            rows = rows.index_put((torch.tensor([0, 0]), torch.tensor([1, 3])), torch.stack([z0, col3]))
+            rows = rows.index_put(self._rear_idx, torch.stack([z0, col3]))
         return rows
 
     def loss(self, rows, seed):
@@ -256,17 +303,26 @@ class LensDesignProblem:
         for k, (s, src) in enumerate(zip(self.sensors, self.sources)):
             img = spot_image(rows, s, src, seed=seed * 64 + k, spp=self.spp, seed_grad=(seed * 64 + k) ^ 0x5bd1e995,
                              spp_grad=self.spp_grad, shard=self.shard, origin_offset=self.origin_offset)
+            # sample-index sharding: the (non-linear) loss is evaluated on the image summed over ranks, never on a partial one
+            img = sum_over_ranks(img) if self.shard[1] > 1 else img
             total = total + rms_loss(img) * (self.pitch * 1e3) ** 2       # mm^2, as evaluate_rms_loss (design_problem.py:268-282)
         return total
 
-    def step(self, all_reduce=None):
-        """One optimisation iteration; `all_reduce(tensor)` sums the table gradient over ranks when sharded."""
+    def step(self, all_reduce=None, record_loss=True):
+        """One optimisation iteration. Sharded runs (shard[1] > 1): every rank renders its share of the sample indices, the spot
+        accumulators are all-reduced BEFORE the loss (loss()), and the table gradients — each rank's own samples against the
+        common image gradient — are summed here: the result equals the single-process gradient up to float summation order.
+        record_loss=False keeps the loss on the device (no synchronisation in the iteration)."""
+        from .parallel import all_reduce_sum
         self.opt.zero_grad(set_to_none=True)
         l = self.loss(self.rows(), self.iteration)
         l.backward()
-        if all_reduce is not None:
-            all_reduce(self.theta.grad)
+        if self.shard[1] > 1:
+            (all_reduce or all_reduce_sum)(self.theta.grad)
         self.opt.step()
         self.iteration += 1
-        self.losses.append(float(l.detach()))
-        return self.losses[-1]
+        self.last_loss = l.detach()
+        if record_loss:
+            self.losses.append(float(self.last_loss))
+            return self.losses[-1]
+        return self.last_loss

@@ -166,6 +166,13 @@ class RealisticLensCamera(Sensor):
         rows = np.ascontiguousarray(rows, f32)
         capi.check(capi.lib.lrt_sensor_set_interfaces(self.handle, C.c_int32(len(rows)), capi.fp(rows)))
 
+    def set_interfaces_dev(self, rows):
+        """parameters_changed() with the table on the device (torch CUDA tensor [n,16] float32): no host round trip."""
+        assert rows.is_cuda and rows.dtype.is_floating_point and rows.shape[-1] == 16
+        rows = rows.detach().contiguous().float()
+        capi.check(capi.lib.lrt_sensor_set_interfaces_dev(self.handle, C.c_int32(rows.shape[0]), capi.dev_ptr(rows), capi.stream_ptr()))
+        self._rows_dev = rows        # keeps the tensor alive until the kernel has read it
+
     def set_to_world(self, to_world):
         self.to_world = _to_world_array(to_world)
         capi.check(capi.lib.lrt_sensor_set_to_world(self.handle, capi.fp(self.to_world)))

@@ -136,4 +136,4 @@ def test_gpu_adam_recovers_wall_colour(mi):
     loss1 = clean_loss()
     err = (opt[key].detach() - target_value).abs().max().item()
     print("loss", loss0, "->", loss1, "recovered", opt[key].detach().tolist(), "err", err)
-    assert loss1 < 0.2 * loss0 and err < 0.08
+    assert loss1 < 0.3 * loss0 and err < 0.08

@@ -174,3 +174,65 @@ def test_spot_with_near_origin_from_a_distant_source(mi, name, angle, rfilter, f
     got = np.array([gr[i, col] for i, col in sel], np.float64)
     cos = float(got @ wantg / (np.linalg.norm(got) * np.linalg.norm(wantg)))
     assert cos >= 0.9999 and np.abs(got - wantg).max() <= 2e-2 * np.abs(wantg).max(), (cos, got, wantg)
+
+
+def _sharded_design_worker(rank, world, port, q):
+    import os, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    sys.path.insert(0, root); sys.path.insert(0, os.path.join(root, "tests"))
+    os.environ.update(RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK="0", MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    import torch
+    import torch.distributed as dist
+    import lensrt as mi
+    dist.init_process_group("gloo")              # both ranks share the one GPU of the box: gloo moves the CUDA tensors
+    L = mi.lens_design
+    rows = _doublet_rows(mi)
+    prob = L.LensDesignProblem(mi, rows, [0.0, 2.5, 5.0], resolution=64, full_res=2048, spp=32, spp_grad=16, lr=2e-4, shard=(rank, world))
+    prob.opt.zero_grad(set_to_none=True)
+    l = prob.loss(prob.rows(), 0); l.backward()
+    from mitsuba3_camera_b200.parallel import all_reduce_sum
+    all_reduce_sum(prob.theta.grad)
+    g0 = prob.theta.grad.detach().cpu().numpy().copy()
+    for _ in range(3):
+        prob.step()
+    q.put((rank, float(l), g0, prob.theta.detach().cpu().numpy()))
+    dist.destroy_process_group()
+
+
+def _doublet_rows(mi):
+    L = mi.lens_design
+    n1, n2 = L.cauchy_ior(1.45608, 0.021087), L.cauchy_ior(1.56895, 0.026305)
+    return L.asphere_table([24.0, -24.0, -168.0107], [3.0, 2.2529, 46.7471], [8, 8, 8], [n1, n2, 1.000277])
+
+
+@pytest.mark.gpu
+@pytest.mark.timeout(600)
+def test_gpu_sharded_design_equals_single_process(mi):
+    """C2-shaped design problem on 2 ranks (sample-index sharding, spot accumulators all-reduced before the loss, table
+    gradients after the adjoint) = the single-process loss, gradient and Adam trajectory to float summation order."""
+    import socket
+    import torch
+    import torch.multiprocessing as mp
+    L = mi.lens_design
+    prob = L.LensDesignProblem(mi, _doublet_rows(mi), [0.0, 2.5, 5.0], resolution=64, full_res=2048, spp=32, spp_grad=16, lr=2e-4)
+    assert prob.theta.is_cuda and prob.rows().is_cuda
+    prob.opt.zero_grad(set_to_none=True)
+    l = prob.loss(prob.rows(), 0); l.backward()
+    g1 = prob.theta.grad.detach().cpu().numpy().copy()
+    for _ in range(3):
+        prob.step()
+    th1 = prob.theta.detach().cpu().numpy()
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    ps = [ctx.Process(target=_sharded_design_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in ps:
+        p.start()
+    res = sorted((q.get(timeout=400) for _ in ps), key=lambda t: t[0])
+    for p in ps:
+        p.join(60)
+        assert p.exitcode == 0
+    for rank, loss, g, th in res:
+        assert abs(loss - float(l)) <= 1e-4 * abs(float(l)), (loss, float(l))
+        assert np.abs(g - g1).max() <= 1e-4 * np.abs(g1).max(), (np.abs(g - g1).max(), np.abs(g1).max())
+        assert np.abs(th - th1).max() <= 1e-5 * max(np.abs(th1).max(), 1.0)
