@@ -253,6 +253,10 @@ typedef struct lrt_spot_params {
     float origin_offset;               /* 0: rays start at src_p as in sample_direction (:2336). > 0: the same ray starts this
                                           many metres in front of the sampled front-plane point (well-conditioned in float32
                                           for distant sources; see lrt_lens.cuh) */
+    int32_t fast;                      /* 0: strict float32 (every operation rounded as the reference's scalar build does: the
+                                          miss masks are bit-exact). 1: the same algorithm with fused multiply-adds and hardware
+                                          reciprocal / square-root approximations (last-ulp differences, ~2x the rays per second):
+                                          what design loops use; primal and adjoint must use the same flavour */
 } lrt_spot_params;
 
 /* Accumulates intensity*weight/spp (R,G,B) and 1/spp (W) times the normalised filter weights into accum_dev

@@ -49,7 +49,15 @@ LRT_HD float u2f(uint32_t u) {
 }
 
 namespace strict {
-#ifdef __CUDA_ARCH__
+#if defined(__CUDA_ARCH__) && defined(LRT_FAST_ARITH)
+// the fast flavour (lrt_spot_fast.cu only): plain operators (nvcc contracts a * b + c into one FFMA) and the MUFU
+// approximations (1-2 ulp) — the same functions, the same algorithm, no claim on the last bit
+LRT_HD float mul(float a, float b) { return a * b; }
+LRT_HD float add(float a, float b) { return a + b; }
+LRT_HD float sub(float a, float b) { return a - b; }
+LRT_HD float div(float a, float b) { return __fdividef(a, b); }
+LRT_HD float sqrt(float a) { float r; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(a)); return r; }
+#elif defined(__CUDA_ARCH__)
 LRT_HD float mul(float a, float b) { return __fmul_rn(a, b); }
 LRT_HD float add(float a, float b) { return __fadd_rn(a, b); }
 LRT_HD float sub(float a, float b) { return __fsub_rn(a, b); }
@@ -65,12 +73,16 @@ LRT_HD float sqrt(float a) { return ::sqrtf(a); }
 LRT_HD float sqr(float a) { return mul(a, a); }
 // 1 / a: the correctly rounded reciprocal IS the correctly rounded quotient 1.f / a, so the shorter __frcp_rn sequence
 // gives the same bits as the division the reference performs (dr::rcp in scalar mode, array_utils.h:212-214)
-#ifdef __CUDA_ARCH__
+#if defined(__CUDA_ARCH__) && defined(LRT_FAST_ARITH)
+LRT_HD float rcp(float a) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(a)); return r; }
+LRT_HD float rsqrt(float a) { float r; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(a)); return r; }
+#elif defined(__CUDA_ARCH__)
 LRT_HD float rcp(float a) { return __frcp_rn(a); }
+LRT_HD float rsqrt(float a) { return rcp(sqrt(a)); }
 #else
 LRT_HD float rcp(float a) { return div(1.f, a); }
-#endif
 LRT_HD float rsqrt(float a) { return rcp(sqrt(a)); }
+#endif
 LRT_HD float fmadd(float a, float b, float c) { return add(mul(a, b), c); }    // two roundings
 LRT_HD float fmsub(float a, float b, float c) { return sub(mul(a, b), c); }
 LRT_HD float fnmadd(float a, float b, float c) { return sub(c, mul(a, b)); }

@@ -21,7 +21,7 @@ f32 = np.float32
 
 class SpotParams(C.Structure):
     _fields_ = [("seed", C.c_uint32), ("spp", C.c_int32), ("src_p", C.c_float * 3), ("intensity", C.c_float * 3),
-                ("shard_index", C.c_int32), ("shard_count", C.c_int32), ("origin_offset", C.c_float)]
+                ("shard_index", C.c_int32), ("shard_count", C.c_int32), ("origin_offset", C.c_float), ("fast", C.c_int32)]
 
 
 def field_source(angle_deg, distance=1.0e3, azimuth_deg=0.0, front_z=0.0):
@@ -36,32 +36,33 @@ def _film_desc(film):
     return FilmDesc(film.crop_w, film.crop_h, film.crop_x, film.crop_y, 0, 4, rf.kind, rf.param, 0, 1)
 
 
-def _params(seed, spp, src_p, intensity, shard, origin_offset=0.0):
+def _params(seed, spp, src_p, intensity, shard, origin_offset=0.0, fast=False):
     p = SpotParams()
     p.seed, p.spp = int(seed) & 0xffffffff, int(spp)
     for k in range(3):
         p.src_p[k] = float(src_p[k]); p.intensity[k] = float(intensity[k])
     p.shard_index, p.shard_count = int(shard[0]), int(shard[1])
     p.origin_offset = float(origin_offset)
+    p.fast = int(bool(fast))
     return p
 
 
 def spot_render(sensor, src_p, intensity=(1.0, 1.0, 1.0), seed=0, spp=None, shard=(0, 1), storage=None, stats=None,
-                origin_offset=0.0):
+                origin_offset=0.0, fast=False):
     """One light-traced spot image: storage [H,W,4] (R,G,B,W accumulators; the image is [..., :3])."""
     import torch
     film = sensor.film
     spp = int(spp if spp else sensor.sampler.sample_count())
     if storage is None:
         storage = torch.zeros((film.crop_h, film.crop_w, 4), dtype=torch.float32, device="cuda")
-    fd, p = _film_desc(film), _params(seed, spp, src_p, intensity, shard, origin_offset)
+    fd, p = _film_desc(film), _params(seed, spp, src_p, intensity, shard, origin_offset, fast)
     capi.check(capi.lib.lrt_spot_render(sensor.handle, C.byref(fd), C.byref(p), capi.dev_ptr(storage),
                                         capi.dev_ptr(stats) if stats is not None else None, capi.stream_ptr()))
     return storage
 
 
 def spot_render_backward(sensor, src_p, grad_storage, intensity=(1.0, 1.0, 1.0), seed=0, spp=None, shard=(0, 1), grad_rows=None,
-                         stats=None, origin_offset=0.0):
+                         stats=None, origin_offset=0.0, fast=False):
     """Adjoint of spot_render: grad_storage [H,W,4] -> d/d(interface table) [n_if,16] (torch CUDA tensor, accumulated)."""
     import torch
     film = sensor.film
@@ -69,7 +70,7 @@ def spot_render_backward(sensor, src_p, grad_storage, intensity=(1.0, 1.0, 1.0),
     if grad_rows is None:
         grad_rows = torch.zeros((sensor.num_interfaces(), 16), dtype=torch.float32, device="cuda")
     g = grad_storage.contiguous()
-    fd, p = _film_desc(film), _params(seed, spp, src_p, intensity, shard, origin_offset)
+    fd, p = _film_desc(film), _params(seed, spp, src_p, intensity, shard, origin_offset, fast)
     capi.check(capi.lib.lrt_spot_render_backward(sensor.handle, C.byref(fd), C.byref(p), capi.dev_ptr(g), capi.dev_ptr(grad_rows),
                                                  capi.dev_ptr(stats) if stats is not None else None, capi.stream_ptr()))
     return grad_rows
@@ -141,21 +142,21 @@ def _spot_function():
         tensor [n_if,16]) -> spot image [H,W,3]; backward replays the samples with seed_grad / spp_grad."""
 
         @staticmethod
-        def forward(ctx, rows, sensor, src_p, intensity, seed, spp, seed_grad, spp_grad, shard, origin_offset):
+        def forward(ctx, rows, sensor, src_p, intensity, seed, spp, seed_grad, spp_grad, shard, origin_offset, fast):
             ctx.rows = rows.detach()
             _set_rows(sensor, ctx.rows)
-            st = spot_render(sensor, src_p, intensity, seed, spp, shard, origin_offset=origin_offset)
-            ctx.args = (sensor, src_p, intensity, seed_grad, spp_grad, shard, rows.device, origin_offset)
+            st = spot_render(sensor, src_p, intensity, seed, spp, shard, origin_offset=origin_offset, fast=fast)
+            ctx.args = (sensor, src_p, intensity, seed_grad, spp_grad, shard, rows.device, origin_offset, fast)
             return st[..., :3]
 
         @staticmethod
         def backward(ctx, grad_img):
-            sensor, src_p, intensity, seed_grad, spp_grad, shard, dev, origin_offset = ctx.args
+            sensor, src_p, intensity, seed_grad, spp_grad, shard, dev, origin_offset, fast = ctx.args
             _set_rows(sensor, ctx.rows)
             g = torch.zeros(grad_img.shape[:2] + (4,), dtype=torch.float32, device=grad_img.device)
             g[..., :3] = grad_img
-            gr = spot_render_backward(sensor, src_p, g, intensity, seed_grad, spp_grad, shard, origin_offset=origin_offset)
-            return (gr.to(dev),) + (None,) * 9
+            gr = spot_render_backward(sensor, src_p, g, intensity, seed_grad, spp_grad, shard, origin_offset=origin_offset, fast=fast)
+            return (gr.to(dev),) + (None,) * 10
 
     return SpotRender
 
@@ -164,7 +165,7 @@ _SpotRender = None
 
 
 def spot_image(rows, sensor, src_p, intensity=(1.0, 1.0, 1.0), seed=0, spp=None, seed_grad=None, spp_grad=None, shard=(0, 1),
-               origin_offset=0.0):
+               origin_offset=0.0, fast=False):
     """Differentiable spot image (torch autograd): d(image)/d(rows) comes from lrt_spot_render_backward.
     seed_grad defaults to seed (same samples in the adjoint: the exact derivative of the primal estimate)."""
     global _SpotRender
@@ -172,7 +173,7 @@ def spot_image(rows, sensor, src_p, intensity=(1.0, 1.0, 1.0), seed=0, spp=None,
         _SpotRender = _spot_function()
     spp = int(spp if spp else sensor.sampler.sample_count())
     return _SpotRender.apply(rows, sensor, src_p, tuple(intensity), int(seed), spp, int(seed if seed_grad is None else seed_grad),
-                             int(spp_grad if spp_grad else spp), shard, float(origin_offset))
+                             int(spp_grad if spp_grad else spp), shard, float(origin_offset), bool(fast))
 
 
 # ------------------------------------------------------------------------------------------------ design problem
@@ -237,13 +238,13 @@ class LensDesignProblem:
     image-space loss gradient, adjoint renders at `spp_grad` (fresh seed), Adam update."""
 
     def __init__(self, mi, rows0, field_angles, resolution=128, full_res=4096, diagonal=35.0, spp=256, spp_grad=128,
-                 free=None, lr=3e-5, source_distance=1.0e3, rfilter="tent", efl_target=None, shard=(0, 1), film_z=0.0, device="cuda"):
+                 free=None, lr=3e-5, source_distance=1.0e3, rfilter="tent", efl_target=None, shard=(0, 1), film_z=0.0, device="cuda", fast=True):
         import torch
         from .lens_designs import InterfaceList
         self.mi, self.torch = mi, torch
         self.rows0 = np.ascontiguousarray(rows0, f32).copy()
         self.n = len(self.rows0)
-        self.spp, self.spp_grad, self.shard = int(spp), int(spp_grad), shard
+        self.spp, self.spp_grad, self.shard, self.fast = int(spp), int(spp_grad), shard, bool(fast)
         self.origin_offset = 2.0 * float(self.rows0[-1, 2])      # rays start two front semi-diameters before the front plane
         self.pitch = 1e-3 * diagonal / np.sqrt(2.0) / full_res          # square film: side = diagonal / sqrt(2)
         self.efl_target = efl_target
@@ -302,7 +303,7 @@ class LensDesignProblem:
         total = 0.0
         for k, (s, src) in enumerate(zip(self.sensors, self.sources)):
             img = spot_image(rows, s, src, seed=seed * 64 + k, spp=self.spp, seed_grad=(seed * 64 + k) ^ 0x5bd1e995,
-                             spp_grad=self.spp_grad, shard=self.shard, origin_offset=self.origin_offset)
+                             spp_grad=self.spp_grad, shard=self.shard, origin_offset=self.origin_offset, fast=self.fast)
             # sample-index sharding: the (non-linear) loss is evaluated on the image summed over ranks, never on a partial one
             img = sum_over_ranks(img) if self.shard[1] > 1 else img
             total = total + rms_loss(img) * (self.pitch * 1e3) ** 2       # mm^2, as evaluate_rms_loss (design_problem.py:268-282)

@@ -236,3 +236,27 @@ def test_gpu_sharded_design_equals_single_process(mi):
         assert abs(loss - float(l)) <= 1e-4 * abs(float(l)), (loss, float(l))
         assert np.abs(g - g1).max() <= 1e-4 * np.abs(g1).max(), (np.abs(g - g1).max(), np.abs(g1).max())
         assert np.abs(th - th1).max() <= 1e-5 * max(np.abs(th1).max(), 1.0)
+
+
+@pytest.mark.gpu
+def test_gpu_fast_flavour_agrees_with_strict(mi):
+    """lrt_spot_params.fast: fused multiply-adds + hardware rcp / sqrt approximations. Same samples, same algorithm: the spot
+    image agrees to 2e-3 rel-RMSE (measured 6e-4: film positions move by ~1e-3 pixel, which the tent weights see), the
+    transmitted-sample count to 1e-4, the table gradient to cosine 0.9999."""
+    import torch
+    import bench
+    L = mi.lens_design
+    prob = L.LensDesignProblem(mi, bench.triplet_table(mi), [3.75], resolution=128, full_res=4096, spp=64, spp_grad=64)
+    s, src = prob.sensors[0], prob.sources[0]
+    out = {}
+    G = torch.randn((128, 128, 4), device="cuda", generator=torch.Generator(device="cuda").manual_seed(1))
+    for fast in (False, True):
+        stats = torch.zeros(2, dtype=torch.int64, device="cuda")
+        st = L.spot_render(s, src, seed=3, spp=64, origin_offset=prob.origin_offset, stats=stats, fast=fast)
+        gr = L.spot_render_backward(s, src, G, seed=3, spp=64, origin_offset=prob.origin_offset, fast=fast)
+        out[fast] = (st.cpu().numpy(), gr.cpu().numpy().ravel().astype(np.float64), stats.cpu().numpy())
+    a, b = out[False], out[True]
+    assert rel_rmse(b[0][..., :3], a[0][..., :3]) < 2e-3
+    assert abs(int(a[2][1]) - int(b[2][1])) <= 1e-4 * a[2][1] and a[2][1] > 1e5
+    cos = float(a[1] @ b[1] / (np.linalg.norm(a[1]) * np.linalg.norm(b[1])))
+    assert cos >= 0.9999, cos
