@@ -189,6 +189,17 @@ int lrt_scene_create(const lrt_scene_desc *desc, lrt_scene **out);
 int lrt_scene_set_params(lrt_scene *s, const float *bsdfs, const float *emitter_radiance3);
 void lrt_scene_destroy(lrt_scene *s);
 int lrt_scene_info(const lrt_scene *s, int64_t *n_nodes, int64_t *n_tris, int32_t *bvh_depth, double *build_seconds);
+/* Mesh-lens mode (notebooks/scripts/lens_design/lens.py:343-565): the vertices of an existing scene moved (same topology).
+ * vertices_dev [n_vertices,3] / normals_dev [n_vertices,3] (NULL: keep) are DEVICE pointers; the triangle records are rewritten
+ * and the 8-wide BVH is refitted bottom-up on `stream` — the stand-in for Mesh::parameters_changed + the accelerator rebuild
+ * (src/render/mesh.cpp:85-162). */
+int lrt_scene_refit(lrt_scene *s, const float *vertices_dev, const float *normals_dev, void *stream);
+/* Rays through refractive meshes: od6 = o[3], d[3]; shape_eta_dev [n_shapes] = int_ior / ext_ior of the interface a shape
+ * models (interior = behind its normal; 0 = absorber, e.g. a baffle); at most max_interactions surfaces. out8 = o[3], d[3] of the
+ * ray leaving the last surface, alive (1/0), product of the Fresnel transmittances: the transmission lobe of the `dispersive` /
+ * `dielectric` BSDF (src/bsdfs/dispersive_dielectric.cpp:250-431) applied about the interpolated vertex normal. */
+int lrt_scene_trace_refractive(const lrt_scene *s, int64_t n, const float *od6_dev, const float *shape_eta_dev,
+                               int32_t max_interactions, float *out8_dev, void *stream);
 /* Scene::ray_intersect_preliminary / ray_test (src/render/scene.cpp:181-210) for n rays:
  * od7 = o[3], d[3], maxt; out4 = t, u, v, primitive index (-1: miss; t = inf). */
 int lrt_scene_intersect(const lrt_scene *s, int32_t any_hit, int64_t n, const float *od7_dev, float *out4_dev, void *stream);

@@ -11,7 +11,7 @@ from .transform import Transform4f, ScalarTransform4f
 from .scene import (Scene, SceneData, PathIntegrator, PRBIntegrator, IndependentSampler, load_dict, render, cornell_box, bsdf_row,
                     film_desc, RenderParams, SceneDesc, load_obj, load_ply, scene_data_from_dict, render_backward, traverse,
                     SceneParameters)
-from . import scene, workloads, lens_design, parallel, imageio, ad
+from . import scene, workloads, lens_design, parallel, imageio, ad, mesh_lens
 from . import imageio as util          # mi.util.write_bitmap (src/python/python/util.py) for .exr / .pfm
 from .lens_design import spot_render, spot_render_backward, spot_image, rms_loss, field_source
 

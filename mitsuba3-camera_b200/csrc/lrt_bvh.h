@@ -28,7 +28,12 @@ struct alignas(16) BvhTri {
 };
 static_assert(sizeof(BvhTri) == 48, "BvhTri layout");
 
-struct BvhBuildStats { int nodes = 0, leaves = 0, max_depth = 0; double sah = 0; };
+struct BvhBuildStats {
+    int nodes = 0, leaves = 0, max_depth = 0; double sah = 0;
+    // nodes are emitted breadth-first: level l = nodes [level_begin[l], level_begin[l+1]); every child index > its parent's
+    // (what the device refit walks bottom-up, lrt_refit.cu)
+    std::vector<int> level_begin;
+};
 
 // verts [nv,3], idx [nt,3], tri_shape [nt]; outputs the wide nodes and the reordered triangle array
 void build_bvh8(const float *verts, const int32_t *idx, const int32_t *tri_shape, int64_t nt,

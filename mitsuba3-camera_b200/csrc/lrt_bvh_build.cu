@@ -108,7 +108,7 @@ void build_bvh8(const float *verts, const int32_t *idx, const int32_t *tri_shape
         BvhNode n; memset(&n, 0, sizeof n); n.ex = n.ey = n.ez = 1;
         memset(n.qlo_x, 255, 24);   // qlo_x, qlo_y, qlo_z: inverted boxes (lo 255, hi 0) never pass the slab test
         nodes.push_back(n);
-        if (stats) *stats = BvhBuildStats();
+        if (stats) { *stats = BvhBuildStats(); stats->level_begin = { 0, 1 }; }
         return;
     }
     B.bn.reserve(2 * (size_t) nt);
@@ -119,7 +119,10 @@ void build_bvh8(const float *verts, const int32_t *idx, const int32_t *tri_shape
     std::vector<int> queue; queue.push_back(0);
     nodes.resize(1);
     size_t head = 0; int leaves = 0;
+    std::vector<int> level_begin; level_begin.push_back(0);
+    size_t level_end = 1;          // first queue index of the next level
     while (head < queue.size()) {
+        if (head == level_end) { level_begin.push_back((int) head); level_end = queue.size(); }
         int bin_root = queue[head]; size_t self = head; head++;
         // gather up to 8 children by repeatedly opening the inner child with the largest area
         int ch[8]; int nch = 0;
@@ -170,7 +173,8 @@ void build_bvh8(const float *verts, const int32_t *idx, const int32_t *tri_shape
         if (nodes.size() < queue.size()) nodes.resize(queue.size());
         nodes[self] = n;
     }
-    if (stats) { stats->nodes = (int) nodes.size(); stats->leaves = leaves; stats->max_depth = max_depth; }
+    level_begin.push_back((int) nodes.size());
+    if (stats) { stats->nodes = (int) nodes.size(); stats->leaves = leaves; stats->max_depth = max_depth; stats->level_begin = level_begin; }
 }
 
 }  // namespace lrt

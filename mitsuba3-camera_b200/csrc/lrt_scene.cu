@@ -74,7 +74,10 @@ int lrt_scene_create(const lrt_scene_desc *d, lrt_scene **out) {
             }
         }
     }
+    std::vector<int32_t> tri_vidx(tris.size() * 3);
+    for (size_t i = 0; i < tris.size(); ++i) for (int k = 0; k < 3; ++k) tri_vidx[3 * i + k] = d->indices[3 * (size_t) tris[i].prim + k];
     lrt_scene *s = new lrt_scene();
+    s->level_begin = st.level_begin; s->n_vertices = d->n_vertices;
     s->build_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     s->n_nodes = (int64_t) nodes.size(); s->n_tris = (int64_t) tris.size(); s->bvh_depth = st.max_depth;
     s->n_shapes = d->n_shapes; s->n_bsdfs = d->n_bsdfs; s->n_emitters = d->n_emitters;
@@ -98,6 +101,8 @@ int lrt_scene_create(const lrt_scene_desc *d, lrt_scene **out) {
         (rc = upload(&s->d_bsdfs, d->bsdfs, (size_t) d->n_bsdfs * 16)) || (rc = upload(&s->d_emitters, em.data(), em.size()))) {
         lrt_scene_destroy(s); return rc;
     }
+    if ((rc = upload(&s->d_tri_vidx, tri_vidx.data(), tri_vidx.size()))) { lrt_scene_destroy(s); return rc; }
+    if (cudaMalloc(&s->d_node_box, std::max<size_t>(nodes.size(), 1) * 6 * sizeof(float)) != cudaSuccess) { lrt_scene_destroy(s); return cuda_fail(cudaGetLastError(), "cudaMalloc"); }
     if (!attr.empty() && (rc = upload(&s->d_tri_attr, attr.data(), attr.size()))) { lrt_scene_destroy(s); return rc; }
     if (d->n_textures) {
         size_t total = 0;
@@ -140,7 +145,7 @@ int lrt_scene_set_params(lrt_scene *s, const float *bsdfs, const float *emitter_
 void lrt_scene_destroy(lrt_scene *s) {
     if (!s) return;
     void *p[] = { s->d_nodes, s->d_tris, s->d_shape_bsdf, s->d_shape_emitter, s->d_bsdfs, s->d_emitters, s->d_counter,
-                  s->d_tri_attr, s->d_tex_data, s->d_textures };
+                  s->d_tri_attr, s->d_tex_data, s->d_textures, s->d_tri_vidx, s->d_node_box };
     for (void *q : p) if (q) cudaFree(q);
     delete s;
 }

@@ -1,0 +1,253 @@
+"""Mesh-lens parity mode: the notebooks' representation of a lens — every refracting surface a triangle mesh
+whose vertex z follows the sag function — rendered with the B200 scene kernels.
+
+Restates notebooks/scripts/lens_design/geometry.py (get_hemisphere_ico :44-70, get_spherical_cap :121-160,
+create_surface_geometry :296-390) and the sag functions of lens.py (:67-85 conic, :210-237 even asphere) on top of the interface
+table this package uses everywhere else (rows16, rear -> front, metres). One optimisation step of the notebooks
+(lens.py:509-565: new sag -> params['lensN.vertex_positions'] -> params.update()) becomes: new vertex z on the device ->
+lrt_scene_refit (BVH refit kernels) -> lrt_scene_trace_refractive."""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _capi as capi
+
+f32 = np.float32
+
+
+def icosphere(n):
+    """gpytoolbox.icosphere(n): icosahedron subdivided n times (each triangle into four), vertices pushed to the unit sphere."""
+    t = (1 + 5 ** 0.5) / 2
+    v = [[-1, t, 0], [1, t, 0], [-1, -t, 0], [1, -t, 0], [0, -1, t], [0, 1, t], [0, -1, -t], [0, 1, -t], [t, 0, -1], [t, 0, 1],
+         [-t, 0, -1], [-t, 0, 1]]
+    f = [[0, 11, 5], [0, 5, 1], [0, 1, 7], [0, 7, 10], [0, 10, 11], [1, 5, 9], [5, 11, 4], [11, 10, 2], [10, 7, 6], [7, 1, 8],
+         [3, 9, 4], [3, 4, 2], [3, 2, 6], [3, 6, 8], [3, 8, 9], [4, 9, 5], [2, 4, 11], [6, 2, 10], [8, 6, 7], [9, 8, 1]]
+    v = [np.asarray(p, np.float64) / np.linalg.norm(p) for p in v]
+    for _ in range(n):
+        cache, nf = {}, []
+
+        def mid(a, b):
+            k = (min(a, b), max(a, b))
+            if k not in cache:
+                p = v[a] + v[b]; v.append(p / np.linalg.norm(p)); cache[k] = len(v) - 1
+            return cache[k]
+        for a, b, c in f:
+            ab, bc, ca = mid(a, b), mid(b, c), mid(c, a)
+            nf += [[a, ab, ca], [b, bc, ab], [c, ca, bc], [ab, bc, ca]]
+        f = nf
+    return np.asarray(v, np.float64), np.asarray(f, np.int64)
+
+
+def hemisphere_ico(n):
+    """geometry.py:44-70: the +z half of the icosphere, open at z = 0 (faces with a vertex below -edge/2 are dropped)."""
+    V, F = icosphere(n)
+    avg_edge = np.sqrt(4.0 * np.pi / len(F))
+    bad = V[:, 2] < -avg_edge / 2.0
+    F = F[~bad[F].any(axis=1)]
+    used, inv = np.unique(F.reshape(-1), return_inverse=True)
+    return V[used], inv.reshape(-1, 3)
+
+
+def spherical_cap(n, elem_radius, abs_curvature):
+    """geometry.py:121-160: the hemisphere's polar angles rescaled so that the cap subtends the surface's own aperture angle."""
+    V, F = hemisphere_ico(n)
+    target = np.arcsin(elem_radius * max(abs_curvature, 1e-3))
+    vlen = np.linalg.norm(V, axis=1)
+    ang = np.arccos(np.clip(V[:, 2] / vlen, -1, 1)) * (target / (0.5 * np.pi))
+    rxy = np.linalg.norm(V[:, :2], axis=1)
+    out = V.copy()
+    out[:, 2] = vlen * np.cos(ang)
+    with np.errstate(invalid="ignore", divide="ignore"):
+        out[:, :2] *= (vlen * np.sin(ang) / rxy)[:, None]
+    out[np.isnan(out)] = 0.0
+    out[:, 2] -= np.cos(target)
+    out *= elem_radius / np.sin(target)
+    return out, F
+
+
+def sag(row, x, y, xp=np):
+    """Vertex z of an interface-table row at (x, y), metres, camera space (film at z = 0, +z towards the scene): sphere
+    (kind 0: z_vertex + R - sign(R) sqrt(R^2 - r^2)), plane / stop, or the even asphere in unitless radius r / R_e
+    (kind 3; realisticlens.cpp:680-704 == lens.py:210-237). `xp` = numpy or torch."""
+    kind = int(row[0])
+    r2 = x * x + y * y
+    if kind == 0:
+        R = row[3]
+        return row[1] + R - xp.sign(R) * xp.sqrt(R * R - r2) if xp is not np else row[1] + R - np.sign(R) * np.sqrt(R * R - r2)
+    if kind in (1, 2):
+        return row[1] + 0 * r2
+    Re = row[2]
+    r2_ = r2 / (Re * Re)
+    z = 0 * r2_
+    for i in range(6, -1, -1):
+        z = z * r2_ + row[6 + i]
+    z = z * r2_ * r2_
+    z = z + row[3] * r2_ / (1 + xp.sqrt(xp.clip(1 - (1 + row[4]) * row[3] * row[3] * r2_, 0, None) if xp is np
+                                        else xp.clamp(1 - (1 + row[4]) * row[3] * row[3] * r2_, min=0)))
+    return row[1] - Re * z
+
+
+def curvature(row):
+    """|second-order curvature| of a table row (1 / m)."""
+    kind = int(row[0])
+    if kind == 0:
+        return abs(1.0 / float(row[3]))
+    if kind == 3:
+        return abs(float(row[3]) / float(row[2]))
+    return 0.0
+
+
+def surface_meshes(rows, subdiv=5, baffle_scale=3.0):
+    """create_surface_geometry (geometry.py:296-390) for every refracting row of the table: (caps, baffles), each a list of
+    (vertices [nv,3] float64, faces [nf,3]) — the cap's xy grid is fixed, its z is sag(row, x, y); normals face +z."""
+    caps, baffles = [], []
+    for row in rows:
+        if int(row[0]) == 2:          # the aperture stop has no glass: an annular baffle only
+            caps.append(None)
+            V, F = hemisphere_ico(2)
+            rim = _boundary_loop(F)
+            el = V[rim] * np.array([row[2], row[2], 0.0]) / np.maximum(np.linalg.norm(V[rim, :2], axis=1, keepdims=True), 1e-30)
+            el[:, 2] = row[1]
+            baffles.append(_annulus(el, baffle_scale * float(row[2])))
+            continue
+        V, F = spherical_cap(subdiv, float(row[2]), curvature(row))
+        V[:, 2] = sag(np.asarray(row, np.float64), V[:, 0], V[:, 1])
+        caps.append((V, F))
+        rim = _boundary_loop(F)
+        baffles.append(_annulus(V[rim], baffle_scale * float(row[2])))
+    return caps, baffles
+
+
+def _boundary_loop(F):
+    """Ordered vertex loop of the open boundary (gpytoolbox.boundary_loops(F)[0])."""
+    edges = {}
+    for a, b, c in F:
+        for u, v in ((a, b), (b, c), (c, a)):
+            edges[(u, v)] = edges.get((u, v), 0) + 1
+    nxt = {u: v for (u, v) in edges if (v, u) not in edges}
+    start = next(iter(nxt)); loop = [start]
+    while nxt[loop[-1]] != start:
+        loop.append(nxt[loop[-1]])
+    return np.asarray(loop)
+
+
+def _annulus(rim_pts, outer):
+    """Flat-ish ring from the cap's rim out to the square |x|, |y| <= outer (geometry.py:355-388, both orientations)."""
+    el = np.asarray(rim_pts, np.float64)
+    edge = el.copy()
+    edge[:, :2] *= outer / np.max(np.abs(el[:, :2]), axis=1, keepdims=True)
+    n = len(el)
+    F = []
+    for i in range(n):
+        j = (i + 1) % n
+        F += [[j, i, n + j], [n + i, n + j, i]]
+    return np.vstack([edge, el]), np.asarray(F, np.int64)
+
+
+class MeshLens:
+    """The meshed lens as a lensrt scene: one shape per refracting surface (relative index across it) + absorbing baffles.
+
+    rows: interface table (rear -> front). The ray direction convention of the trace: light travels from the scene (+z) to
+    the film (z = 0), so it enters surface i from the medium ior_right (world side) into ior_left (film side); cap normals
+    face +z, i.e. the 'interior' (behind the normal) is the film-side medium: eta_i = ior_left / ior_right."""
+
+    def __init__(self, mi, rows, subdiv=5, smooth=True):
+        import torch
+        from .scene import SceneData, Scene, PathIntegrator, vertex_normals
+        self.mi, self.rows0 = mi, np.ascontiguousarray(rows, f32).copy()
+        caps, baffles = surface_meshes(self.rows0, subdiv)
+        data = SceneData()
+        glass = data.add_bsdf("glass", np.zeros(16, f32)); black = data.add_bsdf("black", np.zeros(16, f32))
+        eta, self.cap_slices, self.cap_xy, self.baffle_slices, nv = [], [], [], [], 0
+        for i, cap in enumerate(caps):
+            if cap is not None:
+                V, F = cap
+                normals = vertex_normals(V.astype(f32), F) if smooth else None      # from the stored (float32) positions, as Mesh does
+                data.add_shape(f"lens{i}", V.astype(f32), F.astype(np.int32), glass, normals=normals)
+                eta.append(float(self.rows0[i, 13]) / float(self.rows0[i, 14]))
+                self.cap_slices.append((i, nv, nv + len(V))); self.cap_xy.append(V[:, :2].copy()); nv += len(V)
+            V, F = baffles[i]
+            data.add_shape(f"baffle{i}", V.astype(f32), F.astype(np.int32), black)
+            # the ring's 2 x n vertices (outer edge, then the cap's rim) follow the rim's sag when the surface moves
+            self.baffle_slices.append((i, nv, len(V) // 2, V[len(V) // 2:, :2].copy()))
+            eta.append(0.0); nv += len(V)
+        self.scene = Scene(data, [], PathIntegrator())
+        self.faces = self.scene.arrays["indices"]
+        self.vertices = torch.tensor(self.scene.arrays["vertices"], device="cuda")
+        self.eta = torch.tensor(eta, dtype=torch.float32, device="cuda")
+        self.n_surfaces = len(caps)
+        self._xy = [torch.tensor(xy, dtype=torch.float64, device="cuda") for xy in self.cap_xy]
+        self._faces_t = torch.tensor(self.faces.astype(np.int64), device="cuda")
+        self._rim_xy = [torch.tensor(xy, dtype=torch.float64, device="cuda") for (_, _, _, xy) in self.baffle_slices]
+        self.smooth = smooth
+        self._normals = None
+
+    # ---- one design step: new table -> vertex z from the sag function -> refit
+    def update(self, rows):
+        """rows: torch CUDA tensor [n,16] (or array): moves every cap's vertices onto the new surfaces and refits the BVH."""
+        import torch
+        # float64 sag, rounded once to float32 — like the host path that builds a scene from scratch: a float32 sag would add
+        # ~4e-9 m of noise per vertex, i.e. ~1e-5 rad of facet-normal noise at this mesh density (a micron on the film)
+        rows = torch.as_tensor(rows, device="cuda").double()
+        V = self.vertices
+        for (i, a, b), xy in zip(self.cap_slices, self._xy):
+            V[a:b, 2] = sag(rows[i], xy[:, 0], xy[:, 1], xp=torch).float()
+        for (i, a, n, _), xy in zip(self.baffle_slices, self._rim_xy):        # baffles stay sewn to their surface's rim
+            z = sag(rows[i], xy[:, 0], xy[:, 1], xp=torch).float()
+            V[a:a + n, 2] = z; V[a + n:a + 2 * n, 2] = z
+        normals = self._vertex_normals(V) if self.smooth else None
+        capi.check(capi.lib.lrt_scene_refit(self.scene.handle, capi.dev_ptr(V), capi.dev_ptr(normals) if normals is not None else None,
+                                            capi.stream_ptr()))
+        self._normals = normals
+
+    def rebuild(self):
+        """Full rebuild of the acceleration structure from the current vertices (host round trip): what the reference does on
+        every params.update(); here only needed when a deformation is large enough for the refitted tree to degrade."""
+        a = self.scene.arrays
+        a["vertices"] = np.ascontiguousarray(self.vertices.detach().cpu().numpy(), f32)
+        if getattr(self, "_normals", None) is not None:
+            a["vertex_normals"] = np.ascontiguousarray(self._normals.detach().cpu().numpy(), f32)
+        self.scene._upload()
+
+    def _vertex_normals(self, V):
+        """Mesh::recompute_vertex_normals (src/render/mesh.cpp:321-375: face normals weighted by the angle at the vertex) on the device."""
+        import torch
+        F = self._faces_t
+        V = V.double()          # edge vectors of a float32 mesh carry ~1e-5 relative noise: accumulate the normals in float64
+        p = [V[F[:, k]] for k in range(3)]
+        n = torch.linalg.cross(p[1] - p[0], p[2] - p[0])
+        n = n / n.norm(dim=1, keepdim=True).clamp_min(1e-30)
+        out = torch.zeros_like(V)
+        for k in range(3):
+            d0 = torch.nn.functional.normalize(p[(k + 1) % 3] - p[k], dim=1); d1 = torch.nn.functional.normalize(p[(k + 2) % 3] - p[k], dim=1)
+            ang = torch.acos((d0 * d1).sum(1).clamp(-1, 1))
+            out.index_add_(0, F[:, k], n * ang[:, None])
+        return torch.nn.functional.normalize(out, dim=1).float().contiguous()
+
+    def trace(self, o, d):
+        """Rays (camera space, travelling towards -z) through the meshed surfaces: (o, d, alive, weight) torch tensors."""
+        import torch
+        od = torch.cat([torch.as_tensor(o, dtype=torch.float32, device="cuda").reshape(-1, 3),
+                        torch.as_tensor(d, dtype=torch.float32, device="cuda").reshape(-1, 3)], 1).contiguous()
+        out = torch.empty((od.shape[0], 8), dtype=torch.float32, device="cuda")
+        capi.check(capi.lib.lrt_scene_trace_refractive(self.scene.handle, C.c_int64(od.shape[0]), capi.dev_ptr(od), capi.dev_ptr(self.eta),
+                                                       C.c_int32(self.n_surfaces + 1), capi.dev_ptr(out), capi.stream_ptr()))
+        return out[:, 0:3], out[:, 3:6], out[:, 6] > 0, out[:, 7]
+
+    def spot_positions(self, src_p, n, seed=0, origin_offset=0.0):
+        """Film-plane (z = 0) landing points of n rays from the point source `src_p` through uniformly sampled points of the front
+        element's disk: the geometric spot diagram (what the notebooks' prb_basic geo_tracer draws, design_problem.py:399-428)."""
+        import torch
+        g = torch.Generator(device="cuda").manual_seed(seed)
+        u = torch.rand((n, 2), device="cuda", generator=g)
+        r, phi = float(self.rows0[-1, 2]) * torch.sqrt(u[:, 0]), 2 * np.pi * u[:, 1]
+        ap = torch.stack([r * torch.cos(phi), r * torch.sin(phi), torch.full_like(r, float(self.rows0[-1, 1]))], 1)
+        src = torch.tensor(np.asarray(src_p, f32), device="cuda")
+        d = torch.nn.functional.normalize(ap - src, dim=1)
+        o = ap - d * float(origin_offset) if origin_offset > 0 else src.expand_as(ap)
+        po, pd, alive, w = self.trace(o, d)
+        t = -po[:, 2] / pd[:, 2]
+        pf = po + t[:, None] * pd
+        return pf[:, :2], alive & (pd[:, 2] < 0), ap, d
