@@ -81,6 +81,56 @@ struct Builder {
     }
 };
 
+// Optimal collapse of the binary tree into 8-wide nodes (the dynamic programme of Ylitie, Karras & Laine, "Efficient
+// Incoherent Ray Traversal on GPUs Through Compressed Wide BVHs", HPG 2017, section 3.1): cost[n][i] = cheapest way to
+// represent the subtree of binary node n as a forest of at most i+1 wide-node children (i = 0..6 -> 1..7 slots).
+//   C(n, 1) = min(C_leaf(n), C_internal(n)),  C_internal(n) = A(n) c_node + min_k C(l, k) + C(r, 8 - k)
+//   C(n, i) = min(C(n, i - 1), min_k C(l, k) + C(r, i - k))
+// The greedy "open the largest child" collapse left 60 % of the nodes of a 1M-triangle height field with only 2-3 children
+// (subtrees of 2-3 leaves that never got opened because their parent's slots had run out); the optimum fills the bottom.
+struct Collapse {
+    const std::vector<BinNode> &bn;
+    static constexpr float kNodeCost = 1.f, kTriCost = 0.3f;
+    std::vector<float> cost;        // [n][7]
+    std::vector<uint8_t> dec;       // [n][7]: 0 = leaf (i = 1 only), 255 = internal node (i = 1 only), 254 = same as i - 1, else k = slots of the left child
+    std::vector<uint8_t> split8;    // [n]: left-child slots of the best 8-slot distribution (the node itself as a wide node)
+    explicit Collapse(const std::vector<BinNode> &b) : bn(b), cost(b.size() * 7), dec(b.size() * 7), split8(b.size(), 0) {
+        for (int n = (int) bn.size() - 1; n >= 0; --n) solve(n);      // children have larger indices than their parent (pre-order)
+    }
+    float C(int n, int i) const { return cost[(size_t) n * 7 + (i - 1)]; }
+    void solve(int n) {
+        const BinNode &b = bn[n];
+        float *c = &cost[(size_t) n * 7]; uint8_t *d = &dec[(size_t) n * 7];
+        const float A = b.box.area();
+        if (b.left < 0) {                 // binary leaf (<= 3 triangles)
+            for (int i = 0; i < 7; ++i) { c[i] = A * kTriCost * (float) b.count; d[i] = i == 0 ? 0 : 254; }
+            return;
+        }
+        const int l = b.left, r = b.right;
+        float best8 = std::numeric_limits<float>::infinity(); int k8 = 1;
+        for (int k = 1; k <= 7; ++k) { const float v = C(l, k) + C(r, 8 - k); if (v < best8) { best8 = v; k8 = k; } }
+        split8[n] = (uint8_t) k8;
+        c[0] = A * kNodeCost + best8; d[0] = 255;
+        for (int i = 2; i <= 7; ++i) {
+            float best = c[i - 2]; uint8_t how = 254;
+            for (int k = 1; k < i; ++k) { const float v = C(l, k) + C(r, i - k); if (v < best) { best = v; how = (uint8_t) k; } }
+            c[i - 1] = best; d[i - 1] = how;
+        }
+    }
+    // the (binary) nodes that fill `i` slots under n
+    void collect(int n, int i, int *out, int &cnt) const {
+        while (i > 1 && dec[(size_t) n * 7 + (i - 1)] == 254) --i;
+        if (i == 1) { out[cnt++] = n; return; }
+        const int k = dec[(size_t) n * 7 + (i - 1)];
+        collect(bn[n].left, k, out, cnt); collect(bn[n].right, i - k, out, cnt);
+    }
+    int children(int n, int *out) const {     // children of the wide node rooted at the inner binary node n
+        int cnt = 0;
+        collect(bn[n].left, split8[n], out, cnt); collect(bn[n].right, 8 - split8[n], out, cnt);
+        return cnt;
+    }
+};
+
 uint8_t exponent_for(float extent) {
     // smallest e with 253 * 2^(e-127) >= extent (one quantisation step is reserved on each side, see below)
     if (!(extent > 0.f)) return 1;
@@ -114,6 +164,9 @@ void build_bvh8(const float *verts, const int32_t *idx, const int32_t *tri_shape
     B.bn.reserve(2 * (size_t) nt);
     B.build(0, (int) nt, 0, max_depth);
 
+    const char *cm = getenv("LRT_BVH_COLLAPSE");
+    const bool optimal = !(cm && cm[0] == 'g');          // LRT_BVH_COLLAPSE=greedy restores the round-1 collapse
+    Collapse *dp = optimal ? new Collapse(B.bn) : nullptr;
     // collapse: breadth-first emission so that the inner children of a node are contiguous
     struct Pending { int bin; };   // binary subtree root that becomes one wide node
     std::vector<int> queue; queue.push_back(0);
@@ -128,8 +181,9 @@ void build_bvh8(const float *verts, const int32_t *idx, const int32_t *tri_shape
         int ch[8]; int nch = 0;
         const BinNode &root = B.bn[bin_root];
         if (root.left < 0) { ch[nch++] = bin_root; }
+        else if (dp) nch = dp->children(bin_root, ch);
         else { ch[nch++] = root.left; ch[nch++] = root.right; }
-        while (nch < 8) {
+        while (!dp && nch < 8) {
             int best = -1; float ba = -1.f;
             for (int i = 0; i < nch; ++i) if (B.bn[ch[i]].left >= 0) { float a = B.bn[ch[i]].box.area(); if (a > ba) { ba = a; best = i; } }
             if (best < 0) break;
@@ -155,6 +209,7 @@ void build_bvh8(const float *verts, const int32_t *idx, const int32_t *tri_shape
                 ql[a][i] = (uint8_t) std::min(255.f, std::max(0.f, lo - 1.f));
                 qh[a][i] = (uint8_t) std::min(255.f, std::max(0.f, hi + 1.f));
             }
+            // (optimal collapse: a child is an inner wide node iff the programme decided so; a binary leaf is always a leaf)
             if (c.left >= 0) { n.meta[i] = (uint8_t) (0x80 | inner_k); inner_k++; queue.push_back(ch[i]); }
             else {
                 n.meta[i] = (uint8_t) ((c.count << 5) | tri_off); tri_off += c.count; leaves++;
@@ -173,6 +228,7 @@ void build_bvh8(const float *verts, const int32_t *idx, const int32_t *tri_shape
         if (nodes.size() < queue.size()) nodes.resize(queue.size());
         nodes[self] = n;
     }
+    delete dp;
     level_begin.push_back((int) nodes.size());
     if (stats) { stats->nodes = (int) nodes.size(); stats->leaves = leaves; stats->max_depth = max_depth; stats->level_begin = level_begin; }
 }
