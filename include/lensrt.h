@@ -268,6 +268,10 @@ typedef struct lrt_spot_params {
                                           miss masks are bit-exact). 1: the same algorithm with fused multiply-adds and hardware
                                           reciprocal / square-root approximations (last-ulp differences, ~2x the rays per second):
                                           what design loops use; primal and adjoint must use the same flavour */
+    /* Optional device-side seed for loops captured in a CUDA graph (launch parameters are frozen at capture): when
+     * seed_dev != NULL the effective seed is (seed + *seed_dev * seed_stride) ^ seed_xor, read by the kernel at run time. */
+    const uint32_t *seed_dev;
+    uint32_t seed_stride, seed_xor;
 } lrt_spot_params;
 
 /* Accumulates intensity*weight/spp (R,G,B) and 1/spp (W) times the normalised filter weights into accum_dev

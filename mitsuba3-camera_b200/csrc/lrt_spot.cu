@@ -39,6 +39,7 @@ static int spot_launch(lrt_sensor *s, const lrt_film_desc *film, const lrt_spot_
     LRT_REQUIRE(n_total < 4294967296.0, "W*H*spp exceeds 2^32: render in passes");
     rc = s->upload(stream); if (rc) return rc;
     A.lens = s->dev; A.seed = sp->seed; A.spp = sp->spp;
+    A.seed_dev = sp->seed_dev; A.seed_stride = sp->seed_stride; A.seed_xor = sp->seed_xor;
     for (int k = 0; k < 3; ++k) { A.src[k] = sp->src_p[k]; A.intensity[k] = sp->intensity[k]; }
     A.origin_offset = sp->origin_offset;
     const long long nt = (long long) n_total;

@@ -18,6 +18,7 @@ struct SpotArgs {
     const LensSystem *lens;
     FilmParams film;
     uint32_t seed; int spp;
+    const uint32_t *seed_dev; uint32_t seed_stride, seed_xor;   // seed = (seed + *seed_dev * seed_stride) ^ seed_xor when seed_dev is set
     float src[3], intensity[3], origin_offset;
     long long n_my; int shard_index, shard_count;
     float scale;
@@ -108,13 +109,15 @@ __global__ void __launch_bounds__(kSpotThreads) k_spot(SpotArgs A) {
     const int sw = F.size_x + 2 * F.border, sh = F.size_y + 2 * F.border;
     const strict::V3 src_p = strict::v3(A.src[0], A.src[1], A.src[2]);
     const int n_if = L.n;
+    // CUDA-graph friendly seeding: the iteration counter lives on the device, the launch parameters never change
+    const uint32_t seed = A.seed_dev ? ((A.seed + __ldg(A.seed_dev) * A.seed_stride) ^ A.seed_xor) : A.seed;
     unsigned long long n_samples = 0, n_valid = 0;
     float g_loc[kAdjoint ? kMaxInterfaces : 1][kSlots];
     if (kAdjoint) for (int i = 0; i < n_if; ++i) for (int k = 0; k < kSlots; ++k) g_loc[i][k] = 0.f;
 
     for (long long i = (long long) blockIdx.x * kSpotThreads + tid; i < A.n_my; i += (long long) gridDim.x * kSpotThreads) {
         const uint32_t idx = (uint32_t) (A.shard_index + i * A.shard_count);
-        Pcg32 rng; rng.seed_sample(A.seed, idx);
+        Pcg32 rng; rng.seed_sample(seed, idx);
         const float sa = rng.next_f32(), sb = rng.next_f32();
         n_samples++;
         if (!kAdjoint) {

@@ -21,7 +21,8 @@ f32 = np.float32
 
 class SpotParams(C.Structure):
     _fields_ = [("seed", C.c_uint32), ("spp", C.c_int32), ("src_p", C.c_float * 3), ("intensity", C.c_float * 3),
-                ("shard_index", C.c_int32), ("shard_count", C.c_int32), ("origin_offset", C.c_float), ("fast", C.c_int32)]
+                ("shard_index", C.c_int32), ("shard_count", C.c_int32), ("origin_offset", C.c_float), ("fast", C.c_int32),
+                ("seed_dev", C.c_void_p), ("seed_stride", C.c_uint32), ("seed_xor", C.c_uint32)]
 
 
 def field_source(angle_deg, distance=1.0e3, azimuth_deg=0.0, front_z=0.0):
@@ -36,9 +37,23 @@ def _film_desc(film):
     return FilmDesc(film.crop_w, film.crop_h, film.crop_x, film.crop_y, 0, 4, rf.kind, rf.param, 0, 1)
 
 
+class DeviceSeed:
+    """seed = (base + counter * stride) ^ xor with `counter` a uint32 CUDA tensor (for loops replayed from a CUDA graph)."""
+
+    def __init__(self, counter, base=0, stride=1, xor=0):
+        self.counter, self.base, self.stride, self.xor = counter, int(base), int(stride), int(xor)
+
+    def __xor__(self, mask):
+        return DeviceSeed(self.counter, self.base, self.stride, self.xor ^ int(mask))
+
+
 def _params(seed, spp, src_p, intensity, shard, origin_offset=0.0, fast=False):
     p = SpotParams()
-    p.seed, p.spp = int(seed) & 0xffffffff, int(spp)
+    if isinstance(seed, DeviceSeed):
+        p.seed, p.seed_dev, p.seed_stride, p.seed_xor = seed.base & 0xffffffff, seed.counter.data_ptr(), seed.stride & 0xffffffff, seed.xor & 0xffffffff
+    else:
+        p.seed = int(seed) & 0xffffffff
+    p.spp = int(spp)
     for k in range(3):
         p.src_p[k] = float(src_p[k]); p.intensity[k] = float(intensity[k])
     p.shard_index, p.shard_count = int(shard[0]), int(shard[1])
@@ -172,7 +187,8 @@ def spot_image(rows, sensor, src_p, intensity=(1.0, 1.0, 1.0), seed=0, spp=None,
     if _SpotRender is None:
         _SpotRender = _spot_function()
     spp = int(spp if spp else sensor.sampler.sample_count())
-    return _SpotRender.apply(rows, sensor, src_p, tuple(intensity), int(seed), spp, int(seed if seed_grad is None else seed_grad),
+    keep = lambda v: v if isinstance(v, DeviceSeed) else int(v)     # noqa: E731
+    return _SpotRender.apply(rows, sensor, src_p, tuple(intensity), keep(seed), spp, keep(seed if seed_grad is None else seed_grad),
                              int(spp_grad if spp_grad else spp), shard, float(origin_offset), bool(fast))
 
 
@@ -300,9 +316,11 @@ class LensDesignProblem:
         return rows
 
     def loss(self, rows, seed):
+        """seed: the iteration number (int), or a uint32 CUDA tensor holding it (graph replay)."""
         total = 0.0
         for k, (s, src) in enumerate(zip(self.sensors, self.sources)):
-            img = spot_image(rows, s, src, seed=seed * 64 + k, spp=self.spp, seed_grad=(seed * 64 + k) ^ 0x5bd1e995,
+            sd = DeviceSeed(seed, base=k, stride=64) if hasattr(seed, "data_ptr") else seed * 64 + k
+            img = spot_image(rows, s, src, seed=sd, spp=self.spp, seed_grad=sd ^ 0x5bd1e995,
                              spp_grad=self.spp_grad, shard=self.shard, origin_offset=self.origin_offset, fast=self.fast)
             # sample-index sharding: the (non-linear) loss is evaluated on the image summed over ranks, never on a partial one
             img = sum_over_ranks(img) if self.shard[1] > 1 else img
@@ -326,4 +344,39 @@ class LensDesignProblem:
         if record_loss:
             self.losses.append(float(self.last_loss))
             return self.losses[-1]
+        return self.last_loss
+
+    # ---- the whole iteration as one CUDA graph (ms-scale iterations are launch / host-latency bound)
+    def capture(self, warmup=3):
+        """Captures rows() -> per-field primal renders -> loss -> adjoint renders -> (all-reduces) -> Adam step into a CUDA graph.
+        The iteration counter is a device scalar the spot kernels read their seeds from, so every replay draws fresh samples.
+        Afterwards step_graph() replays it; self.last_loss holds the loss of the last replay (device tensor)."""
+        torch = self.torch
+        self._it_dev = torch.full((1,), self.iteration, dtype=torch.int32, device=self.device)
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for _ in range(warmup):
+                self._graph_body()
+        torch.cuda.current_stream().wait_stream(side)
+        self._graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self._graph):
+            self._graph_body()
+        return self
+
+    def _graph_body(self):
+        from .parallel import all_reduce_sum
+        if self.theta.grad is not None:         # (static gradient tensor: created by the first warm-up iteration, zeroed afterwards)
+            self.theta.grad.zero_()
+        l = self.loss(self.rows(), self._it_dev)
+        l.backward()
+        if self.shard[1] > 1:
+            all_reduce_sum(self.theta.grad)
+        self.opt.step()
+        self._it_dev += 1
+        self.last_loss = l.detach()
+
+    def step_graph(self):
+        self._graph.replay()
+        self.iteration += 1
         return self.last_loss

@@ -260,3 +260,24 @@ def test_gpu_fast_flavour_agrees_with_strict(mi):
     assert abs(int(a[2][1]) - int(b[2][1])) <= 1e-4 * a[2][1] and a[2][1] > 1e5
     cos = float(a[1] @ b[1] / (np.linalg.norm(a[1]) * np.linalg.norm(b[1])))
     assert cos >= 0.9999, cos
+
+
+@pytest.mark.gpu
+def test_gpu_design_iteration_as_cuda_graph(mi):
+    """LensDesignProblem.capture(): the iteration replayed from one CUDA graph draws fresh samples every replay (device-side
+    seed counter) and follows the eager trajectory (same seeds, same arithmetic: equal to float atomics' summation order)."""
+    import torch
+    L = mi.lens_design
+    rows = _doublet_rows(mi)
+    eager = L.LensDesignProblem(mi, rows, [0.0, 2.5, 5.0], resolution=64, full_res=2048, spp=32, spp_grad=16, lr=2e-4)
+    for _ in range(3 + 5):
+        eager.step()
+    graph = L.LensDesignProblem(mi, rows, [0.0, 2.5, 5.0], resolution=64, full_res=2048, spp=32, spp_grad=16, lr=2e-4)
+    graph.capture(warmup=3)               # three warm-up iterations run eagerly and count as iterations 0..2
+    losses = []
+    for _ in range(5):
+        losses.append(float(graph.step_graph()))
+    assert len(set(losses)) == 5                                   # fresh samples every replay
+    a, b = eager.theta.detach().cpu().numpy(), graph.theta.detach().cpu().numpy()
+    assert np.abs(a - b).max() <= 1e-4 * max(np.abs(a).max(), 1.0), np.abs(a - b).max()
+    assert np.allclose(losses, eager.losses[3:8], rtol=1e-3)
