@@ -154,7 +154,10 @@ int lrt_filter_eval_host(int32_t filter, float param, int32_t n, const float *x,
  *                            or specular_reflectance rgb, eta rgb, k rgb (conductor), specular_transmittance
  *                            rgb, eta = int_ior/ext_ior (dielectric), texture id + 1 of a diffuse `reflectance`
  *                            bitmap (0 = the constant rgb)
- *   emitters[n_emitters,16]: radiance rgb, shape id, centre xyz, half-edge u xyz, half-edge v xyz, pad
+ *   emitters[n_emitters,16]: radiance rgb, shape id, centre xyz, half-edge u xyz, half-edge v xyz, kind (col 13), pad.
+ *                            kind 0 = `area` on a `rectangle` (sampled through the rectangle's parameterisation, rectangle.cpp:166-185);
+ *                            kind 1 = `area` on any mesh: faces sampled by area, Mesh::sample_position (src/render/mesh.cpp:430-470,
+ *                            745-803); centre / half-edges are ignored, the shape's triangles (and vertex normals) are used
  * BitmapTexture (src/textures/bitmap.cpp:115-310): RGB float texels (already linear), bilinear filter. */
 typedef struct lrt_texture_desc {
     int32_t width, height;

@@ -306,7 +306,7 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
                                 // iteration are committed when the bounce is finished
                                 Pcg32 peek = rng;
                                 float e_sx = peek.next_f32(), e_sy = peek.next_f32();
-                                EmitterSample es = sample_emitter_direction(A.sc, si.p, e_sx, e_sy);
+                                EmitterSample es = sample_emitter_direction<kAttr>(A.sc, si.p, e_sx, e_sy);
                                 if (es.pdf != 0.f) {   // shadow ray: Interaction::spawn_ray_to (interaction.h:139-146)
                                     float3 so = offset_p(si.p, si.n, es.p - si.p);
                                     float3 sd = es.p - so; float sdist = sqrtf(dot(sd, sd));
@@ -330,7 +330,7 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
                     float rr_sample = rng.next_f32();
                     EmitterSample es; es.pdf = 0.f; float3 wo = make_float3(0, 0, 0);
                     const bool active_em = phase == 2 && !occluded;
-                    if (active_em) { es = sample_emitter_direction(A.sc, si.p, e_sx, e_sy); wo = si.to_local(es.d); }
+                    if (active_em) { es = sample_emitter_direction<kAttr>(A.sc, si.p, e_sx, e_sy); wo = si.to_local(es.d); }
                     BsdfResult bs = bsdf_eval_pdf_sample<kAttr>(A.sc, bsdf_id, si.uv, si.wi, wo, s1, s2x, s2y);
                     if (kAdj) {   // everything gathered from here on is linear in this surface's (specular) reflectance
                         // the sampled lobe's colour: (specular) reflectance, or the dielectric's specular_transmittance
@@ -486,7 +486,7 @@ int launch_render(const lrt_scene *sc, lrt_sensor *sensor, const lrt_film_desc *
                 "lrt_render_backward: max_depth must be in [0, 17] (one gradient record per bounce; unbounded paths are not supported)");
     A.grad_storage = grad_storage; A.grad_bsdfs = grad_bsdfs; A.grad_emitters = grad_emitters; A.n_bsdfs = sc->n_bsdfs;
     int per_sm = 1;
-    const bool attr = sc->view.tri_attr != nullptr || sc->view.textures != nullptr;
+    const bool attr = sc->view.tri_attr != nullptr || sc->view.textures != nullptr || sc->view.em_tris != nullptr;
     void (*kern)(RenderArgs) = adjoint ? (attr ? k_render<true, true> : k_render<true, false>) : (attr ? k_render<false, true> : k_render<false, false>);
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kCtaThreads, smem);
     if (per_sm < 1) per_sm = 1;

@@ -83,9 +83,31 @@ int lrt_scene_create(const lrt_scene_desc *d, lrt_scene **out) {
     s->n_shapes = d->n_shapes; s->n_bsdfs = d->n_bsdfs; s->n_emitters = d->n_emitters;
     // emitters: 16-float rows -> 5 x float4 with the rectangle's normal and 1/area (rectangle.cpp:115-123)
     std::vector<float> em((size_t) d->n_emitters * 20, 0.f);
+    std::vector<float> em_tris;     // 24 floats per triangle of a mesh emitter
     for (int i = 0; i < d->n_emitters; ++i) {
         const float *r = d->emitters + 16 * i; float *o = em.data() + 20 * (size_t) i;
         o[0] = r[0]; o[1] = r[1]; o[2] = r[2]; o[3] = r[3];
+        if (r[13] == 1.f) {   // area light on a general mesh: Mesh::build_pmf (src/render/mesh.cpp:430-470) + DiscreteDistribution
+            const int shape = (int) r[3];
+            const bool has_n = d->vertex_normals && d->shape_flags && (d->shape_flags[shape] & 1);
+            const int first = (int) (em_tris.size() / 24); int count = 0; double sum = 0.0;
+            for (int64_t t = 0; t < d->n_triangles; ++t) {
+                if (d->tri_shape[t] != shape) continue;
+                const int32_t *f = d->indices + 3 * t;
+                const float *p0 = d->vertices + 3 * (size_t) f[0], *p1 = d->vertices + 3 * (size_t) f[1], *p2 = d->vertices + 3 * (size_t) f[2];
+                const float a[3] = { p1[0] - p0[0], p1[1] - p0[1], p1[2] - p0[2] }, b[3] = { p2[0] - p0[0], p2[1] - p0[1], p2[2] - p0[2] };
+                const float cx = a[1] * b[2] - a[2] * b[1], cy = a[2] * b[0] - a[0] * b[2], cz = a[0] * b[1] - a[1] * b[0];
+                const float area = .5f * std::sqrt((cx * cx + cy * cy) + cz * cz);
+                sum += (double) area;
+                float rec[24] = { p0[0], p0[1], p0[2], (float) sum, a[0], a[1], a[2], area, b[0], b[1], b[2], has_n ? 1.f : 0.f };
+                for (int k = 0; k < 3 && has_n; ++k) for (int c = 0; c < 3; ++c) rec[12 + 4 * k + c] = d->vertex_normals[3 * (size_t) f[k] + c];
+                em_tris.insert(em_tris.end(), rec, rec + 24); count++;
+            }
+            LRT_REQUIRE(count > 0 && sum > 0.0, "a mesh emitter needs triangles with a non-zero area");
+            const float fsum = em_tris[em_tris.size() - 24 + 3];      // m_sum = the last cdf entry (float)
+            memcpy(o + 4, &first, 4); memcpy(o + 5, &count, 4); o[6] = fsum; o[7] = 1.f / fsum; o[19] = 1.f;
+            continue;
+        }
         o[4] = r[4]; o[5] = r[5]; o[6] = r[6];
         for (int k = 0; k < 3; ++k) { o[8 + k] = r[7 + k]; o[12 + k] = r[10 + k]; }
         float ex[3] = { r[7], r[8], r[9] }, ey[3] = { r[10], r[11], r[12] };
@@ -98,7 +120,8 @@ int lrt_scene_create(const lrt_scene_desc *d, lrt_scene **out) {
     if ((rc = upload(&s->d_nodes, nodes.data(), nodes.size())) || (rc = upload(&s->d_tris, tris.data(), tris.size())) ||
         (rc = upload(&s->d_shape_bsdf, d->shape_bsdf, (size_t) d->n_shapes)) ||
         (rc = upload(&s->d_shape_emitter, d->shape_emitter, (size_t) d->n_shapes)) ||
-        (rc = upload(&s->d_bsdfs, d->bsdfs, (size_t) d->n_bsdfs * 16)) || (rc = upload(&s->d_emitters, em.data(), em.size()))) {
+        (rc = upload(&s->d_bsdfs, d->bsdfs, (size_t) d->n_bsdfs * 16)) || (rc = upload(&s->d_emitters, em.data(), em.size())) ||
+        (!em_tris.empty() && (rc = upload(&s->d_em_tris, em_tris.data(), em_tris.size())))) {
         lrt_scene_destroy(s); return rc;
     }
     if ((rc = upload(&s->d_tri_vidx, tri_vidx.data(), tri_vidx.size()))) { lrt_scene_destroy(s); return rc; }
@@ -127,6 +150,7 @@ int lrt_scene_create(const lrt_scene_desc *d, lrt_scene **out) {
     s->view.bsdfs = (const float4 *) s->d_bsdfs; s->view.emitters = (const float4 *) s->d_emitters;
     s->view.n_emitters = d->n_emitters;
     s->view.tri_attr = (const float4 *) s->d_tri_attr; s->view.textures = (const TexView *) s->d_textures;
+    s->view.em_tris = (const float4 *) s->d_em_tris;
     *out = s;
     return LRT_OK;
 }
@@ -145,7 +169,7 @@ int lrt_scene_set_params(lrt_scene *s, const float *bsdfs, const float *emitter_
 void lrt_scene_destroy(lrt_scene *s) {
     if (!s) return;
     void *p[] = { s->d_nodes, s->d_tris, s->d_shape_bsdf, s->d_shape_emitter, s->d_bsdfs, s->d_emitters, s->d_counter,
-                  s->d_tri_attr, s->d_tex_data, s->d_textures, s->d_tri_vidx, s->d_node_box };
+                  s->d_tri_attr, s->d_tex_data, s->d_textures, s->d_tri_vidx, s->d_node_box, s->d_em_tris };
     for (void *q : p) if (q) cudaFree(q);
     delete s;
 }

@@ -31,6 +31,10 @@ struct SceneView {
     // (bits 2 / 3 mark the two triangles of a tessellated rectangle, see make_surface)
     const float4 *tri_attr;
     const TexView *textures;
+    // area emitters on general meshes (src/render/mesh.cpp:430-470,745-803): per emitter triangle 6 x float4 =
+    // [p0.xyz, cdf | e0.xyz, pmf | e1.xyz, has_normals | n0 | n1 | n2], in the mesh's own face order; the emitter record
+    // (second float4) then holds (first triangle, count, area sum, 1 / area sum) and its last float4 .w = 1 marks the kind
+    const float4 *em_tris;
 };
 
 struct Surface {
@@ -206,8 +210,33 @@ LRT_D bool bsdf_is_smooth(const SceneView &sc, int bsdf_id) { return (int) __ldg
 
 struct EmitterSample { float3 p, n, d; float dist, pdf; float3 weight; };
 
+// Mesh::sample_position (mesh.cpp:745-803): face by the area distribution with sample reuse (distr_1d.h:116-182), uniform
+// point on it (warp.h:153-156), interpolated vertex normal when the mesh has normals. Out of line: cold for rectangle lights.
+static __device__ __noinline__ void mesh_emitter_sample_position(const SceneView &sc, float4 e1, float sx, float sy, float3 &p, float3 &n) {
+    const int first = __float_as_int(e1.x), count = __float_as_int(e1.y);
+    const float sum = e1.z, norm = e1.w;
+    const float target = sy * sum;
+    int lo = 0, hi = count - 1;                       // first index whose cdf is not < target (all faces have area > 0)
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        if (__ldg(sc.em_tris + 6 * (size_t) (first + mid)).w < target) lo = mid + 1; else hi = mid;
+    }
+    const float4 *t = sc.em_tris + 6 * (size_t) (first + lo);
+    const float4 t0 = __ldg(t), t1 = __ldg(t + 1), t2 = __ldg(t + 2);
+    const float cdf_prev = lo > 0 ? __ldg(sc.em_tris + 6 * (size_t) (first + lo - 1)).w * norm : 0.f;
+    const float sy2 = (sy - cdf_prev) / (t1.w * norm);
+    const float tt = sqrtf(fmaxf(1.f - sx, 0.f)), b0 = 1.f - tt, b1 = tt * sy2;
+    const float3 p0 = make_float3(t0.x, t0.y, t0.z), e0 = make_float3(t1.x, t1.y, t1.z), ee1 = make_float3(t2.x, t2.y, t2.z);
+    p = e0 * b0 + (ee1 * b1 + p0);
+    if (t2.w != 0.f) {
+        const float4 a = __ldg(t + 3), b = __ldg(t + 4), c = __ldg(t + 5);
+        n = make_float3(a.x, a.y, a.z) * (1.f - b0 - b1) + (make_float3(b.x, b.y, b.z) * b0 + make_float3(c.x, c.y, c.z) * b1);
+    } else n = cross(e0, ee1);
+    n = normalize(n);
+}
+
 // Scene::sample_emitter_direction (scene.cpp:299-353) without the visibility test (done by the caller)
-LRT_D EmitterSample sample_emitter_direction(const SceneView &sc, float3 ref_p, float sx, float sy) {
+template <bool kAttr = true> LRT_D EmitterSample sample_emitter_direction(const SceneView &sc, float3 ref_p, float sx, float sy) {
     EmitterSample es; es.pdf = 0.f; es.weight = make_float3(0, 0, 0); es.p = es.n = es.d = make_float3(0, 0, 0); es.dist = 0.f;
     int count = sc.n_emitters;
     if (count == 0) return es;
@@ -219,16 +248,20 @@ LRT_D EmitterSample sample_emitter_direction(const SceneView &sc, float3 ref_p, 
     }
     const float4 *ep = sc.emitters + 5 * (size_t) index;
     float4 e0 = __ldg(ep), e1 = __ldg(ep + 1), e2 = __ldg(ep + 2), e3 = __ldg(ep + 3), e4 = __ldg(ep + 4);
-    float ux = sx * 2.f - 1.f, uy = sy * 2.f - 1.f;
-    es.p = make_float3(e1.x, e1.y, e1.z) + make_float3(e2.x, e2.y, e2.z) * ux + make_float3(e3.x, e3.y, e3.z) * uy;
-    es.n = make_float3(e4.x, e4.y, e4.z);
+    float inv_area = e1.w;
+    if (kAttr && e4.w != 0.f) mesh_emitter_sample_position(sc, e1, sx, sy, es.p, es.n);
+    else {
+        float ux = sx * 2.f - 1.f, uy = sy * 2.f - 1.f;
+        es.p = make_float3(e1.x, e1.y, e1.z) + make_float3(e2.x, e2.y, e2.z) * ux + make_float3(e3.x, e3.y, e3.z) * uy;
+        es.n = make_float3(e4.x, e4.y, e4.z);
+    }
     float3 d = es.p - ref_p;
     float dist2 = dot(d, d);
     es.dist = sqrtf(dist2);
     es.d = d * (1.f / es.dist);
     float dn = dot(es.d, es.n);
     float x = dist2 / fabsf(dn);
-    float pdf = e1.w * (isfinite(x) ? x : 0.f);
+    float pdf = inv_area * (isfinite(x) ? x : 0.f);
     bool active = dn < 0.f && pdf != 0.f;
     if (active) {
         es.weight = make_float3(e0.x, e0.y, e0.z) * (emitter_weight / pdf);

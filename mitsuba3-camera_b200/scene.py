@@ -323,6 +323,7 @@ class SceneData:
         if emitter is not None:
             row = np.zeros(16, f32); row[0:3] = emitter["radiance"]; row[3] = sid
             row[4:7], row[7:10], row[10:13] = emitter["center"], emitter["ex"], emitter["ey"]
+            row[13] = emitter.get("kind", 0)
             self.emitter_rows.append(row); self.shape_emitter.append(len(self.emitter_rows) - 1)
         else:
             self.shape_emitter.append(-1)
@@ -720,7 +721,9 @@ def scene_data_from_dict(d: dict):
     for key, v in d.items():   # named BSDFs first: they are the targets of {'type': 'ref'}
         if isinstance(v, dict) and v.get("type") in _BSDFS:
             named_bsdf[v.get("id", key)] = data.add_bsdf(key, bsdf_row(v, data.textures))
-    for key, v in d.items():
+    # child objects in the order of their keys: the reference keeps a scene's properties in a sorted map (shapes / emitters come
+    # out alphabetically, e.g. scene.emitters()), and the emitter index a sample selects depends on that order
+    for key, v in sorted(d.items(), key=lambda kv: kv[0]):
         if not isinstance(v, dict):
             continue
         vt = v.get("type")
@@ -770,10 +773,14 @@ def scene_data_from_dict(d: dict):
             em = v.get("emitter")
             emitter = None
             if em is not None:
-                if em.get("type") != "area" or vt != "rectangle":
-                    raise ValueError("this build supports `area` emitters on `rectangle` shapes")
-                emitter = {"radiance": _rgb(em.get("radiance"), [1, 1, 1]), "center": tw.transform_affine(np.zeros(3, f32)),
-                           "ex": tw.transform_vector(np.array([1, 0, 0], f32)), "ey": tw.transform_vector(np.array([0, 1, 0], f32))}
+                if em.get("type") != "area":
+                    raise ValueError(f"emitter plugin '{em.get('type')}' is outside the hot path of this build (only `area`)")
+                rad = em.get("radiance")
+                if isinstance(rad, dict) and rad.get("type") not in (None, "rgb", "spectrum", "uniform"):
+                    raise ValueError("area emitters: only a constant radiance is built")
+                emitter = {"radiance": _rgb(rad, [1, 1, 1]), "center": tw.transform_affine(np.zeros(3, f32)),
+                           "ex": tw.transform_vector(np.array([1, 0, 0], f32)), "ey": tw.transform_vector(np.array([0, 1, 0], f32)),
+                           "kind": 0 if vt == "rectangle" else 1}      # 1: faces sampled by area (Mesh::sample_position)
             sid = data.add_shape(key, verts, faces, bid, emitter, normals, uvs, rectangle=vt == "rectangle")
             if vt == "rectangle":
                 data.rectangles.append((sid, tw.matrix.copy()))

@@ -21,11 +21,25 @@ class Transform4f:
     __mul__ = __matmul__
 
     def transform_affine(self, p):
+        """transform.h:104-111: start from the translation column, then one multiply-add per matrix column in float32 —
+        product and sum rounded separately, as the reference's portable scalar build evaluates dr::fmadd (the build the
+        oracle is pinned to; a build with hardware FMA differs in the last bit). Mesh loaders (ply.cpp:295, obj.cpp:237,
+        cube.cpp:148) apply exactly this to every vertex, so vertices come out bit-equal."""
         p = np.asarray(p, f32)
-        return (p @ self.matrix[:3, :3].T + self.matrix[:3, 3]).astype(f32)
+        m = self.matrix
+        r = np.broadcast_to(m[:3, 3], p.shape).astype(f32)
+        for i in range(3):
+            r = (m[:3, i] * p[..., i:i + 1]).astype(f32) + r
+        return r.astype(f32)
 
     def transform_vector(self, v):
-        return (np.asarray(v, f32) @ self.matrix[:3, :3].T).astype(f32)
+        """transform.h:128-137: column 0 times x, then multiply-adds of the other two columns."""
+        v = np.asarray(v, f32)
+        m = self.matrix
+        r = (m[:3, 0] * v[..., 0:1]).astype(f32)
+        for i in (1, 2):
+            r = (m[:3, i] * v[..., i:i + 1]).astype(f32) + r
+        return r.astype(f32)
 
     def inverse(self):
         return Transform4f(np.linalg.inv(self.matrix.astype(np.float64)).astype(f32))

@@ -33,7 +33,8 @@ namespace orc {
 
 struct Tri { V3 p0, p1, p2; int shape; int flags; V3 n0, n1, n2; V2 uv0, uv1, uv2; };   // flags: 1 normals, 2 uvs
 struct Bsdf { int type; bool twosided; V3 refl, eta, k, trans; float eta_s; int tex; };  // 0 diffuse 1 conductor 2 dielectric
-struct Emitter { V3 radiance; int shape; V3 c, ex, ey, n; float inv_area; };
+struct EmTri { V3 p0, e0, e1; float pmf, cdf; bool has_n; V3 n0, n1, n2; };
+struct Emitter { V3 radiance; int shape; V3 c, ex, ey, n; float inv_area; int kind = 0; std::vector<EmTri> tris; float sum = 0; };   // kind 1: mesh
 struct Rect { int shape; float M[12], Minv[12]; V3 dp_du, dp_dv, n; };                  // rows of the affine 3x4 matrices
 struct Texture { int w, h, wrap; std::vector<float> data; float to_uv[6]; };            // wrap: 0 repeat 1 mirror 2 clamp
 
@@ -349,12 +350,33 @@ static float mis_weight(float a, float b) {     // path.cpp:300-305
 struct DS { V3 p, n, d; float dist = 0, pdf = 0; int emitter = -1; };
 
 // rectangle.cpp:166-180 + shape.cpp:358-375 + area.cpp:115-166 (uniform radiance branch)
+// Mesh::sample_position (src/render/mesh.cpp:745-803) with DiscreteDistribution::sample_reuse (core/distr_1d.h:116-182) and
+// warp::square_to_uniform_triangle (core/warp.h:153-156)
+static void mesh_sample_position(const Emitter &e, V2 sample, V3 &p, V3 &n) {
+    float target = sample.y * e.sum;
+    size_t lo = 0, hi = e.tris.size() - 1;              // dr::binary_search over [valid.x, valid.y]: first index with !(cdf < target)
+    while (lo < hi) { size_t mid = (lo + hi) >> 1; if (e.tris[mid].cdf < target) lo = mid + 1; else hi = mid; }
+    const EmTri &t = e.tris[lo];
+    float norm = e.inv_area;
+    float pmf_n = t.pmf * norm, cdf_prev = lo > 0 ? e.tris[lo - 1].cdf * norm : 0.f;
+    float sy = (sample.y - cdf_prev) / pmf_n;
+    float tt = std::sqrt(std::fmax(1.f - sample.x, 0.f)), b0 = 1.f - tt, b1 = tt * sy;
+    p = fmadd3(t.e0, b0, fmadd3(t.e1, b1, t.p0));
+    if (t.has_n) n = fmadd3(t.n0, 1.f - b0 - b1, fmadd3(t.n1, b0, t.n2 * b1));
+    else n = cross(t.e0, t.e1);
+    n = normalize(n);
+}
+
 static bool emitter_sample_direction(const Emitter &e, V3 ref_p, V2 sample, DS &ds, V3 &spec) {
-    float sx = sample.x * 2.f - 1.f, sy = sample.y * 2.f - 1.f;
-    // to_world.transform_affine(Point3f(sx, sy, 0)): fmadd chain over the matrix columns (ex, ey, -, c)
-    ds.p = { fmadd(e.ey.x, sy, fmadd(e.ex.x, sx, e.c.x)), fmadd(e.ey.y, sy, fmadd(e.ex.y, sx, e.c.y)),
-             fmadd(e.ey.z, sy, fmadd(e.ex.z, sx, e.c.z)) };
-    ds.n = e.n; ds.pdf = e.inv_area;
+    if (e.kind == 1) mesh_sample_position(e, sample, ds.p, ds.n);
+    else {
+        float sx = sample.x * 2.f - 1.f, sy = sample.y * 2.f - 1.f;
+        // to_world.transform_affine(Point3f(sx, sy, 0)): fmadd chain over the matrix columns (ex, ey, -, c)
+        ds.p = { fmadd(e.ey.x, sy, fmadd(e.ex.x, sx, e.c.x)), fmadd(e.ey.y, sy, fmadd(e.ex.y, sx, e.c.y)),
+                 fmadd(e.ey.z, sy, fmadd(e.ex.z, sx, e.c.z)) };
+        ds.n = e.n;
+    }
+    ds.pdf = e.inv_area;
     ds.d = ds.p - ref_p;
     float dist2 = squared_norm(ds.d);
     ds.dist = std::sqrt(dist2);
@@ -566,6 +588,18 @@ void *orc_scene_create2(int nv, const float *verts, const float *normals, const 
         // rectangle.cpp:115-123: frame from dp_du = 2 ex, dp_dv = 2 ey; area = |dp_du x dp_dv|
         V3 cr = cross(e.ex * 2.f, e.ey * 2.f);
         e.n = normalize(cross(e.ex, e.ey)); e.inv_area = rcp(norm(cr));
+        if (r[13] == 1.f) {     // mesh emitter: Mesh::build_pmf (mesh.cpp:430-470), cdf accumulated in double (distr_1d.h:233-262)
+            e.kind = 1; double sum = 0.0;
+            for (int t = 0; t < nt; ++t) {
+                if (tri_shape[t] != e.shape) continue;
+                const Tri &tr = s->tris[t];
+                EmTri q; q.p0 = tr.p0; q.e0 = tr.p1 - tr.p0; q.e1 = tr.p2 - tr.p0;
+                q.pmf = .5f * norm(cross(q.e0, q.e1)); sum += (double) q.pmf; q.cdf = (float) sum;
+                q.has_n = (tr.flags & 1) != 0; q.n0 = tr.n0; q.n1 = tr.n1; q.n2 = tr.n2;
+                e.tris.push_back(q);
+            }
+            e.sum = e.tris.back().cdf; e.inv_area = rcp(e.sum);
+        }
         s->emitters.push_back(e);
     }
     size_t off = 0;

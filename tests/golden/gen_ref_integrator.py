@@ -143,6 +143,21 @@ def gen_functions(out):
             vals[i] = [*tex.eval(si)]
         out["tex_" + wrap] = vals
 
+    # ---- I2 on general meshes: emitter sampling in the mesh_lights scene (cube with normals, smooth icosphere, rectangle)
+    d, _ = rs.scene_dicts(T)["mesh_lights"]
+    scene = mi.load_dict(d)
+    emitters = list(scene.emitters()); em_ids = [e.shape().id() for e in emitters]
+    n = 2048
+    ref_p = rng.uniform(-0.9, 0.9, (n, 3)).astype(f32)
+    smp = rng.random((n, 2)).astype(f32)
+    rows = np.zeros((n, 16), f32)
+    for i in range(n):
+        it = mi.SurfaceInteraction3f(); it.p = [float(x) for x in ref_p[i]]; it.n = [0, 0, 1]; it.t = 1.0
+        ds, w = scene.sample_emitter_direction(it, [float(smp[i, 0]), float(smp[i, 1])], False)
+        pdf2 = scene.pdf_emitter_direction(it, ds) if ds.pdf > 0 else 0.0
+        rows[i] = [*ds.p, *ds.n, *ds.d, ds.dist, ds.pdf, *w, pdf2, em_ids.index(ds.emitter.shape().id()) if ds.pdf > 0 else -1]
+    out["mesh_em_ref_p"], out["mesh_em_sample"], out["mesh_em_dir"], out["mesh_em_ids"] = ref_p, smp, rows, np.array(em_ids)
+
 
 def matrices_of(d, prefix, store):
     for k, v in d.items():

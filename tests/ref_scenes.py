@@ -183,4 +183,16 @@ def scene_dicts(T):
          "lamp": {"type": "rectangle", "to_world": T(mm(m_translate([0, 3.0, 0.5]), m_rotate([1, 0, 0], 90), m_scale([0.8, 0.8, 1.0]))),
                   "bsdf": white, "emitter": {"type": "area", "radiance": {"type": "rgb", "value": [12.0, 11.0, 10.0]}}}}
     out["textured"] = (d, 32)
+
+    # area lights on general meshes (faces sampled by area): a cube (vertex normals + uvs), a smooth icosphere, next to a rectangle
+    d = {"type": "scene", "integrator": {"type": "path", "max_depth": 5},
+         "sensor": {"type": "perspective", "fov": 39.3077, "fov_axis": "smaller", "near_clip": 1e-3, "far_clip": 100.0, "to_world": cam,
+                    "sampler": {"type": "independent", "sample_count": 32}, "film": _film(96)},
+         "light": light,
+         "cube-light": {"type": "cube", "to_world": T(mm(m_translate([-0.5, -0.75, 0.2]), m_rotate([0, 1, 0], 30), m_scale([0.2, 0.25, 0.15]))),
+                        "bsdf": white, "emitter": {"type": "area", "radiance": {"type": "rgb", "value": [1.0, 4.0, 2.0]}}},
+         "ball-light": {"type": "ply", "filename": MESH_SMOOTH, "to_world": T(mm(m_translate([0.45, -0.2, -0.2]), m_scale(0.25))),
+                        "bsdf": white, "emitter": {"type": "area", "radiance": {"type": "rgb", "value": [5.0, 2.0, 1.0]}}}}
+    d.update(_box_walls(T, white, green, red))
+    out["mesh_lights"] = (d, 32)
     return out

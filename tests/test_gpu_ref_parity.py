@@ -38,7 +38,7 @@ def oracle_jit_render(mi, sc, d, spp, seed):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("name", ["cbox", "cbox_doublet", "cbox_materials", "textured"])
+@pytest.mark.parametrize("name", ["cbox", "cbox_doublet", "cbox_materials", "textured", "mesh_lights"])
 def test_gpu_scalar_convention_vs_reference_images(mi, R, name):
     d, spp = ref_scene(mi, R, name)
     sc = mi.load_dict(d)
@@ -62,7 +62,7 @@ def test_gpu_scalar_convention_other_seed_and_1spp(mi, R):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("name", ["cbox", "cbox_doublet", "cbox_materials", "textured"])
+@pytest.mark.parametrize("name", ["cbox", "cbox_doublet", "cbox_materials", "textured", "mesh_lights"])
 def test_gpu_default_mode_vs_pinned_oracle(mi, R, name):
     """The fast path (per-sample streams, coalesced splat) against the pinned oracle's JIT-convention render: C1 at its own
     size, the lens scene, conductor + dielectric + twosided + two emitters with Russian roulette, textures + vertex normals."""
