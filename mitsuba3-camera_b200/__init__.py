@@ -12,6 +12,7 @@ from .scene import (Scene, SceneData, PathIntegrator, PRBIntegrator, Independent
                     film_desc, RenderParams, SceneDesc, load_obj, load_ply, scene_data_from_dict, render_backward, traverse,
                     SceneParameters)
 from . import scene, workloads, lens_design, parallel, imageio, ad, mesh_lens
+from .xml import load_file, load_string, xml_to_dict, XMLError
 from . import imageio as util          # mi.util.write_bitmap (src/python/python/util.py) for .exr / .pfm
 from .lens_design import spot_render, spot_render_backward, spot_image, rms_loss, field_source
 

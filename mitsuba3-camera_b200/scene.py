@@ -67,10 +67,33 @@ IOR = {"vacuum": 1.0, "air": 1.000277, "water": 1.3330, "bk7": 1.5046, "diamond"
 WRAP_MODES = {"repeat": 0, "mirror": 1, "clamp": 2}
 
 
+# procedural textures: `checkerboard` (src/textures/checkerboard.cpp) and the fork's line patterns `checkerlines`, `comb2d`,
+# `polarlines` (src/textures/{checkerlines,comb2d,polarlines}.cpp): kind, default color0 / color1 / linewidth / spokes
+PROCEDURAL_TEXTURES = {"checkerboard": (1, .4, .2, 0.0, 0), "checkerlines": (2, .4, .05, .05, 0), "comb2d": (3, .4, .05, .01, 0),
+                       "polarlines": (4, .4, .05, .05, 16)}
+TEXTURE_TYPES = ("bitmap",) + tuple(PROCEDURAL_TEXTURES)
+
+
+def _to_uv(d):
+    tu = d.get("to_uv")
+    m = np.eye(3, dtype=f32) if tu is None else np.asarray(getattr(tu, "matrix", tu), f32)
+    if m.shape == (4, 4):      # "A 4x4 matrix can also be provided. In that case, the last row and columns will be ignored"
+        m = np.array([[m[0, 0], m[0, 1], m[0, 3]], [m[1, 0], m[1, 1], m[1, 3]], [0, 0, 1]], f32)
+    return np.ascontiguousarray(m.reshape(3, 3)[:2].reshape(-1), f32)
+
+
 def load_texture(d: dict) -> dict:
     """`bitmap` texture plugin (src/textures/bitmap.cpp:115-310) -> {'rgb': [h,w,3] float32 linear, 'wrap', 'to_uv'}.
     Sources: 'filename' (.exr / .pfm natively; 8-bit formats through OpenCV when present, sRGB -> linear unless raw)
-    or 'data' ([h,w,3] array). Only the bilinear filter of RGB textures is on the hot path."""
+    or 'data' ([h,w,3] array). Only the bilinear filter of RGB textures is on the hot path.
+    Procedural patterns (PROCEDURAL_TEXTURES) with constant colours add 'kind', 'color0', 'color1', 'linewidth', 'spokes'."""
+    if d.get("type") in PROCEDURAL_TEXTURES:
+        kind, c0, c1, lw, spokes = PROCEDURAL_TEXTURES[d["type"]]
+        for k in ("color0", "color1"):
+            if isinstance(d.get(k), dict) and d[k].get("type") not in (None, "rgb", "spectrum", "uniform"):
+                raise ValueError(f"{d['type']} texture: only constant colours are built")
+        return {"rgb": np.zeros((1, 1, 3), f32), "wrap": 0, "to_uv": _to_uv(d), "kind": kind, "color0": _rgb(d.get("color0"), [c0] * 3),
+                "color1": _rgb(d.get("color1"), [c1] * 3), "linewidth": f32(d.get("linewidth", lw)), "spokes": int(d.get("spokes", spokes))}
     if d.get("type") != "bitmap":
         raise ValueError(f"texture plugin '{d.get('type')}' is outside the hot path of this build")
     if d.get("filter_type", "bilinear") != "bilinear":
@@ -100,10 +123,7 @@ def load_texture(d: dict) -> dict:
         img = img[..., None].repeat(3, -1)
     if img.ndim != 3 or img.shape[2] < 3:
         raise ValueError("bitmap texture: expected an RGB image")
-    tu = d.get("to_uv")
-    m = np.eye(3, dtype=f32) if tu is None else np.asarray(getattr(tu, "matrix", tu), f32).reshape(3, 3)
-    return {"rgb": np.ascontiguousarray(img[..., :3], f32), "wrap": WRAP_MODES[d.get("wrap_mode", "repeat")],
-            "to_uv": np.ascontiguousarray(m[:2].reshape(-1), f32)}
+    return {"rgb": np.ascontiguousarray(img[..., :3], f32), "wrap": WRAP_MODES[d.get("wrap_mode", "repeat")], "to_uv": _to_uv(d), "kind": 0}
 
 
 def bsdf_row(d: dict, textures=None) -> np.ndarray:
@@ -117,7 +137,7 @@ def bsdf_row(d: dict, textures=None) -> np.ndarray:
         return r
     if t == "diffuse":
         refl = d.get("reflectance")
-        if isinstance(refl, dict) and refl.get("type") == "bitmap":
+        if isinstance(refl, dict) and refl.get("type") in TEXTURE_TYPES:
             if textures is None:
                 raise ValueError("a textured BSDF needs a scene to live in")
             hit = next((i for i, t in enumerate(textures) if t.get("_src") is refl), None)    # one dictionary shared by many BSDFs = one texture
@@ -305,7 +325,24 @@ class SceneData:
         self.bsdf_rows, self.bsdf_names, self.emitter_rows = [], [], []
         self.normals, self.uvs, self.shape_flags, self.textures = [], [], [], []
         self.rectangles = []      # (shape id, to_world 4x4) of `rectangle` shapes (the oracle can intersect them analytically)
+        self.spheres = []         # analytic `sphere` shapes: (shape id, centre, radius, flip_normals, to_world 4x4)
         self._nv = 0
+
+    def add_environment(self, radiance):
+        """`constant` emitter (src/emitters/constant.cpp): row kind 2; its bounding sphere is filled in by arrays()."""
+        if any(r[13] == 2 for r in self.emitter_rows):
+            raise ValueError("Only one environment emitter can be specified per scene.")
+        row = np.zeros(16, f32); row[0:3] = radiance; row[3] = -1; row[13] = 2
+        self.emitter_rows.append(row)
+
+    def add_sphere(self, name, to_world, bsdf_id, flip_normals=False):
+        """`sphere` shape (src/shapes/sphere.cpp:148-174): centre and radius extracted from to_world in float32."""
+        sid = self.add_shape(name, np.zeros((0, 3), f32), np.zeros((0, 3), np.int32), bsdf_id)
+        m = to_world.matrix
+        col = m[:3, 0]
+        radius = np.sqrt(f32(f32(col[0] * col[0]) + f32(col[1] * col[1])) + f32(col[2] * col[2]), dtype=f32)
+        self.spheres.append((sid, m[:3, 3].copy(), f32(radius), bool(flip_normals), m.copy()))
+        return sid
 
     def add_bsdf(self, name, row):
         self.bsdf_rows.append(np.asarray(row, f32)); self.bsdf_names.append(name)
@@ -329,9 +366,33 @@ class SceneData:
             self.shape_emitter.append(-1)
         return sid
 
+    def bounding_sphere(self):
+        """Scene bbox (scene.cpp:43) -> BoundingBox::bounding_sphere (bbox.h:113-115,330-333), padded as constant.cpp:77-82; float32."""
+        lo, hi = np.full(3, np.inf, f32), np.full(3, -np.inf, f32)
+        for v in self.vertices:
+            if len(v):
+                lo, hi = np.minimum(lo, v.min(0)), np.maximum(hi, v.max(0))
+        for _, c, r, _, _ in self.spheres:
+            lo, hi = np.minimum(lo, (c - r).astype(f32)), np.maximum(hi, (c + r).astype(f32))
+        if not np.all(lo <= hi):
+            return np.zeros(3, f32), f32(1)
+        c = ((hi + lo) * f32(.5)).astype(f32)
+        d = (c - hi).astype(f32)
+        r = np.sqrt(f32(f32(d[0] * d[0]) + f32(d[1] * d[1])) + f32(d[2] * d[2]), dtype=f32)
+        eps = f32(8.94069671630859375e-05)
+        return c, max(eps, f32(r * f32(f32(1) + eps)))
+
     def arrays(self):
         cat = lambda xs, dt, shape: (np.ascontiguousarray(np.concatenate(xs), dt) if xs else np.zeros(shape, dt))
-        return dict(vertices=cat(self.vertices, f32, (0, 3)), indices=cat(self.indices, np.int32, (0, 3)),
+        for row in self.emitter_rows:
+            if row[13] == 2:
+                row[4:7], row[7] = self.bounding_sphere()
+        sph = np.zeros((len(self.spheres), 32), f32)
+        for i, (sid, c, r, flip, m) in enumerate(self.spheres):
+            sph[i, 0:3], sph[i, 3], sph[i, 4], sph[i, 5] = c, r, sid, float(flip)
+            sph[i, 8:20] = m[:3].reshape(-1)
+            sph[i, 20:32] = np.linalg.inv(m.astype(np.float64))[:3].astype(f32).reshape(-1)
+        return dict(spheres=sph, vertices=cat(self.vertices, f32, (0, 3)), indices=cat(self.indices, np.int32, (0, 3)),
                     tri_shape=cat(self.tri_shape, np.int32, (0,)),
                     shape_bsdf=np.array(self.shape_bsdf, np.int32), shape_emitter=np.array(self.shape_emitter, np.int32),
                     bsdfs=np.ascontiguousarray(np.stack(self.bsdf_rows) if self.bsdf_rows else np.zeros((0, 16), f32), f32),
@@ -708,8 +769,35 @@ def _sensor_from(d):
     return s
 
 
-_SHAPES = ("rectangle", "cube", "mesh", "obj", "ply")
+_SHAPES = ("rectangle", "cube", "mesh", "obj", "ply", "sphere")
 _BSDFS = ("diffuse", "conductor", "dielectric", "dispersive", "twosided")
+
+
+def natural_key(name: str):
+    """Order of the reference's property map (src/core/properties.cpp:49-75 SortKey): names compare as strings except that
+    a trailing run of digits compares as a number ('_arg_2' < '_arg_10'; 'lamp' < 'lamp2'). Children of a scene — hence its
+    shapes and emitters, and the emitter a sample selects — come out in this order, for dictionaries and XML alike."""
+    import functools
+
+    def cmp(a, b):
+        i = 0
+        while i < len(a) and i < len(b) and a[i] == b[i]:
+            i += 1
+        while i > 0 and a[i - 1].isdigit():
+            i -= 1
+        ta, tb = a[i:], b[i:]
+        if ta[:1].isdigit() and tb[:1].isdigit() and ta.isdigit() and tb.isdigit() and not (int(ta) == int(tb) and len(a) != len(b)):
+            return -1 if int(ta) < int(tb) else (1 if int(ta) > int(tb) else 0)
+        return -1 if ta < tb else (1 if ta > tb else 0)
+    return functools.cmp_to_key(cmp)(name)
+
+
+def _child(v: dict, key: str, types):
+    """A shape's nested plugin: under its conventional key, or (as the reference does) whichever child has a matching type."""
+    c = v.get(key)
+    if isinstance(c, dict):
+        return c
+    return next((x for x in v.values() if isinstance(x, dict) and x.get("type") in types), None)
 
 
 def scene_data_from_dict(d: dict):
@@ -717,23 +805,50 @@ def scene_data_from_dict(d: dict):
     integrator sub-dictionaries. Also what the tests hand to the CPU oracle."""
     data = SceneData()
     named_bsdf, sensor_dicts, integ = {}, [], None
-    default_bsdf = None
+    default_bsdf = default_black = None
     for key, v in d.items():   # named BSDFs first: they are the targets of {'type': 'ref'}
         if isinstance(v, dict) and v.get("type") in _BSDFS:
-            named_bsdf[v.get("id", key)] = data.add_bsdf(key, bsdf_row(v, data.textures))
-    # child objects in the order of their keys: the reference keeps a scene's properties in a sorted map (shapes / emitters come
-    # out alphabetically, e.g. scene.emitters()), and the emitter index a sample selects depends on that order
-    for key, v in sorted(d.items(), key=lambda kv: kv[0]):
+            named_bsdf[v.get("id", key)] = data.add_bsdf(v.get("id", key), bsdf_row(v, data.textures))
+    # child objects in the order of the reference's property map (natural_key): scene.shapes() / scene.emitters() come out in
+    # this order, and the emitter index a sample selects depends on it
+    for key, v in sorted(d.items(), key=lambda kv: natural_key(kv[0])):
         if not isinstance(v, dict):
             continue
         vt = v.get("type")
+        name = v.get("id", key)
         if vt in ("perspective", "realisticlens"):
             sensor_dicts.append(v)
         elif vt in ("path", "prb"):
             integ = v
+        elif vt == "constant":
+            rad = v.get("radiance")
+            if isinstance(rad, dict) and rad.get("type") not in (None, "rgb", "spectrum", "uniform"):
+                raise ValueError("constant emitter: only a constant radiance is built")
+            data.add_environment(_rgb(rad, [1, 1, 1]))
         elif vt in _SHAPES:
             tw = v.get("to_world")
             tw = tw if isinstance(tw, Transform4f) else Transform4f(tw)
+            b = _child(v, "bsdf", _BSDFS + ("ref",))
+            em = _child(v, "emitter", ("area",))
+            if b is None and em is not None:       # shape.cpp:66-73: the default BSDF of an emitter is a BLACK diffuse one
+                if default_black is None:
+                    default_black = data.add_bsdf("__default_emitter", bsdf_row({"type": "diffuse", "reflectance": 0.0}))
+                bid = default_black
+            elif b is None:
+                if default_bsdf is None:
+                    default_bsdf = data.add_bsdf("__default", bsdf_row({"type": "diffuse"}))
+                bid = default_bsdf
+            elif b.get("type") == "ref":
+                bid = named_bsdf[b["id"]]
+            else:
+                bid = data.add_bsdf(f"{name}.bsdf", bsdf_row(b, data.textures))
+            if vt == "sphere":
+                if em is not None:
+                    raise ValueError("area emitters on `sphere` shapes are outside the hot path of this build (use a mesh)")
+                if "center" in v or "radius" in v:       # sphere.cpp:128-133: to_world * translate(center) * scale(radius)
+                    tw = tw @ Transform4f.translate(np.asarray(v.get("center", [0, 0, 0]), f32)) @ Transform4f.scale(float(v.get("radius", 1.0)))
+                data.add_sphere(name, tw, bid, v.get("flip_normals", False))
+                continue
             if v.get("flip_normals", False) and vt == "rectangle":
                 tw = tw @ Transform4f(np.diag(np.array([1, 1, -1, 1], f32)))     # rectangle.cpp:100-103
             if vt == "rectangle":
@@ -761,16 +876,6 @@ def scene_data_from_dict(d: dict):
                 faces = faces[:, ::-1]                              # mesh.cpp:1539-1542: si.n and sh_frame.n change sign
                 if normals is not None:
                     normals = -np.asarray(normals, f32)
-            b = v.get("bsdf")
-            if b is None:
-                if default_bsdf is None:
-                    default_bsdf = data.add_bsdf("__default", bsdf_row({"type": "diffuse"}))
-                bid = default_bsdf
-            elif b.get("type") == "ref":
-                bid = named_bsdf[b["id"]]
-            else:
-                bid = data.add_bsdf(f"{key}.bsdf", bsdf_row(b, data.textures))
-            em = v.get("emitter")
             emitter = None
             if em is not None:
                 if em.get("type") != "area":
@@ -781,7 +886,7 @@ def scene_data_from_dict(d: dict):
                 emitter = {"radiance": _rgb(rad, [1, 1, 1]), "center": tw.transform_affine(np.zeros(3, f32)),
                            "ex": tw.transform_vector(np.array([1, 0, 0], f32)), "ey": tw.transform_vector(np.array([0, 1, 0], f32)),
                            "kind": 0 if vt == "rectangle" else 1}      # 1: faces sampled by area (Mesh::sample_position)
-            sid = data.add_shape(key, verts, faces, bid, emitter, normals, uvs, rectangle=vt == "rectangle")
+            sid = data.add_shape(name, verts, faces, bid, emitter, normals, uvs, rectangle=vt == "rectangle")
             if vt == "rectangle":
                 data.rectangles.append((sid, tw.matrix.copy()))
         elif vt in _BSDFS or vt is None:

@@ -128,8 +128,11 @@ class RealisticLensCamera(Sensor):
                 capi.c_f(self.near_clip), capi.c_f(self.far_clip), C.byref(h))
         capi.check(rc)
         self.handle = h
-        if self.sample_exit_pupil:   # realisticlens.cpp:913-921: build the exit-pupil LUT (a GPU kernel here)
-            capi.check(capi.lib.lrt_sensor_set_exit_pupil(self.handle, C.c_int32(1), capi.c_f(self._shutter_open_time), None))
+        # realisticlens.cpp:913-921: build the exit-pupil LUT (a GPU kernel here). An open shutter is registered either way:
+        # render_sample draws a time sample whenever shutter_open_time() > 0 (integrator.cpp:442-444)
+        if self.sample_exit_pupil or self._shutter_open_time != 0.0:
+            capi.check(capi.lib.lrt_sensor_set_exit_pupil(self.handle, C.c_int32(int(bool(self.sample_exit_pupil))),
+                                                          capi.c_f(self._shutter_open_time), None))
 
     def needs_aperture_sample(self) -> bool:   # m_needs_sample_3 = true (:840)
         return True

@@ -32,6 +32,36 @@ void sincos(float x, float &s_out, float &c_out) {
     c_out = bits2f(f2bits(polymask ? c : s) ^ (sign_cos & 0x80000000u));
 }
 
+// ext/drjit/include/drjit/math.h:519-594 — atan2, single precision: minimax polynomial in (min/max)^2, Estrin's scheme
+// (math.h:26-41: pairs combined with fmadd, then the same on x^2, x^4)
+float atan2_drjit(float y, float x) {
+    float abs_x = std::fabs(x), abs_y = std::fabs(y), min_val = std::fmin(abs_y, abs_x), max_val = std::fmax(abs_x, abs_y);
+    float scaled_min = min_val / max_val, z = sqr(scaled_min);
+    const float c0 = 0.99999934166683966009f, c1 = -0.33326497518773606976f, c2 = 0.19881342388439013552f, c3 = -0.13486708938456973185f,
+                c4 = 0.083863120428809689910f, c5 = -0.037006525670417265220f, c6 = 0.0078613793713198150252f;
+    float a0 = fmadd(z, c1, c0), a1 = fmadd(z, c3, c2), a2 = fmadd(z, c5, c4), a3 = c6, z2 = sqr(z);
+    float b0 = fmadd(z2, a1, a0), b1 = fmadd(z2, a3, a2);
+    float t = fmadd(sqr(z2), b1, b0);
+    t = t * scaled_min;
+    if (abs_y > abs_x) t = Pi * .5f - t;
+    if (x < 0.f) t = Pi - t;
+    float r = y < 0.f ? -t : t;
+    return max_val != 0.f ? r : 0.f;
+}
+// math.h:366-412 — asin, single precision (CEPHES)
+float asin_drjit(float x) {
+    float xa = std::fabs(x), x2 = sqr(x);
+    bool big = xa > .5f;
+    float x1 = .5f * (1.f - xa), x3 = big ? x1 : x2, x4 = big ? std::sqrt(x1) : xa;
+    const float c0 = 1.6666752422e-1f, c1 = 7.4953002686e-2f, c2 = 4.5470025998e-2f, c3 = 2.4181311049e-2f, c4 = 4.2163199048e-2f;
+    float a0 = fmadd(x3, c1, c0), a1 = fmadd(x3, c3, c2), a2 = c4, y2 = sqr(x3);
+    float b0 = fmadd(y2, a1, a0), b1 = a2;
+    float z1 = fmadd(sqr(y2), b1, b0);
+    z1 = fmadd(z1, x3 * x4, x4);
+    float r = big ? (.5f * Pi) - (z1 + z1) : z1;
+    return std::copysign(r, x);
+}
+
 // include/mitsuba/core/warp.h:54-90
 V2 square_to_uniform_disk_concentric(V2 u) {
     float x = fmsub(2.f, u.x, 1.f), y = fmsub(2.f, u.y, 1.f);

@@ -34,9 +34,12 @@ namespace orc {
 struct Tri { V3 p0, p1, p2; int shape; int flags; V3 n0, n1, n2; V2 uv0, uv1, uv2; };   // flags: 1 normals, 2 uvs
 struct Bsdf { int type; bool twosided; V3 refl, eta, k, trans; float eta_s; int tex; };  // 0 diffuse 1 conductor 2 dielectric
 struct EmTri { V3 p0, e0, e1; float pmf, cdf; bool has_n; V3 n0, n1, n2; };
-struct Emitter { V3 radiance; int shape; V3 c, ex, ey, n; float inv_area; int kind = 0; std::vector<EmTri> tris; float sum = 0; };   // kind 1: mesh
+// kind 0 rectangle, 1 mesh, 2 constant environment (c = bounding-sphere centre, inv_area slot unused, bs_radius)
+struct Emitter { V3 radiance; int shape; V3 c, ex, ey, n; float inv_area; int kind = 0; std::vector<EmTri> tris; float sum = 0; float bs_radius = 1; };
 struct Rect { int shape; float M[12], Minv[12]; V3 dp_du, dp_dv, n; };                  // rows of the affine 3x4 matrices
-struct Texture { int w, h, wrap; std::vector<float> data; float to_uv[6]; };            // wrap: 0 repeat 1 mirror 2 clamp
+// kind 0 bitmap (wrap: 0 repeat 1 mirror 2 clamp); procedural: 1 checkerboard, 2 checkerlines, 3 comb2d, 4 polarlines
+struct Texture { int w, h, wrap; std::vector<float> data; float to_uv[6]; int kind = 0; V3 color0 { 0, 0, 0 }, color1 { 0, 0, 0 }; float linewidth = 0, spokes = 0; };
+struct Sphere { int shape; V3 center; float radius; bool flip; float M[12], Minv[12]; };   // rows of to_world / to_object
 
 struct BNode { V3 lo, hi; int left, right, first, count; };
 
@@ -47,6 +50,9 @@ struct Scene {
     std::vector<Emitter> emitters;
     std::vector<Rect> rects;
     std::vector<Texture> textures;
+    std::vector<Sphere> spheres;
+    int env = -1;                      // index of the environment emitter in `emitters`
+    bool hide_emitters = false;
     std::vector<char> shape_is_rect;   // triangles of these shapes are left out of the BVH
     std::vector<BNode> nodes;
     std::vector<int> order;
@@ -132,7 +138,38 @@ static V3 xf_vector(const float *M, V3 v) {
     return r;
 }
 
-struct Hit { float t = Infinity, u = 0, v = 0; int prim = -1, rect = -1; };
+struct Hit { float t = Infinity, u = 0, v = 0; int prim = -1, rect = -1, sphere = -1; };
+
+// sphere.cpp:493-562 (ray_intersect_preliminary_impl, scalar variants: double precision) with math::solve_quadratic
+// (include/mitsuba/core/math.h:358-402)
+static bool sphere_intersect(const Sphere &sp, const Ray &ray, float &t_out) {
+    double radius = sp.radius, cx = sp.center.x, cy = sp.center.y, cz = sp.center.z;
+    double maxt = ray.maxt;
+    double lx = (double) ray.o.x - cx, ly = (double) ray.o.y - cy, lz = (double) ray.o.z - cz;
+    double dx = ray.d.x, dy = ray.d.y, dz = ray.d.z;
+    double plane_t = (-lx * dx + -ly * dy + -lz * dz) / std::sqrt(dx * dx + dy * dy + dz * dz);
+    bool no_hit = plane_t == 0 && ray.o.x != sp.center.x && ray.o.y != sp.center.y && ray.o.z != sp.center.z;
+    float pt = (float) plane_t;                                  // ray(FloatP(plane_t)): evaluated in single precision
+    V3 plane_p = fmadd3(ray.d, pt, ray.o);
+    double ox = (double) plane_p.x - cx, oy = (double) plane_p.y - cy, oz = (double) plane_p.z - cz;
+    no_hit = no_hit && (std::sqrt(ox * ox + oy * oy + oz * oz) > radius);
+    double A = dx * dx + dy * dy + dz * dz, B = 2.0 * (ox * dx + oy * dy + oz * dz), C = (ox * ox + oy * oy + oz * oz) - radius * radius;
+    bool linear_case = A == 0.0, valid_linear = linear_case && B != 0.0;
+    double x0 = -C / B, x1 = x0;
+    double discrim = B * B - 4.0 * A * C;                       // dr::fmsub, two roundings in the pinned build
+    bool valid_quadratic = !linear_case && discrim >= 0.0;
+    if (valid_quadratic) {
+        double sq = std::sqrt(discrim), temp = -0.5 * (B + std::copysign(sq, B));
+        double x0p = temp / A, x1p = C / temp;
+        x0 = std::fmin(x0p, x1p); x1 = std::fmax(x0p, x1p);
+    }
+    bool found = valid_linear || valid_quadratic;
+    double near_t = x0 + plane_t, far_t = x1 + plane_t;
+    bool out_bounds = !(near_t <= maxt && far_t >= 0.0), in_bounds = near_t < 0.0 && far_t > maxt;
+    if (!(found && !no_hit && !out_bounds && !in_bounds)) return false;
+    t_out = near_t < 0.0 ? (float) far_t : (float) near_t;
+    return true;
+}
 
 // rectangle.cpp:449-470 (ray_intersect_preliminary_impl) / :472-492 (ray_test_impl)
 static bool rect_intersect(const Rect &rc, const Ray &ray, float &t, float &lx, float &ly) {
@@ -168,6 +205,14 @@ static Hit intersect(const Scene &s, const Ray &ray, bool any_hit) {
         float t, lx, ly;
         if (rect_intersect(s.rects[k], r, t, lx, ly) && t < best.t) {
             best.t = t; best.u = lx; best.v = ly; best.prim = -1; best.rect = (int) k;
+            if (any_hit) return best;
+            r.maxt = t;
+        }
+    }
+    for (size_t k = 0; k < s.spheres.size(); ++k) {
+        float t;
+        if (sphere_intersect(s.spheres[k], r, t) && t < best.t) {
+            best.t = t; best.u = best.v = 0.f; best.prim = -1; best.rect = -1; best.sphere = (int) k;
             if (any_hit) return best;
             r.maxt = t;
         }
@@ -216,6 +261,27 @@ static SI surface_interaction(const Scene &s, const Ray &ray, const Hit &h) {
         si.uv = { fmadd(h.u, .5f, .5f), fmadd(h.v, .5f, .5f) };
         si.shape = rc.shape;
         finalize_si(si, rc.dp_du, ray);
+        return si;
+    }
+    if (h.sphere >= 0) {        // sphere.cpp:609-718 (non-differentiable branch)
+        const Sphere &sp = s.spheres[h.sphere];
+        si.t = h.t;
+        si.sh_n = normalize(fmadd3(ray.d, h.t, ray.o) - sp.center);
+        si.p = fmadd3(si.sh_n, sp.radius, sp.center);
+        V3 local = xf_point(sp.Minv, si.p);
+        float rd_2 = sqr(local.x) + sqr(local.y);
+        // unit_angle_z (include/mitsuba/core/vector.h): 2 asin(|v - sign(z) e_z| / 2), mirrored for z < 0
+        V3 q { local.x, local.y, local.z - std::copysign(1.f, local.z) };
+        float temp = 2.f * asin_drjit(.5f * norm(q)), theta = local.z >= 0.f ? temp : Pi - temp;
+        float phi = atan2_drjit(local.y, local.x);
+        if (phi < 0.f) phi += 2.f * Pi;
+        si.uv = { phi * (.5f * InvPi), theta * InvPi };
+        V3 dp_du = xf_vector(sp.M, V3 { -local.y, local.x, 0.f }) * (2.f * Pi);
+        (void) rd_2;
+        if (sp.flip) si.sh_n = -si.sh_n;
+        si.n = si.sh_n;
+        si.shape = sp.shape;
+        finalize_si(si, dp_du, ray);
         return si;
     }
     if (h.prim < 0) return si;
@@ -286,7 +352,30 @@ static int tex_wrap(int pos, int shape, int mode) {   // texture.h:1143-1172
     if (mode == 1 && !(((div & 1) == 0) ^ (pos < 0))) mod = shape - 1 - mod;
     return mod;
 }
+// checkerboard.cpp:70-89, checkerlines.cpp / comb2d.cpp / polarlines.cpp eval (the fork's line patterns); colours are constants
+static V3 procedural_eval(const Texture &t, V2 uv_in) {
+    auto xf = [&](V2 p) { return V2 { fmadd(t.to_uv[1], p.y, fmadd(t.to_uv[0], p.x, t.to_uv[2])), fmadd(t.to_uv[4], p.y, fmadd(t.to_uv[3], p.x, t.to_uv[5])) }; };
+    bool m0;
+    if (t.kind == 1) {
+        V2 uv = xf(uv_in);
+        bool mx = uv.x - std::floor(uv.x) > .5f, my = uv.y - std::floor(uv.y) > .5f;
+        m0 = mx == my;
+    } else if (t.kind == 2 || t.kind == 3) {
+        V2 uv = xf(uv_in); uv.x *= 2.f; uv.y *= 2.f;
+        uv.x -= std::floor(uv.x); uv.y -= std::floor(uv.y);
+        bool mx = std::fabs(2.f * uv.x - 1.f) > 1.f - t.linewidth, my = std::fabs(2.f * uv.y - 1.f) > 1.f - t.linewidth;
+        m0 = t.kind == 2 ? (mx || my) : !(mx && my);
+    } else {
+        V2 uv = xf(V2 { 2.f * uv_in.x - 1.f, 2.f * uv_in.y - 1.f });
+        float theta = atan2_drjit(uv.x, uv.y), radius = std::sqrt(uv.x * uv.x + uv.y * uv.y);
+        theta = theta / (2.f * Pi) * t.spokes;
+        m0 = (std::fabs(2.f * (radius - std::floor(radius)) - 1.f) > 1.f - t.linewidth) ||
+             (std::fabs(2.f * (theta - std::floor(theta)) - 1.f) > 1.f - t.linewidth * t.spokes / (2.f * Pi * radius));
+    }
+    return m0 ? t.color0 : t.color1;
+}
 static V3 texture_eval(const Texture &t, V2 uv_in) {
+    if (t.kind != 0) return procedural_eval(t, uv_in);
     V2 uv { fmadd(t.to_uv[1], uv_in.y, fmadd(t.to_uv[0], uv_in.x, t.to_uv[2])), fmadd(t.to_uv[4], uv_in.y, fmadd(t.to_uv[3], uv_in.x, t.to_uv[5])) };
     float px = fmadd(uv.x, (float) t.w, -.5f), py = fmadd(uv.y, (float) t.h, -.5f);
     int ix = (int) std::floor(px), iy = (int) std::floor(py);
@@ -368,6 +457,16 @@ static void mesh_sample_position(const Emitter &e, V2 sample, V3 &p, V3 &n) {
 }
 
 static bool emitter_sample_direction(const Emitter &e, V3 ref_p, V2 sample, DS &ds, V3 &spec) {
+    if (e.kind == 2) {          // constant.cpp:113-142: uniform direction, the point 2 max(R, |p - c|) away
+        float z = fnmadd(2.f, sample.y, 1.f), r = std::sqrt(std::fmax(fnmadd(z, z, 1.f), 0.f)), sn, cs;   // warp.h:250-255 (circ)
+        sincos(2.f * Pi * sample.x, sn, cs);
+        V3 d { r * cs, r * sn, z };
+        float radius = std::fmax(e.bs_radius, norm(ref_p - e.c)), dist = 2.f * radius;
+        ds.p = fmadd3(d, dist, ref_p); ds.n = -d; ds.d = d; ds.dist = dist;
+        ds.pdf = .25f * InvPi;
+        spec = e.radiance / ds.pdf;
+        return true;
+    }
     if (e.kind == 1) mesh_sample_position(e, sample, ds.p, ds.n);
     else {
         float sx = sample.x * 2.f - 1.f, sy = sample.y * 2.f - 1.f;
@@ -407,13 +506,15 @@ static void sample_emitter_direction(const Scene &s, const SI &si, V2 sample, bo
     active = active && ds.pdf != 0.f;
     if (active && test_visibility) {
         Hit h = intersect(s, spawn_ray_to(si.p, si.n, ds.p), true);
-        if (h.prim >= 0 || h.rect >= 0) { spec = { 0, 0, 0 }; ds.pdf = 0.f; }
+        if (h.prim >= 0 || h.rect >= 0 || h.sphere >= 0) { spec = { 0, 0, 0 }; ds.pdf = 0.f; }
     }
 }
 
 // scene.cpp:355-366 + area.cpp:168-196 + shape.cpp:377-388
 static float pdf_emitter_direction(const Scene &s, const DS &ds) {
     const Emitter &e = s.emitters[ds.emitter];
+    float pmf0 = s.emitters.size() > 1 ? 1.f / (float) s.emitters.size() : 1.f;
+    if (e.kind == 2) return (.25f * InvPi) * pmf0;      // constant.cpp:144-149
     float dp = dot(ds.d, ds.n);
     if (!(dp < 0.f)) return 0.f;
     float adp = std::fabs(dp);
@@ -430,6 +531,7 @@ static float pdf_emitter_direction(const Scene &s, const DS &ds) {
 // survival probabilities and the termination test follow the throughput of this frozen copy of the scene, so that finite
 // differences of a perturbed scene's render see the same paths with the same roulette weights.
 static const Scene *g_rr_scene = nullptr;
+static bool g_trace = false;     // orc_set_trace: print every vertex of path_sample (debugging aid for pinning)
 
 static V3 path_sample(const Scene &s, PCG32 &rng, Ray ray, int max_depth, int rr_depth, bool scalar, bool &valid_ray) {
     V3 throughput { 1, 1, 1 }, result { 0, 0, 0 }, throughput_rr { 1, 1, 1 };
@@ -437,17 +539,21 @@ static V3 path_sample(const Scene &s, PCG32 &rng, Ray ray, int max_depth, int rr
     valid_ray = false;
     V3 prev_p { 0, 0, 0 }; float prev_bsdf_pdf = 1.f; bool prev_bsdf_delta = true;
     if (max_depth == 0) return result;
+    valid_ray = !s.hide_emitters && s.env >= 0;        // path.cpp:113-114
     bool active = true;
     while (active) {
         Hit h = intersect(s, ray, false);
         SI si = surface_interaction(s, ray, h);
-        int em = si.valid() ? s.shape_emitter[si.shape] : -1;
+        int em = si.valid() ? s.shape_emitter[si.shape] : s.env;     // si.emitter(scene): the environment for a ray that escaped
+        if (g_trace) std::printf("depth %d hit %d t %.9g p %.9g %.9g %.9g shape %d n %.6g %.6g %.6g wi %.6g %.6g %.6g thr %.6g %.6g %.6g res %.6g %.6g %.6g\n", depth, (int) si.valid(), si.t,
+                                 si.p.x, si.p.y, si.p.z, si.shape, si.n.x, si.n.y, si.n.z, si.wi.x, si.wi.y, si.wi.z, throughput.x, throughput.y, throughput.z, result.x, result.y, result.z);
         if (em >= 0) {     // direct emission + MIS (:158-174)
             DS ds; ds.p = si.p; ds.n = si.sh_n; ds.emitter = em;
             V3 rel = si.p - prev_p; ds.dist = norm(rel); ds.d = rel / ds.dist;
+            if (!si.valid()) ds.d = ray.d;                          // records.h: d = -si.wi for an invalid interaction
             float em_pdf = !prev_bsdf_delta ? pdf_emitter_direction(s, ds) : 0.f;
             float mis_bsdf = mis_weight(prev_bsdf_pdf, em_pdf);
-            V3 le = (si.wi.z > 0.f && prev_bsdf_pdf > 0.f) ? s.emitters[em].radiance : V3 { 0, 0, 0 };
+            V3 le = ((si.wi.z > 0.f || !si.valid()) && prev_bsdf_pdf > 0.f) ? s.emitters[em].radiance : V3 { 0, 0, 0 };
             le = le * mis_bsdf;
             result = fmadd3(throughput, le, result);
         }
@@ -471,6 +577,8 @@ static V3 path_sample(const Scene &s, PCG32 &rng, Ray ray, int max_depth, int rr
             wo = si.to_local(ds.d);
         }
         BsdfOut b = eval_pdf_sample(s, *bsdf, si.uv, si.wi, wo, sample_1, sample_2);
+        if (g_trace) std::printf("   em_active %d ds.pdf %.9g emitter %d em_w %.6g %.6g %.6g | bsdf val %.6g %.6g %.6g pdf %.6g wo %.6g %.6g %.6g spdf %.6g w %.6g %.6g %.6g\n", (int) active_em, ds.pdf,
+                                 ds.emitter, em_weight.x, em_weight.y, em_weight.z, b.val.x, b.val.y, b.val.z, b.pdf, b.wo.x, b.wo.y, b.wo.z, b.spdf, b.weight.x, b.weight.y, b.weight.z);
         if (active_em) {
             float mis_em = mis_weight(ds.pdf, b.pdf);
             V3 c = b.val * em_weight * mis_em;
@@ -490,7 +598,6 @@ static V3 path_sample(const Scene &s, PCG32 &rng, Ray ray, int max_depth, int rr
         if (rr_active) { throughput = throughput * rcp(rr_prob); if (g_rr_scene) throughput_rr = throughput_rr * rcp(rr_prob); }
         active = active_next && (!rr_active || rr_continue) && tmax != 0.f;
     }
-    // (a camera ray that escapes or a path cut short leaves valid_ray as is: no environment emitter)
     return valid_ray ? result : V3 { 0, 0, 0 };
 }
 
@@ -588,6 +695,7 @@ void *orc_scene_create2(int nv, const float *verts, const float *normals, const 
         // rectangle.cpp:115-123: frame from dp_du = 2 ex, dp_dv = 2 ey; area = |dp_du x dp_dv|
         V3 cr = cross(e.ex * 2.f, e.ey * 2.f);
         e.n = normalize(cross(e.ex, e.ey)); e.inv_area = rcp(norm(cr));
+        if (r[13] == 2.f) { e.kind = 2; e.shape = -1; e.bs_radius = r[7]; s->env = i; }     // constant environment: c = bounding-sphere centre
         if (r[13] == 1.f) {     // mesh emitter: Mesh::build_pmf (mesh.cpp:430-470), cdf accumulated in double (distr_1d.h:233-262)
             e.kind = 1; double sum = 0.0;
             for (int t = 0; t < nt; ++t) {
@@ -635,6 +743,28 @@ void orc_scene_set_rectangles(void *h, int n, const int *shape_ids, const float 
     }
     s->build();
 }
+// Analytic spheres (sphere.cpp): per sphere 8 floats (centre xyz, radius, flip_normals, -, -, -) and the rows of to_world / to_object
+void orc_scene_set_spheres(void *h, int n, const int *shape_ids, const float *sph8, const float *to_world12, const float *to_object12) {
+    Scene *s = (Scene *) h;
+    s->spheres.clear();
+    for (int i = 0; i < n; ++i) {
+        Sphere sp; sp.shape = shape_ids[i]; const float *q = sph8 + 8 * i;
+        sp.center = { q[0], q[1], q[2] }; sp.radius = q[3]; sp.flip = q[4] != 0.f;
+        std::memcpy(sp.M, to_world12 + 12 * i, 48); std::memcpy(sp.Minv, to_object12 + 12 * i, 48);
+        s->spheres.push_back(sp);
+    }
+}
+// Procedural textures: kinds[i] != 0 turns texture i into checkerboard (1) / checkerlines (2) / comb2d (3) / polarlines (4);
+// params8 = color0 rgb, color1 rgb, linewidth, spokes
+void orc_scene_set_procedural(void *h, int n, const int *kinds, const float *params8) {
+    Scene *s = (Scene *) h;
+    for (int i = 0; i < n && i < (int) s->textures.size(); ++i) {
+        Texture &t = s->textures[i]; const float *q = params8 + 8 * i;
+        t.kind = kinds[i]; t.color0 = { q[0], q[1], q[2] }; t.color1 = { q[3], q[4], q[5] }; t.linewidth = q[6]; t.spokes = q[7];
+    }
+}
+void orc_set_trace(int on) { g_trace = on != 0; }
+void orc_scene_set_hide_emitters(void *h, int hide) { ((Scene *) h)->hide_emitters = hide != 0; }
 void orc_scene_destroy(void *h) { delete (Scene *) h; }
 // Russian roulette follows this (unperturbed) scene in every later render; NULL restores the attached behaviour
 void orc_set_rr_scene(void *h) { g_rr_scene = (const Scene *) h; }
@@ -681,6 +811,21 @@ void orc_scene_sample_emitter(void *h, int64_t n, const float *ref_p3, const flo
         o[0] = ds.p.x; o[1] = ds.p.y; o[2] = ds.p.z; o[3] = ds.n.x; o[4] = ds.n.y; o[5] = ds.n.z; o[6] = ds.d.x; o[7] = ds.d.y; o[8] = ds.d.z;
         o[9] = ds.dist; o[10] = ds.pdf; o[11] = w.x; o[12] = w.y; o[13] = w.z;
         o[14] = ds.pdf > 0.f ? pdf_emitter_direction(s, ds) : 0.f; o[15] = ds.pdf > 0.f ? (float) ds.emitter : -1.f;
+    }
+}
+
+// PathIntegrator::sample (scalar control flow) for n given rays: ray i uses a PCG32 stream seeded like a scalar sampler after
+// sampler->seed(seeds[i]) (sampler.cpp:131). out5 = radiance rgb, valid flag, number of random numbers consumed
+void orc_path_sample(void *h, int64_t n, const float *od7, const uint32_t *seeds, int max_depth, int rr_depth, float *out5) {
+    const Scene &s = *(Scene *) h;
+    for (int64_t i = 0; i < n; ++i) {
+        const float *r = od7 + 7 * i; Ray ray; ray.o = { r[0], r[1], r[2] }; ray.d = { r[3], r[4], r[5] }; ray.maxt = r[6];
+        PCG32 rng; rng.seed((uint64_t) seeds[i], 0xda3e39cb94b95bdbULL);
+        PCG32 probe = rng;
+        bool valid; V3 L = path_sample(s, rng, ray, max_depth, rr_depth, true, valid);
+        int used = 0;
+        while (!(probe.state == rng.state) && used < 4096) { (void) probe.next_float32(); ++used; }
+        float *o = out5 + 5 * i; o[0] = L.x; o[1] = L.y; o[2] = L.z; o[3] = valid ? 1.f : 0.f; o[4] = (float) used;
     }
 }
 

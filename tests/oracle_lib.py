@@ -170,9 +170,10 @@ def bits(a):
 
 
 # ------------------------------------------------------------------------------------------------ scenes / render
-def orc_scene(a, analytic_rectangles=False):
+def orc_scene(a, analytic_rectangles=False, hide_emitters=False):
     """a: dict of flat arrays (mitsuba3-camera_b200/scene.py SceneData.arrays()) -> oracle scene handle.
-    analytic_rectangles: intersect `rectangle` shapes as the reference does (rectangle.cpp) instead of as two triangles."""
+    analytic_rectangles: intersect `rectangle` shapes as the reference does (rectangle.cpp) instead of as two triangles.
+    Analytic spheres, procedural textures and the environment emitter of `a` are registered too."""
     L = oracle()
     L.orc_scene_create2.restype = C.c_void_p
     keep = {k: np.ascontiguousarray(v) for k, v in a.items() if isinstance(v, np.ndarray)}
@@ -193,6 +194,20 @@ def orc_scene(a, analytic_rectangles=False):
         inv = np.stack([np.linalg.inv(m.astype(np.float64)) for m in tw]).astype(f32)
         L.orc_scene_set_rectangles(h, C.c_int(len(tw)), ip(keep["rect_shapes"]), fp(np.ascontiguousarray(tw[:, :3, :].reshape(-1))),
                                    fp(np.ascontiguousarray(inv[:, :3, :].reshape(-1))))
+    sph = keep.get("spheres")
+    if sph is not None and len(sph):
+        L.orc_scene_set_spheres(h, C.c_int(len(sph)), ip(np.ascontiguousarray(sph[:, 4].astype(np.int32))),
+                                fp(np.ascontiguousarray(np.concatenate([sph[:, 0:4], sph[:, 5:6], np.zeros((len(sph), 3), f32)], 1), f32)),
+                                fp(np.ascontiguousarray(sph[:, 8:20])), fp(np.ascontiguousarray(sph[:, 20:32])))
+    if any(t.get("kind", 0) for t in tex):
+        kinds = np.array([t.get("kind", 0) for t in tex], np.int32)
+        par = np.zeros((len(tex), 8), f32)
+        for i, t in enumerate(tex):
+            if t.get("kind", 0):
+                par[i, 0:3], par[i, 3:6], par[i, 6], par[i, 7] = t["color0"], t["color1"], t["linewidth"], t["spokes"]
+        L.orc_scene_set_procedural(h, C.c_int(len(tex)), ip(kinds), fp(par))
+    if hide_emitters:
+        L.orc_scene_set_hide_emitters(h, C.c_int(1))
     return h
 
 

@@ -1,0 +1,206 @@
+"""XML scene loader (mitsuba3-camera_b200/xml.py) and what the fork's XML scenes add to the path — analytic spheres, the constant
+environment emitter, procedural textures — checked on the CPU: the loader's dictionaries against what the reference's own
+`mi.load_file` built from the same files, and the pinned oracle against the reference's function outputs and images
+(tests/golden/ref_xml.npz, written by tests/golden/gen_ref_xml.py with the reference's scalar_rgb build)."""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+
+from oracle_lib import bits, f32, fp, oracle, orc_scene
+from test_ref_parity import oracle_scalar_render, rel_rmse
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+XML = os.path.join(HERE, "golden", "assets", "xml")
+SCENES = ("room", "charts", "studio")
+
+
+@pytest.fixture(scope="module")
+def G():
+    return np.load(os.path.join(HERE, "golden", "ref_xml.npz"))
+
+
+def load(mi, name, **kw):
+    d = mi.xml_to_dict(path=os.path.join(XML, name + ".xml"), **kw)
+    data, sensors, integ = mi.scene.scene_data_from_dict(d)
+    return d, data, sensors, integ
+
+
+# ------------------------------------------------------------------------------------------------ loader
+@pytest.mark.parametrize("name", SCENES)
+def test_loader_builds_what_the_reference_builds(mi, G, name):
+    d, data, sensors, integ = load(mi, name)
+    assert data.shape_names == [str(x) for x in G[name + "/shape_ids"]]              # children in document order (_arg_2 < _arg_10)
+    a = data.arrays()
+    ours = ["__env" if e[13] == 2 else data.shape_names[int(e[3])] for e in a["emitters"]]
+    assert ours == [str(x) for x in G[name + "/emitter_ids"]]                        # scene.emitters(): the order a sample indexes
+    by_id = {v["id"]: v for v in d.values() if isinstance(v, dict) and "id" in v}
+    n_checked = 0
+    for k in G.files:
+        if k.startswith(name + "/param/"):
+            sid = k.split("/param/")[1].rsplit(".", 1)[0]
+            if sid in by_id and "to_world" in by_id[sid] and by_id[sid]["type"] != "sphere":
+                assert np.abs(by_id[sid]["to_world"].matrix - G[k]).max() <= 1e-6
+                n_checked += 1
+    assert n_checked >= 1
+    sd = sensors[0]     # (a realisticlens sensor object needs the device; the dictionary is what the loader produced)
+    assert [sd["film"]["width"], sd["film"]["height"]] == G[name + "/film_size"].tolist()
+    assert sd["sampler"]["sample_count"] == int(G[name + "/spp"])
+
+
+def test_defaults_and_parameters(mi):
+    d = mi.xml_to_dict(path=os.path.join(XML, "charts.xml"))
+    assert d["_arg_1"]["lens_design"] == "doublet" and d["_arg_0"]["hide_emitters"] is False and d["_arg_0"]["max_depth"] == 4
+    d = mi.xml_to_dict(path=os.path.join(XML, "charts.xml"), lens="gauss", hide="true", resx=64)
+    assert d["_arg_1"]["lens_design"] == "gauss" and d["_arg_0"]["hide_emitters"] is True and d["_arg_1"]["film"]["width"] == 64
+    assert d["_arg_1"]["film"]["rfilter"] == {"type": "tent"} and d["_arg_1"]["sampler"]["sample_count"] == 8
+    with pytest.raises(mi.XMLError, match="unused"):
+        mi.xml_to_dict(path=os.path.join(XML, "charts.xml"), no_such_parameter=1)
+    with pytest.raises(mi.XMLError, match="undefined parameter"):
+        mi.xml_to_dict(text='<scene version="3.0.0"><integrator type="$nope"/></scene>')
+    with pytest.raises(mi.XMLError, match="version"):
+        mi.xml_to_dict(text='<scene><integrator type="path"/></scene>')
+    with pytest.raises(mi.XMLError, match="does not exist"):
+        mi.load_file("/nonexistent/scene.xml")
+    with pytest.raises(mi.XMLError, match="leading underscores"):
+        mi.xml_to_dict(text='<scene version="3.0.0"><float name="_x" value="1"/></scene>')
+    with pytest.raises(ValueError, match="outside the hot path"):
+        mi.scene.scene_data_from_dict(mi.xml_to_dict(text='<scene version="3.0.0"><shape type="cylinder"/></scene>'))
+
+
+def test_transform_operations_compose_from_the_left(mi):
+    d = mi.xml_to_dict(text='''<scene version="3.0.0"><shape type="rectangle" id="r"><transform name="to_world">
+        <scale value="2, 3, 1"/><rotate z="1" angle="90"/><translate x="1" y="-1" z="0.5"/><matrix value="1 0 0 0  0 1 0 0  0 0 1 2  0 0 0 1"/>
+        </transform></shape></scene>''')
+    m = d["_arg_0"]["to_world"]
+    p = m.transform_affine(np.array([1, 0, 0], f32))        # scale -> (2,0,0); rotate z 90 -> (0,2,0); translate -> (1,1,.5); +2 in z
+    assert np.allclose(p, [1, 1, 2.5], atol=1e-6)
+
+
+def test_include_and_named_children(mi, tmp_path):
+    inc = tmp_path / "materials.xml"
+    inc.write_text('<scene version="3.0.0"><bsdf type="diffuse" id="m"><rgb name="reflectance" value="0.25"/></bsdf></scene>')
+    main = tmp_path / "main.xml"
+    main.write_text('''<scene version="3.0.0"><include filename="materials.xml"/>
+        <shape type="rectangle" id="a"><ref id="m"/></shape>
+        <shape type="rectangle" id="b"><bsdf type="twosided"><bsdf type="diffuse"/></bsdf></shape></scene>''')
+    data, _, _ = mi.scene.scene_data_from_dict(mi.xml_to_dict(path=str(main)))
+    a = data.arrays()
+    assert data.shape_names == ["a", "b"] and np.allclose(a["bsdfs"][a["shape_bsdf"][0], 2:5], 0.25)
+    assert a["bsdfs"][a["shape_bsdf"][1], 1] == 1 and np.allclose(a["bsdfs"][a["shape_bsdf"][1], 2:5], 0.5)
+
+
+def test_natural_key_is_the_property_map_order(mi):
+    names = ["_arg_10", "_arg_2", "_arg_1", "lamp2", "lamp", "ball-light", "ball10", "ball9", "b", "a01", "a1"]
+    got = sorted(names, key=mi.scene.natural_key)
+    assert got.index("_arg_1") < got.index("_arg_2") < got.index("_arg_10")
+    assert got.index("lamp") < got.index("lamp2") and got.index("ball9") < got.index("ball10")
+    assert got.index("ball-light") < got.index("ball9")
+
+
+FORK_SCENES = "/root/reference/notebooks/scenes/cboxes"
+
+
+@pytest.mark.skipif(not os.path.isdir(FORK_SCENES), reason="the reference checkout is not on this machine")
+@pytest.mark.parametrize("name,kw", [("cbox_path", {}), ("cbox_real", {"integrator": "path"}), ("cbox_ref", {"integrator": "path"}), ("focus_near", {}),
+                                     ("grid", {}), ("grid_SA_coma", {}), ("grid_astig", {}), ("grid_chromatic", {}), ("grid_distortion", {}),
+                                     ("grid_exp-doublet", {})])
+def test_the_forks_own_scenes_load(mi, name, kw):
+    """notebooks/scenes/cboxes/*.xml, unmodified and read in place: every plugin they use is on the path."""
+    d = mi.xml_to_dict(path=os.path.join(FORK_SCENES, name + ".xml"), **kw)
+    data, sensors, integ = mi.scene.scene_data_from_dict(d)
+    a = data.arrays()
+    assert len(sensors) == 1 and integ["type"] == "path" and len(a["emitters"]) >= 1
+    assert len(a["indices"]) + len(a["spheres"]) > 0
+    assert sensors[0]["film"]["rfilter"]["type"] == "tent" and sensors[0]["sampler"]["sample_count"] >= 1
+
+
+# ------------------------------------------------------------------------------------------------ functions
+def test_sphere_and_procedural_textures_vs_reference(mi, G):
+    """sphere.cpp (double-precision quadratic, re-projected hit point, spherical parameterisation) and the four procedural
+    textures: hit distance, point, normals, shading frame, uv and reflectance bit-exact."""
+    _, data, _, _ = load(mi, "charts")
+    a = data.arrays()
+    assert [t["kind"] for t in a["textures"]] == [1, 2, 3, 4, 1] and len(a["spheres"]) == 1
+    h = orc_scene(a, analytic_rectangles=True)
+    for nm in ("isect", "inside"):
+        o, d = G[f"charts/{nm}_o"], G[f"charts/{nm}_d"]; n = len(o)
+        od = np.ascontiguousarray(np.concatenate([o, d, np.full((n, 1), 3.4e38, f32)], 1), f32)
+        out = np.zeros((n, 25), f32)
+        oracle().orc_scene_interaction(h, C.c_int64(n), fp(od), fp(out))
+        ref = G[f"charts/{nm}"]
+        hit = np.isfinite(ref[:, 0])
+        assert (hit == np.isfinite(out[:, 0])).all() and (ref[hit, 21] == out[hit, 21]).all()
+        assert (bits(out[hit, 0:16]) == bits(ref[hit, 0:16])).all()                  # t, p, n, shading frame
+        assert (bits(out[hit, 18:21]) == bits(ref[hit, 18:21])).all()                # wi
+        assert (bits(out[hit, 16:18]) == bits(ref[hit, 16:18])).all()                # uv (Dr.Jit's atan2 / asin polynomials restated)
+        assert (out[hit, 22:25] == ref[hit, 22:25]).all()                            # texture value at the hit
+        sph = hit & (ref[:, 21] == data.shape_names.index("probe"))
+        assert sph.sum() > 400
+        for k in range(4 if nm == "isect" else 0):
+            assert (hit & (ref[:, 21] == k)).sum() > 300
+    # Scene::ray_test with a finite maxt
+    o, d, maxt = G["charts/isect_o"], G["charts/isect_d"], G["charts/test_maxt"]
+    od = np.ascontiguousarray(np.concatenate([o, d, maxt[:, None]], 1), f32)
+    out = np.zeros((len(o), 4), f32)
+    oracle().orc_scene_intersect(h, C.c_int(1), C.c_int64(len(o)), fp(od), fp(out))
+    assert (np.isfinite(out[:, 0]).astype(np.int32) == G["charts/test_occluded"]).all()
+
+
+def test_environment_emitter_sampling_vs_reference(mi, G):
+    """Scene::sample_emitter_direction over {mesh area light, constant environment}: constant.cpp:113-149."""
+    _, data, _, _ = load(mi, "studio")
+    a = data.arrays()
+    h = orc_scene(a, analytic_rectangles=True)
+    p, s2 = np.ascontiguousarray(G["studio/em_ref_p"]), np.ascontiguousarray(G["studio/em_sample"])
+    out = np.zeros((len(p), 16), f32)
+    oracle().orc_scene_sample_emitter(h, C.c_int64(len(p)), fp(p), fp(s2), fp(out))
+    er = G["studio/em_dir"]
+    assert (out[:, 15] == er[:, 15]).all()
+    env = er[:, 15] == 1
+    assert env.sum() > 800 and (er[:, 15] == 0).sum() > 300
+    assert (bits(out[env, :15]) == bits(er[env, :15])).all()              # point, normal, direction, distance, pdf, weight, pdf()
+    mesh = er[:, 15] == 0
+    assert (bits(out[mesh, :3]) == bits(er[mesh, :3])).all()
+    assert np.allclose(out[mesh, 3:15], er[mesh, 3:15], rtol=3e-6, atol=1e-7)
+
+
+@pytest.mark.parametrize("name", SCENES)
+def test_path_sample_per_ray_vs_reference(mi, G, name):
+    """PathIntegrator::sample for 400 individual camera rays, each with its own scalar sampler seed: radiance and the valid flag."""
+    d, data, sensors, integ = load(mi, name)
+    a = data.arrays()
+    h = orc_scene(a, analytic_rectangles=True)
+    o, dd, ref = G[name + "/path_o"], G[name + "/path_d"], G[name + "/path_L"]
+    n = len(o)
+    od = np.ascontiguousarray(np.concatenate([o, dd, np.full((n, 1), 3.4e38, f32)], 1), f32)
+    seeds = np.arange(1000, 1000 + n, dtype=np.uint32)
+    out = np.zeros((n, 5), f32)
+    oracle().orc_path_sample(h, C.c_int64(n), fp(od), seeds.ctypes.data_as(C.POINTER(C.c_uint32)), C.c_int(integ.get("max_depth", -1)),
+                             C.c_int(integ.get("rr_depth", 5)), fp(out))
+    assert (out[:, 3] == ref[:, 3]).all()
+    assert np.abs(out[:, :3] - ref[:, :3]).max() <= 1e-6 * max(1.0, float(ref[:, :3].max()))
+    assert (ref[:, :3].max(1) > 0).mean() > 0.5
+
+
+# ------------------------------------------------------------------------------------------------ images
+def xml_cases():
+    return [("room", {}), ("charts", {}), ("charts", {"hide": "true", "spp": "4"}), ("charts", {"lens": "gauss", "spp": "4"}), ("studio", {})]
+
+
+def case_key(name, kw):
+    return name + "".join(f"@{k}={v}" for k, v in sorted(kw.items())) + "/image"
+
+
+@pytest.mark.parametrize("name,kw", xml_cases())
+def test_xml_render_vs_reference(mi, G, name, kw):
+    """mi.load_file + mi.render of the reference vs our loader + the pinned oracle in the scalar sampling convention."""
+    d = mi.xml_to_dict(path=os.path.join(XML, name + ".xml"), **kw)
+    spp = mi.scene.scene_data_from_dict(d)[1][0]["sampler"]["sample_count"]
+    img, _ = oracle_scalar_render(mi, d, spp, analytic=True)
+    ref = G[case_key(name, kw)]
+    assert img.shape == ref.shape
+    assert rel_rmse(img, ref) <= 2e-4
+    close = np.abs(img - ref).max(-1) <= 1e-4 * np.maximum(ref.max(-1), 1e-3)
+    assert close.mean() >= 0.99
