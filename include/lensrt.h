@@ -157,13 +157,22 @@ int lrt_filter_eval_host(int32_t filter, float param, int32_t n, const float *x,
  *   emitters[n_emitters,16]: radiance rgb, shape id, centre xyz, half-edge u xyz, half-edge v xyz, kind (col 13), pad.
  *                            kind 0 = `area` on a `rectangle` (sampled through the rectangle's parameterisation, rectangle.cpp:166-185);
  *                            kind 1 = `area` on any mesh: faces sampled by area, Mesh::sample_position (src/render/mesh.cpp:430-470,
- *                            745-803); centre / half-edges are ignored, the shape's triangles (and vertex normals) are used
- * BitmapTexture (src/textures/bitmap.cpp:115-310): RGB float texels (already linear), bilinear filter. */
+ *                            745-803); centre / half-edges are ignored, the shape's triangles (and vertex normals) are used;
+ *                            kind 2 = `constant` environment emitter (src/emitters/constant.cpp): shape id -1, columns 4..6 the
+ *                            centre and column 7 the (padded) radius of the scene's bounding sphere (constant.cpp:75-85). The
+ *                            order of the rows is the order of Scene::emitters(): a sample picks row floor(u * n_emitters).
+ * Textures: kind 0 = BitmapTexture (src/textures/bitmap.cpp:115-310), RGB float texels (already linear), bilinear filter;
+ * kinds 1..4 = the procedural patterns `checkerboard` (src/textures/checkerboard.cpp:70-89) and the fork's `checkerlines`,
+ * `comb2d`, `polarlines` (src/textures/{checkerlines,comb2d,polarlines}.cpp) with constant colours. */
 typedef struct lrt_texture_desc {
     int32_t width, height;
     int32_t wrap;              /* wrap_mode: 0 repeat, 1 mirror, 2 clamp */
-    const float *rgb;          /* [height, width, 3] host memory */
+    const float *rgb;          /* [height, width, 3] host memory (kind 0) */
     float to_uv[6];            /* first two rows of the 3x3 `to_uv` transform (identity: 1 0 0 / 0 1 0) */
+    int32_t kind;              /* 0 bitmap, 1 checkerboard, 2 checkerlines, 3 comb2d, 4 polarlines */
+    float color0[3], color1[3];
+    float linewidth;           /* kinds 2..4 */
+    float spokes;              /* kind 4 */
 } lrt_texture_desc;
 
 typedef struct lrt_scene_desc {
@@ -182,6 +191,11 @@ typedef struct lrt_scene_desc {
     const float *vertex_uvs;                         /* [n_vertices,2] */
     const int32_t *shape_flags;                      /* [n_shapes] */
     int32_t n_textures; const lrt_texture_desc *textures;
+    /* Analytic `sphere` shapes (src/shapes/sphere.cpp), intersected in double precision like the reference's scalar variants
+     * and kept outside the BVH (tested one by one: meant for the handful of spheres scene files use). 32 floats each:
+     * centre xyz, radius, shape id, flip_normals, 0, 0, then the three rows of to_world (12) and of to_object (12): the
+     * spherical parameterisation (si.uv, dp_du) lives in object space. Such shapes own no triangles. */
+    int32_t n_spheres; const float *spheres;
 } lrt_scene_desc;
 
 /* Scene::Scene (src/render/scene.cpp:22-96): builds the acceleration structure (8-wide quantised BVH, on the
@@ -225,6 +239,7 @@ typedef struct lrt_render_params {
     int32_t rng_mode;
     int32_t block_size;       /* rng_mode 1: render block size, 0 = 32 (MI_BLOCK_SIZE) */
     uint32_t base_seed;       /* rng_mode 1: the sampler's `seed` property (rng_mode 0 callers fold it into `seed`) */
+    int32_t hide_emitters;    /* path.cpp:113-114: with an environment emitter, camera rays that escape yield no valid sample */
 } lrt_render_params;
 
 /* Accumulates R,G,B,W into accum_dev [size_y+2b, size_x+2b, 4] (caller zeroes it; ImageBlock storage of

@@ -108,7 +108,7 @@ __global__ void __launch_bounds__(128) k_trace_refractive(SceneView sc, int64_t 
             unsigned work = 0;
             const RayHit h = bvh_intersect(sc.bvh, o, d, kLargest, false, work);
             if (h.tri < 0) break;
-            const Surface si = make_surface(sc, h, d);
+            const Surface si = make_surface(sc, h, o, d);
             const float eta = __ldg(shape_eta + si.shape);
             if (!(eta > 0.f)) { alive = false; break; }                    // absorber (baffle)
             float r_i, ct, eit, eti;

@@ -37,7 +37,7 @@ struct RenderArgs {
     SceneView sc;
     const LensSystem *lens;
     FilmParams film;
-    uint32_t seed; int spp, max_depth, rr_depth;
+    uint32_t seed; int spp, max_depth, rr_depth, hide_emitters;
     // base work items = (pixel tile, sample chunk), tile-major. The LAST `n_split` base items are handed out in `n_sub`
     // pieces each (guided self-scheduling): when the work counter runs out, the items still in flight are short, so the
     // tail of the launch is a fraction of a tile's work while all but a few per cent of the samples run in full-size items
@@ -85,10 +85,12 @@ LRT_D void splat_to_tile(const FilmParams &F, float *tile, int smem_w, int ox, i
 #ifndef LRT_RENDER_MIN_BLOCKS
 #define LRT_RENDER_MIN_BLOCKS 4
 #endif
-// kAttr: the scene has vertex normals / texture coordinates / textures (lrt_shade.cuh); without them the attribute code is
-// compiled out so that the hot loop keeps its instruction-cache footprint
-template <bool kAdj, bool kAttr>
+// kLevel 1 (kAttr): the scene has vertex normals / texture coordinates / textures / mesh emitters (lrt_shade.cuh); kLevel 2
+// (kAnalytic) adds analytic spheres and the environment emitter. Without them that code is compiled out so that the hot loop
+// keeps its instruction-cache footprint and its registers (level 0 is the headline variant).
+template <bool kAdj, int kLevel>
 __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(RenderArgs A) {
+    constexpr bool kAttr = kLevel >= 1, kAnalytic = kLevel >= 2;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     LensSystem &L = *reinterpret_cast<LensSystem *>(smem_raw);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -156,6 +158,20 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
         int depth = 0; bool prev_delta = true, valid_ray = false;
         RayHit seg; seg.t = 0.f; seg.u = seg.v = 0.f; seg.tri = -1;                           // hit of the current segment
         Trav T; trav_init(T, 0.f); T.cur = kTravDone;
+        // analytic spheres (kAttr variant only): tested when a ray starts; the BVH traversal then runs with the sphere's
+        // distance as its limit, and a shadow ray that a sphere blocks skips the traversal altogether
+        // (the sphere's index + 1 rides in T.hit.u, which only an accepted triangle overwrites; its distance is T.tmax; the
+        // segment's origin — needed to rebuild a sphere hit in the second half of the bounce — is parked in shared memory)
+        auto start_ray = [&](float maxt, bool any_hit) {
+            int k = -1;
+            if (kAnalytic && A.sc.n_spheres > 0) {
+                float t = maxt;
+                k = spheres_intersect(A.sc, ro, rd, maxt, any_hit, t);
+                if (k >= 0) maxt = t;
+            }
+            trav_init(T, maxt);
+            if (kAnalytic && k >= 0) { T.hit.u = __int_as_float(k + 1); if (any_hit) T.cur = kTravDone; }
+        };
 
         // drain `n` entries from the top of the splat queue (n <= 32), one per lane
         auto drain = [&](int n) {
@@ -226,14 +242,15 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
                     const int s = (fifo_head + rank) & (kFifo - 1);
                     ro = make_float3(fifo[0 * kFifo + s], fifo[1 * kFifo + s], fifo[2 * kFifo + s]);
                     rd = make_float3(fifo[3 * kFifo + s], fifo[4 * kFifo + s], fifo[5 * kFifo + s]);
-                    trav_init(T, fifo[6 * kFifo + s]);
+                    start_ray(fifo[6 * kFifo + s], false);
                     const float cam_weight = fifo[7 * kFifo + s], sx = fifo[8 * kFifo + s], sy = fifo[9 * kFifo + s];
                     park[0 * kCtaThreads] = cam_weight; park[1 * kCtaThreads] = sx; park[2 * kCtaThreads] = sy;
                     park[3 * kCtaThreads] = fifo[12 * kFifo + s]; park[4 * kCtaThreads] = fifo[13 * kFifo + s];
                     rng_state = (uint64_t) __float_as_uint(fifo[10 * kFifo + s]) | ((uint64_t) __float_as_uint(fifo[11 * kFifo + s]) << 32);
                     phase = 1;
                     throughput = make_float3(1, 1, 1); result = make_float3(0, 0, 0); eta = 1.f; depth = 0;
-                    prev_p = make_float3(0, 0, 0); prev_pdf = 1.f; prev_delta = true; valid_ray = false;
+                    prev_p = make_float3(0, 0, 0); prev_pdf = 1.f; prev_delta = true;
+                    valid_ray = kAnalytic && A.sc.env >= 0 && !A.hide_emitters;     // path.cpp:113-114
                     if (kAdj) {   // transpose of the splat: dL = sum over the footprint of w * d(loss)/d(storage RGB)
                         nrec = 0; dL = make_float3(0, 0, 0);
                         Footprint fp;
@@ -269,7 +286,8 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
             // ---- D. lanes whose ray is finished shade it
             bool done_path = false; float3 value = make_float3(0, 0, 0);
             if (phase != 0 && T.cur == kTravDone) {
-                const RayHit h = T.hit;
+                RayHit h = T.hit;
+                if (kAnalytic && h.tri < 0 && h.u != 0.f) { h.tri = A.sc.n_tris + __float_as_int(h.u) - 1; h.t = T.tmax; h.u = 0.f; }
                 n_rays++;
                 bool finish = false, occluded = true;
                 Pcg32 rng; rng.state = rng_state;
@@ -279,11 +297,23 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
                     // ---- first half of one iteration of PathIntegrator::sample's loop (path.cpp:142-208)
                     n_bounces++;
                     seg = h; wi_w = rd;
+                    if (kAnalytic) { park[5 * kCtaThreads] = ro.x; park[6 * kCtaThreads] = ro.y; park[7 * kCtaThreads] = ro.z; }
                     const bool hit = h.tri >= 0;
                     bool want_shadow = false;
+                    if (kAnalytic && !hit && A.sc.env >= 0 && prev_pdf > 0.f) {
+                        // the ray escaped: environment emitter, MIS against the previous bounce's BSDF sample (path.cpp:158-174)
+                        const float4 e0 = __ldg(A.sc.emitters + 5 * (size_t) A.sc.env);
+                        const float mw = mis_weight(prev_pdf, prev_delta ? 0.f : pdf_environment(A.sc));
+                        result += throughput * make_float3(e0.x, e0.y, e0.z) * mw;
+                        if (kAdj) {
+                            const float3 g = dL * throughput * mw;
+                            float *gp = A.grad_emitters + 16 * (size_t) A.sc.env; const int sl = A.n_bsdfs * 6 + A.sc.env * 3;
+                            add_grad(sl, gp, g.x); add_grad(sl + 1, gp + 1, g.y); add_grad(sl + 2, gp + 2, g.z);
+                        }
+                    }
                     if (hit) {
                         valid_ray = true;   // path.cpp:256 uses the loop mask `active`, not `active_next`
-                        const Surface si = make_surface<kAttr>(A.sc, h, rd);
+                        const Surface si = make_surface<kAttr, kAnalytic>(A.sc, h, ro, rd);
                         const int em = __ldg(A.sc.shape_emitter + si.shape);
                         if (em >= 0) {     // direct emission, MIS against the previous bounce's BSDF sample (:158-174)
                             float3 rel = si.p - prev_p; float dist = sqrtf(dot(rel, rel)); float3 dd = rel * (1.f / dist);
@@ -306,11 +336,11 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
                                 // iteration are committed when the bounce is finished
                                 Pcg32 peek = rng;
                                 float e_sx = peek.next_f32(), e_sy = peek.next_f32();
-                                EmitterSample es = sample_emitter_direction<kAttr>(A.sc, si.p, e_sx, e_sy);
+                                EmitterSample es = sample_emitter_direction<kAttr, kAnalytic>(A.sc, si.p, e_sx, e_sy);
                                 if (es.pdf != 0.f) {   // shadow ray: Interaction::spawn_ray_to (interaction.h:139-146)
                                     float3 so = offset_p(si.p, si.n, es.p - si.p);
                                     float3 sd = es.p - so; float sdist = sqrtf(dot(sd, sd));
-                                    ro = so; rd = sd * (1.f / sdist); trav_init(T, sdist * (1.f - kShadowEpsilon));
+                                    ro = so; rd = sd * (1.f / sdist); start_ray(sdist * (1.f - kShadowEpsilon), true);
                                     want_shadow = true;
                                 }
                             }
@@ -323,14 +353,15 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
                 }
                 if (finish) {
                     // ---- second half (path.cpp:210-281): BSDF eval/sample, NEE contribution, next ray, Russian roulette
-                    const Surface si = make_surface<kAttr>(A.sc, seg, wi_w);
+                    const float3 seg_o = kAnalytic ? make_float3(park[5 * kCtaThreads], park[6 * kCtaThreads], park[7 * kCtaThreads]) : make_float3(0, 0, 0);
+                    const Surface si = make_surface<kAttr, kAnalytic>(A.sc, seg, seg_o, wi_w);
                     const int bsdf_id = __ldg(A.sc.shape_bsdf + si.shape);
                     float e_sx = rng.next_f32(), e_sy = rng.next_f32();
                     float s1 = rng.next_f32(), s2x = rng.next_f32(), s2y = rng.next_f32();
                     float rr_sample = rng.next_f32();
                     EmitterSample es; es.pdf = 0.f; float3 wo = make_float3(0, 0, 0);
                     const bool active_em = phase == 2 && !occluded;
-                    if (active_em) { es = sample_emitter_direction<kAttr>(A.sc, si.p, e_sx, e_sy); wo = si.to_local(es.d); }
+                    if (active_em) { es = sample_emitter_direction<kAttr, kAnalytic>(A.sc, si.p, e_sx, e_sy); wo = si.to_local(es.d); }
                     BsdfResult bs = bsdf_eval_pdf_sample<kAttr>(A.sc, bsdf_id, si.uv, si.wi, wo, s1, s2x, s2y);
                     if (kAdj) {   // everything gathered from here on is linear in this surface's (specular) reflectance
                         // the sampled lobe's colour: (specular) reflectance, or the dielectric's specular_transmittance
@@ -351,7 +382,7 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
                         }
                     }
                     float3 wo_w = si.to_world(bs.wo);
-                    ro = offset_p(si.p, si.n, wo_w); rd = wo_w; trav_init(T, kLargest);
+                    ro = offset_p(si.p, si.n, wo_w); rd = wo_w; start_ray(kLargest, false);
                     throughput *= bs.weight; eta *= bs.seta;
                     valid_ray = true;
                     prev_p = si.p; prev_pdf = bs.spdf; prev_delta = bs.delta;
@@ -424,10 +455,11 @@ __global__ void __launch_bounds__(128) k_intersect(SceneView sc, int any_hit, in
         const float *r = od7 + 7 * i;
         float3 o = make_float3(r[0], r[1], r[2]), d = make_float3(r[3], r[4], r[5]);
         unsigned work = 0;
-        RayHit h = bvh_intersect(sc.bvh, o, d, r[6], any_hit != 0, work);
+        RayHit h = scene_intersect(sc, o, d, r[6], any_hit != 0, work);
         float *q = out4 + 4 * i;
         q[0] = h.t; q[1] = h.u; q[2] = h.v;
-        q[3] = h.tri >= 0 ? (float) __float_as_int(__ldg(sc.bvh.tris + 3 * (size_t) h.tri + 2).z) : -1.f;
+        if (h.tri >= sc.n_tris) q[3] = (float) (-2 - (h.tri - sc.n_tris));                 // analytic sphere k: -2 - k
+        else q[3] = h.tri >= 0 ? (float) __float_as_int(__ldg(sc.bvh.tris + 3 * (size_t) h.tri + 2).z) : -1.f;
     }
 }
 
@@ -447,6 +479,7 @@ int launch_render(const lrt_scene *sc, lrt_sensor *sensor, const lrt_film_desc *
     rc = sensor->upload(stream); if (rc) return rc;
     A.sc = sc->view; A.lens = sensor->dev;
     A.seed = rp->seed; A.spp = rp->spp; A.max_depth = rp->max_depth < 0 ? 0x7fffffff : rp->max_depth; A.rr_depth = rp->rr_depth;
+    A.hide_emitters = rp->hide_emitters;
     A.film.coalesce = rp->spp >= 4 ? film->coalesce : 0;   // integrator.cpp:290
     const FilmParams &F = A.film;
     A.pad = F.kind == FILTER_BOX ? 0 : (F.coalesce ? F.n_half : (int) std::ceil(F.radius + .5f));
@@ -460,7 +493,10 @@ int launch_render(const lrt_scene *sc, lrt_sensor *sensor, const lrt_film_desc *
     // only the header and the interfaces in use are staged (not all 32 records, not the exit-pupil LUT): every KB of
     // shared memory given back is L1 for the traversal
     A.lens_bytes = (int) ((offsetof(LensSystem, ifs) + (size_t) sensor->host.n * sizeof(LensIf) + 15) / 16 * 16);
-    size_t smem = (size_t) A.lens_bytes + (size_t) kCtaThreads * 5 * 4 + (size_t) kWarps * ((size_t) A.smem_w * A.smem_h * 4 + kFifo * kFifoWords + kQueue * kQueueWords) * 4;
+    const bool attr = sc->view.tri_attr != nullptr || sc->view.textures != nullptr || sc->view.em_tris != nullptr || sc->view.n_spheres > 0 ||
+                      sc->view.env >= 0;
+    const bool analytic = sc->view.n_spheres > 0 || sc->view.env >= 0;
+    size_t smem = (size_t) A.lens_bytes + (size_t) kCtaThreads * (analytic ? 8 : 5) * 4 + (size_t) kWarps * ((size_t) A.smem_w * A.smem_h * 4 + kFifo * kFifoWords + kQueue * kQueueWords) * 4;
     {   // traversal bursts end when this many 32nds of their lanes have finished (LRT_EXIT_DROP overrides; tuning knob)
         const char *e = getenv("LRT_EXIT_DROP"); A.exit_drop = e ? atoi(e) : 26;
         if (A.exit_drop < 1) A.exit_drop = 1; if (A.exit_drop > 32) A.exit_drop = 32;
@@ -473,10 +509,8 @@ int launch_render(const lrt_scene *sc, lrt_sensor *sensor, const lrt_film_desc *
         static std::mutex mu; static bool attr_set[64] = {};
         std::lock_guard<std::mutex> lock(mu);
         if (dev >= 64 || !attr_set[dev]) {
-            LRT_CUDA(cudaFuncSetAttribute(k_render<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-            LRT_CUDA(cudaFuncSetAttribute(k_render<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-            LRT_CUDA(cudaFuncSetAttribute(k_render<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-            LRT_CUDA(cudaFuncSetAttribute(k_render<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+            void (*all[])(RenderArgs) = { k_render<false, 0>, k_render<false, 1>, k_render<false, 2>, k_render<true, 0>, k_render<true, 1>, k_render<true, 2> };
+            for (auto f : all) LRT_CUDA(cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
             if (dev < 64) attr_set[dev] = true;
         }
     }
@@ -486,8 +520,8 @@ int launch_render(const lrt_scene *sc, lrt_sensor *sensor, const lrt_film_desc *
                 "lrt_render_backward: max_depth must be in [0, 17] (one gradient record per bounce; unbounded paths are not supported)");
     A.grad_storage = grad_storage; A.grad_bsdfs = grad_bsdfs; A.grad_emitters = grad_emitters; A.n_bsdfs = sc->n_bsdfs;
     int per_sm = 1;
-    const bool attr = sc->view.tri_attr != nullptr || sc->view.textures != nullptr || sc->view.em_tris != nullptr;
-    void (*kern)(RenderArgs) = adjoint ? (attr ? k_render<true, true> : k_render<true, false>) : (attr ? k_render<false, true> : k_render<false, false>);
+    void (*kern)(RenderArgs) = adjoint ? (analytic ? k_render<true, 2> : attr ? k_render<true, 1> : k_render<true, 0>)
+                                       : (analytic ? k_render<false, 2> : attr ? k_render<false, 1> : k_render<false, 0>);
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kCtaThreads, smem);
     if (per_sm < 1) per_sm = 1;
     long long resident = (long long) sms * per_sm;

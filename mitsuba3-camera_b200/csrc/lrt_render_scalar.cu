@@ -23,7 +23,7 @@ struct ScalarArgs {
     const LensSystem *lens;
     FilmParams film;
     uint32_t seed0;                  // base_seed + seed * W * H
-    int spp, max_depth, rr_depth, block_size, blocks_x;
+    int spp, max_depth, rr_depth, block_size, blocks_x, hide_emitters;
     const uint32_t *block_id;        // [blocks_y * blocks_x] spiral position of every block
     float *accum;
     unsigned long long *stats;       // [0] samples, [1] lens misses, [2] rays, [3] bounces
@@ -42,12 +42,19 @@ LRT_D float3 path_sample_scalar(const ScalarArgs &A, Pcg32 &rng, float3 ro, floa
     float eta = 1.f, prev_pdf = 1.f; bool prev_delta = true, valid_ray = false;
     int depth = 0;
     if (A.max_depth == 0) return result;
+    valid_ray = A.sc.env >= 0 && !A.hide_emitters;                   // path.cpp:113-114
     while (true) {
         unsigned work = 0;
-        const RayHit h = bvh_intersect(A.sc.bvh, ro, rd, maxt, false, work);
+        const RayHit h = scene_intersect(A.sc, ro, rd, maxt, false, work);
         n_rays++; n_bounces++;
-        if (h.tri < 0) break;
-        const Surface si = make_surface(A.sc, h, rd);
+        if (h.tri < 0) {     // the ray escaped: the environment emitter, MIS against the previous bounce (path.cpp:158-174)
+            if (A.sc.env >= 0 && prev_pdf > 0.f) {
+                const float4 e0 = __ldg(A.sc.emitters + 5 * (size_t) A.sc.env);
+                result += throughput * make_float3(e0.x, e0.y, e0.z) * mis_weight(prev_pdf, prev_delta ? 0.f : pdf_environment(A.sc));
+            }
+            break;
+        }
+        const Surface si = make_surface(A.sc, h, ro, rd);
         const int em = __ldg(A.sc.shape_emitter + si.shape);
         if (em >= 0) {   // direct emission, MIS against the previous bounce's BSDF sample (path.cpp:158-174)
             const float3 rel = si.p - prev_p; const float dist = sqrtf(dot(rel, rel)); const float3 dd = rel * (1.f / dist);
@@ -68,7 +75,7 @@ LRT_D float3 path_sample_scalar(const ScalarArgs &A, Pcg32 &rng, float3 ro, floa
                 const float3 so = offset_p(si.p, si.n, es.p - si.p);
                 const float3 sd = es.p - so; const float sdist = sqrtf(dot(sd, sd));
                 unsigned w2 = 0;
-                const RayHit sh = bvh_intersect(A.sc.bvh, so, sd * (1.f / sdist), sdist * (1.f - kShadowEpsilon), true, w2);
+                const RayHit sh = scene_intersect(A.sc, so, sd * (1.f / sdist), sdist * (1.f - kShadowEpsilon), true, w2);
                 n_rays++;
                 if (sh.tri >= 0) es.pdf = 0.f;
             }
@@ -183,6 +190,7 @@ int launch_render_scalar(const lrt_scene *sc, lrt_sensor *sensor, const lrt_film
     const int blocks_y = (film->size_y + A.block_size - 1) / A.block_size;
     A.seed0 = rp->base_seed + rp->seed * (uint32_t) (film->size_x * film->size_y);   // integrator.cpp:196, sampler.cpp:119
     A.spp = rp->spp; A.max_depth = rp->max_depth < 0 ? 0x7fffffff : rp->max_depth; A.rr_depth = rp->rr_depth;
+    A.hide_emitters = rp->hide_emitters;
     const std::vector<uint32_t> ids = spiral_ids(A.blocks_x, blocks_y);
     uint32_t *d_ids = nullptr;
     LRT_CUDA(cudaMallocAsync((void **) &d_ids, ids.size() * sizeof(uint32_t), stream));

@@ -37,9 +37,23 @@ int lrt_scene_create(const lrt_scene_desc *d, lrt_scene **out) {
         LRT_REQUIRE(d->shape_emitter[s] >= -1 && d->shape_emitter[s] < d->n_emitters, "shape_emitter out of range");
     }
     LRT_REQUIRE(d->n_textures >= 0 && (d->n_textures == 0 || d->textures), "bad texture table");
-    for (int t = 0; t < d->n_textures; ++t)
-        LRT_REQUIRE(d->textures[t].width > 0 && d->textures[t].height > 0 && d->textures[t].rgb && d->textures[t].wrap >= 0 && d->textures[t].wrap <= 2,
-                    "bad texture");
+    for (int t = 0; t < d->n_textures; ++t) {
+        const lrt_texture_desc &x = d->textures[t];
+        LRT_REQUIRE(x.kind >= 0 && x.kind <= 4, "texture kind must be 0 (bitmap) .. 4 (polarlines)");
+        LRT_REQUIRE(x.kind != 0 || (x.width > 0 && x.height > 0 && x.rgb && x.wrap >= 0 && x.wrap <= 2), "bad bitmap texture");
+    }
+    LRT_REQUIRE(d->n_spheres >= 0 && (d->n_spheres == 0 || d->spheres), "bad sphere table");
+    for (int k = 0; k < d->n_spheres; ++k) {
+        const float *q = d->spheres + 32 * (size_t) k;
+        LRT_REQUIRE(q[3] > 0.f && q[4] >= 0.f && q[4] < (float) d->n_shapes && q[4] == (float) (int) q[4], "bad sphere (radius / shape id)");
+    }
+    int env = -1;
+    for (int i = 0; i < d->n_emitters; ++i) {
+        const float kind = d->emitters[16 * i + 13];
+        LRT_REQUIRE(kind == 0.f || kind == 1.f || kind == 2.f, "emitter kind must be 0 (rectangle), 1 (mesh) or 2 (constant environment)");
+        if (kind == 2.f) { LRT_REQUIRE(env < 0, "Only one environment emitter can be specified per scene."); env = i; }
+        else LRT_REQUIRE(d->emitters[16 * i + 3] >= 0.f && d->emitters[16 * i + 3] < (float) d->n_shapes, "emitter shape id out of range");
+    }
     for (int b = 0; b < d->n_bsdfs; ++b) {
         const float tid = d->bsdfs[16 * b + 15];
         LRT_REQUIRE(tid >= 0.f && tid <= (float) d->n_textures && tid == (float) (int) tid, "bsdf texture id out of range");
@@ -87,6 +101,7 @@ int lrt_scene_create(const lrt_scene_desc *d, lrt_scene **out) {
     for (int i = 0; i < d->n_emitters; ++i) {
         const float *r = d->emitters + 16 * i; float *o = em.data() + 20 * (size_t) i;
         o[0] = r[0]; o[1] = r[1]; o[2] = r[2]; o[3] = r[3];
+        if (r[13] == 2.f) { o[4] = r[4]; o[5] = r[5]; o[6] = r[6]; o[7] = r[7]; o[19] = 2.f; continue; }   // environment: bounding sphere
         if (r[13] == 1.f) {   // area light on a general mesh: Mesh::build_pmf (src/render/mesh.cpp:430-470) + DiscreteDistribution
             const int shape = (int) r[3];
             const bool has_n = d->vertex_normals && d->shape_flags && (d->shape_flags[shape] & 1);
@@ -128,21 +143,26 @@ int lrt_scene_create(const lrt_scene_desc *d, lrt_scene **out) {
     if (cudaMalloc(&s->d_node_box, std::max<size_t>(nodes.size(), 1) * 6 * sizeof(float)) != cudaSuccess) { lrt_scene_destroy(s); return cuda_fail(cudaGetLastError(), "cudaMalloc"); }
     if (!attr.empty() && (rc = upload(&s->d_tri_attr, attr.data(), attr.size()))) { lrt_scene_destroy(s); return rc; }
     if (d->n_textures) {
+        auto texels_of = [&](int t) { return d->textures[t].kind == 0 ? (size_t) d->textures[t].width * d->textures[t].height * 3 : (size_t) 0; };
         size_t total = 0;
-        for (int t = 0; t < d->n_textures; ++t) total += (size_t) d->textures[t].width * d->textures[t].height * 3;
+        for (int t = 0; t < d->n_textures; ++t) total += texels_of(t);
         std::vector<float> texels; texels.reserve(total);
-        for (int t = 0; t < d->n_textures; ++t) texels.insert(texels.end(), d->textures[t].rgb, d->textures[t].rgb + (size_t) d->textures[t].width * d->textures[t].height * 3);
+        for (int t = 0; t < d->n_textures; ++t) if (texels_of(t)) texels.insert(texels.end(), d->textures[t].rgb, d->textures[t].rgb + texels_of(t));
         if ((rc = upload(&s->d_tex_data, texels.data(), texels.size()))) { lrt_scene_destroy(s); return rc; }
         std::vector<TexView> tv(d->n_textures); size_t off = 0;
         for (int t = 0; t < d->n_textures; ++t) {
-            tv[t].data = (const float *) s->d_tex_data + off; tv[t].w = d->textures[t].width; tv[t].h = d->textures[t].height;
-            tv[t].wrap = d->textures[t].wrap; tv[t].pad = 0;
-            for (int k = 0; k < 6; ++k) tv[t].to_uv[k] = d->textures[t].to_uv[k];
-            off += (size_t) tv[t].w * tv[t].h * 3;
+            const lrt_texture_desc &x = d->textures[t];
+            tv[t].data = (const float *) s->d_tex_data + off; tv[t].w = x.width; tv[t].h = x.height;
+            tv[t].wrap = x.wrap; tv[t].kind = x.kind;
+            for (int k = 0; k < 6; ++k) tv[t].to_uv[k] = x.to_uv[k];
+            for (int k = 0; k < 3; ++k) { tv[t].color0[k] = x.color0[k]; tv[t].color1[k] = x.color1[k]; }
+            tv[t].linewidth = x.linewidth; tv[t].spokes = x.spokes;
+            off += texels_of(t);
         }
         if ((rc = upload(&s->d_textures, tv.data(), tv.size()))) { lrt_scene_destroy(s); return rc; }
         s->n_textures = d->n_textures;
     }
+    if (d->n_spheres && (rc = upload(&s->d_spheres, d->spheres, (size_t) d->n_spheres * 32))) { lrt_scene_destroy(s); return rc; }
     if (cudaMalloc(&s->d_counter, (kCounterRing + 8) * sizeof(unsigned long long)) != cudaSuccess) { lrt_scene_destroy(s); return cuda_fail(cudaGetLastError(), "cudaMalloc"); }
     s->view.bvh.nodes = (const uint4 *) s->d_nodes; s->view.bvh.tris = (const float4 *) s->d_tris;
     s->view.bvh.kb = 0x4B000000u; s->view.bvh.km = 0xfffffff8u;
@@ -151,6 +171,8 @@ int lrt_scene_create(const lrt_scene_desc *d, lrt_scene **out) {
     s->view.n_emitters = d->n_emitters;
     s->view.tri_attr = (const float4 *) s->d_tri_attr; s->view.textures = (const TexView *) s->d_textures;
     s->view.em_tris = (const float4 *) s->d_em_tris;
+    s->view.spheres = (const float4 *) s->d_spheres; s->view.n_spheres = d->n_spheres; s->view.n_tris = (int) s->n_tris;
+    s->view.env = env;
     *out = s;
     return LRT_OK;
 }
@@ -169,7 +191,7 @@ int lrt_scene_set_params(lrt_scene *s, const float *bsdfs, const float *emitter_
 void lrt_scene_destroy(lrt_scene *s) {
     if (!s) return;
     void *p[] = { s->d_nodes, s->d_tris, s->d_shape_bsdf, s->d_shape_emitter, s->d_bsdfs, s->d_emitters, s->d_counter,
-                  s->d_tri_attr, s->d_tex_data, s->d_textures, s->d_tri_vidx, s->d_node_box, s->d_em_tris };
+                  s->d_tri_attr, s->d_tex_data, s->d_textures, s->d_tri_vidx, s->d_node_box, s->d_em_tris, s->d_spheres };
     for (void *q : p) if (q) cudaFree(q);
     delete s;
 }

@@ -18,7 +18,8 @@ namespace lrt {
 
 enum : int { BSDF_DIFFUSE = 0, BSDF_CONDUCTOR = 1, BSDF_DIELECTRIC = 2 };
 
-struct TexView { const float *data; int w, h, wrap, pad; float to_uv[6]; };   // RGB float texels, row-major; wrap 0 repeat 1 mirror 2 clamp
+// kind 0: RGB float texels, row-major; wrap 0 repeat 1 mirror 2 clamp. kinds 1..4: checkerboard, checkerlines, comb2d, polarlines
+struct TexView { const float *data; int w, h, wrap, kind; float to_uv[6]; float color0[3], color1[3], linewidth, spokes; };
 
 struct SceneView {
     BvhView bvh;
@@ -35,6 +36,11 @@ struct SceneView {
     // [p0.xyz, cdf | e0.xyz, pmf | e1.xyz, has_normals | n0 | n1 | n2], in the mesh's own face order; the emitter record
     // (second float4) then holds (first triangle, count, area sum, 1 / area sum) and its last float4 .w = 1 marks the kind
     const float4 *em_tris;
+    // analytic spheres (sphere.cpp), outside the BVH: 8 x float4 = [c.xyz, r | shape, flip, -, - | to_world rows | to_object rows].
+    // A hit on sphere k is reported as primitive n_tris + k.
+    const float4 *spheres;
+    int n_spheres, n_tris;
+    int env;                  // row of the `constant` environment emitter, -1 = none
 };
 
 struct Surface {
@@ -75,8 +81,79 @@ static __device__ __noinline__ void surface_attributes(const float4 *__restrict_
     }
 }
 
-// kAttr = false compiles the vertex-attribute path out (scenes without normals / uvs / textures: the fast kernel variant)
-template <bool kAttr = true> LRT_D Surface make_surface(const SceneView &sc, const RayHit &h, float3 ray_d) {
+// ---- Dr.Jit's single-precision atan2 / asin (ext/drjit/include/drjit/math.h:519-594, 366-412): minimax / CEPHES polynomials
+// in Estrin form. The spherical parameterisation and the `polarlines` pattern branch on their results.
+LRT_D float atan2_drjit(float y, float x) {
+    const float abs_x = fabsf(x), abs_y = fabsf(y), min_val = fminf(abs_y, abs_x), max_val = fmaxf(abs_x, abs_y);
+    const float scaled_min = min_val / max_val, z = scaled_min * scaled_min, z2 = z * z;
+    const float a0 = z * -0.33326497518773606976f + 0.99999934166683966009f, a1 = z * -0.13486708938456973185f + 0.19881342388439013552f,
+                a2 = z * -0.037006525670417265220f + 0.083863120428809689910f, a3 = 0.0078613793713198150252f;
+    const float b0 = z2 * a1 + a0, b1 = z2 * a3 + a2;
+    float t = ((z2 * z2) * b1 + b0) * scaled_min;
+    if (abs_y > abs_x) t = kPi * .5f - t;
+    if (x < 0.f) t = kPi - t;
+    const float r = y < 0.f ? -t : t;
+    return max_val != 0.f ? r : 0.f;
+}
+LRT_D float asin_drjit(float x) {
+    const float xa = fabsf(x), x2 = x * x;
+    const bool big = xa > .5f;
+    const float x1 = .5f * (1.f - xa), x3 = big ? x1 : x2, x4 = big ? sqrtf(x1) : xa, y2 = x3 * x3;
+    const float a0 = x3 * 7.4953002686e-2f + 1.6666752422e-1f, a1 = x3 * 2.4181311049e-2f + 4.5470025998e-2f, a2 = 4.2163199048e-2f;
+    float z1 = (y2 * y2) * a2 + (y2 * a1 + a0);
+    z1 = z1 * (x3 * x4) + x4;
+    const float r = big ? (.5f * kPi) - (z1 + z1) : z1;
+    return copysignf(r, x);
+}
+
+// Sphere::ray_intersect_preliminary / ray_test (src/shapes/sphere.cpp:493-607) over the scene's analytic spheres, double
+// precision with every operation rounded separately as in the reference's scalar build (math::solve_quadratic,
+// include/mitsuba/core/math.h:358-402). Returns the index of the closest sphere hit in [0, maxt] (any_hit: the first found),
+// -1 if none. Out of line: scenes without spheres never come here.
+static __device__ __noinline__ int spheres_intersect(const SceneView &sc, float3 o, float3 d, float maxt_f, bool any_hit, float &t_out) {
+    int best = -1;
+    for (int k = 0; k < sc.n_spheres; ++k) {
+        const float4 s0 = __ldg(sc.spheres + 8 * (size_t) k);
+        const double radius = s0.w, cx = s0.x, cy = s0.y, cz = s0.z, maxt = maxt_f;
+        const double lx = __dsub_rn((double) o.x, cx), ly = __dsub_rn((double) o.y, cy), lz = __dsub_rn((double) o.z, cz);
+        const double dx = d.x, dy = d.y, dz = d.z;
+        auto dot3 = [](double ax, double ay, double az, double bx, double by, double bz) {
+            return __dadd_rn(__dadd_rn(__dmul_rn(ax, bx), __dmul_rn(ay, by)), __dmul_rn(az, bz));
+        };
+        const double A = dot3(dx, dy, dz, dx, dy, dz);
+        const double plane_t = __ddiv_rn(dot3(-lx, -ly, -lz, dx, dy, dz), __dsqrt_rn(A));
+        bool no_hit = plane_t == 0.0 && o.x != s0.x && o.y != s0.y && o.z != s0.z;
+        const float pt = (float) plane_t;                      // ray(FloatP(plane_t)) is evaluated in single precision
+        const double ox = __dsub_rn((double) strict::fmadd(d.x, pt, o.x), cx), oy = __dsub_rn((double) strict::fmadd(d.y, pt, o.y), cy),
+                     oz = __dsub_rn((double) strict::fmadd(d.z, pt, o.z), cz);
+        const double oo = dot3(ox, oy, oz, ox, oy, oz);
+        no_hit = no_hit && __dsqrt_rn(oo) > radius;
+        const double B = __dmul_rn(2.0, dot3(ox, oy, oz, dx, dy, dz)), C = __dsub_rn(oo, __dmul_rn(radius, radius));
+        const bool linear_case = A == 0.0, valid_linear = linear_case && B != 0.0;
+        double x0 = __ddiv_rn(-C, B), x1 = x0;
+        const double discrim = __dsub_rn(__dmul_rn(B, B), __dmul_rn(__dmul_rn(4.0, A), C));
+        const bool valid_quadratic = !linear_case && discrim >= 0.0;
+        if (valid_quadratic) {
+            const double sq = __dsqrt_rn(discrim), temp = __dmul_rn(-0.5, __dadd_rn(B, copysign(sq, B)));
+            const double x0p = __ddiv_rn(temp, A), x1p = __ddiv_rn(C, temp);
+            x0 = fmin(x0p, x1p); x1 = fmax(x0p, x1p);
+        }
+        const double near_t = __dadd_rn(x0, plane_t), far_t = __dadd_rn(x1, plane_t);
+        const bool out_bounds = !(near_t <= maxt && far_t >= 0.0), in_bounds = near_t < 0.0 && far_t > maxt;
+        if (!((valid_linear || valid_quadratic) && !no_hit && !out_bounds && !in_bounds)) continue;
+        const float t = near_t < 0.0 ? (float) far_t : (float) near_t;
+        if (best < 0 || t < t_out) { best = k; t_out = t; maxt_f = fminf(maxt_f, t); }
+        if (any_hit) break;
+    }
+    return best;
+}
+
+static __device__ __noinline__ void sphere_surface(const SceneView &sc, int k, float3 ray_o, float3 ray_d, float t, Surface &si);
+
+// kAttr = false compiles the vertex-attribute path out (scenes without normals / uvs / textures / spheres: the fast kernel
+// variant). ray_o is only needed for hits on analytic spheres (primitive index >= n_tris).
+template <bool kAttr = true, bool kAnalytic = kAttr> LRT_D Surface make_surface(const SceneView &sc, const RayHit &h, float3 ray_o, float3 ray_d) {
+    if (kAnalytic && h.tri >= sc.n_tris) { Surface ss; sphere_surface(sc, h.tri - sc.n_tris, ray_o, ray_d, h.t, ss); return ss; }
     const float4 *tp = sc.bvh.tris + 3 * (size_t) h.tri;
     float4 a = __ldg(tp), b = __ldg(tp + 1), c = __ldg(tp + 2);
     float3 p0 = make_float3(a.x, a.y, a.z), p1 = make_float3(a.w, b.x, b.y), p2 = make_float3(b.z, b.w, c.x);
@@ -84,7 +161,11 @@ template <bool kAttr = true> LRT_D Surface make_surface(const SceneView &sc, con
     float b1 = h.u, b2 = h.v, b0 = 1.f - b1 - b2;
     si.p = p0 * b0 + (p1 * b1 + p2 * b2);
     const float3 dp0 = p1 - p0, dp1 = p2 - p0;
-    si.n = normalize(cross(dp0, dp1));
+    // the face normal's cross product with separately rounded products: a component that cancels exactly (a planar shape whose
+    // normal lies in a coordinate plane) must come out as the reference's exact 0 — with a fused multiply-add it would be the
+    // product's rounding error, of either sign, and coordinate_system() below branches on the sign of n.z
+    si.n = normalize(make_float3(strict::sub(strict::mul(dp0.y, dp1.z), strict::mul(dp0.z, dp1.y)), strict::sub(strict::mul(dp0.z, dp1.x), strict::mul(dp0.x, dp1.z)),
+                                 strict::sub(strict::mul(dp0.x, dp1.y), strict::mul(dp0.y, dp1.x))));
     float3 dp_du, dp_dv; coordinate_system(si.n, dp_du, dp_dv);
     si.sn = si.n; si.uv = make_float2(b1, b2);
     const int flags = __float_as_int(c.w);
@@ -98,6 +179,32 @@ template <bool kAttr = true> LRT_D Surface make_surface(const SceneView &sc, con
     si.wi = si.to_local(-ray_d);
     si.shape = __float_as_int(c.y);
     return si;
+}
+
+// Sphere::compute_surface_interaction (sphere.cpp:609-718, non-differentiable branch) + initialize_sh_frame
+static __device__ __noinline__ void sphere_surface(const SceneView &sc, int k, float3 ray_o, float3 ray_d, float t, Surface &si) {
+    const float4 *sp = sc.spheres + 8 * (size_t) k;
+    const float4 s0 = __ldg(sp), s1 = __ldg(sp + 1);
+    const float3 c = make_float3(s0.x, s0.y, s0.z);
+    float3 n = normalize((ray_o + ray_d * t) - c);
+    si.p = c + n * s0.w;                                         // re-projected onto the sphere
+    const float4 w0 = __ldg(sp + 2), w1 = __ldg(sp + 3), w2 = __ldg(sp + 4), m0 = __ldg(sp + 5), m1 = __ldg(sp + 6), m2 = __ldg(sp + 7);
+    const float3 local = make_float3(m0.z * si.p.z + (m0.y * si.p.y + (m0.x * si.p.x + m0.w)), m1.z * si.p.z + (m1.y * si.p.y + (m1.x * si.p.x + m1.w)),
+                                     m2.z * si.p.z + (m2.y * si.p.y + (m2.x * si.p.x + m2.w)));
+    const float3 q = make_float3(local.x, local.y, local.z - copysignf(1.f, local.z));       // unit_angle_z (drjit/sphere.h:73-82)
+    const float temp = 2.f * asin_drjit(.5f * sqrtf(dot(q, q))), theta = local.z >= 0.f ? temp : kPi - temp;
+    float phi = atan2_drjit(local.y, local.x);
+    if (phi < 0.f) phi += 2.f * kPi;
+    si.uv = make_float2(phi * (.5f * kInvPi), theta * kInvPi);
+    const float ux = -local.y, uy = local.x;                     // dp_du = to_world * (-y, x, 0) * 2 pi
+    const float3 dp_du = make_float3(w0.y * uy + w0.x * ux, w1.y * uy + w1.x * ux, w2.y * uy + w2.x * ux) * (2.f * kPi);
+    if (s1.y != 0.f) n = -n;
+    si.n = si.sn = n;
+    if (dp_du.x == 0.f && dp_du.y == 0.f && dp_du.z == 0.f) { float3 tt; coordinate_system(n, si.s, tt); }
+    else si.s = normalize(dp_du - n * dot(n, dp_du));
+    si.t = cross(n, si.s);
+    si.wi = si.to_local(-ray_d);
+    si.shape = (int) s1.x;
 }
 
 LRT_D float3 offset_p(float3 p, float3 n, float3 d) {
@@ -142,8 +249,33 @@ LRT_D int tex_wrap(int pos, int shape, int mode) {
     return mod;
 }
 
+// checkerboard.cpp:70-89 and the fork's checkerlines / comb2d / polarlines patterns (constant colours)
+static __device__ __noinline__ float3 procedural_eval(const TexView *tv, float2 uv_in) {
+    const float *m = tv->to_uv;
+    const int kind = tv->kind;
+    bool m0;
+    if (kind == 4) {
+        const float x = 2.f * uv_in.x - 1.f, y = 2.f * uv_in.y - 1.f;
+        const float u = m[1] * y + (m[0] * x + m[2]), v = m[4] * y + (m[3] * x + m[5]);
+        const float radius = sqrtf(u * u + v * v), theta = atan2_drjit(u, v) / (2.f * kPi) * tv->spokes;
+        m0 = (fabsf(2.f * (radius - floorf(radius)) - 1.f) > 1.f - tv->linewidth) ||
+             (fabsf(2.f * (theta - floorf(theta)) - 1.f) > 1.f - tv->linewidth * tv->spokes / (2.f * kPi * radius));
+    } else {
+        float u = m[1] * uv_in.y + (m[0] * uv_in.x + m[2]), v = m[4] * uv_in.y + (m[3] * uv_in.x + m[5]);
+        if (kind == 1) m0 = (u - floorf(u) > .5f) == (v - floorf(v) > .5f);
+        else {
+            u *= 2.f; v *= 2.f; u -= floorf(u); v -= floorf(v);
+            const bool mx = fabsf(2.f * u - 1.f) > 1.f - tv->linewidth, my = fabsf(2.f * v - 1.f) > 1.f - tv->linewidth;
+            m0 = kind == 2 ? (mx || my) : !(mx && my);
+        }
+    }
+    const float *c = m0 ? tv->color0 : tv->color1;
+    return make_float3(c[0], c[1], c[2]);
+}
+
 // BitmapTexture::eval for an RGB texture, bilinear filter (out of line: cold for untextured scenes)
 static __device__ __noinline__ float3 texture_eval(const TexView *tv, float2 uv_in) {
+    if (tv->kind != 0) return procedural_eval(tv, uv_in);
     const float *m = tv->to_uv;
     const float u = m[1] * uv_in.y + (m[0] * uv_in.x + m[2]), v = m[4] * uv_in.y + (m[3] * uv_in.x + m[5]);
     const int w = tv->w, h = tv->h, mode = tv->wrap;
@@ -236,7 +368,7 @@ static __device__ __noinline__ void mesh_emitter_sample_position(const SceneView
 }
 
 // Scene::sample_emitter_direction (scene.cpp:299-353) without the visibility test (done by the caller)
-template <bool kAttr = true> LRT_D EmitterSample sample_emitter_direction(const SceneView &sc, float3 ref_p, float sx, float sy) {
+template <bool kAttr = true, bool kAnalytic = kAttr> LRT_D EmitterSample sample_emitter_direction(const SceneView &sc, float3 ref_p, float sx, float sy) {
     EmitterSample es; es.pdf = 0.f; es.weight = make_float3(0, 0, 0); es.p = es.n = es.d = make_float3(0, 0, 0); es.dist = 0.f;
     int count = sc.n_emitters;
     if (count == 0) return es;
@@ -249,7 +381,18 @@ template <bool kAttr = true> LRT_D EmitterSample sample_emitter_direction(const 
     const float4 *ep = sc.emitters + 5 * (size_t) index;
     float4 e0 = __ldg(ep), e1 = __ldg(ep + 1), e2 = __ldg(ep + 2), e3 = __ldg(ep + 3), e4 = __ldg(ep + 4);
     float inv_area = e1.w;
-    if (kAttr && e4.w != 0.f) mesh_emitter_sample_position(sc, e1, sx, sy, es.p, es.n);
+    if (kAnalytic && e4.w == 2.f) {     // `constant` environment (constant.cpp:113-142): uniform direction, the point 2 max(R, |p - c|) away
+        const float z = 1.f - 2.f * sy, r = sqrtf(fmaxf(1.f - z * z, 0.f));
+        float sn, cs; sincos_drjit(2.f * kPi * sx, sn, cs);
+        es.d = make_float3(r * cs, r * sn, z);
+        const float3 rel = ref_p - make_float3(e1.x, e1.y, e1.z);
+        es.dist = 2.f * fmaxf(e1.w, sqrtf(dot(rel, rel)));
+        es.p = ref_p + es.d * es.dist; es.n = -es.d;
+        es.weight = make_float3(e0.x, e0.y, e0.z) * (emitter_weight * (4.f * kPi));
+        es.pdf = (.25f * kInvPi) * pmf;
+        return es;
+    }
+    if (kAttr && e4.w == 1.f) mesh_emitter_sample_position(sc, e1, sx, sy, es.p, es.n);
     else {
         float ux = sx * 2.f - 1.f, uy = sy * 2.f - 1.f;
         es.p = make_float3(e1.x, e1.y, e1.z) + make_float3(e2.x, e2.y, e2.z) * ux + make_float3(e3.x, e3.y, e3.z) * uy;
@@ -278,6 +421,25 @@ LRT_D float pdf_emitter_direction(const SceneView &sc, int em, float3 d, float d
     float adp = fabsf(dp);
     float pdf = inv_area * (adp != 0.f ? dist * dist / adp : 0.f);
     return sc.n_emitters > 1 ? pdf / (float) sc.n_emitters : pdf;
+}
+
+// the environment seen by a ray that escaped (constant.cpp:144-149): uniform over the sphere of directions
+LRT_D float pdf_environment(const SceneView &sc) {
+    const float pdf = .25f * kInvPi;
+    return sc.n_emitters > 1 ? pdf / (float) sc.n_emitters : pdf;
+}
+
+// closest hit over the BVH and the analytic spheres (callers outside the render megakernel's resumable traversal)
+template <bool kAttr = true> LRT_D RayHit scene_intersect(const SceneView &sc, float3 o, float3 d, float maxt, bool any_hit, unsigned &work) {
+    int sph = -1; float sph_t = maxt;
+    if (kAttr && sc.n_spheres > 0) {
+        sph = spheres_intersect(sc, o, d, maxt, any_hit, sph_t);
+        if (sph >= 0 && any_hit) { RayHit h; h.t = sph_t; h.u = h.v = 0.f; h.tri = sc.n_tris + sph; return h; }
+        if (sph >= 0) maxt = sph_t;
+    }
+    RayHit h = bvh_intersect(sc.bvh, o, d, maxt, any_hit, work);
+    if (kAttr && h.tri < 0 && sph >= 0) { h.t = sph_t; h.u = h.v = 0.f; h.tri = sc.n_tris + sph; }
+    return h;
 }
 
 LRT_D float mis_weight(float a, float b) {

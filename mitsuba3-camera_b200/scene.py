@@ -22,7 +22,8 @@ f32 = np.float32
 
 class TextureDesc(C.Structure):
     _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("wrap", C.c_int32), ("rgb", C.POINTER(C.c_float)),
-                ("to_uv", C.c_float * 6)]
+                ("to_uv", C.c_float * 6), ("kind", C.c_int32), ("color0", C.c_float * 3), ("color1", C.c_float * 3),
+                ("linewidth", C.c_float), ("spokes", C.c_float)]
 
 
 class SceneDesc(C.Structure):
@@ -33,13 +34,14 @@ class SceneDesc(C.Structure):
                 ("n_emitters", C.c_int32), ("emitters", C.POINTER(C.c_float)),
                 ("vertex_normals", C.POINTER(C.c_float)), ("vertex_uvs", C.POINTER(C.c_float)),
                 ("shape_flags", C.POINTER(C.c_int32)),
-                ("n_textures", C.c_int32), ("textures", C.POINTER(TextureDesc))]
+                ("n_textures", C.c_int32), ("textures", C.POINTER(TextureDesc)),
+                ("n_spheres", C.c_int32), ("spheres", C.POINTER(C.c_float))]
 
 
 class RenderParams(C.Structure):
     _fields_ = [("seed", C.c_uint32), ("spp", C.c_int32), ("max_depth", C.c_int32), ("rr_depth", C.c_int32),
                 ("shard_index", C.c_int32), ("shard_count", C.c_int32), ("chunks", C.c_int32),
-                ("rng_mode", C.c_int32), ("block_size", C.c_int32), ("base_seed", C.c_uint32)]
+                ("rng_mode", C.c_int32), ("block_size", C.c_int32), ("base_seed", C.c_uint32), ("hide_emitters", C.c_int32)]
 
 
 # ------------------------------------------------------------------------------------------------ plugins
@@ -491,13 +493,17 @@ class Scene:
         tdesc = (TextureDesc * max(len(tex), 1))()
         for i, t in enumerate(tex):
             h, w, _ = t["rgb"].shape
-            tdesc[i] = TextureDesc(w, h, int(t["wrap"]), capi.fp(t["rgb"].reshape(-1)), (C.c_float * 6)(*[float(x) for x in t["to_uv"]]))
+            f3 = lambda v: (C.c_float * 3)(*[float(x) for x in v])   # noqa: E731
+            tdesc[i] = TextureDesc(w, h, int(t["wrap"]), capi.fp(t["rgb"].reshape(-1)), (C.c_float * 6)(*[float(x) for x in t["to_uv"]]),
+                                   int(t.get("kind", 0)), f3(t.get("color0", [0, 0, 0])), f3(t.get("color1", [0, 0, 0])),
+                                   float(t.get("linewidth", 0.0)), float(t.get("spokes", 0)))
         d = SceneDesc(len(a["vertices"]), opt(a["vertices"], capi.fp), len(a["indices"]), opt(a["indices"], capi.ip),
                       opt(a["tri_shape"], capi.ip), len(a["shape_bsdf"]), opt(a["shape_bsdf"], capi.ip),
                       opt(a["shape_emitter"], capi.ip), len(a["bsdfs"]), opt(a["bsdfs"], capi.fp),
                       len(a["emitters"]), opt(a["emitters"], capi.fp),
                       opt(a["vertex_normals"], capi.fp) if has_attr else None, opt(a["vertex_uvs"], capi.fp) if has_attr else None,
-                      opt(flags, capi.ip) if has_attr else None, len(tex), tdesc if tex else None)
+                      opt(flags, capi.ip) if has_attr else None, len(tex), tdesc if tex else None,
+                      len(a.get("spheres", ())), opt(a["spheres"], capi.fp) if len(a.get("spheres", ())) else None)
         h = C.c_void_p()
         capi.check(capi.lib.lrt_scene_create(C.byref(d), C.byref(h)))
         if self.handle:
@@ -605,13 +611,13 @@ def render(scene: Scene, params=None, sensor=0, integrator=None, seed=0, seed_gr
     if storage is None:
         storage = torch.zeros((s.film.crop_h, s.film.crop_w, 4), dtype=torch.float32, device="cuda")
     if rng_mode == 1:
-        rp = RenderParams(int(seed) & 0xffffffff, spp, it.max_depth, it.rr_depth, 0, 1, 0, 1, 0, s.sampler.base_seed & 0xffffffff)
+        rp = RenderParams(int(seed) & 0xffffffff, spp, it.max_depth, it.rr_depth, 0, 1, 0, 1, 0, s.sampler.base_seed & 0xffffffff, int(it.hide_emitters))
         if tuple(shard) != (0, 1):
             raise ValueError("rng_mode=1 (scalar sampler convention) is a single-GPU parity mode")
         capi.check(capi.lib.lrt_render(scene.handle, s.handle, C.byref(fd), C.byref(rp), capi.dev_ptr(storage), capi.stream_ptr()))
     else:
         for pseed, pspp in render_passes(s.film.crop_w * s.film.crop_h, spp, s.sampler.base_seed + int(seed), wavefront_limit):
-            rp = RenderParams(pseed, pspp, it.max_depth, it.rr_depth, shard[0], shard[1], 0, 0, 0, 0)
+            rp = RenderParams(pseed, pspp, it.max_depth, it.rr_depth, shard[0], shard[1], 0, 0, 0, 0, int(it.hide_emitters))
             capi.check(capi.lib.lrt_render(scene.handle, s.handle, C.byref(fd), C.byref(rp), capi.dev_ptr(storage), capi.stream_ptr()))
     return develop_rgb(storage) if develop else storage
 
@@ -629,7 +635,7 @@ def render_backward(scene: Scene, grad_storage, sensor=0, integrator=None, seed=
     ge = torch.zeros((max(len(scene.arrays["emitters"]), 1), 16), dtype=torch.float32, device="cuda")
     gs = grad_storage.contiguous()
     for pseed, pspp in render_passes(s.film.crop_w * s.film.crop_h, spp, s.sampler.base_seed + int(seed), wavefront_limit):
-        rp = RenderParams(pseed, pspp, it.max_depth, it.rr_depth, shard[0], shard[1], 0, 0, 0, 0)
+        rp = RenderParams(pseed, pspp, it.max_depth, it.rr_depth, shard[0], shard[1], 0, 0, 0, 0, int(it.hide_emitters))
         capi.check(capi.lib.lrt_render_backward(scene.handle, s.handle, C.byref(fd), C.byref(rp), capi.dev_ptr(gs),
                                                 capi.dev_ptr(gb), capi.dev_ptr(ge), capi.stream_ptr()))
     return gb[:len(scene.arrays["bsdfs"])], ge[:len(scene.arrays["emitters"])]
@@ -909,8 +915,7 @@ def load_dict(d: dict):
     if t in ("gaussian", "tent", "box"):
         return ReconstructionFilter(t, float(d.get("stddev", d.get("radius", 0.0))) if t != "box" else 0.0)
     if t in ("path", "prb"):
-        # hide_emitters only removes an environment emitter from directly visible pixels (path.cpp:113-114); this build has no
-        # environment emitter, so the flag has nothing to act on — as in the reference for such scenes
+        # hide_emitters: with an environment emitter, camera rays that escape yield no valid sample (path.cpp:113-114)
         return (PRBIntegrator if t == "prb" else PathIntegrator)(d.get("max_depth", -1), d.get("rr_depth", 5), d.get("hide_emitters", False))
     if t != "scene":
         raise ValueError(f"plugin '{t}' is outside the hot path of this build")

@@ -28,10 +28,14 @@ def oracle_jit_render(mi, sc, d, spp, seed):
     if sd["type"] == "realisticlens":
         cam = orc_camera(ld.design(sd["lens_design"], {"object_distance": sd.get("object_distance", 6.0)}), film, to_world=tw,
                          near=sd.get("near_clip", 1e-2), far=sd.get("far_clip", 1e4), object_distance=sd.get("object_distance", 6.0))
+        sot = sd.get("shutter_close", sd.get("shutter_open", 0.0)) - sd.get("shutter_open", 0.0)
         if sd.get("sample_exit_pupil"):
-            lut = cam_exit_pupil(oracle(), "orc", cam, shutter_open_time=sd.get("shutter_close", 0.0) - sd.get("shutter_open", 0.0))
+            lut = cam_exit_pupil(oracle(), "orc", cam, shutter_open_time=sot)
             assert (bits(sc.sensors()[0].exit_pupil_bounds()) == bits(lut)).all()
-    st, miss = orc_render(orc_scene(sc.arrays), film, spp, seed=seed, max_depth=integ.get("max_depth", -1), rr_depth=integ.get("rr_depth", 5),
+        elif sot != 0.0:     # an open shutter alone makes render_sample draw a time sample (integrator.cpp:442-444)
+            oracle().orc_cam_set_exit_pupil(cam, C.c_int(0), C.c_float(sot))
+    integ = integ or {}
+    st, miss = orc_render(orc_scene(sc.arrays, hide_emitters=integ.get("hide_emitters", False)), film, spp, seed=seed, max_depth=integ.get("max_depth", -1), rr_depth=integ.get("rr_depth", 5),
                           cam_h=cam, fov=x_fov(sd, film.width, film.height), to_world=tw, near=sd.get("near_clip", 1e-2),
                           far=sd.get("far_clip", 1e4), filter_kind=FK[fd.get("rfilter", {"type": "gaussian"})["type"]])
     return develop(st), miss
