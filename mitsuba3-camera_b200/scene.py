@@ -566,6 +566,19 @@ def tea32(v0, v1, rounds=4):
     return v0, v1
 
 
+def reference_block_size(width, height, n_threads, block_size=0):
+    """The block size the reference's scalar render loop settles on (src/render/integrator.cpp:171-183): the integrator's
+    `block_size` if set, else MI_BLOCK_SIZE = 32 halved until there is a block for every worker thread. Per-pixel sampler seeds
+    depend on it (block id x block_size^2 + Morton index), so a sample-for-sample comparison of a SMALL image with the reference
+    (rng_mode=1) has to pass the value the reference used: render(..., rng_mode=1, block_size=reference_block_size(w, h, threads))."""
+    if block_size:
+        return int(block_size)
+    bs = 32
+    while not (bs == 1 or ((width + bs - 1) // bs) * ((height + bs - 1) // bs) >= n_threads):
+        bs //= 2
+    return bs
+
+
 def render_passes(n_pixels, spp, seed, wavefront_limit=WAVEFRONT_LIMIT):
     """[(pass seed, pass spp)] of one render: SamplingIntegrator::render splits W*H*spp > 2^32 - 1 samples into equal passes
     (src/render/integrator.cpp:247-265: spp_per_pass = spp / ceil(wavefront / limit)). The reference keeps the 2^32 sampler
@@ -587,7 +600,7 @@ def render_passes(n_pixels, spp, seed, wavefront_limit=WAVEFRONT_LIMIT):
 
 
 def render(scene: Scene, params=None, sensor=0, integrator=None, seed=0, seed_grad=0, spp=0, spp_grad=0, develop=True,
-           shard=(0, 1), storage=None, rng_mode=0, wavefront_limit=WAVEFRONT_LIMIT):
+           shard=(0, 1), storage=None, rng_mode=0, wavefront_limit=WAVEFRONT_LIMIT, block_size=0):
     """mi.render (src/python/python/util.py:410-525), forward part: returns the developed [H,W,3] image as a
     torch CUDA tensor (or the raw R,G,B,W storage with develop=False). rng_mode=1 selects the scalar variants' sampler
     convention (lensrt.h). Renders of more than 2^32 - 1 samples run as several passes (render_passes)."""
@@ -611,7 +624,8 @@ def render(scene: Scene, params=None, sensor=0, integrator=None, seed=0, seed_gr
     if storage is None:
         storage = torch.zeros((s.film.crop_h, s.film.crop_w, 4), dtype=torch.float32, device="cuda")
     if rng_mode == 1:
-        rp = RenderParams(int(seed) & 0xffffffff, spp, it.max_depth, it.rr_depth, 0, 1, 0, 1, 0, s.sampler.base_seed & 0xffffffff, int(it.hide_emitters))
+        rp = RenderParams(int(seed) & 0xffffffff, spp, it.max_depth, it.rr_depth, 0, 1, 0, 1, int(block_size), s.sampler.base_seed & 0xffffffff,
+                          int(it.hide_emitters))
         if tuple(shard) != (0, 1):
             raise ValueError("rng_mode=1 (scalar sampler convention) is a single-GPU parity mode")
         capi.check(capi.lib.lrt_render(scene.handle, s.handle, C.byref(fd), C.byref(rp), capi.dev_ptr(storage), capi.stream_ptr()))
@@ -761,10 +775,20 @@ def _sensor_from(d):
     smp = d.pop("sampler", {"type": "independent"})
     sampler = IndependentSampler(smp.get("sample_count", 4), smp.get("seed", 0))
     d.pop("focus_distance", None)
+    d.pop("id", None) if t == "perspective" else None
     if t == "perspective":
         s = PerspectiveCamera(film, fov=d.get("fov", 45.0), to_world=d.get("to_world"), near_clip=d.get("near_clip", 1e-2),
                               far_clip=d.get("far_clip", 1e4), fov_axis=d.get("fov_axis", "x"))
     elif t == "realisticlens":
+        # the properties the plugin and its bases query (realisticlens.cpp:844-878, sensor.cpp, endpoint.cpp); anything else is
+        # the reference's "unreferenced properties" error (xml.cpp:1100, e.g. `fov` on a realistic lens)
+        known = {"id", "to_world", "near_clip", "far_clip", "lens_design", "object_distance", "lens_focal_length", "lens_diameter", "stop_ratio",
+                 "ap_size", "ap_offset", "sample_exit_pupil", "shutter_open", "shutter_close", "pupil_render_pos", "pupil_render_wv", "srf",
+                 "prescription"}
+        extra = sorted(k for k in d if k not in known and not isinstance(d[k], dict))
+        if extra:
+            raise ValueError(f"unreferenced properties {extra} in sensor plugin of type \"realisticlens\"")
+        d.pop("id", None)
         tw = d.pop("to_world", None)
         nc = d.pop("near_clip", 1e-2)
         fc = d.pop("far_clip", 1e4)

@@ -539,6 +539,7 @@ static V3 path_sample(const Scene &s, PCG32 &rng, Ray ray, int max_depth, int rr
     valid_ray = false;
     V3 prev_p { 0, 0, 0 }; float prev_bsdf_pdf = 1.f; bool prev_bsdf_delta = true;
     if (max_depth == 0) return result;
+    if (max_depth < 0) max_depth = 0x7fffffff;         // -1 = unbounded (integrator.cpp:765-790)
     valid_ray = !s.hide_emitters && s.env >= 0;        // path.cpp:113-114
     bool active = true;
     while (active) {
