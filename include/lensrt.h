@@ -262,6 +262,16 @@ int lrt_render_backward(const lrt_scene *scene, const lrt_sensor *sensor, const 
 /* mi.render(scene) for host callers: render + HDRFilm::develop; rgb_out [size_y,size_x,3] host memory. */
 int lrt_render_host(const lrt_scene *scene, const lrt_sensor *sensor, const lrt_film_desc *film,
                     const lrt_render_params *params, float *rgb_out);
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid allocation). lrt_render_host without any allocation:
+ * render (rng_mode 0) + HDRFilm::develop with the R,G,B,W accumulator in a fixed 4 MiB device array inside the library, so the
+ * film may have at most lrt_render_rgb_noalloc_max_pixels() = 2^18 pixels (e.g. 512 x 512), border 0, 4 channels; larger films
+ * are refused with LRT_EINVAL. rgb_out_dev [size_y, size_x, 3] is DEVICE memory owned by the caller; asynchronous on `stream`.
+ * Calls no cudaMalloc / cudaFree. The sensor must have been used once before (its first use allocates its device table), else
+ * LRT_EINVAL. All calls share the one array (cleared at the start of each call): calls that overlap on the GPU race. */
+int lrt_render_rgb_noalloc(const lrt_scene *scene, const lrt_sensor *sensor, const lrt_film_desc *film,
+                           const lrt_render_params *params, float *rgb_out_dev, void *stream);
+int64_t lrt_render_rgb_noalloc_max_pixels(void);
 /* counters of the last render on this scene: samples, lens misses, rays traced, path-loop iterations,
  * BVH nodes fetched (80 B each), triangles tested (48 B each), traversal-stack clamp events (must be 0: a clamped stack
  * may miss the closest hit) */
