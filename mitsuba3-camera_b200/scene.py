@@ -327,7 +327,7 @@ class SceneData:
         self.bsdf_rows, self.bsdf_names, self.emitter_rows = [], [], []
         self.normals, self.uvs, self.shape_flags, self.textures = [], [], [], []
         self.rectangles = []      # (shape id, to_world 4x4) of `rectangle` shapes (the oracle can intersect them analytically)
-        self.spheres = []         # analytic `sphere` shapes: (shape id, centre, radius, flip_normals, to_world 4x4)
+        self.spheres = []         # analytic `sphere` shapes: (shape id, centre, radius, flip_normals, to_world 4x4, to_object 4x4)
         self._nv = 0
 
     def add_environment(self, radiance):
@@ -343,7 +343,7 @@ class SceneData:
         m = to_world.matrix
         col = m[:3, 0]
         radius = np.sqrt(f32(f32(col[0] * col[0]) + f32(col[1] * col[1])) + f32(col[2] * col[2]), dtype=f32)
-        self.spheres.append((sid, m[:3, 3].copy(), f32(radius), bool(flip_normals), m.copy()))
+        self.spheres.append((sid, m[:3, 3].copy(), f32(radius), bool(flip_normals), m.copy(), to_world.inverse_matrix.copy()))
         return sid
 
     def add_bsdf(self, name, row):
@@ -374,7 +374,7 @@ class SceneData:
         for v in self.vertices:
             if len(v):
                 lo, hi = np.minimum(lo, v.min(0)), np.maximum(hi, v.max(0))
-        for _, c, r, _, _ in self.spheres:
+        for _, c, r, _, _, _ in self.spheres:
             lo, hi = np.minimum(lo, (c - r).astype(f32)), np.maximum(hi, (c + r).astype(f32))
         if not np.all(lo <= hi):
             return np.zeros(3, f32), f32(1)
@@ -390,10 +390,10 @@ class SceneData:
             if row[13] == 2:
                 row[4:7], row[7] = self.bounding_sphere()
         sph = np.zeros((len(self.spheres), 32), f32)
-        for i, (sid, c, r, flip, m) in enumerate(self.spheres):
+        for i, (sid, c, r, flip, m, minv) in enumerate(self.spheres):
             sph[i, 0:3], sph[i, 3], sph[i, 4], sph[i, 5] = c, r, sid, float(flip)
             sph[i, 8:20] = m[:3].reshape(-1)
-            sph[i, 20:32] = np.linalg.inv(m.astype(np.float64))[:3].astype(f32).reshape(-1)
+            sph[i, 20:32] = minv[:3].reshape(-1)      # m_to_object = m_to_world.inverse(): the transform's own float32 inverse
         return dict(spheres=sph, vertices=cat(self.vertices, f32, (0, 3)), indices=cat(self.indices, np.int32, (0, 3)),
                     tri_shape=cat(self.tri_shape, np.int32, (0,)),
                     shape_bsdf=np.array(self.shape_bsdf, np.int32), shape_emitter=np.array(self.shape_emitter, np.int32),
@@ -403,7 +403,9 @@ class SceneData:
                     shape_flags=np.array(self.shape_flags, np.int32), textures=list(self.textures),
                     rect_shapes=np.array([r[0] for r in self.rectangles], np.int32),
                     rect_to_world=np.ascontiguousarray(np.stack([r[1] for r in self.rectangles]) if self.rectangles
-                                                       else np.zeros((0, 4, 4), f32), f32))
+                                                       else np.zeros((0, 4, 4), f32), f32),
+                    rect_to_object=np.ascontiguousarray(np.stack([r[2] for r in self.rectangles]) if self.rectangles
+                                                        else np.zeros((0, 4, 4), f32), f32))
 
 
 # ------------------------------------------------------------------------------------------------ objects
@@ -848,7 +850,7 @@ def scene_data_from_dict(d: dict):
         name = v.get("id", key)
         if vt in ("perspective", "realisticlens"):
             sensor_dicts.append(v)
-        elif vt in ("path", "prb"):
+        elif vt in ("path", "prb", "ptracer"):
             integ = v
         elif vt == "constant":
             rad = v.get("radiance")
@@ -876,7 +878,10 @@ def scene_data_from_dict(d: dict):
                 if em is not None:
                     raise ValueError("area emitters on `sphere` shapes are outside the hot path of this build (use a mesh)")
                 if "center" in v or "radius" in v:       # sphere.cpp:128-133: to_world * translate(center) * scale(radius)
-                    tw = tw @ Transform4f.translate(np.asarray(v.get("center", [0, 0, 0]), f32)) @ Transform4f.scale(float(v.get("radius", 1.0)))
+                    c32, r32 = np.asarray(v.get("center", [0, 0, 0]), f32), f32(v.get("radius", 1.0))       # float32 operands, float32 products
+                    tr = Transform4f.translate(c32); sc = Transform4f.scale(r32)
+                    sc = Transform4f(sc.matrix, np.diag(np.array([f32(1) / r32] * 3 + [f32(1)], f32)))                   # dr::rcp in float32
+                    tw = tw.matmul32(tr).matmul32(sc)
                 data.add_sphere(name, tw, bid, v.get("flip_normals", False))
                 continue
             if v.get("flip_normals", False) and vt == "rectangle":
@@ -918,7 +923,7 @@ def scene_data_from_dict(d: dict):
                            "kind": 0 if vt == "rectangle" else 1}      # 1: faces sampled by area (Mesh::sample_position)
             sid = data.add_shape(name, verts, faces, bid, emitter, normals, uvs, rectangle=vt == "rectangle")
             if vt == "rectangle":
-                data.rectangles.append((sid, tw.matrix.copy()))
+                data.rectangles.append((sid, tw.matrix.copy(), tw.inverse_matrix.copy()))
         elif vt in _BSDFS or vt is None:
             pass
         else:

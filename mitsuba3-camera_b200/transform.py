@@ -8,17 +8,45 @@ import numpy as np
 f32 = np.float32
 
 
+def mm32(a, b):
+    """4x4 product as Dr.Jit's scalar Matrix * Matrix evaluates it in float32 (ext/drjit/include/drjit/matrix.h:102-117): entry
+    (r, j) = ((a[r,0] b[0,j] + a[r,1] b[1,j]) + a[r,2] b[2,j]) + a[r,3] b[3,j], every product and sum rounded (the reference's
+    portable build does not fuse them)."""
+    a = np.asarray(a, f32); b = np.asarray(b, f32)
+    out = (a[:, 0:1] * b[0:1, :]).astype(f32)
+    for i in range(1, 4):
+        out = ((a[:, i:i + 1] * b[i:i + 1, :]).astype(f32) + out).astype(f32)
+    return out
+
+
 class Transform4f:
-    def __init__(self, matrix=None):
-        self.matrix = np.eye(4, dtype=f32) if matrix is None else np.array(getattr(matrix, "matrix", matrix), dtype=f32).reshape(4, 4)
+    """Carries the matrix AND its inverse, the latter built the way the reference builds it (transform.h:173-282): every
+    constructor knows its exact inverse (translate(-v), scale(1/v), the transpose of a rotation, look_at's analytic inverse)
+    and products multiply both sides. Scene descriptions are assembled in DOUBLE precision — the XML parser and `Properties`
+    work with `Transform<Point<double, 4>>` (src/core/xml.cpp, include/mitsuba/core/properties.h) — and a plugin reads the
+    result rounded once to float32, inverse included: `.matrix` / `.inverse_matrix` are those float32 arrays. A transform made
+    from a bare matrix gets a numerically inverted one."""
+
+    def __init__(self, matrix=None, inverse=None):
+        if isinstance(matrix, Transform4f):
+            matrix, inverse = matrix.m64, (matrix.inv64 if inverse is None else inverse)
+        self.m64 = np.eye(4) if matrix is None else np.array(getattr(matrix, "matrix", matrix), dtype=np.float64).reshape(4, 4)
+        self.inv64 = np.linalg.inv(self.m64) if inverse is None else np.array(inverse, dtype=np.float64).reshape(4, 4)
+        self.matrix = self.m64.astype(f32)
+        self.inverse_matrix = self.inv64.astype(f32)
 
     def __matmul__(self, other):
         if isinstance(other, Transform4f):
-            return Transform4f((self.matrix.astype(np.float64) @ other.matrix.astype(np.float64)).astype(f32))
+            return Transform4f(self.m64 @ other.m64, other.inv64 @ self.inv64)
         v = np.asarray(other, dtype=f32)
         return self.transform_affine(v)
 
     __mul__ = __matmul__
+
+    def matmul32(self, other):
+        """The product as a PLUGIN forms it: ScalarTransform4f operands, float32 arithmetic (e.g. sphere.cpp:128-133
+        `to_world * translate(center) * scale(radius)`), both for the matrix and for the inverse."""
+        return Transform4f(mm32(self.matrix, other.matrix), mm32(other.inverse_matrix, self.inverse_matrix))
 
     def transform_affine(self, p):
         """transform.h:104-111: start from the translation column, then one multiply-add per matrix column in float32 —
@@ -42,7 +70,7 @@ class Transform4f:
         return r.astype(f32)
 
     def inverse(self):
-        return Transform4f(np.linalg.inv(self.matrix.astype(np.float64)).astype(f32))
+        return Transform4f(self.inv64, self.m64)
 
     def has_scale(self):
         m = self.matrix[:3, :3].astype(np.float64)
@@ -55,19 +83,25 @@ class Transform4f:
 
         def __get__(self, obj, cls):
             if obj is None:
-                return lambda *a, **k: Transform4f(self.fn(*a, **k))
-            return lambda *a, **k: obj @ Transform4f(self.fn(*a, **k))
+                return lambda *a, **k: Transform4f(*self.fn(*a, **k))
+            return lambda *a, **k: obj @ Transform4f(*self.fn(*a, **k))
 
+    # each constructor returns (matrix, inverse) as the reference's static constructors do, in double precision
     @staticmethod
     def _translate(v):
-        m = np.eye(4, dtype=np.float64); m[:3, 3] = np.asarray(v, np.float64); return m
+        v = np.asarray(v, np.float64).reshape(3)
+        m = np.eye(4); m[:3, 3] = v
+        inv = np.eye(4); inv[:3, 3] = -v
+        return m, inv
 
     @staticmethod
     def _scale(v):
         v = np.asarray(v, np.float64)
         if v.ndim == 0:
             v = np.repeat(v, 3)
-        m = np.eye(4, dtype=np.float64); m[0, 0], m[1, 1], m[2, 2] = v; return m
+        m = np.eye(4); m[0, 0], m[1, 1], m[2, 2] = v
+        inv = np.eye(4); inv[0, 0], inv[1, 1], inv[2, 2] = 1.0 / v
+        return m, inv
 
     @staticmethod
     def _rotate(axis, angle):
@@ -78,7 +112,7 @@ class Transform4f:
         m[:3, :3] = [[c + x * x * (1 - c), x * y * (1 - c) - z * s, x * z * (1 - c) + y * s],
                      [y * x * (1 - c) + z * s, c + y * y * (1 - c), y * z * (1 - c) - x * s],
                      [z * x * (1 - c) - y * s, z * y * (1 - c) + x * s, c + z * z * (1 - c)]]
-        return m
+        return m, m.T.copy()                       # Transform(matrix, matrix): the inverse transpose IS the matrix
 
     @staticmethod
     def _look_at(origin, target, up):
@@ -88,7 +122,11 @@ class Transform4f:
         new_up = np.cross(d, left)
         m = np.eye(4, dtype=np.float64)
         m[:3, 0], m[:3, 1], m[:3, 2], m[:3, 3] = left, new_up, d, o
-        return m
+        # transform.h:272-279: inverse = transpose(rotation), its translation = inverse * (-origin, 1)
+        inv = np.eye(4); inv[:3, :3] = m[:3, :3].T
+        no = -o
+        inv[:3, 3] = (inv[:3, 0] * no[0] + inv[:3, 1] * no[1]) + inv[:3, 2] * no[2]      # Matrix * Vector: column by column
+        return m, inv
 
     translate = _Chain(_translate.__func__)
     scale = _Chain(_scale.__func__)

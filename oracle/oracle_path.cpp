@@ -969,3 +969,5 @@ void orc_render_scalar(void *scene_h, void *cam_h, float fov, const float *to_wo
     if (n_lens_miss) *n_lens_miss = miss;
 }
 }
+
+#include "oracle_ptracer_impl.h"   // the particle tracer (uses the static helpers above)

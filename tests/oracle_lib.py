@@ -191,7 +191,7 @@ def orc_scene(a, analytic_rectangles=False, hide_emitters=False):
         C.c_int(len(tex)), ip(dims), fp(tdata), fp(tuv)))
     if analytic_rectangles and len(keep.get("rect_shapes", [])):
         tw = keep["rect_to_world"].astype(f32)
-        inv = np.stack([np.linalg.inv(m.astype(np.float64)) for m in tw]).astype(f32)
+        inv = keep["rect_to_object"].astype(f32) if "rect_to_object" in keep else np.stack([np.linalg.inv(m.astype(np.float64)) for m in tw]).astype(f32)
         L.orc_scene_set_rectangles(h, C.c_int(len(tw)), ip(keep["rect_shapes"]), fp(np.ascontiguousarray(tw[:, :3, :].reshape(-1))),
                                    fp(np.ascontiguousarray(inv[:, :3, :].reshape(-1))))
     sph = keep.get("spheres")
@@ -292,3 +292,20 @@ def orc_spot_grad(rows, f2s, normalization, near, far, film: FilmSpec, src_p, in
                           dl.ctypes.data_as(C.POINTER(C.c_double)) if dl is not None else None,
                           out.ctypes.data_as(C.POINTER(C.c_double)))
     return phi, out
+
+
+# ------------------------------------------------------------------------------------------------ particle tracer
+def orc_ptracer_render(scene_h, cam_h, film, spp, to_world, to_camera=None, seed=0, base_seed=0, max_depth=-1, rr_depth=5, hide_emitters=False,
+                       shutter_open_time=0.0, filter_kind=2, filter_param=0.0, scalar=True, n_threads=8):
+    """AdjointIntegrator::render + ParticleTracerIntegrator (oracle_ptracer_impl.h). Returns storage float64 [ch, cw, 4];
+    the image is its RGB channels (particle-tracer films are not divided by a weight)."""
+    L = oracle()
+    cw, ch, cx, cy = (int(v) for v in film.crop)
+    st = np.zeros((ch, cw, 4), np.float64)
+    tw = np.ascontiguousarray(to_world, f32)
+    tc = None if to_camera is None else np.ascontiguousarray(to_camera, f32)
+    L.orc_ptracer_render(scene_h, cam_h, fp(tw), None if tc is None else fp(tc), C.c_int(film.width), C.c_int(film.height), C.c_int(cw), C.c_int(ch), C.c_int(cx), C.c_int(cy),
+                         C.c_int(filter_kind), c_f(filter_param), C.c_uint32(base_seed), C.c_uint32(seed), C.c_int(spp), C.c_int(max_depth),
+                         C.c_int(rr_depth), C.c_int(int(hide_emitters)), c_f(shutter_open_time), C.c_int(int(scalar)), C.c_int(n_threads),
+                         st.ctypes.data_as(C.POINTER(C.c_double)))
+    return st

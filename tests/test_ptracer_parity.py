@@ -1,0 +1,63 @@
+"""The particle tracer (`ptracer`, src/integrators/ptracer.cpp: visible emitters, emitter rays, scene bounces, connect_sensor
+through RealisticLensCamera::sample_direction, normalised splat) — the oracle's restatement (oracle/oracle_ptracer_impl.h) against
+images the reference's own scalar_rgb build rendered from the same XML files (tests/golden/ref_ptracer.npz, written by
+tests/golden/gen_ref_ptracer.py): sample for sample in the scalar AdjointIntegrator's seeding convention."""
+import os
+
+import numpy as np
+import pytest
+
+from oracle_lib import *  # noqa
+from test_ref_parity import FK
+
+ld = load_lens_designs()
+HERE = os.path.dirname(os.path.abspath(__file__))
+XML = os.path.join(HERE, "golden", "assets", "xml")
+CASES = [("lens_room", {}), ("lens_room", {"max_depth": "2", "lens": "gauss"}), ("lens_room", {"max_depth": "-1", "spp": "4"}),
+         ("charts", {"integrator": "ptracer"}), ("charts", {"integrator": "ptracer", "hide": "true", "spp": "4"}), ("lens_studio", {})]
+
+
+def case_key(name, kw, what="image"):
+    return name + "".join(f"@{k}={v}" for k, v in sorted(kw.items())) + "/" + what
+
+
+@pytest.fixture(scope="module")
+def P():
+    return np.load(os.path.join(HERE, "golden", "ref_ptracer.npz"))
+
+
+def oracle_ptracer(mi, d, seed, n_threads, scalar=True, spp=None):
+    data, sds, integ = mi.scene_data_from_dict(d)
+    sd = sds[0]; fd = sd["film"]
+    assert sd["type"] == "realisticlens" and integ["type"] == "ptracer"
+    film = FilmSpec(fd["width"], fd["height"], None, fd.get("diagonal", 35.0))
+    tw = sd["to_world"].matrix
+    od = sd.get("object_distance", 6.0)
+    cam = orc_camera(ld.design(sd.get("lens_design", "singlet"), {"object_distance": od}), film, to_world=tw, near=sd.get("near_clip", 1e-2),
+                     far=sd.get("far_clip", 1e4), object_distance=od)
+    sot = sd.get("shutter_close", sd.get("shutter_open", 0.0)) - sd.get("shutter_open", 0.0)
+    h = orc_scene(data.arrays(), analytic_rectangles=True)
+    rf = fd.get("rfilter", {"type": "gaussian"})
+    st = orc_ptracer_render(h, cam, film, spp or sd["sampler"]["sample_count"], tw, sd["to_world"].inverse_matrix, seed=seed, base_seed=sd["sampler"].get("seed", 0),
+                            max_depth=integ.get("max_depth", -1), rr_depth=integ.get("rr_depth", 5), hide_emitters=integ.get("hide_emitters", False),
+                            shutter_open_time=sot, filter_kind=FK[rf["type"]], scalar=scalar, n_threads=n_threads)
+    return st[..., :3].astype(f32)
+
+
+@pytest.mark.parametrize("name,kw", CASES)
+def test_ptracer_oracle_vs_reference_images(mi, P, name, kw):
+    d = mi.xml_to_dict(path=os.path.join(XML, name + ".xml"), **kw)
+    img = oracle_ptracer(mi, d, 0, int(P["n_threads"]))
+    ref = P[case_key(name, kw)]
+    assert img.shape == ref.shape
+    err = rel_rmse(img, ref)
+    close = np.abs(img - ref).max(-1) <= 1e-4 * np.maximum(ref.max(-1), 1e-3)
+    print(f"{name} {kw}: rel-RMSE {err:.3e}, pixels within 1e-4: {close.mean():.4f}")
+    assert err <= 2e-4
+    assert close.mean() >= 0.99
+
+
+def test_ptracer_oracle_other_seed(mi, P):
+    d = mi.xml_to_dict(path=os.path.join(XML, "lens_room.xml"))
+    img = oracle_ptracer(mi, d, 3, int(P["n_threads"]))
+    assert rel_rmse(img, P[case_key("lens_room", {}, "image_seed3")]) <= 2e-4
