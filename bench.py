@@ -426,6 +426,34 @@ def main():
     ms_bwd = torch.tensor([eb[0].elapsed_time(eb[1]) / max(a.steps // 2, 1)], device="cuda", dtype=torch.float64)
     if world > 1:
         dist.all_reduce(ms_bwd, op=dist.ReduceOp.MAX)
+    # particle tracer (8f-1) on the SAME scene through the same lens: light paths per second at a 1024 x 576 film, 4 spp
+    ptr = None
+    if not a.no_lens_grad:
+        try:
+            sens0 = scene.sensors()[0]
+            pfilm = mi.Film(1024, 576, diagonal=sens0.film.diagonal, rfilter="tent")
+            psens = mi.RealisticLensCamera(pfilm, sens0.lens_design, to_world=mi.Transform4f(sens0.to_world), near_clip=sens0.near_clip,
+                                           far_clip=sens0.far_clip, **sens0.props)
+            psens.sampler = mi.IndependentSampler(4, 0)
+            pit = mi.PTracerIntegrator(a.max_depth if hasattr(a, "max_depth") else 6, 5, False)
+            pit.render(scene, sensor=psens, seed=1, spp=4, shard=(rank, world)); torch.cuda.synchronize()
+            ep = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+            ep[0].record()
+            n_pt = max(a.steps, 3)
+            for i in range(n_pt):
+                pit.render(scene, sensor=psens, seed=10 + i, spp=4, shard=(rank, world))
+            ep[1].record(); torch.cuda.synchronize()
+            ms_pt = torch.tensor([ep[0].elapsed_time(ep[1]) / n_pt], device="cuda", dtype=torch.float64)
+            if world > 1:
+                dist.all_reduce(ms_pt, op=dist.ReduceOp.MAX)
+            pst = scene.stats()
+            ptr = {"value": 1024 * 576 * 4 / (ms_pt.item() * 1e-3) / 1e6, "unit": "M light paths/s", "ms_per_render": ms_pt.item(),
+                   "film": [1024, 576], "spp": 4, "connections_per_path": pst["lens_misses"] / max(pst["samples"], 1),
+                   "rays_per_path": pst["rays"] / max(pst["samples"], 1),
+                   "what": "lrt_ptrace on the headline scene and lens: visible emitters + emitter rays + scene bounces, every vertex "
+                           "connected to the lens (sample_direction) and splatted (normalised, atomics); per-rank counters"}
+        except Exception as e:     # the extra measurement must never take the headline line down
+            ptr = {"error": str(e)[:200]}
     lens_grad = None if a.no_lens_grad else lens_grad_section(mi, torch, dist, a, rank, world)
     pupil = None
     if rank == 0 and not a.no_lens_grad:   # exit-pupil LUT of the workload's lens: 64 x 2^20 lens traces in one kernel
@@ -510,6 +538,8 @@ def main():
         line["render_backward"] = {"value": paths_per_step / (ms_bwd.item() * 1e-3) / 1e6, "unit": "Mpaths/s", "ms_per_step": ms_bwd.item(),
                                    "what": "lrt_render_backward on the same workload: gradients of diffuse reflectance / conductor "
                                            "specular reflectance / area-light radiance (one-pass PRB)"}
+        if ptr is not None:
+            line["ptracer"] = ptr
         if lens_grad is not None:
             line["lens_grad"] = lens_grad
         if pupil is not None:

@@ -262,6 +262,34 @@ int lrt_render_backward(const lrt_scene *scene, const lrt_sensor *sensor, const 
 /* mi.render(scene) for host callers: render + HDRFilm::develop; rgb_out [size_y,size_x,3] host memory. */
 int lrt_render_host(const lrt_scene *scene, const lrt_sensor *sensor, const lrt_film_desc *film,
                     const lrt_render_params *params, float *rgb_out);
+/* ------------------------------------------------------------------------------------------- particle tracer
+ * ParticleTracerIntegrator (src/integrators/ptracer.cpp:77-371) under AdjointIntegrator::render (src/render/integrator.cpp:
+ * 544-760): every sample connects a point on an emitter to the sensor (sample_visible_emitters), then shoots a light path from
+ * an emitter (Scene::sample_emitter_ray) and connects each of its vertices to the sensor through Sensor::sample_direction
+ * (realistic lens: src/sensors/realisticlens.cpp:2301-2394) — the integrator the fork's lens-design notebooks render with. */
+typedef struct lrt_ptrace_params {
+    uint32_t seed;
+    int32_t spp;              /* samples = film width * height * spp (the FULL film size, integrator.cpp:573-574) */
+    int32_t max_depth;        /* -1 = unbounded */
+    int32_t rr_depth;         /* default 5 */
+    int32_t hide_emitters;    /* skip the directly visible emitters (ptracer.cpp:80-81) */
+    int32_t shard_index, shard_count;   /* rng_mode 0: sample idx = shard_index + k * shard_count (multi-GPU) */
+    /* 0: one PCG32 stream per sample, (v0, v1) = tea(seed, idx) — the JIT variants' convention, the fast path.
+     * 1: the scalar variants' convention (integrator.cpp:600-640): ranges of max(total / (4 n_threads), 1) samples, range k drawn
+     *    from ONE stream seeded with base_seed + seed * (total / grain) + k, discretised filter: images comparable sample for
+     *    sample with a scalar_rgb build of the reference running n_threads threads. Single GPU, one thread per range. */
+    int32_t rng_mode;
+    int32_t n_threads;        /* rng_mode 1 */
+    uint32_t base_seed;       /* the sampler's `seed` property */
+    float to_camera[12];      /* rows of the inverse of the sensor's to_world as the scene description carries it (Transform4f keeps
+                                 an inverse next to every matrix); all zero = invert to_world numerically */
+} lrt_ptrace_params;
+/* Accumulates R,G,B into accum_dev [size_y, size_x, 4] (caller zeroes it; the weight channel stays 0: the image is the RGB
+ * channels as they are). film: channels 4, normalize 1, coalesce 0 (integrator.cpp:706-717), border 0. Asynchronous on `stream`.
+ * lrt_render_stats afterwards: [0] light paths, [1] connections splatted, [2] rays traced. */
+int lrt_ptrace(const lrt_scene *scene, const lrt_sensor *sensor, const lrt_film_desc *film, const lrt_ptrace_params *params,
+               float *accum_dev, void *stream);
+
 /* No counterpart in the reference: added for callers that cannot call cudaMalloc (code
  * under CUDA graph capture, tight serving loops, harnesses that forbid allocation). lrt_render_host without any allocation:
  * render (rng_mode 0) + HDRFilm::develop with the R,G,B,W accumulator in a fixed 4 MiB device array inside the library, so the

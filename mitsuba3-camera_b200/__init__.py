@@ -8,7 +8,7 @@ from .sensors import Film, Sensor, RealisticLensCamera, PerspectiveCamera
 
 __version__ = "0.1.0"
 from .transform import Transform4f, ScalarTransform4f
-from .scene import (Scene, SceneData, PathIntegrator, PRBIntegrator, IndependentSampler, load_dict, render, cornell_box, bsdf_row,
+from .scene import (Scene, SceneData, PathIntegrator, PRBIntegrator, PTracerIntegrator, PtraceParams, IndependentSampler, load_dict, render, cornell_box, bsdf_row,
                     film_desc, RenderParams, SceneDesc, load_obj, load_ply, scene_data_from_dict, render_backward, traverse,
                     SceneParameters)
 from . import scene, workloads, lens_design, parallel, imageio, ad, mesh_lens

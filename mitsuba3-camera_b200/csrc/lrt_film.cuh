@@ -74,7 +74,10 @@ template <bool kDisc = false> LRT_HD bool film_footprint(const FilmParams &F, fl
             for (int i = 0; i < F.count_max; ++i) { fp.wx[i] = filter_eval(F, rx); fp.wy[i] = filter_eval(F, ry); rx += 1.f; ry += 1.f; }
         if (F.normalize) {
             float a = 0.f, b = 0.f, r2x = ceilf(p0x) - pfx, r2y = ceilf(p0y) - pfy;
-            for (int i = 0; i < F.count_max; ++i) { a += filter_eval(F, r2x); b += filter_eval(F, r2y); r2x += 1.f; r2y += 1.f; }
+            for (int i = 0; i < F.count_max; ++i) {     // (scalar variants normalise with the discretised weights, imageblock.cpp:322-331)
+                a += kDisc ? filter_eval_discretized(F, r2x) : filter_eval(F, r2x); b += kDisc ? filter_eval_discretized(F, r2y) : filter_eval(F, r2y);
+                r2x += 1.f; r2y += 1.f;
+            }
             float f = a * b; f = f != 0.f ? 1.f / f : 0.f;
             for (int i = 0; i < F.count_max; ++i) fp.wx[i] *= f;
         }

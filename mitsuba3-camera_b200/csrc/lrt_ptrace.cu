@@ -1,0 +1,379 @@
+// lensrt — the particle tracer: light paths from the emitters, connected to the realistic lens at every vertex.
+// Replaces ParticleTracerIntegrator (src/integrators/ptracer.cpp:77-371: sample, sample_visible_emitters, prepare_ray,
+// trace_light_ray, connect_sensor) under AdjointIntegrator::render (src/render/integrator.cpp:544-760), with
+// Scene::sample_emitter / sample_emitter_ray (src/render/scene.cpp:227-296), AreaLight::sample_ray / sample_position
+// (src/emitters/area.cpp:92-115,210-245), ConstantBackgroundEmitter::sample_ray (src/emitters/constant.cpp:93-111),
+// RealisticLensCamera::sample_direction (src/sensors/realisticlens.cpp:2301-2394) in world space and the normalised,
+// non-coalesced ImageBlock::put (src/render/imageblock.cpp:264-379) with weight 0: the image is the R,G,B channels of the
+// accumulator as they are (particle-tracer films are not divided by a weight).
+//
+// One thread walks one light path (rng_mode 0: one PCG32 stream per sample, the JIT variants' convention) and splats every
+// connection with global float atomics; rng_mode 1 is the SCALAR AdjointIntegrator's convention — the samples are cut into ranges
+// of max(total / (4 n_threads), 1), range k is ONE stream seeded with seed * (total / grain) + k, one thread per range — a parity
+// mode whose images can be compared with a scalar_rgb build of the reference (n_threads = that build's thread count).
+// Draw order follows the reference as GCC compiles it: bsdf->sample(ctx, si, next_1d(), next_2d()) draws the 2D sample first
+// (function arguments are evaluated right to left), and a masked draw of an inactive lane does not advance the generator.
+#include "lrt_internal.h"
+#include "lrt_rng.cuh"
+#include "lrt_shade.cuh"
+#include "lrt_scene.h"
+
+namespace lrt {
+
+struct PtArgs {
+    SceneView sc;
+    const LensSystem *lens;
+    FilmParams film;
+    float to_world[12], to_camera[12];     // rows of the sensor's to_world and of its inverse
+    uint32_t seed; int scalar;
+    long long n_total, grain, n_ranges;    // scalar convention: ranges of `grain` samples
+    int shard_index, shard_count;
+    int max_depth, rr_depth, hide_emitters, shutter_open;
+    float sample_scale;
+    float *accum;
+    unsigned long long *stats;             // [0] light paths, [1] connections splatted, [2] rays traced
+};
+
+struct PtVertex {
+    float3 p, n, s, t, sn, wi; float2 uv; int shape;   // shape -1: not on a surface (environment)
+    LRT_D float3 to_local(float3 v) const { return make_float3(dot(v, s), dot(v, t), dot(v, sn)); }
+    LRT_D float3 to_world(float3 v) const { return s * v.x + t * v.y + sn * v.z; }
+};
+
+struct SensorDS { bool valid; float u, v; float3 p, d; float dist, pdf, weight; };
+
+// Transform4f::transform_affine (transform.h:104-111): translation column first, then one multiply-add per column, strict
+LRT_D float3 xf_point_strict(const float *M, float3 p) {
+    using strict::fmadd;
+    float x = M[3], y = M[7], z = M[11];
+    x = fmadd(M[0], p.x, x); y = fmadd(M[4], p.x, y); z = fmadd(M[8], p.x, z);
+    x = fmadd(M[1], p.y, x); y = fmadd(M[5], p.y, y); z = fmadd(M[9], p.y, z);
+    x = fmadd(M[2], p.z, x); y = fmadd(M[6], p.z, y); z = fmadd(M[10], p.z, z);
+    return make_float3(x, y, z);
+}
+
+// Sensor::sample_direction, world space in and out (the camera-space part is lens_sample_direction, lrt_lens.cuh)
+LRT_D SensorDS sensor_sample_direction(const PtArgs &A, const LensSystem &L, float3 p_world, float a, float b) {
+    SensorDS r; r.valid = false; r.u = r.v = 0.f; r.p = r.d = make_float3(0, 0, 0); r.dist = r.pdf = r.weight = 0.f;
+    const float3 ref = xf_point_strict(A.to_camera, p_world);
+    const DirectionSample ds = lens_sample_direction(L, L.ifs, strict::v3(ref.x, ref.y, ref.z), a, b);
+    if (!ds.valid) return r;
+    r.valid = true; r.u = ds.uv_x; r.v = ds.uv_y;
+    r.p = xf_point_strict(A.to_world, make_float3(ds.p.x, ds.p.y, ds.p.z));
+    r.dist = ds.dist;
+    const float inv = strict::rcp(ds.dist);
+    r.d = make_float3(strict::mul(strict::sub(r.p.x, p_world.x), inv), strict::mul(strict::sub(r.p.y, p_world.y), inv),
+                      strict::mul(strict::sub(r.p.z, p_world.z), inv));
+    r.pdf = ds.pdf; r.weight = ds.weight;
+    return r;
+}
+
+LRT_D void splat(const PtArgs &A, float u, float v, float3 value, unsigned &n_splat) {
+    const FilmParams &F = A.film;
+    Footprint fp;
+    const float px = u + (float) F.off_x, py = v + (float) F.off_y;     // sensor_ds.uv + block->offset()
+    const bool ok = A.scalar ? film_footprint<true>(F, px, py, fp) : film_footprint<false>(F, px, py, fp);
+    if (!ok) return;
+    const int sw = F.size_x + 2 * F.border, sh = F.size_y + 2 * F.border;
+    n_splat++;
+    for (int iy = 0; iy < fp.ny; ++iy) {
+        const int y = fp.y0 + iy;
+        if ((unsigned) y >= (unsigned) sh) continue;
+        for (int ix = 0; ix < fp.nx; ++ix) {
+            const int x = fp.x0 + ix;
+            if ((unsigned) x >= (unsigned) sw) continue;
+            const float w = fp.wx[ix] * fp.wy[iy];
+            if (w == 0.f) continue;
+            float *dst = A.accum + ((size_t) y * sw + x) * 4;
+            if (value.x != 0.f) atomicAdd(dst, value.x * w);
+            if (value.y != 0.f) atomicAdd(dst + 1, value.y * w);
+            if (value.z != 0.f) atomicAdd(dst + 2, value.z * w);
+        }
+    }
+}
+
+// BSDF::eval(ctx, si, wo) for the connection: only the diffuse lobe is non-zero (delta lobes evaluate to 0)
+LRT_D float3 bsdf_eval(const SceneView &sc, int bsdf_id, float2 uv, float3 wi, float3 wo) {
+    const float4 *bp = sc.bsdfs + 4 * (size_t) bsdf_id;
+    const float4 b0 = __ldg(bp), b1 = __ldg(bp + 1), b3 = __ldg(bp + 3);
+    if (b0.y != 0.f && wi.z < 0.f) { wi.z = -wi.z; wo.z = -wo.z; }
+    if ((int) b0.x != BSDF_DIFFUSE || !(wi.z > 0.f && wo.z > 0.f)) return make_float3(0, 0, 0);
+    float3 refl = make_float3(b0.z, b0.w, b1.x);
+    if (b3.w != 0.f) refl = texture_eval(sc.textures + ((int) b3.w - 1), uv);
+    return refl * (kInvPi * wo.z);
+}
+
+// ptracer.cpp:285-371. bsdf_id < 0: a directly visible emitter (no scattering)
+LRT_D void connect_sensor(const PtArgs &A, const PtVertex &v, const SensorDS &sds, int bsdf_id, float3 weight,
+                          unsigned &n_rays, unsigned &n_splat) {
+    const bool has_bsdf = bsdf_id >= 0;
+    if (!(sds.valid && sds.pdf > 0.f && (weight.x != 0.f || weight.y != 0.f || weight.z != 0.f))) return;
+    // Interaction::spawn_ray_to (interaction.h:139-146)
+    const float3 so = offset_p(v.p, v.n, sds.p - v.p);
+    float3 sd = sds.p - so; const float sdist = sqrtf(dot(sd, sd)); sd = sd * (1.f / sdist);
+    unsigned work = 0;
+    const RayHit sh = scene_intersect(A.sc, so, sd, sdist * (1.f - kShadowEpsilon), true, work);
+    n_rays++;
+    if (sh.tri >= 0) return;
+    float3 surface_weight = make_float3(1, 1, 1);
+    const float3 local_d = v.to_local(sd);
+    if (v.shape >= 0) {
+        if (!has_bsdf) surface_weight *= fmaxf(0.f, local_d.z);
+        else {
+            const float wi_dot_geo_n = dot(v.n, v.to_world(v.wi)), wo_dot_geo_n = dot(v.n, sd);
+            const bool valid = (wi_dot_geo_n * v.wi.z > 0.f) && (wo_dot_geo_n * local_d.z > 0.f);
+            const float correction = valid ? fabsf((v.wi.z * wo_dot_geo_n) / (local_d.z * wi_dot_geo_n)) : 0.f;
+            surface_weight = bsdf_eval(A.sc, bsdf_id, v.uv, v.wi, local_d) * correction;
+        }
+    } else if (!has_bsdf && local_d.z <= 0.f) surface_weight = make_float3(0, 0, 0);
+    splat(A, sds.u, sds.v, weight * surface_weight * A.sample_scale, n_splat);
+}
+
+LRT_D float3 uniform_sphere(float sx, float sy) {      // warp.h:250-255
+    const float z = strict::fnmadd(2.f, sy, 1.f), r = strict::sqrt(fmaxf(strict::fnmadd(z, z, 1.f), 0.f));
+    float sn, cs; sincos_drjit(strict::mul(strict::mul(2.f, kPi), sx), sn, cs);
+    return make_float3(strict::mul(r, cs), strict::mul(r, sn), z);
+}
+
+LRT_D float3 cosine_hemisphere(float sx, float sy) {   // warp.h:241-252, the same (strict) disk warp as the aperture
+    float px, py; square_to_disk_concentric(sx, sy, px, py);
+    return make_float3(px, py, sqrtf(fmaxf(1.f - (px * px + py * py), 0.f)));
+}
+
+// Scene::sample_emitter (scene.cpp:227-250): uniform choice, the sample is reused
+LRT_D int pick_emitter(const SceneView &sc, float &sample, float &weight) {
+    const int count = sc.n_emitters;
+    weight = 1.f;
+    if (count < 2) return 0;
+    const float cf = (float) count, scaled = sample * cf;
+    const int index = min((int) scaled, count - 1);
+    weight = cf; sample = scaled - (float) index;
+    return index;
+}
+
+// Emitter::sample_position for area lights (area.cpp:210-245): point, normal, weight = 1 / pdf
+LRT_D void emitter_sample_position(const SceneView &sc, const float4 *ep, float sx, float sy, float3 &p, float3 &n, float &weight) {
+    const float4 e1 = __ldg(ep + 1), e4 = __ldg(ep + 4);
+    if (e4.w == 1.f) mesh_emitter_sample_position(sc, e1, sx, sy, p, n);
+    else {
+        const float4 e2 = __ldg(ep + 2), e3 = __ldg(ep + 3);
+        const float ux = sx * 2.f - 1.f, uy = sy * 2.f - 1.f;
+        p = make_float3(e1.x, e1.y, e1.z) + make_float3(e2.x, e2.y, e2.z) * ux + make_float3(e3.x, e3.y, e3.z) * uy;
+        n = make_float3(e4.x, e4.y, e4.z);
+    }
+    weight = e1.w > 0.f ? 1.f / e1.w : 0.f;
+}
+
+// ptracer.cpp:96-167
+LRT_D void sample_visible_emitters(const PtArgs &A, const LensSystem &L, Pcg32 &rng, unsigned &n_rays, unsigned &n_splat) {
+    if (A.shutter_open) (void) rng.next_f32();
+    float idx_sample = rng.next_f32(), idx_weight;
+    const int index = pick_emitter(A.sc, idx_sample, idx_weight);
+    const float4 *ep = A.sc.emitters + 5 * (size_t) index;
+    const float4 e0 = __ldg(ep), e1 = __ldg(ep + 1), e4 = __ldg(ep + 4);
+    const float s2x = rng.next_f32(), s2y = rng.next_f32();
+    PtVertex v; float ew;
+    if (e4.w == 2.f) {
+        // a direction towards the environment as seen from the sensor's position, converted to area measure (:117-141)
+        const float3 ref_p = make_float3(A.to_world[3], A.to_world[7], A.to_world[11]);
+        const float3 d = uniform_sphere(s2x, s2y);
+        const float3 rel = ref_p - make_float3(e1.x, e1.y, e1.z);
+        const float dist = 2.f * fmaxf(e1.w, sqrtf(dot(rel, rel)));
+        ew = (4.f * kPi) * (dist * dist);
+        v.p = ref_p + d * dist; v.n = -d; v.shape = -1; v.uv = make_float2(s2x, s2y);
+    } else {
+        emitter_sample_position(A.sc, ep, s2x, s2y, v.p, v.n, ew);
+        v.shape = (int) e0.w; v.uv = make_float2(0, 0);
+    }
+    v.sn = v.n; coordinate_system(v.n, v.s, v.t);
+    const float s3x = rng.next_f32(), s3y = rng.next_f32();
+    const SensorDS sds = sensor_sample_direction(A, L, v.p, s3x, s3y);
+    v.wi = sds.d;
+    (void) rng.next_f32();                                       // the wavelength sample (unused in RGB variants)
+    const float3 weight = make_float3(e0.x, e0.y, e0.z) * (ew * idx_weight) * sds.weight;
+    connect_sensor(A, v, sds, -1, weight, n_rays, n_splat);
+}
+
+// ptracer.cpp:170-186 + scene.cpp:260-296 + area.cpp:92-115 / constant.cpp:93-111
+LRT_D void prepare_ray(const PtArgs &A, Pcg32 &rng, float3 &ro, float3 &rd, float3 &throughput) {
+    if (A.shutter_open) (void) rng.next_f32();
+    float sample1 = rng.next_f32(), idx_weight;
+    const float s2x = rng.next_f32(), s2y = rng.next_f32(), s3x = rng.next_f32(), s3y = rng.next_f32();
+    const int index = pick_emitter(A.sc, sample1, idx_weight);
+    const float4 *ep = A.sc.emitters + 5 * (size_t) index;
+    const float4 e0 = __ldg(ep), e1 = __ldg(ep + 1), e4 = __ldg(ep + 4);
+    const float3 radiance = make_float3(e0.x, e0.y, e0.z);
+    if (e4.w == 2.f) {
+        const float3 v0 = uniform_sphere(s2x, s2y);
+        ro = make_float3(e1.x, e1.y, e1.z) + v0 * e1.w;
+        const float3 v1 = cosine_hemisphere(s3x, s3y);
+        float3 s, t; coordinate_system(-v0, s, t);
+        rd = s * v1.x + t * v1.y + (-v0) * v1.z;
+        throughput = radiance * ((4.f * kPi * e1.w * e1.w) * kPi);
+    } else {
+        float3 p, n; float w; emitter_sample_position(A.sc, ep, s2x, s2y, p, n, w);
+        float3 s, t; coordinate_system(n, s, t);
+        const float3 local = cosine_hemisphere(s3x, s3y);
+        rd = s * local.x + t * local.y + n * local.z;
+        ro = offset_p(p, n, rd);
+        throughput = radiance * (w * kPi);
+    }
+    throughput *= idx_weight;
+}
+
+// ptracer.cpp:205-283
+LRT_D void trace_light_ray(const PtArgs &A, const LensSystem &L, Pcg32 &rng, float3 ro, float3 rd, float3 throughput,
+                           unsigned &n_rays, unsigned &n_splat) {
+    float eta = 1.f; int depth = 1;
+    bool active = throughput.x != 0.f || throughput.y != 0.f || throughput.z != 0.f;
+    if (!active) return;
+    unsigned work = 0;
+    RayHit h = scene_intersect(A.sc, ro, rd, kLargest, false, work); n_rays++;
+    active = h.tri >= 0 && depth < A.max_depth;
+    while (active) {
+        const Surface si = make_surface(A.sc, h, ro, rd);
+        const int bsdf_id = __ldg(A.sc.shape_bsdf + si.shape);
+        const float ssx = rng.next_f32(), ssy = rng.next_f32();
+        const SensorDS sds = sensor_sample_direction(A, L, si.p, ssx, ssy);
+        PtVertex v; v.p = si.p; v.n = si.n; v.s = si.s; v.t = si.t; v.sn = si.sn; v.wi = si.wi; v.uv = si.uv; v.shape = si.shape;
+        connect_sensor(A, v, sds, bsdf_id, throughput * sds.weight, n_rays, n_splat);
+        // bsdf->sample(ctx, si, next_1d(), next_2d()): the 2D sample is drawn first (see the header)
+        const float s2x = rng.next_f32(), s2y = rng.next_f32(), s1 = rng.next_f32();
+        BsdfResult bs = bsdf_eval_pdf_sample(A.sc, bsdf_id, si.uv, si.wi, make_float3(0, 0, 1), s1, s2x, s2y);
+        if (bs.transmitted) {     // TransportMode::Importance: no eta^2 factor on a refraction (dielectric.cpp:363-368)
+            const float4 b2 = __ldg(A.sc.bsdfs + 4 * (size_t) bsdf_id + 2), b3 = __ldg(A.sc.bsdfs + 4 * (size_t) bsdf_id + 3);
+            bs.weight = make_float3(b2.w, b3.x, b3.y);
+        }
+        const float3 wo_w = si.to_world(bs.wo);
+        const float wi_dot_geo_n = dot(si.n, -rd), wo_dot_geo_n = dot(si.n, wo_w);
+        active = (wi_dot_geo_n * si.wi.z > 0.f) && (wo_dot_geo_n * bs.wo.z > 0.f);
+        const float correction = fabsf((si.wi.z * wo_dot_geo_n) / (bs.wo.z * wi_dot_geo_n));
+        throughput *= bs.weight * correction;
+        eta *= bs.seta;
+        active = active && (throughput.x != 0.f || throughput.y != 0.f || throughput.z != 0.f);
+        if (!active) break;
+        ro = offset_p(si.p, si.n, wo_w); rd = wo_w;
+        h = scene_intersect(A.sc, ro, rd, kLargest, false, work); n_rays++;
+        depth++;
+        active = depth < A.max_depth && h.tri >= 0;
+        const bool use_rr = depth > A.rr_depth;
+        if (use_rr || !A.scalar) {
+            const float q = fminf(max3(throughput) * eta * eta, .95f);
+            const float r = active ? rng.next_f32() : 0.f;          // a masked draw: inactive lanes keep their state
+            if (use_rr) { active = active && r < q; throughput *= 1.f / q; }
+        }
+    }
+}
+
+// ptracer.cpp:77-90
+LRT_D void ptrace_sample(const PtArgs &A, const LensSystem &L, Pcg32 &rng, unsigned &n_rays, unsigned &n_splat) {
+    if (A.max_depth != 0 && !A.hide_emitters) sample_visible_emitters(A, L, rng, n_rays, n_splat);
+    float3 ro, rd, throughput;
+    prepare_ray(A, rng, ro, rd, throughput);
+    trace_light_ray(A, L, rng, ro, rd, throughput, n_rays, n_splat);
+}
+
+__global__ void __launch_bounds__(128) k_ptrace(PtArgs A) {
+    __shared__ LensSystem L;
+    {
+        const uint4 *src = reinterpret_cast<const uint4 *>(A.lens);
+        uint4 *dst = reinterpret_cast<uint4 *>(&L);
+        for (int i = threadIdx.x; i < (int) (sizeof(LensSystem) / 16); i += blockDim.x) dst[i] = src[i];
+    }
+    __syncthreads();
+    unsigned n_paths = 0, n_rays = 0, n_splat = 0;
+    const long long tid = blockIdx.x * (long long) blockDim.x + threadIdx.x, stride = (long long) gridDim.x * blockDim.x;
+    if (!A.scalar) {
+        // sample idx = shard_index + k * shard_count: identical streams for any number of GPUs
+        for (long long k = tid; ; k += stride) {
+            const long long idx = (long long) A.shard_index + k * A.shard_count;
+            if (idx >= A.n_total) break;
+            Pcg32 rng; rng.seed_sample(A.seed, (uint32_t) idx);
+            ptrace_sample(A, L, rng, n_rays, n_splat); n_paths++;
+        }
+    } else {
+        for (long long r = tid; r < A.n_ranges; r += stride) {
+            const long long begin = r * A.grain, end = min(begin + A.grain, A.n_total);
+            Pcg32 rng; rng.seed((uint64_t) (A.seed + (uint32_t) r), 0xda3e39cb94b95bdbULL);
+            for (long long i = begin; i < end; ++i) { ptrace_sample(A, L, rng, n_rays, n_splat); n_paths++; }
+        }
+    }
+    if (A.stats) {
+        unsigned long long c[3] = { n_paths, n_splat, n_rays };
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            for (int o = 16; o > 0; o >>= 1) c[k] += __shfl_down_sync(0xffffffffu, c[k], o);
+            if ((threadIdx.x & 31) == 0 && c[k]) atomicAdd(A.stats + k, c[k]);
+        }
+    }
+}
+
+}  // namespace lrt
+
+using namespace lrt;
+extern "C" {
+
+int lrt_ptrace(const lrt_scene *sc, const lrt_sensor *sensor_, const lrt_film_desc *film, const lrt_ptrace_params *pp, float *accum_dev,
+               void *stream_) {
+    LRT_NEED_DEVICE();
+    LRT_REQUIRE(sc && sensor_ && film && pp && accum_dev, "null argument");
+    lrt_sensor *sensor = const_cast<lrt_sensor *>(sensor_);
+    cudaStream_t stream = (cudaStream_t) stream_;
+    LRT_REQUIRE(sensor->host.kind == 0, "lrt_ptrace connects light paths to a realistic lens (perspective sensors are not built)");
+    LRT_REQUIRE(film->channels == 4 && film->normalize == 1 && film->coalesce == 0,
+                "lrt_ptrace needs the particle tracer's film: 4 channels, normalize = 1, coalesce = 0 (integrator.cpp:706-717)");
+    LRT_REQUIRE(pp->spp > 0 && pp->max_depth >= -1 && pp->rr_depth > 0, "bad parameters (spp > 0, max_depth >= -1, rr_depth > 0)");
+    LRT_REQUIRE(pp->shard_count >= 1 && pp->shard_index >= 0 && pp->shard_index < pp->shard_count, "bad shard");
+    LRT_REQUIRE(pp->rng_mode == 0 || pp->rng_mode == 1, "rng_mode must be 0 (per-sample streams) or 1 (scalar convention)");
+    LRT_REQUIRE(pp->rng_mode == 0 || (pp->shard_count == 1 && pp->n_threads >= 1), "rng_mode 1 is a single-GPU parity mode and needs n_threads >= 1");
+    if (sc->n_emitters == 0) return LRT_OK;                       // "no emitters found, returning black image"
+    PtArgs A; memset(&A, 0, sizeof A);
+    int rc = film_params_from_desc(film, A.film); if (rc) return rc;
+    rc = sensor->upload(stream); if (rc) return rc;
+    A.sc = sc->view; A.lens = sensor->dev;
+    for (int i = 0; i < 12; ++i) A.to_world[i] = sensor->host.to_world[i];
+    bool given = false;
+    for (int i = 0; i < 12; ++i) given = given || pp->to_camera[i] != 0.f;
+    if (given) for (int i = 0; i < 12; ++i) A.to_camera[i] = pp->to_camera[i];
+    else {    // numerical inverse of the affine matrix, in double, rounded once
+        const float *T = A.to_world;
+        const double a = T[0], b = T[1], c = T[2], d = T[4], e = T[5], f = T[6], g = T[8], h = T[9], k = T[10];
+        const double det = a * (e * k - f * h) - b * (d * k - f * g) + c * (d * h - e * g);
+        LRT_REQUIRE(det != 0.0, "the sensor's to_world matrix is singular");
+        const double R[9] = { (e * k - f * h) / det, (c * h - b * k) / det, (b * f - c * e) / det, (f * g - d * k) / det, (a * k - c * g) / det,
+                              (c * d - a * f) / det, (d * h - e * g) / det, (b * g - a * h) / det, (a * e - b * d) / det };
+        for (int r = 0; r < 3; ++r) {
+            for (int q = 0; q < 3; ++q) A.to_camera[4 * r + q] = (float) R[3 * r + q];
+            A.to_camera[4 * r + 3] = (float) -(R[3 * r] * T[3] + R[3 * r + 1] * T[7] + R[3 * r + 2] * T[11]);
+        }
+    }
+    const lrt_film_geom &g = sensor->film;
+    const long long film_pixels = (long long) g.width * g.height;
+    A.n_total = film_pixels * pp->spp;                            // integrator.cpp:573-574: the FULL film size x spp
+    LRT_REQUIRE(A.n_total <= 0xffffffffll, "width * height * spp must stay below 2^32 (split the render into passes)");
+    A.sample_scale = (float) ((long long) film->size_x * film->size_y) / (float) ((uint32_t) pp->spp * (uint32_t) film_pixels);
+    A.scalar = pp->rng_mode; A.max_depth = pp->max_depth < 0 ? 0x7fffffff : pp->max_depth; A.rr_depth = pp->rr_depth;
+    A.hide_emitters = pp->hide_emitters; A.shutter_open = sensor->host.shutter_open_time > 0.f;
+    A.shard_index = pp->shard_index; A.shard_count = pp->shard_count;
+    A.film.discretized = A.scalar;
+    long long work_items;
+    if (A.scalar) {
+        A.grain = std::max<long long>(A.n_total / (4ll * pp->n_threads), 1);
+        A.n_ranges = (A.n_total + A.grain - 1) / A.grain;
+        A.seed = pp->base_seed + pp->seed * (uint32_t) ((uint32_t) A.n_total / (uint32_t) A.grain);   // integrator.cpp:621 + sampler.cpp:131
+        work_items = A.n_ranges;
+    } else {
+        A.seed = pp->base_seed + pp->seed;
+        work_items = (A.n_total - pp->shard_index + pp->shard_count - 1) / pp->shard_count;
+    }
+    A.accum = accum_dev; A.stats = sc->d_counter + kCounterRing;
+    LRT_CUDA(cudaMemsetAsync(A.stats, 0, 8 * sizeof(unsigned long long), stream));
+    int dev = 0, sms = 148; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    long long grid = (work_items + 127) / 128; grid = std::max<long long>(1, std::min<long long>(grid, (long long) sms * 16));
+    k_ptrace<<<(int) grid, 128, 0, stream>>>(A);
+    LRT_LAUNCHED();
+    LRT_CUDA(cudaGetLastError());
+    return LRT_OK;
+}
+
+}  // extern "C"

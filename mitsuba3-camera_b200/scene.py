@@ -8,6 +8,7 @@ BSDFs: diffuse, conductor, dielectric, twosided(diffuse|conductor). Emitters: ar
 from __future__ import annotations
 
 import ctypes as C
+import os
 import struct
 
 import numpy as np
@@ -449,6 +450,30 @@ class PRBIntegrator(PathIntegrator):
         raise ValueError("render_forward: forward-mode differentiation is outside the hot path of this build (use render_backward)")
 
 
+class PtraceParams(C.Structure):
+    _fields_ = [("seed", C.c_uint32), ("spp", C.c_int32), ("max_depth", C.c_int32), ("rr_depth", C.c_int32), ("hide_emitters", C.c_int32),
+                ("shard_index", C.c_int32), ("shard_count", C.c_int32), ("rng_mode", C.c_int32), ("n_threads", C.c_int32),
+                ("base_seed", C.c_uint32), ("to_camera", C.c_float * 12)]
+
+
+class PTracerIntegrator(PathIntegrator):
+    """`ptracer` plugin (src/integrators/ptracer.cpp under AdjointIntegrator::render, src/render/integrator.cpp:544-760):
+    max_depth, rr_depth, hide_emitters. The image is the RGB of the film's storage as it is (no division by a weight)."""
+
+    def render(self, scene, sensor=0, seed=0, spp=0, develop=True, evaluate=True, shard=(0, 1), rng_mode=0, n_threads=0):
+        """rng_mode=1 / n_threads: the scalar AdjointIntegrator's seeding convention for that many worker threads (parity mode)."""
+        import torch
+        s = scene.sensors()[sensor] if isinstance(sensor, int) else sensor
+        spp = int(spp) if spp else s.sampler.sample_count()
+        fd = film_desc(s.film, coalesce=False, normalize=True)
+        storage = torch.zeros((s.film.crop_h, s.film.crop_w, 4), dtype=torch.float32, device="cuda")
+        tc = (C.c_float * 12)(*[float(x) for x in np.asarray(getattr(s, "to_camera", np.zeros((4, 4), f32)), f32)[:3].reshape(-1)])
+        pp = PtraceParams(int(seed) & 0xffffffff, spp, self.max_depth, self.rr_depth, int(self.hide_emitters), shard[0], shard[1], int(rng_mode),
+                          int(n_threads) if n_threads else (os.cpu_count() or 1), s.sampler.base_seed & 0xffffffff, tc)
+        capi.check(capi.lib.lrt_ptrace(scene.handle, s.handle, C.byref(fd), C.byref(pp), capi.dev_ptr(storage), capi.stream_ptr()))
+        return storage[..., :3].contiguous() if develop else storage
+
+
 class IndependentSampler:
     """`independent` plugin (src/samplers/independent.cpp): sample_count, seed (base seed)."""
 
@@ -621,6 +646,8 @@ def render(scene: Scene, params=None, sensor=0, integrator=None, seed=0, seed_gr
         params.update()
     s = scene.sensors()[sensor] if isinstance(sensor, int) else sensor
     it = integrator or scene.integrator()
+    if isinstance(it, PTracerIntegrator):
+        return it.render(scene, sensor=s, seed=seed, spp=spp, develop=develop, shard=shard, rng_mode=rng_mode, n_threads=block_size)
     spp = int(spp) if spp else s.sampler.sample_count()
     fd = film_desc(s.film)
     if storage is None:
@@ -943,6 +970,8 @@ def load_dict(d: dict):
         return IndependentSampler(d.get("sample_count", 4), d.get("seed", 0))
     if t in ("gaussian", "tent", "box"):
         return ReconstructionFilter(t, float(d.get("stddev", d.get("radius", 0.0))) if t != "box" else 0.0)
+    if t == "ptracer":
+        return PTracerIntegrator(d.get("max_depth", -1), d.get("rr_depth", 5), d.get("hide_emitters", False))
     if t in ("path", "prb"):
         # hide_emitters: with an environment emitter, camera rays that escape yield no valid sample (path.cpp:113-114)
         return (PRBIntegrator if t == "prb" else PathIntegrator)(d.get("max_depth", -1), d.get("rr_depth", 5), d.get("hide_emitters", False))

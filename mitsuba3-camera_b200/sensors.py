@@ -103,6 +103,9 @@ class RealisticLensCamera(Sensor):
         self.props = dict(props)
         self.near_clip, self.far_clip = float(near_clip), float(far_clip)
         self.to_world = _to_world_array(to_world)
+        # the inverse the scene description carries next to the matrix (Transform4f), else inverted numerically
+        self.to_camera = (np.ascontiguousarray(to_world.inverse_matrix, f32) if hasattr(to_world, "inverse_matrix")
+                          else np.linalg.inv(self.to_world.astype(np.float64)).astype(f32))
         self.object_distance = float(props.get("object_distance", 6.0))
         # ProjectiveCamera / Sensor: shutter_open, shutter_close (src/render/sensor.cpp:27-33); the pupil-mode weight
         # is scaled by shutter_open_time() = close - open, which is 0 unless the scene sets them (as in the reference)
@@ -178,6 +181,8 @@ class RealisticLensCamera(Sensor):
 
     def set_to_world(self, to_world):
         self.to_world = _to_world_array(to_world)
+        self.to_camera = (np.ascontiguousarray(to_world.inverse_matrix, f32) if hasattr(to_world, "inverse_matrix")
+                          else np.linalg.inv(self.to_world.astype(np.float64)).astype(f32))
         capi.check(capi.lib.lrt_sensor_set_to_world(self.handle, capi.fp(self.to_world)))
 
     def info(self):
