@@ -147,7 +147,7 @@ def cpu_sample(a, scene_arrays, sensor_dict, steps=1, warmup=0, keep_image=False
     return out, sec
 
 
-def reference_sample(a, steps=1, warmup=0):
+def reference_sample(a, steps=1, warmup=0, extra=()):
     """The CPU arm proper: the REFERENCE's own scalar_rgb build (tools/build_reference.sh -> baseline/_ref, shipped to the GPU box)
     renders the same scene over the FULL film at --ref-spp samples per pixel with every host core, in a subprocess that never
     imports the product (tools/ref_bench.py). None if the build is not there."""
@@ -160,10 +160,14 @@ def reference_sample(a, steps=1, warmup=0):
     cmd = [sys.executable, os.path.join(ROOT, "tools", "ref_bench.py"), "--workload", a.workload, "--n-boxes", str(a.n_boxes),
            "--tex-size", str(a.tex_size), "--width", str(a.width), "--height", str(a.height),
            "--n-side", str(a.n_side), "--lens", a.lens, "--max-depth", str(a.max_depth), "--spp", str(a.ref_spp),
-           "--steps", str(steps), "--warmup", str(warmup)]
+           "--steps", str(steps), "--warmup", str(warmup)] + list(extra)
+    for k in range(0, len(extra), 2):        # later options override earlier ones in argparse; drop the duplicates for readability
+        if extra[k] in cmd[:-len(extra)]:
+            i = cmd.index(extra[k]); del cmd[i:i + 2]
     try:
         out = subprocess.run(cmd, capture_output=True, text=True, timeout=1500, env=env, cwd="/tmp")
-        r = json.loads([ln for ln in out.stdout.splitlines() if ln.startswith("{")][-1])
+        # (the particle tracer's progress bar shares the last line with the result: take the JSON object from its first brace)
+        r = json.loads([ln[ln.index('{"seconds"'):] for ln in out.stdout.splitlines() if '{"seconds"' in ln][-1])
     except Exception as e:
         sys.stderr.write(f"reference build failed to run: {e}\n{out.stderr[-2000:] if 'out' in dir() else ''}\n")
         return None
@@ -539,6 +543,11 @@ def main():
                                    "what": "lrt_render_backward on the same workload: gradients of diffuse reflectance / conductor "
                                            "specular reflectance / area-light radiance (one-pass PRB)"}
         if ptr is not None:
+            if "value" in ptr and not a.no_cpu_baseline and world == 1:
+                pr = reference_sample(a, extra=("--integrator", "ptracer", "--width", "1024", "--height", "576", "--spp", "4"))
+                if pr is not None:
+                    ptr["cpu_baseline"] = {"value": pr[0]["value"], "unit": "M light paths/s", "cores": pr[0]["cores"], "kind": "reference",
+                                           "sample": "the reference's scalar_rgb ptracer on the same scene, 1024x576 film, 4 spp"}
             line["ptracer"] = ptr
         if lens_grad is not None:
             line["lens_grad"] = lens_grad

@@ -290,6 +290,16 @@ typedef struct lrt_ptrace_params {
 int lrt_ptrace(const lrt_scene *scene, const lrt_sensor *sensor, const lrt_film_desc *film, const lrt_ptrace_params *params,
                float *accum_dev, void *stream);
 
+/* Lens adjoint of lrt_ptrace — what `dr.backward(loss)` through a `ptracer` render delivers to the lens parameters in the
+ * notebooks' design loop (notebooks/scripts/lens_design/design_problem.py:495-584; generic Integrator::render_backward,
+ * src/render/integrator.cpp:66-84), here for the analytic interface table. grad_accum_dev = d(loss)/d(accum) [size_y, size_x, 4]
+ * (RGB used); ADDS d(loss)/d(rows16) to grad_rows16_dev [n_if, 16] (caller zeroes it; columns as in lrt_spot_render_backward).
+ * The same light paths are replayed (rng_mode 0, equal params): every connection contributes the adjoint of its splat position and
+ * of the sensor's importance weight; light-path vertices, BSDF values and visibility do not depend on the lens; vignetting masks
+ * are piecewise constant and detached, as in the spot path. */
+int lrt_ptrace_backward(const lrt_scene *scene, const lrt_sensor *sensor, const lrt_film_desc *film, const lrt_ptrace_params *params,
+                        const float *grad_accum_dev, float *grad_rows16_dev, void *stream);
+
 /* No counterpart in the reference: added for callers that cannot call cudaMalloc (code
  * under CUDA graph capture, tight serving loops, harnesses that forbid allocation). lrt_render_host without any allocation:
  * render (rng_mode 0) + HDRFilm::develop with the R,G,B,W accumulator in a fixed 4 MiB device array inside the library, so the

@@ -17,6 +17,7 @@
 #include "lrt_rng.cuh"
 #include "lrt_shade.cuh"
 #include "lrt_scene.h"
+#include "lrt_spot_adj.cuh"
 
 namespace lrt {
 
@@ -32,6 +33,8 @@ struct PtArgs {
     float sample_scale;
     float *accum;
     unsigned long long *stats;             // [0] light paths, [1] connections splatted, [2] rays traced
+    // lens adjoint (k_ptrace<true>): d(loss)/d(accum) in, d(loss)/d(interface table) out
+    const float *grad_accum; float *grad_rows;
 };
 
 struct PtVertex {
@@ -40,7 +43,7 @@ struct PtVertex {
     LRT_D float3 to_world(float3 v) const { return s * v.x + t * v.y + sn * v.z; }
 };
 
-struct SensorDS { bool valid; float u, v; float3 p, d; float dist, pdf, weight; };
+struct SensorDS { bool valid; float u, v; float3 p, d; float dist, pdf, weight; float3 ref; float a, b; };   // ref: camera-space point
 
 // Transform4f::transform_affine (transform.h:104-111): translation column first, then one multiply-add per column, strict
 LRT_D float3 xf_point_strict(const float *M, float3 p) {
@@ -56,6 +59,7 @@ LRT_D float3 xf_point_strict(const float *M, float3 p) {
 LRT_D SensorDS sensor_sample_direction(const PtArgs &A, const LensSystem &L, float3 p_world, float a, float b) {
     SensorDS r; r.valid = false; r.u = r.v = 0.f; r.p = r.d = make_float3(0, 0, 0); r.dist = r.pdf = r.weight = 0.f;
     const float3 ref = xf_point_strict(A.to_camera, p_world);
+    r.ref = ref; r.a = a; r.b = b;
     const DirectionSample ds = lens_sample_direction(L, L.ifs, strict::v3(ref.x, ref.y, ref.z), a, b);
     if (!ds.valid) return r;
     r.valid = true; r.u = ds.uv_x; r.v = ds.uv_y;
@@ -103,11 +107,13 @@ LRT_D float3 bsdf_eval(const SceneView &sc, int bsdf_id, float2 uv, float3 wi, f
     return refl * (kInvPi * wo.z);
 }
 
-// ptracer.cpp:285-371. bsdf_id < 0: a directly visible emitter (no scattering)
-LRT_D void connect_sensor(const PtArgs &A, const PtVertex &v, const SensorDS &sds, int bsdf_id, float3 weight,
-                          unsigned &n_rays, unsigned &n_splat) {
+// ptracer.cpp:285-371. bsdf_id < 0: a directly visible emitter (no scattering). `weight` comes WITHOUT the sensor's importance
+// (sds.weight), which the forward multiplies in and the lens adjoint differentiates.
+template <bool kAdj>
+LRT_D void connect_sensor(const PtArgs &A, const LensSystem &L, const PtVertex &v, const SensorDS &sds, int bsdf_id, float3 weight,
+                          unsigned &n_rays, unsigned &n_splat, float (*g_loc)[kSlots]) {
     const bool has_bsdf = bsdf_id >= 0;
-    if (!(sds.valid && sds.pdf > 0.f && (weight.x != 0.f || weight.y != 0.f || weight.z != 0.f))) return;
+    if (!(sds.valid && sds.pdf > 0.f && sds.weight != 0.f && (weight.x != 0.f || weight.y != 0.f || weight.z != 0.f))) return;
     // Interaction::spawn_ray_to (interaction.h:139-146)
     const float3 so = offset_p(v.p, v.n, sds.p - v.p);
     float3 sd = sds.p - so; const float sdist = sqrtf(dot(sd, sd)); sd = sd * (1.f / sdist);
@@ -126,7 +132,14 @@ LRT_D void connect_sensor(const PtArgs &A, const PtVertex &v, const SensorDS &sd
             surface_weight = bsdf_eval(A.sc, bsdf_id, v.uv, v.wi, local_d) * correction;
         }
     } else if (!has_bsdf && local_d.z <= 0.f) surface_weight = make_float3(0, 0, 0);
-    splat(A, sds.u, sds.v, weight * surface_weight * A.sample_scale, n_splat);
+    const float3 value = weight * surface_weight;
+    if (!kAdj) splat(A, sds.u, sds.v, value * (sds.weight * A.sample_scale), n_splat);
+    else if (value.x != 0.f || value.y != 0.f || value.z != 0.f) {
+        // the vertex, its BSDF value and the visibility do not depend on the lens (the aperture point's dependence on the front
+        // vertex is detached, like the masks): what remains is the spot path's connection adjoint for this reference point
+        if (lens_connection_adjoint(L, A.film, strict::v3(sds.ref.x, sds.ref.y, sds.ref.z), sds.a, sds.b, 0.f, value.x, value.y, value.z,
+                                    A.sample_scale, 0.f, A.grad_accum, g_loc)) n_splat++;
+    }
 }
 
 LRT_D float3 uniform_sphere(float sx, float sy) {      // warp.h:250-255
@@ -165,7 +178,8 @@ LRT_D void emitter_sample_position(const SceneView &sc, const float4 *ep, float 
 }
 
 // ptracer.cpp:96-167
-LRT_D void sample_visible_emitters(const PtArgs &A, const LensSystem &L, Pcg32 &rng, unsigned &n_rays, unsigned &n_splat) {
+template <bool kAdj>
+LRT_D void sample_visible_emitters(const PtArgs &A, const LensSystem &L, Pcg32 &rng, unsigned &n_rays, unsigned &n_splat, float (*g_loc)[kSlots]) {
     if (A.shutter_open) (void) rng.next_f32();
     float idx_sample = rng.next_f32(), idx_weight;
     const int index = pick_emitter(A.sc, idx_sample, idx_weight);
@@ -190,8 +204,8 @@ LRT_D void sample_visible_emitters(const PtArgs &A, const LensSystem &L, Pcg32 &
     const SensorDS sds = sensor_sample_direction(A, L, v.p, s3x, s3y);
     v.wi = sds.d;
     (void) rng.next_f32();                                       // the wavelength sample (unused in RGB variants)
-    const float3 weight = make_float3(e0.x, e0.y, e0.z) * (ew * idx_weight) * sds.weight;
-    connect_sensor(A, v, sds, -1, weight, n_rays, n_splat);
+    const float3 weight = make_float3(e0.x, e0.y, e0.z) * (ew * idx_weight);
+    connect_sensor<kAdj>(A, L, v, sds, -1, weight, n_rays, n_splat, g_loc);
 }
 
 // ptracer.cpp:170-186 + scene.cpp:260-296 + area.cpp:92-115 / constant.cpp:93-111
@@ -222,8 +236,9 @@ LRT_D void prepare_ray(const PtArgs &A, Pcg32 &rng, float3 &ro, float3 &rd, floa
 }
 
 // ptracer.cpp:205-283
+template <bool kAdj>
 LRT_D void trace_light_ray(const PtArgs &A, const LensSystem &L, Pcg32 &rng, float3 ro, float3 rd, float3 throughput,
-                           unsigned &n_rays, unsigned &n_splat) {
+                           unsigned &n_rays, unsigned &n_splat, float (*g_loc)[kSlots]) {
     float eta = 1.f; int depth = 1;
     bool active = throughput.x != 0.f || throughput.y != 0.f || throughput.z != 0.f;
     if (!active) return;
@@ -236,7 +251,7 @@ LRT_D void trace_light_ray(const PtArgs &A, const LensSystem &L, Pcg32 &rng, flo
         const float ssx = rng.next_f32(), ssy = rng.next_f32();
         const SensorDS sds = sensor_sample_direction(A, L, si.p, ssx, ssy);
         PtVertex v; v.p = si.p; v.n = si.n; v.s = si.s; v.t = si.t; v.sn = si.sn; v.wi = si.wi; v.uv = si.uv; v.shape = si.shape;
-        connect_sensor(A, v, sds, bsdf_id, throughput * sds.weight, n_rays, n_splat);
+        connect_sensor<kAdj>(A, L, v, sds, bsdf_id, throughput, n_rays, n_splat, g_loc);
         // bsdf->sample(ctx, si, next_1d(), next_2d()): the 2D sample is drawn first (see the header)
         const float s2x = rng.next_f32(), s2y = rng.next_f32(), s1 = rng.next_f32();
         BsdfResult bs = bsdf_eval_pdf_sample(A.sc, bsdf_id, si.uv, si.wi, make_float3(0, 0, 1), s1, s2x, s2y);
@@ -266,15 +281,23 @@ LRT_D void trace_light_ray(const PtArgs &A, const LensSystem &L, Pcg32 &rng, flo
 }
 
 // ptracer.cpp:77-90
-LRT_D void ptrace_sample(const PtArgs &A, const LensSystem &L, Pcg32 &rng, unsigned &n_rays, unsigned &n_splat) {
-    if (A.max_depth != 0 && !A.hide_emitters) sample_visible_emitters(A, L, rng, n_rays, n_splat);
+template <bool kAdj>
+LRT_D void ptrace_sample(const PtArgs &A, const LensSystem &L, Pcg32 &rng, unsigned &n_rays, unsigned &n_splat, float (*g_loc)[kSlots]) {
+    if (A.max_depth != 0 && !A.hide_emitters) sample_visible_emitters<kAdj>(A, L, rng, n_rays, n_splat, g_loc);
     float3 ro, rd, throughput;
     prepare_ray(A, rng, ro, rd, throughput);
-    trace_light_ray(A, L, rng, ro, rd, throughput, n_rays, n_splat);
+    trace_light_ray<kAdj>(A, L, rng, ro, rd, throughput, n_rays, n_splat, g_loc);
 }
 
+template <bool kAdj>
 __global__ void __launch_bounds__(128) k_ptrace(PtArgs A) {
     __shared__ LensSystem L;
+    __shared__ float s_grad[kAdj ? kMaxInterfaces * kSlots : 1];
+    float g_loc[kAdj ? kMaxInterfaces : 1][kSlots];
+    if (kAdj) {
+        for (int i = threadIdx.x; i < kMaxInterfaces * kSlots; i += blockDim.x) s_grad[i] = 0.f;
+        for (int i = 0; i < kMaxInterfaces; ++i) for (int k = 0; k < kSlots; ++k) g_loc[i][k] = 0.f;
+    }
     {
         const uint4 *src = reinterpret_cast<const uint4 *>(A.lens);
         uint4 *dst = reinterpret_cast<uint4 *>(&L);
@@ -289,13 +312,30 @@ __global__ void __launch_bounds__(128) k_ptrace(PtArgs A) {
             const long long idx = (long long) A.shard_index + k * A.shard_count;
             if (idx >= A.n_total) break;
             Pcg32 rng; rng.seed_sample(A.seed, (uint32_t) idx);
-            ptrace_sample(A, L, rng, n_rays, n_splat); n_paths++;
+            ptrace_sample<kAdj>(A, L, rng, n_rays, n_splat, g_loc); n_paths++;
         }
     } else {
         for (long long r = tid; r < A.n_ranges; r += stride) {
             const long long begin = r * A.grain, end = min(begin + A.grain, A.n_total);
             Pcg32 rng; rng.seed((uint64_t) (A.seed + (uint32_t) r), 0xda3e39cb94b95bdbULL);
-            for (long long i = begin; i < end; ++i) { ptrace_sample(A, L, rng, n_rays, n_splat); n_paths++; }
+            for (long long i = begin; i < end; ++i) { ptrace_sample<kAdj>(A, L, rng, n_rays, n_splat, g_loc); n_paths++; }
+        }
+    }
+    if (kAdj) {     // per-thread slots -> warp -> CTA -> one global atomic per slot (as the spot adjoint)
+        const int n_if = L.n;
+        for (int i = 0; i < n_if; ++i)
+            for (int k = 0; k < kSlots; ++k) {
+                float v = g_loc[i][k];
+                for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+                if ((threadIdx.x & 31) == 0 && v != 0.f) atomicAdd(&s_grad[i * kSlots + k], v);
+            }
+        __syncthreads();
+        for (int i = threadIdx.x; i < n_if * kSlots; i += blockDim.x) {
+            const float v = s_grad[i];
+            if (v == 0.f) continue;
+            const int r = i / kSlots, k = i - r * kSlots;
+            const int col = k == 0 ? G_Z : (k == 1 ? G_R : (k == 2 ? G_K : (k < 10 ? G_A0 + (k - 3) : (k == 10 ? G_IORL : G_IORR))));
+            atomicAdd(A.grad_rows + r * kGradRow + col, v);
         }
     }
     if (A.stats) {
@@ -313,10 +353,11 @@ __global__ void __launch_bounds__(128) k_ptrace(PtArgs A) {
 using namespace lrt;
 extern "C" {
 
-int lrt_ptrace(const lrt_scene *sc, const lrt_sensor *sensor_, const lrt_film_desc *film, const lrt_ptrace_params *pp, float *accum_dev,
-               void *stream_) {
+static int ptrace_launch(const lrt_scene *sc, const lrt_sensor *sensor_, const lrt_film_desc *film, const lrt_ptrace_params *pp, float *accum_dev,
+                         const float *grad_accum_dev, float *grad_rows_dev, void *stream_) {
     LRT_NEED_DEVICE();
-    LRT_REQUIRE(sc && sensor_ && film && pp && accum_dev, "null argument");
+    LRT_REQUIRE(sc && sensor_ && film && pp && (accum_dev || (grad_accum_dev && grad_rows_dev)), "null argument");
+    LRT_REQUIRE(!grad_accum_dev || pp->rng_mode == 0, "the lens adjoint follows the per-sample streams (rng_mode 0)");
     lrt_sensor *sensor = const_cast<lrt_sensor *>(sensor_);
     cudaStream_t stream = (cudaStream_t) stream_;
     LRT_REQUIRE(sensor->host.kind == 0, "lrt_ptrace connects light paths to a realistic lens (perspective sensors are not built)");
@@ -366,14 +407,27 @@ int lrt_ptrace(const lrt_scene *sc, const lrt_sensor *sensor_, const lrt_film_de
         A.seed = pp->base_seed + pp->seed;
         work_items = (A.n_total - pp->shard_index + pp->shard_count - 1) / pp->shard_count;
     }
-    A.accum = accum_dev; A.stats = sc->d_counter + kCounterRing;
+    A.accum = accum_dev; A.grad_accum = grad_accum_dev; A.grad_rows = grad_rows_dev; A.stats = sc->d_counter + kCounterRing;
     LRT_CUDA(cudaMemsetAsync(A.stats, 0, 8 * sizeof(unsigned long long), stream));
     int dev = 0, sms = 148; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     long long grid = (work_items + 127) / 128; grid = std::max<long long>(1, std::min<long long>(grid, (long long) sms * 16));
-    k_ptrace<<<(int) grid, 128, 0, stream>>>(A);
+    if (grad_accum_dev) k_ptrace<true><<<(int) grid, 128, 0, stream>>>(A);
+    else k_ptrace<false><<<(int) grid, 128, 0, stream>>>(A);
     LRT_LAUNCHED();
     LRT_CUDA(cudaGetLastError());
     return LRT_OK;
+}
+
+int lrt_ptrace(const lrt_scene *sc, const lrt_sensor *sensor, const lrt_film_desc *film, const lrt_ptrace_params *pp, float *accum_dev,
+               void *stream) {
+    LRT_REQUIRE(accum_dev, "null argument");
+    return ptrace_launch(sc, sensor, film, pp, accum_dev, nullptr, nullptr, stream);
+}
+
+int lrt_ptrace_backward(const lrt_scene *sc, const lrt_sensor *sensor, const lrt_film_desc *film, const lrt_ptrace_params *pp,
+                        const float *grad_accum_dev, float *grad_rows16_dev, void *stream) {
+    LRT_REQUIRE(grad_accum_dev && grad_rows16_dev, "null argument");
+    return ptrace_launch(sc, sensor, film, pp, nullptr, grad_accum_dev, grad_rows16_dev, stream);
 }
 
 }  // extern "C"

@@ -473,6 +473,24 @@ class PTracerIntegrator(PathIntegrator):
         capi.check(capi.lib.lrt_ptrace(scene.handle, s.handle, C.byref(fd), C.byref(pp), capi.dev_ptr(storage), capi.stream_ptr()))
         return storage[..., :3].contiguous() if develop else storage
 
+    def render_backward_lens(self, scene, grad_image, sensor=0, seed=0, spp=0, shard=(0, 1)):
+        """d(loss)/d(interface table) [n_if, 16] for grad_image = d(loss)/d(image) [H, W, 3] of render(seed, spp): the same light
+        paths replayed, every lens connection differentiated (lrt_ptrace_backward). Sum the result over ranks when sharded."""
+        import torch
+        s = scene.sensors()[sensor] if isinstance(sensor, int) else sensor
+        spp = int(spp) if spp else s.sampler.sample_count()
+        fd = film_desc(s.film, coalesce=False, normalize=True)
+        gs = torch.zeros((s.film.crop_h, s.film.crop_w, 4), dtype=torch.float32, device="cuda")
+        gs[..., :3] = torch.as_tensor(grad_image, dtype=torch.float32, device="cuda")
+        n_if = len(s.interfaces())
+        rows = torch.zeros((n_if, 16), dtype=torch.float32, device="cuda")
+        tc = (C.c_float * 12)(*[float(x) for x in np.asarray(getattr(s, "to_camera", np.zeros((4, 4), f32)), f32)[:3].reshape(-1)])
+        pp = PtraceParams(int(seed) & 0xffffffff, spp, self.max_depth, self.rr_depth, int(self.hide_emitters), shard[0], shard[1], 0, 1,
+                          s.sampler.base_seed & 0xffffffff, tc)
+        capi.check(capi.lib.lrt_ptrace_backward(scene.handle, s.handle, C.byref(fd), C.byref(pp), capi.dev_ptr(gs), capi.dev_ptr(rows),
+                                                capi.stream_ptr()))
+        return rows
+
 
 class IndependentSampler:
     """`independent` plugin (src/samplers/independent.cpp): sample_count, seed (base seed)."""

@@ -60,3 +60,45 @@ def test_gpu_ptracer_errors(mi):
     sc = mi.load_dict(d)
     with pytest.raises(mi.capi.LensrtError, match="realistic lens"):
         mi.render(sc)
+
+
+@pytest.mark.gpu
+def test_gpu_ptracer_lens_adjoint_equals_spot_adjoint_for_a_point_like_emitter(mi):
+    """lrt_ptrace_backward: d<G, image>/d(interface table). With max_depth = 1 (directly visible emitters only) and a tiny
+    rectangle light, the particle tracer IS the spot path of a point source of intensity radiance x area x cos(theta_emitter) at
+    the light's position — whose adjoint is pinned (float64 dual numbers + finite differences, tests/test_gpu_spot.py). Both are
+    Monte Carlo estimates over different streams (2^20 samples each): stated tolerance cosine >= 0.999, per entry 3 % of the largest.
+    The forward images must agree the same way (rel-RMSE <= 2 %)."""
+    import torch
+    T = mi.Transform4f
+    P = np.array([0.12, -0.08, 2.0], f32); half = 2e-4
+    radiance = np.array([3.0, 2.0, 1.0], f32)
+    d = {"type": "scene", "integrator": {"type": "ptracer", "max_depth": 1},
+         "sensor": {"type": "realisticlens", "lens_design": "gauss", "object_distance": 2.0,
+                    "film": {"type": "hdrfilm", "width": 32, "height": 32, "rfilter": {"type": "tent"}},
+                    "sampler": {"type": "independent", "sample_count": 1024}},
+         "light": {"type": "rectangle", "to_world": T.translate(P).rotate([1, 0, 0], 180).scale(half),
+                   "emitter": {"type": "area", "radiance": {"type": "rgb", "value": radiance.tolist()}}}}
+    sc = mi.load_dict(d)
+    it, s = sc.integrator(), sc.sensors()[0]
+    H, W = s.film.crop_h, s.film.crop_w
+    yy, xx = np.meshgrid(np.arange(H), np.arange(W), indexing="ij")
+    G = np.stack([1 + .5 * np.cos(2 * np.pi * xx / W), 1 + .5 * np.sin(2 * np.pi * yy / H), 1 + .5 * np.cos(2 * np.pi * (xx + yy) / W)], -1).astype(f32)
+    Gt = torch.as_tensor(G, device="cuda")
+    front_z = float(s.interfaces()[-1, 1])
+    rel = P - np.array([0, 0, front_z], f32)
+    intensity = radiance * (2 * half) ** 2 * (rel[2] / np.linalg.norm(rel))
+    img_pt = it.render(sc, seed=5).cpu().numpy()
+    img_sp = mi.spot_render(s, P, intensity=tuple(intensity), seed=7, spp=1024)[..., :3].cpu().numpy()
+    assert img_pt.sum() > 0 and rel_rmse(img_pt, img_sp) <= 2e-2, rel_rmse(img_pt, img_sp)
+    g_pt = it.render_backward_lens(sc, Gt, seed=5).cpu().numpy()
+    gs = torch.zeros((H, W, 4), device="cuda"); gs[..., :3] = Gt
+    g_sp = mi.spot_render_backward(s, P, gs, intensity=tuple(intensity), seed=7, spp=1024).cpu().numpy()
+    rows = s.interfaces()
+    scale = np.ones(16, f32); scale[1] = 1e-4; scale[3] = 1e-3; scale[13] = scale[14] = 1e-3    # first-order loss changes for typical steps
+    a, b = (g_pt * scale)[:, [1, 3, 13, 14]].ravel(), (g_sp * scale)[:, [1, 3, 13, 14]].ravel()
+    cos = float(a @ b / (np.linalg.norm(a) * np.linalg.norm(b)))
+    print("ptracer adjoint", a); print("spot adjoint   ", b); print("cosine", cos, "forward rel-RMSE", rel_rmse(img_pt, img_sp))
+    assert np.abs(b).max() > 0 and len(rows) == 11
+    assert cos >= 0.999
+    assert np.abs(a - b).max() <= 0.03 * np.abs(b).max()

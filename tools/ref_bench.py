@@ -69,6 +69,7 @@ def main():
     p.add_argument("--crop", type=int, nargs=4, default=None, help="crop_width crop_height offset_x offset_y")
     p.add_argument("--steps", type=int, default=1); p.add_argument("--warmup", type=int, default=0)
     p.add_argument("--threads", type=int, default=0)
+    p.add_argument("--integrator", default="path", help="path | ptracer")
     a = p.parse_args()
     threads = a.threads or os.cpu_count()
     mi.Thread.thread().logger().set_log_level(mi.LogLevel.Warn)
@@ -89,6 +90,8 @@ def main():
             d["sensor"]["film"]["width"] = a.width; d["sensor"]["film"]["height"] = a.height
         else:
             raise SystemExit("unknown workload " + a.workload)
+        if a.integrator != "path":
+            d["integrator"]["type"] = a.integrator
         if a.crop:
             d["sensor"]["film"].update(crop_width=a.crop[0], crop_height=a.crop[1], crop_offset_x=a.crop[2], crop_offset_y=a.crop[3])
         t0 = time.perf_counter()
