@@ -217,6 +217,17 @@ int lrt_scene_refit(lrt_scene *s, const float *vertices_dev, const float *normal
  * `dielectric` BSDF (src/bsdfs/dispersive_dielectric.cpp:250-431) applied about the interpolated vertex normal. */
 int lrt_scene_trace_refractive(const lrt_scene *s, int64_t n, const float *od6_dev, const float *shape_eta_dev,
                                int32_t max_interactions, float *out8_dev, void *stream);
+/* The adjoint of lrt_scene_trace_refractive — what Dr.Jit's reverse mode yields for the notebooks' mesh lenses: Möller–Trumbore
+ * differentiable in the vertex positions (include/mitsuba/render/mesh.h:432-452; Mesh::compute_surface_interaction,
+ * src/render/mesh.cpp:1370-1500), the interpolated vertex normal, fresnel / refract (include/mitsuba/render/fresnel.h:35-84,311-315).
+ * grad_out8 = d(loss)/d(out8) (o[3], d[3], -, weight). Writes grad_od6 [n,6] = d(loss)/d(od6); ACCUMULATES (float atomics; the
+ * caller zeroes) grad_vertices [n_vertices,3], grad_normals [n_vertices,3] (the interpolated vertex normals as independent
+ * inputs; their dependence on the positions, mesh.cpp:321-375, is chained by the caller) and grad_eta [n_shapes]; each of the
+ * three may be NULL. Which triangle is hit, absorption and total internal reflection are detached, as in the reference's AD;
+ * dead rays contribute nothing. max_interactions <= 32. */
+int lrt_scene_trace_refractive_backward(const lrt_scene *s, int64_t n, const float *od6_dev, const float *shape_eta_dev,
+                                        int32_t max_interactions, const float *grad_out8_dev, float *grad_od6_dev,
+                                        float *grad_vertices_dev, float *grad_normals_dev, float *grad_eta_dev, void *stream);
 /* Scene::ray_intersect_preliminary / ray_test (src/render/scene.cpp:181-210) for n rays:
  * od7 = o[3], d[3], maxt; out4 = t, u, v, primitive index (-1: miss; t = inf). */
 int lrt_scene_intersect(const lrt_scene *s, int32_t any_hit, int64_t n, const float *od7_dev, float *out4_dev, void *stream);

@@ -226,6 +226,63 @@ class MeshLens:
             out.index_add_(0, F[:, k], n * ang[:, None])
         return torch.nn.functional.normalize(out, dim=1).float().contiguous()
 
+    # ---- the differentiable route: table rows -> vertices -> vertex normals -> trace, with the adjoint kernel behind autograd
+    def vertices_of(self, rows):
+        """Vertex positions [nv,3] (float32, CUDA) as a differentiable function of the table rows (torch tensor [n,16]): what
+        update() writes, as an expression — the sag in float64, rounded once."""
+        import torch
+        rows = torch.as_tensor(rows, device="cuda").double()
+        z = self.vertices[:, 2].detach().double().clone()
+        for (i, a, b), xy in zip(self.cap_slices, self._xy):
+            z[a:b] = sag(rows[i], xy[:, 0], xy[:, 1], xp=torch)
+        for (i, a, n, _), xy in zip(self.baffle_slices, self._rim_xy):
+            zr = sag(rows[i], xy[:, 0], xy[:, 1], xp=torch)
+            z[a:a + n] = zr; z[a + n:a + 2 * n] = zr
+        return torch.cat([self.vertices[:, :2].detach().double(), z[:, None]], 1).float()
+
+    def eta_of(self, rows):
+        """Relative index of every shape (caps: ior_left / ior_right of their row; baffles: 0 = absorber), differentiable."""
+        import torch
+        rows = torch.as_tensor(rows, device="cuda").double()
+        eta = self.eta.detach().double().clone()
+        k = 0
+        for i in range(self.n_surfaces):
+            if any(ci == i for (ci, _, _) in self.cap_slices):
+                eta[k] = rows[i, 13] / rows[i, 14]; k += 1
+            k += 1                                                    # the surface's baffle
+        return eta.float()
+
+    def trace_ad(self, rows, o, d):
+        """trace() as a differentiable function of the table rows (and of the rays): moves the vertices onto the surfaces of
+        `rows`, refits the BVH, traces; backward runs lrt_scene_trace_refractive_backward and torch chains its vertex / normal /
+        index gradients through the vertex normals (mesh.cpp:321-375) and the sag function down to `rows`.
+        The scene must not be moved again between this call and backward(): the adjoint kernel replays the trace."""
+        import torch
+        V = self.vertices_of(rows)
+        N = self._vertex_normals(V) if self.smooth else None
+        od = torch.cat([torch.as_tensor(o, dtype=torch.float32, device="cuda").reshape(-1, 3),
+                        torch.as_tensor(d, dtype=torch.float32, device="cuda").reshape(-1, 3)], 1)
+        out = _RefractiveTrace.apply(self, V, N, self.eta_of(rows), od)
+        return out[:, 0:3], out[:, 3:6], out[:, 6] > 0, out[:, 7]
+
+    def spot_positions_ad(self, rows, src_p, n, seed=0, origin_offset=0.0):
+        """spot_positions() with the landing points differentiable in `rows`: (pf [n,2], alive)."""
+        ap, d, o = self._spot_rays(src_p, n, seed, origin_offset)
+        po, pd, alive, w = self.trace_ad(rows, o, d)
+        t = -po[:, 2] / pd[:, 2]
+        return (po + t[:, None] * pd)[:, :2], alive & (pd[:, 2] < 0)
+
+    def _spot_rays(self, src_p, n, seed, origin_offset):
+        import torch
+        g = torch.Generator(device="cuda").manual_seed(seed)
+        u = torch.rand((n, 2), device="cuda", generator=g)
+        r, phi = float(self.rows0[-1, 2]) * torch.sqrt(u[:, 0]), 2 * np.pi * u[:, 1]
+        ap = torch.stack([r * torch.cos(phi), r * torch.sin(phi), torch.full_like(r, float(self.rows0[-1, 1]))], 1)
+        src = torch.tensor(np.asarray(src_p, f32), device="cuda")
+        d = torch.nn.functional.normalize(ap - src, dim=1)
+        o = ap - d * float(origin_offset) if origin_offset > 0 else src.expand_as(ap)
+        return ap, d, o
+
     def trace(self, o, d):
         """Rays (camera space, travelling towards -z) through the meshed surfaces: (o, d, alive, weight) torch tensors."""
         import torch
@@ -239,15 +296,61 @@ class MeshLens:
     def spot_positions(self, src_p, n, seed=0, origin_offset=0.0):
         """Film-plane (z = 0) landing points of n rays from the point source `src_p` through uniformly sampled points of the front
         element's disk: the geometric spot diagram (what the notebooks' prb_basic geo_tracer draws, design_problem.py:399-428)."""
-        import torch
-        g = torch.Generator(device="cuda").manual_seed(seed)
-        u = torch.rand((n, 2), device="cuda", generator=g)
-        r, phi = float(self.rows0[-1, 2]) * torch.sqrt(u[:, 0]), 2 * np.pi * u[:, 1]
-        ap = torch.stack([r * torch.cos(phi), r * torch.sin(phi), torch.full_like(r, float(self.rows0[-1, 1]))], 1)
-        src = torch.tensor(np.asarray(src_p, f32), device="cuda")
-        d = torch.nn.functional.normalize(ap - src, dim=1)
-        o = ap - d * float(origin_offset) if origin_offset > 0 else src.expand_as(ap)
+        ap, d, o = self._spot_rays(src_p, n, seed, origin_offset)
         po, pd, alive, w = self.trace(o, d)
         t = -po[:, 2] / pd[:, 2]
         pf = po + t[:, None] * pd
         return pf[:, :2], alive & (pd[:, 2] < 0), ap, d
+
+
+def _make_trace_op():
+    import torch
+
+    class RefractiveTrace(torch.autograd.Function):
+        """lrt_scene_refit + lrt_scene_trace_refractive forward, lrt_scene_trace_refractive_backward backward: the analogue, for the
+        mesh-lens trace, of what Dr.Jit's reverse mode does for the notebooks (design_problem.py:495-584)."""
+
+        @staticmethod
+        def forward(ctx, lens, V, N, eta, od):
+            V = V.detach().contiguous(); od = od.detach().contiguous(); eta = eta.detach().contiguous()
+            Nc = N.detach().contiguous() if N is not None else None
+            capi.check(capi.lib.lrt_scene_refit(lens.scene.handle, capi.dev_ptr(V), capi.dev_ptr(Nc) if Nc is not None else None, capi.stream_ptr()))
+            lens.vertices, lens._normals, lens.eta = V, Nc, eta
+            out = torch.empty((od.shape[0], 8), dtype=torch.float32, device="cuda")
+            capi.check(capi.lib.lrt_scene_trace_refractive(lens.scene.handle, C.c_int64(od.shape[0]), capi.dev_ptr(od), capi.dev_ptr(eta),
+                                                           C.c_int32(lens.n_surfaces + 1), capi.dev_ptr(out), capi.stream_ptr()))
+            ctx.lens, ctx.has_normals = lens, Nc is not None
+            ctx.save_for_backward(V, eta, od)
+            ctx.mark_non_differentiable()
+            return out
+
+        @staticmethod
+        def backward(ctx, grad_out):
+            V, eta, od = ctx.saved_tensors
+            lens = ctx.lens
+            if lens.vertices is not V:
+                raise RuntimeError("the mesh lens was moved between trace_ad() and backward(): the adjoint kernel replays the trace")
+            grad_out = grad_out.contiguous().float()
+            g_od = torch.empty_like(od)
+            g_V = torch.zeros_like(V); g_eta = torch.zeros_like(eta)
+            g_N = torch.zeros_like(V) if ctx.has_normals else None
+            capi.check(capi.lib.lrt_scene_trace_refractive_backward(
+                lens.scene.handle, C.c_int64(od.shape[0]), capi.dev_ptr(od), capi.dev_ptr(eta), C.c_int32(lens.n_surfaces + 1),
+                capi.dev_ptr(grad_out), capi.dev_ptr(g_od), capi.dev_ptr(g_V), capi.dev_ptr(g_N) if g_N is not None else None,
+                capi.dev_ptr(g_eta), capi.stream_ptr()))
+            return None, g_V, g_N, g_eta, g_od
+
+    return RefractiveTrace
+
+
+class _LazyOp:
+    """torch is imported on first use (the package imports without it for host-only work)."""
+    _op = None
+
+    def apply(self, *a):
+        if _LazyOp._op is None:
+            _LazyOp._op = _make_trace_op()
+        return _LazyOp._op.apply(*a)
+
+
+_RefractiveTrace = _LazyOp()

@@ -94,3 +94,156 @@ def test_refit_follows_a_design_step(mi):
     old = mi.mesh_lens.MeshLens(mi, rows, subdiv=4)
     pf0, al0, _, _ = old.spot_positions(src, 8000, seed=2, origin_offset=off)
     assert (pf0[m] - pf1[m]).abs().max().item() > 1e-5
+
+
+# ------------------------------------------------------------------------------------------------ the adjoint (lrt_mesh_adj.cu)
+def _golden():
+    import os
+    return dict(np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_mesh_lens.npz")))
+
+
+def _mesh_trace():
+    import os
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle"))
+    import mesh_trace
+    return mesh_trace
+
+
+@pytest.mark.parametrize("smooth", [True, False])
+def test_trace_adjoint_matches_oracle_reverse_mode(mi, smooth):
+    """lrt_scene_trace_refractive_backward against torch.autograd over the float64 restatement (oracle/mesh_trace.py, itself
+    pinned to the reference build on this very lens: tests/test_mesh_lens_parity.py): gradients with respect to the vertex
+    positions, the vertex normals (as independent inputs), the relative indices and the rays, for a random adjoint of
+    (o, d, weight). Interpolated vertex normals and flat facets."""
+    import torch
+    MT = _mesh_trace()
+    G = _golden()
+    lens = mi.mesh_lens.MeshLens(mi, G["rows"], subdiv=3, smooth=smooth)
+    rng = np.random.default_rng(11)
+    od = np.concatenate([G["rays"], G["rays"] + rng.normal(0, 2e-3, G["rays"].shape).astype(f32) * [1, 1, 0, 1, 1, 0]], 0).astype(f32)
+    od_t = torch.tensor(od, device="cuda")
+    n = len(od)
+    out = torch.empty((n, 8), dtype=torch.float32, device="cuda")
+    capi, lib = mi.capi, mi.capi.lib
+    import ctypes as C
+    K = C.c_int32(lens.n_surfaces + 1)
+    capi.check(lib.lrt_scene_trace_refractive(lens.scene.handle, C.c_int64(n), capi.dev_ptr(od_t), capi.dev_ptr(lens.eta), K, capi.dev_ptr(out), None))
+    torch.cuda.synchronize()
+    # the oracle on the same float32 inputs
+    a = lens.scene.arrays
+    V = torch.tensor(lens.vertices.cpu().numpy(), dtype=torch.float64, requires_grad=True)
+    N = torch.tensor(a["vertex_normals"], dtype=torch.float64, requires_grad=True) if smooth else None
+    eta = torch.tensor(lens.eta.cpu().numpy(), dtype=torch.float64, requires_grad=True)
+    odc = torch.tensor(od, dtype=torch.float64, requires_grad=True)
+    F = torch.tensor(a["indices"].astype(np.int64)); ts = torch.tensor(a["tri_shape"].astype(np.int64))
+    o, d, alive, w = MT.trace(V, F, N, ts, eta, odc[:, :3], odc[:, 3:], lens.n_surfaces + 1)
+    got = out.cpu().numpy()
+    assert (alive.numpy() == (got[:, 6] > 0)).mean() > 0.99
+    both = alive.numpy() & (got[:, 6] > 0)
+    assert both.sum() > 0.8 * n
+    assert np.abs(got[both, 0:3] - o.detach().numpy()[both]).max() < 1e-6 and np.abs(got[both, 3:6] - d.detach().numpy()[both]).max() < 2e-6
+    assert np.abs(got[both, 7] - w.detach().numpy()[both]).max() < 1e-5
+    # a random adjoint of (o, d, weight) for the rays both sides carry through (a ray on a facet edge may be classified differently)
+    g_np = rng.standard_normal((n, 8)).astype(f32) * both[:, None]
+    g_out = torch.tensor(g_np, device="cuda")
+    g_od = torch.empty((n, 6), dtype=torch.float32, device="cuda")
+    g_V = torch.zeros_like(lens.vertices); g_N = torch.zeros_like(lens.vertices); g_eta = torch.zeros_like(lens.eta)
+    capi.check(lib.lrt_scene_trace_refractive_backward(lens.scene.handle, C.c_int64(n), capi.dev_ptr(od_t), capi.dev_ptr(lens.eta), K, capi.dev_ptr(g_out),
+                                                       capi.dev_ptr(g_od), capi.dev_ptr(g_V), capi.dev_ptr(g_N) if smooth else None, capi.dev_ptr(g_eta), None))
+    torch.cuda.synchronize()
+    go = g_out.cpu().double()
+    m = torch.tensor(both)
+    loss = ((o * go[:, 0:3]).sum(1) + (d * go[:, 3:6]).sum(1) + w * go[:, 7])[m].sum()
+    loss.backward()
+    # rays alive on one side only contribute to one side: drop them from the per-ray comparison, bound them in the sums
+    def close(name, x, y, tol):
+        x = x.cpu().double().numpy(); y = y.numpy()
+        err = np.linalg.norm(x - y) / max(np.linalg.norm(y), 1e-30)
+        print(f"smooth={smooth} {name}: |oracle| {np.linalg.norm(y):.4e} rel err {err:.2e}")
+        assert err < tol, (name, err)
+    close("d/d rays", g_od[m.cuda()], odc.grad[m], 2e-4)
+    close("d/d vertices", g_V, V.grad, 5e-4)
+    close("d/d eta", g_eta, eta.grad, 5e-4)
+    if smooth:
+        close("d/d normals", g_N, N.grad, 5e-4)
+
+
+def test_mesh_lens_gradients_match_finite_differences_of_the_reference(mi):
+    """The whole differentiable route of the product — table rows -> vertices (sag) -> vertex normals -> refit -> trace ->
+    landing points, backward through lrt_scene_trace_refractive_backward and torch — against central finite differences of the
+    REFERENCE's own forward on the same meshed singlet (tests/golden/ref_mesh_lens.npz), variable by variable: curvatures, a
+    vertex position, a conic constant, an asphere coefficient."""
+    import torch
+    G = _golden()
+    lens = mi.mesh_lens.MeshLens(mi, G["rows"], subdiv=3)
+    rows = torch.tensor(G["rows"], dtype=torch.float64, device="cuda", requires_grad=True)
+    od = G["rays"]
+    po, pd, alive, w = lens.trace_ad(rows, od[:, :3], od[:, 3:])
+    assert alive.cpu().numpy().tolist() == G["alive"].tolist()
+    t = -po[:, 2] / pd[:, 2]
+    pf = (po + t[:, None] * pd)[:, :2]
+    assert np.abs(pf.detach().cpu().numpy() - G["landing"]).max() < 2e-7
+    a = torch.tensor(np.random.default_rng(3).standard_normal((len(od), 2)), device="cuda")
+    (pf.double() * a).sum().backward()
+    fd = G["fd_landing"]
+    for j, (ri, ci) in enumerate(G["var_index"]):
+        want = float((fd[j] * a.cpu().numpy()).sum()); got = float(rows.grad[ri, ci])
+        print(f"{G['variables'][j]}: product {got:.6e}  reference FD {want:.6e}")
+        assert abs(got - want) <= 1e-2 * abs(want) + 1e-6, (G["variables"][j], got, want)
+    # per-ray Jacobian columns for a few rays
+    for ray in (0, 17, 55, 90):
+        for c in range(2):
+            rows.grad = None
+            po, pd, alive, w = lens.trace_ad(rows, od[:, :3], od[:, 3:])
+            pfr = (po[ray] - po[ray, 2] / pd[ray, 2] * pd[ray])[c]
+            pfr.backward()
+            for j, (ri, ci) in enumerate(G["var_index"]):
+                assert abs(float(rows.grad[ri, ci]) - fd[j, ray, c]) <= 3e-2 * np.abs(fd[j]).max(), (G["variables"][j], ray, c)
+
+
+def test_mesh_lens_gradient_agrees_with_the_analytic_lens_adjoint(mi):
+    """A design loss differentiated through the MESHED doublet (subdivision 5: 2 x 5 000 triangles) equals, up to the meshing
+    error, the same loss differentiated through the ANALYTIC interface table (central differences of the bit-exact lens trace):
+    the two lens representations of the package give the same design gradients for curvatures and vertex positions."""
+    import torch
+    rows_np = doublet_rows(mi)
+    src = mi.lens_design.field_source(2.0, 1.0e3, front_z=float(rows_np[-1, 1]))
+    off = 2.0 * float(rows_np[-1, 2])
+    lens = mi.mesh_lens.MeshLens(mi, rows_np, subdiv=5)
+    rows = torch.tensor(rows_np, dtype=torch.float64, device="cuda", requires_grad=True)
+    pf, alive = lens.spot_positions_ad(rows, src, 20000, seed=4, origin_offset=off)
+    ap, d, o = lens._spot_rays(src, 20000, 4, off)
+    R = float(rows_np[-1, 2])
+    inner = alive & (ap[:, :2].norm(dim=1) < 0.9 * R)
+    # a loss LINEAR in the landing points (defocus-like moment + centroid): its gradient does not pick up the facet noise of the
+    # landing points themselves, only the meshing error of their derivatives
+    def design_loss(pf, apxy, m):
+        return ((pf[m] * apxy[m]).sum(1).mean() / R + pf[m][:, 0].mean())
+    loss = design_loss(pf.double(), ap[:, :2].double(), inner)
+    loss.backward()
+    g_mesh = rows.grad.cpu().numpy()
+    # the same rays through the analytic table, differentiated by central differences of the (float32, bit-exact) lens trace
+    o_np, d_np, ap_np, in_np = o.cpu().numpy(), d.cpu().numpy(), ap.cpu().numpy(), inner.cpu().numpy()
+
+    def analytic_fd(rp, rm):
+        """central difference over the rays BOTH perturbed tables transmit (a ray that one of them vignettes would turn the
+        difference quotient into the derivative of the mask)"""
+        (qp, actp), (qm, actm) = (analytic_positions(mi, r.astype(f32), ap_np, d_np, off) for r in (rp, rm))
+        m = in_np & actp & actm
+        assert m.sum() > 0.99 * in_np.sum()
+        val = lambda q: ((q[m].astype(np.float64) * ap_np[m, :2]).sum(1).mean() / R + q[m][:, 0].astype(np.float64).mean())  # noqa: E731
+        return val(qp) - val(qm)
+    groups = {"curvature": [(2, 3, 1e-3), (1, 3, 1e-3), (0, 3, 1e-3)], "vertex z": [(2, 1, 1e-4), (1, 1, 1e-4), (0, 1, 1e-4)]}
+    for name, cols in groups.items():
+        pairs = []
+        for ri, ci, h in cols:
+            rp, rm = rows_np.astype(np.float64).copy(), rows_np.astype(np.float64).copy()
+            rp[ri, ci] += h; rm[ri, ci] -= h
+            rp, rm = rp.astype(f32), rm.astype(f32)
+            fdv = analytic_fd(rp, rm) / (float(rp[ri, ci]) - float(rm[ri, ci]))
+            pairs.append((g_mesh[ri, ci], fdv))
+            print(f"{name} row {ri}: mesh adjoint {g_mesh[ri, ci]:.5e}  analytic FD {fdv:.5e}")
+        scale = max(abs(f) for _, f in pairs)
+        for gm, fdv in pairs:
+            assert abs(gm - fdv) <= 0.01 * scale, (name, gm, fdv)
