@@ -63,6 +63,15 @@ int lrt_sensor_create_prescription(int32_t n, const int32_t *kinds, const float 
                                    int32_t fine_focus, float object_distance, const lrt_film_geom *film,
                                    const float *to_world16, float near_clip, float far_clip,
                                    lrt_sensor **out);
+/* The same camera as a SPECTRAL variant builds it (the fork's `*_spectral*` dispersion mode): identical, except that the
+ * autofocus traces rays of Wavelength(589.3f) nm (:2122-2146), so the nominal IORs of the table are taken at 0.001f * 589.3f um —
+ * one ulp above the rgb variants' 0.5893f. Use with the wavelength-aware entry points below. */
+int lrt_sensor_create_prescription_spectral(int32_t n, const int32_t *kinds, const float *thickness_mm,
+                                            const float *radius_mm, const float *semi_diameter_mm, const float *kappa,
+                                            const float *ai7, const float *mats7, float scale, float stop_ratio,
+                                            int32_t fine_focus, float object_distance, const lrt_film_geom *film,
+                                            const float *to_world16, float near_clip, float far_clip,
+                                            lrt_sensor **out);
 /* Same camera from ready-made interfaces (rear -> front, metres), rows of 16 floats:
  * [kind, z, semi_diameter, R (sphere) | c,K,r_scale (asphere, unitless as :557-572), -, a0..a6 at [6..12],
  *  ior_left (film side), ior_right, -]. Used for the parametric designs (:936-975, :1322-1370) and for
@@ -101,6 +110,23 @@ float lrt_radical_inverse(int32_t base_index, uint64_t index);
 int lrt_sensor_sample_ray(const lrt_sensor *s, int64_t n, const float *pos2_dev, const float *ap2_dev,
                           float *out10_dev, void *stream);
 int lrt_sensor_sample_ray_host(const lrt_sensor *s, int64_t n, const float *pos2, const float *ap2, float *out10);
+/* Dispersion (the spectral variants of the fork: DispersiveMaterial::compute_ior(ray), realisticlens.cpp:169-183,226-240):
+ * every ray carries a wavelength in nm (the FIRST entry of the reference's wavelength vector) and each interface refracts
+ * with the IORs of its two media at that wavelength — Cauchy A + B / w^2 or Sellmeier sqrt(1 + sum B_i w^2 / (w^2 - C_i)),
+ * w = 0.001 * wavelength in um. Sensors built from a prescription carry their media; sensors built from ready-made
+ * interfaces need lrt_sensor_set_materials: per interface (rear -> front) two rows of 7 floats, left (film side) then right,
+ * [0, A, B, -, -, -, -] or [1, B1, B2, B3, C1, C2, C3].
+ * lrt_sensor_sample_ray_wl = Sensor::sample_ray of a spectral variant, geometric part: out10 as lrt_sensor_sample_ray (the
+ * caller multiplies the weight by sample_wavelengths()' own). lrt_sensor_trace_wl = trace_ray_from_film / _from_world with the
+ * ray's wavelength, on the device: od6 / out7 as lrt_sensor_trace_host. Rear-element sampling only. */
+int lrt_sensor_set_materials(lrt_sensor *s, int32_t n, const float *mat_lr14);
+int lrt_sensor_get_materials(const lrt_sensor *s, float *mat_lr14);
+int lrt_sensor_sample_ray_wl(const lrt_sensor *s, int64_t n, const float *pos2_dev, const float *ap2_dev,
+                             const float *wavelength_nm_dev, float *out10_dev, void *stream);
+int lrt_sensor_trace_wl(const lrt_sensor *s, int32_t from_world, int64_t n, const float *od6_dev,
+                        const float *wavelength_nm_dev, float *out7_dev, void *stream);
+int lrt_sensor_trace_wl_host(const lrt_sensor *s, int32_t from_world, int64_t n, const float *od6,
+                             const float *wavelength_nm, float *out7);
 /* trace_ray_from_film / trace_ray_from_world (:1654-1683 / :1960-1984) in camera space:
  * od6 = o[3], d[3]; out7 = o[3], d[3], active (1/0). */
 int lrt_sensor_trace_host(const lrt_sensor *s, int32_t from_world, int64_t n, const float *od6, float *out7);

@@ -49,5 +49,8 @@ struct lrt_sensor {
     // host -> dev if dirty, ordered on `stream` (renders launched earlier on that stream keep reading the old table)
     int upload(cudaStream_t stream = nullptr);
     bool host_stale = false;              // the device table is newer than `host.ifs` (lrt_sensor_set_interfaces_dev)
+    // dispersion mode (spectral variants): per interface the Cauchy / Sellmeier rows of its two media (left 7, right 7), in the
+    // order of host.ifs; empty when the sensor was built from ready-made interfaces and lrt_sensor_set_materials was not called
+    std::vector<float> mat_lr; float *d_mat_lr = nullptr;
     int sync_host();
 };

@@ -240,7 +240,7 @@ LRT_HD LensHit hit_asphere(const LensIf &f, const LensRay &ray) {
 
 // LensInterface::compute_interaction (:269-297) / ApertureStop (:505-517).
 // Returns the `active` mask of the reference; `ray` is advanced only when active.
-LRT_HD bool lens_interact(const LensIf &f, LensRay &ray) {
+template <bool kOwnEta> LRT_HD bool lens_interact_t(const LensIf &f, LensRay &ray, float eta_ray, float rcp_eta_ray) {
     using namespace strict;
     LensHit si = f.kind == IF_SPHERE ? hit_sphere(f, ray) : (f.kind == IF_ASPHERE ? hit_asphere(f, ray) : hit_plane(f, ray));
     bool active = si.t != inf_f();
@@ -252,13 +252,43 @@ LRT_HD bool lens_interact(const LensIf &f, LensRay &ray) {
     V3 wi = neg(ray.d);
     float cos_theta_i = dot(wi, si.n);
     float r, ct, eti;
-    lens_fresnel(cos_theta_i, f.eta, f.rcp_eta, r, ct, eti);
+    if (kOwnEta) lens_fresnel(cos_theta_i, eta_ray, rcp_eta_ray, r, ct, eti);
+    else lens_fresnel(cos_theta_i, f.eta, f.rcp_eta, r, ct, eti);
     active = active && (r <= kOneMinusEpsilon);
     // refract (fresnel.h:311-315): fmsub(m, fmadd(dot(wi,m), eta_ti, cos_theta_t), wi*eta_ti)
     float g = fmadd(cos_theta_i, eti, ct);
     V3 d_out = v3(sub(mul(si.n.x, g), mul(wi.x, eti)), sub(mul(si.n.y, g), mul(wi.y, eti)), sub(mul(si.n.z, g), mul(wi.z, eti)));
     if (active) { ray.o = si.p; ray.d = d_out; }
     return active;
+}
+
+LRT_HD bool lens_interact(const LensIf &f, LensRay &ray) { return lens_interact_t<false>(f, ray, 0.f, 0.f); }
+
+// ---- the spectral variants' lens step (`*_spectral*`, the fork's dispersion mode): every ray carries a wavelength and
+// DispersiveMaterial::compute_ior(ray) (:169-183) evaluates both media of every interface at 0.001 * wavelengths[0]
+// (nm -> um): Cauchy A + B / w^2 or Sellmeier sqrt(1 + sum B_i w^2 / (w^2 - C_i)) (:226-240). mat = 7 floats
+// [0 = Cauchy | 1 = Sellmeier, A, B, -, -, -, -] or [1, B1, B2, B3, C1, C2, C3]; mat_lr = per interface (left 7, right 7).
+LRT_HD float lens_material_ior(const float *m, float w_um) {
+    using namespace strict;
+    const float w2 = sqr(w_um);
+    if (m[0] == 0.f) return add(m[1], div(m[2], w2));
+    float ior = 1.f;
+    ior = add(ior, div(mul(m[1], w2), sub(w2, m[4])));
+    ior = add(ior, div(mul(m[2], w2), sub(w2, m[5])));
+    ior = add(ior, div(mul(m[3], w2), sub(w2, m[6])));
+    return sqrt(ior);
+}
+LRT_HD bool lens_interact_wl(const LensIf &f, LensRay &ray, const float *mat_lr, float w_um) {
+    // compute_interaction (:279-284): ext_ior = left, int_ior = right, eta = int / ext; fresnel() takes its own reciprocal
+    const float ext_ior = lens_material_ior(mat_lr, w_um), int_ior = lens_material_ior(mat_lr + 7, w_um);
+    const float eta = strict::div(int_ior, ext_ior);
+    return lens_interact_t<true>(f, ray, eta, strict::rcp(eta));
+}
+LRT_HD bool lens_trace_wl(const LensIf *ifs, int n, LensRay &ray, const float *mat_lr, float wavelength_nm, bool from_world) {
+    const float w_um = strict::mul(0.001f, wavelength_nm);
+    if (from_world) { for (int i = n - 1; i >= 0; --i) if (!lens_interact_wl(ifs[i], ray, mat_lr + 14 * i, w_um)) return false; }
+    else { for (int i = 0; i < n; ++i) if (!lens_interact_wl(ifs[i], ray, mat_lr + 14 * i, w_um)) return false; }
+    return true;
 }
 
 LRT_HD bool lens_trace_from_film(const LensIf *ifs, int n, LensRay &ray) {
@@ -309,7 +339,13 @@ LRT_HD strict::V3 lens_sample_exit_pupil(const LensSystem &L, strict::V3 film_p,
     return v3(sub(mul(cos_t, px), mul(sin_t, py)), add(mul(sin_t, px), mul(cos_t, py)), L.rear_z);
 }
 
-LRT_HD CameraRay lens_sample_ray(const LensSystem &L, const LensIf *ifs, float u, float v, float a, float b) {
+struct TraceFromFilm { const LensIf *ifs; int n; LRT_HD bool operator()(LensRay &ray) const { return lens_trace_from_film(ifs, n, ray); } };
+struct TraceFromFilmWl {
+    const LensIf *ifs; int n; const float *mat_lr; float wavelength_nm;
+    LRT_HD bool operator()(LensRay &ray) const { return lens_trace_wl(ifs, n, ray, mat_lr, wavelength_nm, false); }
+};
+
+template <class Trace> LRT_HD CameraRay lens_sample_ray_with(const LensSystem &L, float u, float v, float a, float b, const Trace &trace) {
     using namespace strict;
     V3 film_p = v3(add(mul(L.s2f_m00, u), L.s2f_m03), add(mul(L.s2f_m11, v), L.s2f_m13), 0.f);
     V3 ap; float bounds_area = 0.f;
@@ -319,7 +355,7 @@ LRT_HD CameraRay lens_sample_ray(const LensSystem &L, const LensIf *ifs, float u
         ap = v3(mul(L.rear_radius, dx), mul(L.rear_radius, dy), L.rear_z);
     }
     LensRay ray; ray.o = film_p; ray.d = normalize(sub(ap, film_p));
-    bool active = lens_trace_from_film(ifs, L.n, ray);
+    bool active = trace(ray);
     V3 dl = ray.d, o = ray.o;
     o.z = add(o.z, L.film_z);
     const float *m = L.to_world;
@@ -340,6 +376,13 @@ LRT_HD CameraRay lens_sample_ray(const LensSystem &L, const LensIf *ifs, float u
     r.weight = active ? w : 0.f;
     r.active = active; r.d_local = f3(dl);
     return r;
+}
+LRT_HD CameraRay lens_sample_ray(const LensSystem &L, const LensIf *ifs, float u, float v, float a, float b) {
+    return lens_sample_ray_with(L, u, v, a, b, TraceFromFilm { ifs, L.n });
+}
+// the spectral variants' sample_ray: the geometric part (the caller multiplies the weight by sample_wavelengths()' own)
+LRT_HD CameraRay lens_sample_ray_wl(const LensSystem &L, const LensIf *ifs, const float *mat_lr, float wavelength_nm, float u, float v, float a, float b) {
+    return lens_sample_ray_with(L, u, v, a, b, TraceFromFilmWl { ifs, L.n, mat_lr, wavelength_nm });
 }
 
 

@@ -227,6 +227,47 @@ __global__ void __launch_bounds__(256) k_sample_ray(const LensSystem *__restrict
     }
 }
 
+// the spectral variants' sample_ray / lens trace: one wavelength (nm) per ray, IORs from the media's dispersion formulas
+__global__ void __launch_bounds__(256) k_sample_ray_wl(const LensSystem *__restrict__ Lg, const float *__restrict__ mat_lr, int64_t n,
+                                                        const float2 *__restrict__ pos, const float2 *__restrict__ ap,
+                                                        const float *__restrict__ wl, float *__restrict__ out10) {
+    __shared__ LensSystem L;
+    __shared__ float M[kMaxInterfaces * 14];
+    {
+        const uint4 *src = reinterpret_cast<const uint4 *>(Lg);
+        uint4 *dst = reinterpret_cast<uint4 *>(&L);
+        for (int i = threadIdx.x; i < (int) (sizeof(LensSystem) / 16); i += blockDim.x) dst[i] = src[i];
+        for (int i = threadIdx.x; i < Lg->n * 14; i += blockDim.x) M[i] = mat_lr[i];
+    }
+    __syncthreads();
+    for (int64_t i = blockIdx.x * (int64_t) blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) {
+        float2 p = pos[i], q = ap[i];
+        CameraRay r = lens_sample_ray_wl(L, L.ifs, M, wl[i], p.x, p.y, q.x, q.y);
+        float *o = out10 + 10 * i;
+        o[0] = r.o.x; o[1] = r.o.y; o[2] = r.o.z; o[3] = r.d.x; o[4] = r.d.y; o[5] = r.d.z;
+        o[6] = r.maxt; o[7] = o[8] = o[9] = r.weight;
+    }
+}
+__global__ void __launch_bounds__(256) k_trace_wl(const LensSystem *__restrict__ Lg, const float *__restrict__ mat_lr, int from_world, int64_t n,
+                                                   const float *__restrict__ od6, const float *__restrict__ wl, float *__restrict__ out7) {
+    __shared__ LensSystem L;
+    __shared__ float M[kMaxInterfaces * 14];
+    {
+        const uint4 *src = reinterpret_cast<const uint4 *>(Lg);
+        uint4 *dst = reinterpret_cast<uint4 *>(&L);
+        for (int i = threadIdx.x; i < (int) (sizeof(LensSystem) / 16); i += blockDim.x) dst[i] = src[i];
+        for (int i = threadIdx.x; i < Lg->n * 14; i += blockDim.x) M[i] = mat_lr[i];
+    }
+    __syncthreads();
+    for (int64_t i = blockIdx.x * (int64_t) blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) {
+        const float *r = od6 + 6 * i;
+        LensRay ray; ray.o = strict::v3(r[0], r[1], r[2]); ray.d = strict::v3(r[3], r[4], r[5]);
+        const bool a = lens_trace_wl(L.ifs, L.n, ray, M, wl[i], from_world != 0);
+        float *o = out7 + 7 * i;
+        o[0] = ray.o.x; o[1] = ray.o.y; o[2] = ray.o.z; o[3] = ray.d.x; o[4] = ray.d.y; o[5] = ray.d.z; o[6] = a ? 1.f : 0.f;
+    }
+}
+
 __global__ void __launch_bounds__(256) k_sampler_draw(uint32_t seed, uint32_t idx0, int64_t n, int ndraw, float *__restrict__ out) {
     for (int64_t i = blockIdx.x * (int64_t) blockDim.x + threadIdx.x; i < n; i += (int64_t) gridDim.x * blockDim.x) {
         Pcg32 rng; rng.seed_sample(seed, idx0 + (uint32_t) i);
@@ -328,11 +369,11 @@ uint64_t lrt_launch_count(void) { return g_launches.load(); }
 int lrt_device_count(void) { int c = 0; if (cudaGetDeviceCount(&c) != cudaSuccess) { cudaGetLastError(); return 0; } return c; }
 int lrt_set_device(int device) { LRT_NEED_DEVICE(); LRT_CUDA(cudaSetDevice(device)); return LRT_OK; }
 
-int lrt_sensor_create_prescription(int32_t n, const int32_t *kinds, const float *thick, const float *curv,
-                                   const float *elemr, const float *kappa, const float *ai7, const float *mats7,
-                                   float scale, float stop_ratio, int32_t fine_focus, float object_distance,
-                                   const lrt_film_geom *film, const float *tw, float near_clip, float far_clip,
-                                   lrt_sensor **out) {
+static int create_prescription(int32_t n, const int32_t *kinds, const float *thick, const float *curv,
+                               const float *elemr, const float *kappa, const float *ai7, const float *mats7,
+                               float scale, float stop_ratio, int32_t fine_focus, float object_distance,
+                               const lrt_film_geom *film, const float *tw, float near_clip, float far_clip,
+                               float nominal_um, lrt_sensor **out) {
     LRT_REQUIRE(n > 0 && n <= kMaxInterfaces, "lens must have 1..32 interfaces");
     LRT_REQUIRE(kinds && thick && curv && elemr && kappa && ai7 && mats7 && film && tw && out, "null argument");
     lrt_sensor *s = new lrt_sensor();
@@ -343,7 +384,10 @@ int lrt_sensor_create_prescription(int32_t n, const int32_t *kinds, const float 
     for (int i = n - 1; i >= 0; --i) {
         float elem_radius = elemr[i];
         z_pos += thick[i];
-        float il = material_ior(mats7 + 7 * (i + 1), 0.5893f), ir = material_ior(mats7 + 7 * i, 0.5893f);
+        float il = material_ior(mats7 + 7 * (i + 1), nominal_um), ir = material_ior(mats7 + 7 * i, nominal_um);
+        // the two media of this interface, for the per-ray IOR of the dispersion mode (the stop sits inside its left medium)
+        s->mat_lr.insert(s->mat_lr.end(), mats7 + 7 * (i + 1), mats7 + 7 * (i + 1) + 7);
+        { const float *right = kinds[i] == IF_APERTURE ? mats7 + 7 * (i + 1) : mats7 + 7 * i; s->mat_lr.insert(s->mat_lr.end(), right, right + 7); }
         LensIf f;
         switch (kinds[i]) {
             case IF_APERTURE: f = blank(IF_APERTURE, 0.001f * scale * z_pos, 0.001f * scale * elem_radius * stop_ratio, il, il); break;
@@ -367,6 +411,25 @@ int lrt_sensor_create_prescription(int32_t n, const int32_t *kinds, const float 
     if (rc != LRT_OK) { delete s; return rc; }
     *out = s;
     return LRT_OK;
+}
+
+int lrt_sensor_create_prescription(int32_t n, const int32_t *kinds, const float *thick, const float *curv,
+                                   const float *elemr, const float *kappa, const float *ai7, const float *mats7,
+                                   float scale, float stop_ratio, int32_t fine_focus, float object_distance,
+                                   const lrt_film_geom *film, const float *tw, float near_clip, float far_clip,
+                                   lrt_sensor **out) {
+    return create_prescription(n, kinds, thick, curv, elemr, kappa, ai7, mats7, scale, stop_ratio, fine_focus, object_distance, film, tw,
+                               near_clip, far_clip, 0.5893f, out);              // compute_ior(Float(0.5893f)), :170-173
+}
+int lrt_sensor_create_prescription_spectral(int32_t n, const int32_t *kinds, const float *thick, const float *curv,
+                                            const float *elemr, const float *kappa, const float *ai7, const float *mats7,
+                                            float scale, float stop_ratio, int32_t fine_focus, float object_distance,
+                                            const lrt_film_geom *film, const float *tw, float near_clip, float far_clip,
+                                            lrt_sensor **out) {
+    // the spectral variants focus with rays of Wavelength(589.3f) nm (:2122-2146), i.e. IORs at 0.001f * 589.3f um — one ulp
+    // above the rgb variants' 0.5893f
+    return create_prescription(n, kinds, thick, curv, elemr, kappa, ai7, mats7, scale, stop_ratio, fine_focus, object_distance, film, tw,
+                               near_clip, far_clip, 0.001f * 589.3f, out);
 }
 
 int lrt_sensor_create_interfaces(int32_t n, const float *rows16, float film_z, int32_t fine_focus, float object_distance,
@@ -416,6 +479,7 @@ int lrt_sensor_create_perspective(float x_fov_deg, const lrt_film_geom *film, co
 void lrt_sensor_destroy(lrt_sensor *s) {
     if (!s) return;
     if (s->dev) cudaFree(s->dev);
+    if (s->d_mat_lr) cudaFree(s->d_mat_lr);
     if (s->staging) cudaFreeHost(s->staging);
     if (s->staged) cudaEventDestroy(s->staged);
     delete s;
@@ -505,6 +569,57 @@ int lrt_sensor_sample_ray(const lrt_sensor *s_, int64_t n, const float *pos2, co
     return LRT_OK;
 }
 
+static int upload_materials(lrt_sensor *s, cudaStream_t stream) {
+    LRT_REQUIRE(s->host.kind == 0 && (int) s->mat_lr.size() == 14 * s->host.n,
+                "this sensor has no dispersion data: build it from a prescription or call lrt_sensor_set_materials");
+    LRT_REQUIRE(!s->host.pupil_mode, "the wavelength-aware entry points sample the rear element (the spectral exit-pupil LUT is not built)");
+    if (!s->d_mat_lr) {
+        LRT_CUDA(cudaMalloc(&s->d_mat_lr, sizeof(float) * 14 * kMaxInterfaces));
+        LRT_CUDA(cudaMemcpyAsync(s->d_mat_lr, s->mat_lr.data(), sizeof(float) * s->mat_lr.size(), cudaMemcpyHostToDevice, stream));
+        LRT_CUDA(cudaStreamSynchronize(stream));        // mat_lr is pageable host memory
+    }
+    return LRT_OK;
+}
+
+int lrt_sensor_set_materials(lrt_sensor *s, int32_t n, const float *mat_lr14) {
+    LRT_REQUIRE(s && mat_lr14 && s->host.kind == 0 && n == s->host.n, "lrt_sensor_set_materials: one (left, right) pair of 7-float rows per interface");
+    for (int i = 0; i < 2 * n; ++i)
+        LRT_REQUIRE(mat_lr14[7 * i] == 0.f || mat_lr14[7 * i] == 1.f, "material row: first entry 0 (Cauchy) or 1 (Sellmeier)");
+    s->mat_lr.assign(mat_lr14, mat_lr14 + 14 * (size_t) n);
+    if (s->d_mat_lr) { LRT_CUDA(cudaDeviceSynchronize()); LRT_CUDA(cudaFree(s->d_mat_lr)); s->d_mat_lr = nullptr; }
+    return LRT_OK;
+}
+int lrt_sensor_get_materials(const lrt_sensor *s, float *mat_lr14) {
+    LRT_REQUIRE(s && mat_lr14 && (int) s->mat_lr.size() == 14 * s->host.n, "this sensor has no dispersion data");
+    memcpy(mat_lr14, s->mat_lr.data(), sizeof(float) * s->mat_lr.size());
+    return LRT_OK;
+}
+
+int lrt_sensor_sample_ray_wl(const lrt_sensor *s_, int64_t n, const float *pos2, const float *ap2, const float *wl_nm, float *out10, void *stream) {
+    LRT_NEED_DEVICE();
+    LRT_REQUIRE(s_ && n >= 0 && (n == 0 || (pos2 && ap2 && wl_nm && out10)), "bad argument");
+    if (n == 0) return LRT_OK;
+    lrt_sensor *s = const_cast<lrt_sensor *>(s_);
+    int rc = s->upload((cudaStream_t) stream); if (rc) return rc;
+    rc = upload_materials(s, (cudaStream_t) stream); if (rc) return rc;
+    k_sample_ray_wl<<<grid_for(n, 256), 256, 0, (cudaStream_t) stream>>>(s->dev, s->d_mat_lr, n, (const float2 *) pos2, (const float2 *) ap2, wl_nm, out10);
+    LRT_LAUNCHED();
+    LRT_CUDA(cudaGetLastError());
+    return LRT_OK;
+}
+int lrt_sensor_trace_wl(const lrt_sensor *s_, int32_t from_world, int64_t n, const float *od6, const float *wl_nm, float *out7, void *stream) {
+    LRT_NEED_DEVICE();
+    LRT_REQUIRE(s_ && n >= 0 && (n == 0 || (od6 && wl_nm && out7)), "bad argument");
+    if (n == 0) return LRT_OK;
+    lrt_sensor *s = const_cast<lrt_sensor *>(s_);
+    int rc = s->upload((cudaStream_t) stream); if (rc) return rc;
+    rc = upload_materials(s, (cudaStream_t) stream); if (rc) return rc;
+    k_trace_wl<<<grid_for(n, 256), 256, 0, (cudaStream_t) stream>>>(s->dev, s->d_mat_lr, from_world, n, od6, wl_nm, out7);
+    LRT_LAUNCHED();
+    LRT_CUDA(cudaGetLastError());
+    return LRT_OK;
+}
+
 int lrt_sensor_sample_ray_host(const lrt_sensor *s, int64_t n, const float *pos2, const float *ap2, float *out10) {
     LRT_NEED_DEVICE();
     LRT_REQUIRE(s && n >= 0 && (n == 0 || (pos2 && ap2 && out10)), "bad argument");
@@ -528,6 +643,21 @@ int lrt_sensor_trace_host(const lrt_sensor *s, int32_t from_world, int64_t n, co
         const float *r = od6 + 6 * i;
         LensRay ray; ray.o = strict::v3(r[0], r[1], r[2]); ray.d = strict::v3(r[3], r[4], r[5]);
         bool a = from_world ? lens_trace_from_world(s->host.ifs, s->host.n, ray) : lens_trace_from_film(s->host.ifs, s->host.n, ray);
+        float *o = out7 + 7 * i;
+        o[0] = ray.o.x; o[1] = ray.o.y; o[2] = ray.o.z; o[3] = ray.d.x; o[4] = ray.d.y; o[5] = ray.d.z; o[6] = a ? 1.f : 0.f;
+    }
+    return LRT_OK;
+}
+
+// host-side twin of lrt_sensor_trace_wl (same LRT_HD code), like lrt_sensor_trace_host
+int lrt_sensor_trace_wl_host(const lrt_sensor *s, int32_t from_world, int64_t n, const float *od6, const float *wl_nm, float *out7) {
+    if (s) { int rc_ = const_cast<lrt_sensor *>(s)->sync_host(); if (rc_) return rc_; }
+    LRT_REQUIRE(s && od6 && wl_nm && out7 && n >= 0 && s->host.kind == 0, "bad argument");
+    LRT_REQUIRE((int) s->mat_lr.size() == 14 * s->host.n, "this sensor has no dispersion data: build it from a prescription or call lrt_sensor_set_materials");
+    for (int64_t i = 0; i < n; ++i) {
+        const float *r = od6 + 6 * i;
+        LensRay ray; ray.o = strict::v3(r[0], r[1], r[2]); ray.d = strict::v3(r[3], r[4], r[5]);
+        bool a = lens_trace_wl(s->host.ifs, s->host.n, ray, s->mat_lr.data(), wl_nm[i], from_world != 0);
         float *o = out7 + 7 * i;
         o[0] = ray.o.x; o[1] = ray.o.y; o[2] = ray.o.z; o[3] = ray.d.x; o[4] = ray.d.y; o[5] = ray.d.z; o[6] = a ? 1.f : 0.f;
     }

@@ -84,6 +84,7 @@ class InterfaceList:
     film_z: np.float32 = f32(0)
     fine_focus: bool = True
     stop_ratio: np.float32 = f32(1)
+    materials: np.ndarray | None = None      # [n,2,7] Cauchy / Sellmeier rows of every interface's (left, right) media: dispersion mode
 
 
 def prescription_from_preset(name: str, stop_ratio=1.0) -> Prescription:
@@ -116,7 +117,11 @@ def _row(kind, z, elem_r, curv=0.0, il=1.0, ir=1.0):
     return r
 
 
-def singlet(object_distance, curvature_radius, lens_radius) -> InterfaceList:
+NOMINAL_RGB = f32(0.5893)                          # compute_ior(Float(0.5893f)), realisticlens.cpp:170-173
+NOMINAL_SPECTRAL = f32(f32(0.001) * f32(589.3))    # compute_ior(0.001f * ray.wavelengths[0]) with Wavelength(589.3f) focus rays
+
+
+def singlet(object_distance, curvature_radius, lens_radius, nominal=NOMINAL_RGB) -> InterfaceList:
     """realisticlens.cpp:936-954 (biconvex singlet placed by the thin-lens equation)."""
     od, R, lr = f32(object_distance), f32(curvature_radius), f32(lens_radius)
     distance = max(od, f32(f32(4.001) * R))
@@ -124,12 +129,12 @@ def singlet(object_distance, curvature_radius, lens_radius) -> InterfaceList:
     q = f32(f32(lr / R) * f32(lr / R))
     thick = f32(f32(f32(2) * R) * f32(f32(1) - np.sqrt(f32(f32(1) - q))))
     glass = np.array([0, 1.5046, f32(f32(5) * f32(0.00420)), 0, 0, 0, 0], f32)
-    na, ng = material_ior(_AIR), material_ior(glass)
+    na, ng = material_ior(_AIR, nominal), material_ior(glass, nominal)
     rows = np.stack([_row(0, z, lr, R, na, ng), _row(0, f32(z + thick), lr, -R, ng, na)])
-    return InterfaceList(rows)
+    return InterfaceList(rows, materials=np.array([[_AIR, glass], [glass, _AIR]], f32))
 
 
-def doublet(object_distance, R, lens_radius) -> InterfaceList:
+def doublet(object_distance, R, lens_radius, nominal=NOMINAL_RGB) -> InterfaceList:
     """realisticlens.cpp:957-975 (plano / sphere / sphere / stop)."""
     od, R, lr = f32(object_distance), f32(R), f32(lens_radius)
     fl = f32(f32(2) * R)
@@ -139,21 +144,21 @@ def doublet(object_distance, R, lens_radius) -> InterfaceList:
     thick = f32(f32(f32(2) * R) * f32(f32(1) - np.sqrt(f32(f32(1) - q))))
     g1 = np.array([0, 1.5046, 0.00420, 0, 0, 0, 0], f32)
     g2 = np.array([0, 1.5046, 0.00860948454, 0, 0, 0, 0], f32)
-    na, n1, n2 = material_ior(_AIR), material_ior(g1), material_ior(g2)
+    na, n1, n2 = material_ior(_AIR, nominal), material_ior(g1, nominal), material_ior(g2, nominal)
     rows = np.stack([
         _row(1, z, lr, 0, na, n2),
         _row(0, f32(z + thick), lr, R, n2, n1),
         _row(0, f32(z + f32(f32(2) * thick)), lr, -R, n1, na),
         _row(2, f32(z + f32(f32(3) * thick)), f32(f32(1) * lr), 0, na, na),
     ])
-    return InterfaceList(rows)
+    return InterfaceList(rows, materials=np.array([[_AIR, g2], [g2, g1], [g1, _AIR], [_AIR, _AIR]], f32))
 
 
-def hypercentric(ap_radius=1.0, focal_lengths=2.0) -> InterfaceList:
+def hypercentric(ap_radius=1.0, focal_lengths=2.0, nominal=NOMINAL_RGB) -> InterfaceList:
     """realisticlens.cpp:1322-1370 (telecentric / hypercentric test optic; no fine focus)."""
     apr, fls = f32(ap_radius), f32(focal_lengths)
     sf6 = np.array([0, 1.757435971209294, 0.016580283248837778, 0, 0, 0, 0], f32)
-    na, ng = material_ior(_AIR), material_ior(sf6)
+    na, ng = material_ior(_AIR, nominal), material_ior(sf6, nominal)
     target, lens_radius, focal, track, curv, lens_t = map(f32, (5.0, 120.0, 210.0, 450.0, 310.505660861, 50.0))
     z_ap_to_lens = f32(focal * fls)
     z_film_to_ap = f32(f32(z_ap_to_lens * f32(target - apr)) * f32(f32(1) / f32(lens_radius + apr)))
@@ -161,16 +166,19 @@ def hypercentric(ap_radius=1.0, focal_lengths=2.0) -> InterfaceList:
     thick = [lens_t, f32(z_ap_to_lens - f32(lens_t * f32(0.5))), z_film_to_ap]
     elem = [lens_radius, lens_radius, apr]
     iors = [na, ng, na, na]
-    rows, z_pos = [], f32(0)
+    media = [_AIR, sf6, _AIR, _AIR]
+    rows, z_pos, mats = [], f32(0), []
     for i in (2, 1, 0):
         z_pos = f32(z_pos + thick[i])
         if i == 2:
             rows.append(_row(2, f32(f32(0.001) * z_pos), f32(f32(0.001) * elem[i]), 0, na, na))
+            mats.append([_AIR, _AIR])
         else:
+            mats.append([media[i + 1], media[i]])
             rows.append(_row(0, f32(f32(0.001) * z_pos), f32(f32(0.001) * elem[i]),
                              f32(f32(-0.001) * curv_radii[i]), iors[i + 1], iors[i]))
     film_z = f32(f32(0.001) * f32(track - f32(f32(thick[0] + thick[1]) + thick[2])))
-    return InterfaceList(np.stack(rows), film_z=film_z, fine_focus=False)
+    return InterfaceList(np.stack(rows), film_z=film_z, fine_focus=False, materials=np.array(mats, f32))
 
 
 PARAMETRIC = ("singlet", "doublet", "hypercentric")
@@ -183,14 +191,15 @@ def design(lens_design: str, props: dict | None = None):
     fl = props.get("lens_focal_length", 0.05)
     ld = props.get("lens_diameter", 0.01)
     sr = props.get("stop_ratio", 1.0)
+    nominal = NOMINAL_SPECTRAL if props.get("spectral", False) else NOMINAL_RGB
     if lens_design == "doublet":
-        return doublet(od, f32(f32(fl) / f32(2)), f32(f32(ld) / f32(2)))
+        return doublet(od, f32(f32(fl) / f32(2)), f32(f32(ld) / f32(2)), nominal)
     if lens_design == "hypercentric":
-        return hypercentric(props.get("ap_size", 1.0), props.get("ap_offset", 2.0))
+        return hypercentric(props.get("ap_size", 1.0), props.get("ap_offset", 2.0), nominal)
     if lens_design in presets():
         return prescription_from_preset(lens_design, sr)
     # "singlet" and every unknown name (:895-897)
-    return singlet(od, f32(fl), f32(f32(ld) / f32(2)))
+    return singlet(od, f32(fl), f32(f32(ld) / f32(2)), nominal)
 
 
 def all_designs():

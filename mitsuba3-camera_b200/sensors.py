@@ -112,6 +112,7 @@ class RealisticLensCamera(Sensor):
         self._shutter_open = float(props.get("shutter_open", 0.0))
         self._shutter_open_time = float(props.get("shutter_close", self._shutter_open)) - self._shutter_open
         self.sample_exit_pupil = bool(props.get("sample_exit_pupil", False))
+        self.spectral = bool(props.get("spectral", False))
         d = prescription if prescription is not None else ld.design(lens_design, props)
         self.design = d
         h = C.c_void_p()
@@ -123,7 +124,9 @@ class RealisticLensCamera(Sensor):
                 capi.c_f(self.object_distance), C.byref(g), capi.fp(self.to_world), capi.c_f(self.near_clip),
                 capi.c_f(self.far_clip), C.byref(h))
         else:
-            rc = capi.lib.lrt_sensor_create_prescription(
+            # spectral=True: the table a `*_spectral*` variant of the fork builds (nominal IORs at 0.001f * 589.3f um)
+            create = capi.lib.lrt_sensor_create_prescription_spectral if self.spectral else capi.lib.lrt_sensor_create_prescription
+            rc = create(
                 C.c_int32(len(d.kinds)), capi.ip(d.kinds), capi.fp(d.thickness), capi.fp(d.radius),
                 capi.fp(d.semi_diameter), capi.fp(d.kappa), capi.fp(np.ascontiguousarray(d.ai)),
                 capi.fp(np.ascontiguousarray(d.materials)), capi.c_f(d.scale), capi.c_f(d.stop_ratio),
@@ -131,6 +134,8 @@ class RealisticLensCamera(Sensor):
                 capi.c_f(self.near_clip), capi.c_f(self.far_clip), C.byref(h))
         capi.check(rc)
         self.handle = h
+        if hasattr(d, "rows") and getattr(d, "materials", None) is not None:
+            self.set_materials(d.materials)
         # realisticlens.cpp:913-921: build the exit-pupil LUT (a GPU kernel here). An open shutter is registered either way:
         # render_sample draws a time sample whenever shutter_open_time() > 0 (integrator.cpp:442-444)
         if self.sample_exit_pupil or self._shutter_open_time != 0.0:
@@ -190,6 +195,49 @@ class RealisticLensCamera(Sensor):
         fd, fz = C.c_float(), C.c_float()
         capi.check(capi.lib.lrt_sensor_get_info(self.handle, capi.fp(m), C.byref(fd), C.byref(fz)))
         return {"sample_to_film": m.reshape(4, 4), "focus_delta": fd.value, "film_z": fz.value}
+
+    # ---- dispersion (the fork's spectral variants: every ray carries a wavelength, realisticlens.cpp:169-183)
+    def set_materials(self, mat_lr):
+        """Cauchy / Sellmeier rows of the two media of every interface, [n_if, 2, 7] (left = film side, right), for sensors
+        built from ready-made interfaces; sensors built from a prescription carry them already."""
+        m = np.ascontiguousarray(mat_lr, f32).reshape(-1, 14)
+        capi.check(capi.lib.lrt_sensor_set_materials(self.handle, C.c_int32(len(m)), capi.fp(m)))
+
+    def materials(self):
+        m = np.zeros((self.num_interfaces(), 2, 7), f32)
+        capi.check(capi.lib.lrt_sensor_get_materials(self.handle, capi.fp(m.reshape(-1))))
+        return m
+
+    def sample_ray_wavelength(self, sample2, sample3, wavelength_nm):
+        """Sensor::sample_ray of a spectral variant for [n,2] film / aperture samples and one wavelength (nm) per ray (the first
+        entry of the reference's wavelength vector decides the IORs): (o, d, maxt, weight) torch CUDA tensors; the weight is
+        the geometric one (multiply by sample_wavelengths()' own)."""
+        import torch
+        pos = torch.as_tensor(sample2, dtype=torch.float32, device="cuda").reshape(-1, 2).contiguous()
+        ap = torch.as_tensor(sample3, dtype=torch.float32, device="cuda").reshape(-1, 2).contiguous()
+        wl = torch.as_tensor(wavelength_nm, dtype=torch.float32, device="cuda").reshape(-1).expand(pos.shape[0]).contiguous()
+        out = torch.empty((pos.shape[0], 10), dtype=torch.float32, device="cuda")
+        capi.check(capi.lib.lrt_sensor_sample_ray_wl(self.handle, C.c_int64(pos.shape[0]), capi.dev_ptr(pos), capi.dev_ptr(ap), capi.dev_ptr(wl),
+                                                     capi.dev_ptr(out), capi.stream_ptr()))
+        return out[:, 0:3], out[:, 3:6], out[:, 6], out[:, 7]
+
+    def trace_wavelength(self, origins, directions, wavelength_nm, from_world=False, device=True):
+        """trace_ray_from_film / trace_ray_from_world with per-ray wavelengths (nm), camera space: (o, d, active).
+        device=True runs the kernel (torch CUDA tensors in and out); device=False the host twin (numpy)."""
+        if not device:
+            od = np.ascontiguousarray(np.concatenate([np.asarray(origins, f32).reshape(-1, 3), np.asarray(directions, f32).reshape(-1, 3)], axis=1))
+            wl = np.ascontiguousarray(np.broadcast_to(np.asarray(wavelength_nm, f32).reshape(-1), (len(od),)))
+            out = np.zeros((len(od), 7), f32)
+            capi.check(capi.lib.lrt_sensor_trace_wl_host(self.handle, C.c_int32(int(from_world)), C.c_int64(len(od)), capi.fp(od), capi.fp(wl), capi.fp(out)))
+            return out[:, 0:3], out[:, 3:6], out[:, 6] > 0
+        import torch
+        od = torch.cat([torch.as_tensor(origins, dtype=torch.float32, device="cuda").reshape(-1, 3),
+                        torch.as_tensor(directions, dtype=torch.float32, device="cuda").reshape(-1, 3)], 1).contiguous()
+        wl = torch.as_tensor(wavelength_nm, dtype=torch.float32, device="cuda").reshape(-1).expand(od.shape[0]).contiguous()
+        out = torch.empty((od.shape[0], 7), dtype=torch.float32, device="cuda")
+        capi.check(capi.lib.lrt_sensor_trace_wl(self.handle, C.c_int32(int(from_world)), C.c_int64(od.shape[0]), capi.dev_ptr(od), capi.dev_ptr(wl),
+                                                capi.dev_ptr(out), capi.stream_ptr()))
+        return out[:, 0:3], out[:, 3:6], out[:, 6] > 0
 
     def trace(self, origins, directions, from_world=False):
         """trace_ray_from_film / trace_ray_from_world in camera space (host; chief-ray queries)."""

@@ -96,6 +96,7 @@ struct RefLensCamera {
     Float m_near_clip = 1e-2f, m_far_clip = 1e4f, m_shutter_open_time = 0;
     ScalarVector2f m_resolution;
     bool m_sample_exit_pupil = false;
+    Float m_ray_wavelength = 589.3f;   // harness only: the wavelength (nm) sample_ray() gives its ray in the spectral instantiation
 
     // the reference dumps every focus ray to stdout here (realisticlens.cpp:2028-2099); silenced
     void draw_ray_from_world(const Ray3f &) const {}
@@ -122,6 +123,9 @@ struct RefLensCamera {
         Spectrum wav_weight(1.f);   // sample_wavelengths() in *_rgb: weight 1, no wavelengths
         Ray3f ray;
         ray.time = time;
+        // spectral instantiation: realisticlens.cpp:2215-2221 draws the wavelengths (sample_wavelengths: the film's sensor
+        // response, outside this path) and stores them in the ray; the test passes the wavelength in
+        if constexpr (is_spectral_v<Spectrum>) ray.wavelengths = Wavelength(m_ray_wavelength);
         #include "_ref/ref_sample_ray_body.inc"   // :2223-2291
     }
 
@@ -200,10 +204,12 @@ void ref_solve_quadratic(int n, const float *abc, float *out3) {
 
 // ---- camera ----------------------------------------------------------------------------------
 // film: width, height, crop (w,h,ox,oy), diagonal in mm (film.cpp:46-48: m_diagonal = 0.001*diag)
-void *ref_cam_create(const char *lens_design, int width, int height, const int *crop4,
-                     float diagonal_mm, const float *to_world16, float near_clip, float far_clip,
-                     float shutter_open_time, int n_props, const char **prop_names,
-                     const double *prop_values) {
+}   // extern "C"
+template <typename Cam>
+static void *cam_create(const char *lens_design, int width, int height, const int *crop4,
+                        float diagonal_mm, const float *to_world16, float near_clip, float far_clip,
+                        float shutter_open_time, int n_props, const char **prop_names,
+                        const double *prop_values) {
     CoutSilencer quiet;
     Cam *c = new Cam();
     c->film_stub.m_size = { (uint32_t) width, (uint32_t) height };
@@ -213,7 +219,7 @@ void *ref_cam_create(const char *lens_design, int width, int height, const int *
     c->m_resolution = { (float) crop4[0], (float) crop4[1] };
     dr::Matrix<float, 4> m;
     for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) m(i, j) = to_world16[4 * i + j];
-    c->m_to_world.v = Cam::Transform4f(m);
+    c->m_to_world.v = typename Cam::Transform4f(m);
     c->m_near_clip = near_clip; c->m_far_clip = far_clip; c->m_shutter_open_time = shutter_open_time;
     // ctor order of realisticlens.cpp:832-842
     c->update_camera_transforms();
@@ -225,6 +231,59 @@ void *ref_cam_create(const char *lens_design, int width, int height, const int *
         fprintf(stderr, "ref_cam_create: %s\n", e.what()); delete c; return nullptr;
     }
     return c;
+}
+// the same lens classes and camera methods instantiated as a SPECTRAL variant (Spectrum = mitsuba::Spectrum<float, 4>):
+// DispersiveMaterial::compute_ior(ray) then evaluates the media at 0.001 * ray.wavelengths[0] (realisticlens.cpp:169-179)
+using SCam = RefLensCamera<float, mitsuba::Spectrum<float, 4>>;
+using SRayF = mitsuba::Ray<Point<float, 3>, mitsuba::Spectrum<float, 4>>;
+extern "C" {
+void *ref_cam_create(const char *lens_design, int width, int height, const int *crop4,
+                     float diagonal_mm, const float *to_world16, float near_clip, float far_clip,
+                     float shutter_open_time, int n_props, const char **prop_names,
+                     const double *prop_values) {
+    return cam_create<Cam>(lens_design, width, height, crop4, diagonal_mm, to_world16, near_clip, far_clip, shutter_open_time, n_props,
+                           prop_names, prop_values);
+}
+void *ref_scam_create(const char *lens_design, int width, int height, const int *crop4,
+                      float diagonal_mm, const float *to_world16, float near_clip, float far_clip,
+                      float shutter_open_time, int n_props, const char **prop_names,
+                      const double *prop_values) {
+    return cam_create<SCam>(lens_design, width, height, crop4, diagonal_mm, to_world16, near_clip, far_clip, shutter_open_time, n_props,
+                            prop_names, prop_values);
+}
+void ref_scam_destroy(void *h) { delete (SCam *) h; }
+int ref_scam_num_interfaces(void *h) { return (int) ((SCam *) h)->m_interfaces.size(); }
+float ref_scam_film_z(void *h) { return ((SCam *) h)->m_film_z_position; }
+// per interface z, element radius and the two IORs at the spectral variants' nominal wavelength (Wavelength(589.3f))
+void ref_scam_interface(void *h, int i, float *out4) {
+    auto *it = ((SCam *) h)->m_interfaces[i];
+    SRayF ray(Point<float, 3>(0.f), Vector<float, 3>(0.f, 0.f, 1.f), 0.f, mitsuba::Spectrum<float, 4>(589.3f));
+    out4[0] = it->m_z_intercept; out4[1] = it->m_element_radius;
+    out4[2] = it->m_left_material.compute_ior(ray); out4[3] = it->m_right_material.compute_ior(ray);
+}
+// Sensor::sample_ray of the spectral instantiation, one wavelength (nm) per sample: out = o[3] d[3] maxt weight(first channel)
+void ref_scam_sample_ray(void *h, int n, const float *pos2, const float *ap2, const float *wl_nm, float *out10) {
+    SCam *c = (SCam *) h;
+    for (int i = 0; i < n; ++i) {
+        c->m_ray_wavelength = wl_nm[i];
+        auto [ray, w] = c->sample_ray(0.f, P2(pos2[2 * i], pos2[2 * i + 1]), P2(ap2[2 * i], ap2[2 * i + 1]), true);
+        float *o = out10 + 10 * i;
+        o[0] = ray.o.x(); o[1] = ray.o.y(); o[2] = ray.o.z();
+        o[3] = ray.d.x(); o[4] = ray.d.y(); o[5] = ray.d.z();
+        o[6] = ray.maxt; o[7] = w[0]; o[8] = w[1]; o[9] = w[2];
+    }
+}
+// trace_ray_from_film / trace_ray_from_world with the ray's wavelength
+void ref_scam_trace(void *h, int from_world, int n, const float *od6, const float *wl_nm, float *out7) {
+    SCam *c = (SCam *) h;
+    for (int i = 0; i < n; ++i) {
+        const float *r = od6 + 6 * i;
+        SRayF ray(P3(r[0], r[1], r[2]), V3(r[3], r[4], r[5]), 0.f, mitsuba::Spectrum<float, 4>(wl_nm[i]));
+        auto [ro, act] = from_world ? c->trace_ray_from_world(ray) : c->trace_ray_from_film(ray);
+        float *o = out7 + 7 * i;
+        o[0] = ro.o.x(); o[1] = ro.o.y(); o[2] = ro.o.z();
+        o[3] = ro.d.x(); o[4] = ro.d.y(); o[5] = ro.d.z(); o[6] = act ? 1.f : 0.f;
+    }
 }
 void ref_cam_destroy(void *h) { delete (Cam *) h; }
 int ref_cam_num_interfaces(void *h) { return (int) ((Cam *) h)->m_interfaces.size(); }
