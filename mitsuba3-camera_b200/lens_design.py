@@ -211,6 +211,20 @@ def asphere_table(curv_mm, thickness_mm, semi_diameter_mm, glass_iors, air=1.000
     return np.stack(rows)
 
 
+def glass_ior(n_d, V_d, wavelength_um=0.5893):
+    """DispersiveDielectric::eval_ior (src/bsdfs/dispersive_dielectric.cpp:425-431): the Cauchy fit through (n_d, V_d) the
+    notebooks' lens materials are parameterised by — B = (n_d - 1) / (V_d (1/0.48613^2 - 1/0.65627^2)) (0 if V_d = 0),
+    A = n_d - B / 0.5893^2, n(w) = A + B / w^2. Works on floats, numpy arrays and torch tensors (differentiable)."""
+    k = 1.0 / (0.48613 * 0.48613) - 1.0 / (0.65627 * 0.65627)
+    if hasattr(V_d, "clamp_min"):
+        import torch
+        B = torch.where(V_d > 5.9604644775390625e-08, (n_d - 1.0) / (V_d.clamp_min(1e-30) * k), torch.zeros_like(V_d))
+    else:
+        B = np.where(np.asarray(V_d) > 5.9604644775390625e-08, (n_d - 1.0) / (np.maximum(V_d, 1e-30) * k), 0.0)
+    A = n_d - B / (0.5893 * 0.5893)
+    return A + B / (wavelength_um * wavelength_um)
+
+
 def cauchy_ior(A, B, wavelength_um=0.5893):
     return A + B / (wavelength_um * wavelength_um)     # realisticlens.cpp:169-179
 
@@ -254,7 +268,8 @@ class LensDesignProblem:
     image-space loss gradient, adjoint renders at `spp_grad` (fresh seed), Adam update."""
 
     def __init__(self, mi, rows0, field_angles, resolution=128, full_res=4096, diagonal=35.0, spp=256, spp_grad=128,
-                 free=None, lr=3e-5, source_distance=1.0e3, rfilter="tent", efl_target=None, shard=(0, 1), film_z=0.0, device="cuda", fast=True):
+                 free=None, lr=3e-5, source_distance=1.0e3, rfilter="tent", efl_target=None, shard=(0, 1), film_z=0.0, device="cuda", fast=True,
+                 glasses=None, wavelengths=None, free_glass=False, lr_glass=None):
         import torch
         from .lens_designs import InterfaceList
         self.mi, self.torch = mi, torch
@@ -279,6 +294,27 @@ class LensDesignProblem:
         self._idx = (torch.tensor([i for i, _ in self.free], device=self.device), torch.tensor([c for _, c in self.free], device=self.device))
         self._sph = torch.tensor(self.rows0[:, 0] == 0, device=self.device); self._asp = torch.tensor(self.rows0[:, 0] == 3, device=self.device)
         self._rear_idx = (torch.tensor([0, 0], device=self.device), torch.tensor([1, 3], device=self.device))
+        # glass variables and wavelengths (the notebooks' lens materials: `dispersive` BSDFs parameterised by (n_d, V_d),
+        # lens.py:343-420; chromatic designs evaluate the spots at several wavelengths). glasses: {medium: (n_d, V_d)} with
+        # medium m = the space on the film side of table row m (row m's ior_left, row m-1's ior_right; m = n: object space).
+        # The IOR columns of those media then follow glass_ior(n_d, V_d, wavelength) for every wavelength of `wavelengths`
+        # (nm; default: the rgb variants' single 589.3) and the loss is the mean over the wavelengths. free_glass=True makes
+        # (n_d, V_d) design variables (their gradients arrive through the IOR columns of the adjoint).
+        self.wavelengths = [589.3] if wavelengths is None else [float(w) for w in wavelengths]
+        if len(self.wavelengths) * len(field_angles) > 64:
+            raise ValueError("fields x wavelengths must not exceed 64 (one sample stream each per iteration)")
+        self.glass_media = sorted(glasses) if glasses else []
+        if self.glass_media:
+            g = torch.tensor([[glasses[m][0], glasses[m][1]] for m in self.glass_media], dtype=torch.float32, device=self.device)
+            self.glass = g.clone().requires_grad_(bool(free_glass))
+            if free_glass:
+                self.opt.add_param_group({"params": [self.glass], "lr": lr if lr_glass is None else lr_glass})
+            il = [(m, 13) for m in self.glass_media if m < self.n]; ir = [(m - 1, 14) for m in self.glass_media if m >= 1]
+            self._glass_idx = (torch.tensor([i for i, _ in il + ir], device=self.device), torch.tensor([c for _, c in il + ir], device=self.device))
+            self._glass_src = torch.tensor([self.glass_media.index(m) for m in self.glass_media if m < self.n] +
+                                           [self.glass_media.index(m) for m in self.glass_media if m >= 1], device=self.device)
+        elif wavelengths is not None and len(self.wavelengths) > 1:
+            raise ValueError("several wavelengths need `glasses`: the table itself holds one IOR per medium")
         self.sensors, self.sources = [], []
         probe = mi.RealisticLensCamera(mi.Film(full_res, full_res, diagonal=diagonal, rfilter=rfilter), "custom",
                                        prescription=InterfaceList(self.rows0, film_z=film_z, fine_focus=False))
@@ -302,10 +338,15 @@ class LensDesignProblem:
             self.sensors.append(s); self.sources.append(src)
         self.iteration, self.losses = 0, []
 
-    def rows(self):
-        """theta -> interface table (torch, differentiable); applies the EFL constraint when one is set."""
+    def rows(self, wavelength_nm=None):
+        """theta -> interface table (torch, differentiable); applies the EFL constraint when one is set. With glass variables:
+        the table at `wavelength_nm` (default: the first of self.wavelengths)."""
         torch = self.torch
         rows = self._rows0_t.index_put(self._idx, self.theta)
+        if self.glass_media:
+            w = 1e-3 * (self.wavelengths[0] if wavelength_nm is None else float(wavelength_nm))
+            ior = glass_ior(self.glass[:, 0], self.glass[:, 1], w)
+            rows = rows.index_put(self._glass_idx, ior[self._glass_src])
         if self.efl_target is not None:
             Re = rows[:, 2]
             safe_R = torch.where(self._sph, rows[:, 3], torch.ones_like(Re))
@@ -315,10 +356,21 @@ class LensDesignProblem:
             rows = rows.index_put(self._rear_idx, torch.stack([z0, col3]))
         return rows
 
-    def loss(self, rows, seed):
-        """seed: the iteration number (int), or a uint32 CUDA tensor holding it (graph replay)."""
+    def loss_all_wavelengths(self, seed):
+        """mean over self.wavelengths of loss(rows(wavelength)): the polychromatic spot loss"""
+        if len(self.wavelengths) == 1:
+            return self.loss(self.rows(), seed)
+        total = 0.0
+        for j, w in enumerate(self.wavelengths):
+            total = total + self.loss(self.rows(w), seed, stream=j)
+        return total / len(self.wavelengths)
+
+    def loss(self, rows, seed, stream=0):
+        """seed: the iteration number (int), or a uint32 CUDA tensor holding it (graph replay). stream: decorrelates the
+        samples of the wavelengths of one iteration."""
         total = 0.0
         for k, (s, src) in enumerate(zip(self.sensors, self.sources)):
+            k = k + len(self.sensors) * stream          # (fields x wavelengths <= 64 sample streams per iteration)
             sd = DeviceSeed(seed, base=k, stride=64) if hasattr(seed, "data_ptr") else seed * 64 + k
             img = spot_image(rows, s, src, seed=sd, spp=self.spp, seed_grad=sd ^ 0x5bd1e995,
                              spp_grad=self.spp_grad, shard=self.shard, origin_offset=self.origin_offset, fast=self.fast)
@@ -334,10 +386,12 @@ class LensDesignProblem:
         record_loss=False keeps the loss on the device (no synchronisation in the iteration)."""
         from .parallel import all_reduce_sum
         self.opt.zero_grad(set_to_none=True)
-        l = self.loss(self.rows(), self.iteration)
+        l = self.loss_all_wavelengths(self.iteration)
         l.backward()
         if self.shard[1] > 1:
             (all_reduce or all_reduce_sum)(self.theta.grad)
+            if self.glass_media and self.glass.grad is not None:
+                (all_reduce or all_reduce_sum)(self.glass.grad)
         self.opt.step()
         self.iteration += 1
         self.last_loss = l.detach()
@@ -368,10 +422,14 @@ class LensDesignProblem:
         from .parallel import all_reduce_sum
         if self.theta.grad is not None:         # (static gradient tensor: created by the first warm-up iteration, zeroed afterwards)
             self.theta.grad.zero_()
-        l = self.loss(self.rows(), self._it_dev)
+        if self.glass_media and self.glass.grad is not None:
+            self.glass.grad.zero_()
+        l = self.loss_all_wavelengths(self._it_dev)
         l.backward()
         if self.shard[1] > 1:
             all_reduce_sum(self.theta.grad)
+            if self.glass_media and self.glass.grad is not None:
+                all_reduce_sum(self.glass.grad)
         self.opt.step()
         self._it_dev += 1
         self.last_loss = l.detach()
