@@ -195,6 +195,59 @@ def triplet_table(mi):
                            [crown, 1.000277, flint, 1.000277, crown, 1.000277])
 
 
+def widened_rows_section(mi, torch, a, scene):
+    """Device-timed figures for two rows built after the headline path: the mesh-lens trace with its adjoint and
+    the dispersion mode of the lens step (8f-4). CUDA events, 3 warm-up + 5 timed repetitions each."""
+    def timed(fn, reps=5, warm=3):
+        for _ in range(warm):
+            fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            fn()
+        e1.record(); torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / reps
+    out = {}
+    # mesh lens: the notebooks' doublet, subdivision 6 (2 x 20 000 triangles + baffles), 2^20 rays from a field point
+    rows = doublet_table(mi)
+    lens = mi.mesh_lens.MeshLens(mi, rows, subdiv=6)
+    src = mi.lens_design.field_source(2.0, 1.0e3, front_z=float(rows[-1, 1]))
+    off = 2.0 * float(rows[-1, 2])
+    n = 1 << 20
+    ap, d, o = lens._spot_rays(src, n, 1, off)
+    rt = torch.tensor(rows, dtype=torch.float64, device="cuda", requires_grad=True)
+
+    def fwd():
+        lens.trace(o, d)
+
+    def fwd_bwd():
+        rt.grad = None
+        po, pd, alive, w = lens.trace_ad(rt, o, d)
+        t = -po[:, 2] / pd[:, 2]
+        pf = (po + t[:, None] * pd)[:, :2][alive]
+        ((pf - pf.mean(0)) ** 2).sum(1).mean().backward()
+    ms_f, ms_fb = timed(fwd), timed(fwd_bwd)
+    out["mesh_lens"] = {"rays": n, "triangles": int(lens.scene.info()["triangles"]), "trace_ms": ms_f, "Mrays_per_s": n / ms_f / 1e3,
+                        "design_iteration_ms": ms_fb, "iters_per_s": 1e3 / ms_fb,
+                        "what": "meshed doublet, subdivision 6: lrt_scene_trace_refractive alone; and one design iteration = sag -> vertices -> "
+                                "vertex normals (torch) -> BVH refit -> trace -> rms-spot loss -> lrt_scene_trace_refractive_backward -> torch "
+                                "chain to the 3 x 16 table entries"}
+    # dispersion: sample_ray with one wavelength per ray through the headline lens
+    sens = mi.RealisticLensCamera(scene.sensors()[0].film, a.lens, spectral=True)
+    g = torch.Generator(device="cuda").manual_seed(0)
+    m = 1 << 24
+    pos = torch.rand((m, 2), device="cuda", generator=g); apx = torch.rand((m, 2), device="cuda", generator=g)
+    wl = 380.0 + 320.0 * torch.rand(m, device="cuda", generator=g)
+    ms_wl = timed(lambda: sens.sample_ray_wavelength(pos, apx, wl))
+    ms_rgb = timed(lambda: sens.sample_ray(0.0, None, pos, apx))
+    out["dispersion"] = {"rays": m, "sample_ray_wl_ms": ms_wl, "Grays_per_s": m / ms_wl / 1e6, "sample_ray_rgb_ms": ms_rgb,
+                         "Grays_per_s_rgb": m / ms_rgb / 1e6,
+                         "what": "lrt_sensor_sample_ray_wl on the `%s` lens (per-ray Cauchy / Sellmeier IOR of both media of each of its "
+                                 "interfaces) beside lrt_sensor_sample_ray (constant IORs)" % a.lens}
+    return out
+
+
 def lens_grad_section(mi, torch, dist, a, rank, world):
     """Lens-gradient iterations/s: one iteration = per field a primal spot render (spp), the RMS-spot loss, the adjoint
     render (spp_grad, fresh seed), an all-reduce of the table gradient (N > 1: samples are sharded by index) and an Adam
@@ -470,6 +523,13 @@ def main():
         pupil = {"ms": sec * 1e3, "lens_rays": 64 << 20, "Grays_per_s": (64 << 20) / sec / 1e9,
                  "what": "lrt_sensor_set_exit_pupil: compute_exit_pupil_bounds of the `%s` lens (host wall clock, synchronous call)" % a.lens}
 
+    extras = None
+    if rank == 0 and not a.no_lens_grad:
+        try:
+            extras = widened_rows_section(mi, torch, a, scene)
+        except Exception as e:     # the extra measurements must never take the headline line down
+            extras = {"error": str(e)[:200]}
+
     if rank == 0:
         value = paths_per_step / (ms * 1e-3) / 1e6
         e2e_v = paths_per_step / (ms_e2e * 1e-3) / 1e6
@@ -553,6 +613,8 @@ def main():
             line["lens_grad"] = lens_grad
         if pupil is not None:
             line["exit_pupil_lut"] = pupil
+        if extras is not None:
+            line["widened_rows"] = extras
         if not a.no_cpu_baseline and world == 1:     # the contract wants the CPU baseline on rank 0 at N = 1 only
             port, _ = cpu_sample(a, scene.arrays, d["sensor"], keep_image=True)
             ref = reference_sample(a)

@@ -280,7 +280,7 @@ typedef struct lrt_render_params {
 } lrt_render_params;
 
 /* Accumulates R,G,B,W into accum_dev [size_y+2b, size_x+2b, 4] (caller zeroes it; ImageBlock storage of
- * hdrfilm). Asynchronous on `stream`. */
+ * hdrfilm; 16-byte aligned: pixels are flushed with 128-bit reductions). Asynchronous on `stream`. */
 int lrt_render(const lrt_scene *scene, const lrt_sensor *sensor, const lrt_film_desc *film,
                const lrt_render_params *params, float *accum_dev, void *stream);
 /* Adjoint of lrt_render for the scene parameters the path is linear in — the part of PRBIntegrator.render_backward

@@ -420,11 +420,8 @@ __global__ void __launch_bounds__(kCtaThreads, LRT_RENDER_MIN_BLOCKS) k_render(R
             if ((unsigned) x >= (unsigned) sw || (unsigned) y >= (unsigned) shh) continue;
             float4 v = reinterpret_cast<const float4 *>(tile)[i];
             if (v.w == 0.f && v.x == 0.f && v.y == 0.f && v.z == 0.f) continue;
-            float *dst = A.accum + ((size_t) y * sw + x) * 4;
-            if (v.x != 0.f) atomicAdd(dst, v.x);
-            if (v.y != 0.f) atomicAdd(dst + 1, v.y);
-            if (v.z != 0.f) atomicAdd(dst + 2, v.z);
-            if (v.w != 0.f) atomicAdd(dst + 3, v.w);
+            // one 128-bit reduction per pixel (sm_90+: atomicAdd on float4, element-wise atomic) instead of four scalar ones
+            atomicAdd(reinterpret_cast<float4 *>(A.accum) + ((size_t) y * sw + x), v);
         }
         __syncwarp();
     }

@@ -210,6 +210,7 @@ int lrt_render(const lrt_scene *sc, const lrt_sensor *sensor, const lrt_film_des
     LRT_NEED_DEVICE();
     LRT_REQUIRE(sc && sensor && film && rp && accum_dev, "null argument");
     LRT_REQUIRE(rp->rng_mode == 0 || rp->rng_mode == 1, "rng_mode must be 0 (per-sample streams) or 1 (scalar convention)");
+    LRT_REQUIRE((reinterpret_cast<uintptr_t>(accum_dev) & 15) == 0, "accum_dev must be 16-byte aligned (the tiles are flushed with 128-bit reductions)");
     if (rp->rng_mode == 1) return launch_render_scalar(sc, const_cast<lrt_sensor *>(sensor), film, rp, accum_dev, (cudaStream_t) stream);
     return launch_render(sc, const_cast<lrt_sensor *>(sensor), film, rp, accum_dev, nullptr, nullptr, nullptr, (cudaStream_t) stream);
 }
