@@ -257,12 +257,20 @@ class MeshLens:
         `rows`, refits the BVH, traces; backward runs lrt_scene_trace_refractive_backward and torch chains its vertex / normal /
         index gradients through the vertex normals (mesh.cpp:321-375) and the sag function down to `rows`.
         The scene must not be moved again between this call and backward(): the adjoint kernel replays the trace."""
-        import torch
+        return self.trace_prepared(self.prepare(rows), o, d)
+
+    def prepare(self, rows):
+        """(vertices, vertex normals | None, relative indices) of the table `rows`, differentiable: computed once per design
+        iteration and shared by every bundle traced through the lens in that iteration (trace_prepared)."""
         V = self.vertices_of(rows)
-        N = self._vertex_normals(V) if self.smooth else None
+        return V, (self._vertex_normals(V) if self.smooth else None), self.eta_of(rows)
+
+    def trace_prepared(self, prepared, o, d):
+        import torch
+        V, N, eta = prepared
         od = torch.cat([torch.as_tensor(o, dtype=torch.float32, device="cuda").reshape(-1, 3),
                         torch.as_tensor(d, dtype=torch.float32, device="cuda").reshape(-1, 3)], 1)
-        out = _RefractiveTrace.apply(self, V, N, self.eta_of(rows), od)
+        out = _RefractiveTrace.apply(self, V, N, eta, od)
         return out[:, 0:3], out[:, 3:6], out[:, 6] > 0, out[:, 7]
 
     def spot_positions_ad(self, rows, src_p, n, seed=0, origin_offset=0.0):
@@ -314,8 +322,10 @@ def _make_trace_op():
         def forward(ctx, lens, V, N, eta, od):
             V = V.detach().contiguous(); od = od.detach().contiguous(); eta = eta.detach().contiguous()
             Nc = N.detach().contiguous() if N is not None else None
-            capi.check(capi.lib.lrt_scene_refit(lens.scene.handle, capi.dev_ptr(V), capi.dev_ptr(Nc) if Nc is not None else None, capi.stream_ptr()))
-            lens.vertices, lens._normals, lens.eta = V, Nc, eta
+            if lens.vertices.data_ptr() != V.data_ptr():      # (several bundles of one iteration share one set of vertices: one refit)
+                capi.check(capi.lib.lrt_scene_refit(lens.scene.handle, capi.dev_ptr(V), capi.dev_ptr(Nc) if Nc is not None else None, capi.stream_ptr()))
+                lens.vertices, lens._normals = V, Nc
+            lens.eta = eta
             out = torch.empty((od.shape[0], 8), dtype=torch.float32, device="cuda")
             capi.check(capi.lib.lrt_scene_trace_refractive(lens.scene.handle, C.c_int64(od.shape[0]), capi.dev_ptr(od), capi.dev_ptr(eta),
                                                            C.c_int32(lens.n_surfaces + 1), capi.dev_ptr(out), capi.stream_ptr()))
@@ -328,7 +338,7 @@ def _make_trace_op():
         def backward(ctx, grad_out):
             V, eta, od = ctx.saved_tensors
             lens = ctx.lens
-            if lens.vertices is not V:
+            if lens.vertices.data_ptr() != V.data_ptr():
                 raise RuntimeError("the mesh lens was moved between trace_ad() and backward(): the adjoint kernel replays the trace")
             grad_out = grad_out.contiguous().float()
             g_od = torch.empty_like(od)
@@ -354,3 +364,72 @@ class _LazyOp:
 
 
 _RefractiveTrace = _LazyOp()
+
+
+class MeshDesignProblem:
+    """The notebooks' design loop on the MESH representation of the lens (design_problem.py:355-584 over lens.py's mesh lenses):
+    per field a bundle of PARALLEL rays filling the front element — what the notebooks' `directionalarea` disk field sources
+    emit (design_problem.py:46-120), which only a mesh lens can receive: a delta direction cannot be connected to the analytic
+    lens — traced through the meshed surfaces; loss = sum over fields of the geometric rms spot radius squared about the
+    (detached) centroid, mm^2 (rms_loss, losses.py:8-28, on the landing points instead of a splatted image); Adam over table
+    entries. One step = sag -> vertices -> vertex normals -> BVH refit -> trace -> loss -> adjoint kernel -> torch chain."""
+
+    def __init__(self, mi, rows0, field_angles, subdiv=5, rays=1 << 16, free=None, lr=3e-5, seed=0, fill=0.95):
+        import torch
+        self.torch = torch
+        self.rows0 = np.ascontiguousarray(rows0, f32).copy()
+        self.lens = MeshLens(mi, self.rows0, subdiv=subdiv)
+        n = len(self.rows0)
+        if free is None:      # every curvature and vertex position of the refracting rows (+ conic and polynomial terms of aspheres)
+            free = [(i, c) for i in range(n) for c in ([1, 3] + ([4] + list(range(6, 13)) if self.rows0[i, 0] == 3 else []))
+                    if self.rows0[i, 0] != 2]
+        self.free = list(free)
+        self._rows0_t = torch.tensor(self.rows0, dtype=torch.float64, device="cuda")
+        self._idx = (torch.tensor([i for i, _ in self.free], device="cuda"), torch.tensor([c for _, c in self.free], device="cuda"))
+        self.theta = torch.tensor([self.rows0[i, c] for i, c in self.free], dtype=torch.float64, device="cuda", requires_grad=True)
+        self.opt = torch.optim.Adam([self.theta], lr=lr)
+        front_z, R = float(self.rows0[-1, 1]), float(self.rows0[-1, 2])
+        g = torch.Generator(device="cuda").manual_seed(seed)
+        self.bundles = []
+        for a in field_angles:
+            a = np.radians(a)
+            d = np.array([-np.sin(a), 0.0, -np.cos(a)])
+            u = np.array([np.cos(a), 0.0, -np.sin(a)]); v = np.array([0.0, 1.0, 0.0])          # the disk's plane, normal = d
+            centre = np.array([0.0, 0.0, front_z]) - d * (2.0 * R)
+            s = torch.rand((rays, 2), device="cuda", generator=g)
+            r, phi = fill * R * torch.sqrt(s[:, 0]), 2 * np.pi * s[:, 1]
+            o = (torch.tensor(centre, device="cuda")[None] + (r * torch.cos(phi))[:, None] * torch.tensor(u, device="cuda")[None]
+                 + (r * torch.sin(phi))[:, None] * torch.tensor(v, device="cuda")[None]).float()
+            self.bundles.append((o.contiguous(), torch.tensor(d, dtype=torch.float32, device="cuda").expand(rays, 3).contiguous()))
+        self.iteration, self.losses = 0, []
+
+    def rows(self):
+        return self._rows0_t.index_put(self._idx, self.theta)
+
+    def spots(self, rows):
+        """per field (landing points [n,2], alive mask) on the film plane z = 0, differentiable in `rows`"""
+        out = []
+        prepared = self.lens.prepare(rows)
+        for o, d in self.bundles:
+            po, pd, alive, w = self.lens.trace_prepared(prepared, o, d)
+            t = -po[:, 2] / pd[:, 2]
+            out.append(((po + t[:, None] * pd)[:, :2], alive & (pd[:, 2] < 0)))
+        return out
+
+    def loss(self, rows):
+        # one trace_ad per field; each keeps its own autograd node, and every node replays the SAME scene state (the table
+        # does not move inside an iteration), so backward() through all of them is consistent
+        total = 0.0
+        for pf, alive in self.spots(rows):
+            q = pf[alive].double() * 1e3                     # mm
+            total = total + ((q - q.mean(0).detach()) ** 2).sum(1).mean()
+        return total
+
+    def step(self):
+        self.opt.zero_grad(set_to_none=True)
+        l = self.loss(self.rows())
+        l.backward()
+        self.opt.step()
+        self.iteration += 1
+        self.losses.append(float(l.detach()))
+        return self.losses[-1]
