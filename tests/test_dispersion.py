@@ -99,3 +99,25 @@ def test_gpu_dispersion_kernels_match_the_reference(mi, G, name):
         a = a.cpu().numpy()
         assert (a == (want[:, 6] > 0)).all(), key
         assert (bits(np.concatenate([po.cpu().numpy(), pd.cpu().numpy()], 1)[a]) == bits(want[a, :6])).all(), key
+
+
+@pytest.mark.gpu
+def test_gpu_dispersion_limits(mi, G):
+    """no rays; a sensor without dispersion data; exit-pupil sampling (whose spectral LUT is not built) is refused."""
+    import ctypes as C
+    import torch
+    capi, lib = mi.capi, mi.capi.lib
+    s = mi.RealisticLensCamera(film(mi), "gauss", spectral=True)
+    assert lib.lrt_sensor_trace_wl(s.handle, C.c_int32(1), C.c_int64(0), None, None, None, None) == 0
+    assert lib.lrt_sensor_sample_ray_wl(s.handle, C.c_int64(0), None, None, None, None, None) == 0
+    rows = s.interfaces()
+    c = mi.RealisticLensCamera(film(mi), "custom", prescription=ld.InterfaceList(rows, film_z=0.0, fine_focus=False))
+    with pytest.raises(mi.capi.LensrtError):
+        c.sample_ray_wavelength(np.full((4, 2), 0.5, f32), np.full((4, 2), 0.5, f32), 550.0)
+    p = mi.RealisticLensCamera(film(mi), "gauss", spectral=True, sample_exit_pupil=True)
+    with pytest.raises(mi.capi.LensrtError):
+        p.sample_ray_wavelength(np.full((4, 2), 0.5, f32), np.full((4, 2), 0.5, f32), 550.0)
+    # a scalar wavelength broadcasts; 589.3 nm through the spectral table = the table's own nominal IORs
+    o, d, maxt, w = s.sample_ray_wavelength(G["gauss.pos"][:64], G["gauss.ap"][:64], 589.3)
+    o2, d2, maxt2, w2 = s.sample_ray(0.0, None, torch.tensor(G["gauss.pos"][:64], device="cuda"), torch.tensor(G["gauss.ap"][:64], device="cuda"))
+    assert (bits(o.cpu().numpy()) == bits(o2.cpu().numpy())).all() and (bits(d.cpu().numpy()) == bits(d2.cpu().numpy())).all()

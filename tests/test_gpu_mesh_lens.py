@@ -280,3 +280,38 @@ def test_mesh_design_loop_refocuses_a_perturbed_doublet(mi):
     prob.lens.trace_ad(r * 1.0001, *prob.bundles[0])
     with pytest.raises(RuntimeError):
         po.sum().backward()
+
+
+def test_trace_adjoint_limits(mi):
+    """edge cases of lrt_scene_trace_refractive_backward: no rays, too many interactions, rays that miss everything (the
+    adjoint passes straight through: d/d rays = the normalisation's Jacobian), absorbed rays (nothing)."""
+    import ctypes as C
+    import torch
+    capi, lib = mi.capi, mi.capi.lib
+    rows = doublet_rows(mi)
+    lens = mi.mesh_lens.MeshLens(mi, rows, subdiv=3)
+    z = torch.zeros((4, 8), dtype=torch.float32, device="cuda")
+    g_od = torch.full((4, 6), 7.0, dtype=torch.float32, device="cuda")
+    g_V = torch.zeros_like(lens.vertices)
+    od = torch.zeros((4, 6), dtype=torch.float32, device="cuda")
+    assert lib.lrt_scene_trace_refractive_backward(lens.scene.handle, C.c_int64(0), None, None, C.c_int32(4), None, None, None, None, None, None) == 0
+    rc = lib.lrt_scene_trace_refractive_backward(lens.scene.handle, C.c_int64(4), capi.dev_ptr(od), capi.dev_ptr(lens.eta), C.c_int32(33), capi.dev_ptr(z),
+                                                 capi.dev_ptr(g_od), capi.dev_ptr(g_V), None, None, None)
+    assert rc != 0 and b"at most 32" in lib.lrt_last_error()
+    R, fz = float(rows[-1, 2]), float(rows[-1, 1])
+    # ray 0 flies past everything (sideways, far from the lens); ray 1 hits the front baffle; rays 2, 3 go through the glass
+    od_np = np.array([[1.0, 1.0, fz + 0.5, 0.0, 2.0, 0.0], [2.0 * R, 0.0, fz + 0.02, 0.0, 0.0, -1.0],
+                      [0.2 * R, 0.0, fz + 0.02, 0.0, 0.0, -1.0], [0.0, 0.3 * R, fz + 0.02, 0.0, 0.0, -3.0]], f32)
+    od = torch.tensor(od_np, device="cuda")
+    out = torch.empty((4, 8), dtype=torch.float32, device="cuda")
+    K = C.c_int32(lens.n_surfaces + 1)
+    capi.check(lib.lrt_scene_trace_refractive(lens.scene.handle, C.c_int64(4), capi.dev_ptr(od), capi.dev_ptr(lens.eta), K, capi.dev_ptr(out), None))
+    assert out[:, 6].cpu().numpy().tolist() == [1.0, 0.0, 1.0, 1.0]
+    g = torch.zeros((4, 8), dtype=torch.float32, device="cuda"); g[:, 0:6] = 1.0
+    capi.check(lib.lrt_scene_trace_refractive_backward(lens.scene.handle, C.c_int64(4), capi.dev_ptr(od), capi.dev_ptr(lens.eta), K, capi.dev_ptr(g),
+                                                       capi.dev_ptr(g_od), capi.dev_ptr(g_V), None, None, None))
+    got = g_od.cpu().numpy()
+    assert np.allclose(got[0], [1, 1, 1, 0.5, 0.0, 0.5], atol=1e-6)          # (I - d d^T) / |d_in| applied to (1,1,1), d = +y, |d_in| = 2
+    assert (got[1] == 0).all()                                                # absorbed by the baffle
+    assert np.isfinite(got).all() and np.abs(got[2:]).max() > 0
+    assert float(g_V.abs().max()) > 0
