@@ -355,7 +355,7 @@ def main():
     config = {"workload": f"{what}, {a.width}x{a.height}, path max_depth={a.max_depth}, {a.spp_per_step} spp per step "
                           f"(1/{job // max(a.spp_per_step, 1)} of the {job}-spp job)",
               "l2": "flushed between steps (256 MiB write); BVH+triangles ~60 MB are L2-resident by design",
-              "parallelism": f"tile-sharded x{world}, one NCCL reduce of the film to rank 0 per step" if world > 1 else "single GPU"}
+              "parallelism": f"tile-sharded x{world}, one NCCL all-reduce of the film per step, overlapped with the next step's kernel" if world > 1 else "single GPU"}
 
     if a.impl == "reference":
         if rank != 0:

@@ -109,18 +109,18 @@ LRT_D float3 bsdf_eval(const SceneView &sc, int bsdf_id, float2 uv, float3 wi, f
 
 // ptracer.cpp:285-371. bsdf_id < 0: a directly visible emitter (no scattering). `weight` comes WITHOUT the sensor's importance
 // (sds.weight), which the forward multiplies in and the lens adjoint differentiates.
-template <bool kAdj>
-LRT_D void connect_sensor(const PtArgs &A, const LensSystem &L, const PtVertex &v, const SensorDS &sds, int bsdf_id, float3 weight,
-                          unsigned &n_rays, unsigned &n_splat, float (*g_loc)[kSlots]) {
+// connect_sensor (ptracer.cpp:286-371) in pieces around its shadow ray. connect_prepare: is a connection worth a shadow ray, and
+// the ray (Interaction::spawn_ray_to, interaction.h:139-146). connect_value: what the connection carries once it is known to be
+// unoccluded (nothing in it depends on the visibility).
+LRT_D bool connect_prepare(const PtVertex &v, const SensorDS &sds, float3 weight, float3 &so, float3 &sd, float &smax) {
+    if (!(sds.valid && sds.pdf > 0.f && sds.weight != 0.f && (weight.x != 0.f || weight.y != 0.f || weight.z != 0.f))) return false;
+    so = offset_p(v.p, v.n, sds.p - v.p);
+    sd = sds.p - so; const float sdist = sqrtf(dot(sd, sd)); sd = sd * (1.f / sdist);
+    smax = sdist * (1.f - kShadowEpsilon);
+    return true;
+}
+LRT_D float3 connect_value(const PtArgs &A, const PtVertex &v, int bsdf_id, float3 weight, float3 sd) {
     const bool has_bsdf = bsdf_id >= 0;
-    if (!(sds.valid && sds.pdf > 0.f && sds.weight != 0.f && (weight.x != 0.f || weight.y != 0.f || weight.z != 0.f))) return;
-    // Interaction::spawn_ray_to (interaction.h:139-146)
-    const float3 so = offset_p(v.p, v.n, sds.p - v.p);
-    float3 sd = sds.p - so; const float sdist = sqrtf(dot(sd, sd)); sd = sd * (1.f / sdist);
-    unsigned work = 0;
-    const RayHit sh = scene_intersect(A.sc, so, sd, sdist * (1.f - kShadowEpsilon), true, work);
-    n_rays++;
-    if (sh.tri >= 0) return;
     float3 surface_weight = make_float3(1, 1, 1);
     const float3 local_d = v.to_local(sd);
     if (v.shape >= 0) {
@@ -132,7 +132,18 @@ LRT_D void connect_sensor(const PtArgs &A, const LensSystem &L, const PtVertex &
             surface_weight = bsdf_eval(A.sc, bsdf_id, v.uv, v.wi, local_d) * correction;
         }
     } else if (!has_bsdf && local_d.z <= 0.f) surface_weight = make_float3(0, 0, 0);
-    const float3 value = weight * surface_weight;
+    return weight * surface_weight;
+}
+template <bool kAdj>
+LRT_D void connect_sensor(const PtArgs &A, const LensSystem &L, const PtVertex &v, const SensorDS &sds, int bsdf_id, float3 weight,
+                          unsigned &n_rays, unsigned &n_splat, float (*g_loc)[kSlots]) {
+    float3 so, sd; float smax;
+    if (!connect_prepare(v, sds, weight, so, sd, smax)) return;
+    unsigned work = 0;
+    const RayHit sh = scene_intersect(A.sc, so, sd, smax, true, work);
+    n_rays++;
+    if (sh.tri >= 0) return;
+    const float3 value = connect_value(A, v, bsdf_id, weight, sd);
     if (!kAdj) splat(A, sds.u, sds.v, value * (sds.weight * A.sample_scale), n_splat);
     else if (value.x != 0.f || value.y != 0.f || value.z != 0.f) {
         // the vertex, its BSDF value and the visibility do not depend on the lens (the aperture point's dependence on the front
@@ -178,15 +189,16 @@ LRT_D void emitter_sample_position(const SceneView &sc, const float4 *ep, float 
 }
 
 // ptracer.cpp:96-167
-template <bool kAdj>
-LRT_D void sample_visible_emitters(const PtArgs &A, const LensSystem &L, Pcg32 &rng, unsigned &n_rays, unsigned &n_splat, float (*g_loc)[kSlots]) {
+// (up to the connection itself: the vertex on the emitter, the sensor's direction sample for it, the weight to connect with)
+// part A: every draw and the vertex (v.wi is the sensor sample's direction: set by the caller); (s3x, s3y) = the aperture sample
+LRT_D void visible_emitter_vertex_a(const PtArgs &A, Pcg32 &rng, PtVertex &v, float3 &weight, float &s3x_out, float &s3y_out) {
     if (A.shutter_open) (void) rng.next_f32();
     float idx_sample = rng.next_f32(), idx_weight;
     const int index = pick_emitter(A.sc, idx_sample, idx_weight);
     const float4 *ep = A.sc.emitters + 5 * (size_t) index;
     const float4 e0 = __ldg(ep), e1 = __ldg(ep + 1), e4 = __ldg(ep + 4);
     const float s2x = rng.next_f32(), s2y = rng.next_f32();
-    PtVertex v; float ew;
+    float ew;
     if (e4.w == 2.f) {
         // a direction towards the environment as seen from the sensor's position, converted to area measure (:117-141)
         const float3 ref_p = make_float3(A.to_world[3], A.to_world[7], A.to_world[11]);
@@ -201,10 +213,21 @@ LRT_D void sample_visible_emitters(const PtArgs &A, const LensSystem &L, Pcg32 &
     }
     v.sn = v.n; coordinate_system(v.n, v.s, v.t);
     const float s3x = rng.next_f32(), s3y = rng.next_f32();
-    const SensorDS sds = sensor_sample_direction(A, L, v.p, s3x, s3y);
-    v.wi = sds.d;
+    s3x_out = s3x; s3y_out = s3y;
     (void) rng.next_f32();                                       // the wavelength sample (unused in RGB variants)
-    const float3 weight = make_float3(e0.x, e0.y, e0.z) * (ew * idx_weight);
+    weight = make_float3(e0.x, e0.y, e0.z) * (ew * idx_weight);
+}
+
+LRT_D void visible_emitter_vertex(const PtArgs &A, const LensSystem &L, Pcg32 &rng, PtVertex &v, SensorDS &sds, float3 &weight) {
+    float a, b;
+    visible_emitter_vertex_a(A, rng, v, weight, a, b);
+    sds = sensor_sample_direction(A, L, v.p, a, b);
+    v.wi = sds.d;
+}
+template <bool kAdj>
+LRT_D void sample_visible_emitters(const PtArgs &A, const LensSystem &L, Pcg32 &rng, unsigned &n_rays, unsigned &n_splat, float (*g_loc)[kSlots]) {
+    PtVertex v; SensorDS sds; float3 weight;
+    visible_emitter_vertex(A, L, rng, v, sds, weight);
     connect_sensor<kAdj>(A, L, v, sds, -1, weight, n_rays, n_splat, g_loc);
 }
 
@@ -348,6 +371,151 @@ __global__ void __launch_bounds__(128) k_ptrace(PtArgs A) {
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------------------
+// The fast forward kernel (default sampler convention, triangle scenes): the same light paths with the render megakernel's
+// execution scheme (lrt_render.cu) instead of one thread per path run to completion. Persistent warps; every lane carries one
+// light path as a small state machine — phase 1: a path segment (closest hit), phase 2: the shadow ray of a connection — and
+// all lanes advance together through ONE traversal site in warp-uniform bursts (bvh_burst). A burst ends when 26/32 of its
+// lanes are done; those lanes then do their shading step (connection set-up through the lens, BSDF sample, next ray) and a lane
+// whose path has ended takes the next sample index of the warp's chunk at once, so traversal runs near full width although
+// the paths differ in length by orders of magnitude (profiles/r02w_ptrace_lines.txt: 5.4 lanes in the per-thread kernel).
+// Every lane draws its samples in the reference's order: the image equals k_ptrace<false>'s up to the order of the atomics.
+constexpr int kPtChunk = 64;          // sample indices handed to a warp per fetch
+
+__global__ void __launch_bounds__(128, 4) k_ptrace_queue(PtArgs A, long long n_my, int exit_drop, int leaf_min) {
+    __shared__ LensSystem L;
+    {
+        const uint4 *src = reinterpret_cast<const uint4 *>(A.lens);
+        uint4 *dst = reinterpret_cast<uint4 *>(&L);
+        for (int i = threadIdx.x; i < (int) (sizeof(LensSystem) / 16); i += blockDim.x) dst[i] = src[i];
+    }
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    unsigned n_paths = 0, n_rays = 0, n_splat = 0;
+    uint2 st[kTravStack];
+    // ---- per-lane path state
+    int phase = 0;                     // 0 idle, 1 path segment, 2 shadow ray of a connection
+    bool stage0 = false, first_ray = false;   // stage0: the connection in flight is the emitter vertex's (next: the emitter ray)
+    Pcg32 rng; rng.state = 0; rng.inc = 1;
+    float3 ro = make_float3(0, 0, 0), rd = make_float3(0, 0, 1), throughput = make_float3(0, 0, 0);
+    float3 seg_o = ro, seg_d = rd;     // the segment that produced the current vertex (its surface is rebuilt after the shadow ray)
+    RayHit seg; seg.t = 0.f; seg.u = seg.v = 0.f; seg.tri = -1;
+    float eta = 1.f; int depth = 1;
+    float pu = 0.f, pv = 0.f; float3 pval = make_float3(0, 0, 0);      // the connection waiting for its shadow ray
+    Trav T; trav_init(T, 0.f); T.cur = kTravDone;
+    long long next = 0, end = 0;       // the warp's chunk of sample numbers k (idx = shard_index + k * shard_count), warp-uniform
+    bool more = true;
+    while (true) {
+        // ---- A. idle lanes take the next sample indices (a new chunk whenever the current one is used up)
+        const unsigned im = __ballot_sync(0xffffffffu, phase == 0);
+        if (im != 0u && next >= end && more) {
+            long long c = 0;
+            if (lane == 0) c = (long long) atomicAdd(A.stats + 7, 1ULL);
+            c = __shfl_sync(0xffffffffu, c, 0);
+            next = c * kPtChunk; end = min(next + kPtChunk, n_my);
+            if (next >= n_my) { more = false; next = end = 0; }
+        }
+        const int take = (int) min((long long) __popc(im), end - next), rank = __popc(im & lt_mask);
+        bool fresh = false;
+        if (phase == 0 && rank < take) {
+            const long long idx = (long long) A.shard_index + (next + rank) * A.shard_count;
+            rng.seed_sample(A.seed, (uint32_t) idx);
+            n_paths++; fresh = true;
+        }
+        next += take;
+        if (__ballot_sync(0xffffffffu, phase != 0 || fresh) == 0u) {
+            if (!more) break;
+            continue;
+        }
+        // ---- B. the one traversal site: segments and shadow rays of different lanes advance together
+        unsigned work = 0;
+        bvh_burst(A.sc.bvh, ro, rd, T, st, phase != 0, phase == 2, exit_drop, leaf_min, work);
+        // ---- C. lanes whose ray is finished (or that have just taken a sample) do their shading step
+        if (fresh || (phase != 0 && T.cur == kTravDone)) {
+            bool need_next = false, have_si = false, want_sds = false, on_emitter = false;
+            Surface si; int bsdf_id = -1;
+            PtVertex v; float3 w_conn = make_float3(0, 0, 0); float sa = 0.f, sb = 0.f;
+            if (fresh) {
+                stage0 = true; first_ray = true; depth = 1; eta = 1.f;
+                if (A.max_depth != 0 && !A.hide_emitters) { visible_emitter_vertex_a(A, rng, v, w_conn, sa, sb); want_sds = on_emitter = true; }
+                else need_next = true;
+            } else if (phase == 2) {
+                n_rays++;
+                if (T.hit.tri < 0) splat(A, pu, pv, pval, n_splat);
+                need_next = true;
+            } else {
+                const RayHit h = T.hit;
+                n_rays++;
+                if (!first_ray) depth++;
+                bool active = depth < A.max_depth && h.tri >= 0;
+                if (!first_ray) {
+                    const bool use_rr = depth > A.rr_depth;
+                    const float q = fminf(max3(throughput) * eta * eta, .95f);
+                    const float r = active ? rng.next_f32() : 0.f;          // a masked draw: inactive lanes keep their state
+                    if (use_rr) { active = active && r < q; throughput *= 1.f / q; }
+                }
+                first_ray = false;
+                if (!active) phase = 0;
+                else {
+                    seg = h; seg_o = ro; seg_d = rd;
+                    si = make_surface(A.sc, h, ro, rd); have_si = true;
+                    bsdf_id = __ldg(A.sc.shape_bsdf + si.shape);
+                    sa = rng.next_f32(); sb = rng.next_f32();
+                    v.p = si.p; v.n = si.n; v.s = si.s; v.t = si.t; v.sn = si.sn; v.wi = si.wi; v.uv = si.uv; v.shape = si.shape;
+                    w_conn = throughput; want_sds = true;
+                }
+            }
+            // the ONE site of the sensor's direction sample (a lens trace front -> rear in strict arithmetic, the most expensive
+            // step of a vertex): emitter vertices of new paths and scene vertices of running paths go through it together
+            if (want_sds) {
+                const SensorDS sds = sensor_sample_direction(A, L, v.p, sa, sb);
+                if (on_emitter) v.wi = sds.d;
+                float3 so, sd; float smax;
+                if (connect_prepare(v, sds, w_conn, so, sd, smax)) {
+                    pval = connect_value(A, v, bsdf_id, w_conn, sd) * (sds.weight * A.sample_scale); pu = sds.u; pv = sds.v;
+                    ro = so; rd = sd; trav_init(T, smax); phase = 2;
+                } else need_next = true;
+            }
+            if (need_next) {
+                if (stage0) {            // the emitter ray (prepare_ray)
+                    stage0 = false;
+                    prepare_ray(A, rng, ro, rd, throughput);
+                    if (throughput.x != 0.f || throughput.y != 0.f || throughput.z != 0.f) { trav_init(T, kLargest); phase = 1; }
+                    else phase = 0;
+                } else {                 // sample the BSDF at the current vertex
+                    if (!have_si) { si = make_surface(A.sc, seg, seg_o, seg_d); bsdf_id = __ldg(A.sc.shape_bsdf + si.shape); }
+                    // bsdf->sample(ctx, si, next_1d(), next_2d()): the 2D sample is drawn first (see the header)
+                    const float s2x = rng.next_f32(), s2y = rng.next_f32(), s1 = rng.next_f32();
+                    BsdfResult bs = bsdf_eval_pdf_sample(A.sc, bsdf_id, si.uv, si.wi, make_float3(0, 0, 1), s1, s2x, s2y);
+                    if (bs.transmitted) {     // TransportMode::Importance: no eta^2 factor on a refraction (dielectric.cpp:363-368)
+                        const float4 b2 = __ldg(A.sc.bsdfs + 4 * (size_t) bsdf_id + 2), b3 = __ldg(A.sc.bsdfs + 4 * (size_t) bsdf_id + 3);
+                        bs.weight = make_float3(b2.w, b3.x, b3.y);
+                    }
+                    const float3 wo_w = si.to_world(bs.wo);
+                    const float wi_dot_geo_n = dot(si.n, -seg_d), wo_dot_geo_n = dot(si.n, wo_w);
+                    bool active = (wi_dot_geo_n * si.wi.z > 0.f) && (wo_dot_geo_n * bs.wo.z > 0.f);
+                    const float correction = fabsf((si.wi.z * wo_dot_geo_n) / (bs.wo.z * wi_dot_geo_n));
+                    throughput *= bs.weight * correction;
+                    eta *= bs.seta;
+                    active = active && (throughput.x != 0.f || throughput.y != 0.f || throughput.z != 0.f);
+                    if (active) { ro = offset_p(si.p, si.n, wo_w); rd = wo_w; trav_init(T, kLargest); phase = 1; }
+                    else phase = 0;
+                }
+            }
+        }
+        __syncwarp();
+    }
+    if (A.stats) {
+        unsigned long long c[3] = { n_paths, n_splat, n_rays };
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            for (int o = 16; o > 0; o >>= 1) c[k] += __shfl_down_sync(0xffffffffu, c[k], o);
+            if (lane == 0 && c[k]) atomicAdd(A.stats + k, c[k]);
+        }
+    }
+}
+
 }  // namespace lrt
 
 using namespace lrt;
@@ -411,8 +579,18 @@ static int ptrace_launch(const lrt_scene *sc, const lrt_sensor *sensor_, const l
     LRT_CUDA(cudaMemsetAsync(A.stats, 0, 8 * sizeof(unsigned long long), stream));
     int dev = 0, sms = 148; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     long long grid = (work_items + 127) / 128; grid = std::max<long long>(1, std::min<long long>(grid, (long long) sms * 16));
+    // forward renders of triangle scenes in the default convention take the queue kernel (LRT_PTRACE_SIMPLE=1: the per-thread one)
+    static const bool simple = getenv("LRT_PTRACE_SIMPLE") != nullptr && atoi(getenv("LRT_PTRACE_SIMPLE")) != 0;
     if (grad_accum_dev) k_ptrace<true><<<(int) grid, 128, 0, stream>>>(A);
-    else k_ptrace<false><<<(int) grid, 128, 0, stream>>>(A);
+    else if (A.scalar || sc->view.n_spheres > 0 || simple) k_ptrace<false><<<(int) grid, 128, 0, stream>>>(A);
+    else {
+        const char *e = getenv("LRT_PT_EXIT_DROP"); int exit_drop = e ? atoi(e) : 32;
+        exit_drop = std::max(1, std::min(32, exit_drop));
+        e = getenv("LRT_PT_LEAF_MIN"); const int leaf_min = std::max(1, e ? atoi(e) : 6);
+        const long long chunks = (work_items + kPtChunk - 1) / kPtChunk;
+        const int qgrid = (int) std::max<long long>(1, std::min<long long>((chunks + 3) / 4, (long long) sms * 4));
+        k_ptrace_queue<<<qgrid, 128, 0, stream>>>(A, work_items, exit_drop, leaf_min);
+    }
     LRT_LAUNCHED();
     LRT_CUDA(cudaGetLastError());
     return LRT_OK;
