@@ -507,8 +507,8 @@ def main():
             ptr = {"value": 1024 * 576 * 4 / (ms_pt.item() * 1e-3) / 1e6, "unit": "M light paths/s", "ms_per_render": ms_pt.item(),
                    "film": [1024, 576], "spp": 4, "connections_per_path": pst["lens_misses"] / max(pst["samples"], 1),
                    "rays_per_path": pst["rays"] / max(pst["samples"], 1),
-                   "what": "lrt_ptrace on the headline scene and lens: visible emitters + emitter rays + scene bounces, every vertex "
-                           "connected to the lens (sample_direction) and splatted (normalised, atomics); per-rank counters"}
+                   "what": "lrt_ptrace (queue kernel) on the headline scene and lens: visible emitters + emitter rays + scene bounces, every "
+                           "vertex connected to the lens (sample_direction) and splatted (normalised, atomics); per-rank counters"}
         except Exception as e:     # the extra measurement must never take the headline line down
             ptr = {"error": str(e)[:200]}
     lens_grad = None if a.no_lens_grad else lens_grad_section(mi, torch, dist, a, rank, world)
