@@ -382,7 +382,7 @@ __global__ void __launch_bounds__(128) k_ptrace(PtArgs A) {
 // Every lane draws its samples in the reference's order: the image equals k_ptrace<false>'s up to the order of the atomics.
 constexpr int kPtChunk = 64;          // sample indices handed to a warp per fetch
 
-__global__ void __launch_bounds__(128, 4) k_ptrace_queue(PtArgs A, long long n_my, int exit_drop, int leaf_min) {
+__global__ void __launch_bounds__(128, 4) k_ptrace_queue(PtArgs A, unsigned long long *counter, long long n_my, int exit_drop, int leaf_min) {
     __shared__ LensSystem L;
     {
         const uint4 *src = reinterpret_cast<const uint4 *>(A.lens);
@@ -411,7 +411,7 @@ __global__ void __launch_bounds__(128, 4) k_ptrace_queue(PtArgs A, long long n_m
         const unsigned im = __ballot_sync(0xffffffffu, phase == 0);
         if (im != 0u && next >= end && more) {
             long long c = 0;
-            if (lane == 0) c = (long long) atomicAdd(A.stats + 7, 1ULL);
+            if (lane == 0) c = (long long) atomicAdd(counter, 1ULL);
             c = __shfl_sync(0xffffffffu, c, 0);
             next = c * kPtChunk; end = min(next + kPtChunk, n_my);
             if (next >= n_my) { more = false; next = end = 0; }
@@ -589,7 +589,11 @@ static int ptrace_launch(const lrt_scene *sc, const lrt_sensor *sensor_, const l
         e = getenv("LRT_PT_LEAF_MIN"); const int leaf_min = std::max(1, e ? atoi(e) : 6);
         const long long chunks = (work_items + kPtChunk - 1) / kPtChunk;
         const int qgrid = (int) std::max<long long>(1, std::min<long long>((chunks + 3) / 4, (long long) sms * 4));
-        k_ptrace_queue<<<qgrid, 128, 0, stream>>>(A, work_items, exit_drop, leaf_min);
+        // the chunk counter: a slot of the scene's per-launch ring (as lrt_render), so that particle-tracer launches of one
+        // scene on different streams do not share their work distribution
+        unsigned long long *ctr = sc->d_counter + (sc->launch_seq.fetch_add(1, std::memory_order_relaxed) % kCounterRing);
+        LRT_CUDA(cudaMemsetAsync(ctr, 0, sizeof(unsigned long long), stream));
+        k_ptrace_queue<<<qgrid, 128, 0, stream>>>(A, ctr, work_items, exit_drop, leaf_min);
     }
     LRT_LAUNCHED();
     LRT_CUDA(cudaGetLastError());

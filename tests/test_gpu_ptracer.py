@@ -55,6 +55,79 @@ def test_gpu_ptracer_shards_sum_to_the_whole(mi):
 
 
 @pytest.mark.gpu
+def test_gpu_ptracer_launches_of_one_scene_may_overlap(mi):
+    """two renders of ONE scene issued on two streams (their kernels may run at the same time): each has its own work counter
+    (a slot of the scene's per-launch ring), so each image equals the one rendered alone"""
+    import torch
+    sc = mi.load_dict(triangle_scene(mi))          # (no spheres: the queue kernel and its chunk counter)
+    it = sc.integrator()
+    alone = [it.render(sc, seed=s).cpu().numpy() for s in (7, 8)]
+    streams = [torch.cuda.Stream(), torch.cuda.Stream()]
+    out = [None, None]
+    torch.cuda.synchronize()
+    for rep in range(3):
+        for k, s in enumerate((7, 8)):
+            with torch.cuda.stream(streams[k]):
+                out[k] = it.render(sc, seed=s)
+        torch.cuda.synchronize()
+        for k in range(2):
+            assert rel_rmse(out[k].cpu().numpy(), alone[k]) <= 1e-5, (rep, k)
+
+
+def triangle_scene(mi, lens="gauss", spp=16, res=96):
+    """a scene WITHOUT analytic spheres (those take the per-thread kernel): the Cornell box with a copper box, a glass box and
+    two emitters (tests/ref_scenes.py cbox_materials: conductor, dielectric, twosided, roulette active) behind a realistic lens"""
+    import ref_scenes as rs
+    d = dict(rs.scene_dicts(lambda m: mi.Transform4f(m))["cbox_materials"][0])
+    cam = d["sensor"]["to_world"]
+    d["integrator"] = {"type": "ptracer", "max_depth": 10, "rr_depth": 3}
+    d["sensor"] = {"type": "realisticlens", "lens_design": lens, "object_distance": 3.9, "to_world": cam, "near_clip": 1e-3, "far_clip": 100.0,
+                   "sampler": {"type": "independent", "sample_count": spp},
+                   "film": {"type": "hdrfilm", "width": res, "height": res, "rfilter": {"type": "tent"}}}
+    return d
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("lens", ["gauss", "doublet"])
+def test_gpu_ptracer_queue_kernel_vs_pinned_oracle(mi, lens):
+    """the default forward kernel of triangle scenes (k_ptrace_queue) against the pinned oracle, JIT convention, same seed"""
+    d = triangle_scene(mi, lens)
+    sc = mi.load_dict(d)
+    img = mi.render(sc, seed=5).cpu().numpy()
+    want = oracle_ptracer(mi, d, 5, 8, scalar=False)
+    err = rel_rmse(img, want)
+    st = sc.stats()
+    print(f"triangle scene, {lens}: rel-RMSE vs oracle {err:.3e}; light paths {st['samples']}, connections {st['lens_misses']}, rays {st['rays']}")
+    assert np.isfinite(img).all() and img.mean() > 0
+    assert err <= 2e-3, err
+    assert abs(img.mean() / want.mean() - 1) <= 2e-3
+
+
+@pytest.mark.gpu
+def test_gpu_ptracer_queue_kernel_equals_per_thread_kernel(mi):
+    """the queue kernel (persistent warps, per-lane path state machines) draws the same samples per path as the
+    one-thread-per-path kernel it replaced (still behind LRT_PTRACE_SIMPLE / the adjoint / the scalar convention / spheres):
+    same image up to the order of the float atomics, same path / ray / connection counts"""
+    import subprocess
+    import sys
+    import tempfile
+    code = ("import os, sys, numpy as np; sys.path.insert(0, %r); sys.path.insert(0, %r); import lensrt as mi\n"
+            "from test_gpu_ptracer import triangle_scene\n"
+            "sc = mi.load_dict(triangle_scene(mi)); img = mi.render(sc, seed=3).cpu().numpy()\n"
+            "st = sc.stats(); np.savez(sys.argv[1], img=img, st=np.array([st['samples'], st['rays'], st['lens_misses']]))\n"
+            % (ROOT, os.path.join(ROOT, "tests")))
+    res = []
+    with tempfile.TemporaryDirectory() as tmp:
+        for k, simple in enumerate(("0", "1")):
+            fn = os.path.join(tmp, f"r{k}.npz")
+            env = dict(os.environ, LRT_PTRACE_SIMPLE=simple)
+            subprocess.run([sys.executable, "-c", code, fn], check=True, env=env, timeout=300)
+            res.append(dict(np.load(fn)))
+    assert (res[0]["st"] == res[1]["st"]).all(), (res[0]["st"], res[1]["st"])
+    assert res[0]["st"][0] > 0 and rel_rmse(res[0]["img"], res[1]["img"]) <= 1e-5
+
+
+@pytest.mark.gpu
 def test_gpu_ptracer_errors(mi):
     d = mi.xml_to_dict(path=os.path.join(XML, "room.xml"), integrator="ptracer")
     sc = mi.load_dict(d)
