@@ -372,7 +372,7 @@ __global__ void __launch_bounds__(128) k_ptrace(PtArgs A) {
 }
 
 // ---------------------------------------------------------------------------------------------------------------------------
-// The fast forward kernel (default sampler convention, triangle scenes): the same light paths with the render megakernel's
+// The fast forward kernel (default sampler convention): the same light paths with the render megakernel's
 // execution scheme (lrt_render.cu) instead of one thread per path run to completion. Persistent warps; every lane carries one
 // light path as a small state machine — phase 1: a path segment (closest hit), phase 2: the shadow ray of a connection — and
 // all lanes advance together through ONE traversal site in warp-uniform bursts (bvh_burst). A burst ends when 26/32 of its
@@ -404,6 +404,18 @@ __global__ void __launch_bounds__(128, 4) k_ptrace_queue(PtArgs A, unsigned long
     float eta = 1.f; int depth = 1;
     float pu = 0.f, pv = 0.f; float3 pval = make_float3(0, 0, 0);      // the connection waiting for its shadow ray
     Trav T; trav_init(T, 0.f); T.cur = kTravDone;
+    // analytic spheres (outside the BVH) are tested when a ray starts, as in the render kernel: the traversal then runs with the
+    // sphere's distance as its limit, a shadow ray that a sphere blocks skips it; the sphere's index + 1 rides in T.hit.u
+    auto start_ray = [&](float maxt, bool any_hit) {
+        int sph = -1;
+        if (A.sc.n_spheres > 0) {
+            float t = maxt;
+            sph = spheres_intersect(A.sc, ro, rd, maxt, any_hit, t);
+            if (sph >= 0) maxt = t;
+        }
+        trav_init(T, maxt);
+        if (sph >= 0) { T.hit.u = __int_as_float(sph + 1); if (any_hit) T.cur = kTravDone; }
+    };
     long long next = 0, end = 0;       // the warp's chunk of sample numbers k (idx = shard_index + k * shard_count), warp-uniform
     bool more = true;
     while (true) {
@@ -442,10 +454,11 @@ __global__ void __launch_bounds__(128, 4) k_ptrace_queue(PtArgs A, unsigned long
                 else need_next = true;
             } else if (phase == 2) {
                 n_rays++;
-                if (T.hit.tri < 0) splat(A, pu, pv, pval, n_splat);
+                if (T.hit.tri < 0 && T.hit.u == 0.f) splat(A, pu, pv, pval, n_splat);      // (u != 0 without a triangle: a sphere is in the way)
                 need_next = true;
             } else {
-                const RayHit h = T.hit;
+                RayHit h = T.hit;
+                if (h.tri < 0 && h.u != 0.f) { h.tri = A.sc.n_tris + __float_as_int(h.u) - 1; h.t = T.tmax; h.u = 0.f; }     // the sphere is the closest hit
                 n_rays++;
                 if (!first_ray) depth++;
                 bool active = depth < A.max_depth && h.tri >= 0;
@@ -474,14 +487,14 @@ __global__ void __launch_bounds__(128, 4) k_ptrace_queue(PtArgs A, unsigned long
                 float3 so, sd; float smax;
                 if (connect_prepare(v, sds, w_conn, so, sd, smax)) {
                     pval = connect_value(A, v, bsdf_id, w_conn, sd) * (sds.weight * A.sample_scale); pu = sds.u; pv = sds.v;
-                    ro = so; rd = sd; trav_init(T, smax); phase = 2;
+                    ro = so; rd = sd; start_ray(smax, true); phase = 2;
                 } else need_next = true;
             }
             if (need_next) {
                 if (stage0) {            // the emitter ray (prepare_ray)
                     stage0 = false;
                     prepare_ray(A, rng, ro, rd, throughput);
-                    if (throughput.x != 0.f || throughput.y != 0.f || throughput.z != 0.f) { trav_init(T, kLargest); phase = 1; }
+                    if (throughput.x != 0.f || throughput.y != 0.f || throughput.z != 0.f) { start_ray(kLargest, false); phase = 1; }
                     else phase = 0;
                 } else {                 // sample the BSDF at the current vertex
                     if (!have_si) { si = make_surface(A.sc, seg, seg_o, seg_d); bsdf_id = __ldg(A.sc.shape_bsdf + si.shape); }
@@ -499,7 +512,7 @@ __global__ void __launch_bounds__(128, 4) k_ptrace_queue(PtArgs A, unsigned long
                     throughput *= bs.weight * correction;
                     eta *= bs.seta;
                     active = active && (throughput.x != 0.f || throughput.y != 0.f || throughput.z != 0.f);
-                    if (active) { ro = offset_p(si.p, si.n, wo_w); rd = wo_w; trav_init(T, kLargest); phase = 1; }
+                    if (active) { ro = offset_p(si.p, si.n, wo_w); rd = wo_w; start_ray(kLargest, false); phase = 1; }
                     else phase = 0;
                 }
             }
@@ -582,7 +595,7 @@ static int ptrace_launch(const lrt_scene *sc, const lrt_sensor *sensor_, const l
     // forward renders of triangle scenes in the default convention take the queue kernel (LRT_PTRACE_SIMPLE=1: the per-thread one)
     static const bool simple = getenv("LRT_PTRACE_SIMPLE") != nullptr && atoi(getenv("LRT_PTRACE_SIMPLE")) != 0;
     if (grad_accum_dev) k_ptrace<true><<<(int) grid, 128, 0, stream>>>(A);
-    else if (A.scalar || sc->view.n_spheres > 0 || simple) k_ptrace<false><<<(int) grid, 128, 0, stream>>>(A);
+    else if (A.scalar || simple) k_ptrace<false><<<(int) grid, 128, 0, stream>>>(A);
     else {
         const char *e = getenv("LRT_PT_EXIT_DROP"); int exit_drop = e ? atoi(e) : 32;
         exit_drop = std::max(1, std::min(32, exit_drop));

@@ -75,7 +75,7 @@ def test_gpu_ptracer_launches_of_one_scene_may_overlap(mi):
 
 
 def triangle_scene(mi, lens="gauss", spp=16, res=96):
-    """a scene WITHOUT analytic spheres (those take the per-thread kernel): the Cornell box with a copper box, a glass box and
+    """a triangle-only scene: the Cornell box with a copper box, a glass box and
     two emitters (tests/ref_scenes.py cbox_materials: conductor, dielectric, twosided, roulette active) behind a realistic lens"""
     import ref_scenes as rs
     d = dict(rs.scene_dicts(lambda m: mi.Transform4f(m))["cbox_materials"][0])
@@ -106,7 +106,7 @@ def test_gpu_ptracer_queue_kernel_vs_pinned_oracle(mi, lens):
 @pytest.mark.gpu
 def test_gpu_ptracer_queue_kernel_equals_per_thread_kernel(mi):
     """the queue kernel (persistent warps, per-lane path state machines) draws the same samples per path as the
-    one-thread-per-path kernel it replaced (still behind LRT_PTRACE_SIMPLE / the adjoint / the scalar convention / spheres):
+    one-thread-per-path kernel it replaced (still behind LRT_PTRACE_SIMPLE / the adjoint / the scalar convention):
     same image up to the order of the float atomics, same path / ray / connection counts"""
     import subprocess
     import sys
