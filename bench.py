@@ -504,7 +504,17 @@ def main():
             if world > 1:
                 dist.all_reduce(ms_pt, op=dist.ReduceOp.MAX)
             pst = scene.stats()
+            # its lens adjoint (lrt_ptrace_backward: every connection of the same light paths differentiated), rank 0's share
+            gimg = torch.ones((576, 1024, 3), dtype=torch.float32, device="cuda")
+            pit.render_backward_lens(scene, gimg, sensor=psens, seed=1, spp=4, shard=(rank, world)); torch.cuda.synchronize()
+            eb2 = [torch.cuda.Event(enable_timing=True) for _ in range(2)]
+            eb2[0].record()
+            for i in range(3):
+                pit.render_backward_lens(scene, gimg, sensor=psens, seed=10 + i, spp=4, shard=(rank, world))
+            eb2[1].record(); torch.cuda.synchronize()
+            ms_ptb = eb2[0].elapsed_time(eb2[1]) / 3
             ptr = {"value": 1024 * 576 * 4 / (ms_pt.item() * 1e-3) / 1e6, "unit": "M light paths/s", "ms_per_render": ms_pt.item(),
+                   "lens_adjoint_ms": ms_ptb, "lens_adjoint_M_paths_per_s": 1024 * 576 * 4 / world / (ms_ptb * 1e-3) / 1e6,
                    "film": [1024, 576], "spp": 4, "connections_per_path": pst["lens_misses"] / max(pst["samples"], 1),
                    "rays_per_path": pst["rays"] / max(pst["samples"], 1),
                    "what": "lrt_ptrace (queue kernel) on the headline scene and lens: visible emitters + emitter rays + scene bounces, every "

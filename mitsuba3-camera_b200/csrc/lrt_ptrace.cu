@@ -382,8 +382,15 @@ __global__ void __launch_bounds__(128) k_ptrace(PtArgs A) {
 // Every lane draws its samples in the reference's order: the image equals k_ptrace<false>'s up to the order of the atomics.
 constexpr int kPtChunk = 64;          // sample indices handed to a warp per fetch
 
+template <bool kAdj>
 __global__ void __launch_bounds__(128, 4) k_ptrace_queue(PtArgs A, unsigned long long *counter, long long n_my, int exit_drop, int leaf_min) {
     __shared__ LensSystem L;
+    __shared__ float s_grad[kAdj ? kMaxInterfaces * kSlots : 1];
+    float g_loc[kAdj ? kMaxInterfaces : 1][kSlots];       // kAdj: this thread's share of d(loss)/d(interface table)
+    if (kAdj) {
+        for (int i = threadIdx.x; i < kMaxInterfaces * kSlots; i += blockDim.x) s_grad[i] = 0.f;
+        for (int i = 0; i < kMaxInterfaces; ++i) for (int q = 0; q < kSlots; ++q) g_loc[i][q] = 0.f;
+    }
     {
         const uint4 *src = reinterpret_cast<const uint4 *>(A.lens);
         uint4 *dst = reinterpret_cast<uint4 *>(&L);
@@ -403,6 +410,7 @@ __global__ void __launch_bounds__(128, 4) k_ptrace_queue(PtArgs A, unsigned long
     RayHit seg; seg.t = 0.f; seg.u = seg.v = 0.f; seg.tri = -1;
     float eta = 1.f; int depth = 1;
     float pu = 0.f, pv = 0.f; float3 pval = make_float3(0, 0, 0);      // the connection waiting for its shadow ray
+    float3 pref = make_float3(0, 0, 0);                                  // kAdj: its camera-space reference point; (pu, pv) = the aperture sample
     Trav T; trav_init(T, 0.f); T.cur = kTravDone;
     // analytic spheres (outside the BVH) are tested when a ray starts, as in the render kernel: the traversal then runs with the
     // sphere's distance as its limit, a shadow ray that a sphere blocks skips it; the sphere's index + 1 rides in T.hit.u
@@ -454,7 +462,14 @@ __global__ void __launch_bounds__(128, 4) k_ptrace_queue(PtArgs A, unsigned long
                 else need_next = true;
             } else if (phase == 2) {
                 n_rays++;
-                if (T.hit.tri < 0 && T.hit.u == 0.f) splat(A, pu, pv, pval, n_splat);      // (u != 0 without a triangle: a sphere is in the way)
+                if (T.hit.tri < 0 && T.hit.u == 0.f) {                                     // (u != 0 without a triangle: a sphere is in the way)
+                    if (!kAdj) splat(A, pu, pv, pval, n_splat);
+                    else if (pval.x != 0.f || pval.y != 0.f || pval.z != 0.f) {
+                        // the connection's lens adjoint (see connect_sensor<true>): the spot path's adjoint for this reference point
+                        if (lens_connection_adjoint(L, A.film, strict::v3(pref.x, pref.y, pref.z), pu, pv, 0.f, pval.x, pval.y, pval.z,
+                                                    A.sample_scale, 0.f, A.grad_accum, g_loc)) n_splat++;
+                    }
+                }
                 need_next = true;
             } else {
                 RayHit h = T.hit;
@@ -486,7 +501,9 @@ __global__ void __launch_bounds__(128, 4) k_ptrace_queue(PtArgs A, unsigned long
                 if (on_emitter) v.wi = sds.d;
                 float3 so, sd; float smax;
                 if (connect_prepare(v, sds, w_conn, so, sd, smax)) {
-                    pval = connect_value(A, v, bsdf_id, w_conn, sd) * (sds.weight * A.sample_scale); pu = sds.u; pv = sds.v;
+                    pval = connect_value(A, v, bsdf_id, w_conn, sd);
+                    if (!kAdj) { pval *= sds.weight * A.sample_scale; pu = sds.u; pv = sds.v; }
+                    else { pref = sds.ref; pu = sds.a; pv = sds.b; }
                     ro = so; rd = sd; start_ray(smax, true); phase = 2;
                 } else need_next = true;
             }
@@ -518,6 +535,23 @@ __global__ void __launch_bounds__(128, 4) k_ptrace_queue(PtArgs A, unsigned long
             }
         }
         __syncwarp();
+    }
+    if (kAdj) {     // per-thread slots -> warp -> CTA -> one global atomic per slot (as k_ptrace<true> and the spot adjoint)
+        const int n_if = L.n;
+        for (int i = 0; i < n_if; ++i)
+            for (int q = 0; q < kSlots; ++q) {
+                float v = g_loc[i][q];
+                for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+                if (lane == 0 && v != 0.f) atomicAdd(&s_grad[i * kSlots + q], v);
+            }
+        __syncthreads();
+        for (int i = threadIdx.x; i < n_if * kSlots; i += blockDim.x) {
+            const float v = s_grad[i];
+            if (v == 0.f) continue;
+            const int r = i / kSlots, q = i - r * kSlots;
+            const int col = q == 0 ? G_Z : (q == 1 ? G_R : (q == 2 ? G_K : (q < 10 ? G_A0 + (q - 3) : (q == 10 ? G_IORL : G_IORR))));
+            atomicAdd(A.grad_rows + r * kGradRow + col, v);
+        }
     }
     if (A.stats) {
         unsigned long long c[3] = { n_paths, n_splat, n_rays };
@@ -594,9 +628,10 @@ static int ptrace_launch(const lrt_scene *sc, const lrt_sensor *sensor_, const l
     long long grid = (work_items + 127) / 128; grid = std::max<long long>(1, std::min<long long>(grid, (long long) sms * 16));
     // forward renders of triangle scenes in the default convention take the queue kernel (LRT_PTRACE_SIMPLE=1: the per-thread one)
     static const bool simple = getenv("LRT_PTRACE_SIMPLE") != nullptr && atoi(getenv("LRT_PTRACE_SIMPLE")) != 0;
-    if (grad_accum_dev) k_ptrace<true><<<(int) grid, 128, 0, stream>>>(A);
-    else if (A.scalar || simple) k_ptrace<false><<<(int) grid, 128, 0, stream>>>(A);
-    else {
+    if (A.scalar || simple) {
+        if (grad_accum_dev) k_ptrace<true><<<(int) grid, 128, 0, stream>>>(A);
+        else k_ptrace<false><<<(int) grid, 128, 0, stream>>>(A);
+    } else {
         const char *e = getenv("LRT_PT_EXIT_DROP"); int exit_drop = e ? atoi(e) : 32;
         exit_drop = std::max(1, std::min(32, exit_drop));
         e = getenv("LRT_PT_LEAF_MIN"); const int leaf_min = std::max(1, e ? atoi(e) : 6);
@@ -606,7 +641,8 @@ static int ptrace_launch(const lrt_scene *sc, const lrt_sensor *sensor_, const l
         // scene on different streams do not share their work distribution
         unsigned long long *ctr = sc->d_counter + (sc->launch_seq.fetch_add(1, std::memory_order_relaxed) % kCounterRing);
         LRT_CUDA(cudaMemsetAsync(ctr, 0, sizeof(unsigned long long), stream));
-        k_ptrace_queue<<<qgrid, 128, 0, stream>>>(A, ctr, work_items, exit_drop, leaf_min);
+        if (grad_accum_dev) k_ptrace_queue<true><<<qgrid, 128, 0, stream>>>(A, ctr, work_items, exit_drop, leaf_min);
+        else k_ptrace_queue<false><<<qgrid, 128, 0, stream>>>(A, ctr, work_items, exit_drop, leaf_min);
     }
     LRT_LAUNCHED();
     LRT_CUDA(cudaGetLastError());

@@ -114,7 +114,10 @@ def test_gpu_ptracer_queue_kernel_equals_per_thread_kernel(mi):
     code = ("import os, sys, numpy as np; sys.path.insert(0, %r); sys.path.insert(0, %r); import lensrt as mi\n"
             "from test_gpu_ptracer import triangle_scene\n"
             "sc = mi.load_dict(triangle_scene(mi)); img = mi.render(sc, seed=3).cpu().numpy()\n"
-            "st = sc.stats(); np.savez(sys.argv[1], img=img, st=np.array([st['samples'], st['rays'], st['lens_misses']]))\n"
+            "st = sc.stats(); G = np.random.default_rng(1).standard_normal(img.shape).astype(np.float32)\n"
+            "rows = sc.integrator().render_backward_lens(sc, G, seed=3).cpu().numpy(); st2 = sc.stats()\n"
+            "np.savez(sys.argv[1], img=img, rows=rows, st=np.array([st['samples'], st['rays'], st['lens_misses']]),\n"
+            "         st2=np.array([st2['samples'], st2['rays'], st2['lens_misses']]))\n"
             % (ROOT, os.path.join(ROOT, "tests")))
     res = []
     with tempfile.TemporaryDirectory() as tmp:
@@ -125,6 +128,10 @@ def test_gpu_ptracer_queue_kernel_equals_per_thread_kernel(mi):
             res.append(dict(np.load(fn)))
     assert (res[0]["st"] == res[1]["st"]).all(), (res[0]["st"], res[1]["st"])
     assert res[0]["st"][0] > 0 and rel_rmse(res[0]["img"], res[1]["img"]) <= 1e-5
+    # ... and the lens adjoint (k_ptrace_queue<true> vs k_ptrace<true>): same connections, same gradient of the interface table
+    assert (res[0]["st2"] == res[1]["st2"]).all(), (res[0]["st2"], res[1]["st2"])
+    g0, g1 = res[0]["rows"].astype(np.float64), res[1]["rows"].astype(np.float64)
+    assert np.abs(g1).max() > 0 and np.abs(g0 - g1).max() <= 1e-4 * np.abs(g1).max(), (np.abs(g0 - g1).max(), np.abs(g1).max())
 
 
 @pytest.mark.gpu
