@@ -118,7 +118,10 @@ int lrt_sensor_sample_ray_host(const lrt_sensor *s, int64_t n, const float *pos2
  * [0, A, B, -, -, -, -] or [1, B1, B2, B3, C1, C2, C3].
  * lrt_sensor_sample_ray_wl = Sensor::sample_ray of a spectral variant, geometric part: out10 as lrt_sensor_sample_ray (the
  * caller multiplies the weight by sample_wavelengths()' own). lrt_sensor_trace_wl = trace_ray_from_film / _from_world with the
- * ray's wavelength, on the device: od6 / out7 as lrt_sensor_trace_host. Rear-element sampling only. */
+ * ray's wavelength, on the device: od6 / out7 as lrt_sensor_trace_host. */
+/* compute_exit_pupil_bounds as a SPECTRAL variant runs it (realisticlens.cpp:1718-1727): every ray of the LUT build carries the
+ * wavelength lerp(380, 700, RadicalInverse(2, i)) nm. Needed before the _wl entry points may sample the exit pupil. */
+int lrt_sensor_set_exit_pupil_spectral(lrt_sensor *s, int32_t enable, float shutter_open_time, void *stream);
 int lrt_sensor_set_materials(lrt_sensor *s, int32_t n, const float *mat_lr14);
 int lrt_sensor_get_materials(const lrt_sensor *s, float *mat_lr14);
 int lrt_sensor_sample_ray_wl(const lrt_sensor *s, int64_t n, const float *pos2_dev, const float *ap2_dev,

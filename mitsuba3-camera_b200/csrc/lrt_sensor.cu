@@ -280,12 +280,17 @@ __global__ void __launch_bounds__(256) k_sampler_draw(uint32_t seed, uint32_t id
 // already inside the box found so far; the box is the min / max over TRANSMITTED points either way, so the order does not
 // matter. out[seg] = { min.x, min.y, max.x, max.y as order-preserving uints, transmitted count }.
 LRT_D uint32_t ordered_bits(float f) { const uint32_t u = __float_as_uint(f); return (u & 0x80000000u) ? ~u : (u | 0x80000000u); }
-__global__ void __launch_bounds__(256) k_exit_pupil(const LensSystem *__restrict__ Lg, uint32_t *__restrict__ out) {
+// kWl: the spectral variants' LUT (realisticlens.cpp:1718-1727): every ray of a segment carries the wavelength
+// lerp(380, 700, RadicalInverse(2, i)) nm and refracts with the media's IORs at that wavelength
+template <bool kWl>
+__global__ void __launch_bounds__(256) k_exit_pupil(const LensSystem *__restrict__ Lg, const float *__restrict__ mat_lr, uint32_t *__restrict__ out) {
     __shared__ LensSystem L;
+    __shared__ float M[kWl ? kMaxInterfaces * 14 : 1];
     {
         const uint4 *src = reinterpret_cast<const uint4 *>(Lg);
         uint4 *dst = reinterpret_cast<uint4 *>(&L);
         for (int i = threadIdx.x; i < (int) (sizeof(LensSystem) / 16); i += blockDim.x) dst[i] = src[i];
+        if (kWl) for (int i = threadIdx.x; i < Lg->n * 14; i += blockDim.x) M[i] = mat_lr[i];
     }
     __syncthreads();
     using namespace strict;
@@ -299,7 +304,9 @@ __global__ void __launch_bounds__(256) k_exit_pupil(const LensSystem *__restrict
         const float fx = lerp_drjit(r0, r1, div(add((float) i, .5f), (float) n_rays));
         const float px = lerp_drjit(-R, R, radical_inverse(0, i)), py = lerp_drjit(-R, R, radical_inverse(1, i));
         LensRay ray; ray.o = v3(fx, 0.f, 0.f); ray.d = normalize(sub(v3(px, py, rear_z), ray.o));
-        if (lens_trace_from_film(L.ifs, L.n, ray)) {
+        const bool through = kWl ? lens_trace_wl(L.ifs, L.n, ray, M, lerp_drjit(380.f, 700.f, radical_inverse(2, i)), false)
+                                 : lens_trace_from_film(L.ifs, L.n, ray);
+        if (through) {
             mnx = min(mnx, ordered_bits(px)); mxx = max(mxx, ordered_bits(px));
             mny = min(mny, ordered_bits(py)); mxy = max(mxy, ordered_bits(py));
             cnt++;
@@ -319,8 +326,22 @@ __global__ void __launch_bounds__(256) k_exit_pupil(const LensSystem *__restrict
 static float from_ordered_bits(uint32_t u) { u = (u & 0x80000000u) ? (u & 0x7fffffffu) : ~u; float f; memcpy(&f, &u, 4); return f; }
 
 // compute_exit_pupil_bounds (realisticlens.cpp:1769-1809): fills host.pupil_bounds from the current interfaces
-static int build_exit_pupil(lrt_sensor *s, cudaStream_t stream) {
+static int upload_materials(lrt_sensor *s, cudaStream_t stream) {
+    LRT_REQUIRE(s->host.kind == 0 && (int) s->mat_lr.size() == 14 * s->host.n,
+                "this sensor has no dispersion data: build it from a prescription or call lrt_sensor_set_materials");
+    LRT_REQUIRE(!s->host.pupil_mode || s->pupil_spectral,
+                "exit-pupil sampling with per-ray wavelengths needs the spectral LUT: enable it with lrt_sensor_set_exit_pupil_spectral");
+    if (!s->d_mat_lr) {
+        LRT_CUDA(cudaMalloc(&s->d_mat_lr, sizeof(float) * 14 * kMaxInterfaces));
+        LRT_CUDA(cudaMemcpyAsync(s->d_mat_lr, s->mat_lr.data(), sizeof(float) * s->mat_lr.size(), cudaMemcpyHostToDevice, stream));
+        LRT_CUDA(cudaStreamSynchronize(stream));        // mat_lr is pageable host memory
+    }
+    return LRT_OK;
+}
+
+static int build_exit_pupil(lrt_sensor *s, cudaStream_t stream, bool spectral = false) {
     LRT_REQUIRE(s->host.kind == 0 && s->host.n > 0, "exit-pupil sampling needs a lens sensor");
+    if (spectral) { const int was_mode = s->host.pupil_mode; s->host.pupil_mode = 0; int rc_ = upload_materials(s, stream); s->host.pupil_mode = was_mode; if (rc_) return rc_; }
     const int was = s->host.pupil_mode;
     s->host.pupil_mode = 0; s->dev_dirty = true;      // the build itself traces plain film -> world rays
     int rc = s->upload(stream); if (rc) return rc;
@@ -329,7 +350,8 @@ static int build_exit_pupil(lrt_sensor *s, cudaStream_t stream) {
     LRT_CUDA(cudaMalloc(&d, sizeof init));
     cudaError_t e = cudaMemcpyAsync(d, init, sizeof init, cudaMemcpyHostToDevice, stream);
     if (e == cudaSuccess) {
-        k_exit_pupil<<<dim3(148, kPupilSegments), 256, 0, stream>>>(s->dev, d);
+        if (spectral) k_exit_pupil<true><<<dim3(148, kPupilSegments), 256, 0, stream>>>(s->dev, s->d_mat_lr, d);
+        else k_exit_pupil<false><<<dim3(148, kPupilSegments), 256, 0, stream>>>(s->dev, nullptr, d);
         LRT_LAUNCHED();
         e = cudaGetLastError();
     }
@@ -531,7 +553,17 @@ int lrt_sensor_set_exit_pupil(lrt_sensor *s, int32_t enable, float shutter_open_
     if (!enable) { s->host.pupil_mode = 0; return LRT_OK; }
     LRT_NEED_DEVICE();
     int rc = build_exit_pupil(s, (cudaStream_t) stream); if (rc) return rc;
-    s->host.pupil_mode = 1; s->dev_dirty = true;
+    s->host.pupil_mode = 1; s->pupil_spectral = false; s->dev_dirty = true;
+    return LRT_OK;
+}
+int lrt_sensor_set_exit_pupil_spectral(lrt_sensor *s, int32_t enable, float shutter_open_time, void *stream) {
+    LRT_REQUIRE(s, "null argument");
+    s->host.shutter_open_time = shutter_open_time;
+    s->dev_dirty = true;
+    if (!enable) { s->host.pupil_mode = 0; s->pupil_spectral = false; return LRT_OK; }
+    LRT_NEED_DEVICE();
+    int rc = build_exit_pupil(s, (cudaStream_t) stream, true); if (rc) return rc;
+    s->host.pupil_mode = 1; s->pupil_spectral = true; s->dev_dirty = true;
     return LRT_OK;
 }
 int lrt_sensor_get_exit_pupil(const lrt_sensor *s, float *bounds256) {
@@ -566,18 +598,6 @@ int lrt_sensor_sample_ray(const lrt_sensor *s_, int64_t n, const float *pos2, co
     k_sample_ray<<<grid_for(n, 256), 256, 0, (cudaStream_t) stream>>>(s->dev, n, (const float2 *) pos2, (const float2 *) ap2, out10);
     LRT_LAUNCHED();
     LRT_CUDA(cudaGetLastError());
-    return LRT_OK;
-}
-
-static int upload_materials(lrt_sensor *s, cudaStream_t stream) {
-    LRT_REQUIRE(s->host.kind == 0 && (int) s->mat_lr.size() == 14 * s->host.n,
-                "this sensor has no dispersion data: build it from a prescription or call lrt_sensor_set_materials");
-    LRT_REQUIRE(!s->host.pupil_mode, "the wavelength-aware entry points sample the rear element (the spectral exit-pupil LUT is not built)");
-    if (!s->d_mat_lr) {
-        LRT_CUDA(cudaMalloc(&s->d_mat_lr, sizeof(float) * 14 * kMaxInterfaces));
-        LRT_CUDA(cudaMemcpyAsync(s->d_mat_lr, s->mat_lr.data(), sizeof(float) * s->mat_lr.size(), cudaMemcpyHostToDevice, stream));
-        LRT_CUDA(cudaStreamSynchronize(stream));        // mat_lr is pageable host memory
-    }
     return LRT_OK;
 }
 

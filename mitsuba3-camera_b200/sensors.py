@@ -139,7 +139,8 @@ class RealisticLensCamera(Sensor):
         # realisticlens.cpp:913-921: build the exit-pupil LUT (a GPU kernel here). An open shutter is registered either way:
         # render_sample draws a time sample whenever shutter_open_time() > 0 (integrator.cpp:442-444)
         if self.sample_exit_pupil or self._shutter_open_time != 0.0:
-            capi.check(capi.lib.lrt_sensor_set_exit_pupil(self.handle, C.c_int32(int(bool(self.sample_exit_pupil))),
+            fn = capi.lib.lrt_sensor_set_exit_pupil_spectral if self.spectral else capi.lib.lrt_sensor_set_exit_pupil
+            capi.check(fn(self.handle, C.c_int32(int(bool(self.sample_exit_pupil))),
                                                           capi.c_f(self._shutter_open_time), None))
 
     def needs_aperture_sample(self) -> bool:   # m_needs_sample_3 = true (:840)
@@ -155,7 +156,8 @@ class RealisticLensCamera(Sensor):
         """Switch `sample_exit_pupil` on an existing sensor (builds the LUT when enabling)."""
         if shutter_open_time is not None:
             self._shutter_open_time = float(shutter_open_time)
-        capi.check(capi.lib.lrt_sensor_set_exit_pupil(self.handle, C.c_int32(int(enable)), capi.c_f(self._shutter_open_time), None))
+        fn = capi.lib.lrt_sensor_set_exit_pupil_spectral if self.spectral else capi.lib.lrt_sensor_set_exit_pupil
+        capi.check(fn(self.handle, C.c_int32(int(enable)), capi.c_f(self._shutter_open_time), None))
         self.sample_exit_pupil = bool(enable)
 
     def exit_pupil_bounds(self) -> np.ndarray:

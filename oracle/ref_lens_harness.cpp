@@ -317,7 +317,9 @@ float ref_material_ior(int cauchy, const float *coef, float wavelength_um) {
 // Exit-pupil LUT (realisticlens.cpp:913-921): `m_qmc_sampler = new RadicalInverse()` then compute_exit_pupil_bounds().
 // The generator object is assembled without its constructor (src/core/qmc.cpp is not linkable here): the three prime
 // bases eval() can be asked for (2, 3, 5) are filled as qmc.cpp:46-52 does. Returns 64 x (min.x, min.y, max.x, max.y).
-void ref_cam_compute_exit_pupil(void *h, float *out256) {
+}   // extern "C"
+template <typename Cam>
+static void cam_compute_exit_pupil(void *h, float *out256) {
     CoutSilencer quiet;
     Cam *c = (Cam *) h;
     if (!c->m_qmc_sampler) {
@@ -341,6 +343,11 @@ void ref_cam_compute_exit_pupil(void *h, float *out256) {
         out256[4 * i] = b.min.x(); out256[4 * i + 1] = b.min.y(); out256[4 * i + 2] = b.max.x(); out256[4 * i + 3] = b.max.y();
     }
 }
+extern "C" {
+void ref_cam_compute_exit_pupil(void *h, float *out256) { cam_compute_exit_pupil<Cam>(h, out256); }
+// the spectral instantiation's LUT: every ray of the build carries lerp(380, 700, RadicalInverse(2, i)) nm (:1718-1727)
+void ref_scam_compute_exit_pupil(void *h, float *out256) { cam_compute_exit_pupil<SCam>(h, out256); }
+void ref_scam_set_shutter_open_time(void *h, float t) { ((SCam *) h)->m_shutter_open_time = t; }
 float ref_radical_inverse(int base_index, uint64_t index) {
     static RadicalInverse *q = nullptr;
     if (!q) {

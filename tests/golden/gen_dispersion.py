@@ -59,6 +59,15 @@ for name in ld.all_designs():
         t2 = np.zeros((N, 7), f32)
         R.ref_scam_trace(h, C.c_int(1), C.c_int(N), fp(od), fp(np.full(N, w, f32)), fp(t2))
         out[f"{name}.world_{tag}"] = t2
+    if name in ("doublet", "gauss"):
+        # the spectral variants' exit-pupil LUT (64 x 2^20 rays, each with its own Halton wavelength) and sample_ray through it
+        lut = np.zeros((64, 4), f32)
+        R.ref_scam_compute_exit_pupil(h, fp(lut))
+        R.ref_scam_set_shutter_open_time(h, c_f(1.0))
+        rayp = np.zeros((N, 10), f32)
+        R.ref_scam_sample_ray(h, C.c_int(N), fp(pos), fp(ap), fp(wl), fp(rayp))
+        out[name + ".pupil_lut"] = lut; out[name + ".pupil_ray"] = rayp
+        print(f"   spectral exit-pupil LUT: sample_ray active {(rayp[:, 7] > 0).mean():.2f}")
     act = ray[:, 7] > 0
     print(f"{name:14s} {n:2d} interfaces, sample_ray active {act.mean():.2f}, world trace active {(tr[:, 6] > 0).mean():.2f}")
     R.ref_scam_destroy(h)

@@ -114,10 +114,31 @@ def test_gpu_dispersion_limits(mi, G):
     c = mi.RealisticLensCamera(film(mi), "custom", prescription=ld.InterfaceList(rows, film_z=0.0, fine_focus=False))
     with pytest.raises(mi.capi.LensrtError):
         c.sample_ray_wavelength(np.full((4, 2), 0.5, f32), np.full((4, 2), 0.5, f32), 550.0)
-    p = mi.RealisticLensCamera(film(mi), "gauss", spectral=True, sample_exit_pupil=True)
+    # a LUT built the rgb way (constant IORs) is not the spectral variants' LUT: refused for per-ray wavelengths
+    p = mi.RealisticLensCamera(film(mi), "gauss", spectral=True)
+    capi.check(lib.lrt_sensor_set_exit_pupil(p.handle, C.c_int32(1), C.c_float(1.0), None))
     with pytest.raises(mi.capi.LensrtError):
         p.sample_ray_wavelength(np.full((4, 2), 0.5, f32), np.full((4, 2), 0.5, f32), 550.0)
     # a scalar wavelength broadcasts; 589.3 nm through the spectral table = the table's own nominal IORs
     o, d, maxt, w = s.sample_ray_wavelength(G["gauss.pos"][:64], G["gauss.ap"][:64], 589.3)
     o2, d2, maxt2, w2 = s.sample_ray(0.0, None, torch.tensor(G["gauss.pos"][:64], device="cuda"), torch.tensor(G["gauss.ap"][:64], device="cuda"))
     assert (bits(o.cpu().numpy()) == bits(o2.cpu().numpy())).all() and (bits(d.cpu().numpy()) == bits(d2.cpu().numpy())).all()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["doublet", "gauss"])
+def test_gpu_spectral_exit_pupil_lut_and_sampling(mi, G, name):
+    """compute_exit_pupil_bounds as a spectral variant runs it — every ray of the 64 x 2^20-ray build carries the wavelength
+    lerp(380, 700, RadicalInverse(2, i)) nm (realisticlens.cpp:1718-1727) — and sample_ray through that LUT with per-ray
+    wavelengths: LUT, rays, weights and miss masks bit for bit against the reference's spectral instantiation."""
+    s = mi.RealisticLensCamera(film(mi), name, spectral=True, sample_exit_pupil=True, shutter_open=0.0, shutter_close=1.0)
+    lut = s.exit_pupil_bounds()
+    assert (bits(lut) == bits(G[name + ".pupil_lut"])).all()
+    rgb = mi.RealisticLensCamera(film(mi), name, sample_exit_pupil=True).exit_pupil_bounds()
+    assert np.abs(rgb - lut).max() > 0                                  # (not the constant-IOR LUT)
+    o, d, maxt, w = s.sample_ray_wavelength(G[name + ".pos"], G[name + ".ap"], G[name + ".wl"])
+    got = np.concatenate([o.cpu().numpy(), d.cpu().numpy(), maxt.cpu().numpy()[:, None], w.cpu().numpy()[:, None]], 1)
+    want = G[name + ".pupil_ray"]
+    act = want[:, 7] > 0
+    assert act.mean() > 0.5 and ((got[:, 7] > 0) == act).all()
+    assert (bits(got[act]) == bits(want[act, :8])).all()
