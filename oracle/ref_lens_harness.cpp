@@ -398,4 +398,18 @@ void ref_cam_sample_direction(void *h, int n, const float *p3, const float *s2, 
     }
 }
 
+// the same for the spectral instantiation (which, like the rgb one, traces the connection at Wavelength(589.3f):
+// realisticlens.cpp:2339-2344 "TODO: account for effect of dispersion on ray path")
+void ref_scam_sample_direction(void *h, int n, const float *p3, const float *s2, float *out11) {
+    SCam *c = (SCam *) h;
+    for (int i = 0; i < n; ++i) {
+        SCam::Interaction3f it = dr::zeros<SCam::Interaction3f>();
+        it.p = P3(p3[3 * i], p3[3 * i + 1], p3[3 * i + 2]); it.t = 0.f;
+        auto [ds, w] = c->sample_direction(it, P2(s2[2 * i], s2[2 * i + 1]), true);
+        float *o = out11 + 11 * i;
+        o[0] = ds.uv.x(); o[1] = ds.uv.y(); o[2] = ds.p.x(); o[3] = ds.p.y(); o[4] = ds.p.z();
+        o[5] = ds.d.x(); o[6] = ds.d.y(); o[7] = ds.d.z(); o[8] = ds.dist; o[9] = ds.pdf; o[10] = w[0];
+    }
+}
+
 }  // extern "C"

@@ -68,6 +68,15 @@ for name in ld.all_designs():
         R.ref_scam_sample_ray(h, C.c_int(N), fp(pos), fp(ap), fp(wl), fp(rayp))
         out[name + ".pupil_lut"] = lut; out[name + ".pupil_ray"] = rayp
         print(f"   spectral exit-pupil LUT: sample_ray active {(rayp[:, 7] > 0).mean():.2f}")
+    # Sensor::sample_direction of the spectral instantiation: distant / near reference points in camera space
+    pd_ = np.zeros((N, 3), f32)
+    ang = np.radians(rng.random(N) * 6.0); phi = rng.random(N) * 2 * np.pi
+    dist = np.where(np.arange(N) % 2 == 0, 1000.0, 0.5 + rng.random(N) * 5)
+    pd_[:, 0] = dist * np.tan(ang) * np.cos(phi); pd_[:, 1] = dist * np.tan(ang) * np.sin(phi); pd_[:, 2] = front_z + dist
+    s2 = rng.random((N, 2), dtype=f32); s2[N // 2:] = 0.5 + (s2[N // 2:] - 0.5) * 0.1
+    od11 = np.zeros((N, 11), f32)
+    R.ref_scam_sample_direction(h, C.c_int(N), fp(pd_), fp(s2), fp(od11))
+    out[name + ".dir_p"] = pd_; out[name + ".dir_s"] = s2; out[name + ".dir_out"] = od11
     act = ray[:, 7] > 0
     print(f"{name:14s} {n:2d} interfaces, sample_ray active {act.mean():.2f}, world trace active {(tr[:, 6] > 0).mean():.2f}")
     R.ref_scam_destroy(h)

@@ -142,3 +142,19 @@ def test_gpu_spectral_exit_pupil_lut_and_sampling(mi, G, name):
     act = want[:, 7] > 0
     assert act.mean() > 0.5 and ((got[:, 7] > 0) == act).all()
     assert (bits(got[act]) == bits(want[act, :8])).all()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ld.all_designs())
+def test_gpu_spectral_sample_direction(mi, G, name):
+    """Sensor::sample_direction of a spectral variant: the reference traces the connection at Wavelength(589.3f) whatever the
+    ray carries (realisticlens.cpp:2339-2344, its own TODO), i.e. with the nominal IORs of the spectral table — what
+    lrt_sensor_sample_direction does on a sensor built with spectral=True. Bit for bit, all designs."""
+    import ctypes as C
+    s = mi.RealisticLensCamera(film(mi), name, spectral=True)
+    p, s2, want = G[name + ".dir_p"], G[name + ".dir_s"], G[name + ".dir_out"]
+    got = np.zeros_like(want)
+    mi.capi.check(mi.capi.lib.lrt_sensor_sample_direction_host(s.handle, C.c_int64(len(p)), fp(np.ascontiguousarray(p)),
+                                                               fp(np.ascontiguousarray(s2)), fp(got)))
+    assert ((got[:, 9] > 0) == (want[:, 9] > 0)).all(), "connection mask differs"
+    assert (bits(got) == bits(want)).all()
