@@ -52,6 +52,7 @@ struct lrt_sensor {
     // dispersion mode (spectral variants): per interface the Cauchy / Sellmeier rows of its two media (left 7, right 7), in the
     // order of host.ifs; empty when the sensor was built from ready-made interfaces and lrt_sensor_set_materials was not called
     std::vector<float> mat_lr; float *d_mat_lr = nullptr;
+    float persp_fov = 0.f;                // perspective sensors: x fov in degrees (the particle tracer rebuilds camera -> sample from it)
     bool pupil_spectral = false;          // the exit-pupil LUT in use was built with per-ray wavelengths (lrt_sensor_set_exit_pupil_spectral)
     int sync_host();
 };

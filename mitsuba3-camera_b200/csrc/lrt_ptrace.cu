@@ -30,6 +30,9 @@ struct PtArgs {
     long long n_total, grain, n_ranges;    // scalar convention: ranges of `grain` samples
     int shard_index, shard_count;
     int max_depth, rr_depth, hide_emitters, shutter_open;
+    // perspective sensor (persp != 0; src/sensors/perspective.cpp:283-386): camera -> sample projection, image rectangle at z = 1,
+    // its normalisation, crop resolution, clip planes
+    int persp; float c2s[16], rect_min[2], rect_max[2], persp_norm, persp_res[2], near_clip, far_clip;
     float sample_scale;
     float *accum;
     unsigned long long *stats;             // [0] light paths, [1] connections splatted, [2] rays traced
@@ -56,7 +59,33 @@ LRT_D float3 xf_point_strict(const float *M, float3 p) {
 }
 
 // Sensor::sample_direction, world space in and out (the camera-space part is lens_sample_direction, lrt_lens.cuh)
+// PerspectiveCamera::sample_direction + importance (perspective.cpp:283-321,337-386): the pinhole needs no aperture sample
+static __device__ __noinline__ SensorDS persp_sample_direction(const PtArgs &A, float3 p_world) {
+    using namespace strict;
+    SensorDS r; r.valid = false; r.u = r.v = 0.f; r.p = r.d = make_float3(0, 0, 0); r.dist = r.pdf = r.weight = 0.f; r.a = r.b = 0.f;
+    const float3 ref = xf_point_strict(A.to_camera, p_world);
+    r.ref = ref;
+    if (!(ref.z >= A.near_clip && ref.z <= A.far_clip)) return r;
+    const float *m = A.c2s;
+    const float x = fmadd(m[2], ref.z, fmadd(m[1], ref.y, fmadd(m[0], ref.x, m[3]))), y = fmadd(m[6], ref.z, fmadd(m[5], ref.y, fmadd(m[4], ref.x, m[7]))),
+                w = fmadd(m[14], ref.z, fmadd(m[13], ref.y, fmadd(m[12], ref.x, m[15])));
+    const float iw = rcp(w), u = mul(x, iw), v = mul(y, iw);
+    if (!(u >= 0.f && u <= 1.f && v >= 0.f && v <= 1.f)) return r;
+    const float dist = sqrt(add(add(mul(ref.x, ref.x), mul(ref.y, ref.y)), mul(ref.z, ref.z))), inv_dist = rcp(dist);
+    const float lx = mul(ref.x, inv_dist), ly = mul(ref.y, inv_dist), lz = mul(ref.z, inv_dist);
+    const float inv_ct = rcp(lz), px = mul(lx, inv_ct), py = mul(ly, inv_ct);
+    const bool inside = lz > 0.f && px >= A.rect_min[0] && px <= A.rect_max[0] && py >= A.rect_min[1] && py <= A.rect_max[1];
+    const float importance = inside ? mul(mul(mul(A.persp_norm, inv_ct), inv_ct), inv_ct) : 0.f;
+    r.valid = true; r.u = mul(u, A.persp_res[0]); r.v = mul(v, A.persp_res[1]);
+    r.p = xf_point_strict(A.to_world, make_float3(0, 0, 0));
+    r.dist = dist;
+    r.d = make_float3(mul(sub(r.p.x, p_world.x), inv_dist), mul(sub(r.p.y, p_world.y), inv_dist), mul(sub(r.p.z, p_world.z), inv_dist));
+    r.pdf = 1.f; r.weight = mul(mul(importance, inv_dist), inv_dist);
+    return r;
+}
+
 LRT_D SensorDS sensor_sample_direction(const PtArgs &A, const LensSystem &L, float3 p_world, float a, float b) {
+    if (A.persp) return persp_sample_direction(A, p_world);
     SensorDS r; r.valid = false; r.u = r.v = 0.f; r.p = r.d = make_float3(0, 0, 0); r.dist = r.pdf = r.weight = 0.f;
     const float3 ref = xf_point_strict(A.to_camera, p_world);
     r.ref = ref; r.a = a; r.b = b;
@@ -191,12 +220,19 @@ LRT_D void emitter_sample_position(const SceneView &sc, const float4 *ep, float 
 // ptracer.cpp:96-167
 // (up to the connection itself: the vertex on the emitter, the sensor's direction sample for it, the weight to connect with)
 // part A: every draw and the vertex (v.wi is the sensor sample's direction: set by the caller); (s3x, s3y) = the aperture sample
-LRT_D void visible_emitter_vertex_a(const PtArgs &A, Pcg32 &rng, PtVertex &v, float3 &weight, float &s3x_out, float &s3y_out) {
+// false: a delta emitter (`directionalarea`) — nothing to connect, its draws are done
+LRT_D bool visible_emitter_vertex_a(const PtArgs &A, Pcg32 &rng, PtVertex &v, float3 &weight, float &s3x_out, float &s3y_out) {
     if (A.shutter_open) (void) rng.next_f32();
     float idx_sample = rng.next_f32(), idx_weight;
     const int index = pick_emitter(A.sc, idx_sample, idx_weight);
     const float4 *ep = A.sc.emitters + 5 * (size_t) index;
     const float4 e0 = __ldg(ep), e1 = __ldg(ep + 1), e4 = __ldg(ep + 4);
+    if (__ldg(ep + 3).w == 1.f) {
+        // EmitterFlags::Delta (ptracer.cpp:111): the emitter is not connected and the function's MASKED draws — position sample,
+        // wavelength sample — do not advance the generator; the sensor's 2D sample (unmasked, :155) does
+        (void) rng.next_f32(); (void) rng.next_f32();
+        return false;
+    }
     const float s2x = rng.next_f32(), s2y = rng.next_f32();
     float ew;
     if (e4.w == 2.f) {
@@ -216,18 +252,20 @@ LRT_D void visible_emitter_vertex_a(const PtArgs &A, Pcg32 &rng, PtVertex &v, fl
     s3x_out = s3x; s3y_out = s3y;
     (void) rng.next_f32();                                       // the wavelength sample (unused in RGB variants)
     weight = make_float3(e0.x, e0.y, e0.z) * (ew * idx_weight);
+    return true;
 }
 
-LRT_D void visible_emitter_vertex(const PtArgs &A, const LensSystem &L, Pcg32 &rng, PtVertex &v, SensorDS &sds, float3 &weight) {
+LRT_D bool visible_emitter_vertex(const PtArgs &A, const LensSystem &L, Pcg32 &rng, PtVertex &v, SensorDS &sds, float3 &weight) {
     float a, b;
-    visible_emitter_vertex_a(A, rng, v, weight, a, b);
+    if (!visible_emitter_vertex_a(A, rng, v, weight, a, b)) return false;
     sds = sensor_sample_direction(A, L, v.p, a, b);
     v.wi = sds.d;
+    return true;
 }
 template <bool kAdj>
 LRT_D void sample_visible_emitters(const PtArgs &A, const LensSystem &L, Pcg32 &rng, unsigned &n_rays, unsigned &n_splat, float (*g_loc)[kSlots]) {
     PtVertex v; SensorDS sds; float3 weight;
-    visible_emitter_vertex(A, L, rng, v, sds, weight);
+    if (!visible_emitter_vertex(A, L, rng, v, sds, weight)) return;
     connect_sensor<kAdj>(A, L, v, sds, -1, weight, n_rays, n_splat, g_loc);
 }
 
@@ -247,6 +285,11 @@ LRT_D void prepare_ray(const PtArgs &A, Pcg32 &rng, float3 &ro, float3 &rd, floa
         float3 s, t; coordinate_system(-v0, s, t);
         rd = s * v1.x + t * v1.y + (-v0) * v1.z;
         throughput = radiance * ((4.f * kPi * e1.w * e1.w) * kPi);
+    } else if (__ldg(ep + 3).w == 1.f) {
+        // DirectionalArea::sample_ray (directionalarea.cpp:86-110): a point on the shape, direction = its normal, weight = area x radiance
+        float3 p, n; float w; emitter_sample_position(A.sc, ep, s2x, s2y, p, n, w);
+        rd = n; ro = offset_p(p, n, rd);
+        throughput = radiance * w;
     } else {
         float3 p, n; float w; emitter_sample_position(A.sc, ep, s2x, s2y, p, n, w);
         float3 s, t; coordinate_system(n, s, t);
@@ -458,7 +501,7 @@ __global__ void __launch_bounds__(128, 4) k_ptrace_queue(PtArgs A, unsigned long
             PtVertex v; float3 w_conn = make_float3(0, 0, 0); float sa = 0.f, sb = 0.f;
             if (fresh) {
                 stage0 = true; first_ray = true; depth = 1; eta = 1.f;
-                if (A.max_depth != 0 && !A.hide_emitters) { visible_emitter_vertex_a(A, rng, v, w_conn, sa, sb); want_sds = on_emitter = true; }
+                if (A.max_depth != 0 && !A.hide_emitters && visible_emitter_vertex_a(A, rng, v, w_conn, sa, sb)) want_sds = on_emitter = true;
                 else need_next = true;
             } else if (phase == 2) {
                 n_rays++;
@@ -575,7 +618,7 @@ static int ptrace_launch(const lrt_scene *sc, const lrt_sensor *sensor_, const l
     LRT_REQUIRE(!grad_accum_dev || pp->rng_mode == 0, "the lens adjoint follows the per-sample streams (rng_mode 0)");
     lrt_sensor *sensor = const_cast<lrt_sensor *>(sensor_);
     cudaStream_t stream = (cudaStream_t) stream_;
-    LRT_REQUIRE(sensor->host.kind == 0, "lrt_ptrace connects light paths to a realistic lens (perspective sensors are not built)");
+    LRT_REQUIRE(sensor->host.kind == 0 || !grad_accum_dev, "the lens adjoint needs a realistic lens sensor");
     LRT_REQUIRE(film->channels == 4 && film->normalize == 1 && film->coalesce == 0,
                 "lrt_ptrace needs the particle tracer's film: 4 channels, normalize = 1, coalesce = 0 (integrator.cpp:706-717)");
     LRT_REQUIRE(pp->spp > 0 && pp->max_depth >= -1 && pp->rr_depth > 0, "bad parameters (spp > 0, max_depth >= -1, rr_depth > 0)");
@@ -604,6 +647,29 @@ static int ptrace_launch(const lrt_scene *sc, const lrt_sensor *sensor_, const l
         }
     }
     const lrt_film_geom &g = sensor->film;
+    if (sensor->host.kind == 1) {
+        // perspective sensor: camera -> sample (sensor.h:228-265: scale * translate * scale * translate * perspective, composed in
+        // double and rounded once), the image rectangle at z = 1 and its normalisation (perspective.cpp:186-194)
+        A.persp = 1; A.near_clip = sensor->host.near_clip; A.far_clip = sensor->host.far_clip;
+        const double W = g.width, H = g.height, aspect = W / H, relx = g.crop_w / W, rely = g.crop_h / H, offx = g.crop_x / W, offy = g.crop_y / H;
+        const double n_ = A.near_clip, f_ = A.far_clip, recip = 1.0 / (f_ - n_), cot = 1.0 / std::tan(0.5 * (double) sensor->persp_fov * 3.14159265358979323846 / 180.0);
+        auto mul4 = [](const double a[16], const double b[16], double out[16]) {
+            for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) { double v = 0; for (int k = 0; k < 4; ++k) v += a[4 * i + k] * b[4 * k + j]; out[4 * i + j] = v; }
+        };
+        const double P[16] = { cot, 0, 0, 0, 0, cot, 0, 0, 0, 0, f_ * recip, -n_ * f_ * recip, 0, 0, 1, 0 };
+        const double T2[16] = { 1, 0, 0, -1, 0, 1, 0, -1.0 / aspect, 0, 0, 1, 0, 0, 0, 0, 1 };
+        const double S2[16] = { -0.5, 0, 0, 0, 0, -0.5 * aspect, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1 };
+        const double T1[16] = { 1, 0, 0, -offx, 0, 1, 0, -offy, 0, 0, 1, 0, 0, 0, 0, 1 };
+        const double S1[16] = { 1.0 / relx, 0, 0, 0, 0, 1.0 / rely, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1 };
+        double a[16], b[16], c[16], m[16];
+        mul4(T2, P, a); mul4(S2, a, b); mul4(T1, b, c); mul4(S1, c, m);
+        for (int i = 0; i < 16; ++i) A.c2s[i] = (float) m[i];
+        const float *q = sensor->host.persp_s2c;
+        const float x0 = q[3] / q[11], y0 = q[7] / q[11], x1 = (q[0] + q[3]) / q[11], y1 = (q[5] + q[7]) / q[11];
+        A.rect_min[0] = std::min(x0, x1); A.rect_max[0] = std::max(x0, x1); A.rect_min[1] = std::min(y0, y1); A.rect_max[1] = std::max(y0, y1);
+        A.persp_norm = 1.f / ((A.rect_max[0] - A.rect_min[0]) * (A.rect_max[1] - A.rect_min[1]));
+        A.persp_res[0] = (float) g.crop_w; A.persp_res[1] = (float) g.crop_h;
+    }
     const long long film_pixels = (long long) g.width * g.height;
     A.n_total = film_pixels * pp->spp;                            // integrator.cpp:573-574: the FULL film size x spp
     LRT_REQUIRE(A.n_total <= 0xffffffffll, "width * height * spp must stay below 2^32 (split the render into passes)");

@@ -95,12 +95,16 @@ int lrt_scene_create(const lrt_scene_desc *d, lrt_scene **out) {
     s->build_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     s->n_nodes = (int64_t) nodes.size(); s->n_tris = (int64_t) tris.size(); s->bvh_depth = st.max_depth;
     s->n_shapes = d->n_shapes; s->n_bsdfs = d->n_bsdfs; s->n_emitters = d->n_emitters;
+    for (int i = 0; i < d->n_emitters; ++i) if (d->emitters[16 * i + 14] == 1.f) s->has_directional = true;
+    for (int i = 0; i < d->n_emitters; ++i)
+        if (d->emitters[16 * i + 14] == 1.f && d->emitters[16 * i + 13] == 2.f) { set_error("a `directionalarea` emitter needs a shape"); delete s; return LRT_EINVAL; }
     // emitters: 16-float rows -> 5 x float4 with the rectangle's normal and 1/area (rectangle.cpp:115-123)
     std::vector<float> em((size_t) d->n_emitters * 20, 0.f);
     std::vector<float> em_tris;     // 24 floats per triangle of a mesh emitter
     for (int i = 0; i < d->n_emitters; ++i) {
         const float *r = d->emitters + 16 * i; float *o = em.data() + 20 * (size_t) i;
         o[0] = r[0]; o[1] = r[1]; o[2] = r[2]; o[3] = r[3];
+        o[15] = r[14] == 1.f ? 1.f : 0.f;                  // `directionalarea` (directionalarea.cpp): emits along the normal only
         if (r[13] == 2.f) { o[4] = r[4]; o[5] = r[5]; o[6] = r[6]; o[7] = r[7]; o[19] = 2.f; continue; }   // environment: bounding sphere
         if (r[13] == 1.f) {   // area light on a general mesh: Mesh::build_pmf (src/render/mesh.cpp:430-470) + DiscreteDistribution
             const int shape = (int) r[3];
@@ -210,6 +214,7 @@ int lrt_render(const lrt_scene *sc, const lrt_sensor *sensor, const lrt_film_des
     LRT_NEED_DEVICE();
     LRT_REQUIRE(sc && sensor && film && rp && accum_dev, "null argument");
     LRT_REQUIRE(rp->rng_mode == 0 || rp->rng_mode == 1, "rng_mode must be 0 (per-sample streams) or 1 (scalar convention)");
+    LRT_REQUIRE(!sc->has_directional, "`directionalarea` emitters are built for the particle tracer only (lrt_ptrace)");
     LRT_REQUIRE((reinterpret_cast<uintptr_t>(accum_dev) & 15) == 0, "accum_dev must be 16-byte aligned (the tiles are flushed with 128-bit reductions)");
     if (rp->rng_mode == 1) return launch_render_scalar(sc, const_cast<lrt_sensor *>(sensor), film, rp, accum_dev, (cudaStream_t) stream);
     return launch_render(sc, const_cast<lrt_sensor *>(sensor), film, rp, accum_dev, nullptr, nullptr, nullptr, (cudaStream_t) stream);
@@ -217,6 +222,7 @@ int lrt_render(const lrt_scene *sc, const lrt_sensor *sensor, const lrt_film_des
 
 int lrt_render_backward(const lrt_scene *sc, const lrt_sensor *sensor, const lrt_film_desc *film, const lrt_render_params *rp,
                         const float *grad_storage_dev, float *grad_bsdfs_dev, float *grad_emitters_dev, void *stream) {
+    LRT_REQUIRE(!sc || !sc->has_directional, "`directionalarea` emitters are built for the particle tracer only (lrt_ptrace)");
     LRT_NEED_DEVICE();
     LRT_REQUIRE(sc && sensor && film && rp && grad_storage_dev && grad_bsdfs_dev && grad_emitters_dev, "null argument");
     LRT_REQUIRE(rp->rng_mode == 0, "the adjoint follows the JIT sampler convention (rng_mode 0)");

@@ -15,5 +15,6 @@ struct lrt_scene {
     unsigned long long *d_counter = nullptr;   // ring of work counters [0..kCounterRing), then 8 statistics words
     mutable std::atomic<unsigned> launch_seq { 0 };
     int64_t n_nodes = 0, n_tris = 0; int n_shapes = 0, n_bsdfs = 0, n_emitters = 0, n_textures = 0, bvh_depth = 0;
+    bool has_directional = false;         // some emitter is a `directionalarea` (row[14] = 1): the particle tracer only
     double build_seconds = 0;
 };

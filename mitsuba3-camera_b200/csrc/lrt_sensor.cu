@@ -474,7 +474,7 @@ int lrt_sensor_create_perspective(float x_fov_deg, const lrt_film_geom *film, co
     LRT_REQUIRE(film && tw && out, "null argument");
     lrt_sensor *s = new lrt_sensor();
     set_common(s, film, tw, near_clip, far_clip);
-    s->host.kind = 1;
+    s->host.kind = 1; s->persp_fov = x_fov_deg;
     // inverse of perspective_projection (sensor.h:262-303): S(1/rel) T(-off) S(-.5,-.5a,1) T(-1,-1/a,0) P(fov)
     double W = film->width, H = film->height, aspect = W / H;
     double relx = film->crop_w / W, rely = film->crop_h / H, offx = film->crop_x / W, offy = film->crop_y / H;

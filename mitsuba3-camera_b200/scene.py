@@ -364,6 +364,7 @@ class SceneData:
             row = np.zeros(16, f32); row[0:3] = emitter["radiance"]; row[3] = sid
             row[4:7], row[7:10], row[10:13] = emitter["center"], emitter["ex"], emitter["ey"]
             row[13] = emitter.get("kind", 0)
+            row[14] = 1.0 if emitter.get("directional", False) else 0.0
             self.emitter_rows.append(row); self.shape_emitter.append(len(self.emitter_rows) - 1)
         else:
             self.shape_emitter.append(-1)
@@ -479,6 +480,8 @@ class PTracerIntegrator(PathIntegrator):
         import torch
         s = scene.sensors()[sensor] if isinstance(sensor, int) else sensor
         spp = int(spp) if spp else s.sampler.sample_count()
+        if not hasattr(s, "interfaces"):
+            raise ValueError("render_backward_lens: the lens adjoint needs a realistic lens sensor")
         fd = film_desc(s.film, coalesce=False, normalize=True)
         gs = torch.zeros((s.film.crop_h, s.film.crop_w, 4), dtype=torch.float32, device="cuda")
         gs[..., :3] = torch.as_tensor(grad_image, dtype=torch.float32, device="cuda")
@@ -906,7 +909,7 @@ def scene_data_from_dict(d: dict):
             tw = v.get("to_world")
             tw = tw if isinstance(tw, Transform4f) else Transform4f(tw)
             b = _child(v, "bsdf", _BSDFS + ("ref",))
-            em = _child(v, "emitter", ("area",))
+            em = _child(v, "emitter", ("area", "directionalarea"))
             if b is None and em is not None:       # shape.cpp:66-73: the default BSDF of an emitter is a BLACK diffuse one
                 if default_black is None:
                     default_black = data.add_bsdf("__default_emitter", bsdf_row({"type": "diffuse", "reflectance": 0.0}))
@@ -958,14 +961,17 @@ def scene_data_from_dict(d: dict):
                     normals = -np.asarray(normals, f32)
             emitter = None
             if em is not None:
-                if em.get("type") != "area":
-                    raise ValueError(f"emitter plugin '{em.get('type')}' is outside the hot path of this build (only `area`)")
+                if em.get("type") not in ("area", "directionalarea"):
+                    raise ValueError(f"emitter plugin '{em.get('type')}' is outside the hot path of this build (only `area`, `directionalarea`)")
                 rad = em.get("radiance")
                 if isinstance(rad, dict) and rad.get("type") not in (None, "rgb", "spectrum", "uniform"):
                     raise ValueError("area emitters: only a constant radiance is built")
                 emitter = {"radiance": _rgb(rad, [1, 1, 1]), "center": tw.transform_affine(np.zeros(3, f32)),
                            "ex": tw.transform_vector(np.array([1, 0, 0], f32)), "ey": tw.transform_vector(np.array([0, 1, 0], f32)),
-                           "kind": 0 if vt == "rectangle" else 1}      # 1: faces sampled by area (Mesh::sample_position)
+                           "kind": 0 if vt == "rectangle" else 1,      # 1: faces sampled by area (Mesh::sample_position)
+                           # src/emitters/directionalarea.cpp: emits along the surface normal only (the notebooks' field sources,
+                           # design_problem.py:46-120); seen by the particle tracer alone — `path` refuses such scenes
+                           "directional": em.get("type") == "directionalarea"}
             sid = data.add_shape(name, verts, faces, bid, emitter, normals, uvs, rectangle=vt == "rectangle")
             if vt == "rectangle":
                 data.rectangles.append((sid, tw.matrix.copy(), tw.inverse_matrix.copy()))

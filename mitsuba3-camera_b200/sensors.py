@@ -289,6 +289,9 @@ class PerspectiveCamera(Sensor):
         self.film = film
         self.near_clip, self.far_clip = float(near_clip), float(far_clip)
         self.to_world = _to_world_array(to_world)
+        # the inverse the scene description carries next to the matrix (the particle tracer's sample_direction uses it)
+        self.to_camera = (np.ascontiguousarray(to_world.inverse_matrix, f32) if hasattr(to_world, "inverse_matrix")
+                          else np.linalg.inv(self.to_world.astype(np.float64)).astype(f32))
         aspect = film.width / film.height
         fov = float(fov)
         if fov_axis == "smaller":
@@ -310,4 +313,6 @@ class PerspectiveCamera(Sensor):
 
     def set_to_world(self, to_world):
         self.to_world = _to_world_array(to_world)
+        self.to_camera = (np.ascontiguousarray(to_world.inverse_matrix, f32) if hasattr(to_world, "inverse_matrix")
+                          else np.linalg.inv(self.to_world.astype(np.float64)).astype(f32))
         capi.check(capi.lib.lrt_sensor_set_to_world(self.handle, capi.fp(self.to_world)))

@@ -35,7 +35,8 @@ struct Tri { V3 p0, p1, p2; int shape; int flags; V3 n0, n1, n2; V2 uv0, uv1, uv
 struct Bsdf { int type; bool twosided; V3 refl, eta, k, trans; float eta_s; int tex; };  // 0 diffuse 1 conductor 2 dielectric
 struct EmTri { V3 p0, e0, e1; float pmf, cdf; bool has_n; V3 n0, n1, n2; };
 // kind 0 rectangle, 1 mesh, 2 constant environment (c = bounding-sphere centre, inv_area slot unused, bs_radius)
-struct Emitter { V3 radiance; int shape; V3 c, ex, ey, n; float inv_area; int kind = 0; std::vector<EmTri> tris; float sum = 0; float bs_radius = 1; };
+struct Emitter { V3 radiance; int shape; V3 c, ex, ey, n; float inv_area; int kind = 0; std::vector<EmTri> tris; float sum = 0; float bs_radius = 1;
+                 bool directional = false; };      // directional: src/emitters/directionalarea.cpp (particle tracer only)
 struct Rect { int shape; float M[12], Minv[12]; V3 dp_du, dp_dv, n; };                  // rows of the affine 3x4 matrices
 // kind 0 bitmap (wrap: 0 repeat 1 mirror 2 clamp); procedural: 1 checkerboard, 2 checkerlines, 3 comb2d, 4 polarlines
 struct Texture { int w, h, wrap; std::vector<float> data; float to_uv[6]; int kind = 0; V3 color0 { 0, 0, 0 }, color1 { 0, 0, 0 }; float linewidth = 0, spokes = 0; };
@@ -709,6 +710,7 @@ void *orc_scene_create2(int nv, const float *verts, const float *normals, const 
             }
             e.sum = e.tris.back().cdf; e.inv_area = rcp(e.sum);
         }
+        e.directional = r[14] == 1.f;
         s->emitters.push_back(e);
     }
     size_t off = 0;

@@ -25,14 +25,44 @@ struct PtCtx {
     int max_depth, rr_depth; bool hide_emitters;
     float sample_scale; bool scalar;           // scalar variants splat with the discretised filter
     Filter flt; int cw, ch, cx, cy;
+    // perspective sensor (cam == nullptr): camera -> sample projection (sensor.h:228-265), the image rectangle at z = 1 and
+    // its normalisation (perspective.cpp:174-194), the crop resolution
+    float c2s[16]; float rect_min[2], rect_max[2]; float normalization; float res[2]; float near_clip, far_clip;
 };
+
+// the perspective sensor of the next orc_ptracer_render / orc_ptracer_sample call with cam == NULL
+static struct { float fov = 39.3077f, near_clip = 1e-2f, far_clip = 1e4f; } g_pt_persp;
+
+// PerspectiveCamera::sample_direction (src/sensors/perspective.cpp:283-321) + importance (:337-386), camera space
+static bool persp_sample_direction(const PtCtx &C, V3 ref_p, float out[11]) {
+    if (!(ref_p.z >= C.near_clip && ref_p.z <= C.far_clip)) return false;
+    const float *m = C.c2s;
+    // Transform4f * Point3f: homogeneous product, then the division by w (transform.h:118-131)
+    float x = fmadd(m[2], ref_p.z, fmadd(m[1], ref_p.y, fmadd(m[0], ref_p.x, m[3]))),
+          y = fmadd(m[6], ref_p.z, fmadd(m[5], ref_p.y, fmadd(m[4], ref_p.x, m[7]))),
+          w = fmadd(m[14], ref_p.z, fmadd(m[13], ref_p.y, fmadd(m[12], ref_p.x, m[15])));
+    float iw = rcp(w);
+    float u = x * iw, v = y * iw;
+    if (!(u >= 0.f && u <= 1.f && v >= 0.f && v <= 1.f)) return false;
+    float dist = norm(ref_p), inv_dist = rcp(dist);
+    V3 local_d = ref_p * inv_dist;
+    float ct = local_d.z, inv_ct = rcp(ct);
+    float px = local_d.x * inv_ct, py = local_d.y * inv_ct;
+    bool valid = ct > 0.f && px >= C.rect_min[0] && px <= C.rect_max[0] && py >= C.rect_min[1] && py <= C.rect_max[1];
+    float importance = valid ? C.normalization * inv_ct * inv_ct * inv_ct : 0.f;
+    out[0] = u * C.res[0]; out[1] = v * C.res[1];
+    out[2] = out[3] = out[4] = 0.f;                 // ds.p = the pinhole (camera space origin)
+    out[8] = dist; out[9] = 1.f; out[10] = importance * inv_dist * inv_dist;
+    return true;
+}
 
 // Sensor::sample_direction for the realistic lens, world space in and out
 static SensorDS sensor_sample_direction(const PtCtx &C, V3 p_world, V2 sample) {
     SensorDS ds;
     V3 ref_p = xf_point(C.to_camera, p_world);
     float o[11];
-    if (!camera_sample_direction(*C.cam, ref_p, sample, o, 0.f)) return ds;
+    if (!C.cam) { if (!persp_sample_direction(C, ref_p, o)) return ds; }
+    else if (!camera_sample_direction(*C.cam, ref_p, sample, o, 0.f)) return ds;
     ds.valid = true;
     ds.uv = { o[0], o[1] };
     ds.p = xf_point(C.to_world, V3 { o[2], o[3], o[4] });
@@ -119,6 +149,12 @@ static void sample_visible_emitters(const PtCtx &C, PCG32 &rng, double *block) {
         index = (int) std::min((uint32_t) scaled, (uint32_t) count - 1u); idx_weight = cf;
     }
     const Emitter &e = s.emitters[index];
+    if (e.directional) {
+        // EmitterFlags::Delta (ptracer.cpp:111): the emitter is not connected, and the MASKED draws of the function — position
+        // sample, wavelength sample — do not advance the generator; the sensor's 2D sample (unmasked, :155) does
+        (void) rng.next_float32(); (void) rng.next_float32();
+        return;
+    }
     PtVertex v; V3 emitter_weight { 0, 0, 0 };
     V2 s2; s2.x = rng.next_float32(); s2.y = rng.next_float32();
     if (e.kind == 2) {
@@ -167,6 +203,11 @@ static bool prepare_ray(const PtCtx &C, PCG32 &rng, Ray &ray, V3 &throughput) {
         ray.o = orig; ray.d = f.to_world(v1); ray.maxt = Largest;
         float area = 4.f * Pi * sqr(e.bs_radius);
         throughput = e.radiance * (area * Pi);
+    } else if (e.directional) {
+        // DirectionalArea::sample_ray (directionalarea.cpp:86-110): a point on the shape, direction = its normal, weight = area * radiance
+        PtVertex v; float w; emitter_sample_position(e, sample2, v.p, v.n, w);
+        throughput = e.radiance * w;
+        ray = spawn_ray(v.p, v.n, v.n);
     } else {
         PtVertex v; float w; emitter_sample_position(e, sample2, v.p, v.n, w);
         frame_from_normal(v, v.n);
@@ -288,9 +329,52 @@ static void pt_setup(PtCtx &C, void *scene_h, void *cam_h, const float *to_world
     C.shutter_open_time = shutter_open_time; C.max_depth = max_depth; C.rr_depth = rr_depth; C.hide_emitters = hide_emitters != 0;
     C.flt.init(filter, filter_param); C.cw = cw; C.ch = ch; C.cx = cx; C.cy = cy;
 }
+// the perspective sensor's projection data (cam == nullptr): camera -> sample matrix of sensor.h:228-265 composed in double and
+// rounded once, image rectangle and normalisation of perspective.cpp:186-194
+static void pt_setup_persp(PtCtx &C, int w, int h) {
+    if (C.cam) return;
+    C.near_clip = g_pt_persp.near_clip; C.far_clip = g_pt_persp.far_clip;
+    const double W = w, H = h, aspect = W / H, relx = C.cw / W, rely = C.ch / H, offx = C.cx / W, offy = C.cy / H;
+    const double n_ = C.near_clip, f_ = C.far_clip, recip = 1.0 / (f_ - n_), cot = 1.0 / std::tan(0.5 * (double) g_pt_persp.fov * 3.14159265358979323846 / 180.0);
+    auto mul = [](const double a[16], const double b[16], double out[16]) {
+        for (int i = 0; i < 4; ++i) for (int j = 0; j < 4; ++j) { double v = 0; for (int k = 0; k < 4; ++k) v += a[4 * i + k] * b[4 * k + j]; out[4 * i + j] = v; }
+    };
+    const double P[16] = { cot, 0, 0, 0, 0, cot, 0, 0, 0, 0, f_ * recip, -n_ * f_ * recip, 0, 0, 1, 0 };
+    const double T2[16] = { 1, 0, 0, -1, 0, 1, 0, -1.0 / aspect, 0, 0, 1, 0, 0, 0, 0, 1 };
+    const double S2[16] = { -0.5, 0, 0, 0, 0, -0.5 * aspect, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1 };
+    const double T1[16] = { 1, 0, 0, -offx, 0, 1, 0, -offy, 0, 0, 1, 0, 0, 0, 0, 1 };
+    const double S1[16] = { 1.0 / relx, 0, 0, 0, 0, 1.0 / rely, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1 };
+    double a[16], b[16], c[16], m[16];
+    mul(T2, P, a); mul(S2, a, b); mul(T1, b, c); mul(S1, c, m);
+    for (int i = 0; i < 16; ++i) C.c2s[i] = (float) m[i];
+    // image rectangle at z = 1: sample_to_camera * (0,0,0) and (1,1,0), divided by their z (the near plane)
+    Persp Pp; Pp.near_clip = C.near_clip; Pp.far_clip = C.far_clip; persp_setup(Pp, g_pt_persp.fov, w, h, C.cw, C.ch, C.cx, C.cy);
+    const float x0 = Pp.s2c[3] / Pp.s2c[11], y0 = Pp.s2c[7] / Pp.s2c[11];
+    const float x1 = (Pp.s2c[0] + Pp.s2c[3]) / Pp.s2c[11], y1 = (Pp.s2c[5] + Pp.s2c[7]) / Pp.s2c[11];
+    C.rect_min[0] = std::min(x0, x1); C.rect_max[0] = std::max(x0, x1); C.rect_min[1] = std::min(y0, y1); C.rect_max[1] = std::max(y0, y1);
+    C.normalization = 1.f / ((C.rect_max[0] - C.rect_min[0]) * (C.rect_max[1] - C.rect_min[1]));
+    C.res[0] = (float) C.cw; C.res[1] = (float) C.ch;
+}
 }  // namespace orc
 
 extern "C" {
+// the perspective sensor (x fov in degrees, clip planes) used by the next particle-tracer calls that pass cam_h == NULL
+void orc_ptracer_perspective(float fov, float near_clip, float far_clip) { orc::g_pt_persp.fov = fov; orc::g_pt_persp.near_clip = near_clip; orc::g_pt_persp.far_clip = far_clip; }
+// PerspectiveCamera::sample_direction for n WORLD-space points: out11 = uv[2], p[3] (world), d[3], dist, pdf, weight
+void orc_persp_sample_direction(float fov, float near_clip, float far_clip, const float *to_world16, int w, int h, int n, const float *p3, float *out11) {
+    using namespace orc;
+    g_pt_persp.fov = fov; g_pt_persp.near_clip = near_clip; g_pt_persp.far_clip = far_clip;
+    PtCtx C; pt_setup(C, nullptr, nullptr, to_world16, nullptr, 1, 0.f, 4, 5, 0, 0.f, w, h, 0, 0);
+    pt_setup_persp(C, w, h);
+    for (int i = 0; i < n; ++i) {
+        SensorDS ds = sensor_sample_direction(C, V3 { p3[3 * i], p3[3 * i + 1], p3[3 * i + 2] }, V2 { .5f, .5f });
+        float *o = out11 + 11 * i;
+        for (int k = 0; k < 11; ++k) o[k] = 0.f;
+        if (!ds.valid) continue;
+        o[0] = ds.uv.x; o[1] = ds.uv.y; o[2] = ds.p.x; o[3] = ds.p.y; o[4] = ds.p.z; o[5] = ds.d.x; o[6] = ds.d.y; o[7] = ds.d.z;
+        o[8] = ds.dist; o[9] = ds.pdf; o[10] = ds.weight;
+    }
+}
 // n_samples consecutive ParticleTracerIntegrator::sample calls drawn from ONE scalar sampler stream seeded with `seed`
 // (sampler.cpp:131), sample_scale 1, into storage64 [ch, cw, 4] — the unit the reference exposes to Python as integrator.sample()
 void orc_ptracer_sample(void *scene_h, void *cam_h, const float *to_world16, const float *to_camera16, int w, int h, int filter, float filter_param, uint32_t seed,
@@ -304,6 +388,7 @@ void orc_ptracer_render(void *scene_h, void *cam_h, const float *to_world16, con
                         float filter_param, uint32_t base_seed, uint32_t seed, int spp, int max_depth, int rr_depth, int hide_emitters,
                         float shutter_open_time, int scalar, int n_threads, double *storage64) {
     PtCtx C; pt_setup(C, scene_h, cam_h, to_world16, to_camera16, filter, filter_param, max_depth, rr_depth, hide_emitters, shutter_open_time, cw, ch, cx, cy);
+    pt_setup_persp(C, w, h);
     C.sample_scale = (float) (cw * ch) / (float) ((uint32_t) spp * (uint32_t) (w * h));
     C.scalar = scalar != 0;
     size_t total = (size_t) w * h * spp, npix = (size_t) cw * ch;
@@ -341,6 +426,7 @@ void orc_ptracer_render(void *scene_h, void *cam_h, const float *to_world16, con
 void orc_ptracer_sample(void *scene_h, void *cam_h, const float *to_world16, const float *to_camera16, int w, int h, int filter, float filter_param, uint32_t seed,
                         int n_samples, int max_depth, int rr_depth, int hide_emitters, float shutter_open_time, double *storage64) {
     PtCtx C; pt_setup(C, scene_h, cam_h, to_world16, to_camera16, filter, filter_param, max_depth, rr_depth, hide_emitters, shutter_open_time, w, h, 0, 0);
+    pt_setup_persp(C, w, h);
     C.sample_scale = 1.f; C.scalar = true;
     PCG32 rng; rng.seed((uint64_t) seed, 0xda3e39cb94b95bdbULL);
     for (int i = 0; i < n_samples; ++i) {

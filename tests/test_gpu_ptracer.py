@@ -135,11 +135,16 @@ def test_gpu_ptracer_queue_kernel_equals_per_thread_kernel(mi):
 
 
 @pytest.mark.gpu
-def test_gpu_ptracer_errors(mi):
+def test_gpu_ptracer_through_a_perspective_sensor(mi):
+    """the particle tracer connects to a pinhole as well (PerspectiveCamera::sample_direction, perspective.cpp:283-386): the room
+    scene (spheres, mirror, glass) through its own perspective sensor, default mode against the pinned oracle"""
     d = mi.xml_to_dict(path=os.path.join(XML, "room.xml"), integrator="ptracer")
     sc = mi.load_dict(d)
-    with pytest.raises(mi.capi.LensrtError, match="realistic lens"):
-        mi.render(sc)
+    img = mi.render(sc, seed=2).cpu().numpy()
+    want = oracle_ptracer(mi, d, 2, 8, scalar=False)
+    err = rel_rmse(img, want)
+    print(f"room.xml, perspective sensor, ptracer: rel-RMSE vs oracle {err:.3e}, mean {img.mean():.5f}")
+    assert np.isfinite(img).all() and img.mean() > 0 and err <= 2e-3
 
 
 @pytest.mark.gpu
@@ -182,3 +187,35 @@ def test_gpu_ptracer_lens_adjoint_equals_spot_adjoint_for_a_point_like_emitter(m
     assert np.abs(b).max() > 0 and len(rows) == 11
     assert cos >= 0.999
     assert np.abs(a - b).max() <= 0.03 * np.abs(b).max()
+
+
+# ------------------------------------------------------------------------------------------------ the notebooks' "Path B"
+@pytest.mark.gpu
+def test_gpu_path_b_mesh_lens_directional_source_perspective_sensor(mi):
+    """The notebooks' own pipeline in miniature (tests/ref_scenes.py path_b_scene; design_problem.py:46-120,355-428): a MESH lens
+    (dielectric caps with smooth normals), a `directionalarea` field source, a diffuse film plane, a PERSPECTIVE sensor looking
+    at it, the particle tracer. Default mode against the pinned oracle (same seed); the scalar convention against the
+    reference's own renders of the same scene dictionary."""
+    import ref_scenes as rs
+    R = np.load(os.path.join(ROOT, "tests", "golden", "ref_pathb.npz"))
+    d = rs.path_b_scene(lambda m: mi.Transform4f(m))
+    sc = mi.load_dict(d)
+    assert isinstance(sc.integrator(), mi.PTracerIntegrator) and isinstance(sc.sensors()[0], mi.PerspectiveCamera)
+    img = mi.render(sc, seed=5).cpu().numpy()
+    want = oracle_ptracer(mi, d, 5, 8, scalar=False)
+    err = rel_rmse(img, want)
+    st = sc.stats()
+    print(f"path B, default mode: rel-RMSE vs oracle {err:.3e}; light paths {st['samples']}, connections {st['lens_misses']}, rays {st['rays']}")
+    assert err <= 2e-3 and abs(img.mean() / want.mean() - 1) <= 2e-3
+    for seed in (0, 3):
+        img = sc.integrator().render(sc, seed=seed, rng_mode=1, n_threads=int(R["n_threads"])).cpu().numpy()
+        ref = R[f"image_seed{seed}"]
+        close = np.abs(img - ref).max(-1) <= 1e-4 * np.maximum(ref.max(-1), 1e-3)
+        print(f"path B, scalar convention, seed {seed}: rel-RMSE vs the reference's image {rel_rmse(img, ref):.3e}, pixels within 1e-4: {close.mean():.4f}")
+        assert close.mean() >= 0.95 and abs(img.mean() / ref.mean() - 1) <= 1e-2
+    # `directionalarea` emitters exist for the particle tracer only
+    d2 = dict(d); d2["integrator"] = {"type": "path", "max_depth": 4}
+    with pytest.raises(mi.capi.LensrtError, match="particle tracer"):
+        mi.render(mi.load_dict(d2), spp=1)
+    with pytest.raises(ValueError, match="realistic lens"):
+        sc.integrator().render_backward_lens(sc, np.zeros((64, 64, 3), f32))

@@ -29,12 +29,23 @@ def P():
 def oracle_ptracer(mi, d, seed, n_threads, scalar=True, spp=None):
     data, sds, integ = mi.scene_data_from_dict(d)
     sd = sds[0]; fd = sd["film"]
-    assert sd["type"] == "realisticlens" and integ["type"] == "ptracer"
+    assert sd["type"] in ("realisticlens", "perspective") and integ["type"] == "ptracer"
     film = FilmSpec(fd["width"], fd["height"], None, fd.get("diagonal", 35.0))
     tw = sd["to_world"].matrix
-    od = sd.get("object_distance", 6.0)
-    cam = orc_camera(ld.design(sd.get("lens_design", "singlet"), {"object_distance": od}), film, to_world=tw, near=sd.get("near_clip", 1e-2),
-                     far=sd.get("far_clip", 1e4), object_distance=od)
+    if sd["type"] == "perspective":        # the pinhole: no oracle camera, the projection comes from (x fov, clip planes)
+        cam = None
+        aspect = fd["width"] / fd["height"]; fov = float(sd.get("fov", 45.0)); axis = sd.get("fov_axis", "x")
+        if axis == "smaller":
+            axis = "y" if aspect > 1 else "x"
+        elif axis == "larger":
+            axis = "x" if aspect > 1 else "y"
+        if axis == "y":
+            fov = np.degrees(2.0 * np.arctan(np.tan(0.5 * np.radians(fov)) * aspect))
+        oracle().orc_ptracer_perspective(c_f(fov), c_f(sd.get("near_clip", 1e-2)), c_f(sd.get("far_clip", 1e4)))
+    else:
+        od = sd.get("object_distance", 6.0)
+        cam = orc_camera(ld.design(sd.get("lens_design", "singlet"), {"object_distance": od}), film, to_world=tw, near=sd.get("near_clip", 1e-2),
+                         far=sd.get("far_clip", 1e4), object_distance=od)
     sot = sd.get("shutter_close", sd.get("shutter_open", 0.0)) - sd.get("shutter_open", 0.0)
     h = orc_scene(data.arrays(), analytic_rectangles=True)
     rf = fd.get("rfilter", {"type": "gaussian"})
@@ -61,3 +72,20 @@ def test_ptracer_oracle_other_seed(mi, P):
     d = mi.xml_to_dict(path=os.path.join(XML, "lens_room.xml"))
     img = oracle_ptracer(mi, d, 3, int(P["n_threads"]))
     assert rel_rmse(img, P[case_key("lens_room", {}, "image_seed3")]) <= 2e-4
+
+
+# ------------------------------------------------------------------------------------------------ the notebooks' "Path B"
+def test_path_b_oracle_vs_reference_images(mi):
+    """mesh lens + `directionalarea` field source + diffuse film plane + perspective sensor + ptracer (tests/ref_scenes.py
+    path_b_scene): the oracle's particle tracer — PerspectiveCamera::sample_direction, DirectionalArea::sample_ray — in the
+    scalar convention against the reference's own renders of the same scene dictionary (tests/golden/gen_ref_pathb.py)."""
+    import ref_scenes as rs
+    R = np.load(os.path.join(HERE, "golden", "ref_pathb.npz"))
+    d = rs.path_b_scene(lambda m: mi.Transform4f(m))
+    for seed in (0, 3):
+        img = oracle_ptracer(mi, d, seed, int(R["n_threads"]))
+        ref = R[f"image_seed{seed}"]
+        err = rel_rmse(img, ref)
+        close = np.abs(img - ref).max(-1) <= 1e-4 * np.maximum(ref.max(-1), 1e-3)
+        print(f"path B seed {seed}: rel-RMSE {err:.3e}, pixels within 1e-4: {close.mean():.4f}, mean {img.mean():.5f} / {ref.mean():.5f}")
+        assert err <= 2e-3 and close.mean() >= 0.97
