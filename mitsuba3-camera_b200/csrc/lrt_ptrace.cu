@@ -415,14 +415,16 @@ __global__ void __launch_bounds__(128) k_ptrace(PtArgs A) {
 }
 
 // ---------------------------------------------------------------------------------------------------------------------------
-// The fast forward kernel (default sampler convention): the same light paths with the render megakernel's
-// execution scheme (lrt_render.cu) instead of one thread per path run to completion. Persistent warps; every lane carries one
-// light path as a small state machine — phase 1: a path segment (closest hit), phase 2: the shadow ray of a connection — and
-// all lanes advance together through ONE traversal site in warp-uniform bursts (bvh_burst). A burst ends when 26/32 of its
-// lanes are done; those lanes then do their shading step (connection set-up through the lens, BSDF sample, next ray) and a lane
-// whose path has ended takes the next sample index of the warp's chunk at once, so traversal runs near full width although
-// the paths differ in length by orders of magnitude (profiles/r02w_ptrace_lines.txt: 5.4 lanes in the per-thread kernel).
-// Every lane draws its samples in the reference's order: the image equals k_ptrace<false>'s up to the order of the atomics.
+// The default kernel (per-sample streams; forward renders and, kAdj, the lens adjoint): the same light paths with the render
+// megakernel's execution scheme (lrt_render.cu) instead of one thread per path run to completion. Persistent warps; every lane
+// carries one light path as a small state machine — phase 1: a path segment (closest hit), phase 2: the shadow ray of a
+// connection — and all lanes advance together through ONE traversal site in warp-uniform bursts (bvh_burst; by default a burst
+// runs until all its lanes are done: LRT_PT_EXIT_DROP = 32 measured best, the shading step below being the expensive part).
+// Lanes whose ray is finished do their shading step — ONE site for the sensor's direction sample (a strict lens trace, half of
+// all instructions) shared by the emitter vertices of new paths and the scene vertices of running ones, then the connection's
+// shadow ray or the BSDF sample — and a lane whose path has ended takes the next sample index of the warp's chunk at once
+// (profiles/r02w_ptrace_lines.txt: 5.4 lanes of traversal in the per-thread kernel; r02z_ptrace_queue_lines.txt: this one).
+// Every lane draws its samples in the reference's order: the image equals k_ptrace's up to the order of the atomics.
 constexpr int kPtChunk = 64;          // sample indices handed to a warp per fetch
 
 template <bool kAdj>
@@ -692,7 +694,7 @@ static int ptrace_launch(const lrt_scene *sc, const lrt_sensor *sensor_, const l
     LRT_CUDA(cudaMemsetAsync(A.stats, 0, 8 * sizeof(unsigned long long), stream));
     int dev = 0, sms = 148; cudaGetDevice(&dev); cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     long long grid = (work_items + 127) / 128; grid = std::max<long long>(1, std::min<long long>(grid, (long long) sms * 16));
-    // forward renders of triangle scenes in the default convention take the queue kernel (LRT_PTRACE_SIMPLE=1: the per-thread one)
+    // the default convention takes the queue kernel (LRT_PTRACE_SIMPLE=1: the per-thread one); the scalar parity mode the per-thread one
     static const bool simple = getenv("LRT_PTRACE_SIMPLE") != nullptr && atoi(getenv("LRT_PTRACE_SIMPLE")) != 0;
     if (A.scalar || simple) {
         if (grad_accum_dev) k_ptrace<true><<<(int) grid, 128, 0, stream>>>(A);
