@@ -245,6 +245,22 @@ def widened_rows_section(mi, torch, a, scene):
                          "Grays_per_s_rgb": m / ms_rgb / 1e6,
                          "what": "lrt_sensor_sample_ray_wl on the `%s` lens (per-ray Cauchy / Sellmeier IOR of both media of each of its "
                                  "interfaces) beside lrt_sensor_sample_ray (constant IORs)" % a.lens}
+    # the notebooks' "Path B" (tests/ref_scenes.py path_b_scene): mesh lens + directionalarea source + film plane + perspective sensor
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import ref_scenes as rs
+    res, spp = 256, 64
+    sc = mi.load_dict(rs.path_b_scene(lambda m: mi.Transform4f(m), spp=spp, res=res))
+    it = sc.integrator()
+    seeds = iter(range(1000))
+    ms_pb = timed(lambda: it.render(sc, seed=next(seeds)))
+    out["path_b"] = {"light_paths": res * res * spp, "ms_per_render": ms_pb, "M_light_paths_per_s": res * res * spp / ms_pb / 1e3,
+                     "what": "ptracer on the notebooks' pipeline in miniature: meshed singlet (dielectric caps), directionalarea field source, "
+                             "diffuse film plane, perspective sensor; %d x %d film, %d spp" % (res, res, spp)}
+    if not a.no_cpu_baseline:
+        pr = reference_sample(a, extra=("--workload", "pathb", "--width", str(res), "--spp", str(spp)))
+        if pr is not None:
+            out["path_b"]["cpu_baseline"] = {"value": pr[0]["value"], "unit": "M light paths/s", "cores": pr[0]["cores"], "kind": "reference",
+                                             "sample": "the reference's scalar_rgb ptracer on the same scene dictionary, same film and spp"}
     return out
 
 

@@ -88,11 +88,15 @@ def main():
         elif a.workload == "c1":
             d = mi.cornell_box(); d["integrator"]["max_depth"] = a.max_depth
             d["sensor"]["film"]["width"] = a.width; d["sensor"]["film"]["height"] = a.height
+        elif a.workload == "pathb":      # the notebooks' pipeline in miniature (tests/ref_scenes.py path_b_scene): ptracer, perspective sensor
+            rs = load_by_path("ref_scenes", os.path.join(ROOT, "tests", "ref_scenes.py"))
+            d = rs.path_b_scene(lambda m: mi.ScalarTransform4f(np.asarray(m, np.float32)), spp=a.spp, res=a.width)
+            a.height = a.width
         else:
             raise SystemExit("unknown workload " + a.workload)
-        if a.integrator != "path":
+        if a.integrator != "path" and a.workload != "pathb":
             d["integrator"]["type"] = a.integrator
-        if a.crop:
+        if a.crop and a.workload != "pathb":
             d["sensor"]["film"].update(crop_width=a.crop[0], crop_height=a.crop[1], crop_offset_x=a.crop[2], crop_offset_y=a.crop[3])
         t0 = time.perf_counter()
         scene = mi.load_dict(to_reference(d, tmp) if a.workload in ("c5", "c4") else d)
