@@ -366,6 +366,27 @@ class _LazyOp:
 _RefractiveTrace = _LazyOp()
 
 
+def splat_tent(points, weights, res, pitch, centre):
+    """The film-plane spot IMAGE of landing points (what the notebooks' perspective sensors see on their diffuse film plane, up
+    to a constant): `points` [n,2] (metres, film plane), `weights` [n] -> image [res,res,3] of pixels of size `pitch` centred on
+    `centre`, splatted with the tent filter (radius 1: ImageBlock::put, src/render/imageblock.cpp:264-379, continuous weights,
+    footprint normalised to 1 like the particle tracer's film). Plain torch: differentiable in the points (the derivative of the
+    filter weights is the splat-position adjoint the notebooks' AD propagates) and in the weights."""
+    import torch
+    pos = (points - torch.as_tensor(centre, dtype=points.dtype, device=points.device)) / pitch + 0.5 * res      # pixel coordinates
+    base = torch.floor(pos - 0.5)                                   # the 2 x 2 pixel centres within the tent's radius
+    img = torch.zeros((res * res,), dtype=points.dtype, device=points.device)
+    fx = pos[:, 0] - (base[:, 0] + 0.5); fy = pos[:, 1] - (base[:, 1] + 0.5)        # in [0, 1): distance to the lower centre
+    for dy in (0, 1):
+        wy = (1.0 - fy) if dy == 0 else fy
+        for dx in (0, 1):
+            wx = (1.0 - fx) if dx == 0 else fx
+            ix = base[:, 0].long() + dx; iy = base[:, 1].long() + dy
+            ok = (ix >= 0) & (ix < res) & (iy >= 0) & (iy < res)
+            img = img.index_add(0, (iy * res + ix)[ok], (weights * wx * wy)[ok])
+    return img.reshape(res, res, 1).expand(res, res, 3)
+
+
 class MeshDesignProblem:
     """The notebooks' design loop on the MESH representation of the lens (design_problem.py:355-584 over lens.py's mesh lenses):
     per field a bundle of PARALLEL rays filling the front element — what the notebooks' `directionalarea` disk field sources
@@ -374,9 +395,16 @@ class MeshDesignProblem:
     (detached) centroid, mm^2 (rms_loss, losses.py:8-28, on the landing points instead of a splatted image); Adam over table
     entries. One step = sag -> vertices -> vertex normals -> BVH refit -> trace -> loss -> adjoint kernel -> torch chain."""
 
-    def __init__(self, mi, rows0, field_angles, subdiv=5, rays=1 << 16, free=None, lr=3e-5, seed=0, fill=0.95):
+    def __init__(self, mi, rows0, field_angles, subdiv=5, rays=1 << 16, free=None, lr=3e-5, seed=0, fill=0.95, loss="geometric",
+                 resolution=64, pitch=None):
+        """loss="geometric": rms radius of the landing points. loss="image": the notebooks' loss itself — rms_loss
+        (losses.py:8-28) of the spot IMAGE, the landing points splatted with the tent filter into `resolution`^2 pixels of size
+        `pitch` (default: 1/400 of the front semi-diameter; it should resolve the spot) centred on each field's initial centroid; mm^2 either way."""
         import torch
-        self.torch = torch
+        self.torch, self.mi = torch, mi
+        self.loss_kind, self.resolution = loss, int(resolution)
+        self.pitch = float(pitch) if pitch else float(np.asarray(rows0, f32)[-1, 2]) / 400.0
+        self._centres = None
         self.rows0 = np.ascontiguousarray(rows0, f32).copy()
         self.lens = MeshLens(mi, self.rows0, subdiv=subdiv)
         n = len(self.rows0)
@@ -420,10 +448,29 @@ class MeshDesignProblem:
         # one trace_ad per field; each keeps its own autograd node, and every node replays the SAME scene state (the table
         # does not move inside an iteration), so backward() through all of them is consistent
         total = 0.0
-        for pf, alive in self.spots(rows):
+        spots = self.spots(rows)
+        if self.loss_kind == "image":
+            from .lens_design import rms_loss
+            if self._centres is None:        # the windows stay where the first iteration's spots are (the notebooks' sensors do not move)
+                self._centres = [pf[alive].detach().double().mean(0) for pf, alive in spots]
+            for (pf, alive), c in zip(spots, self._centres):
+                img = splat_tent(pf[alive].double(), self.torch.ones(int(alive.sum()), dtype=self.torch.float64, device=pf.device),
+                                 self.resolution, self.pitch, c)
+                total = total + rms_loss(img) * (self.pitch * 1e3) ** 2
+            return total
+        for pf, alive in spots:
             q = pf[alive].double() * 1e3                     # mm
             total = total + ((q - q.mean(0).detach()) ** 2).sum(1).mean()
         return total
+
+    def images(self):
+        """the spot images of the current table (loss="image" windows), [fields, res, res, 3]"""
+        torch = self.torch
+        with torch.no_grad():
+            spots = self.spots(self.rows())
+            cs = self._centres or [pf[alive].double().mean(0) for pf, alive in spots]
+            return torch.stack([splat_tent(pf[alive].double(), torch.ones(int(alive.sum()), dtype=torch.float64, device=pf.device),
+                                           self.resolution, self.pitch, c) for (pf, alive), c in zip(spots, cs)])
 
     def step(self):
         self.opt.zero_grad(set_to_none=True)

@@ -315,3 +315,30 @@ def test_trace_adjoint_limits(mi):
     assert (got[1] == 0).all()                                                # absorbed by the baffle
     assert np.isfinite(got).all() and np.abs(got[2:]).max() > 0
     assert float(g_V.abs().max()) > 0
+
+
+def test_mesh_design_loop_with_the_notebooks_image_loss(mi):
+    """loss="image": the landing points splatted with the tent filter into a spot image (what the notebooks' perspective sensors
+    see on the film plane) and rms_loss of that image (losses.py:8-28) — differentiable through the filter weights, the
+    splat-position adjoint the notebooks' AD propagates. Interpolating onto pixel centres preserves the centroid and adds
+    f (1 - f) px^2 per axis to the second moment (1/6 on average): the image loss is the geometric one plus pitch^2 / 3. The loop
+    brings the perturbed doublet back with this loss as well."""
+    import torch
+    rows = doublet_rows(mi)
+    bad = rows.copy(); bad[0, 3] *= 1.06
+    free = [(i, 3) for i in range(3)]
+    geo = mi.mesh_lens.MeshDesignProblem(mi, bad, [0.0, 2.5], subdiv=5, rays=1 << 14, lr=1e-4, free=free)
+    prob = mi.mesh_lens.MeshDesignProblem(mi, bad, [0.0, 2.5], subdiv=5, rays=1 << 14, lr=1e-4, free=free, loss="image", resolution=96, pitch=1.5e-5)
+    lg = float(geo.loss(geo.rows()).detach()); li = float(prob.loss(prob.rows()).detach())
+    want = lg + 2 * (prob.pitch * 1e3) ** 2 / 3.0            # two fields
+    print(f"geometric loss {lg:.5e} mm^2, image loss {li:.5e} mm^2 (geometric + pitch^2/3 per field: {want:.5e})")
+    assert abs(li - want) <= 0.03 * want
+    imgs = prob.images()
+    assert imgs.shape == (2, 96, 96, 3) and float(imgs[0, ..., 0].sum()) > 0.99 * (1 << 14) * 0.9       # the window holds the spot
+    g_geo = torch.autograd.grad(geo.loss(geo.rows()), geo.theta)[0]; g_img = torch.autograd.grad(prob.loss(prob.rows()), prob.theta)[0]
+    cos = float((g_geo * g_img).sum() / (g_geo.norm() * g_img.norm()))
+    print("gradient cosine image vs geometric", cos)
+    assert cos > 0.99
+    losses = [prob.step() for _ in range(60)]
+    print("image loss", losses[0], "->", losses[-1])
+    assert np.isfinite(losses).all() and np.mean(losses[-10:]) - 2 * (prob.pitch * 1e3) ** 2 / 3.0 < 0.3 * (losses[0] - 2 * (prob.pitch * 1e3) ** 2 / 3.0)
