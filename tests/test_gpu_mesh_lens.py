@@ -342,3 +342,39 @@ def test_mesh_design_loop_with_the_notebooks_image_loss(mi):
     losses = [prob.step() for _ in range(60)]
     print("image loss", losses[0], "->", losses[-1])
     assert np.isfinite(losses).all() and np.mean(losses[-10:]) - 2 * (prob.pitch * 1e3) ** 2 / 3.0 < 0.3 * (losses[0] - 2 * (prob.pitch * 1e3) ** 2 / 3.0)
+
+
+def test_mesh_lens_spot_image_agrees_with_the_particle_tracer_on_path_b(mi):
+    """Two independent routes to the same picture: (1) the particle tracer on the notebooks' pipeline (path_b_scene: emitter rays of
+    the `directionalarea` source -> dielectric BSDF sampling on the meshed caps -> diffuse film plane -> perspective sensor,
+    pinned to the reference's render), (2) MeshLens: the same parallel bundle through lrt_scene_trace_refractive, the landing
+    points splatted (splat_tent, Fresnel weights) at the sensor's pixel pitch on the film plane. Different samples, different
+    kernels: the normalised images agree to the Monte Carlo noise."""
+    import torch
+    import ref_scenes as rs
+    res, spp = 64, 256
+    d = rs.path_b_scene(lambda m: mi.Transform4f(m), spp=spp, res=res)
+    img_p = mi.render(mi.load_dict(d), seed=1).cpu().numpy()[..., 0].astype(np.float64)
+    rows = mi.lens_design.asphere_table([30.0, -45.0], [4.0, 52.0], [8, 8], [1.5168, 1.000277]).astype(f32)       # the caps of the assets
+    lens = mi.mesh_lens.MeshLens(mi, rows, subdiv=3)
+    M = d["field_source"]["to_world"].matrix.astype(np.float64)
+    g = torch.Generator(device="cuda").manual_seed(3)
+    n = res * res * spp
+    uv = (2.0 * torch.rand((n, 2), device="cuda", generator=g, dtype=torch.float64) - 1.0)
+    Mt = torch.tensor(M, device="cuda")
+    o = (Mt[:3, 3][None] + uv[:, :1] * Mt[:3, 0][None] + uv[:, 1:] * Mt[:3, 1][None]).float()
+    nrm = torch.nn.functional.normalize(Mt[:3, 2], dim=0).float()
+    po, pd, alive, w = lens.trace(o, nrm.expand(n, 3).contiguous())
+    t = -po[:, 2] / pd[:, 2]
+    pf = (po + t[:, None] * pd)[:, :2].double()
+    pitch = 2.0 * 0.03 * np.tan(np.radians(15.0)) / res
+    pts = torch.stack([pf[:, 0], -pf[:, 1]], 1)[alive]                     # image column ~ +x, row ~ -y (the sensor looks down -z, up = +y)
+    img_s = mi.mesh_lens.splat_tent(pts, w[alive].double(), res, pitch, [0.0, 0.0])[..., 0].cpu().numpy()
+    a, b = img_p / img_p.sum(), img_s / img_s.sum()
+    lit = (a + b) > 0.2 * max(a.max(), b.max())
+    err = np.sqrt(((a - b)[lit] ** 2).mean()) / a[lit].mean()
+    corr = np.corrcoef(a.ravel(), b.ravel())[0, 1]
+    yy, xx = np.mgrid[0:res, 0:res]
+    ca, cb = np.array([(a * xx).sum(), (a * yy).sum()]), np.array([(b * xx).sum(), (b * yy).sum()])
+    print(f"path B vs mesh-lens spot image: rel-RMSE over lit pixels {err:.3e}, correlation {corr:.5f}, centroids {ca} / {cb} px")
+    assert corr > 0.995 and err < 0.06 and np.abs(ca - cb).max() < 0.05
