@@ -18,7 +18,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 XML = os.path.join(HERE, "assets", "xml")
 CASES = [("lens_room", {}), ("lens_room", {"max_depth": "2", "lens": "gauss"}), ("lens_room", {"max_depth": "-1", "spp": "4"}),
          ("charts", {"integrator": "ptracer"}), ("charts", {"integrator": "ptracer", "hide": "true", "spp": "4"}),
-         ("lens_studio", {})]
+         ("lens_studio", {}),
+         ("room", {"integrator": "ptracer"})]          # (its own PERSPECTIVE sensor: PerspectiveCamera::sample_direction)
 
 
 def tag(kw):

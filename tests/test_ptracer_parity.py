@@ -14,7 +14,8 @@ ld = load_lens_designs()
 HERE = os.path.dirname(os.path.abspath(__file__))
 XML = os.path.join(HERE, "golden", "assets", "xml")
 CASES = [("lens_room", {}), ("lens_room", {"max_depth": "2", "lens": "gauss"}), ("lens_room", {"max_depth": "-1", "spp": "4"}),
-         ("charts", {"integrator": "ptracer"}), ("charts", {"integrator": "ptracer", "hide": "true", "spp": "4"}), ("lens_studio", {})]
+         ("charts", {"integrator": "ptracer"}), ("charts", {"integrator": "ptracer", "hide": "true", "spp": "4"}), ("lens_studio", {}),
+         ("room", {"integrator": "ptracer"})]          # (its own PERSPECTIVE sensor: PerspectiveCamera::sample_direction)
 
 
 def case_key(name, kw, what="image"):
