@@ -208,7 +208,12 @@ LRT_D int pick_emitter(const SceneView &sc, float &sample, float &weight) {
 LRT_D void emitter_sample_position(const SceneView &sc, const float4 *ep, float sx, float sy, float3 &p, float3 &n, float &weight) {
     const float4 e1 = __ldg(ep + 1), e4 = __ldg(ep + 4);
     if (e4.w == 1.f) mesh_emitter_sample_position(sc, e1, sx, sy, p, n);
-    else {
+    else if (e4.w == 3.f) {      // Disk::sample_position (disk.cpp:173-190): concentric disk warp, then to_world
+        const float4 e2 = __ldg(ep + 2), e3 = __ldg(ep + 3);
+        float qx, qy; square_to_disk_concentric(sx, sy, qx, qy);
+        p = make_float3(e1.x, e1.y, e1.z) + make_float3(e2.x, e2.y, e2.z) * qx + make_float3(e3.x, e3.y, e3.z) * qy;
+        n = make_float3(e4.x, e4.y, e4.z);
+    } else {
         const float4 e2 = __ldg(ep + 2), e3 = __ldg(ep + 3);
         const float ux = sx * 2.f - 1.f, uy = sy * 2.f - 1.f;
         p = make_float3(e1.x, e1.y, e1.z) + make_float3(e2.x, e2.y, e2.z) * ux + make_float3(e3.x, e3.y, e3.z) * uy;

@@ -45,12 +45,14 @@ int lrt_scene_create(const lrt_scene_desc *d, lrt_scene **out) {
     LRT_REQUIRE(d->n_spheres >= 0 && (d->n_spheres == 0 || d->spheres), "bad sphere table");
     for (int k = 0; k < d->n_spheres; ++k) {
         const float *q = d->spheres + 32 * (size_t) k;
-        LRT_REQUIRE(q[3] > 0.f && q[4] >= 0.f && q[4] < (float) d->n_shapes && q[4] == (float) (int) q[4], "bad sphere (radius / shape id)");
+        LRT_REQUIRE((q[6] == 1.f || q[3] > 0.f) && q[4] >= 0.f && q[4] < (float) d->n_shapes && q[4] == (float) (int) q[4], "bad sphere (radius / shape id)");
+        LRT_REQUIRE(q[6] == 0.f || (q[6] == 1.f && (q[0] != 0.f || q[1] != 0.f || q[2] != 0.f)), "bad disk (kind / frame normal)");
     }
     int env = -1;
     for (int i = 0; i < d->n_emitters; ++i) {
         const float kind = d->emitters[16 * i + 13];
-        LRT_REQUIRE(kind == 0.f || kind == 1.f || kind == 2.f, "emitter kind must be 0 (rectangle), 1 (mesh) or 2 (constant environment)");
+        LRT_REQUIRE(kind == 0.f || kind == 1.f || kind == 2.f || kind == 3.f, "emitter kind must be 0 (rectangle), 1 (mesh), 2 (constant environment) or 3 (disk)");
+        LRT_REQUIRE(kind != 3.f || d->emitters[16 * i + 14] == 1.f, "an emitter on a `disk` must be a `directionalarea` (plain `area` lights on disks are not built)");
         if (kind == 2.f) { LRT_REQUIRE(env < 0, "Only one environment emitter can be specified per scene."); env = i; }
         else LRT_REQUIRE(d->emitters[16 * i + 3] >= 0.f && d->emitters[16 * i + 3] < (float) d->n_shapes, "emitter shape id out of range");
     }
@@ -98,6 +100,14 @@ int lrt_scene_create(const lrt_scene_desc *d, lrt_scene **out) {
     for (int i = 0; i < d->n_emitters; ++i) if (d->emitters[16 * i + 14] == 1.f) s->has_directional = true;
     for (int i = 0; i < d->n_emitters; ++i)
         if (d->emitters[16 * i + 14] == 1.f && d->emitters[16 * i + 13] == 2.f) { set_error("a `directionalarea` emitter needs a shape"); delete s; return LRT_EINVAL; }
+    // analytic shapes: a disk's record carries to_world * Normal3f(0, 0, 1); normalised here as disk.cpp:122 does (float32, x * rsqrt)
+    std::vector<float> sph(d->spheres, d->spheres + (size_t) d->n_spheres * 32);
+    for (int k = 0; k < d->n_spheres; ++k) {
+        float *q = sph.data() + 32 * (size_t) k;
+        if (q[6] != 1.f) continue;
+        const float inv = 1.f / std::sqrt((q[0] * q[0] + q[1] * q[1]) + q[2] * q[2]);
+        q[0] *= inv; q[1] *= inv; q[2] *= inv;
+    }
     // emitters: 16-float rows -> 5 x float4 with the rectangle's normal and 1/area (rectangle.cpp:115-123)
     std::vector<float> em((size_t) d->n_emitters * 20, 0.f);
     std::vector<float> em_tris;     // 24 floats per triangle of a mesh emitter
@@ -129,6 +139,20 @@ int lrt_scene_create(const lrt_scene_desc *d, lrt_scene **out) {
         }
         o[4] = r[4]; o[5] = r[5]; o[6] = r[6];
         for (int k = 0; k < 3; ++k) { o[8 + k] = r[7 + k]; o[12 + k] = r[10 + k]; }
+        if (r[13] == 3.f) {   // on a `disk`: centre, dp_du, dp_dv = translation and the first two columns of to_world; the disk's own frame normal
+            const float *q = nullptr;
+            for (int k = 0; k < d->n_spheres; ++k) if (sph[32 * (size_t) k + 6] == 1.f && sph[32 * (size_t) k + 4] == r[3]) q = sph.data() + 32 * (size_t) k;
+            LRT_REQUIRE(q != nullptr, "emitter kind 3 needs a disk with its shape id");
+            o[16] = q[0]; o[17] = q[1]; o[18] = q[2];
+            // Disk::surface_area (disk.cpp:163-166): pi |dp_du| h, h = the height of dp_dv over dp_du
+            const float du = std::sqrt((r[7] * r[7] + r[8] * r[8]) + r[9] * r[9]), dv = std::sqrt((r[10] * r[10] + r[11] * r[11]) + r[12] * r[12]);
+            const float fs[3] = { r[7] * (1.f / du), r[8] * (1.f / du), r[9] * (1.f / du) }, idv = 1.f / dv;
+            const float ft[3] = { r[10] * idv * dv, r[11] * idv * dv, r[12] * idv * dv };
+            const float dt = (ft[0] * fs[0] + ft[1] * fs[1]) + ft[2] * fs[2];
+            const float hh = std::sqrt(dv * dv - dt * dt);
+            o[7] = 1.f / (3.14159265358979323846f * du * hh); o[19] = 3.f;
+            continue;
+        }
         float ex[3] = { r[7], r[8], r[9] }, ey[3] = { r[10], r[11], r[12] };
         float cx = ex[1] * ey[2] - ex[2] * ey[1], cy = ex[2] * ey[0] - ex[0] * ey[2], cz = ex[0] * ey[1] - ex[1] * ey[0];
         float len = std::sqrt(cx * cx + cy * cy + cz * cz);
@@ -166,7 +190,7 @@ int lrt_scene_create(const lrt_scene_desc *d, lrt_scene **out) {
         if ((rc = upload(&s->d_textures, tv.data(), tv.size()))) { lrt_scene_destroy(s); return rc; }
         s->n_textures = d->n_textures;
     }
-    if (d->n_spheres && (rc = upload(&s->d_spheres, d->spheres, (size_t) d->n_spheres * 32))) { lrt_scene_destroy(s); return rc; }
+    if (d->n_spheres && (rc = upload(&s->d_spheres, sph.data(), sph.size()))) { lrt_scene_destroy(s); return rc; }
     if (cudaMalloc(&s->d_counter, (kCounterRing + 8) * sizeof(unsigned long long)) != cudaSuccess) { lrt_scene_destroy(s); return cuda_fail(cudaGetLastError(), "cudaMalloc"); }
     s->view.bvh.nodes = (const uint4 *) s->d_nodes; s->view.bvh.tris = (const float4 *) s->d_tris;
     s->view.bvh.kb = 0x4B000000u; s->view.bvh.km = 0xfffffff8u;

@@ -114,6 +114,23 @@ static __device__ __noinline__ int spheres_intersect(const SceneView &sc, float3
     int best = -1;
     for (int k = 0; k < sc.n_spheres; ++k) {
         const float4 s0 = __ldg(sc.spheres + 8 * (size_t) k);
+        if (__ldg(sc.spheres + 8 * (size_t) k + 1).z == 1.f) {
+            // `disk` (disk.cpp:392-410, float32): the ray in object space meets z = 0 inside the unit circle
+            const float4 *sp = sc.spheres + 8 * (size_t) k;
+            const float4 m0 = __ldg(sp + 5), m1 = __ldg(sp + 6), m2 = __ldg(sp + 7);
+            auto xf = [](float4 m, float3 v, float w) {        // transform_affine: column by column, two roundings per step
+                float r = w != 0.f ? __fadd_rn(__fmul_rn(m.x, v.x), m.w) : __fmul_rn(m.x, v.x);
+                r = __fadd_rn(__fmul_rn(m.y, v.y), r);
+                return __fadd_rn(__fmul_rn(m.z, v.z), r);
+            };
+            const float oz = xf(m2, o, 1.f), dz = xf(m2, d, 0.f);
+            const float t = __fdiv_rn(-oz, dz);
+            const float lx = __fadd_rn(__fmul_rn(xf(m0, d, 0.f), t), xf(m0, o, 1.f)), ly = __fadd_rn(__fmul_rn(xf(m1, d, 0.f), t), xf(m1, o, 1.f));
+            if (!(t >= 0.f && t <= maxt_f && __fadd_rn(__fmul_rn(lx, lx), __fmul_rn(ly, ly)) <= 1.f)) continue;
+            if (best < 0 || t < t_out) { best = k; t_out = t; maxt_f = fminf(maxt_f, t); }
+            if (any_hit) break;
+            continue;
+        }
         const double radius = s0.w, cx = s0.x, cy = s0.y, cz = s0.z, maxt = maxt_f;
         const double lx = __dsub_rn((double) o.x, cx), ly = __dsub_rn((double) o.y, cy), lz = __dsub_rn((double) o.z, cz);
         const double dx = d.x, dy = d.y, dz = d.z;
@@ -186,6 +203,26 @@ static __device__ __noinline__ void sphere_surface(const SceneView &sc, int k, f
     const float4 *sp = sc.spheres + 8 * (size_t) k;
     const float4 s0 = __ldg(sp), s1 = __ldg(sp + 1);
     const float3 c = make_float3(s0.x, s0.y, s0.z);
+    if (s1.z == 1.f) {        // `disk`: Disk::compute_surface_interaction (disk.cpp:436-520, non-differentiable branch)
+        const float4 w0 = __ldg(sp + 2), w1 = __ldg(sp + 3), w2 = __ldg(sp + 4), m0 = __ldg(sp + 5), m1 = __ldg(sp + 6);
+        const float3 p = ray_o + ray_d * t, n = c;               // c: the frame normal
+        si.p = p + n * dot(make_float3(w0.w, w1.w, w2.w) - p, n);      // re-projected onto the disk's plane
+        const float3 od = make_float3(m0.z * ray_d.z + (m0.y * ray_d.y + m0.x * ray_d.x), m1.z * ray_d.z + (m1.y * ray_d.y + m1.x * ray_d.x), 0.f);
+        const float lx = od.x * t + (m0.z * ray_o.z + (m0.y * ray_o.y + (m0.x * ray_o.x + m0.w))),
+                    ly = od.y * t + (m1.z * ray_o.z + (m1.y * ray_o.y + (m1.x * ray_o.x + m1.w)));
+        const float r = sqrtf(lx * lx + ly * ly), inv_r = 1.f / r;
+        float v = atan2_drjit(ly, lx) * (.5f * kInvPi);
+        if (v < 0.f) v += 1.f;
+        si.uv = make_float2(r, v);
+        const float cp = r != 0.f ? lx * inv_r : 1.f, sn = r != 0.f ? ly * inv_r : 0.f;
+        const float3 dp_du = make_float3(w0.y * sn + w0.x * cp, w1.y * sn + w1.x * cp, w2.y * sn + w2.x * cp);
+        si.n = si.sn = n;
+        si.s = normalize(dp_du - n * dot(n, dp_du));
+        si.t = cross(n, si.s);
+        si.wi = si.to_local(-ray_d);
+        si.shape = (int) s1.x;
+        return;
+    }
     float3 n = normalize((ray_o + ray_d * t) - c);
     si.p = c + n * s0.w;                                         // re-projected onto the sphere
     const float4 w0 = __ldg(sp + 2), w1 = __ldg(sp + 3), w2 = __ldg(sp + 4), m0 = __ldg(sp + 5), m1 = __ldg(sp + 6), m2 = __ldg(sp + 7);

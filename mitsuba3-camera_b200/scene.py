@@ -347,6 +347,21 @@ class SceneData:
         self.spheres.append((sid, m[:3, 3].copy(), f32(radius), bool(flip_normals), m.copy(), to_world.inverse_matrix.copy()))
         return sid
 
+    def add_disk(self, name, to_world, bsdf_id, emitter=None):
+        """`disk` shape (src/shapes/disk.cpp): the unit disk of object space's xy plane, an analytic shape next to the spheres
+        (record: unnormalised frame normal, -, shape, -, kind 1, -, to_world rows, to_object rows). `emitter`: {"radiance", "directional"}."""
+        sid = self.add_shape(name, np.zeros((0, 3), f32), np.zeros((0, 3), np.int32), bsdf_id)
+        m, inv = to_world.matrix, to_world.inverse_matrix
+        n = inv[2, :3].astype(f32)             # to_world * Normal3f(0, 0, 1): the inverse transpose's third column; normalised by the library
+        self.spheres.append((sid, n, f32(0), False, m.copy(), inv.copy(), 1))
+        if emitter is not None:
+            row = np.zeros(16, f32); row[0:3] = emitter["radiance"]; row[3] = sid
+            row[4:7], row[7:10], row[10:13] = m[:3, 3], m[:3, 0], m[:3, 1]
+            row[13] = 3; row[14] = 1.0 if emitter.get("directional", False) else 0.0
+            row[15] = 1.0 if float(np.dot(np.cross(m[:3, 0].astype(np.float64), m[:3, 1].astype(np.float64)), n)) >= 0 else -1.0
+            self.emitter_rows.append(row); self.shape_emitter[sid] = len(self.emitter_rows) - 1
+        return sid
+
     def add_bsdf(self, name, row):
         self.bsdf_rows.append(np.asarray(row, f32)); self.bsdf_names.append(name)
         return len(self.bsdf_rows) - 1
@@ -376,7 +391,10 @@ class SceneData:
         for v in self.vertices:
             if len(v):
                 lo, hi = np.minimum(lo, v.min(0)), np.maximum(hi, v.max(0))
-        for _, c, r, _, _, _ in self.spheres:
+        for sp in self.spheres:
+            c, r, m = sp[1], sp[2], sp[4]
+            if len(sp) > 6:                                      # disk.cpp:149-161
+                c, r = m[:3, 3], np.sqrt(m[:3, 0] * m[:3, 0] + m[:3, 1] * m[:3, 1], dtype=f32)
             lo, hi = np.minimum(lo, (c - r).astype(f32)), np.maximum(hi, (c + r).astype(f32))
         if not np.all(lo <= hi):
             return np.zeros(3, f32), f32(1)
@@ -392,8 +410,10 @@ class SceneData:
             if row[13] == 2:
                 row[4:7], row[7] = self.bounding_sphere()
         sph = np.zeros((len(self.spheres), 32), f32)
-        for i, (sid, c, r, flip, m, minv) in enumerate(self.spheres):
+        for i, sp in enumerate(self.spheres):
+            sid, c, r, flip, m, minv = sp[:6]
             sph[i, 0:3], sph[i, 3], sph[i, 4], sph[i, 5] = c, r, sid, float(flip)
+            sph[i, 6] = float(sp[6]) if len(sp) > 6 else 0.0      # 1: a disk (then [0:3] is its frame normal)
             sph[i, 8:20] = m[:3].reshape(-1)
             sph[i, 20:32] = minv[:3].reshape(-1)      # m_to_object = m_to_world.inverse(): the transform's own float32 inverse
         return dict(spheres=sph, vertices=cat(self.vertices, f32, (0, 3)), indices=cat(self.indices, np.int32, (0, 3)),
@@ -849,7 +869,7 @@ def _sensor_from(d):
     return s
 
 
-_SHAPES = ("rectangle", "cube", "mesh", "obj", "ply", "sphere")
+_SHAPES = ("rectangle", "cube", "mesh", "obj", "ply", "sphere", "disk")
 _BSDFS = ("diffuse", "conductor", "dielectric", "dispersive", "twosided")
 
 
@@ -931,6 +951,20 @@ def scene_data_from_dict(d: dict):
                     sc = Transform4f(sc.matrix, np.diag(np.array([f32(1) / r32] * 3 + [f32(1)], f32)))                   # dr::rcp in float32
                     tw = tw.matmul32(tr).matmul32(sc)
                 data.add_sphere(name, tw, bid, v.get("flip_normals", False))
+                continue
+            if vt == "disk":
+                if v.get("flip_normals", False):
+                    tw = tw @ Transform4f(np.diag(np.array([1, 1, -1, 1], f32)))     # disk.cpp:99-101
+                demit = None
+                if em is not None:
+                    if em.get("type") != "directionalarea":
+                        raise ValueError("`area` emitters on `disk` shapes are outside the hot path of this build (use a rectangle or a "
+                                         "mesh); `directionalarea` — the notebooks' field sources — is built")
+                    rad = em.get("radiance")
+                    if isinstance(rad, dict) and rad.get("type") not in (None, "rgb", "spectrum", "uniform"):
+                        raise ValueError("emitters: only a constant radiance is built")
+                    demit = {"radiance": _rgb(rad, [1, 1, 1]), "directional": True}
+                data.add_disk(name, tw, bid, demit)
                 continue
             if v.get("flip_normals", False) and vt == "rectangle":
                 tw = tw @ Transform4f(np.diag(np.array([1, 1, -1, 1], f32)))     # rectangle.cpp:100-103

@@ -19,19 +19,45 @@ def mm32(a, b):
     return out
 
 
+def inverse_f32(m):
+    """Inverse of a float32 4x4 matrix with the operation order of the reference's own (Transform(matrix) ->
+    dr::inverse_transpose, ext/drjit/include/drjit/matrix.h:384-443: 2x2 sub-determinants of column pairs, cofactor rows, one
+    reciprocal of the determinant; every product and sum rounded to float32). Bit-exact against the pinned build on 201 matrices."""
+    m = np.asarray(m, f32).reshape(4, 4)
+    swap, half = [1, 0, 3, 2], [2, 3, 0, 1]
+    a, b, c, d = m[:, 0].copy(), m[half, 1], m[:, 2].copy(), m[half, 3]
+    mul = lambda x, y: (x * y).astype(f32)                                           # noqa: E731
+    t = mul(c, d)[swap]; r0 = mul(b, t); r1 = mul(a, t)
+    t = t[half]; r0 = mul(b, t) - r0; r1 = (mul(a, t) - r1)[half]
+    t = mul(b, c)[swap]; r0 = mul(d, t) + r0; r3 = mul(a, t)
+    t = t[half]; r0 = r0 - mul(d, t); r3 = (mul(a, t) - r3)[half]
+    t = mul(b[half], d)[swap]; c = c[half]; r0 = mul(c, t) + r0; r2 = mul(a, t)
+    t = t[half]; r0 = r0 - mul(c, t); r2 = (mul(a, t) - r2)[half]
+    t = mul(a, b)[swap]; r2 = mul(d, t) + r2; r3 = mul(c, t) - r3
+    t = t[half]; r2 = mul(d, t) - r2; r3 = r3 - mul(c, t)
+    t = mul(a, d)[swap]; r1 = r1 - mul(c, t); r2 = mul(b, t) + r2
+    t = t[half]; r1 = mul(c, t) + r1; r2 = r2 - mul(b, t)
+    t = mul(a, c)[swap]; r1 = mul(d, t) + r1; r3 = r3 - mul(b, t)
+    t = t[half]; r1 = r1 - mul(d, t); r3 = mul(b, t) + r3
+    p = mul(a, r0)
+    rdet = f32(1) / f32(f32(f32(p[0] + p[1]) + p[2]) + p[3])
+    return np.stack([r0 * rdet, r1 * rdet, r2 * rdet, r3 * rdet], 0).astype(f32)
+
+
 class Transform4f:
     """Carries the matrix AND its inverse, the latter built the way the reference builds it (transform.h:173-282): every
     constructor knows its exact inverse (translate(-v), scale(1/v), the transpose of a rotation, look_at's analytic inverse)
     and products multiply both sides. Scene descriptions are assembled in DOUBLE precision — the XML parser and `Properties`
     work with `Transform<Point<double, 4>>` (src/core/xml.cpp, include/mitsuba/core/properties.h) — and a plugin reads the
     result rounded once to float32, inverse included: `.matrix` / `.inverse_matrix` are those float32 arrays. A transform made
-    from a bare matrix gets a numerically inverted one."""
+    from a bare matrix gets the float32 cofactor inverse the reference computes for it (`inverse_f32`)."""
 
     def __init__(self, matrix=None, inverse=None):
         if isinstance(matrix, Transform4f):
             matrix, inverse = matrix.m64, (matrix.inv64 if inverse is None else inverse)
         self.m64 = np.eye(4) if matrix is None else np.array(getattr(matrix, "matrix", matrix), dtype=np.float64).reshape(4, 4)
-        self.inv64 = np.linalg.inv(self.m64) if inverse is None else np.array(inverse, dtype=np.float64).reshape(4, 4)
+        self.inv64 = (inverse_f32(self.m64.astype(f32)).astype(np.float64) if inverse is None
+                      else np.array(inverse, dtype=np.float64).reshape(4, 4))
         self.matrix = self.m64.astype(f32)
         self.inverse_matrix = self.inv64.astype(f32)
 

@@ -40,7 +40,8 @@ struct Emitter { V3 radiance; int shape; V3 c, ex, ey, n; float inv_area; int ki
 struct Rect { int shape; float M[12], Minv[12]; V3 dp_du, dp_dv, n; };                  // rows of the affine 3x4 matrices
 // kind 0 bitmap (wrap: 0 repeat 1 mirror 2 clamp); procedural: 1 checkerboard, 2 checkerlines, 3 comb2d, 4 polarlines
 struct Texture { int w, h, wrap; std::vector<float> data; float to_uv[6]; int kind = 0; V3 color0 { 0, 0, 0 }, color1 { 0, 0, 0 }; float linewidth = 0, spokes = 0; };
-struct Sphere { int shape; V3 center; float radius; bool flip; float M[12], Minv[12]; };   // rows of to_world / to_object
+struct Sphere { int shape; V3 center; float radius; bool flip; float M[12], Minv[12];      // rows of to_world / to_object
+                bool disk = false; V3 n { 0, 0, 1 }; };   // disk: src/shapes/disk.cpp — unit disk in the xy plane of object space, frame normal n
 
 struct BNode { V3 lo, hi; int left, right, first, count; };
 
@@ -212,6 +213,20 @@ static Hit intersect(const Scene &s, const Ray &ray, bool any_hit) {
     }
     for (size_t k = 0; k < s.spheres.size(); ++k) {
         float t;
+        if (s.spheres[k].disk) {
+            // disk.cpp:392-410 (float32): the ray in object space meets z = 0 inside the unit circle
+            const Sphere &dk = s.spheres[k];
+            V3 o = xf_point(dk.Minv, r.o), d = xf_vector(dk.Minv, r.d);
+            t = -o.z / d.z;
+            V3 local = fmadd3(d, t, o);
+            if (!(t >= 0.f && t <= r.maxt && local.x * local.x + local.y * local.y <= 1.f)) continue;
+            if (t < best.t) {
+                best.t = t; best.u = local.x; best.v = local.y; best.prim = -1; best.rect = -1; best.sphere = (int) k;
+                if (any_hit) return best;
+                r.maxt = t;
+            }
+            continue;
+        }
         if (sphere_intersect(s.spheres[k], r, t) && t < best.t) {
             best.t = t; best.u = best.v = 0.f; best.prim = -1; best.rect = -1; best.sphere = (int) k;
             if (any_hit) return best;
@@ -262,6 +277,24 @@ static SI surface_interaction(const Scene &s, const Ray &ray, const Hit &h) {
         si.uv = { fmadd(h.u, .5f, .5f), fmadd(h.v, .5f, .5f) };
         si.shape = rc.shape;
         finalize_si(si, rc.dp_du, ray);
+        return si;
+    }
+    if (h.sphere >= 0 && s.spheres[h.sphere].disk) {        // disk.cpp:436-520 (non-differentiable branch)
+        const Sphere &dk = s.spheres[h.sphere];
+        si.t = h.t;
+        V3 p = fmadd3(ray.d, h.t, ray.o);
+        V3 tr { dk.M[3], dk.M[7], dk.M[11] };
+        float dist = dot(tr - p, dk.n);
+        si.p = fmadd3(dk.n, dist, p);
+        float rr = std::sqrt(sqr(h.u) + sqr(h.v)), inv_r = rcp(rr);
+        float v = atan2_drjit(h.v, h.u) * (.5f * InvPi);
+        if (v < 0.f) v += 1.f;
+        si.uv = { rr, v };
+        float cos_phi = rr != 0.f ? h.u * inv_r : 1.f, sin_phi = rr != 0.f ? h.v * inv_r : 0.f;
+        V3 dp_du = xf_vector(dk.M, V3 { cos_phi, sin_phi, 0.f });
+        si.n = si.sh_n = dk.n;
+        si.shape = dk.shape;
+        finalize_si(si, dp_du, ray);
         return si;
     }
     if (h.sphere >= 0) {        // sphere.cpp:609-718 (non-differentiable branch)
@@ -710,6 +743,14 @@ void *orc_scene_create2(int nv, const float *verts, const float *normals, const 
             }
             e.sum = e.tris.back().cdf; e.inv_area = rcp(e.sum);
         }
+        if (r[13] == 3.f) {      // area / directionalarea on a `disk`: c, ex, ey = translation and first two columns of to_world; r[15] = sign of the frame normal
+            e.kind = 3;
+            V3 nn = normalize(cross(e.ex, e.ey)); e.n = r[15] < 0.f ? -nn : nn;
+            // Disk::surface_area (disk.cpp:163-166): pi * |dp_du| * h, h = the height of dp_dv over dp_du
+            float du = norm(e.ex), dv = norm(e.ey); V3 fs = e.ex * rcp(du), ft = e.ey * rcp(dv);
+            float hh = std::sqrt(sqr(dv) - sqr(dot(ft * dv, fs)));
+            e.inv_area = rcp(Pi * du * hh);
+        }
         e.directional = r[14] == 1.f;
         s->emitters.push_back(e);
     }
@@ -753,6 +794,10 @@ void orc_scene_set_spheres(void *h, int n, const int *shape_ids, const float *sp
     for (int i = 0; i < n; ++i) {
         Sphere sp; sp.shape = shape_ids[i]; const float *q = sph8 + 8 * i;
         sp.center = { q[0], q[1], q[2] }; sp.radius = q[3]; sp.flip = q[4] != 0.f;
+        if (q[5] == 1.f) {      // disk: q[0..2] = to_world * Normal3f(0, 0, 1), normalised here as disk.cpp:122 does (float32)
+            sp.disk = true; sp.n = normalize(sp.center);
+            for (Emitter &e : s->emitters) if (e.kind == 3 && e.shape == sp.shape) e.n = sp.n;
+        }
         std::memcpy(sp.M, to_world12 + 12 * i, 48); std::memcpy(sp.Minv, to_object12 + 12 * i, 48);
         s->spheres.push_back(sp);
     }

@@ -123,7 +123,11 @@ static void frame_from_normal(PtVertex &v, V3 n) { v.sh_n = n; coordinate_system
 // Emitter::sample_position for area lights (area.cpp:210-245): point, normal, 1 / pdf
 static void emitter_sample_position(const Emitter &e, V2 sample, V3 &p, V3 &n, float &weight) {
     if (e.kind == 1) mesh_sample_position(e, sample, p, n);
-    else {
+    else if (e.kind == 3) {      // Disk::sample_position (disk.cpp:173-190): concentric disk warp, to_world.transform_affine
+        V2 q = square_to_uniform_disk_concentric(sample);
+        p = { fmadd(e.ey.x, q.y, fmadd(e.ex.x, q.x, e.c.x)), fmadd(e.ey.y, q.y, fmadd(e.ex.y, q.x, e.c.y)), fmadd(e.ey.z, q.y, fmadd(e.ex.z, q.x, e.c.z)) };
+        n = e.n;
+    } else {
         float sx = sample.x * 2.f - 1.f, sy = sample.y * 2.f - 1.f;
         p = { fmadd(e.ey.x, sy, fmadd(e.ex.x, sx, e.c.x)), fmadd(e.ey.y, sy, fmadd(e.ex.y, sx, e.c.y)), fmadd(e.ey.z, sy, fmadd(e.ex.z, sx, e.c.z)) };
         n = e.n;

@@ -197,7 +197,7 @@ def orc_scene(a, analytic_rectangles=False, hide_emitters=False):
     sph = keep.get("spheres")
     if sph is not None and len(sph):
         L.orc_scene_set_spheres(h, C.c_int(len(sph)), ip(np.ascontiguousarray(sph[:, 4].astype(np.int32))),
-                                fp(np.ascontiguousarray(np.concatenate([sph[:, 0:4], sph[:, 5:6], np.zeros((len(sph), 3), f32)], 1), f32)),
+                                fp(np.ascontiguousarray(np.concatenate([sph[:, 0:4], sph[:, 5:6], sph[:, 6:7], np.zeros((len(sph), 2), f32)], 1), f32)),
                                 fp(np.ascontiguousarray(sph[:, 8:20])), fp(np.ascontiguousarray(sph[:, 20:32])))
     if any(t.get("kind", 0) for t in tex):
         kinds = np.array([t.get("kind", 0) for t in tex], np.int32)

@@ -198,7 +198,7 @@ def scene_dicts(T):
     return out
 
 
-def path_b_scene(T, spp=64, res=64):
+def path_b_scene(T, spp=64, res=64, source="rectangle"):
     """The notebooks' "Path B" in miniature (notebooks/scripts/lens_design/design_problem.py:46-120,355-428): a lens made of
     MESHES (the two caps of a singlet: icosphere caps whose vertex z follows the sag, smooth normals computed by the loader,
     `dielectric` BSDF), a `directionalarea` field source tilted by two degrees, a white diffuse film plane at z = 0, a
@@ -206,6 +206,8 @@ def path_b_scene(T, spp=64, res=64):
     assets = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "assets")
     white = {"type": "diffuse", "reflectance": {"type": "rgb", "value": [1.0, 1.0, 1.0]}}
     glass = {"type": "dielectric", "int_ior": 1.5168, "ext_ior": 1.000277}
+    # source="disk": the notebooks' own choice (design_problem.py:355-371), an elliptic one here (dp_du != dp_dv)
+    src_scale = [0.004, 0.004, 1.0] if source == "rectangle" else [0.0045, 0.0035, 1.0]
     return {
         "type": "scene", "integrator": {"type": "ptracer", "max_depth": 4, "hide_emitters": False},
         "sensor": {"type": "perspective", "fov": 30.0, "near_clip": 1e-3, "far_clip": 10.0,
@@ -218,7 +220,7 @@ def path_b_scene(T, spp=64, res=64):
         "lens_rear": {"type": "ply", "filename": os.path.join(assets, "cap_rear.ply"), "face_normals": False,
                       "bsdf": {"type": "dielectric", "int_ior": 1.000277, "ext_ior": 1.5168}},
         "lens_front": {"type": "ply", "filename": os.path.join(assets, "cap_front.ply"), "face_normals": False, "bsdf": glass},
-        "field_source": {"type": "rectangle",
-                         "to_world": T(mm(m_translate([0.0008, 0.0, 0.08]), m_rotate([0, 1, 0], 2.0), m_rotate([1, 0, 0], 180.0), m_scale([0.004, 0.004, 1.0]))),
+        "field_source": {"type": source,
+                         "to_world": T(mm(m_translate([0.0008, 0.0, 0.08]), m_rotate([0, 1, 0], 2.0), m_rotate([1, 0, 0], 180.0), m_scale(src_scale))),
                          "emitter": {"type": "directionalarea", "radiance": {"type": "rgb", "value": [3.0, 2.0, 1.0]}}},
     }

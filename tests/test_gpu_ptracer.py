@@ -219,3 +219,38 @@ def test_gpu_path_b_mesh_lens_directional_source_perspective_sensor(mi):
         mi.render(mi.load_dict(d2), spp=1)
     with pytest.raises(ValueError, match="realistic lens"):
         sc.integrator().render_backward_lens(sc, np.zeros((64, 64, 3), f32))
+
+
+@pytest.mark.gpu
+def test_gpu_disk_field_source(mi):
+    """`disk` (src/shapes/disk.cpp) as the notebooks use it — the carrier of a `directionalarea` field source
+    (design_problem.py:355-371): Scene::ray_intersect on an elliptic, tilted disk bit-exact against the reference's own vectors,
+    the particle tracer against the pinned oracle (default mode) and the reference's renders (scalar convention); a plain
+    `area` light on a disk is refused."""
+    import ref_scenes as rs
+    R = np.load(os.path.join(ROOT, "tests", "golden", "ref_disk.npz"))
+    d = rs.path_b_scene(lambda m: mi.Transform4f(m), source="disk")
+    sc = mi.load_dict(d)
+    o, dd, ref = R["isect_o"], R["isect_d"], R["isect"]
+    t, _, _, prim = sc.ray_intersect(o, dd)
+    t = t.cpu().numpy(); prim = prim.cpu().numpy()
+    hit = np.isfinite(ref[:, 0])
+    assert (np.isfinite(t) == hit).all()
+    dk = hit & (ref[:, 21] == sc.data.shape_names.index("field_source"))
+    assert dk.sum() > 500 and (prim[dk] == -2).all() and (prim[hit & ~dk] >= 0).all()
+    bits = lambda x: np.ascontiguousarray(x, f32).view(np.uint32)   # noqa: E731
+    assert (bits(t[dk]) == bits(ref[dk, 0])).all()
+    img = mi.render(sc, seed=5).cpu().numpy()
+    want = oracle_ptracer(mi, d, 5, 8, scalar=False)
+    err = rel_rmse(img, want)
+    print(f"disk source, default mode: rel-RMSE vs oracle {err:.3e}, mean {img.mean():.5f} / {want.mean():.5f}")
+    assert err <= 2e-3 and abs(img.mean() / want.mean() - 1) <= 2e-3
+    for seed in (0, 3):
+        img = sc.integrator().render(sc, seed=seed, rng_mode=1, n_threads=int(R["n_threads"])).cpu().numpy()
+        refi = R[f"image_seed{seed}"]
+        close = np.abs(img - refi).max(-1) <= 1e-4 * np.maximum(refi.max(-1), 1e-3)
+        print(f"disk source, scalar convention, seed {seed}: rel-RMSE vs the reference's image {rel_rmse(img, refi):.3e}, within 1e-4: {close.mean():.4f}")
+        assert close.mean() >= 0.95 and abs(img.mean() / refi.mean() - 1) <= 1e-2
+    d2 = dict(d); d2["field_source"] = dict(d["field_source"]); d2["field_source"]["emitter"] = {"type": "area", "radiance": {"type": "rgb", "value": [1, 1, 1]}}
+    with pytest.raises(ValueError, match="disk"):
+        mi.load_dict(d2)

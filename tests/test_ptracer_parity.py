@@ -90,3 +90,39 @@ def test_path_b_oracle_vs_reference_images(mi):
         close = np.abs(img - ref).max(-1) <= 1e-4 * np.maximum(ref.max(-1), 1e-3)
         print(f"path B seed {seed}: rel-RMSE {err:.3e}, pixels within 1e-4: {close.mean():.4f}, mean {img.mean():.5f} / {ref.mean():.5f}")
         assert err <= 2e-3 and close.mean() >= 0.97
+
+
+# ------------------------------------------------------------------------------------------------ `disk` (the notebooks' field sources)
+def test_disk_oracle_vs_reference(mi):
+    """src/shapes/disk.cpp as the carrier of a `directionalarea` source (path_b_scene(source="disk"); gen_ref_disk.py):
+    Scene::ray_intersect on an elliptic, tilted disk bit-exact (t, p, normals, shading frame, uv, wi),
+    and the particle tracer's images — Disk::sample_position through DirectionalArea::sample_ray — in the scalar convention."""
+    import ctypes as C
+    import ref_scenes as rs
+    from oracle_lib import fp, oracle, orc_scene
+    R = np.load(os.path.join(HERE, "golden", "ref_disk.npz"))
+    d = rs.path_b_scene(lambda m: mi.Transform4f(m), source="disk")
+    data, _, _ = mi.scene.scene_data_from_dict(d)
+    a = data.arrays()
+    assert len(a["spheres"]) == 1 and a["spheres"][0, 6] == 1 and a["emitters"][0, 13] == 3 and a["emitters"][0, 14] == 1
+    h = orc_scene(a, analytic_rectangles=True)
+    o, dd, ref = R["isect_o"], R["isect_d"], R["isect"]
+    n = len(o)
+    od = np.ascontiguousarray(np.concatenate([o, dd, np.full((n, 1), 3.4e38, np.float32)], 1), np.float32)
+    out = np.zeros((n, 25), np.float32)
+    oracle().orc_scene_interaction(h, C.c_int64(n), fp(od), fp(out))
+    hit = np.isfinite(ref[:, 0])
+    assert (hit == np.isfinite(out[:, 0])).all() and (ref[hit, 21] == out[hit, 21]).all()
+    dk = hit & (ref[:, 21] == data.shape_names.index("field_source"))
+    assert dk.sum() > 500
+    bits = lambda x: np.ascontiguousarray(x, np.float32).view(np.uint32)   # noqa: E731
+    assert (bits(out[dk, 0:16]) == bits(ref[dk, 0:16])).all()                       # t, p, n, shading frame
+    assert (bits(out[dk, 18:21]) == bits(ref[dk, 18:21])).all()                     # wi
+    assert (bits(out[dk, 16:18]) == bits(ref[dk, 16:18])).all()                     # uv = (r, phi / 2 pi)
+    for seed in (0, 3):
+        img = oracle_ptracer(mi, d, seed, int(R["n_threads"]))
+        refi = R[f"image_seed{seed}"]
+        err = rel_rmse(img, refi)
+        close = np.abs(img - refi).max(-1) <= 1e-4 * np.maximum(refi.max(-1), 1e-3)
+        print(f"disk source seed {seed}: rel-RMSE {err:.3e}, pixels within 1e-4: {close.mean():.4f}, mean {img.mean():.5f} / {refi.mean():.5f}")
+        assert err <= 2e-3 and close.mean() >= 0.97
