@@ -223,7 +223,11 @@ typedef struct lrt_scene_desc {
     /* Analytic `sphere` shapes (src/shapes/sphere.cpp), intersected in double precision like the reference's scalar variants
      * and kept outside the BVH (tested one by one: meant for the handful of spheres scene files use). 32 floats each:
      * centre xyz, radius, shape id, flip_normals, 0, 0, then the three rows of to_world (12) and of to_object (12): the
-     * spherical parameterisation (si.uv, dp_du) lives in object space. Such shapes own no triangles. */
+     * spherical parameterisation (si.uv, dp_du) lives in object space. Such shapes own no triangles.
+     * A `disk` (src/shapes/disk.cpp: the unit disk of object space's xy plane, float32 like the reference) rides in the same
+     * table: floats [0..2] = to_world * Normal3f(0, 0, 1) (normalised by the library, disk.cpp:122), [3] = 0, [4] = shape id,
+     * [6] = 1, then the same two matrices. An emitter on it is an emitter row of kind 3 ([13] = 3: [4..6] = the translation,
+     * [7..9] and [10..12] = the first two columns of to_world), `directionalarea` only ([14] = 1). */
     int32_t n_spheres; const float *spheres;
 } lrt_scene_desc;
 
