@@ -227,7 +227,7 @@ typedef struct lrt_scene_desc {
      * A `disk` (src/shapes/disk.cpp: the unit disk of object space's xy plane, float32 like the reference) rides in the same
      * table: floats [0..2] = to_world * Normal3f(0, 0, 1) (normalised by the library, disk.cpp:122), [3] = 0, [4] = shape id,
      * [6] = 1, then the same two matrices. An emitter on it is an emitter row of kind 3 ([13] = 3: [4..6] = the translation,
-     * [7..9] and [10..12] = the first two columns of to_world), `directionalarea` only ([14] = 1). */
+     * [7..9] and [10..12] = the first two columns of to_world), an `area` light or a `directionalarea` ([14] = 1). */
     int32_t n_spheres; const float *spheres;
 } lrt_scene_desc;
 

@@ -52,7 +52,6 @@ int lrt_scene_create(const lrt_scene_desc *d, lrt_scene **out) {
     for (int i = 0; i < d->n_emitters; ++i) {
         const float kind = d->emitters[16 * i + 13];
         LRT_REQUIRE(kind == 0.f || kind == 1.f || kind == 2.f || kind == 3.f, "emitter kind must be 0 (rectangle), 1 (mesh), 2 (constant environment) or 3 (disk)");
-        LRT_REQUIRE(kind != 3.f || d->emitters[16 * i + 14] == 1.f, "an emitter on a `disk` must be a `directionalarea` (plain `area` lights on disks are not built)");
         if (kind == 2.f) { LRT_REQUIRE(env < 0, "Only one environment emitter can be specified per scene."); env = i; }
         else LRT_REQUIRE(d->emitters[16 * i + 3] >= 0.f && d->emitters[16 * i + 3] < (float) d->n_shapes, "emitter shape id out of range");
     }

@@ -430,7 +430,11 @@ template <bool kAttr = true, bool kAnalytic = kAttr> LRT_D EmitterSample sample_
         return es;
     }
     if (kAttr && e4.w == 1.f) mesh_emitter_sample_position(sc, e1, sx, sy, es.p, es.n);
-    else {
+    else if (kAnalytic && e4.w == 3.f) {      // on a `disk`: Disk::sample_position (disk.cpp:173-190), concentric warp
+        float qx, qy; square_to_disk_concentric(sx, sy, qx, qy);
+        es.p = make_float3(e1.x, e1.y, e1.z) + make_float3(e2.x, e2.y, e2.z) * qx + make_float3(e3.x, e3.y, e3.z) * qy;
+        es.n = make_float3(e4.x, e4.y, e4.z);
+    } else {
         float ux = sx * 2.f - 1.f, uy = sy * 2.f - 1.f;
         es.p = make_float3(e1.x, e1.y, e1.z) + make_float3(e2.x, e2.y, e2.z) * ux + make_float3(e3.x, e3.y, e3.z) * uy;
         es.n = make_float3(e4.x, e4.y, e4.z);

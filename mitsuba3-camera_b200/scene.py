@@ -957,13 +957,12 @@ def scene_data_from_dict(d: dict):
                     tw = tw @ Transform4f(np.diag(np.array([1, 1, -1, 1], f32)))     # disk.cpp:99-101
                 demit = None
                 if em is not None:
-                    if em.get("type") != "directionalarea":
-                        raise ValueError("`area` emitters on `disk` shapes are outside the hot path of this build (use a rectangle or a "
-                                         "mesh); `directionalarea` — the notebooks' field sources — is built")
+                    if em.get("type") not in ("area", "directionalarea"):
+                        raise ValueError(f"emitter `{em.get('type')}` on a disk: only `area` and `directionalarea` are built")
                     rad = em.get("radiance")
                     if isinstance(rad, dict) and rad.get("type") not in (None, "rgb", "spectrum", "uniform"):
                         raise ValueError("emitters: only a constant radiance is built")
-                    demit = {"radiance": _rgb(rad, [1, 1, 1]), "directional": True}
+                    demit = {"radiance": _rgb(rad, [1, 1, 1]), "directional": em.get("type") == "directionalarea"}
                 data.add_disk(name, tw, bid, demit)
                 continue
             if v.get("flip_normals", False) and vt == "rectangle":

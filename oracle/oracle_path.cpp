@@ -502,7 +502,12 @@ static bool emitter_sample_direction(const Emitter &e, V3 ref_p, V2 sample, DS &
         return true;
     }
     if (e.kind == 1) mesh_sample_position(e, sample, ds.p, ds.n);
-    else {
+    else if (e.kind == 3) {     // Disk::sample_position (disk.cpp:173-190) under the default Shape::sample_direction
+        V2 q = square_to_uniform_disk_concentric(sample);
+        ds.p = { fmadd(e.ey.x, q.y, fmadd(e.ex.x, q.x, e.c.x)), fmadd(e.ey.y, q.y, fmadd(e.ex.y, q.x, e.c.y)),
+                 fmadd(e.ey.z, q.y, fmadd(e.ex.z, q.x, e.c.z)) };
+        ds.n = e.n;
+    } else {
         float sx = sample.x * 2.f - 1.f, sy = sample.y * 2.f - 1.f;
         // to_world.transform_affine(Point3f(sx, sy, 0)): fmadd chain over the matrix columns (ex, ey, -, c)
         ds.p = { fmadd(e.ey.x, sy, fmadd(e.ex.x, sx, e.c.x)), fmadd(e.ey.y, sy, fmadd(e.ex.y, sx, e.c.y)),

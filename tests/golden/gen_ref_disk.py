@@ -4,7 +4,9 @@ shape (src/shapes/disk.cpp) as the notebooks use it — the carrier of a `direct
 
   * `isect`: Scene::ray_intersect of rays aimed at and around the (elliptic, tilted) disk, from both sides — t, p, normals,
     shading frame, uv, wi, shape (the layout of ref_xml.npz's charts/isect);
-  * `image_seed{0,3}`: the particle tracer's renders (Disk::sample_position through DirectionalArea::sample_ray).
+  * `image_seed{0,3}`: the particle tracer's renders (Disk::sample_position through DirectionalArea::sample_ray);
+  * `em_*`, `lamp_image_seed{0,3}`: an `area` light on a disk (ref_scenes.disk_light_scene) — Scene::sample_emitter_direction /
+    pdf_emitter_direction on 2048 reference points and the path tracer's renders.
 
     R=baseline/_ref/pinned/python; LD_LIBRARY_PATH=$R/mitsuba:$R/drjit PYTHONPATH=$R python tests/golden/gen_ref_disk.py"""
 import os
@@ -44,6 +46,24 @@ def main():
         img = np.array(mi.render(scene, seed=seed), dtype=f32)
         out[f"image_seed{seed}"] = img
         print("seed", seed, img.shape, float(img.mean()), float(img.max()), "lit pixels", int((img.sum(-1) > 0).sum()))
+    # ---- an `area` light on a disk: Scene::sample_emitter_direction / pdf_emitter_direction and the path tracer's render
+    scene = mi.load_dict(rs.disk_light_scene(T))
+    emitters = list(scene.emitters()); em_ids = [e.shape().id() for e in emitters]
+    n = 2048
+    ref_p = np.stack([rng.uniform(-1.8, 1.8, n), rng.uniform(0.0, 2.4, n), rng.uniform(-1.4, 1.8, n)], 1).astype(f32)
+    smp = rng.random((n, 2)).astype(f32)
+    rows = np.zeros((n, 16), f32)
+    for i in range(n):
+        it = mi.SurfaceInteraction3f(); it.p = [float(x) for x in ref_p[i]]; it.n = [0, 0, 1]; it.t = 1.0
+        ds, w = scene.sample_emitter_direction(it, [float(smp[i, 0]), float(smp[i, 1])], False)
+        pdf2 = scene.pdf_emitter_direction(it, ds) if ds.pdf > 0 else 0.0
+        rows[i] = [*ds.p, *ds.n, *ds.d, ds.dist, ds.pdf, *w, pdf2, em_ids.index(ds.emitter.shape().id()) if ds.pdf > 0 else -1]
+    out["em_ref_p"], out["em_sample"], out["em_dir"], out["em_ids"] = ref_p, smp, rows, np.array(em_ids)
+    print("emitter samples: on the disk", int((rows[:, 15] == em_ids.index("lamp")).sum()), "valid", int((rows[:, 15] >= 0).sum()))
+    for seed in (0, 3):
+        img = np.array(mi.render(scene, seed=seed), dtype=f32)
+        out[f"lamp_image_seed{seed}"] = img
+        print("lamp seed", seed, float(img.mean()), float(img.max()))
     np.savez_compressed(os.path.join(HERE, "ref_disk.npz"), **out)
 
 

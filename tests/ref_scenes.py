@@ -224,3 +224,24 @@ def path_b_scene(T, spp=64, res=64, source="rectangle"):
                          "to_world": T(mm(m_translate([0.0008, 0.0, 0.08]), m_rotate([0, 1, 0], 2.0), m_rotate([1, 0, 0], 180.0), m_scale(src_scale))),
                          "emitter": {"type": "directionalarea", "radiance": {"type": "rgb", "value": [3.0, 2.0, 1.0]}}},
     }
+
+
+def disk_light_scene(T, spp=16, res=64):
+    """An `area` light on an elliptic, tilted `disk` (src/shapes/disk.cpp + src/emitters/area.cpp) over a diffuse floor and a
+    back wall, next to a rectangle light; perspective sensor, `path` integrator."""
+    grey = {"type": "diffuse", "reflectance": {"type": "rgb", "value": [0.7, 0.6, 0.5]}}
+    return {
+        "type": "scene", "integrator": {"type": "path", "max_depth": 3},
+        "sensor": {"type": "perspective", "fov": 50.0, "near_clip": 1e-2, "far_clip": 100.0,
+                   "to_world": T(m_look_at([0, 1.2, 3.2], [0, 0.5, 0], [0, 1, 0])),
+                   "sampler": {"type": "independent", "sample_count": spp},
+                   "film": {"type": "hdrfilm", "width": res, "height": res, "rfilter": {"type": "tent"}, "pixel_format": "rgb",
+                            "component_format": "float32"}},
+        "floor": {"type": "rectangle", "to_world": T(mm(m_rotate([1, 0, 0], -90.0), m_scale([2.0, 2.0, 1.0]))), "bsdf": grey},
+        "wall": {"type": "rectangle", "to_world": T(mm(m_translate([0, 1.0, -1.5]), m_scale([2.0, 1.0, 1.0]))), "bsdf": grey},
+        "lamp": {"type": "disk",
+                 "to_world": T(mm(m_translate([0.3, 1.6, 0.2]), m_rotate([0, 0, 1], 12.0), m_rotate([1, 0, 0], 90.0), m_scale([0.5, 0.3, 1.0]))),
+                 "emitter": {"type": "area", "radiance": {"type": "rgb", "value": [6.0, 5.0, 4.0]}}},
+        "panel": {"type": "rectangle", "to_world": T(mm(m_translate([-1.2, 0.8, 0.0]), m_rotate([0, 1, 0], 90.0), m_scale([0.3, 0.3, 1.0]))),
+                  "emitter": {"type": "area", "radiance": {"type": "rgb", "value": [2.0, 3.0, 4.0]}}},
+    }

@@ -126,3 +126,40 @@ def test_disk_oracle_vs_reference(mi):
         close = np.abs(img - refi).max(-1) <= 1e-4 * np.maximum(refi.max(-1), 1e-3)
         print(f"disk source seed {seed}: rel-RMSE {err:.3e}, pixels within 1e-4: {close.mean():.4f}, mean {img.mean():.5f} / {refi.mean():.5f}")
         assert err <= 2e-3 and close.mean() >= 0.97
+
+
+def test_disk_area_light_oracle_vs_reference(mi):
+    """An `area` light on a disk (ref_scenes.disk_light_scene; the default Shape::sample_direction over Disk::sample_position):
+    Scene::sample_emitter_direction / pdf_emitter_direction on 2048 reference points — sampled point and normal bit-exact."""
+    import ctypes as C
+    import ref_scenes as rs
+    from oracle_lib import fp, oracle, orc_scene
+    from test_ref_parity import oracle_scalar_render
+    R = np.load(os.path.join(HERE, "golden", "ref_disk.npz"))
+    d = rs.disk_light_scene(lambda m: mi.Transform4f(m))
+    data, _, _ = mi.scene.scene_data_from_dict(d)
+    a = data.arrays()
+    assert sorted(a["emitters"][:, 13].tolist()) == [0.0, 3.0] and (a["emitters"][:, 14] == 0).all()
+    h = orc_scene(a, analytic_rectangles=True)
+    p = np.ascontiguousarray(R["em_ref_p"]); s2 = np.ascontiguousarray(R["em_sample"])
+    out = np.zeros((len(p), 16), np.float32)
+    oracle().orc_scene_sample_emitter(h, C.c_int64(len(p)), fp(p), fp(s2), fp(out))
+    er = R["em_dir"]
+    em_names = [data.shape_names[int(e[3])] for e in a["emitters"]]
+    ref_idx = np.array([em_names.index(str(R["em_ids"][int(x)])) if x >= 0 else -1 for x in er[:, 15]])
+    bits = lambda x: np.ascontiguousarray(x, np.float32).view(np.uint32)   # noqa: E731
+    lamp = ref_idx == em_names.index("lamp")
+    assert lamp.sum() > 900 and (out[lamp, 15] == ref_idx[lamp]).all()
+    assert (bits(out[lamp, :6]) == bits(er[lamp, :6])).all()                          # sampled point and normal
+    # direction, distance, weight, pdf(): one ulp of the normalised direction; the solid-angle pdf amplifies it at grazing angles
+    assert np.allclose(out[lamp, 6:15], er[lamp, 6:15], rtol=1e-5, atol=1e-7)
+    assert np.allclose(out[lamp, 11:14], er[lamp, 11:14], rtol=1.5e-6, atol=1e-7) and (out[lamp, 9] == er[lamp, 9]).all()
+    assert (er[lamp, 10] > 0).sum() > 300                                             # points below the lamp see it
+    # the render: a statistical check only. This scene's camera (look_at from above, fov 50) is not reproduced sample for sample
+    # by the scalar-convention harness — with or without the disk in the scene (the same holds with the lamp deleted), so the
+    # per-function vectors above are what pins the disk light; the image means agree within the Monte Carlo noise.
+    for seed in (0, 3):
+        img, _ = oracle_scalar_render(mi, d, 16, seed=seed, analytic=True)
+        ref = R[f"lamp_image_seed{seed}"]
+        print(f"disk lamp seed {seed}: mean {img.mean():.5f} / {ref.mean():.5f}")
+        assert abs(img.mean() / ref.mean() - 1) <= 0.03
